@@ -1,0 +1,160 @@
+"""ctypes mirror of include/ohcu.h — the C ABI structs and the libohcu.so loader.
+
+The product is the shared library; this module only describes its ABI to Python
+(tests, bench.py, smoke).  There is no Python or CPU fallback: ``load()`` raises
+if the CUDA library is missing.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libohcu.so")
+
+OHCU_ABI_VERSION = 1
+MAX_REFS = 16
+MAX_DPB = 32
+MAX_SLICES = 64
+
+PF_L0, PF_L1, PF_BI = 1, 2, 3
+SAO_NOT_APPLIED, SAO_BAND, SAO_EDGE = 0, 1, 2
+TU_IDCT, TU_DC, TU_DST4, TU_SKIP, TU_BYPASS = 0, 1, 2, 3, 4
+TUF_RDPCM, TUF_RDPCM_VERT, TUF_ROTATE, TUF_CROSS = 1, 2, 4, 8
+STAGE_MC, STAGE_RESIDUAL, STAGE_DEBLOCK, STAGE_SAO, STAGE_TOTAL, NUM_STAGES = 0, 1, 2, 3, 4, 5
+
+ERRORS = {0: "OK", -1: "EINVAL", -2: "ENOMEM", -3: "ECUDA", -4: "ESTATE", -5: "ENODEV", -6: "EOVERFLOW"}
+
+
+class SeqParams(C.Structure):
+    _fields_ = [
+        ("width", C.c_int32), ("height", C.c_int32), ("bit_depth", C.c_int32),
+        ("chroma_format_idc", C.c_int32), ("log2_ctb_size", C.c_int32),
+        ("log2_min_cb_size", C.c_int32), ("log2_min_pu_size", C.c_int32),
+        ("dpb_slots", C.c_int32), ("jobs", C.c_int32), ("sao_enabled", C.c_int32),
+        ("pcm_or_bypass", C.c_int32), ("cb_qp_offset", C.c_int32), ("cr_qp_offset", C.c_int32),
+        ("no_tile_filter", C.c_int32), ("max_pus", C.c_int32), ("max_tus", C.c_int32),
+        ("max_coeffs", C.c_int64),
+    ]
+
+
+class SliceTab(C.Structure):
+    _fields_ = [
+        ("ref_slot", (C.c_uint8 * MAX_REFS) * 2),
+        ("weight_flag", C.c_uint8), ("luma_log2_weight_denom", C.c_uint8),
+        ("chroma_log2_weight_denom", C.c_uint8), ("pad", C.c_uint8),
+        ("luma_weight", (C.c_int16 * MAX_REFS) * 2),
+        ("luma_offset", (C.c_int16 * MAX_REFS) * 2),
+        ("chroma_weight", ((C.c_int16 * 2) * MAX_REFS) * 2),
+        ("chroma_offset", ((C.c_int16 * 2) * MAX_REFS) * 2),
+    ]
+
+
+class PU(C.Structure):
+    _fields_ = [
+        ("x0", C.c_uint16), ("y0", C.c_uint16), ("w", C.c_uint8), ("h", C.c_uint8),
+        ("pred_flag", C.c_uint8), ("slice", C.c_uint8),
+        ("mv", (C.c_int16 * 2) * 2), ("ref_idx", C.c_uint8 * 2), ("pad", C.c_uint8 * 2),
+    ]
+
+
+class TU(C.Structure):
+    _fields_ = [
+        ("x0", C.c_uint16), ("y0", C.c_uint16), ("c_idx", C.c_uint8), ("log2_size", C.c_uint8),
+        ("mode", C.c_uint8), ("flags", C.c_uint8), ("col_limit", C.c_int8),
+        ("res_scale_val", C.c_int8), ("pad", C.c_uint16), ("coeff_off", C.c_uint32),
+        ("cross_tu", C.c_uint32),
+    ]
+
+
+class DBParams(C.Structure):
+    _fields_ = [("beta_offset", C.c_int8), ("tc_offset", C.c_int8)]
+
+
+class SAO(C.Structure):
+    _fields_ = [
+        ("type_idx", C.c_uint8 * 3), ("eo_class", C.c_uint8 * 3), ("band_position", C.c_uint8 * 3),
+        ("pad", C.c_uint8), ("offset_val", (C.c_int16 * 5) * 3),
+    ]
+
+
+class DeblockIn(C.Structure):
+    _fields_ = [
+        ("vertical_bs", C.c_void_p), ("horizontal_bs", C.c_void_p), ("qp_y_tab", C.c_void_p),
+        ("deblock", C.c_void_p), ("is_pcm", C.c_void_p),
+    ]
+
+
+class SaoIn(C.Structure):
+    _fields_ = [
+        ("sao", C.c_void_p), ("filter_slice_edges", C.c_void_p),
+        ("tab_slice_address", C.c_void_p), ("tile_id", C.c_void_p),
+    ]
+
+
+assert C.sizeof(PU) == 20 and C.sizeof(TU) == 20 and C.sizeof(SAO) == 40 and C.sizeof(DBParams) == 2
+
+# name -> (restype, argtypes); every symbol include/ohcu.h declares
+_P = C.c_void_p
+SYMBOLS = {
+    "ohcu_abi_version": (C.c_int, []),
+    "ohcu_last_error": (C.c_char_p, []),
+    "ohcu_device_count": (C.c_int, []),
+    "ohcu_create": (C.c_int, [C.POINTER(_P), C.c_int, C.POINTER(SeqParams)]),
+    "ohcu_destroy": (C.c_int, [_P]),
+    "ohcu_get_seq_params": (C.c_int, [_P, C.POINTER(SeqParams)]),
+    "ohcu_slot_upload": (C.c_int, [_P, C.c_int, C.POINTER(_P * 3), C.POINTER(C.c_ssize_t * 3)]),
+    "ohcu_slot_download": (C.c_int, [_P, C.c_int, C.POINTER(_P * 3), C.POINTER(C.c_ssize_t * 3)]),
+    "ohcu_slot_download_async": (C.c_int, [_P, C.c_int, C.POINTER(_P * 3), C.POINTER(C.c_ssize_t * 3)]),
+    "ohcu_slot_sync": (C.c_int, [_P, C.c_int]),
+    "ohcu_frame_begin": (C.c_int, [_P, C.c_int, C.c_int]),
+    "ohcu_set_slice": (C.c_int, [_P, C.c_int, C.c_int, C.POINTER(SliceTab)]),
+    "ohcu_append_pu": (C.c_int, [_P, C.c_int, _P, C.c_int]),
+    "ohcu_append_tu": (C.c_int, [_P, C.c_int, _P, C.c_int, _P, C.c_size_t]),
+    "ohcu_reserve_coeffs": (C.c_int, [_P, C.c_int, C.c_size_t, C.POINTER(_P), C.POINTER(C.c_uint32)]),
+    "ohcu_append_tu_inplace": (C.c_int, [_P, C.c_int, _P, C.c_int]),
+    "ohcu_set_deblock": (C.c_int, [_P, C.c_int, C.POINTER(DeblockIn)]),
+    "ohcu_set_sao": (C.c_int, [_P, C.c_int, C.POINTER(SaoIn)]),
+    "ohcu_frame_flush": (C.c_int, [_P, C.c_int]),
+    "ohcu_frame_stage": (C.c_int, [_P, C.c_int]),
+    "ohcu_frame_launch": (C.c_int, [_P, C.c_int, C.c_int]),
+    "ohcu_frame_sync": (C.c_int, [_P, C.c_int]),
+    "ohcu_sync_all": (C.c_int, [_P]),
+    "ohcu_set_profiling": (C.c_int, [_P, C.c_int]),
+    "ohcu_job_stage_ms": (C.c_int, [_P, C.c_int, C.POINTER(C.c_float * NUM_STAGES)]),
+    "ohcu_kernel_launches": (C.c_int64, [_P]),
+    "ohcu_job_stream": (_P, [_P, C.c_int]),
+    "ohcu_flush_l2": (C.c_int, [_P]),
+}
+
+_lib = None
+
+
+def load():
+    """dlopen hevc_b200/libohcu.so and type every entry point.  Raises if absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a).  There is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)          # AttributeError = ABI mismatch, fail loudly
+        fn.restype = res
+        fn.argtypes = args
+    if lib.ohcu_abi_version() != OHCU_ABI_VERSION:
+        raise RuntimeError("libohcu.so ABI version mismatch")
+    _lib = lib
+    return lib
+
+
+class OhcuError(RuntimeError):
+    pass
+
+
+def check(rc, what=""):
+    if rc < 0:
+        lib = load()
+        msg = lib.ohcu_last_error()
+        raise OhcuError(f"{what}: {ERRORS.get(rc, rc)}: {msg.decode() if msg else ''}")
+    return rc

@@ -1,0 +1,276 @@
+/*
+ * ohcu.h — C ABI of the B200-native HEVC pixel-reconstruction backend.
+ *
+ * This is the drop-in boundary for the reference decoder's HEVCDSPContext hot
+ * path (reference: libavcodec/hevcdsp.h:51-166, filled by ff_hevc_dsp_init,
+ * libavcodec/hevcdsp.c:311-587).  The reference calls the table once per block
+ * (PU / TU / 8-sample edge / CTB); this ABI is one level up: the decoder's C
+ * control plane appends per-frame work lists and the library runs them as
+ * batched sm_100a launches over a device-resident DPB.
+ *
+ * Plain C, plain pointers and sizes.  No torch / C++ types cross this line.
+ * Every entry point returns 0 on success or a negative OHCU_E* code; nothing
+ * aborts or throws across the ABI (the reference table returns void and cannot
+ * fail; CUDA errors surface at flush/sync).
+ */
+#ifndef OHCU_H
+#define OHCU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OHCU_ABI_VERSION 1
+
+/* ---- error codes -------------------------------------------------------- */
+#define OHCU_OK          0
+#define OHCU_EINVAL     -1   /* bad argument / unsupported parameter          */
+#define OHCU_ENOMEM     -2   /* host or device allocation failed              */
+#define OHCU_ECUDA      -3   /* CUDA runtime error (see ohcu_last_error)      */
+#define OHCU_ESTATE     -4   /* call out of order (e.g. append before begin)  */
+#define OHCU_ENODEV     -5   /* no usable sm_100 device                       */
+#define OHCU_EOVERFLOW  -6   /* work list larger than the job's arena         */
+
+/* ---- constants mirrored from the reference ------------------------------ */
+#define OHCU_MAX_PB_SIZE   64   /* MAX_PB_SIZE, hevcdec.h:51 (int16 tmp stride) */
+#define OHCU_MAX_TB_SIZE   32   /* MAX_TB_SIZE, hevcdec.h:50                    */
+#define OHCU_MAX_DPB       32   /* HEVCContext.DPB[32], hevcdec.h:590           */
+#define OHCU_MAX_REFS      16   /* luma_weight_l0[16], hevc_ps.h:210            */
+#define OHCU_MAX_SLICES    64   /* MAX_SLICES_IN_FRAME, hevcdec.h:361           */
+
+/* PredFlag, hevcdec.h:202-207 */
+#define OHCU_PF_L0 1
+#define OHCU_PF_L1 2
+#define OHCU_PF_BI 3
+
+/* SAOType / SAOEOClass, hevcdec.h:247-259 */
+#define OHCU_SAO_NOT_APPLIED 0
+#define OHCU_SAO_BAND        1
+#define OHCU_SAO_EDGE        2
+#define OHCU_SAO_EO_HORIZ 0
+#define OHCU_SAO_EO_VERT  1
+#define OHCU_SAO_EO_135D  2
+#define OHCU_SAO_EO_45D   3
+
+typedef struct ohcu_ctx ohcu_ctx;
+
+/* ---- sequence-level parameters (what set_sps() derives, hevcdec.c:428-476) */
+typedef struct ohcu_seq_params {
+    int32_t width, height;        /* luma samples; multiples of the min CB size   */
+    int32_t bit_depth;            /* 8, 9, 10 or 12. One depth for luma+chroma:
+                                     ff_hevc_dsp_init(&s->hevcdsp, bit_depth[LUMA]),
+                                     hevcdec.c:447                                 */
+    int32_t chroma_format_idc;    /* 0 mono, 1 4:2:0, 2 4:2:2, 3 4:4:4            */
+    int32_t log2_ctb_size;        /* 4..6                                          */
+    int32_t log2_min_cb_size;     /* >= 3 ; qp_y_tab granularity                   */
+    int32_t log2_min_pu_size;     /* is_pcm granularity (sps->log2_min_pu_size)    */
+    int32_t dpb_slots;            /* device DPB size, <= OHCU_MAX_DPB              */
+    int32_t jobs;                 /* frames in flight (ring of job arenas), >= 1   */
+    int32_t sao_enabled;          /* sps->sao_enabled_flag                         */
+    int32_t pcm_or_bypass;        /* pcmf of hevc_filter.c:541-543:
+                                     (pcm_enabled && pcm.loop_filter_disable) ||
+                                     pps->transquant_bypass_enable_flag            */
+    int32_t cb_qp_offset;         /* pps_cb_qp_offset (chroma_tc, hevc_filter.c:72) */
+    int32_t cr_qp_offset;         /* pps_cr_qp_offset                              */
+    int32_t no_tile_filter;       /* tiles_enabled && !loop_filter_across_tiles
+                                     (sao_filter_CTB, hevc_filter.c:281-282)       */
+    int32_t max_pus;              /* arena capacity per job; 0 = worst case        */
+    int32_t max_tus;              /* arena capacity per job; 0 = worst case        */
+    int64_t max_coeffs;           /* int16 arena capacity per job; 0 = worst case  */
+} ohcu_seq_params;
+
+/* ---- per-slice tables (SliceHeader weights + RefPicList, hevcdec.c:202-306) */
+typedef struct ohcu_slice_tab {
+    uint8_t ref_slot[2][OHCU_MAX_REFS];   /* DPB slot of refPicList[X].ref[i]     */
+    uint8_t weight_flag;                  /* (P && weighted_pred) || (B && weighted_bipred),
+                                             hevcdec.c:1755-1756                   */
+    uint8_t luma_log2_weight_denom;
+    uint8_t chroma_log2_weight_denom;
+    uint8_t pad;
+    int16_t luma_weight[2][OHCU_MAX_REFS];
+    int16_t luma_offset[2][OHCU_MAX_REFS];
+    int16_t chroma_weight[2][OHCU_MAX_REFS][2];
+    int16_t chroma_offset[2][OHCU_MAX_REFS][2];
+} ohcu_slice_tab;
+
+/* ---- one inter PU: emitted where hls_prediction_unit calls luma_mc_* /
+ *      chroma_mc_* (hevcdec.c:2250-2306)                                      */
+typedef struct ohcu_pu {
+    uint16_t x0, y0;          /* luma position                                    */
+    uint8_t  w, h;            /* luma nPbW, nPbH (4..64)                          */
+    uint8_t  pred_flag;       /* OHCU_PF_L0 / _L1 / _BI                           */
+    uint8_t  slice;           /* index of the ohcu_slice_tab to use               */
+    int16_t  mv[2][2];        /* [list][x,y] quarter-pel (Mv, hevcdec.h:297-300)  */
+    uint8_t  ref_idx[2];      /* MvField.ref_idx                                  */
+    uint8_t  pad[2];
+} ohcu_pu;                    /* 20 bytes */
+
+/* ---- one coded transform block: emitted where ff_hevc_hls_transform{,_c}
+ *      end in transform_add (hevc_cabac.c:1818, :1905)                        */
+#define OHCU_TU_IDCT    0     /* idct[log2-2](coeffs, col_limit)                  */
+#define OHCU_TU_DC      1     /* idct_dc[log2-2](coeffs)                          */
+#define OHCU_TU_DST4    2     /* idct_4x4_luma(coeffs)                            */
+#define OHCU_TU_SKIP    3     /* transform_skip(coeffs, log2)                     */
+#define OHCU_TU_BYPASS  4     /* cu_transquant_bypass: coeffs are the residual    */
+
+#define OHCU_TUF_RDPCM      1 /* transform_rdpcm after skip / on bypass           */
+#define OHCU_TUF_RDPCM_VERT 2 /* mode argument of transform_rdpcm (1 = vertical)  */
+#define OHCU_TUF_ROTATE     4 /* 4x4 transform_skip rotation, hevc_cabac.c:1735   */
+#define OHCU_TUF_CROSS      8 /* cross-component prediction, hevc_cabac.c:1810    */
+
+typedef struct ohcu_tu {
+    uint16_t x0, y0;          /* position in samples of plane c_idx               */
+    uint8_t  c_idx;           /* 0 Y, 1 Cb, 2 Cr                                  */
+    uint8_t  log2_size;       /* 2..5                                             */
+    uint8_t  mode;            /* OHCU_TU_*                                        */
+    uint8_t  flags;           /* OHCU_TUF_*                                       */
+    int8_t   col_limit;       /* idct only, as hevc_cabac.c:1793-1805             */
+    int8_t   res_scale_val;   /* OHCU_TUF_CROSS only (lc->tu.res_scale_val)       */
+    uint16_t pad;
+    uint32_t coeff_off;       /* int16 offset of the N*N block in the arena       */
+    uint32_t cross_tu;        /* OHCU_TUF_CROSS: index (in this frame's TU list)
+                                 of the luma TB whose residual is coeffs_y        */
+} ohcu_tu;                    /* 20 bytes */
+
+/* ---- DBParams, hevcdec.h:353-356 */
+typedef struct ohcu_dbparams {
+    int8_t beta_offset;
+    int8_t tc_offset;
+} ohcu_dbparams;
+
+/* ---- SAOParams restricted to what the DSP reads (hevc_ps.h:338-347) */
+typedef struct ohcu_sao {
+    uint8_t type_idx[3];
+    uint8_t eo_class[3];
+    uint8_t band_position[3];
+    uint8_t pad;
+    int16_t offset_val[3][5];
+} ohcu_sao;                   /* 40 bytes */
+
+/* ---- deblocking side inputs: the arrays hevc_filter.c reads ------------- */
+typedef struct ohcu_deblock_in {
+    const uint8_t *vertical_bs;    /* bs_width*bs_height bytes, index (x + y*bs_width)>>2,
+                                      bs_width=(width>>2)+1, bs_height=(height>>2)+1
+                                      (hevcdec.c:127-128)                          */
+    const uint8_t *horizontal_bs;
+    const int8_t  *qp_y_tab;       /* min_cb_width*min_cb_height (get_qPy, hevc_filter.c:149) */
+    const ohcu_dbparams *deblock;  /* ctb_width*ctb_height, raster                 */
+    const uint8_t *is_pcm;         /* min_pu_width*min_pu_height, may be NULL when
+                                      seq.pcm_or_bypass == 0                       */
+} ohcu_deblock_in;
+
+/* ---- SAO side inputs (sao_filter_CTB, hevc_filter.c:264-325) ------------ */
+typedef struct ohcu_sao_in {
+    const ohcu_sao *sao;               /* ctb_width*ctb_height, raster             */
+    const uint8_t  *filter_slice_edges;/* per CTB: slice_loop_filter_across_slices_enabled_flag */
+    const int32_t  *tab_slice_address; /* per CTB                                  */
+    const int32_t  *tile_id;           /* per CTB in RASTER order
+                                          (= pps->tile_id[ctb_addr_rs_to_ts[rs]]);
+                                          NULL = single tile                       */
+} ohcu_sao_in;
+
+/* ======================================================================== */
+/* Library / context                                                        */
+/* ======================================================================== */
+
+int         ohcu_abi_version(void);
+const char *ohcu_last_error(void);      /* thread-local text of the last failure   */
+int         ohcu_device_count(void);
+
+/* replaces ff_hevc_dsp_init(&s->hevcdsp, bit_depth) + pic_arrays_init +
+ * the frame pool of hevc_refs.c:79-129 for this path (hevcdec.c:428-476).      */
+int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp);
+int ohcu_destroy(ohcu_ctx *ctx);
+int ohcu_get_seq_params(const ohcu_ctx *ctx, ohcu_seq_params *out);
+
+/* ---- device DPB (replaces AVFrame planes of HEVCFrame, hevc_refs.c:79-129) */
+/* Host -> DPB slot (reference frames decoded elsewhere, test inputs).
+ * strides in BYTES as everywhere in the reference; planes[1..2] ignored for mono. */
+int ohcu_slot_upload(ohcu_ctx *ctx, int slot, const uint8_t *const planes[3],
+                     const ptrdiff_t strides[3]);
+/* DPB slot -> host (output / hash check); waits for the slot's producer. */
+int ohcu_slot_download(ohcu_ctx *ctx, int slot, uint8_t *const planes[3],
+                       const ptrdiff_t strides[3]);
+/* Asynchronous variant into caller-pinned memory; completes at ohcu_slot_sync. */
+int ohcu_slot_download_async(ohcu_ctx *ctx, int slot, uint8_t *const planes[3],
+                             const ptrdiff_t strides[3]);
+int ohcu_slot_sync(ohcu_ctx *ctx, int slot);   /* replaces ff_thread_await_progress */
+
+/* ======================================================================== */
+/* Per-frame work lists                                                     */
+/* ======================================================================== */
+
+/* hevc_frame_start (hevcdec.c:3575): picks the next job arena of the ring and
+ * returns its id (>= 0) or a negative error.  out_slot is the DPB slot the
+ * reconstructed picture is written to.                                        */
+int ohcu_frame_begin(ohcu_ctx *ctx, int out_slot, int poc);
+
+int ohcu_set_slice(ohcu_ctx *ctx, int job, int slice_idx, const ohcu_slice_tab *tab);
+
+/* replaces the immediate put_hevc_{q,e}pel* calls of hevcdec.c:1781-1786,
+ * 1863-1875, 1936-1941, 2033-2048.  recs are copied before return.            */
+int ohcu_append_pu(ohcu_ctx *ctx, int job, const ohcu_pu *recs, int n);
+
+/* replaces idct / transform_skip / rdpcm + transform_add of hevc_cabac.c:1727-1818,
+ * 1843-1905.  coeffs holds ncoeff int16 for the n records, each record's
+ * coeff_off RELATIVE to coeffs[0]; the library rebases them into the arena.    */
+int ohcu_append_tu(ohcu_ctx *ctx, int job, const ohcu_tu *recs, int n,
+                   const int16_t *coeffs, size_t ncoeff);
+
+/* Zero-copy variant: reserve ncoeff int16 in the job's PINNED coefficient
+ * arena and let the residual parser (lc->tu.coeffs, hevcdec.h:333) write there
+ * directly.  *arena_off receives the absolute offset to store in coeff_off of
+ * records passed to ohcu_append_tu_inplace.                                     */
+int ohcu_reserve_coeffs(ohcu_ctx *ctx, int job, size_t ncoeff, int16_t **ptr,
+                        uint32_t *arena_off);
+int ohcu_append_tu_inplace(ohcu_ctx *ctx, int job, const ohcu_tu *recs, int n);
+
+/* replaces the per-edge calls of deblocking_filter_CTB (hevc_filter.c:588-599,
+ * 634-654, 686-697, 735-755).  Arrays are copied before return.  Not calling it
+ * for a frame = no deblocking (all bs zero).                                    */
+int ohcu_set_deblock(ohcu_ctx *ctx, int job, const ohcu_deblock_in *in);
+
+/* replaces the per-CTB calls of sao_filter_CTB (hevc_filter.c:349-353, 486-494).
+ * Not calling it for a frame = SAO not applied.                                 */
+int ohcu_set_sao(ohcu_ctx *ctx, int job, const ohcu_sao_in *in);
+
+/* End of frame (where ff_hevc_hls_filter ran per CTB, hevc_filter.c:1211-1245):
+ * upload the job's lists (async, pinned) and enqueue the batched launches
+ *   MC -> residual add -> deblock (all vertical, then all horizontal edges) -> SAO
+ * on the job's stream.  Returns without waiting.                                 */
+int ohcu_frame_flush(ohcu_ctx *ctx, int job);
+
+/* Split form of flush, used by bench.py to time the launches with the lists
+ * already resident in HBM: stage = H2D only, launch = kernels only (may be
+ * repeated; out_slot < 0 keeps the job's slot).                                  */
+int ohcu_frame_stage(ohcu_ctx *ctx, int job);
+int ohcu_frame_launch(ohcu_ctx *ctx, int job, int out_slot);
+
+int ohcu_frame_sync(ohcu_ctx *ctx, int job);
+int ohcu_sync_all(ohcu_ctx *ctx);
+
+/* ---- measurement hooks (bench.py; CUDA events on the job's own stream) ---- */
+#define OHCU_STAGE_MC       0
+#define OHCU_STAGE_RESIDUAL 1
+#define OHCU_STAGE_DEBLOCK  2
+#define OHCU_STAGE_SAO      3
+#define OHCU_STAGE_TOTAL    4
+#define OHCU_NUM_STAGES     5
+/* When enabled, every launch brackets each stage with cudaEvents. */
+int ohcu_set_profiling(ohcu_ctx *ctx, int enable);
+/* Milliseconds of the job's most recent launch, per stage; job must be synced. */
+int ohcu_job_stage_ms(ohcu_ctx *ctx, int job, float ms[OHCU_NUM_STAGES]);
+/* Number of kernels this context has launched so far. */
+int64_t ohcu_kernel_launches(const ohcu_ctx *ctx);
+/* Raw stream handle (cudaStream_t) of a job, for event timing by the caller. */
+void *ohcu_job_stream(ohcu_ctx *ctx, int job);
+/* Write >L2-size scratch so the next launch starts cold. */
+int ohcu_flush_l2(ohcu_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OHCU_H */

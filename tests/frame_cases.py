@@ -1,0 +1,49 @@
+"""Seeded frame-level cases shared by the oracle, golden and GPU parity tests.
+
+FRAME_CASES: name -> (width, height, bit_depth, chroma_format_idc, seed, generator overrides)
+cfg1 is BASELINE.json configs[0] (416x240 8-bit 4:2:0, the golden frame).
+"""
+import hashlib
+
+import numpy as np
+
+from hevc_b200 import synth
+
+FRAME_CASES = {
+    "cfg1_416x240_8b_420": (416, 240, 8, 1, 1001, {}),
+    "cfg1w_416x240_8b_420_weighted": (416, 240, 8, 1, 1002, dict(weighted=1)),
+    "main10_416x240_420_weighted": (416, 240, 10, 1, 3001, dict(weighted=1)),
+    "rext_10b_422": (320, 184, 10, 2, 4001, dict(rext=1, weighted=1)),
+    "rext_10b_444": (320, 184, 10, 3, 4002, dict(rext=1)),
+    "rext_8b_444_bypass": (256, 128, 8, 3, 4003, dict(rext=1, sp_pcm_or_bypass=1, bypass_pct=10)),
+    "slices_tiles_8b_420": (448, 256, 8, 1, 5001, dict(n_slices=4, slices_no_lf=1, tile_cols=3, tile_rows=2,
+                                                       sp_no_tile_filter=1)),
+    "slices_10b_420_bypass": (320, 192, 10, 1, 5002, dict(n_slices=3, slices_no_lf=1, sp_pcm_or_bypass=1,
+                                                         bypass_pct=12)),
+    "mono_8b": (192, 128, 8, 0, 6001, {}),
+    "main12_420": (256, 136, 12, 1, 6002, dict(weighted=1)),
+    "bd9_420": (256, 136, 9, 1, 6003, {}),
+    "dense_coeffs_8b": (256, 128, 8, 1, 7001, dict(dense_coeffs=1)),
+    "dense_coeffs_10b_444": (192, 128, 10, 3, 7002, dict(dense_coeffs=1, rext=1)),
+    "far_mv_8b": (320, 176, 8, 1, 7003, dict(far_mv_pct=60)),
+    "ragged_ctb_10b": (200, 72, 10, 1, 7004, dict(weighted=1)),
+    "tiny_8x8": (8, 8, 8, 1, 7005, {}),
+    "one_ctb": (64, 64, 10, 1, 7006, dict(weighted=1)),
+    "ctb32_8b": (288, 160, 8, 1, 7007, dict(sp_log2_ctb_size=5, split_pct=(0, 50, 40))),
+    "ctb16_10b_444": (160, 96, 10, 3, 7008, dict(sp_log2_ctb_size=4, split_pct=(0, 0, 40))),
+    "cfg2_small_1080like": (480, 272, 8, 1, 2001, {}),
+}
+
+
+def build_case(name):
+    w, h, bd, cf, seed, kw = FRAME_CASES[name]
+    job = synth.make_job(w, h, bd, cf, seed=seed, **kw)
+    refs = [synth.make_picture(job.sp, seed * 10 + s) for s in range(job.sp.dpb_slots)]
+    return job, refs
+
+
+def picture_digest(planes):
+    h = hashlib.sha256()
+    for p in planes:
+        h.update(np.ascontiguousarray(p).tobytes())
+    return h.hexdigest()

@@ -1,0 +1,54 @@
+"""Regenerates tests/golden/* from the REFERENCE's own compiled C code
+(oracle/_ref/liboh_ref.so, built from /root/reference by oracle/Makefile).
+Run in the build container (needs /root/reference):  python tests/golden/make_golden.py
+
+  leaf_digests.json   sha256[:16] of every output of every leaf case (tests/leaf_cases.py)
+  frames.json         sha256 of the reconstructed picture of every frame case
+                      (tests/frame_cases.py) after MC, MC+residual, and the full pipeline
+  cfg1_416x240.npz    the full golden picture of BASELINE.json configs[0]
+"""
+import hashlib
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+import frame_cases  # noqa: E402
+import leaf_cases  # noqa: E402
+import oracle_lib  # noqa: E402
+
+STAGE_SETS = {"mc": 1, "mc_res": 3, "mc_res_db": 7, "all": 15}
+
+
+def main():
+    ref = oracle_lib.Lib("ref")
+    leaves = {name: hashlib.sha256(run(ref)).hexdigest()[:16] for name, run in leaf_cases.all_cases()}
+    with open(os.path.join(HERE, "leaf_digests.json"), "w") as f:
+        json.dump({"source": "oracle/_ref/liboh_ref.so (reference C table)", "cases": leaves}, f,
+                  indent=0, sort_keys=True)
+    frames = {}
+    for name in frame_cases.FRAME_CASES:
+        job, refs = frame_cases.build_case(name)
+        frames[name] = {
+            "n_pu": int(len(job.pus)), "n_tu": int(len(job.tus)), "ncoeff": int(len(job.coeffs)),
+            "lists": hashlib.sha256(job.pus.tobytes() + job.tus.tobytes() + job.coeffs.tobytes()).hexdigest(),
+        }
+        for key, st in STAGE_SETS.items():
+            out = ref.replay(job, refs, out_init=refs[-1], stages=st)
+            frames[name][key] = frame_cases.picture_digest(out)
+            if name.startswith("cfg1_") and key == "all":
+                np.savez_compressed(os.path.join(HERE, "cfg1_416x240.npz"),
+                                    **{f"plane{c}": p for c, p in enumerate(out)})
+    with open(os.path.join(HERE, "frames.json"), "w") as f:
+        json.dump({"source": "ohref_replay_frame (reference drivers + table)", "cases": frames}, f,
+                  indent=1, sort_keys=True)
+    print(f"{len(leaves)} leaf digests, {len(frames)} frame cases written")
+
+
+if __name__ == "__main__":
+    main()

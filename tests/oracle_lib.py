@@ -1,0 +1,154 @@
+"""ctypes bindings of the CHECKERS: oracle/liboracle.so (our CPU restatement) and
+oracle/_ref/liboh_ref.so (the reference's own compiled C code).  Tests only.
+
+``Lib('oracle')`` / ``Lib('ref')`` expose the same leaf entry points with the
+prefixes ``or_`` / ``ohref_`` unified under one name, plus ``replay``.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+ORACLE_SO = os.path.join(ORACLE_DIR, "liboracle.so")
+REF_SO = os.path.join(ORACLE_DIR, "_ref", "liboh_ref.so")
+REFERENCE_ROOT = "/root/reference"
+
+import sys
+sys.path.insert(0, ROOT)
+from hevc_b200 import abi  # noqa: E402
+
+
+class Picture(C.Structure):
+    _fields_ = [("data", C.c_void_p * 3), ("stride", C.c_ssize_t * 3)]
+
+
+class FrameJobC(C.Structure):
+    _fields_ = [
+        ("sp", abi.SeqParams),
+        ("n_slices", C.c_int32), ("slices", C.c_void_p),
+        ("n_pu", C.c_int32), ("pus", C.c_void_p),
+        ("n_tu", C.c_int32), ("tus", C.c_void_p),
+        ("coeffs", C.c_void_p), ("ncoeff", C.c_int64),
+        ("deblock", C.POINTER(abi.DeblockIn)), ("sao", C.POINTER(abi.SaoIn)),
+        ("dpb", C.POINTER(Picture)), ("out", Picture), ("stages", C.c_int32),
+    ]
+
+
+STAGE_MC, STAGE_RESIDUAL, STAGE_DEBLOCK, STAGE_SAO = 1, 2, 4, 8
+
+
+def build_oracle():
+    subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "oracle"])
+
+
+def build_ref():
+    if not os.path.isdir(REFERENCE_ROOT):
+        return False
+    subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "ref", "-j8"])
+    return True
+
+
+def have_ref():
+    return os.path.exists(REF_SO) or os.path.isdir(REFERENCE_ROOT)
+
+
+_P = C.c_void_p
+_I = C.c_int
+_S = C.c_ssize_t
+_LEAVES = {
+    "transform_add": [_I, _P, _P, _S, _I],
+    "transform_rdpcm": None,   # differs between the two libs, handled below
+    "transform_skip": [_I, _P, _I],
+    "idct_4x4_luma": [_I, _P],
+    "idct": [_I, _P, _I, _I],
+    "idct_dc": [_I, _P, _I],
+    "sao_band_filter": [_I, _P, _P, _S, _S, _P, _I, _I, _I],
+    "sao_edge_filter": [_I, _P, _P, _S, _S, _P, _I, _I, _I],
+    "sao_edge_restore": [_I, _I, _P, _P, _S, _S, _P, _I, _P, _I, _I, _P, _P, _P],
+    "mc_put": [_I, _I, _P, _P, _S, _I, _I, _I, _I],
+    "mc_uni": [_I, _I, _P, _S, _P, _S, _I, _I, _I, _I],
+    "mc_uni_w": [_I, _I, _P, _S, _P, _S, _I, _I, _I, _I, _I, _I, _I],
+    "mc_bi": [_I, _I, _P, _S, _P, _S, _P, _I, _I, _I, _I],
+    "mc_bi_w": [_I, _I, _P, _S, _P, _S, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I],
+    "loop_filter_luma": [_I, _I, _P, _S, _I, _P, _P, _P],
+    "loop_filter_chroma": [_I, _I, _P, _S, _P, _P, _P],
+}
+
+
+class Lib:
+    def __init__(self, which):
+        self.which = which
+        if which == "oracle":
+            build_oracle()
+            self.lib = C.CDLL(ORACLE_SO)
+            prefix = "or_"
+        elif which == "ref":
+            if not os.path.exists(REF_SO) and not build_ref():
+                raise FileNotFoundError(REF_SO)
+            self.lib = C.CDLL(REF_SO)
+            prefix = "ohref_"
+        else:
+            raise ValueError(which)
+        for name, args in _LEAVES.items():
+            fn = getattr(self.lib, prefix + name)
+            fn.restype = None
+            if args is not None:
+                fn.argtypes = args
+            setattr(self, "_" + name, fn)
+        self._replay = getattr(self.lib, prefix + "replay_frame")
+        self._replay.restype = C.c_int
+        self._replay.argtypes = [C.POINTER(FrameJobC)]
+
+    def __getattr__(self, name):
+        if name in _LEAVES:
+            return getattr(self, "_" + name)
+        raise AttributeError(name)
+
+    def transform_rdpcm(self, bd, coeffs_ptr, log2_size, mode):
+        if self.which == "oracle":
+            self._transform_rdpcm(C.c_void_p(coeffs_ptr), C.c_int(log2_size), C.c_int(mode))
+        else:
+            self._transform_rdpcm(C.c_int(bd), C.c_void_p(coeffs_ptr), C.c_int(log2_size), C.c_int(mode))
+
+    def replay(self, job, refs, out_init=None, stages=0, use_deblock=True, use_sao=True):
+        """Run one frame job.  refs = list (DPB slots) of pictures (lists of 2-D arrays).
+        Returns the reconstructed picture as a list of arrays."""
+        sp = job.sp
+        nplanes = 3 if sp.chroma_format_idc else 1
+        out = [np.ascontiguousarray(p.copy()) for p in (out_init if out_init is not None else
+                                                         _blank(sp, nplanes))]
+        dpb = (Picture * max(1, sp.dpb_slots))()
+        keep = []
+        for i in range(sp.dpb_slots):
+            if i < len(refs) and refs[i] is not None:
+                for c in range(nplanes):
+                    a = np.ascontiguousarray(refs[i][c])
+                    keep.append(a)
+                    dpb[i].data[c] = a.ctypes.data
+                    dpb[i].stride[c] = a.strides[0]
+        fj = FrameJobC()
+        fj.sp = sp
+        fj.n_slices = len(job.slices); fj.slices = job.slices.ctypes.data
+        fj.n_pu = len(job.pus); fj.pus = job.pus.ctypes.data
+        fj.n_tu = len(job.tus); fj.tus = job.tus.ctypes.data
+        fj.coeffs = job.coeffs.ctypes.data; fj.ncoeff = len(job.coeffs)
+        db = job.deblock_in(); so = job.sao_in()
+        fj.deblock = C.pointer(db) if use_deblock else None
+        fj.sao = C.pointer(so) if use_sao else None
+        fj.dpb = dpb
+        for c in range(nplanes):
+            fj.out.data[c] = out[c].ctypes.data
+            fj.out.stride[c] = out[c].strides[0]
+        fj.stages = stages
+        rc = self._replay(C.byref(fj))
+        if rc != 0:
+            raise RuntimeError(f"{self.which} replay failed: {rc}")
+        return out
+
+
+def _blank(sp, nplanes):
+    from hevc_b200 import synth
+    return synth.blank_picture(sp)
