@@ -116,6 +116,7 @@ SYMBOLS = {
     "ohcu_frame_flush": (C.c_int, [_P, C.c_int]),
     "ohcu_frame_stage": (C.c_int, [_P, C.c_int]),
     "ohcu_frame_launch": (C.c_int, [_P, C.c_int, C.c_int]),
+    "ohcu_frame_launch_stages": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
     "ohcu_frame_sync": (C.c_int, [_P, C.c_int]),
     "ohcu_sync_all": (C.c_int, [_P]),
     "ohcu_set_profiling": (C.c_int, [_P, C.c_int]),

@@ -1,0 +1,139 @@
+"""Host-side mirror of the batched backend for Python callers (tests, bench, smoke).
+
+``Context`` wraps one ``ohcu_ctx`` (one per GPU): a device DPB plus a ring of job
+arenas.  Every call goes through the C ABI of include/ohcu.h; nothing here computes.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import abi
+from .abi import check
+
+
+def _plane_args(planes):
+    ptrs = (C.c_void_p * 3)()
+    strides = (C.c_ssize_t * 3)()
+    for i, p in enumerate(planes):
+        assert p.flags["C_CONTIGUOUS"] or p.strides[1] == p.itemsize
+        ptrs[i] = p.ctypes.data
+        strides[i] = p.strides[0]
+    return ptrs, strides
+
+
+class Context:
+    def __init__(self, sp, device=0, dpb_slots=None, jobs=None):
+        self.lib = abi.load()
+        self.sp = abi.SeqParams.from_buffer_copy(sp)
+        if dpb_slots is not None:
+            self.sp.dpb_slots = dpb_slots
+        if jobs is not None:
+            self.sp.jobs = jobs
+        self.handle = C.c_void_p()
+        check(self.lib.ohcu_create(C.byref(self.handle), device, C.byref(self.sp)), "ohcu_create")
+        self.nplanes = 3 if self.sp.chroma_format_idc else 1
+        self.dtype = np.uint8 if self.sp.bit_depth == 8 else np.uint16
+
+    def close(self):
+        if self.handle:
+            self.lib.ohcu_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- DPB ---------------------------------------------------------------
+    def plane_shape(self, c):
+        hs = 1 if (c and self.sp.chroma_format_idc in (1, 2)) else 0
+        vs = 1 if (c and self.sp.chroma_format_idc == 1) else 0
+        return (self.sp.height >> vs, self.sp.width >> hs)
+
+    def upload(self, slot, planes):
+        planes = [np.ascontiguousarray(p, dtype=self.dtype) for p in planes]
+        ptrs, strides = _plane_args(planes)
+        check(self.lib.ohcu_slot_upload(self.handle, slot, C.byref(ptrs), C.byref(strides)), "ohcu_slot_upload")
+
+    def download(self, slot, out=None):
+        if out is None:
+            out = [np.empty(self.plane_shape(c), dtype=self.dtype) for c in range(self.nplanes)]
+        ptrs, strides = _plane_args(out)
+        check(self.lib.ohcu_slot_download(self.handle, slot, C.byref(ptrs), C.byref(strides)), "ohcu_slot_download")
+        return out
+
+    def download_async(self, slot, out):
+        ptrs, strides = _plane_args(out)
+        check(self.lib.ohcu_slot_download_async(self.handle, slot, C.byref(ptrs), C.byref(strides)),
+              "ohcu_slot_download_async")
+
+    def slot_sync(self, slot):
+        check(self.lib.ohcu_slot_sync(self.handle, slot), "ohcu_slot_sync")
+
+    # ---- frames ------------------------------------------------------------
+    def begin(self, out_slot, poc=0):
+        return check(self.lib.ohcu_frame_begin(self.handle, out_slot, poc), "ohcu_frame_begin")
+
+    def append(self, job_id, fj, use_deblock=True, use_sao=True):
+        """Append every list of a synth.FrameJob (or anything with the same arrays)."""
+        lib, h = self.lib, self.handle
+        for i in range(len(fj.slices)):
+            tab = abi.SliceTab.from_buffer_copy(fj.slices[i].tobytes())
+            check(lib.ohcu_set_slice(h, job_id, i, C.byref(tab)), "ohcu_set_slice")
+        check(lib.ohcu_append_pu(h, job_id, fj.pus.ctypes.data, len(fj.pus)), "ohcu_append_pu")
+        if len(fj.tus):
+            check(lib.ohcu_append_tu(h, job_id, fj.tus.ctypes.data, len(fj.tus), fj.coeffs.ctypes.data,
+                                     len(fj.coeffs)), "ohcu_append_tu")
+        if use_deblock:
+            d = fj.deblock_in()
+            check(lib.ohcu_set_deblock(h, job_id, C.byref(d)), "ohcu_set_deblock")
+        if use_sao:
+            s = fj.sao_in()
+            check(lib.ohcu_set_sao(h, job_id, C.byref(s)), "ohcu_set_sao")
+
+    def stage(self, job_id):
+        check(self.lib.ohcu_frame_stage(self.handle, job_id), "ohcu_frame_stage")
+
+    def launch(self, job_id, out_slot=-1, stages=0):
+        check(self.lib.ohcu_frame_launch_stages(self.handle, job_id, out_slot, stages), "ohcu_frame_launch")
+
+    def flush(self, job_id):
+        check(self.lib.ohcu_frame_flush(self.handle, job_id), "ohcu_frame_flush")
+
+    def sync(self, job_id=None):
+        if job_id is None:
+            check(self.lib.ohcu_sync_all(self.handle), "ohcu_sync_all")
+        else:
+            check(self.lib.ohcu_frame_sync(self.handle, job_id), "ohcu_frame_sync")
+
+    def set_profiling(self, on):
+        check(self.lib.ohcu_set_profiling(self.handle, int(on)), "ohcu_set_profiling")
+
+    def stage_ms(self, job_id):
+        ms = (C.c_float * abi.NUM_STAGES)()
+        check(self.lib.ohcu_job_stage_ms(self.handle, job_id, C.byref(ms)), "ohcu_job_stage_ms")
+        return list(ms)
+
+    def kernel_launches(self):
+        return int(self.lib.ohcu_kernel_launches(self.handle))
+
+    def flush_l2(self):
+        check(self.lib.ohcu_flush_l2(self.handle), "ohcu_flush_l2")
+
+    # ---- convenience: one frame, synchronously (tests, smoke) -----------------
+    def reconstruct(self, fj, refs, out_slot=None, out_init=None, stages=0, use_deblock=True, use_sao=True):
+        """Upload refs to slots 0.., run one frame job, return the reconstructed planes."""
+        if out_slot is None:
+            out_slot = self.sp.dpb_slots - 1
+        for i, r in enumerate(refs):
+            if r is not None and i != out_slot:
+                self.upload(i, r)
+        if out_init is not None:
+            self.upload(out_slot, out_init)
+        j = self.begin(out_slot)
+        self.append(j, fj, use_deblock=use_deblock, use_sao=use_sao)
+        self.stage(j)
+        self.launch(j, out_slot, stages)
+        self.sync(j)
+        return self.download(out_slot)

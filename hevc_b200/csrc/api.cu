@@ -1,0 +1,714 @@
+// api.cu — the C ABI of include/ohcu.h: context, device DPB, per-frame job arenas,
+// list staging and the launch sequence.  Host-side counterpart of what set_sps /
+// pic_arrays_init / hevc_frame_start / the hevc_refs.c frame pool do for this path in
+// the reference (hevcdec.c:114-200, 428-476, 3575-3600; hevc_refs.c:79-129).
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+#include "ohcu_internal.h"
+
+namespace ohcu {
+int upload_dct_table();
+}
+using namespace ohcu;
+
+// ------------------------------------------------------------------ errors
+static thread_local char g_err[512] = "";
+static int fail(int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CU(call)                                                                          \
+    do {                                                                                  \
+        cudaError_t e_ = (call);                                                          \
+        if (e_ != cudaSuccess)                                                            \
+            return fail(OHCU_ECUDA, "%s -> %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+// ------------------------------------------------------------------ objects
+struct Picture {
+    uint8_t *base = nullptr;
+    PlaneSet ps{};
+    size_t bytes = 0;
+};
+
+struct Slot {
+    Picture pic;
+    cudaEvent_t ready = nullptr;      // producer finished
+    cudaEvent_t read_done = nullptr;  // last async download finished
+    bool has_ready = false, has_read = false;
+    uint64_t readers = 0;             // jobs that read this slot since its last write
+};
+
+template <typename T> struct Arena {      // pinned host staging + device copy
+    T *h = nullptr;
+    T *d = nullptr;
+    size_t cap = 0;
+};
+
+struct Job {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    cudaEvent_t ev[OHCU_NUM_STAGES + 1] = {};
+    bool has_done = false, timed = false;
+    bool open = false;                // between frame_begin and stage
+    bool staged = false;
+    int out_slot = -1, poc = 0;
+    Picture recon;
+    // lists
+    Arena<ohcu_pu> pus;      int n_pu = 0;
+    Arena<int2> ctb_range;   // per CTB: first PU, count
+    bool pu_sorted = true;   int last_ctb = -1;
+    Arena<ohcu_slice_tab> slices; int n_slices = 0;
+    Arena<ohcu_tu> tus;      int n_tu = 0;
+    Arena<int16_t> coeffs;   size_t ncoeff = 0;
+    Arena<uint32_t> bins[4]; int n_bin[4] = {0, 0, 0, 0};
+    Arena<uint8_t> vbs, hbs, is_pcm; Arena<int8_t> qp; Arena<ohcu_dbparams> db;
+    Arena<ohcu_sao> sao;     Arena<uint16_t> sao_flags;
+    bool has_deblock = false, has_sao = false, has_pcm = false;
+};
+
+struct ohcu_ctx {
+    int device = 0;
+    ohcu_seq_params sp{};
+    int hs = 0, vs = 0, nplanes = 1, P = 1;
+    int pw[3] = {0, 0, 0}, ph[3] = {0, 0, 0};
+    int ctb_w = 0, ctb_h = 0, nctb = 0;
+    int min_cb_w = 0, min_cb_h = 0, min_pu_w = 0, min_pu_h = 0, bs_w = 0, bs_h = 0;
+    std::vector<Slot> slots;
+    std::vector<Job> jobs;
+    int next_job = 0;
+    cudaStream_t copy_stream = nullptr;
+    bool profiling = false;
+    int64_t launches = 0;
+    void *l2_buf = nullptr;
+    size_t l2_bytes = 0;
+};
+
+// ------------------------------------------------------------------ helpers
+static int alloc_picture(const ohcu_ctx *c, Picture *p)
+{
+    size_t off[3], total = 0;
+    for (int i = 0; i < c->nplanes; i++) {
+        p->ps.pitch[i] = (c->pw[i] * c->P + 255) & ~255;
+        off[i] = total;
+        total += (size_t)p->ps.pitch[i] * c->ph[i] + 256;
+    }
+    CU(cudaMalloc(&p->base, total));
+    CU(cudaMemset(p->base, 0, total));
+    for (int i = 0; i < 3; i++) p->ps.p[i] = i < c->nplanes ? p->base + off[i] : nullptr;
+    p->bytes = total;
+    return 0;
+}
+
+template <typename T> static int alloc_arena(Arena<T> *a, size_t n)
+{
+    a->cap = n ? n : 1;
+    CU(cudaHostAlloc((void **)&a->h, a->cap * sizeof(T), cudaHostAllocDefault));
+    CU(cudaMalloc((void **)&a->d, a->cap * sizeof(T)));
+    return 0;
+}
+template <typename T> static void free_arena(Arena<T> *a)
+{
+    if (a->h) cudaFreeHost(a->h);
+    if (a->d) cudaFree(a->d);
+    a->h = nullptr; a->d = nullptr; a->cap = 0;
+}
+template <typename T> static cudaError_t push_arena(const Arena<T> &a, size_t n, cudaStream_t st)
+{
+    if (!n) return cudaSuccess;
+    return cudaMemcpyAsync(a.d, a.h, n * sizeof(T), cudaMemcpyHostToDevice, st);
+}
+
+static int check_job(ohcu_ctx *c, int job)
+{
+    if (!c) return fail(OHCU_EINVAL, "null context");
+    if (job < 0 || job >= (int)c->jobs.size()) return fail(OHCU_EINVAL, "bad job id %d", job);
+    return 0;
+}
+#define ENTER(c)                                              \
+    do {                                                      \
+        if (!(c)) return fail(OHCU_EINVAL, "null context");   \
+        CU(cudaSetDevice((c)->device));                       \
+    } while (0)
+
+// ------------------------------------------------------------------ library
+extern "C" int ohcu_abi_version(void) { return OHCU_ABI_VERSION; }
+extern "C" const char *ohcu_last_error(void) { return g_err; }
+extern "C" int ohcu_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+extern "C" int ohcu_destroy(ohcu_ctx *c)
+{
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    for (auto &s : c->slots) {
+        if (s.pic.base) cudaFree(s.pic.base);
+        if (s.ready) cudaEventDestroy(s.ready);
+        if (s.read_done) cudaEventDestroy(s.read_done);
+    }
+    for (auto &j : c->jobs) {
+        if (j.recon.base) cudaFree(j.recon.base);
+        free_arena(&j.pus); free_arena(&j.ctb_range); free_arena(&j.slices); free_arena(&j.tus);
+        free_arena(&j.coeffs);
+        for (int i = 0; i < 4; i++) free_arena(&j.bins[i]);
+        free_arena(&j.vbs); free_arena(&j.hbs); free_arena(&j.is_pcm); free_arena(&j.qp); free_arena(&j.db);
+        free_arena(&j.sao); free_arena(&j.sao_flags);
+        if (j.done) cudaEventDestroy(j.done);
+        for (auto &e : j.ev) if (e) cudaEventDestroy(e);
+        if (j.stream) cudaStreamDestroy(j.stream);
+    }
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    if (c->l2_buf) cudaFree(c->l2_buf);
+    delete c;
+    return 0;
+}
+
+extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp)
+{
+    if (!out || !sp) return fail(OHCU_EINVAL, "null argument");
+    *out = nullptr;
+    if (sp->width <= 0 || sp->height <= 0 || sp->width > 16384 || sp->height > 16384)
+        return fail(OHCU_EINVAL, "bad picture size %dx%d", sp->width, sp->height);
+    if (sp->bit_depth != 8 && sp->bit_depth != 9 && sp->bit_depth != 10 && sp->bit_depth != 12)
+        return fail(OHCU_EINVAL, "unsupported bit depth %d (8, 9, 10, 12)", sp->bit_depth);
+    if (sp->chroma_format_idc < 0 || sp->chroma_format_idc > 3)
+        return fail(OHCU_EINVAL, "bad chroma_format_idc %d", sp->chroma_format_idc);
+    if (sp->log2_ctb_size < 4 || sp->log2_ctb_size > 6 || sp->log2_min_cb_size < 3 ||
+        sp->log2_min_cb_size > sp->log2_ctb_size || sp->log2_min_pu_size < 2 ||
+        sp->log2_min_pu_size > sp->log2_min_cb_size)
+        return fail(OHCU_EINVAL, "bad block size parameters");
+    if (sp->log2_ctb_size == 4 && (sp->chroma_format_idc == 1 || sp->chroma_format_idc == 2))
+        return fail(OHCU_EINVAL, "16x16 CTBs with subsampled chroma are not supported "
+                                 "(reference SAO reads chroma before its horizontal edges are filtered)");
+    if ((sp->width & ((1 << sp->log2_min_cb_size) - 1)) || (sp->height & ((1 << sp->log2_min_cb_size) - 1)))
+        return fail(OHCU_EINVAL, "picture size must be a multiple of the minimum CB size");
+    if (sp->dpb_slots < 1 || sp->dpb_slots > OHCU_MAX_DPB) return fail(OHCU_EINVAL, "dpb_slots out of range");
+    if (sp->jobs < 1 || sp->jobs > 64) return fail(OHCU_EINVAL, "jobs out of range (1..64)");
+
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) return fail(OHCU_ENODEV, "no CUDA device");
+    if (device < 0 || device >= ndev) return fail(OHCU_ENODEV, "device %d of %d", device, ndev);
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(OHCU_ENODEV, "device is sm_%d%d; this library is built for sm_100a only", prop.major, prop.minor);
+
+    ohcu_ctx *c = new (std::nothrow) ohcu_ctx();
+    if (!c) return fail(OHCU_ENOMEM, "out of memory");
+    c->device = device;
+    c->sp = *sp;
+    c->hs = (sp->chroma_format_idc == 1 || sp->chroma_format_idc == 2);
+    c->vs = (sp->chroma_format_idc == 1);
+    c->nplanes = sp->chroma_format_idc ? 3 : 1;
+    c->P = sp->bit_depth > 8 ? 2 : 1;
+    for (int i = 0; i < 3; i++) {
+        c->pw[i] = i ? sp->width >> c->hs : sp->width;
+        c->ph[i] = i ? sp->height >> c->vs : sp->height;
+    }
+    const int ctb = 1 << sp->log2_ctb_size;
+    c->ctb_w = (sp->width + ctb - 1) >> sp->log2_ctb_size;
+    c->ctb_h = (sp->height + ctb - 1) >> sp->log2_ctb_size;
+    c->nctb = c->ctb_w * c->ctb_h;
+    c->min_cb_w = sp->width >> sp->log2_min_cb_size;  c->min_cb_h = sp->height >> sp->log2_min_cb_size;
+    c->min_pu_w = sp->width >> sp->log2_min_pu_size;  c->min_pu_h = sp->height >> sp->log2_min_pu_size;
+    c->bs_w = (sp->width >> 2) + 1;                   c->bs_h = (sp->height >> 2) + 1;
+
+    // worst-case list sizes: two 8x4 PUs per 8x8 CU; one 4x4 TB per 16 samples; one int16 per sample
+    const size_t nsamp = (size_t)c->pw[0] * c->ph[0] + (c->nplanes == 3 ? 2 * (size_t)c->pw[1] * c->ph[1] : 0);
+    if (c->sp.max_pus <= 0) c->sp.max_pus = (int)(((size_t)sp->width * sp->height) / 32);
+    if (c->sp.max_tus <= 0) c->sp.max_tus = (int)(nsamp / 16);
+    if (c->sp.max_coeffs <= 0) c->sp.max_coeffs = (int64_t)nsamp;
+
+    int rc = 0;
+#define TRY(x) do { rc = (x); if (rc) { ohcu_destroy(c); return rc; } } while (0)
+#define TRYCU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { ohcu_destroy(c); \
+        return fail(e_ == cudaErrorMemoryAllocation ? OHCU_ENOMEM : OHCU_ECUDA, "%s -> %s", #x, cudaGetErrorString(e_)); } } while (0)
+    if (upload_dct_table()) { ohcu_destroy(c); return fail(OHCU_ECUDA, "constant upload failed"); }
+    c->slots.resize(sp->dpb_slots);
+    for (auto &s : c->slots) {
+        TRY(alloc_picture(c, &s.pic));
+        TRYCU(cudaEventCreateWithFlags(&s.ready, cudaEventDisableTiming));
+        TRYCU(cudaEventCreateWithFlags(&s.read_done, cudaEventDisableTiming));
+    }
+    c->jobs.resize(sp->jobs);
+    for (auto &j : c->jobs) {
+        TRYCU(cudaStreamCreateWithFlags(&j.stream, cudaStreamNonBlocking));
+        TRYCU(cudaEventCreateWithFlags(&j.done, cudaEventDisableTiming));
+        for (auto &e : j.ev) TRYCU(cudaEventCreate(&e));
+        TRY(alloc_picture(c, &j.recon));
+        TRY(alloc_arena(&j.pus, c->sp.max_pus));
+        TRY(alloc_arena(&j.ctb_range, c->nctb));
+        TRY(alloc_arena(&j.slices, OHCU_MAX_SLICES));
+        TRY(alloc_arena(&j.tus, c->sp.max_tus));
+        TRY(alloc_arena(&j.coeffs, (size_t)c->sp.max_coeffs));
+        for (int i = 0; i < 4; i++) TRY(alloc_arena(&j.bins[i], c->sp.max_tus));
+        TRY(alloc_arena(&j.vbs, (size_t)c->bs_w * c->bs_h));
+        TRY(alloc_arena(&j.hbs, (size_t)c->bs_w * c->bs_h));
+        TRY(alloc_arena(&j.qp, (size_t)c->min_cb_w * c->min_cb_h));
+        TRY(alloc_arena(&j.db, c->nctb));
+        TRY(alloc_arena(&j.is_pcm, (size_t)c->min_pu_w * c->min_pu_h));
+        TRY(alloc_arena(&j.sao, c->nctb));
+        TRY(alloc_arena(&j.sao_flags, c->nctb));
+    }
+    TRYCU(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+#undef TRY
+#undef TRYCU
+    *out = c;
+    return 0;
+}
+
+extern "C" int ohcu_get_seq_params(const ohcu_ctx *c, ohcu_seq_params *out)
+{
+    if (!c || !out) return fail(OHCU_EINVAL, "null argument");
+    *out = c->sp;
+    return 0;
+}
+
+// ------------------------------------------------------------------ device DPB
+static int check_slot(ohcu_ctx *c, int slot)
+{
+    if (slot < 0 || slot >= (int)c->slots.size()) return fail(OHCU_EINVAL, "bad DPB slot %d", slot);
+    return 0;
+}
+
+extern "C" int ohcu_slot_upload(ohcu_ctx *c, int slot, const uint8_t *const planes[3], const ptrdiff_t strides[3])
+{
+    ENTER(c);
+    if (check_slot(c, slot)) return OHCU_EINVAL;
+    if (!planes || !strides) return fail(OHCU_EINVAL, "null planes");
+    Slot &s = c->slots[slot];
+    // anything still reading or writing this slot must finish first
+    CU(cudaDeviceSynchronize());
+    for (int i = 0; i < c->nplanes; i++)
+        CU(cudaMemcpy2D(s.pic.ps.p[i], s.pic.ps.pitch[i], planes[i], strides[i], (size_t)c->pw[i] * c->P,
+                        c->ph[i], cudaMemcpyHostToDevice));
+    s.has_ready = false;
+    s.readers = 0;
+    return 0;
+}
+
+static int download_impl(ohcu_ctx *c, int slot, uint8_t *const planes[3], const ptrdiff_t strides[3], bool wait)
+{
+    ENTER(c);
+    if (check_slot(c, slot)) return OHCU_EINVAL;
+    if (!planes || !strides) return fail(OHCU_EINVAL, "null planes");
+    Slot &s = c->slots[slot];
+    if (s.has_ready) CU(cudaStreamWaitEvent(c->copy_stream, s.ready, 0));
+    for (int i = 0; i < c->nplanes; i++)
+        CU(cudaMemcpy2DAsync(planes[i], strides[i], s.pic.ps.p[i], s.pic.ps.pitch[i], (size_t)c->pw[i] * c->P,
+                             c->ph[i], cudaMemcpyDeviceToHost, c->copy_stream));
+    CU(cudaEventRecord(s.read_done, c->copy_stream));
+    s.has_read = true;
+    if (wait) CU(cudaEventSynchronize(s.read_done));
+    return 0;
+}
+extern "C" int ohcu_slot_download(ohcu_ctx *c, int slot, uint8_t *const planes[3], const ptrdiff_t strides[3])
+{
+    return download_impl(c, slot, planes, strides, true);
+}
+extern "C" int ohcu_slot_download_async(ohcu_ctx *c, int slot, uint8_t *const planes[3], const ptrdiff_t strides[3])
+{
+    return download_impl(c, slot, planes, strides, false);
+}
+extern "C" int ohcu_slot_sync(ohcu_ctx *c, int slot)
+{
+    ENTER(c);
+    if (check_slot(c, slot)) return OHCU_EINVAL;
+    Slot &s = c->slots[slot];
+    if (s.has_ready) CU(cudaEventSynchronize(s.ready));
+    if (s.has_read) CU(cudaEventSynchronize(s.read_done));
+    return 0;
+}
+
+// ------------------------------------------------------------------ per-frame lists
+extern "C" int ohcu_frame_begin(ohcu_ctx *c, int out_slot, int poc)
+{
+    ENTER(c);
+    if (check_slot(c, out_slot)) return OHCU_EINVAL;
+    const int id = c->next_job;
+    c->next_job = (c->next_job + 1) % (int)c->jobs.size();
+    Job &j = c->jobs[id];
+    // the arena's previous frame must have left the device before its pinned staging is reused
+    if (j.has_done) CU(cudaEventSynchronize(j.done));
+    j.open = true; j.staged = false;
+    j.out_slot = out_slot; j.poc = poc;
+    j.n_pu = 0; j.n_tu = 0; j.ncoeff = 0; j.n_slices = 0;
+    j.pu_sorted = true; j.last_ctb = -1;
+    for (int i = 0; i < 4; i++) j.n_bin[i] = 0;
+    j.has_deblock = j.has_sao = j.has_pcm = false;
+    memset(j.ctb_range.h, 0, sizeof(int2) * c->nctb);
+    return id;
+}
+
+#define OPEN_JOB(c, job)                                                        \
+    ENTER(c);                                                                   \
+    if (check_job(c, job)) return OHCU_EINVAL;                                  \
+    Job &j = (c)->jobs[job];                                                    \
+    if (!j.open) return fail(OHCU_ESTATE, "job %d is not open (call ohcu_frame_begin)", job)
+
+extern "C" int ohcu_set_slice(ohcu_ctx *c, int job, int slice_idx, const ohcu_slice_tab *tab)
+{
+    OPEN_JOB(c, job);
+    if (!tab || slice_idx < 0 || slice_idx >= OHCU_MAX_SLICES) return fail(OHCU_EINVAL, "bad slice index %d", slice_idx);
+    j.slices.h[slice_idx] = *tab;
+    if (slice_idx + 1 > j.n_slices) j.n_slices = slice_idx + 1;
+    return 0;
+}
+
+extern "C" int ohcu_append_pu(ohcu_ctx *c, int job, const ohcu_pu *recs, int n)
+{
+    OPEN_JOB(c, job);
+    if (n < 0 || (n && !recs)) return fail(OHCU_EINVAL, "bad PU list");
+    if ((size_t)j.n_pu + n > j.pus.cap) return fail(OHCU_EOVERFLOW, "PU arena full (%zu)", j.pus.cap);
+    const int l2 = c->sp.log2_ctb_size;
+    int2 *range = j.ctb_range.h;
+    for (int i = 0; i < n; i++) {
+        const ohcu_pu &pu = recs[i];
+        if (pu.pred_flag < 1 || pu.pred_flag > 3 || pu.w < 4 || pu.h < 4 || pu.w > 64 || pu.h > 64 ||
+            pu.x0 + pu.w > c->sp.width || pu.y0 + pu.h > c->sp.height || pu.slice >= OHCU_MAX_SLICES ||
+            pu.ref_idx[0] >= OHCU_MAX_REFS || pu.ref_idx[1] >= OHCU_MAX_REFS)
+            return fail(OHCU_EINVAL, "PU record %d is malformed", j.n_pu + i);
+        const int ctb = (pu.x0 >> l2) + (pu.y0 >> l2) * c->ctb_w;
+        if (ctb != j.last_ctb) {
+            if (range[ctb].y != 0) j.pu_sorted = false;      // CTB seen before: lists not grouped
+            else range[ctb].x = j.n_pu + i;
+            j.last_ctb = ctb;
+        }
+        range[ctb].y++;
+        j.pus.h[j.n_pu + i] = pu;
+    }
+    j.n_pu += n;
+    return 0;
+}
+
+static int add_tus(ohcu_ctx *c, Job &j, const ohcu_tu *recs, int n, uint32_t rebase)
+{
+    if ((size_t)j.n_tu + n > j.tus.cap) return fail(OHCU_EOVERFLOW, "TU arena full (%zu)", j.tus.cap);
+    for (int i = 0; i < n; i++) {
+        ohcu_tu tu = recs[i];
+        const int l = tu.log2_size - 2;
+        if (l < 0 || l > 3 || tu.c_idx > 2 || (tu.c_idx && !c->sp.chroma_format_idc) || tu.mode > OHCU_TU_BYPASS ||
+            (tu.mode == OHCU_TU_DST4 && l != 0))
+            return fail(OHCU_EINVAL, "TU record %d is malformed", j.n_tu + i);
+        const int n1 = 1 << tu.log2_size;
+        if (tu.x0 + n1 > c->pw[tu.c_idx] || tu.y0 + n1 > c->ph[tu.c_idx])
+            return fail(OHCU_EINVAL, "TU record %d lies outside plane %d", j.n_tu + i, tu.c_idx);
+        tu.coeff_off += rebase;
+        if ((size_t)tu.coeff_off + (size_t)n1 * n1 > j.ncoeff || (tu.coeff_off & 1))
+            return fail(OHCU_EINVAL, "TU record %d: coefficient block outside the arena", j.n_tu + i);
+        j.tus.h[j.n_tu + i] = tu;
+        j.bins[l].h[j.n_bin[l]++] = (uint32_t)(j.n_tu + i);
+    }
+    j.n_tu += n;
+    return 0;
+}
+
+extern "C" int ohcu_append_tu(ohcu_ctx *c, int job, const ohcu_tu *recs, int n, const int16_t *coeffs, size_t ncoeff)
+{
+    OPEN_JOB(c, job);
+    if (n < 0 || (n && (!recs || !coeffs))) return fail(OHCU_EINVAL, "bad TU list");
+    if (j.ncoeff + ncoeff > j.coeffs.cap) return fail(OHCU_EOVERFLOW, "coefficient arena full (%zu)", j.coeffs.cap);
+    if (j.ncoeff + ncoeff > 0xffffffffull) return fail(OHCU_EOVERFLOW, "coefficient offsets exceed 32 bits");
+    const uint32_t base = (uint32_t)j.ncoeff;
+    memcpy(j.coeffs.h + j.ncoeff, coeffs, ncoeff * sizeof(int16_t));
+    j.ncoeff += ncoeff;
+    return add_tus(c, j, recs, n, base);
+}
+
+extern "C" int ohcu_reserve_coeffs(ohcu_ctx *c, int job, size_t ncoeff, int16_t **ptr, uint32_t *arena_off)
+{
+    OPEN_JOB(c, job);
+    if (!ptr || !arena_off) return fail(OHCU_EINVAL, "null argument");
+    ncoeff = (ncoeff + 7) & ~(size_t)7;              // keep blocks 16-byte aligned
+    if (j.ncoeff + ncoeff > j.coeffs.cap) return fail(OHCU_EOVERFLOW, "coefficient arena full (%zu)", j.coeffs.cap);
+    *ptr = j.coeffs.h + j.ncoeff;
+    *arena_off = (uint32_t)j.ncoeff;
+    j.ncoeff += ncoeff;
+    return 0;
+}
+
+extern "C" int ohcu_append_tu_inplace(ohcu_ctx *c, int job, const ohcu_tu *recs, int n)
+{
+    OPEN_JOB(c, job);
+    if (n < 0 || (n && !recs)) return fail(OHCU_EINVAL, "bad TU list");
+    return add_tus(c, j, recs, n, 0);
+}
+
+extern "C" int ohcu_set_deblock(ohcu_ctx *c, int job, const ohcu_deblock_in *in)
+{
+    OPEN_JOB(c, job);
+    if (!in || !in->vertical_bs || !in->horizontal_bs || !in->qp_y_tab || !in->deblock)
+        return fail(OHCU_EINVAL, "null deblock input");
+    memcpy(j.vbs.h, in->vertical_bs, (size_t)c->bs_w * c->bs_h);
+    memcpy(j.hbs.h, in->horizontal_bs, (size_t)c->bs_w * c->bs_h);
+    memcpy(j.qp.h, in->qp_y_tab, (size_t)c->min_cb_w * c->min_cb_h);
+    memcpy(j.db.h, in->deblock, sizeof(ohcu_dbparams) * c->nctb);
+    j.has_pcm = c->sp.pcm_or_bypass && in->is_pcm;
+    if (j.has_pcm) memcpy(j.is_pcm.h, in->is_pcm, (size_t)c->min_pu_w * c->min_pu_h);
+    j.has_deblock = true;
+    return 0;
+}
+
+// per-CTB restore flags of sao_filter_CTB (hevc_filter.c:277-325)
+extern "C" int ohcu_set_sao(ohcu_ctx *c, int job, const ohcu_sao_in *in)
+{
+    OPEN_JOB(c, job);
+    if (!in || !in->sao) return fail(OHCU_EINVAL, "null SAO input");
+    memcpy(j.sao.h, in->sao, sizeof(ohcu_sao) * c->nctb);
+    const int cw = c->ctb_w, chh = c->ctb_h;
+    const bool no_tile = c->sp.no_tile_filter != 0;
+    for (int y = 0; y < chh; y++)
+        for (int x = 0; x < cw; x++) {
+            const int rs = y * cw + x;
+            const bool lfase = in->filter_slice_edges ? in->filter_slice_edges[rs] != 0 : true;
+            unsigned fl = 0;
+            if (no_tile || !lfase) {
+                fl |= SAOF_RESTORE;
+                auto slice_at = [&](int dx, int dy) { return in->tab_slice_address ? in->tab_slice_address[rs + dy * cw + dx] : 0; };
+                auto tile_at = [&](int dx, int dy) { return in->tile_id ? in->tile_id[rs + dy * cw + dx] : 0; };
+                auto dslice = [&](int dx, int dy) { return !lfase && slice_at(0, 0) != slice_at(dx, dy); };
+                auto dtile = [&](int dx, int dy) { return no_tile && tile_at(0, 0) != tile_at(dx, dy); };
+                const bool e0 = x == 0, e1 = y == 0, e2 = x == cw - 1, e3 = y == chh - 1;
+                bool lt = false, rt = false, ut = false, bt = false;
+                if (!e0) { lt = dtile(-1, 0); if (dslice(-1, 0) || lt) fl |= SAOF_VERT0; }
+                if (!e2) { rt = dtile(1, 0);  if (dslice(1, 0) || rt)  fl |= SAOF_VERT1; }
+                if (!e1) { ut = dtile(0, -1); if (dslice(0, -1) || ut) fl |= SAOF_HORIZ0; }
+                if (!e3) { bt = dtile(0, 1);  if (dslice(0, 1) || bt)  fl |= SAOF_HORIZ1; }
+                if (!e0 && !e1 && (dslice(-1, -1) || lt || ut)) fl |= SAOF_DIAG0;
+                if (!e1 && !e2 && (dslice(1, -1) || rt || ut))  fl |= SAOF_DIAG1;
+                if (!e2 && !e3 && (dslice(1, 1) || rt || bt))   fl |= SAOF_DIAG2;
+                if (!e0 && !e3 && (dslice(-1, 1) || lt || bt))  fl |= SAOF_DIAG3;
+            }
+            j.sao_flags.h[rs] = (uint16_t)fl;
+        }
+    j.has_sao = true;
+    return 0;
+}
+
+// ------------------------------------------------------------------ stage / launch
+// PUs of one CTB must be contiguous for the CTB-per-CTA MC kernel.  Decoders emit them
+// that way (hls_decode_entry walks CTBs); other orders get a stable counting sort here.
+static void sort_pus_by_ctb(ohcu_ctx *c, Job &j)
+{
+    const int l2 = c->sp.log2_ctb_size;
+    std::vector<ohcu_pu> tmp(j.pus.h, j.pus.h + j.n_pu);
+    int2 *range = j.ctb_range.h;
+    int acc = 0;
+    for (int i = 0; i < c->nctb; i++) { range[i].x = acc; acc += range[i].y; range[i].y = 0; }
+    for (const ohcu_pu &pu : tmp) {
+        const int ctb = (pu.x0 >> l2) + (pu.y0 >> l2) * c->ctb_w;
+        j.pus.h[range[ctb].x + range[ctb].y++] = pu;
+    }
+    j.pu_sorted = true;
+}
+
+extern "C" int ohcu_frame_stage(ohcu_ctx *c, int job)
+{
+    OPEN_JOB(c, job);
+    if (!j.pu_sorted) sort_pus_by_ctb(c, j);
+    for (int i = 0; i < j.n_pu; i++)
+        if (j.pus.h[i].slice >= j.n_slices) return fail(OHCU_EINVAL, "PU %d uses slice %d which was never set", i, j.pus.h[i].slice);
+    for (int i = 0; i < j.n_tu; i++)
+        if ((j.tus.h[i].flags & OHCU_TUF_CROSS) &&
+            (j.tus.h[i].cross_tu >= (uint32_t)j.n_tu || j.tus.h[j.tus.h[i].cross_tu].log2_size != j.tus.h[i].log2_size))
+            return fail(OHCU_EINVAL, "TU %d: bad cross-component reference", i);
+    cudaStream_t st = j.stream;
+    CU(push_arena(j.pus, j.n_pu, st));
+    CU(push_arena(j.ctb_range, c->nctb, st));
+    CU(push_arena(j.slices, j.n_slices, st));
+    CU(push_arena(j.tus, j.n_tu, st));
+    CU(push_arena(j.coeffs, j.ncoeff, st));
+    for (int i = 0; i < 4; i++) CU(push_arena(j.bins[i], j.n_bin[i], st));
+    if (j.has_deblock) {
+        CU(push_arena(j.vbs, (size_t)c->bs_w * c->bs_h, st));
+        CU(push_arena(j.hbs, (size_t)c->bs_w * c->bs_h, st));
+        CU(push_arena(j.qp, (size_t)c->min_cb_w * c->min_cb_h, st));
+        CU(push_arena(j.db, c->nctb, st));
+    }
+    if (j.has_pcm) CU(push_arena(j.is_pcm, (size_t)c->min_pu_w * c->min_pu_h, st));
+    if (j.has_sao) {
+        CU(push_arena(j.sao, c->nctb, st));
+        CU(push_arena(j.sao_flags, c->nctb, st));
+    }
+    j.open = false;
+    j.staged = true;
+    // the pinned staging is reusable once this event has fired
+    CU(cudaEventRecord(j.done, st));
+    j.has_done = true;
+    return 0;
+}
+
+static void fill_frame_dev(const ohcu_ctx *c, const Job &j, FrameDev *f)
+{
+    memset(f, 0, sizeof(*f));
+    const ohcu_seq_params &sp = c->sp;
+    f->width = sp.width; f->height = sp.height; f->bd = sp.bit_depth; f->cfi = sp.chroma_format_idc;
+    f->hs = c->hs; f->vs = c->vs;
+    f->log2_ctb = sp.log2_ctb_size; f->ctb_w = c->ctb_w; f->ctb_h = c->ctb_h;
+    f->log2_min_cb = sp.log2_min_cb_size; f->min_cb_w = c->min_cb_w;
+    f->log2_min_pu = sp.log2_min_pu_size; f->min_pu_w = c->min_pu_w; f->min_pu_h = c->min_pu_h;
+    f->bs_width = c->bs_w;
+    f->pcm_or_bypass = sp.pcm_or_bypass; f->cb_qp_offset = sp.cb_qp_offset; f->cr_qp_offset = sp.cr_qp_offset;
+    f->nplanes = c->nplanes;
+    for (int i = 0; i < 3; i++) { f->pw[i] = c->pw[i]; f->ph[i] = c->ph[i]; }
+    for (size_t i = 0; i < c->slots.size(); i++) f->dpb[i] = c->slots[i].pic.ps;
+    f->pus = j.pus.d; f->n_pu = j.n_pu; f->ctb_pu_range = j.ctb_range.d; f->slices = j.slices.d;
+    f->tus = j.tus.d; f->n_tu = j.n_tu; f->coeffs = j.coeffs.d;
+    for (int i = 0; i < 4; i++) { f->tu_bin[i] = j.bins[i].d; f->n_bin[i] = j.n_bin[i]; }
+    f->vbs = j.has_deblock ? j.vbs.d : nullptr; f->hbs = j.hbs.d; f->qp_y = j.qp.d; f->db = j.db.d;
+    f->is_pcm = j.has_pcm ? j.is_pcm.d : nullptr;
+    f->sao = j.has_sao ? j.sao.d : nullptr; f->sao_ctb_flags = j.sao_flags.d;
+}
+
+// stages: bit mask 1 MC, 2 residual, 4 deblock, 8 SAO (0 = all).  Test / bench hook behind
+// ohcu_frame_launch; when MC is excluded the slot's current content is the starting picture.
+extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int stages)
+{
+    ENTER(c);
+    if (check_job(c, job)) return OHCU_EINVAL;
+    Job &j = c->jobs[job];
+    if (!j.staged) return fail(OHCU_ESTATE, "job %d has no staged lists", job);
+    if (out_slot < 0) out_slot = j.out_slot;
+    if (check_slot(c, out_slot)) return OHCU_EINVAL;
+    if (!stages) stages = 15;
+    cudaStream_t st = j.stream;
+    Slot &os = c->slots[out_slot];
+
+    // ---- ordering between frames: replaces ff_thread_await_progress (hevcdec.c:2051-2058).
+    // Readers: every slot the slice tables name.  Writer: wait for earlier readers/downloads.
+    uint32_t ref_mask = 0;
+    if (stages & 1)
+        for (int s = 0; s < j.n_slices; s++)
+            for (int l = 0; l < 2; l++)
+                for (int r = 0; r < OHCU_MAX_REFS; r++) {
+                    const int slot = j.slices.h[s].ref_slot[l][r];
+                    if (slot < (int)c->slots.size()) ref_mask |= 1u << slot;
+                }
+    if (ref_mask & (1u << out_slot)) ref_mask &= ~(1u << out_slot);   // a picture never references itself
+    for (size_t s = 0; s < c->slots.size(); s++)
+        if ((ref_mask >> s) & 1) {
+            if (c->slots[s].has_ready) CU(cudaStreamWaitEvent(st, c->slots[s].ready, 0));
+            c->slots[s].readers |= 1ull << job;
+        }
+    for (size_t k = 0; k < c->jobs.size(); k++)
+        if (((os.readers >> k) & 1) && (int)k != job && c->jobs[k].has_done)
+            CU(cudaStreamWaitEvent(st, c->jobs[k].done, 0));
+    os.readers = 0;
+    if (os.has_ready) CU(cudaStreamWaitEvent(st, os.ready, 0));
+    if (os.has_read) CU(cudaStreamWaitEvent(st, os.read_done, 0));
+
+    FrameDev f;
+    fill_frame_dev(c, j, &f);
+    const bool do_sao = c->sp.sao_enabled && j.has_sao && (stages & 8);
+    f.out = os.pic.ps;
+    f.work = do_sao ? j.recon.ps : os.pic.ps;
+    const bool timed = c->profiling;
+    int n, total = 0;
+#define STAGE_EVENT(i) do { if (timed) CU(cudaEventRecord(j.ev[i], st)); } while (0)
+#define LAUNCHED(call) do { n = (call); if (n < 0) return fail(OHCU_EINVAL, "launch refused"); total += n; \
+        CU(cudaGetLastError()); } while (0)
+    STAGE_EVENT(0);
+    if (!(stages & 1) && do_sao) LAUNCHED(launch_copy_picture(f, f.work, f.out, st));
+    if (stages & 1) LAUNCHED(launch_mc(f, st));
+    STAGE_EVENT(1);
+    if (stages & 2) LAUNCHED(launch_residual(f, st));
+    STAGE_EVENT(2);
+    if ((stages & 4) && j.has_deblock) LAUNCHED(launch_deblock(f, st));
+    STAGE_EVENT(3);
+    if (do_sao) LAUNCHED(launch_sao(f, st));
+    STAGE_EVENT(4);
+#undef STAGE_EVENT
+#undef LAUNCHED
+    j.timed = timed;
+    c->launches += total;
+    CU(cudaEventRecord(j.done, st));
+    j.has_done = true;
+    CU(cudaEventRecord(os.ready, st));
+    os.has_ready = true;
+    return 0;
+}
+
+extern "C" int ohcu_frame_launch(ohcu_ctx *c, int job, int out_slot)
+{
+    return ohcu_frame_launch_stages(c, job, out_slot, 0);
+}
+
+extern "C" int ohcu_frame_flush(ohcu_ctx *c, int job)
+{
+    int rc = ohcu_frame_stage(c, job);
+    if (rc) return rc;
+    return ohcu_frame_launch_stages(c, job, -1, 0);
+}
+
+extern "C" int ohcu_frame_sync(ohcu_ctx *c, int job)
+{
+    ENTER(c);
+    if (check_job(c, job)) return OHCU_EINVAL;
+    CU(cudaStreamSynchronize(c->jobs[job].stream));
+    return 0;
+}
+
+extern "C" int ohcu_sync_all(ohcu_ctx *c)
+{
+    ENTER(c);
+    CU(cudaDeviceSynchronize());
+    return 0;
+}
+
+// ------------------------------------------------------------------ measurement hooks
+extern "C" int ohcu_set_profiling(ohcu_ctx *c, int enable)
+{
+    if (!c) return fail(OHCU_EINVAL, "null context");
+    c->profiling = enable != 0;
+    return 0;
+}
+
+extern "C" int ohcu_job_stage_ms(ohcu_ctx *c, int job, float ms[OHCU_NUM_STAGES])
+{
+    ENTER(c);
+    if (check_job(c, job)) return OHCU_EINVAL;
+    Job &j = c->jobs[job];
+    if (!j.timed) return fail(OHCU_ESTATE, "job %d was not launched with profiling enabled", job);
+    CU(cudaEventSynchronize(j.ev[4]));
+    for (int i = 0; i < 4; i++) CU(cudaEventElapsedTime(&ms[i], j.ev[i], j.ev[i + 1]));
+    CU(cudaEventElapsedTime(&ms[OHCU_STAGE_TOTAL], j.ev[0], j.ev[4]));
+    return 0;
+}
+
+extern "C" int64_t ohcu_kernel_launches(const ohcu_ctx *c) { return c ? c->launches : 0; }
+
+extern "C" void *ohcu_job_stream(ohcu_ctx *c, int job)
+{
+    if (!c || job < 0 || job >= (int)c->jobs.size()) return nullptr;
+    return (void *)c->jobs[job].stream;
+}
+
+extern "C" int ohcu_flush_l2(ohcu_ctx *c)
+{
+    ENTER(c);
+    if (!c->l2_buf) {
+        c->l2_bytes = (size_t)256 << 20;          // > 126 MB L2
+        CU(cudaMalloc(&c->l2_buf, c->l2_bytes));
+        CU(cudaMemset(c->l2_buf, 0, c->l2_bytes));
+    }
+    CU(cudaDeviceSynchronize());
+    launch_l2_flush(c->l2_buf, c->l2_bytes, 0);
+    CU(cudaGetLastError());
+    CU(cudaDeviceSynchronize());
+    return 0;
+}

@@ -1,0 +1,88 @@
+// ohcu_internal.h — device-side parameter blocks and kernel launchers shared by the
+// sm_100a kernels and the C-ABI host layer (api.cu).  Not part of the public ABI.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ohcu.h"
+
+namespace ohcu {
+
+struct PlaneSet {
+    uint8_t *p[3];
+    int pitch[3];          // bytes
+};
+
+// Everything a launch needs, passed by value as one kernel parameter.
+struct FrameDev {
+    // sequence
+    int width, height, bd, cfi, hs, vs;
+    int log2_ctb, ctb_w, ctb_h;
+    int log2_min_cb, min_cb_w;
+    int log2_min_pu, min_pu_w, min_pu_h;
+    int bs_width;
+    int pcm_or_bypass, cb_qp_offset, cr_qp_offset;
+    int nplanes;
+    int pw[3], ph[3];      // plane dimensions in samples
+    // pictures
+    PlaneSet work;         // picture being reconstructed (pre-SAO)
+    PlaneSet out;          // SAO destination (the DPB slot)
+    PlaneSet dpb[OHCU_MAX_DPB];
+    // MC
+    const ohcu_pu *pus;
+    int n_pu;
+    const int2 *ctb_pu_range;     // per CTB (raster): first PU, number of PUs
+    const ohcu_slice_tab *slices;
+    // residual
+    const ohcu_tu *tus;
+    int n_tu;
+    const int16_t *coeffs;
+    const uint32_t *tu_bin[4];    // TU indices by log2_size - 2
+    int n_bin[4];
+    // deblock
+    const uint8_t *vbs, *hbs;
+    const int8_t *qp_y;
+    const ohcu_dbparams *db;
+    const uint8_t *is_pcm;
+    // SAO
+    const ohcu_sao *sao;
+    const uint16_t *sao_ctb_flags;   // per CTB, see SAOF_* below
+};
+
+// per-CTB SAO flags precomputed on the host from slice addresses / tile ids
+// (sao_filter_CTB, hevc_filter.c:277-325)
+enum {
+    SAOF_RESTORE = 1 << 0,    // restore = no_tile_filter || !lfase
+    SAOF_VERT0 = 1 << 1, SAOF_VERT1 = 1 << 2,
+    SAOF_HORIZ0 = 1 << 3, SAOF_HORIZ1 = 1 << 4,
+    SAOF_DIAG0 = 1 << 5, SAOF_DIAG1 = 1 << 6, SAOF_DIAG2 = 1 << 7, SAOF_DIAG3 = 1 << 8,
+};
+
+// kernel launchers (each returns the number of kernels it enqueued, < 0 on error)
+int launch_mc(const FrameDev &f, cudaStream_t st);
+int launch_residual(const FrameDev &f, cudaStream_t st);
+int launch_deblock(const FrameDev &f, cudaStream_t st);
+int launch_sao(const FrameDev &f, cudaStream_t st);
+int launch_copy_picture(const FrameDev &f, const PlaneSet &dst, const PlaneSet &src, cudaStream_t st);
+int launch_l2_flush(void *buf, size_t bytes, cudaStream_t st);
+
+// ---- small device helpers -------------------------------------------------------
+template <int BD> struct Px { typedef uint16_t T; };
+template <> struct Px<8> { typedef uint8_t T; };
+
+__device__ __forceinline__ int clip3i(int v, int lo, int hi) { return min(max(v, lo), hi); }
+template <int BD> __device__ __forceinline__ int clip_px(int v) { return min(max(v, 0), (1 << BD) - 1); }
+__device__ __forceinline__ int clip_s16(int v) { return min(max(v, -32768), 32767); }
+
+}  // namespace ohcu
+
+// dispatch a template<int BD> launcher on the run-time bit depth
+#define OHCU_DISPATCH_BD(bd, CALL)                 \
+    switch (bd) {                                  \
+    case 8:  { constexpr int BD = 8;  CALL; } break; \
+    case 9:  { constexpr int BD = 9;  CALL; } break; \
+    case 10: { constexpr int BD = 10; CALL; } break; \
+    case 12: { constexpr int BD = 12; CALL; } break; \
+    default: return -1;                            \
+    }

@@ -249,6 +249,11 @@ int ohcu_frame_flush(ohcu_ctx *ctx, int job);
 int ohcu_frame_stage(ohcu_ctx *ctx, int job);
 int ohcu_frame_launch(ohcu_ctx *ctx, int job, int out_slot);
 
+/* Test / measurement hook: run only some stages (bit mask 1 MC, 2 residual,
+ * 4 deblock, 8 SAO; 0 = all).  Without MC the slot's current content is the
+ * starting picture.                                                             */
+int ohcu_frame_launch_stages(ohcu_ctx *ctx, int job, int out_slot, int stages);
+
 int ohcu_frame_sync(ohcu_ctx *ctx, int job);
 int ohcu_sync_all(ohcu_ctx *ctx);
 
