@@ -1,0 +1,373 @@
+#!/usr/bin/env python
+"""bench.py — HEVC pixel-reconstruction hot path on B200: Mpixel/s reconstructed per GPU.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload 4k|1080p|8k]
+
+A step = one pass of the hot path (MC -> residual -> deblock -> SAO) over one batch of
+synthetic frames.  Default workload: BASELINE.json configs[2], 3840x2160 Main10 4:2:0 full
+reconstruction with weighted prediction.
+
+  value        whole-job Mpixel/s (luma W*H*frames / s), work lists resident in HBM
+  e2e          same metric through the C ABI with HOST buffers: list upload from pinned
+               memory, kernels, and the reconstructed picture copied back to pinned memory
+  roofline     the dominant kernel (motion compensation) against the measured HBM peak
+  cpu_baseline the reference's own C hevcdsp path (oracle/_ref) on the host cores
+  --impl reference   times that CPU path alone, same metric / config
+
+One process per GPU (torchrun for N > 1), frames sharded across ranks, no collective on
+the data path ("replicas only" sharding of independent frames); timing = max over ranks.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+WORKLOADS = {
+    # name: (width, height, bit_depth, chroma_format_idc, generator overrides, frames per step per GPU)
+    "4k": (3840, 2160, 10, 1, dict(weighted=1), 8),
+    "1080p": (1920, 1080, 8, 1, dict(), 16),
+    "8k": (7680, 4320, 10, 1, dict(weighted=1), 8),
+}
+WORKLOAD_NAMES = {
+    "4k": "3840x2160 Main10 4:2:0 full reconstruction, weighted prediction (BASELINE configs[2])",
+    "1080p": "1920x1080 Main 8-bit 4:2:0 (BASELINE configs[1])",
+    "8k": "7680x4320 Main10 4:2:0, 64 independent frames sharded across GPUs (BASELINE configs[4])",
+}
+N_DISTINCT = 4        # distinct synthetic frames; jobs reuse them round-robin
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get("hbm_gbs", 6650.0), "measured"
+    return 6650.0, "fallback"
+
+
+def make_inputs(workload, rank):
+    from hevc_b200 import synth
+    w, h, bd, cf, kw, _ = WORKLOADS[workload]
+    jobs = [synth.make_job(w, h, bd, cf, seed=3000 + 17 * rank + i, **kw) for i in range(N_DISTINCT)]
+    refs = [synth.make_picture(jobs[0].sp, 7000 + s) for s in range(2)]
+    return jobs, refs
+
+
+def algorithmic_bytes(job):
+    """per stage, bytes that must move once."""
+    sp = job.sp
+    P = 2 if sp.bit_depth > 8 else 1
+    hs = 1 if sp.chroma_format_idc in (1, 2) else 0
+    vs = 1 if sp.chroma_format_idc == 1 else 0
+    nsamp = sp.width * sp.height + (2 * (sp.width >> hs) * (sp.height >> vs) if sp.chroma_format_idc else 0)
+    S = nsamp * P
+    area = job.pus["w"].astype(np.int64) * job.pus["h"]
+    planes_factor = nsamp / (sp.width * sp.height)
+    nref = np.where(job.pus["pred_flag"] == 3, 2, 1)
+    mc = int((area * (1 + nref)).sum() * planes_factor * P)        # read each ref sample once + write pred
+    coded = int((1 << (2 * job.tus["log2_size"].astype(np.int64))).sum())
+    residual = coded * 2 + coded * P * 2                            # int16 coeffs + RMW of the prediction
+    return {"mc": mc, "residual": residual, "deblock": 2 * S, "sao": 2 * S,
+            "pipeline": mc + residual + 4 * S, "S": S}
+
+
+class ClockSampler:
+    def __init__(self, device):
+        self.device = device
+        self.rows = []
+        self.stop = threading.Event()
+        self.th = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.device)], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([x.strip() for x in out.strip().split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.2)
+
+    def __enter__(self):
+        self.th.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.th.join(timeout=6)
+
+    def summary(self):
+        sm = [int(r[0]) for r in self.rows if len(r) >= 6 and r[0].isdigit()]
+        mx = [int(r[1]) for r in self.rows if len(r) >= 6 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": int(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ reference arm
+def cpu_reference(jobs, refs, steps, warmup, max_threads=None):
+    """The reference's own C path (oracle/_ref, else the oracle port) on the host cores.
+    A step = one frame replayed per thread, all threads in parallel."""
+    import oracle_lib
+    from concurrent.futures import ThreadPoolExecutor
+    kind = "reference" if os.path.exists(oracle_lib.REF_SO) or os.path.isdir(oracle_lib.REFERENCE_ROOT) else "port"
+    lib = oracle_lib.Lib("ref" if kind == "reference" else "oracle")
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
+    if max_threads:
+        cores = min(cores, max_threads)
+    dpb = list(refs) + [None] * (jobs[0].sp.dpb_slots - len(refs))
+
+    def one(i):
+        lib.replay(jobs[i % len(jobs)], dpb)
+
+    pool = ThreadPoolExecutor(cores)
+    for _ in range(warmup):
+        list(pool.map(one, range(cores)))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        list(pool.map(one, range(cores)))
+    dt = time.perf_counter() - t0
+    pool.shutdown()
+    sp = jobs[0].sp
+    frames = steps * cores
+    return {"value": frames * sp.width * sp.height / dt / 1e6, "unit": "Mpixel/s", "cores": cores, "kind": kind,
+            "sample": f"{frames} frames ({cores} threads x {steps} steps, one frame per thread per step)",
+            "ms_per_step": dt / steps * 1e3, "seconds": dt}
+
+
+# ------------------------------------------------------------------ our arm
+def run_ours(args, rank, world):
+    from hevc_b200 import abi, backend
+    jobs, refs = make_inputs(args.workload, rank)
+    sp = jobs[0].sp
+    B = WORKLOADS[args.workload][5]
+    if args.frames:
+        B = args.frames
+    device = int(os.environ.get("LOCAL_RANK", 0))
+    hbm_peak, peak_kind = peaks()
+    ctx = backend.Context(sp, device=device, dpb_slots=2 + B, jobs=B)
+    lib, h = ctx.lib, ctx.handle
+    for s in range(2):
+        ctx.upload(s, refs[s])
+
+    def barrier():
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+
+    # ---------------- resident leg: lists staged once, kernels only in the timed region
+    for k in range(B):
+        j = ctx.begin(2 + k)
+        assert j == k
+        ctx.append(j, jobs[k % len(jobs)])
+        ctx.stage(j)
+    ctx.sync()
+    l0 = ctx.kernel_launches()
+    for _ in range(args.warmup):
+        for k in range(B):
+            ctx.launch(k, 2 + k)
+    ctx.sync()
+    barrier()
+    l1 = ctx.kernel_launches()
+    with ClockSampler(device) as clk:
+        ctx.timer_start()
+        for _ in range(args.steps):
+            for k in range(B):
+                ctx.launch(k, 2 + k)
+        ms_resident = ctx.timer_stop()
+    barrier()
+    launches = ctx.kernel_launches() - l1
+    clocks = clk.summary()
+
+    # ---------------- per-stage timing of single frames (events on the job's own stream)
+    ctx.set_profiling(True)
+    stage_ms = np.zeros(abi.NUM_STAGES)
+    nprof = max(4, min(16, args.steps * B))
+    for i in range(nprof):
+        k = i % B
+        ctx.launch(k, 2 + k)
+        ctx.sync(k)
+        stage_ms += np.array(ctx.stage_ms(k))
+    stage_ms /= nprof
+    ctx.set_profiling(False)
+
+    # ---------------- e2e leg: host buffers -> H2D -> kernels -> D2H, through the C ABI
+    outs = [ctx.pinned_picture() for _ in range(B)]
+    h2d = d2h = 0
+
+    def submit(k, copy_coeffs=False):
+        nonlocal h2d, d2h
+        fj = jobs[k % len(jobs)]
+        j = ctx.begin(2 + k)
+        for i in range(len(fj.slices)):
+            tab = abi.SliceTab.from_buffer_copy(fj.slices[i].tobytes())
+            abi.check(lib.ohcu_set_slice(h, j, i, C.byref(tab)))
+        abi.check(lib.ohcu_append_pu(h, j, fj.pus.ctypes.data, len(fj.pus)))
+        # the residual parser writes coefficients straight into the job's pinned arena
+        # (ohcu_reserve_coeffs, lc->tu.coeffs of hevcdec.h:333); the untimed first pass puts
+        # them there, later passes find them in place like a decoder that just parsed them
+        ptr = C.c_void_p(); off = C.c_uint32()
+        abi.check(lib.ohcu_reserve_coeffs(h, j, len(fj.coeffs), C.byref(ptr), C.byref(off)))
+        if copy_coeffs:
+            C.memmove(ptr.value, fj.coeffs.ctypes.data, fj.coeffs.nbytes)
+        abi.check(lib.ohcu_append_tu_inplace(h, j, fj.tus.ctypes.data, len(fj.tus)))
+        d = fj.deblock_in(); s = fj.sao_in()
+        abi.check(lib.ohcu_set_deblock(h, j, C.byref(d)))
+        abi.check(lib.ohcu_set_sao(h, j, C.byref(s)))
+        ctx.flush(j)
+        ctx.download_async(2 + k, outs[k])
+        nctb = len(fj.sao)
+        h2d = (fj.pus.nbytes + 8 * nctb + fj.slices.nbytes + fj.tus.nbytes + fj.coeffs.nbytes + 4 * len(fj.tus) +
+               fj.vbs.nbytes + fj.hbs.nbytes + fj.qp_y_tab.nbytes + fj.deblock.nbytes + fj.sao.nbytes + 2 * nctb)
+        d2h = sum(p.nbytes for p in outs[k])
+
+    for k in range(B):
+        submit(k, copy_coeffs=True)
+    ctx.sync()
+    for _ in range(args.warmup):
+        for k in range(B):
+            submit(k)
+    ctx.sync()
+    for k in range(B):
+        ctx.slot_sync(2 + k)
+    barrier()
+    ctx.timer_start()
+    t_host = time.perf_counter()
+    for _ in range(args.steps):
+        for k in range(B):
+            submit(k)
+    ms_e2e = ctx.timer_stop()
+    t_host = (time.perf_counter() - t_host) * 1e3
+    barrier()
+
+    # ---------------- correctness spot check of what the timed runs produced
+    import oracle_lib
+    check = "skipped"
+    if rank == 0 and not args.no_check and sp.width * sp.height <= 3840 * 2160:
+        want = oracle_lib.Lib("oracle").replay(jobs[0], list(refs) + [None] * (sp.dpb_slots - 2))
+        got = ctx.download(2)
+        check = "bit-exact" if all(np.array_equal(a, b) for a, b in zip(got, want)) and \
+            all(np.array_equal(a, b) for a, b in zip(outs[0], want)) else "MISMATCH"
+
+    # ---------------- reduce over ranks
+    frames_rank = args.steps * B
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        t = torch.tensor([ms_resident, ms_e2e], dtype=torch.float64, device=f"cuda:{device}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_resident, ms_e2e = t.tolist()
+    ctx.close()
+    if rank != 0:
+        return
+    px = sp.width * sp.height
+    total_frames = frames_rank * world
+    value = total_frames * px / (ms_resident * 1e-3) / 1e6
+    e2e_value = total_frames * px / (ms_e2e * 1e-3) / 1e6
+    ab = algorithmic_bytes(jobs[0])
+    mc_ms = float(stage_ms[abi.STAGE_MC])
+    achieved = ab["mc"] / (mc_ms * 1e-3) / 1e9
+    line = {
+        "metric": "Mpixel/s reconstructed per B200 (4K Main10); HBM GB/s vs peak", "value": round(value, 1),
+        "unit": "Mpixel/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(ms_resident / args.steps, 4), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int32 accumulate on u16 samples / int16 coefficients" if sp.bit_depth > 8
+        else "int32 accumulate on u8 samples / int16 coefficients", "data": "synthetic",
+        "config": {"workload": WORKLOAD_NAMES[args.workload], "frames_per_step_per_gpu": B,
+                   "frames_in_flight": B, "distinct_frames": len(jobs), "sharding": "independent frames per GPU, no collective",
+                   "l2": f"inputs larger than L2: {B} frames x ~{(ab['pipeline']) / 1e6:.0f} MB algorithmic traffic per step",
+                   "pus_per_frame": int(len(jobs[0].pus)), "tus_per_frame": int(len(jobs[0].tus)),
+                   "coded_fraction": round(len(jobs[0].coeffs) / (ab['S'] / (2 if sp.bit_depth > 8 else 1)), 3)},
+        "frames_per_s": round(total_frames / (ms_resident * 1e-3), 1),
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "e2e": {"value": round(e2e_value, 1), "unit": "Mpixel/s", "h2d_bytes_per_step": int(h2d * B),
+                "d2h_bytes_per_step": int(d2h * B), "frames_per_s": round(total_frames / (ms_e2e * 1e-3), 1),
+                "host_ms_per_step": round(t_host / args.steps, 3)},
+        "roofline": {"bound": "hbm", "kernel": "mc_kernel (motion compensation)", "achieved": round(achieved, 1),
+                     "peak": hbm_peak, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "unit": "GB/s",
+                     "frac": round(achieved / hbm_peak, 4), "traffic": None,
+                     "algorithmic_bytes_per_launch": int(ab["mc"]), "ms_per_launch": round(mc_ms, 4)},
+        "stages": {name: {"ms": round(float(stage_ms[i]), 4), "algorithmic_mb": round(ab[key] / 1e6, 2),
+                          "gbs": round(ab[key] / (float(stage_ms[i]) * 1e-3) / 1e9, 1) if stage_ms[i] > 0 else None}
+                   for i, (name, key) in enumerate([("mc", "mc"), ("residual", "residual"), ("deblock", "deblock"),
+                                                    ("sao", "sao")])},
+        "pipeline": {"ms_per_frame_single_stream": round(float(stage_ms[abi.STAGE_TOTAL]), 4),
+                     "algorithmic_mb_per_frame": round(ab["pipeline"] / 1e6, 2),
+                     "gbs_at_value": round(ab["pipeline"] * total_frames / world / (ms_resident * 1e-3) / 1e9, 1),
+                     "frac_of_peak_at_value": round(ab["pipeline"] * total_frames / world / (ms_resident * 1e-3) / 1e9 / hbm_peak, 4)},
+        "parity_check": check,
+    }
+    if world == 1 and not args.no_cpu:
+        cb = cpu_reference(jobs, refs, steps=args.cpu_steps, warmup=1)
+        line["cpu_baseline"] = {k: (round(v, 2) if isinstance(v, float) else v) for k, v in cb.items()
+                                if k in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(line))
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    jobs, refs = make_inputs(args.workload, 0)
+    cb = cpu_reference(jobs, refs, steps=args.steps, warmup=args.warmup)
+    sp = jobs[0].sp
+    line = {
+        "impl": "reference", "metric": "Mpixel/s reconstructed per B200 (4K Main10); HBM GB/s vs peak",
+        "value": round(cb["value"], 2), "unit": "Mpixel/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(cb["ms_per_step"], 2), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None,
+        "dtype": "int32 accumulate on u16 samples / int16 coefficients" if sp.bit_depth > 8 else
+        "int32 accumulate on u8 samples / int16 coefficients",
+        "data": "synthetic", "config": {"workload": WORKLOAD_NAMES[args.workload]},
+        "cpu_baseline": {"value": round(cb["value"], 2), "unit": "Mpixel/s", "cores": cb["cores"], "kind": cb["kind"],
+                         "sample": cb["sample"]},
+        "e2e": {"value": round(cb["value"], 2), "unit": "Mpixel/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="4k", choices=list(WORKLOADS))
+    ap.add_argument("--frames", type=int, default=0, help="frames per step per GPU (default per workload)")
+    ap.add_argument("--cpu-steps", type=int, default=2, help="steps of the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-check", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
+        dist.init_process_group("nccl")
+    import __graft_entry__
+    if not os.path.exists(__graft_entry__.LIB):
+        __graft_entry__.build()
+    run_ours(args, rank, world)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

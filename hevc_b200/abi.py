@@ -124,6 +124,10 @@ SYMBOLS = {
     "ohcu_kernel_launches": (C.c_int64, [_P]),
     "ohcu_job_stream": (_P, [_P, C.c_int]),
     "ohcu_flush_l2": (C.c_int, [_P]),
+    "ohcu_timer_start": (C.c_int, [_P]),
+    "ohcu_timer_stop": (C.c_int, [_P, C.POINTER(C.c_float)]),
+    "ohcu_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
+    "ohcu_host_free": (C.c_int, [_P]),
 }
 
 _lib = None

@@ -121,6 +121,26 @@ class Context:
     def flush_l2(self):
         check(self.lib.ohcu_flush_l2(self.handle), "ohcu_flush_l2")
 
+    def timer_start(self):
+        check(self.lib.ohcu_timer_start(self.handle), "ohcu_timer_start")
+
+    def timer_stop(self):
+        ms = C.c_float()
+        check(self.lib.ohcu_timer_stop(self.handle, C.byref(ms)), "ohcu_timer_stop")
+        return ms.value
+
+    def pinned_picture(self):
+        """Output picture in pinned host memory (for download_async)."""
+        planes = []
+        for c in range(self.nplanes):
+            h, w = self.plane_shape(c)
+            nbytes = h * w * np.dtype(self.dtype).itemsize
+            p = C.c_void_p()
+            check(self.lib.ohcu_host_alloc(nbytes, C.byref(p)), "ohcu_host_alloc")
+            buf = (C.c_char * nbytes).from_address(p.value)
+            planes.append(np.frombuffer(buf, dtype=self.dtype).reshape(h, w))
+        return planes
+
     # ---- convenience: one frame, synchronously (tests, smoke) -----------------
     def reconstruct(self, fj, refs, out_slot=None, out_init=None, stages=0, use_deblock=True, use_sao=True):
         """Upload refs to slots 0.., run one frame job, return the reconstructed planes."""

@@ -92,6 +92,7 @@ struct ohcu_ctx {
     int64_t launches = 0;
     void *l2_buf = nullptr;
     size_t l2_bytes = 0;
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
 };
 
 // ------------------------------------------------------------------ helpers
@@ -174,6 +175,8 @@ extern "C" int ohcu_destroy(ohcu_ctx *c)
     }
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->l2_buf) cudaFree(c->l2_buf);
+    if (c->t0) cudaEventDestroy(c->t0);
+    if (c->t1) cudaEventDestroy(c->t1);
     delete c;
     return 0;
 }
@@ -710,5 +713,41 @@ extern "C" int ohcu_flush_l2(ohcu_ctx *c)
     launch_l2_flush(c->l2_buf, c->l2_bytes, 0);
     CU(cudaGetLastError());
     CU(cudaDeviceSynchronize());
+    return 0;
+}
+
+extern "C" int ohcu_timer_start(ohcu_ctx *c)
+{
+    ENTER(c);
+    if (!c->t0) { CU(cudaEventCreate(&c->t0)); CU(cudaEventCreate(&c->t1)); }
+    CU(cudaDeviceSynchronize());
+    CU(cudaEventRecord(c->t0, c->copy_stream));
+    // nothing enqueued afterwards may start before the start event
+    for (auto &j : c->jobs) CU(cudaStreamWaitEvent(j.stream, c->t0, 0));
+    return 0;
+}
+
+extern "C" int ohcu_timer_stop(ohcu_ctx *c, float *ms)
+{
+    ENTER(c);
+    if (!c->t0 || !ms) return fail(OHCU_ESTATE, "timer not started");
+    for (auto &j : c->jobs)
+        if (j.has_done) CU(cudaStreamWaitEvent(c->copy_stream, j.done, 0));
+    CU(cudaEventRecord(c->t1, c->copy_stream));
+    CU(cudaEventSynchronize(c->t1));
+    CU(cudaEventElapsedTime(ms, c->t0, c->t1));
+    return 0;
+}
+
+extern "C" int ohcu_host_alloc(size_t bytes, void **ptr)
+{
+    if (!ptr) return fail(OHCU_EINVAL, "null argument");
+    CU(cudaHostAlloc(ptr, bytes ? bytes : 1, cudaHostAllocDefault));
+    return 0;
+}
+
+extern "C" int ohcu_host_free(void *ptr)
+{
+    if (ptr) CU(cudaFreeHost(ptr));
     return 0;
 }

@@ -274,6 +274,15 @@ int64_t ohcu_kernel_launches(const ohcu_ctx *ctx);
 void *ohcu_job_stream(ohcu_ctx *ctx, int job);
 /* Write >L2-size scratch so the next launch starts cold. */
 int ohcu_flush_l2(ohcu_ctx *ctx);
+/* Device-side wall clock over everything enqueued on every job stream between the
+ * two calls: start synchronises the device and records an event; stop makes a
+ * timing stream wait for every job's last event, records, synchronises and
+ * returns the elapsed milliseconds.                                              */
+int ohcu_timer_start(ohcu_ctx *ctx);
+int ohcu_timer_stop(ohcu_ctx *ctx, float *ms);
+/* Pinned host memory for callers without their own allocator (output pictures). */
+int ohcu_host_alloc(size_t bytes, void **ptr);
+int ohcu_host_free(void *ptr);
 
 #ifdef __cplusplus
 }
