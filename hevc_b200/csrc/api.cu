@@ -7,14 +7,12 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <new>
 #include <vector>
 
 #include "ohcu_internal.h"
 
-namespace ohcu {
-int upload_dct_table();
-}
 using namespace ohcu;
 
 // ------------------------------------------------------------------ errors
@@ -69,9 +67,12 @@ struct Job {
     Arena<int2> ctb_range;   // per CTB: first PU, count
     bool pu_sorted = true;   int last_ctb = -1;
     Arena<ohcu_slice_tab> slices; int n_slices = 0;
+    std::vector<int> ctb_area;   // luma samples covered by PUs, per CTB
+    bool all_covered = false;
     Arena<ohcu_tu> tus;      int n_tu = 0;
+    Arena<int2> ctb_tu_range;    // per CTB: first TU, count
+    bool tu_sorted = true;   int last_tu_ctb = -1;
     Arena<int16_t> coeffs;   size_t ncoeff = 0;
-    Arena<uint32_t> bins[4]; int n_bin[4] = {0, 0, 0, 0};
     Arena<uint8_t> vbs, hbs, is_pcm; Arena<int8_t> qp; Arena<ohcu_dbparams> db;
     Arena<ohcu_sao> sao;     Arena<uint16_t> sao_flags;
     bool has_deblock = false, has_sao = false, has_pcm = false;
@@ -165,8 +166,7 @@ extern "C" int ohcu_destroy(ohcu_ctx *c)
     for (auto &j : c->jobs) {
         if (j.recon.base) cudaFree(j.recon.base);
         free_arena(&j.pus); free_arena(&j.ctb_range); free_arena(&j.slices); free_arena(&j.tus);
-        free_arena(&j.coeffs);
-        for (int i = 0; i < 4; i++) free_arena(&j.bins[i]);
+        free_arena(&j.coeffs); free_arena(&j.ctb_tu_range);
         free_arena(&j.vbs); free_arena(&j.hbs); free_arena(&j.is_pcm); free_arena(&j.qp); free_arena(&j.db);
         free_arena(&j.sao); free_arena(&j.sao_flags);
         if (j.done) cudaEventDestroy(j.done);
@@ -241,7 +241,7 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
 #define TRY(x) do { rc = (x); if (rc) { ohcu_destroy(c); return rc; } } while (0)
 #define TRYCU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { ohcu_destroy(c); \
         return fail(e_ == cudaErrorMemoryAllocation ? OHCU_ENOMEM : OHCU_ECUDA, "%s -> %s", #x, cudaGetErrorString(e_)); } } while (0)
-    if (upload_dct_table()) { ohcu_destroy(c); return fail(OHCU_ECUDA, "constant upload failed"); }
+    if (upload_dct_table() || upload_mc_taps()) { ohcu_destroy(c); return fail(OHCU_ECUDA, "constant upload failed"); }
     c->slots.resize(sp->dpb_slots);
     for (auto &s : c->slots) {
         TRY(alloc_picture(c, &s.pic));
@@ -259,7 +259,8 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
         TRY(alloc_arena(&j.slices, OHCU_MAX_SLICES));
         TRY(alloc_arena(&j.tus, c->sp.max_tus));
         TRY(alloc_arena(&j.coeffs, (size_t)c->sp.max_coeffs));
-        for (int i = 0; i < 4; i++) TRY(alloc_arena(&j.bins[i], c->sp.max_tus));
+        TRY(alloc_arena(&j.ctb_tu_range, c->nctb));
+        j.ctb_area.assign(c->nctb, 0);
         TRY(alloc_arena(&j.vbs, (size_t)c->bs_w * c->bs_h));
         TRY(alloc_arena(&j.hbs, (size_t)c->bs_w * c->bs_h));
         TRY(alloc_arena(&j.qp, (size_t)c->min_cb_w * c->min_cb_h));
@@ -352,9 +353,11 @@ extern "C" int ohcu_frame_begin(ohcu_ctx *c, int out_slot, int poc)
     j.out_slot = out_slot; j.poc = poc;
     j.n_pu = 0; j.n_tu = 0; j.ncoeff = 0; j.n_slices = 0;
     j.pu_sorted = true; j.last_ctb = -1;
-    for (int i = 0; i < 4; i++) j.n_bin[i] = 0;
+    j.tu_sorted = true; j.last_tu_ctb = -1;
     j.has_deblock = j.has_sao = j.has_pcm = false;
     memset(j.ctb_range.h, 0, sizeof(int2) * c->nctb);
+    memset(j.ctb_tu_range.h, 0, sizeof(int2) * c->nctb);
+    std::fill(j.ctb_area.begin(), j.ctb_area.end(), 0);
     return id;
 }
 
@@ -393,6 +396,7 @@ extern "C" int ohcu_append_pu(ohcu_ctx *c, int job, const ohcu_pu *recs, int n)
             j.last_ctb = ctb;
         }
         range[ctb].y++;
+        j.ctb_area[ctb] += pu.w * pu.h;
         j.pus.h[j.n_pu + i] = pu;
     }
     j.n_pu += n;
@@ -402,6 +406,7 @@ extern "C" int ohcu_append_pu(ohcu_ctx *c, int job, const ohcu_pu *recs, int n)
 static int add_tus(ohcu_ctx *c, Job &j, const ohcu_tu *recs, int n, uint32_t rebase)
 {
     if ((size_t)j.n_tu + n > j.tus.cap) return fail(OHCU_EOVERFLOW, "TU arena full (%zu)", j.tus.cap);
+    int2 *range = j.ctb_tu_range.h;
     for (int i = 0; i < n; i++) {
         ohcu_tu tu = recs[i];
         const int l = tu.log2_size - 2;
@@ -414,8 +419,16 @@ static int add_tus(ohcu_ctx *c, Job &j, const ohcu_tu *recs, int n, uint32_t reb
         tu.coeff_off += rebase;
         if ((size_t)tu.coeff_off + (size_t)n1 * n1 > j.ncoeff || (tu.coeff_off & 1))
             return fail(OHCU_EINVAL, "TU record %d: coefficient block outside the arena", j.n_tu + i);
+        // CTB of the block (plane samples -> luma samples)
+        const int ths = tu.c_idx ? c->hs : 0, tvs = tu.c_idx ? c->vs : 0;
+        const int ctb = ((tu.x0 << ths) >> c->sp.log2_ctb_size) + ((tu.y0 << tvs) >> c->sp.log2_ctb_size) * c->ctb_w;
+        if (ctb != j.last_tu_ctb) {
+            if (range[ctb].y != 0) j.tu_sorted = false;      // CTB seen before: list not grouped
+            else range[ctb].x = j.n_tu + i;
+            j.last_tu_ctb = ctb;
+        }
+        range[ctb].y++;
         j.tus.h[j.n_tu + i] = tu;
-        j.bins[l].h[j.n_bin[l]++] = (uint32_t)(j.n_tu + i);
     }
     j.n_tu += n;
     return 0;
@@ -520,10 +533,48 @@ static void sort_pus_by_ctb(ohcu_ctx *c, Job &j)
     j.pu_sorted = true;
 }
 
+// Same for the TBs of one CTB (fused MC + residual runs one CTA per CTB).  cross_tu
+// references are frame-list indices and follow their block.
+static void sort_tus_by_ctb(ohcu_ctx *c, Job &j)
+{
+    const int l2 = c->sp.log2_ctb_size;
+    std::vector<ohcu_tu> tmp(j.tus.h, j.tus.h + j.n_tu);
+    std::vector<uint32_t> new_index(j.n_tu);
+    int2 *range = j.ctb_tu_range.h;
+    int acc = 0;
+    for (int i = 0; i < c->nctb; i++) { range[i].x = acc; acc += range[i].y; range[i].y = 0; }
+    for (int i = 0; i < j.n_tu; i++) {
+        const ohcu_tu &tu = tmp[i];
+        const int ths = tu.c_idx ? c->hs : 0, tvs = tu.c_idx ? c->vs : 0;
+        const int ctb = ((tu.x0 << ths) >> l2) + ((tu.y0 << tvs) >> l2) * c->ctb_w;
+        new_index[i] = (uint32_t)(range[ctb].x + range[ctb].y++);
+        j.tus.h[new_index[i]] = tu;
+    }
+    for (int i = 0; i < j.n_tu; i++)
+        if ((j.tus.h[i].flags & OHCU_TUF_CROSS) && j.tus.h[i].cross_tu < (uint32_t)j.n_tu)
+            j.tus.h[i].cross_tu = new_index[j.tus.h[i].cross_tu];
+    j.tu_sorted = true;
+}
+
 extern "C" int ohcu_frame_stage(ohcu_ctx *c, int job)
 {
     OPEN_JOB(c, job);
     if (!j.pu_sorted) sort_pus_by_ctb(c, j);
+    if (!j.tu_sorted) sort_tus_by_ctb(c, j);
+    // CTBs whose PUs cover all of their samples need no read of the picture before MC
+    {
+        const int cs = 1 << c->sp.log2_ctb_size;
+        j.all_covered = j.n_pu > 0;
+        for (int y = 0; y < c->ctb_h; y++)
+            for (int x = 0; x < c->ctb_w; x++) {
+                const int rs = y * c->ctb_w + x;
+                const int area = std::min(cs, c->sp.width - x * cs) * std::min(cs, c->sp.height - y * cs);
+                int2 &r = j.ctb_range.h[rs];
+                r.y &= ~CTB_COVERED;
+                if (j.ctb_area[rs] == area) r.y |= CTB_COVERED;
+                else j.all_covered = false;
+            }
+    }
     for (int i = 0; i < j.n_pu; i++)
         if (j.pus.h[i].slice >= j.n_slices) return fail(OHCU_EINVAL, "PU %d uses slice %d which was never set", i, j.pus.h[i].slice);
     for (int i = 0; i < j.n_tu; i++)
@@ -536,7 +587,7 @@ extern "C" int ohcu_frame_stage(ohcu_ctx *c, int job)
     CU(push_arena(j.slices, j.n_slices, st));
     CU(push_arena(j.tus, j.n_tu, st));
     CU(push_arena(j.coeffs, j.ncoeff, st));
-    for (int i = 0; i < 4; i++) CU(push_arena(j.bins[i], j.n_bin[i], st));
+    CU(push_arena(j.ctb_tu_range, c->nctb, st));
     if (j.has_deblock) {
         CU(push_arena(j.vbs, (size_t)c->bs_w * c->bs_h, st));
         CU(push_arena(j.hbs, (size_t)c->bs_w * c->bs_h, st));
@@ -571,8 +622,7 @@ static void fill_frame_dev(const ohcu_ctx *c, const Job &j, FrameDev *f)
     for (int i = 0; i < 3; i++) { f->pw[i] = c->pw[i]; f->ph[i] = c->ph[i]; }
     for (size_t i = 0; i < c->slots.size(); i++) f->dpb[i] = c->slots[i].pic.ps;
     f->pus = j.pus.d; f->n_pu = j.n_pu; f->ctb_pu_range = j.ctb_range.d; f->slices = j.slices.d;
-    f->tus = j.tus.d; f->n_tu = j.n_tu; f->coeffs = j.coeffs.d;
-    for (int i = 0; i < 4; i++) { f->tu_bin[i] = j.bins[i].d; f->n_bin[i] = j.n_bin[i]; }
+    f->tus = j.tus.d; f->n_tu = j.n_tu; f->coeffs = j.coeffs.d; f->ctb_tu_range = j.ctb_tu_range.d;
     f->vbs = j.has_deblock ? j.vbs.d : nullptr; f->hbs = j.hbs.d; f->qp_y = j.qp.d; f->db = j.db.d;
     f->is_pcm = j.has_pcm ? j.is_pcm.d : nullptr;
     f->sao = j.has_sao ? j.sao.d : nullptr; f->sao_ctb_flags = j.sao_flags.d;
@@ -626,10 +676,11 @@ extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int 
 #define LAUNCHED(call) do { n = (call); if (n < 0) return fail(OHCU_EINVAL, "launch refused"); total += n; \
         CU(cudaGetLastError()); } while (0)
     STAGE_EVENT(0);
-    if (!(stages & 1) && do_sao) LAUNCHED(launch_copy_picture(f, f.work, f.out, st));
-    if (stages & 1) LAUNCHED(launch_mc(f, st));
+    // samples this launch does not predict keep the slot's current content
+    if ((!(stages & 1) || !j.all_covered) && do_sao) LAUNCHED(launch_copy_picture(f, f.work, f.out, st));
+    // MC and the residual run fused (recon.cu); stage 1 carries their time
+    LAUNCHED(launch_recon(f, stages & 3, st));
     STAGE_EVENT(1);
-    if (stages & 2) LAUNCHED(launch_residual(f, st));
     STAGE_EVENT(2);
     if ((stages & 4) && j.has_deblock) LAUNCHED(launch_deblock(f, st));
     STAGE_EVENT(3);

@@ -32,14 +32,13 @@ struct FrameDev {
     // MC
     const ohcu_pu *pus;
     int n_pu;
-    const int2 *ctb_pu_range;     // per CTB (raster): first PU, number of PUs
+    const int2 *ctb_pu_range;     // per CTB (raster): first PU, number of PUs | CTB_COVERED
     const ohcu_slice_tab *slices;
     // residual
     const ohcu_tu *tus;
     int n_tu;
     const int16_t *coeffs;
-    const uint32_t *tu_bin[4];    // TU indices by log2_size - 2
-    int n_bin[4];
+    const int2 *ctb_tu_range;     // per CTB (raster): first TU, number of TUs
     // deblock
     const uint8_t *vbs, *hbs;
     const int8_t *qp_y;
@@ -49,6 +48,9 @@ struct FrameDev {
     const ohcu_sao *sao;
     const uint16_t *sao_ctb_flags;   // per CTB, see SAOF_* below
 };
+
+// set in ctb_pu_range[].y when the CTB's PUs cover every sample of it
+constexpr int CTB_COVERED = 1 << 30;
 
 // per-CTB SAO flags precomputed on the host from slice addresses / tile ids
 // (sao_filter_CTB, hevc_filter.c:277-325)
@@ -60,8 +62,9 @@ enum {
 };
 
 // kernel launchers (each returns the number of kernels it enqueued, < 0 on error)
-int launch_mc(const FrameDev &f, cudaStream_t st);
-int launch_residual(const FrameDev &f, cudaStream_t st);
+int launch_recon(const FrameDev &f, int flags, cudaStream_t st);   // flags: 1 MC, 2 residual
+int upload_mc_taps();
+int upload_dct_table();
 int launch_deblock(const FrameDev &f, cudaStream_t st);
 int launch_sao(const FrameDev &f, cudaStream_t st);
 int launch_copy_picture(const FrameDev &f, const PlaneSet &dst, const PlaneSet &src, cudaStream_t st);
