@@ -35,6 +35,7 @@ static int fail(int code, const char *fmt, ...)
 // ------------------------------------------------------------------ objects
 struct Picture {
     uint8_t *base = nullptr;
+    uint8_t *padded_base[3] = {nullptr, nullptr, nullptr};   // first byte of each (padded) plane
     PlaneSet ps{};
     size_t bytes = 0;
 };
@@ -94,21 +95,64 @@ struct ohcu_ctx {
     void *l2_buf = nullptr;
     size_t l2_bytes = 0;
     cudaEvent_t t0 = nullptr, t1 = nullptr;
+    CUtensorMap *tmaps_d = nullptr;
 };
 
 // ------------------------------------------------------------------ helpers
-static int alloc_picture(const ohcu_ctx *c, Picture *p)
+// padded: DPB pictures carry the replicated halo the MC windows are fetched from
+// (PAD_X / PAD_Y, ohcu_internal.h); work pictures do not.
+static int alloc_picture(const ohcu_ctx *c, Picture *p, bool padded)
 {
+    const int px = padded ? PAD_X : 0, py = padded ? PAD_Y : 0;
     size_t off[3], total = 0;
     for (int i = 0; i < c->nplanes; i++) {
-        p->ps.pitch[i] = (c->pw[i] * c->P + 255) & ~255;
+        p->ps.pitch[i] = ((c->pw[i] + 2 * px) * c->P + 255) & ~255;
         off[i] = total;
-        total += (size_t)p->ps.pitch[i] * c->ph[i] + 256;
+        total += (size_t)p->ps.pitch[i] * (c->ph[i] + 2 * py) + 256;
     }
     CU(cudaMalloc(&p->base, total));
     CU(cudaMemset(p->base, 0, total));
-    for (int i = 0; i < 3; i++) p->ps.p[i] = i < c->nplanes ? p->base + off[i] : nullptr;
+    for (int i = 0; i < 3; i++) {
+        p->padded_base[i] = i < c->nplanes ? p->base + off[i] : nullptr;
+        p->ps.p[i] = i < c->nplanes ? p->base + off[i] + (size_t)py * p->ps.pitch[i] + (size_t)px * c->P : nullptr;
+    }
     p->bytes = total;
+    return 0;
+}
+
+// One tensor map per (DPB slot, plane, box class): the MC kernel fetches each PU's
+// reference window with one cp.async.bulk.tensor.2d.  The driver entry point is looked up
+// at run time so that the library has no link-time dependency on libcuda.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static int build_tensor_maps(ohcu_ctx *c)
+{
+    EncodeTiledFn enc = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    CU(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", (void **)&enc, cudaEnableDefault, &qr));
+    if (!enc || qr != cudaDriverEntryPointSuccess) return fail(OHCU_ECUDA, "cuTensorMapEncodeTiled is not available");
+    const bool high = c->P == 2;
+    std::vector<CUtensorMap> maps(c->slots.size() * 3 * N_WCLS * N_HCLS);
+    memset(maps.data(), 0, maps.size() * sizeof(CUtensorMap));
+    for (size_t s = 0; s < c->slots.size(); s++)
+        for (int pl = 0; pl < c->nplanes; pl++)
+            for (int wc = 0; wc < N_WCLS; wc++)
+                for (int hc = 0; hc < N_HCLS; hc++) {
+                    const Picture &p = c->slots[s].pic;
+                    cuuint64_t gdim[2] = {(cuuint64_t)(c->pw[pl] + 2 * PAD_X), (cuuint64_t)(c->ph[pl] + 2 * PAD_Y)};
+                    cuuint64_t gstr[1] = {(cuuint64_t)p.ps.pitch[pl]};
+                    cuuint32_t box[2] = {(cuuint32_t)box_w(high, wc), (cuuint32_t)box_h(hc)};
+                    cuuint32_t estr[2] = {1, 1};
+                    CUresult r = enc(&maps[tmap_index((int)s, pl, wc, hc)],
+                                     high ? CU_TENSOR_MAP_DATA_TYPE_UINT16 : CU_TENSOR_MAP_DATA_TYPE_UINT8, 2,
+                                     p.padded_base[pl], gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    if (r != CUDA_SUCCESS) return fail(OHCU_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+                }
+    CU(cudaMalloc((void **)&c->tmaps_d, maps.size() * sizeof(CUtensorMap)));
+    CU(cudaMemcpy(c->tmaps_d, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
     return 0;
 }
 
@@ -175,6 +219,7 @@ extern "C" int ohcu_destroy(ohcu_ctx *c)
     }
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->l2_buf) cudaFree(c->l2_buf);
+    if (c->tmaps_d) cudaFree(c->tmaps_d);
     if (c->t0) cudaEventDestroy(c->t0);
     if (c->t1) cudaEventDestroy(c->t1);
     delete c;
@@ -244,7 +289,7 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
     if (upload_dct_table() || upload_mc_taps()) { ohcu_destroy(c); return fail(OHCU_ECUDA, "constant upload failed"); }
     c->slots.resize(sp->dpb_slots);
     for (auto &s : c->slots) {
-        TRY(alloc_picture(c, &s.pic));
+        TRY(alloc_picture(c, &s.pic, true));
         TRYCU(cudaEventCreateWithFlags(&s.ready, cudaEventDisableTiming));
         TRYCU(cudaEventCreateWithFlags(&s.read_done, cudaEventDisableTiming));
     }
@@ -253,7 +298,7 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
         TRYCU(cudaStreamCreateWithFlags(&j.stream, cudaStreamNonBlocking));
         TRYCU(cudaEventCreateWithFlags(&j.done, cudaEventDisableTiming));
         for (auto &e : j.ev) TRYCU(cudaEventCreate(&e));
-        TRY(alloc_picture(c, &j.recon));
+        TRY(alloc_picture(c, &j.recon, false));
         TRY(alloc_arena(&j.pus, c->sp.max_pus));
         TRY(alloc_arena(&j.ctb_range, c->nctb));
         TRY(alloc_arena(&j.slices, OHCU_MAX_SLICES));
@@ -270,6 +315,7 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
         TRY(alloc_arena(&j.sao_flags, c->nctb));
     }
     TRYCU(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    TRY(build_tensor_maps(c));
 #undef TRY
 #undef TRYCU
     *out = c;
@@ -281,6 +327,24 @@ extern "C" int ohcu_get_seq_params(const ohcu_ctx *c, ohcu_seq_params *out)
     if (!c || !out) return fail(OHCU_EINVAL, "null argument");
     *out = c->sp;
     return 0;
+}
+
+// sequence-level part of the kernel parameter block
+static void fill_seq_dev(const ohcu_ctx *c, FrameDev *f)
+{
+    memset(f, 0, sizeof(*f));
+    const ohcu_seq_params &sp = c->sp;
+    f->width = sp.width; f->height = sp.height; f->bd = sp.bit_depth; f->cfi = sp.chroma_format_idc;
+    f->hs = c->hs; f->vs = c->vs;
+    f->log2_ctb = sp.log2_ctb_size; f->ctb_w = c->ctb_w; f->ctb_h = c->ctb_h;
+    f->log2_min_cb = sp.log2_min_cb_size; f->min_cb_w = c->min_cb_w;
+    f->log2_min_pu = sp.log2_min_pu_size; f->min_pu_w = c->min_pu_w; f->min_pu_h = c->min_pu_h;
+    f->bs_width = c->bs_w;
+    f->pcm_or_bypass = sp.pcm_or_bypass; f->cb_qp_offset = sp.cb_qp_offset; f->cr_qp_offset = sp.cr_qp_offset;
+    f->nplanes = c->nplanes;
+    for (int i = 0; i < 3; i++) { f->pw[i] = c->pw[i]; f->ph[i] = c->ph[i]; }
+    for (size_t i = 0; i < c->slots.size(); i++) f->dpb[i] = c->slots[i].pic.ps;
+    f->tmaps = c->tmaps_d;
 }
 
 // ------------------------------------------------------------------ device DPB
@@ -301,6 +365,13 @@ extern "C" int ohcu_slot_upload(ohcu_ctx *c, int slot, const uint8_t *const plan
     for (int i = 0; i < c->nplanes; i++)
         CU(cudaMemcpy2D(s.pic.ps.p[i], s.pic.ps.pitch[i], planes[i], strides[i], (size_t)c->pw[i] * c->P,
                         c->ph[i], cudaMemcpyHostToDevice));
+    // replicated halo around the uploaded picture (MC windows are fetched from it)
+    FrameDev f;
+    fill_seq_dev(c, &f);
+    launch_pad_picture(f, s.pic.ps, 0);
+    CU(cudaGetLastError());
+    CU(cudaDeviceSynchronize());
+    c->launches++;
     s.has_ready = false;
     s.readers = 0;
     return 0;
@@ -571,6 +642,9 @@ extern "C" int ohcu_frame_stage(ohcu_ctx *c, int job)
                 const int area = std::min(cs, c->sp.width - x * cs) * std::min(cs, c->sp.height - y * cs);
                 int2 &r = j.ctb_range.h[rs];
                 r.y &= ~CTB_COVERED;
+                if (j.ctb_area[rs] > area || (r.y & 0xffffff) > 128)
+                    return fail(OHCU_EINVAL, "CTB %d: PUs overlap or exceed the CTB (%d PUs, %d samples)", rs, r.y & 0xffffff,
+                                j.ctb_area[rs]);
                 if (j.ctb_area[rs] == area) r.y |= CTB_COVERED;
                 else j.all_covered = false;
             }
@@ -609,18 +683,7 @@ extern "C" int ohcu_frame_stage(ohcu_ctx *c, int job)
 
 static void fill_frame_dev(const ohcu_ctx *c, const Job &j, FrameDev *f)
 {
-    memset(f, 0, sizeof(*f));
-    const ohcu_seq_params &sp = c->sp;
-    f->width = sp.width; f->height = sp.height; f->bd = sp.bit_depth; f->cfi = sp.chroma_format_idc;
-    f->hs = c->hs; f->vs = c->vs;
-    f->log2_ctb = sp.log2_ctb_size; f->ctb_w = c->ctb_w; f->ctb_h = c->ctb_h;
-    f->log2_min_cb = sp.log2_min_cb_size; f->min_cb_w = c->min_cb_w;
-    f->log2_min_pu = sp.log2_min_pu_size; f->min_pu_w = c->min_pu_w; f->min_pu_h = c->min_pu_h;
-    f->bs_width = c->bs_w;
-    f->pcm_or_bypass = sp.pcm_or_bypass; f->cb_qp_offset = sp.cb_qp_offset; f->cr_qp_offset = sp.cr_qp_offset;
-    f->nplanes = c->nplanes;
-    for (int i = 0; i < 3; i++) { f->pw[i] = c->pw[i]; f->ph[i] = c->ph[i]; }
-    for (size_t i = 0; i < c->slots.size(); i++) f->dpb[i] = c->slots[i].pic.ps;
+    fill_seq_dev(c, f);
     f->pus = j.pus.d; f->n_pu = j.n_pu; f->ctb_pu_range = j.ctb_range.d; f->slices = j.slices.d;
     f->tus = j.tus.d; f->n_tu = j.n_tu; f->coeffs = j.coeffs.d; f->ctb_tu_range = j.ctb_tu_range.d;
     f->vbs = j.has_deblock ? j.vbs.d : nullptr; f->hbs = j.hbs.d; f->qp_y = j.qp.d; f->db = j.db.d;
@@ -685,6 +748,8 @@ extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int 
     if ((stages & 4) && j.has_deblock) LAUNCHED(launch_deblock(f, st));
     STAGE_EVENT(3);
     if (do_sao) LAUNCHED(launch_sao(f, st));
+    // the finished picture becomes a reference: replicate its borders into the halo
+    LAUNCHED(launch_pad_picture(f, f.out, st));
     STAGE_EVENT(4);
 #undef STAGE_EVENT
 #undef LAUNCHED

@@ -2,6 +2,7 @@
 // sm_100a kernels and the C-ABI host layer (api.cu).  Not part of the public ABI.
 #pragma once
 
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -10,9 +11,30 @@
 namespace ohcu {
 
 struct PlaneSet {
-    uint8_t *p[3];
+    uint8_t *p[3];         // sample (0, 0) of each plane; DPB planes carry a replicated halo around it
     int pitch[3];          // bytes
 };
+
+// ---- halo-padded DPB planes and the TMA box classes of motion compensation ------------
+// Every DPB plane is allocated with PAD_X samples left/right and PAD_Y rows above/below
+// that replicate the border sample (the reference's ff_emulated_edge_mc, done once per
+// picture instead of once per block).  MC windows are fetched by TMA as 2-D boxes whose
+// inner coordinate must be 16-byte aligned (measured: tools/ubench_tma.cu), so a window
+// starts at the aligned column at or left of the first sample it needs.
+constexpr int PAD_X = 96;                  // samples; >= 71 needed + 15 alignment slack
+constexpr int PAD_Y = 80;                  // rows;    >= 71 needed
+constexpr int N_WCLS = 5, N_HCLS = 5;      // box width / height classes
+// box widths in samples (inner box bytes are multiples of 16 for both sample sizes)
+__host__ __device__ constexpr int box_w(bool high, int cls)
+{
+    return high ? (cls == 0 ? 16 : cls == 1 ? 24 : cls == 2 ? 32 : cls == 3 ? 48 : 80)
+                : (cls == 0 ? 16 : cls == 1 ? 32 : cls == 2 ? 48 : cls == 3 ? 64 : 96);
+}
+__host__ __device__ constexpr int box_h(int cls) { return cls == 0 ? 8 : cls == 1 ? 16 : cls == 2 ? 24 : cls == 3 ? 40 : 72; }
+__host__ __device__ inline int tmap_index(int slot, int plane, int wcls, int hcls)
+{
+    return ((slot * 3 + plane) * N_WCLS + wcls) * N_HCLS + hcls;
+}
 
 // Everything a launch needs, passed by value as one kernel parameter.
 struct FrameDev {
@@ -29,6 +51,7 @@ struct FrameDev {
     PlaneSet work;         // picture being reconstructed (pre-SAO)
     PlaneSet out;          // SAO destination (the DPB slot)
     PlaneSet dpb[OHCU_MAX_DPB];
+    const CUtensorMap *tmaps;     // [slot][plane][width class][height class], see tmap_index()
     // MC
     const ohcu_pu *pus;
     int n_pu;
@@ -67,6 +90,7 @@ int upload_mc_taps();
 int upload_dct_table();
 int launch_deblock(const FrameDev &f, cudaStream_t st);
 int launch_sao(const FrameDev &f, cudaStream_t st);
+int launch_pad_picture(const FrameDev &f, const PlaneSet &pic, cudaStream_t st);   // fill the replicated halo
 int launch_copy_picture(const FrameDev &f, const PlaneSet &dst, const PlaneSet &src, cudaStream_t st);
 int launch_l2_flush(void *buf, size_t bytes, cudaStream_t st);
 

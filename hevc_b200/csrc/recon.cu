@@ -1,43 +1,54 @@
 // recon.cu — fused inter reconstruction of one picture: motion compensation + residual.
 //
-// One CTA owns one CTB.  It builds the CTB's prediction in a shared-memory tile (every
-// inter PU: luma qpel 8-tap / chroma epel 4-tap, uni / bi / weighted), adds the residual
-// of every coded TB of the CTB into the same tile (inverse DCT 4..32 / DC / 4x4 DST /
-// transform_skip / rdpcm / cross-component), and writes the CTB to the picture once with
-// full-line stores.  The prediction is never written to HBM and read back (the
+// One CTA (128 threads) owns one CTB.  It builds the CTB's prediction in a shared-memory
+// tile (every inter PU: luma qpel 8-tap / chroma epel 4-tap, uni / bi / weighted), adds the
+// residual of every coded TB of the CTB into the same tile (inverse DCT 4..32 / DC / 4x4
+// DST / transform_skip / rdpcm / cross-component), and writes the CTB to the picture once
+// with full-line stores.  The prediction is never written to HBM and read back (the
 // transform_add RMW of the reference disappears).
 //
 // Replaces, per picture:
 //   hls_prediction_unit -> luma_mc_uni/bi, chroma_mc_uni/bi     hevcdec.c:1744-2049, 2250-2306
 //   put_hevc_{qpel,epel}{,_uni,_uni_w,_bi,_bi_w}[idx][my][mx]   hevcdsp_template.c:2359-3357
-//   ff_emulated_edge_mc (replicate clamp while staging)         videodsp_template.c:22-100
+//   ff_emulated_edge_mc                                         videodsp_template.c:22-100
 //   ff_hevc_hls_transform / _c + transform_add                  hevc_cabac.c:1695-1906,
 //                                                               hevcdsp_template.c:45-296
 //
-// Arithmetic.  Samples are staged as 16-bit lanes, two per 32-bit word, so the FIR taps
-// run on the integer dot-product pipe: IDP.2A (dp2a) does two 16x8-bit MACs with int32
-// accumulation per instruction, at the same issue rate as IMAD on sm_100a
-// (profiles/r01_ubench_int_pipes.txt).  Horizontal pairs come straight from the staged
-// words (+ one funnel shift for odd phases), vertical pairs are built with PRMT.  The
-// int16 intermediates, shifts and clips are exactly the reference's.
+// Motion compensation.
+//  * Reference windows come from HALO-PADDED DPB planes (PAD_X / PAD_Y replicated samples,
+//    written once per picture by pad_kernel) through TMA: one cp.async.bulk.tensor.2d per
+//    (PU, list, plane) into a shared-memory pool, issued by the thread that owns the PU,
+//    all landing on one mbarrier.  Window positions outside the halo are clamped to it,
+//    which is bit-identical to the reference's per-block edge emulation.
+//  * Work is then re-cut into CELLS of 8x4 luma samples (and their chroma): one thread per
+//    cell, every thread running the same straight-line code, so a CTB of 64 tiny PUs keeps
+//    the lanes as busy as a CTB with one 64x64 PU.  The [my][mx] table dispatch is gone:
+//    every cell runs the separable h+v path with the phase-0 taps {0,0,0,64,0,0,0,0}
+//    standing in for "no filter", which gives the reference's results exactly
+//    (64*x >> 6 == x, and (x << (14-BD)) is what (64*x) >> (BD-8) computes).
+//  * Samples are 16-bit lanes, two per 32-bit word, so the taps run on the integer
+//    dot-product pipe: IDP.2A does two 16x8-bit MACs per instruction at IMAD issue rate
+//    (profiles/r01_ubench_int_pipes.txt).  Horizontal pairs come straight from the window
+//    words (+ funnel shifts for odd positions), vertical pairs are built with PRMT.
+//  * The pool holds one ROUND of windows (<= 32 KB + one window); a CTB whose windows need
+//    more runs several rounds per (list, luma|chroma) kind.  Cells are sorted by PU, so a
+//    round's cells are a contiguous range of the sorted list and lanes stay packed.
 #include "ohcu_internal.h"
 
 namespace ohcu {
 
-int upload_dct_table();
-
-constexpr int RC_WARPS = 8;
+constexpr int RC_WARPS = 4;
 constexpr int RC_THREADS = RC_WARPS * 32;
-constexpr int MC_CHUNK = 16;                 // output rows per task
-constexpr int SRC_ROWS = MC_CHUNK + 7;       // staged rows (8-tap halo)
-constexpr int SRC_PITCH = 36;                // words per staged row: 72 samples, == 4 mod 32
-constexpr int HB_PITCH = 36;                 // words per row of the horizontal-pass output
+constexpr int MAX_CTB_PUS = 128;             // 8x4 PUs of a 64x64 CTB
+constexpr int MAX_CTB_CELLS = 256;           // 4-wide PUs make half-empty cells
 constexpr int MAX_CTB_TUS = 768;             // 4x4 TBs of a 64x64 CTB, 3 full-size planes
+constexpr int POOL_ROUND = 32768;            // window bytes per round (before the last window's overhang)
+constexpr int POOL_BYTES = POOL_ROUND + 80 * 72 * 2;
+constexpr int MAX_ROUNDS = 8;                // per kind
+constexpr int N_KINDS = 4;                   // list slot A luma, slot B luma, slot A chroma, slot B chroma
 
-struct WarpScratch {
-    uint32_t src[SRC_ROWS * SRC_PITCH];      // reference window, 2 samples per word
-    uint32_t hb[SRC_ROWS * HB_PITCH];        // int16 rows after the horizontal pass
-};
+// scratch of one warp in the residual phase (aliases the window pool)
+struct WarpScratch { uint32_t w[2 * 32 * 34 / 2]; };
 
 // ff_hevc_qpel_filters / ff_hevc_epel_filters (hevcdsp.c:181-195) packed four int8 taps
 // per word: [phase][0] = taps 0..3, [phase][1] = taps 4..7
@@ -67,20 +78,58 @@ int upload_mc_taps()
     return 0;
 }
 
+// ---------------------------------------------------------------- mbarrier / TMA
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *b, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *b, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *b, uint32_t parity)
+{
+    uint32_t ok = 0;
+    const long long t0 = clock64();
+    while (!ok) {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+        // a transfer that never completes is a bug, not a reason to hang the GPU: fail the launch
+        if (!ok && clock64() - t0 > 2000000000ll) __trap();
+    }
+}
+// 2-D box at (x, y) of the tensor behind `map` -> dst (128-byte aligned); x*sizeof(sample) must
+// be a multiple of 16 (tools/ubench_tma.cu: anything else faults on this part)
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, int x, int y, uint64_t *bar)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar)) : "memory");
+}
+// tensor maps live in global memory (written once by ohcu_create): make them visible to the
+// TMA unit's descriptor fetch
+__device__ __forceinline__ void tmap_acquire(const CUtensorMap *map)
+{
+    asm volatile("fence.proxy.tensormap::generic.acquire.sys [%0], 128;" ::"l"(map) : "memory");
+}
+
 // ---------------------------------------------------------------- dot-product helpers
 __device__ __forceinline__ int dp2lo(uint32_t a, uint32_t b, int c) { return __dp2a_lo((int)a, (int)b, c); }
 __device__ __forceinline__ int dp2hi(uint32_t a, uint32_t b, int c) { return __dp2a_hi((int)a, (int)b, c); }
 
-// NT-tap FIR over the 16 samples held in W[0..7] (sample 2j in the low half of W[j]):
-// out[i] = sum_k tap[k] * sample[i + k], i = 0..7
-template <int NT>
-__device__ __forceinline__ void fir_row(const uint32_t (&W)[8], uint32_t F0, uint32_t F1, int (&out)[8])
+// NT-tap FIR along a row: W[j] holds samples 2j (low half) and 2j+1;
+// out[i] = sum_k tap[k] * sample[i + k], i = 0..OW-1
+template <int NT, int OW>
+__device__ __forceinline__ void fir_row(const uint32_t (&W)[(OW + NT) / 2], uint32_t F0, uint32_t F1, int (&out)[OW])
 {
-    uint32_t S[7];
+    constexpr int NW = (OW + NT) / 2;
+    uint32_t S[NW - 1];
 #pragma unroll
-    for (int j = 0; j < 7; j++) S[j] = __funnelshift_r(W[j], W[j + 1], 16);
+    for (int j = 0; j < NW - 1; j++) S[j] = __funnelshift_r(W[j], W[j + 1], 16);
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
+    for (int j = 0; j < OW / 2; j++) {
         if (NT == 8) {
             out[2 * j] = dp2hi(W[j + 3], F1, dp2lo(W[j + 2], F1, dp2hi(W[j + 1], F0, dp2lo(W[j], F0, 0))));
             out[2 * j + 1] = dp2hi(S[j + 3], F1, dp2lo(S[j + 2], F1, dp2hi(S[j + 1], F0, dp2lo(S[j], F0, 0))));
@@ -91,7 +140,7 @@ __device__ __forceinline__ void fir_row(const uint32_t (&W)[8], uint32_t F0, uin
     }
 }
 
-// NT-tap FIR down two columns at once: V[i] holds the samples of rows i (two columns per
+// NT-tap FIR down two columns at once: V[i] holds the samples of row i (two columns per
 // word); outA/outB[r] = sum_k tap[k] * column{A,B}[r + k], r = 0..R-1
 template <int NT, int R>
 __device__ __forceinline__ void fir_col(const uint32_t (&V)[R + NT - 1], uint32_t F0, uint32_t F1,
@@ -117,13 +166,13 @@ __device__ __forceinline__ void fir_col(const uint32_t (&V)[R + NT - 1], uint32_
 
 // ---------------------------------------------------------------- prediction epilogue
 // All five table families reduce to  o = ((val*wA + tmp*wB + add) >> sh) + post  on the
-// 14-bit intermediate `val` of this list and `tmp` of list 0 (bi only):
+// 14-bit intermediate `val` of this list and `tmp` of the first list (bi only):
 //   uni     (template :2544)  wA 1          add 1<<(13-BD)            sh 14-BD      post 0
 //   uni_w   (template :2733)  wA wx         add 1<<(shift-1)          sh shift      post ox
 //   bi      (template :2570)  wA 1   wB 1   add 1<<(14-BD)            sh 15-BD      post 0
 //   bi_w    (template :2760)  wA wx1 wB wx0 add (ox0+ox1+1)<<log2Wd   sh log2Wd+1   post 0
-// store_tmp: list 0 of a bi PU parks its intermediate in the tile (the reference's
-// lc->tmp, hevcdec.c:1854), list 1 picks it up.
+// store_tmp: the first list of a bi PU parks its intermediate in the tile (the reference's
+// lc->tmp, hevcdec.c:1854), the second list picks it up.
 struct Epi {
     int wA, wB, add, sh, post, maxv;
     bool store_tmp, bi;
@@ -148,208 +197,11 @@ __device__ __forceinline__ void epi_pair(const Epi &e, int va, int vb, uint32_t 
     *tw = (uint32_t)oa | ((uint32_t)ob << 16);
 }
 
-__device__ __forceinline__ int fastdiv(int n, int inv) { return (n * inv) >> 16; }   // n < 4096, divisor <= 32
+__device__ __forceinline__ int fastdiv(int n, int inv) { return (n * inv) >> 16; }   // n < 2048, divisor <= 32
 __constant__ int c_inv[41] = {0, 65536, 32768, 21846, 16384, 13108, 10923, 9363, 8192, 7282, 6554, 5958, 5462, 5042,
                               4682, 4370, 4096, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428,
                               2341, 2260, 2185, 2115, 2048, 1986, 1928, 1873, 1821, 1772, 1725, 1681, 1639};
 __device__ __forceinline__ int fastinv(int d) { return c_inv[d]; }                   // ceil(65536 / d), d <= 40
-
-// ---------------------------------------------------------------- reference window staging
-// Copies the window [x0, x0+cols) x [y0, y0+rows) of a reference plane into src[] as
-// 16-bit samples, two per word, window column 0 in the low half of word 0 of each row.
-// Coordinates outside the plane replicate the border sample = ff_emulated_edge_mc
-// (videodsp_template.c:22-100).  Windows that do not touch the left/right border take the
-// word path: one (HIGH: or two) aligned 32-bit loads per lane, realigned with a funnel shift.
-template <bool HIGH>
-__device__ __forceinline__ void stage_window(uint32_t *src, const uint8_t *__restrict__ ref, int rpitch, int pw,
-                                             int ph, int x0, int y0, int cols, int rows, int lane)
-{
-    const int nw = (cols + 1) >> 1;                       // smem words per row
-    if (x0 >= 0 && x0 + cols <= pw) {
-        if (HIGH) {
-            const int inv = fastinv(nw), items = rows * nw;
-            const int wa = x0 >> 1;
-            const bool odd = x0 & 1;
-            for (int it = lane; it < items; it += 32) {
-                const int r = fastdiv(it, inv), j = it - r * nw;
-                const int y = clip3i(y0 + r, 0, ph - 1);
-                const uint32_t *g = (const uint32_t *)(ref + (size_t)y * rpitch) + wa + j;
-                uint32_t v = __ldg(g);
-                if (odd) v = __funnelshift_r(v, __ldg(g + 1), 16);
-                src[r * SRC_PITCH + j] = v;
-            }
-        } else {
-            const int nq = (nw + 1) >> 1;                 // 4-sample units per row
-            const int inv = fastinv(nq), items = rows * nq;
-            const int wa = x0 >> 2, sh = (x0 & 3) * 8;
-            for (int it = lane; it < items; it += 32) {
-                const int r = fastdiv(it, inv), j = it - r * nq;
-                const int y = clip3i(y0 + r, 0, ph - 1);
-                const uint32_t *g = (const uint32_t *)(ref + (size_t)y * rpitch) + wa + j;
-                uint32_t v = __ldg(g);
-                if (sh) v = __funnelshift_r(v, __ldg(g + 1), sh);
-                uint2 o;
-                o.x = __byte_perm(v, 0, 0x4140);
-                o.y = __byte_perm(v, 0, 0x4342);
-                *(uint2 *)&src[r * SRC_PITCH + 2 * j] = o;
-            }
-        }
-    } else {
-        const int inv = fastinv(nw), items = rows * nw;
-        for (int it = lane; it < items; it += 32) {
-            const int r = fastdiv(it, inv), j = it - r * nw;
-            const int y = clip3i(y0 + r, 0, ph - 1);
-            const int xa = clip3i(x0 + 2 * j, 0, pw - 1), xb = clip3i(x0 + 2 * j + 1, 0, pw - 1);
-            const uint8_t *row = ref + (size_t)y * rpitch;
-            uint32_t a, b;
-            if (HIGH) { a = __ldg((const uint16_t *)row + xa); b = __ldg((const uint16_t *)row + xb); }
-            else      { a = __ldg(row + xa); b = __ldg(row + xb); }
-            src[r * SRC_PITCH + j] = a | (b << 16);
-        }
-    }
-}
-
-// ---------------------------------------------------------------- one MC task
-// One warp predicts rows [cy, cy+rows) of plane c of one PU: for each list, stage the
-// window, filter (one of four cases by fractional phase), and run the epilogue into the
-// CTB tile.  tile = word pointer to the PU's first row/column inside the CTB tile.
-template <bool HIGH, bool LUMA>
-__device__ void mc_task(const FrameDev &f, const ohcu_pu &pu, int c, int cy, int rows, uint32_t *tile, int tpitch,
-                        WarpScratch &ws, int lane)
-{
-    constexpr int NT = LUMA ? 8 : 4;
-    constexpr int BEFORE = LUMA ? 3 : 1;
-    constexpr int R = 4;                                   // rows per vertical-pass item
-    const int bd = f.bd;
-    const ohcu_slice_tab &sl = f.slices[pu.slice];
-    const int hs = LUMA ? 0 : f.hs, vs = LUMA ? 0 : f.vs;
-    const int bw = pu.w >> hs;
-    const int xo = pu.x0 >> hs, yo = (pu.y0 >> vs) + cy;
-    const int pw = f.pw[c], ph = f.ph[c];
-    const bool bi = pu.pred_flag == OHCU_PF_BI;
-    const bool wflag = sl.weight_flag != 0;
-    const int denom = LUMA ? sl.luma_log2_weight_denom : sl.chroma_log2_weight_denom;
-    const int ncp = bw >> 1;                               // column pairs
-    const int ng = (bw + 7) >> 3;                          // 8-column groups
-    const int inv_cp = fastinv(ncp), inv_g = fastinv(ng);
-
-    int wx[2], ox[2];
-#pragma unroll
-    for (int l = 0; l < 2; l++) {
-        const int ri = pu.ref_idx[l] & (OHCU_MAX_REFS - 1);
-        wx[l] = LUMA ? sl.luma_weight[l][ri] : sl.chroma_weight[l][ri][c - 1];
-        ox[l] = (LUMA ? sl.luma_offset[l][ri] : sl.chroma_offset[l][ri][c - 1]) * (1 << (bd - 8));
-    }
-
-#pragma unroll 1
-    for (int l = 0; l < 2; l++) {
-        if (!(pu.pred_flag & (1 << l))) continue;
-        // ---- epilogue of this list
-        Epi e;
-        e.maxv = (1 << bd) - 1;
-        e.bi = bi;
-        e.store_tmp = bi && l == 0;
-        e.wB = 0; e.post = 0;
-        if (!bi) {
-            if (!wflag) { e.wA = 1; e.sh = 14 - bd; e.add = 1 << (13 - bd); }
-            else { e.wA = wx[l]; e.sh = denom + 14 - bd; e.add = 1 << (e.sh - 1); e.post = ox[l]; }
-        } else {
-            if (!wflag) { e.wA = 1; e.wB = 1; e.sh = 15 - bd; e.add = 1 << (14 - bd); }
-            else {
-                const int log2Wd = denom + 14 - bd;
-                e.wA = wx[1]; e.wB = wx[0]; e.sh = log2Wd + 1; e.add = (ox[0] + ox[1] + 1) * (1 << log2Wd);
-            }
-        }
-        // ---- phases and integer position (hevcdec.c:1753-1760, 1909-1915)
-        const int mvx = pu.mv[l][0], mvy = pu.mv[l][1];
-        int mx, my, sx, sy;
-        if (LUMA) {
-            mx = mvx & 3; my = mvy & 3;
-            sx = xo + (mvx >> 2); sy = yo + (mvy >> 2);
-        } else {
-            mx = (mvx & ((1 << (2 + hs)) - 1)) << (1 - hs);
-            my = (mvy & ((1 << (2 + vs)) - 1)) << (1 - vs);
-            sx = xo + (mvx >> (2 + hs)); sy = yo + (mvy >> (2 + vs));
-        }
-        const uint32_t FX0 = LUMA ? c_qpel4[mx][0] : c_epel4[mx][0], FX1 = LUMA ? c_qpel4[mx][1] : 0;
-        const uint32_t FY0 = LUMA ? c_qpel4[my][0] : c_epel4[my][0], FY1 = LUMA ? c_qpel4[my][1] : 0;
-        const PlaneSet &rp = f.dpb[sl.ref_slot[l][pu.ref_idx[l] & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1)];
-        const int hb = mx ? BEFORE : 0, vb = my ? BEFORE : 0;
-        const int scols = bw + (mx ? NT - 1 : 0), srows = rows + (my ? NT - 1 : 0);
-
-        stage_window<HIGH>(ws.src, rp.p[c], rp.pitch[c], pw, ph, sx - hb, sy - vb, scols, srows, lane);
-        __syncwarp();
-
-        const int sh1 = bd - 8;                            // first-stage shift (template :2486)
-        if (mx && !my) {
-            // ---- horizontal only: rows x 8-column groups
-            const int items = rows * ng;
-            for (int it = lane; it < items; it += 32) {
-                const int r = fastdiv(it, inv_g), g = it - r * ng;
-                uint32_t W[8];
-                const uint4 a = *(const uint4 *)&ws.src[r * SRC_PITCH + 4 * g];
-                const uint4 b = *(const uint4 *)&ws.src[r * SRC_PITCH + 4 * g + 4];
-                W[0] = a.x; W[1] = a.y; W[2] = a.z; W[3] = a.w; W[4] = b.x; W[5] = b.y; W[6] = b.z; W[7] = b.w;
-                int o[8];
-                fir_row<NT>(W, FX0, FX1, o);
-                uint32_t *tw = tile + r * tpitch + 4 * g;
-#pragma unroll
-                for (int k = 0; k < 4; k++)
-                    if (8 * g + 2 * k < bw) epi_pair(e, o[2 * k] >> sh1, o[2 * k + 1] >> sh1, tw + k);
-            }
-        } else if (mx && my) {
-            // ---- horizontal pass over rows + NT-1 rows into int16 rows (tmp_array, template :2522)
-            const int items = srows * ng;
-            for (int it = lane; it < items; it += 32) {
-                const int r = fastdiv(it, inv_g), g = it - r * ng;
-                uint32_t W[8];
-                const uint4 a = *(const uint4 *)&ws.src[r * SRC_PITCH + 4 * g];
-                const uint4 b = *(const uint4 *)&ws.src[r * SRC_PITCH + 4 * g + 4];
-                W[0] = a.x; W[1] = a.y; W[2] = a.z; W[3] = a.w; W[4] = b.x; W[5] = b.y; W[6] = b.z; W[7] = b.w;
-                int o[8];
-                fir_row<NT>(W, FX0, FX1, o);
-                uint4 p;
-                p.x = __byte_perm((uint32_t)(o[0] >> sh1), (uint32_t)(o[1] >> sh1), 0x5410);
-                p.y = __byte_perm((uint32_t)(o[2] >> sh1), (uint32_t)(o[3] >> sh1), 0x5410);
-                p.z = __byte_perm((uint32_t)(o[4] >> sh1), (uint32_t)(o[5] >> sh1), 0x5410);
-                p.w = __byte_perm((uint32_t)(o[6] >> sh1), (uint32_t)(o[7] >> sh1), 0x5410);
-                *(uint4 *)&ws.hb[r * HB_PITCH + 4 * g] = p;
-            }
-            __syncwarp();
-        }
-        if (my) {
-            // ---- vertical pass: column pairs x groups of R rows, from pixels (shift BD-8)
-            //      or from the horizontal-pass rows (shift 6)
-            const uint32_t *in = mx ? ws.hb : ws.src;
-            const int ipitch = mx ? HB_PITCH : SRC_PITCH;
-            const int sh2 = mx ? 6 : sh1;
-            const int nrg = (rows + R - 1) / R;
-            const int items = nrg * ncp;
-            for (int it = lane; it < items; it += 32) {
-                const int rg = fastdiv(it, inv_cp), cp = it - rg * ncp;
-                uint32_t V[R + NT - 1];
-#pragma unroll
-                for (int i = 0; i < R + NT - 1; i++) V[i] = in[(rg * R + i) * ipitch + cp];
-                int oa[R], ob[R];
-                fir_col<NT, R>(V, FY0, FY1, oa, ob);
-                uint32_t *tw = tile + rg * R * tpitch + cp;
-#pragma unroll
-                for (int i = 0; i < R; i++)
-                    if (rg * R + i < rows) epi_pair(e, oa[i] >> sh2, ob[i] >> sh2, tw + i * tpitch);
-            }
-        } else if (!mx) {
-            // ---- full-pel: val = sample << (14 - BD) (template :2359-2373)
-            const int items = rows * ncp;
-            const int sh = 14 - bd;
-            for (int it = lane; it < items; it += 32) {
-                const int r = fastdiv(it, inv_cp), cp = it - r * ncp;
-                const uint32_t v = ws.src[r * SRC_PITCH + cp];
-                epi_pair(e, (int)(v & 0xffffu) << sh, (int)(v >> 16) << sh, tile + r * tpitch + cp);
-            }
-        }
-        __syncwarp();
-    }
-}
 
 // ================================================================= residual
 // transform[32][32] (hevcdsp.c:32-97) as 32-bit constants so that the unrolled butterflies
@@ -545,7 +397,7 @@ __device__ void tu_batch(const FrameDev &f, const CtbTile &tile, int tu0, const 
     }
 }
 
-// ================================================================= the kernel
+// ---------------------------------------------------------------- per-PU records
 __device__ __forceinline__ ohcu_pu load_pu(const ohcu_pu *p)
 {
     union { ohcu_pu pu; uint32_t w[5]; } u;
@@ -556,41 +408,179 @@ __device__ __forceinline__ ohcu_pu load_pu(const ohcu_pu *p)
     return u.pu;
 }
 
+// What the cells of a PU need, prepared once by the thread that owns the PU.
+//   rect  x/4 | y/4 << 4 | w/4 << 8 | h/4 << 13 | bi << 18 | cells per row << 19   (position inside the CTB)
+//   geom  [list slot A,B][luma, chroma]: pool offset / 16 | pitch / 16 << 12 | offx << 16 | mx << 20 | my << 23 | hcls << 26
+//   epi   per plane: (wA & 0xffff) | wB << 16,  add,  sh | post << 16
+struct PuRec {
+    uint32_t rect;
+    uint32_t geom[2][2];
+    uint32_t epi[3][3];
+};
+
+// One reference window: the samples list `l` of the PU reads in plane type luma / chroma
+// (both chroma planes share it).  Always the full separable window (NT-1 extra rows and
+// columns).  Coordinates are clamped so that a window lying entirely outside the picture is
+// fetched from the nearest part of the replicated halo — same samples as
+// ff_emulated_edge_mc would build (videodsp_template.c:37-83).
+struct WinGeom {
+    int ax, y0;           // plane coordinates of the box origin (ax is 16-byte aligned)
+    int offx;             // first needed column inside the box
+    int wcls, hcls;       // box class
+    int mx, my;           // fractional phase: qpel 0..3 / epel 0..7
+};
+
+template <bool HIGH>
+__device__ __forceinline__ WinGeom win_geom(const FrameDev &f, const ohcu_pu &pu, int l, bool luma)
+{
+    WinGeom g;
+    const int hs = luma ? 0 : f.hs, vs = luma ? 0 : f.vs;
+    const int NT = luma ? 8 : 4, BEFORE = luma ? 3 : 1;
+    const int bw = pu.w >> hs, bh = pu.h >> vs;
+    const int xo = pu.x0 >> hs, yo = pu.y0 >> vs;
+    const int pw = f.pw[luma ? 0 : 1], ph = f.ph[luma ? 0 : 1];
+    const int mvx = pu.mv[l][0], mvy = pu.mv[l][1];
+    int sx, sy;
+    if (luma) {                                            // hevcdec.c:1753-1760
+        g.mx = mvx & 3; g.my = mvy & 3;
+        sx = xo + (mvx >> 2); sy = yo + (mvy >> 2);
+    } else {                                               // hevcdec.c:1909-1915
+        g.mx = (mvx & ((1 << (2 + hs)) - 1)) << (1 - hs);
+        g.my = (mvy & ((1 << (2 + vs)) - 1)) << (1 - vs);
+        sx = xo + (mvx >> (2 + hs)); sy = yo + (mvy >> (2 + vs));
+    }
+    const int needw = bw + NT - 1, needh = bh + NT - 1;
+    const int x0 = clip3i(sx - BEFORE, -needw, pw);
+    g.y0 = clip3i(sy - BEFORE, -needh, ph);
+    constexpr int A = HIGH ? 8 : 16;                       // samples per 16 bytes
+    g.ax = x0 & ~(A - 1);
+    g.offx = x0 - g.ax;
+    // the widest read of any cell of the PU: cells are 8 luma columns wide (partial for w = 4, 12)
+    const int cellw = luma ? 8 : (8 >> hs);
+    const int readw = g.offx + ((pu.w + 7) >> 3) * cellw + NT - 1;
+    g.wcls = readw <= box_w(HIGH, 0) ? 0 : readw <= box_w(HIGH, 1) ? 1 : readw <= box_w(HIGH, 2) ? 2 : readw <= box_w(HIGH, 3) ? 3 : 4;
+    g.hcls = needh <= box_h(0) ? 0 : needh <= box_h(1) ? 1 : needh <= box_h(2) ? 2 : needh <= box_h(3) ? 3 : 4;
+    return g;
+}
+
+__device__ __forceinline__ int box_bytes(bool high, int wcls, int hcls) { return box_w(high, wcls) * (high ? 2 : 1) * box_h(hcls); }
+
+// ---------------------------------------------------------------- one cell
+// OW x OH output samples of one plane from the window at `win` (row pitch in bytes):
+// horizontal pass over OH + NT - 1 rows into packed int16 registers (the reference's
+// tmp_array, template :2522), vertical pass, epilogue into the CTB tile.
+//   col0  first output column of the cell relative to the window's first needed column
+//   row0  first output row of the cell relative to the window's first row
+//   ncol  valid output columns (partial cells of 4- and 12-wide PUs)
+template <bool HIGH, int NT, int OW, int OH>
+__device__ __forceinline__ void mc_cell(const uint8_t *win, int pitch, int col0, int row0, uint32_t FX0, uint32_t FX1,
+                                        uint32_t FY0, uint32_t FY1, int sh1, const Epi &e, uint32_t *tw, int tpitch,
+                                        int ncol)
+{
+    constexpr int NW = (OW + NT) / 2, NR = OH + NT - 1;
+    uint32_t hb[NR][OW / 2];
+    const uint8_t *rowp = win + row0 * pitch;
+#pragma unroll
+    for (int r = 0; r < NR; r++) {
+        uint32_t W[NW];
+        if (HIGH) {
+            const uint32_t *p = (const uint32_t *)rowp + (col0 >> 1);
+            const int sh = (col0 & 1) * 16;
+            uint32_t T[NW];
+#pragma unroll
+            for (int j = 0; j < NW; j++) T[j] = p[j];
+#pragma unroll
+            for (int j = 0; j < NW; j++) W[j] = __funnelshift_r(T[j], T[j + 1 < NW ? j + 1 : j], sh);
+        } else {
+            constexpr int NB = NW / 2 + 1;
+            const uint32_t *p = (const uint32_t *)rowp + (col0 >> 2);
+            const int sh = (col0 & 3) * 8;
+            uint32_t T[NB];
+#pragma unroll
+            for (int j = 0; j < NB; j++) T[j] = p[j];
+#pragma unroll
+            for (int j = 0; j < NB - 1; j++) {
+                const uint32_t v = __funnelshift_r(T[j], T[j + 1], sh);
+                W[2 * j] = __byte_perm(v, 0, 0x4140);
+                W[2 * j + 1] = __byte_perm(v, 0, 0x4342);
+            }
+        }
+        int o[OW];
+        fir_row<NT, OW>(W, FX0, FX1, o);
+#pragma unroll
+        for (int k = 0; k < OW / 2; k++)
+            hb[r][k] = __byte_perm((uint32_t)(o[2 * k] >> sh1), (uint32_t)(o[2 * k + 1] >> sh1), 0x5410);
+        rowp += pitch;
+    }
+#pragma unroll
+    for (int k = 0; k < OW / 2; k++) {
+        uint32_t V[NR];
+#pragma unroll
+        for (int r = 0; r < NR; r++) V[r] = hb[r][k];
+        int oa[OH], ob[OH];
+        fir_col<NT, OH>(V, FY0, FY1, oa, ob);
+        if (2 * k < ncol) {
+#pragma unroll
+            for (int r = 0; r < OH; r++) epi_pair(e, oa[r] >> 6, ob[r] >> 6, tw + r * tpitch + k);
+        }
+    }
+}
+
+// ================================================================= the kernel
+__device__ __forceinline__ void unpack_epi(const uint32_t (&w)[3], int bd, bool bi, bool first_of_bi, Epi &e)
+{
+    e.wA = (int)(int16_t)(w[0] & 0xffffu);
+    e.wB = (int)w[0] >> 16;
+    e.add = (int)w[1];
+    e.sh = (int)(w[2] & 0xffffu);
+    e.post = (int)w[2] >> 16;
+    e.maxv = (1 << bd) - 1;
+    e.bi = bi;
+    e.store_tmp = first_of_bi;
+}
+
 // flags: bit 0 run MC, bit 1 run the residual
 template <bool HIGH>
 __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_constant__ FrameDev f, int flags)
 {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    WarpScratch *scratch = (WarpScratch *)smem_raw;
-    uint32_t *tile_base = (uint32_t *)(smem_raw + sizeof(WarpScratch) * RC_WARPS);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int ctb = blockIdx.x;
     const int ctbx = ctb % f.ctb_w, ctby = ctb / f.ctb_w;
     const int cs = 1 << f.log2_ctb;
     const int cx0 = ctbx << f.log2_ctb, cy0 = ctby << f.log2_ctb;      // luma origin of the CTB
+    const int bd = f.bd;
 
+    // ---- shared memory carve-up
+    uint8_t *pool = smem_raw;
     CtbTile tile;
-    int tw[3], th[3], vw[3], vh[3];
-    {
-        uint32_t *p = tile_base;
+    int vw[3], vh[3];
+    uint32_t *sp = (uint32_t *)(smem_raw + POOL_BYTES);
 #pragma unroll
-        for (int c = 0; c < 3; c++) {
-            const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
-            tw[c] = cs >> hs; th[c] = cs >> vs;
-            vw[c] = min(tw[c], f.pw[c] - (cx0 >> hs));
-            vh[c] = min(th[c], f.ph[c] - (cy0 >> vs));
-            tile.pitch[c] = (tw[c] >> 1) + 2;
-            tile.p[c] = p;
-            if (c < f.nplanes) p += tile.pitch[c] * th[c];
-        }
-        // after the tiles: the size-sorted TB list and its counters
-        tile_base = p;
+    for (int c = 0; c < 3; c++) {
+        const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
+        const int tw = cs >> hs, th = cs >> vs;
+        vw[c] = min(tw, f.pw[c] - (cx0 >> hs));
+        vh[c] = min(th, f.ph[c] - (cy0 >> vs));
+        tile.pitch[c] = (tw >> 1) + 2;
+        tile.p[c] = sp;
+        if (c < f.nplanes) sp += tile.pitch[c] * th;
     }
-    uint16_t *tu_list = (uint16_t *)(tile_base + 16);
-    int *tu_cnt = (int *)tile_base;                                      // [0..3] counts, [4..7] bases, [8..11] cursors
+    PuRec *recs = (PuRec *)sp;                  sp += MAX_CTB_PUS * (sizeof(PuRec) / 4);
+    int *cumA = (int *)sp;                      sp += MAX_CTB_PUS + 4;
+    int *cumB = (int *)sp;                      sp += MAX_CTB_PUS + 4;
+    uint16_t *listA = (uint16_t *)sp;           sp += MAX_CTB_CELLS / 2;
+    uint16_t *listB = (uint16_t *)sp;           sp += MAX_CTB_CELLS / 2;
+    int *rnd_pu = (int *)sp;                    sp += N_KINDS * MAX_ROUNDS;      // first PU of each round
+    int *rnd_cell = (int *)sp;                  sp += N_KINDS * MAX_ROUNDS;      // first sorted cell of each round
+    int *rnd_bytes = (int *)sp;                 sp += N_KINDS * MAX_ROUNDS;      // TMA bytes of each round
+    int *scan_tmp = (int *)sp;                  sp += 6 * RC_WARPS + 8;          // warp totals, then [24..29] totals
+    int *tu_cnt = (int *)sp;                    sp += 16;                         // [0..3] counts, [4..7] bases, [8..11] cursors
+    uint16_t *tu_list = (uint16_t *)sp;         sp += MAX_CTB_TUS / 2;
+    uint64_t *mbar = (uint64_t *)(((uintptr_t)sp + 7) & ~(uintptr_t)7);
 
     const int2 prange = f.ctb_pu_range[ctb];
-    const int p0 = prange.x, np = prange.y & 0xffffff;
+    const int p0 = prange.x, np = min(prange.y & 0xffffff, MAX_CTB_PUS);
     const bool covered = (prange.y >> 30) & 1;
     const bool do_mc = (flags & 1) && np > 0;
     const bool do_res = (flags & 2) && f.n_tu > 0;
@@ -603,7 +593,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
             const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
             const uint8_t *plane = f.work.p[c] + (size_t)(cy0 >> vs) * f.work.pitch[c];
             const int units = vw[c] >> 2, items = units * vh[c], inv = fastinv(units);
-            for (int it = threadIdx.x; it < items; it += RC_THREADS) {
+            for (int it = tid; it < items; it += RC_THREADS) {
                 const int r = fastdiv(it, inv), u = it - r * units;
                 uint2 o;
                 if (HIGH) {
@@ -617,55 +607,253 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
             }
         }
     }
-    if (threadIdx.x < 12) tu_cnt[threadIdx.x] = 0;
+    if (tid < 12) tu_cnt[tid] = 0;
+    if (tid < N_KINDS * MAX_ROUNDS) { rnd_pu[tid] = MAX_CTB_PUS; rnd_cell[tid] = MAX_CTB_CELLS; rnd_bytes[tid] = 0; }
+    if (tid == 0) mbar_init(mbar, 1);
     __syncthreads();
 
-    // ---- phase 1: prediction.  Tasks = (PU, plane, chunk of <= 16 rows), round-robin over warps.
+    // ================================================================ phase 1: prediction
     if (do_mc) {
-        int counter = 0;
-        for (int i = 0; i < np; i++) {
-            const ohcu_pu pu = load_pu(f.pus + p0 + i);
-            const int chl = (pu.h + MC_CHUNK - 1) / MC_CHUNK;
-            const int bhc = pu.h >> f.vs;
-            const int chc = f.nplanes == 3 ? (bhc + MC_CHUNK - 1) / MC_CHUNK : 0;
-            const int total = chl + 2 * chc;
-            // does any of counter .. counter+total-1 belong to this warp?
-            const int firstmine = (warp - counter) & (RC_WARPS - 1);
-            if (firstmine < total) {
-                for (int t = firstmine; t < total; t += RC_WARPS) {
-                    int c, ch;
-                    if (t < chl) { c = 0; ch = t; }
-                    else if (t < chl + chc) { c = 1; ch = t - chl; }
-                    else { c = 2; ch = t - chl - chc; }
-                    const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
-                    const int bh = pu.h >> vs;
-                    const int cy = ch * MC_CHUNK, rows = min(MC_CHUNK, bh - cy);
-                    uint32_t *tp = tile.p[c] + (((pu.y0 - cy0) >> vs) + cy) * tile.pitch[c] + (((pu.x0 - cx0) >> hs) >> 1);
-                    if (c == 0) mc_task<HIGH, true>(f, pu, 0, cy, rows, tp, tile.pitch[0], scratch[warp], lane);
-                    else        mc_task<HIGH, false>(f, pu, c, cy, rows, tp, tile.pitch[c], scratch[warp], lane);
+        // ---- 1a. the thread that owns PU `tid` prepares its record
+        int v[6] = {0, 0, 0, 0, 0, 0};                 // cells A, cells B, bytes of the four kinds
+        uint32_t gw[2][2] = {{0, 0}, {0, 0}};
+        bool bi = false;
+        if (tid < np) {
+            const ohcu_pu pu = load_pu(f.pus + p0 + tid);
+            const ohcu_slice_tab &sl = f.slices[pu.slice];
+            bi = pu.pred_flag == OHCU_PF_BI;
+            const int nx = (pu.w + 7) >> 3, ncell = nx * (pu.h >> 2);
+            v[0] = ncell;
+            v[1] = bi ? ncell : 0;
+            PuRec &rc = recs[tid];
+            rc.rect = (uint32_t)(((pu.x0 - cx0) >> 2) | (((pu.y0 - cy0) >> 2) << 4) | ((pu.w >> 2) << 8) | ((pu.h >> 2) << 13) |
+                                 ((bi ? 1 : 0) << 18) | (nx << 19));
+            const int lA = (pu.pred_flag & 1) ? 0 : 1;
+#pragma unroll
+            for (int s = 0; s < 2; s++) {
+                if (s == 1 && !bi) continue;
+                const int l = s ? 1 : lA;
+#pragma unroll
+                for (int pt = 0; pt < 2; pt++) {
+                    if (pt == 1 && f.nplanes != 3) continue;
+                    const WinGeom g = win_geom<HIGH>(f, pu, l, pt == 0);
+                    const int pitch = box_w(HIGH, g.wcls) * (HIGH ? 2 : 1);
+                    v[2 + 2 * pt + s] = pitch * box_h(g.hcls) * (pt ? 2 : 1);
+                    gw[s][pt] = ((uint32_t)(pitch >> 4) << 12) | ((uint32_t)g.offx << 16) | ((uint32_t)g.mx << 20) |
+                                ((uint32_t)g.my << 23) | ((uint32_t)g.hcls << 26);
                 }
             }
-            counter = (counter + total) & (RC_WARPS - 1);
+            // epilogue constants per plane (see Epi)
+            const bool wflag = sl.weight_flag != 0;
+#pragma unroll
+            for (int c = 0; c < 3; c++) {
+                const int denom = c ? sl.chroma_log2_weight_denom : sl.luma_log2_weight_denom;
+                int wx[2], ox[2];
+#pragma unroll
+                for (int l = 0; l < 2; l++) {
+                    const int ri = pu.ref_idx[l] & (OHCU_MAX_REFS - 1);
+                    wx[l] = c ? sl.chroma_weight[l][ri][c - 1] : sl.luma_weight[l][ri];
+                    ox[l] = (c ? sl.chroma_offset[l][ri][c - 1] : sl.luma_offset[l][ri]) * (1 << (bd - 8));
+                }
+                int wA, wB = 0, add, sh, post = 0;
+                if (!bi) {
+                    if (!wflag) { wA = 1; sh = 14 - bd; add = 1 << (13 - bd); }
+                    else { wA = wx[lA]; sh = denom + 14 - bd; add = 1 << (sh - 1); post = ox[lA]; }
+                } else {
+                    if (!wflag) { wA = 1; wB = 1; sh = 15 - bd; add = 1 << (14 - bd); }
+                    else {
+                        const int log2Wd = denom + 14 - bd;
+                        wA = wx[1]; wB = wx[0]; sh = log2Wd + 1; add = (ox[0] + ox[1] + 1) * (1 << log2Wd);
+                    }
+                }
+                rc.epi[c][0] = ((uint32_t)wA & 0xffffu) | ((uint32_t)wB << 16);
+                rc.epi[c][1] = (uint32_t)add;
+                rc.epi[c][2] = ((uint32_t)sh & 0xffffu) | ((uint32_t)post << 16);
+            }
+        }
+        // ---- 1b. exclusive scans over the PUs: sorted-cell positions and pool offsets
+        int excl[6];
+#pragma unroll
+        for (int q = 0; q < 6; q++) {
+            int x = v[q];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, x, d);
+                if (lane >= d) x += y;
+            }
+            excl[q] = x - v[q];
+            if (lane == 31) scan_tmp[q * RC_WARPS + warp] = x;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < 6; q++) {
+            int before = 0, total = 0;
+#pragma unroll
+            for (int w = 0; w < RC_WARPS; w++) {
+                const int t = scan_tmp[q * RC_WARPS + w];
+                if (w < warp) before += t;
+                total += t;
+            }
+            excl[q] += before;
+            if (tid == 0) scan_tmp[6 * RC_WARPS + q] = total;
+        }
+        if (tid < np) {
+            cumA[tid] = excl[0];
+            cumB[tid] = excl[1];
+            PuRec &rc = recs[tid];
+#pragma unroll
+            for (int k = 0; k < N_KINDS; k++) {
+                const int s = k & 1, pt = k >> 1;
+                const int bytes = v[2 + k];
+                uint32_t g = gw[s][pt];
+                if (bytes > 0) {
+                    const int r = excl[2 + k] >> 15;
+                    if (r < MAX_ROUNDS) {
+                        g |= (uint32_t)((excl[2 + k] - (r << 15)) >> 4);
+                        atomicMin(&rnd_pu[k * MAX_ROUNDS + r], tid);
+                        atomicMin(&rnd_cell[k * MAX_ROUNDS + r], excl[s]);
+                        atomicAdd(&rnd_bytes[k * MAX_ROUNDS + r], bytes);
+                    }
+                }
+                rc.geom[s][pt] = g;
+            }
+        }
+        __syncthreads();
+        const int totA = scan_tmp[6 * RC_WARPS + 0], totB = scan_tmp[6 * RC_WARPS + 1];
+        if (tid == 0) { cumA[np] = totA; cumB[np] = totB; }
+        // ---- 1c. cells sorted by PU: entry = PU | cell column << 7 | cell row << 10
+#pragma unroll 1
+        for (int s = 0; s < 2; s++) {
+            const int *cum = s ? cumB : cumA;
+            uint16_t *list = s ? listB : listA;
+            const int tot = min(s ? totB : totA, MAX_CTB_CELLS);
+            for (int i = tid; i < tot; i += RC_THREADS) {
+                int lo = 0, hi = np - 1;                   // largest p with cum[p] <= i
+                while (lo < hi) {
+                    const int mid = (lo + hi + 1) >> 1;
+                    if (cum[mid] <= i) lo = mid; else hi = mid - 1;
+                }
+                const int local = i - cum[lo];
+                const int nx = (recs[lo].rect >> 19) & 15;
+                const int cy = fastdiv(local, fastinv(nx)), cx = local - cy * nx;
+                list[i] = (uint16_t)(lo | (cx << 7) | (cy << 10));
+            }
+        }
+        __syncthreads();
+
+        // ---- 1d. rounds: TMA the windows of a run of PUs into the pool, then one cell per thread
+        const int sh1 = bd - 8;                            // first-stage shift (template :2486)
+        uint32_t parity = 0;
+        const int nkinds = f.nplanes == 3 ? N_KINDS : 2;
+#pragma unroll 1
+        for (int k = 0; k < nkinds; k++) {
+            const int s = k & 1, pt = k >> 1;
+            // rounds of this kind: a round exists iff some window STARTS in its 32 KB slice
+            int nr = 0;
+            while (nr < MAX_ROUNDS && rnd_bytes[k * MAX_ROUNDS + nr] > 0) nr++;
+            const uint16_t *list = s ? listB : listA;
+            const int ncells = min(s ? totB : totA, MAX_CTB_CELLS);
+#pragma unroll 1
+            for (int r = 0; r < nr; r++) {
+                __syncthreads();                           // everyone is done with the pool's previous content
+                const int pa = rnd_pu[k * MAX_ROUNDS + r];
+                const int pb = r + 1 < nr ? min(rnd_pu[k * MAX_ROUNDS + r + 1], np) : np;
+                if (tid == 0) mbar_expect_tx(mbar, (uint32_t)rnd_bytes[k * MAX_ROUNDS + r]);
+                if (pa + tid < pb) {
+                    const int p = pa + tid;
+                    const ohcu_pu pu = load_pu(f.pus + p0 + p);
+                    const bool pbi = pu.pred_flag == OHCU_PF_BI;
+                    if (s == 0 || pbi) {
+                        const int l = s ? 1 : ((pu.pred_flag & 1) ? 0 : 1);
+                        const WinGeom g = win_geom<HIGH>(f, pu, l, pt == 0);
+                        const ohcu_slice_tab &sl = f.slices[pu.slice];
+                        const int slot = sl.ref_slot[l][pu.ref_idx[l] & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1);
+                        const uint32_t gword = recs[p].geom[s][pt];
+                        uint8_t *dst = pool + (gword & 0xfffu) * 16;
+                        const int bytes = box_bytes(HIGH, g.wcls, g.hcls);
+                        if (pt == 0) {
+                            const CUtensorMap *m = f.tmaps + tmap_index(slot, 0, g.wcls, g.hcls);
+                            tmap_acquire(m);
+                            tma_load_2d(dst, m, g.ax + PAD_X, g.y0 + PAD_Y, mbar);
+                        } else {
+#pragma unroll
+                            for (int c = 1; c < 3; c++) {
+                                const CUtensorMap *m = f.tmaps + tmap_index(slot, c, g.wcls, g.hcls);
+                                tmap_acquire(m);
+                                tma_load_2d(dst + (c - 1) * bytes, m, g.ax + PAD_X, g.y0 + PAD_Y, mbar);
+                            }
+                        }
+                    }
+                }
+                mbar_wait(mbar, parity);
+                parity ^= 1;
+
+                const int clo = rnd_cell[k * MAX_ROUNDS + r];
+                const int chi = r + 1 < nr ? rnd_cell[k * MAX_ROUNDS + r + 1] : ncells;
+#pragma unroll 1
+                for (int ci = clo + tid; ci < chi; ci += RC_THREADS) {
+                    const int ent = list[ci];
+                    const int p = ent & 127, cx = (ent >> 7) & 7, cy = ent >> 10;
+                    const PuRec &rc = recs[p];
+                    const uint32_t rect = rc.rect;
+                    const int x4 = rect & 15, y4 = (rect >> 4) & 15, w4 = (rect >> 8) & 31;
+                    const bool pbi = (rect >> 18) & 1;
+                    const uint32_t gword = rc.geom[s][pt];
+                    const uint8_t *win = pool + (gword & 0xfffu) * 16;
+                    const int pitch = ((gword >> 12) & 15) * 16, offx = (gword >> 16) & 15;
+                    const int mx = (gword >> 20) & 7, my = (gword >> 23) & 7;
+                    Epi e;
+                    if (pt == 0) {
+                        const uint32_t ew[3] = {rc.epi[0][0], rc.epi[0][1], rc.epi[0][2]};
+                        unpack_epi(ew, bd, pbi, pbi && s == 0, e);
+                        uint32_t *tp = tile.p[0] + (y4 * 4 + cy * 4) * tile.pitch[0] + ((x4 * 4 + cx * 8) >> 1);
+                        mc_cell<HIGH, 8, 8, 4>(win, pitch, offx + cx * 8, cy * 4, c_qpel4[mx][0], c_qpel4[mx][1], c_qpel4[my][0],
+                                               c_qpel4[my][1], sh1, e, tp, tile.pitch[0], w4 * 4 - cx * 8);
+                    } else {
+                        const int hs = f.hs, vs = f.vs;
+                        const int cw = 8 >> hs, ch = 4 >> vs;
+                        const int bytes = pitch * box_h((gword >> 26) & 7);
+#pragma unroll 1
+                        for (int c = 1; c < 3; c++) {
+                            const uint32_t ew[3] = {rc.epi[c][0], rc.epi[c][1], rc.epi[c][2]};
+                            unpack_epi(ew, bd, pbi, pbi && s == 0, e);
+                            uint32_t *tp = tile.p[c] + (((y4 * 4) >> vs) + cy * ch) * tile.pitch[c] + ((((x4 * 4) >> hs) + cx * cw) >> 1);
+                            const uint8_t *wc = win + (c - 1) * bytes;
+                            const int ncol = ((w4 * 4) >> hs) - cx * cw;
+                            if (hs && vs)
+                                mc_cell<HIGH, 4, 4, 2>(wc, pitch, offx + cx * 4, cy * 2, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
+                                                       tp, tile.pitch[c], ncol);
+                            else if (hs)
+                                mc_cell<HIGH, 4, 4, 4>(wc, pitch, offx + cx * 4, cy * 4, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
+                                                       tp, tile.pitch[c], ncol);
+                            else
+                                mc_cell<HIGH, 4, 8, 4>(wc, pitch, offx + cx * 8, cy * 4, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
+                                                       tp, tile.pitch[c], ncol);
+                        }
+                    }
+                }
+            }
         }
     }
 
-    // ---- phase 2: residual.  Counting sort of the CTB's TBs by size, then batches per warp.
+    // ================================================================ phase 2: residual
+    // Counting sort of the CTB's TBs by size, then batches of equal-size TBs per warp.
     if (nt > 0) {
-        for (int i = threadIdx.x; i < nt; i += RC_THREADS) atomicAdd(&tu_cnt[f.tus[t0 + i].log2_size - 2], 1);
+        for (int i = tid; i < nt; i += RC_THREADS) atomicAdd(&tu_cnt[f.tus[t0 + i].log2_size - 2], 1);
         __syncthreads();
-        if (threadIdx.x == 0) {
-            // largest first: 32x32 batches are the long ones
-            int acc = 0;
+        if (tid == 0) {
+            int acc = 0;                                   // largest first: 32x32 batches are the long ones
             for (int l = 3; l >= 0; l--) { tu_cnt[4 + l] = acc; acc += tu_cnt[l]; }
         }
         __syncthreads();
-        for (int i = threadIdx.x; i < nt; i += RC_THREADS) {
+        for (int i = tid; i < nt; i += RC_THREADS) {
             const int l = f.tus[t0 + i].log2_size - 2;
             tu_list[tu_cnt[4 + l] + atomicAdd(&tu_cnt[8 + l], 1)] = (uint16_t)i;
         }
     }
-    __syncthreads();          // prediction complete, TB list sorted
+    __syncthreads();          // prediction complete (the pool is free), TB list sorted
     if (nt > 0) {
+        WarpScratch &ws = ((WarpScratch *)pool)[warp];
         int b = 0;            // running batch number over all size classes
 #pragma unroll
         for (int l = 3; l >= 0; l--) {
@@ -673,10 +861,10 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
             const int per = 32 >> (l + 2);                 // TBs per batch
             const int nb = (cnt + per - 1) / per;
             for (int k = (warp - b) & (RC_WARPS - 1); k < nb; k += RC_WARPS) {
-                if (l == 3) tu_batch<5>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, scratch[warp], lane);
-                if (l == 2) tu_batch<4>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, scratch[warp], lane);
-                if (l == 1) tu_batch<3>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, scratch[warp], lane);
-                if (l == 0) tu_batch<2>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, scratch[warp], lane);
+                if (l == 3) tu_batch<5>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, lane);
+                if (l == 2) tu_batch<4>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, lane);
+                if (l == 1) tu_batch<3>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, lane);
+                if (l == 0) tu_batch<2>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, lane);
                 __syncwarp();
             }
             b = (b + nb) & (RC_WARPS - 1);
@@ -684,13 +872,13 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     }
     __syncthreads();
 
-    // ---- phase 3: the CTB leaves the SM once, in 8-byte (HIGH) / 4-byte units of four samples
+    // ================================================================ phase 3: the CTB leaves the SM once
     for (int c = 0; c < f.nplanes; c++) {
         const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
         uint8_t *plane = f.work.p[c] + (size_t)(cy0 >> vs) * f.work.pitch[c];
         const int units = vw[c] >> 2, items = units * vh[c];
         const int inv = fastinv(units);
-        for (int it = threadIdx.x; it < items; it += RC_THREADS) {
+        for (int it = tid; it < items; it += RC_THREADS) {
             const int r = fastdiv(it, inv), u = it - r * units;
             const uint2 v = *(const uint2 *)&tile.p[c][r * tile.pitch[c] + 2 * u];
             if (HIGH)
@@ -709,7 +897,9 @@ size_t recon_smem_bytes(const FrameDev &f)
         const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
         words += (size_t)(((cs >> hs) >> 1) + 2) * (cs >> vs);
     }
-    return sizeof(WarpScratch) * RC_WARPS + words * 4 + 16 * 4 + MAX_CTB_TUS * 2;
+    words += MAX_CTB_PUS * (sizeof(PuRec) / 4) + 2 * (MAX_CTB_PUS + 4) + MAX_CTB_CELLS + 3 * N_KINDS * MAX_ROUNDS +
+             6 * RC_WARPS + 8 + 16 + MAX_CTB_TUS / 2 + 4;
+    return POOL_BYTES + words * 4;
 }
 
 int launch_recon(const FrameDev &f, int flags, cudaStream_t st)
@@ -719,8 +909,8 @@ int launch_recon(const FrameDev &f, int flags, cudaStream_t st)
     const size_t smem = recon_smem_bytes(f);
     static bool attr_set = false;
     if (!attr_set) {
-        if (cudaFuncSetAttribute(recon_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024) != cudaSuccess ||
-            cudaFuncSetAttribute(recon_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024) != cudaSuccess)
+        if (cudaFuncSetAttribute(recon_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(recon_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024) != cudaSuccess)
             return -1;
         attr_set = true;
     }

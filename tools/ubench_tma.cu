@@ -128,7 +128,7 @@ int main()
         printf("no cuTensorMapEncodeTiled\n");
         return 1;
     }
-    const int boxes[][2] = {{16, 12}, {16, 16}, {24, 24}, {40, 40}, {72, 72}, {8, 8}, {16, 8}};
+    const int boxes[][2] = {{16, 12}, {16, 16}, {24, 24}, {40, 40}, {72, 72}, {8, 8}, {16, 8}, {32, 8}, {32, 24}, {48, 16}, {48, 40}, {80, 8}, {80, 16}, {80, 24}, {80, 40}, {80, 72}, {24, 72}, {16, 72}};
     const int ncls = sizeof(boxes) / sizeof(boxes[0]);
     std::vector<CUtensorMap> maps(ncls);
     for (int i = 0; i < ncls; i++) {
@@ -163,6 +163,15 @@ int main()
     cudaMemcpy(&hbad, bad, 4, cudaMemcpyDeviceToHost);
     printf("global-map + fence correctness: %d mismatching elements (%s)\n", hbad, cudaGetErrorString(e));
     if (e != cudaSuccess) return 1;
+    for (int i = 0; i < ncls; i++) {
+        cudaMemset(bad, 0, 4);
+        check<<<1, 128, boxes[i][0] * boxes[i][1] * 2>>>(dmaps, i, boxes[i][0], boxes[i][1], 1000 + 8 * i, 777 + 3 * i, plane, pitch / 2, bad);
+        e = cudaDeviceSynchronize();
+        cudaMemcpy(&hbad, bad, 4, cudaMemcpyDeviceToHost);
+        printf("box %dx%d: %d bad (%s)\n", boxes[i][0], boxes[i][1], hbad, cudaGetErrorString(e));
+        if (e != cudaSuccess) return 1;
+    }
+    return 0;
 
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
