@@ -20,7 +20,7 @@
 //    (PU, list, plane) into a shared-memory pool, issued by the thread that owns the PU,
 //    all landing on one mbarrier.  Window positions outside the halo are clamped to it,
 //    which is bit-identical to the reference's per-block edge emulation.
-//  * Work is then re-cut into CELLS of 8x4 luma samples (and their chroma): one thread per
+//  * Work is then re-cut into CELLS of 4x4 luma samples (and their chroma): one thread per
 //    cell, every thread running the same straight-line code, so a CTB of 64 tiny PUs keeps
 //    the lanes as busy as a CTB with one 64x64 PU.  The [my][mx] table dispatch is gone:
 //    every cell runs the separable h+v path with the phase-0 taps {0,0,0,64,0,0,0,0}
@@ -37,18 +37,18 @@
 
 namespace ohcu {
 
-constexpr int RC_WARPS = 4;
+constexpr int RC_WARPS = 8;
 constexpr int RC_THREADS = RC_WARPS * 32;
 constexpr int MAX_CTB_PUS = 128;             // 8x4 PUs of a 64x64 CTB
-constexpr int MAX_CTB_CELLS = 256;           // 4-wide PUs make half-empty cells
+constexpr int MAX_CTB_CELLS = 256;           // 4x4 cells of a 64x64 CTB
 constexpr int MAX_CTB_TUS = 768;             // 4x4 TBs of a 64x64 CTB, 3 full-size planes
 constexpr int POOL_ROUND = 32768;            // window bytes per round (before the last window's overhang)
 constexpr int POOL_BYTES = POOL_ROUND + 80 * 72 * 2;
 constexpr int MAX_ROUNDS = 8;                // per kind
 constexpr int N_KINDS = 4;                   // list slot A luma, slot B luma, slot A chroma, slot B chroma
 
-// scratch of one warp in the residual phase (aliases the window pool)
-struct WarpScratch { uint32_t w[2 * 32 * 34 / 2]; };
+// scratch of one warp in the residual phase (aliases the window pool): one 32x32 int16 block
+struct WarpScratch { uint32_t w[32 * 34 / 2]; };
 
 // ff_hevc_qpel_filters / ff_hevc_epel_filters (hevcdsp.c:181-195) packed four int8 taps
 // per word: [phase][0] = taps 0..3, [phase][1] = taps 4..7
@@ -259,15 +259,15 @@ __device__ __forceinline__ bool idct_reads(int j, int end)
 template <int N> struct Stride { static constexpr int S = N + 2; };   // int16 row stride, S/2 odd
 
 // one TB: coefficients -> residual, in place in blk[N][S]; N lanes (g = 0..N-1) cooperate
+// coef: the TB's N*N coefficients (shared-memory copy of the CTB's arena range, or global)
 template <int LOG2>
-__device__ void tb_residual(const FrameDev &f, const ohcu_tu &tu, int16_t *blk, int g, unsigned mask)
+__device__ __noinline__ void tb_residual(int bd, const ohcu_tu &tu, const int16_t *coef, int16_t *blk, int g, unsigned mask)
 {
     constexpr int N = 1 << LOG2, S = Stride<N>::S;
-    const int bd = f.bd;
     {
-        const uint32_t *src = (const uint32_t *)(f.coeffs + tu.coeff_off);
+        const uint32_t *src = (const uint32_t *)coef;
         for (int i = g; i < N * N / 2; i += N) {
-            const uint32_t v = __ldg(src + i);
+            const uint32_t v = src[i];
             const int e = 2 * i, r = e >> LOG2, c = e & (N - 1);
             *(uint32_t *)&blk[r * S + c] = v;
         }
@@ -361,24 +361,36 @@ struct CtbTile {
     int pitch[3];         // words per tile row
 };
 
+// Where the coefficients of this CTB are: csm != nullptr -> arena range [clo, ...) copied to
+// shared memory by one bulk copy, else read from global memory.
+struct CoefSrc {
+    const int16_t *csm;
+    uint32_t clo, chi;
+    const int16_t *glob;
+    __device__ __forceinline__ const int16_t *at(uint32_t off, int n) const
+    {
+        return (csm && off >= clo && off + n <= chi) ? csm + (off - clo) : glob + off;
+    }
+};
+
 template <int LOG2>
 __device__ void tu_batch(const FrameDev &f, const CtbTile &tile, int tu0, const uint16_t *list, int first, int count,
-                         int cx0, int cy0, WarpScratch &ws, int lane)
+                         int cx0, int cy0, WarpScratch &ws, WarpScratch *ws2, const CoefSrc &cs, int lane)
 {
     constexpr int N = 1 << LOG2, S = Stride<N>::S, GROUPS = 32 / N;
     const int grp = lane >> LOG2, g = lane & (N - 1);
     if (first + grp >= count) return;
     const unsigned mask = N == 32 ? 0xffffffffu : (((1u << N) - 1u) << (lane & ~(N - 1)));
     const ohcu_tu tu = f.tus[tu0 + list[first + grp]];
-    int16_t *blk = (int16_t *)&ws + (size_t)grp * 2 * N * S;
-    static_assert(GROUPS * 2 * N * S * 2 <= (int)sizeof(WarpScratch), "block buffers must fit the warp scratch");
+    int16_t *blk = (int16_t *)&ws + (size_t)grp * N * S;
+    static_assert(GROUPS * N * S * 2 <= (int)sizeof(WarpScratch), "block buffers must fit the warp scratch");
 
-    tb_residual<LOG2>(f, tu, blk, g, mask);
-    if (tu.flags & OHCU_TUF_CROSS) {                           // hevc_cabac.c:1810-1817
-        int16_t *by = blk + N * S;
+    tb_residual<LOG2>(f.bd, tu, cs.at(tu.coeff_off, N * N), blk, g, mask);
+    if ((tu.flags & OHCU_TUF_CROSS) && ws2) {                  // hevc_cabac.c:1810-1817
+        int16_t *by = (int16_t *)ws2 + (size_t)grp * N * S;
         const ohcu_tu ty = f.tus[tu.cross_tu];
         if (ty.log2_size == LOG2) {
-            tb_residual<LOG2>(f, ty, by, g, mask);
+            tb_residual<LOG2>(f.bd, ty, cs.at(ty.coeff_off, N * N), by, g, mask);
             const int scale = tu.res_scale_val;
 #pragma unroll
             for (int k = 0; k < N; k++)
@@ -409,7 +421,7 @@ __device__ __forceinline__ ohcu_pu load_pu(const ohcu_pu *p)
 }
 
 // What the cells of a PU need, prepared once by the thread that owns the PU.
-//   rect  x/4 | y/4 << 4 | w/4 << 8 | h/4 << 13 | bi << 18 | cells per row << 19   (position inside the CTB)
+//   rect  x/4 | y/4 << 4 | w/4 << 8 | h/4 << 13 | bi << 18                        (position inside the CTB)
 //   geom  [list slot A,B][luma, chroma]: pool offset / 16 | pitch / 16 << 12 | offx << 16 | mx << 20 | my << 23 | hcls << 26
 //   epi   per plane: (wA & 0xffff) | wB << 16,  add,  sh | post << 16
 struct PuRec {
@@ -455,9 +467,7 @@ __device__ __forceinline__ WinGeom win_geom(const FrameDev &f, const ohcu_pu &pu
     constexpr int A = HIGH ? 8 : 16;                       // samples per 16 bytes
     g.ax = x0 & ~(A - 1);
     g.offx = x0 - g.ax;
-    // the widest read of any cell of the PU: cells are 8 luma columns wide (partial for w = 4, 12)
-    const int cellw = luma ? 8 : (8 >> hs);
-    const int readw = g.offx + ((pu.w + 7) >> 3) * cellw + NT - 1;
+    const int readw = g.offx + needw;
     g.wcls = readw <= box_w(HIGH, 0) ? 0 : readw <= box_w(HIGH, 1) ? 1 : readw <= box_w(HIGH, 2) ? 2 : readw <= box_w(HIGH, 3) ? 3 : 4;
     g.hcls = needh <= box_h(0) ? 0 : needh <= box_h(1) ? 1 : needh <= box_h(2) ? 2 : needh <= box_h(3) ? 3 : 4;
     return g;
@@ -471,11 +481,9 @@ __device__ __forceinline__ int box_bytes(bool high, int wcls, int hcls) { return
 // tmp_array, template :2522), vertical pass, epilogue into the CTB tile.
 //   col0  first output column of the cell relative to the window's first needed column
 //   row0  first output row of the cell relative to the window's first row
-//   ncol  valid output columns (partial cells of 4- and 12-wide PUs)
 template <bool HIGH, int NT, int OW, int OH>
 __device__ __forceinline__ void mc_cell(const uint8_t *win, int pitch, int col0, int row0, uint32_t FX0, uint32_t FX1,
-                                        uint32_t FY0, uint32_t FY1, int sh1, const Epi &e, uint32_t *tw, int tpitch,
-                                        int ncol)
+                                        uint32_t FY0, uint32_t FY1, int sh1, const Epi &e, uint32_t *tw, int tpitch)
 {
     constexpr int NW = (OW + NT) / 2, NR = OH + NT - 1;
     uint32_t hb[NR][OW / 2];
@@ -492,7 +500,7 @@ __device__ __forceinline__ void mc_cell(const uint8_t *win, int pitch, int col0,
 #pragma unroll
             for (int j = 0; j < NW; j++) W[j] = __funnelshift_r(T[j], T[j + 1 < NW ? j + 1 : j], sh);
         } else {
-            constexpr int NB = NW / 2 + 1;
+            constexpr int NB = (NW + 1) / 2 + 1;
             const uint32_t *p = (const uint32_t *)rowp + (col0 >> 2);
             const int sh = (col0 & 3) * 8;
             uint32_t T[NB];
@@ -502,7 +510,7 @@ __device__ __forceinline__ void mc_cell(const uint8_t *win, int pitch, int col0,
             for (int j = 0; j < NB - 1; j++) {
                 const uint32_t v = __funnelshift_r(T[j], T[j + 1], sh);
                 W[2 * j] = __byte_perm(v, 0, 0x4140);
-                W[2 * j + 1] = __byte_perm(v, 0, 0x4342);
+                if (2 * j + 1 < NW) W[2 * j + 1] = __byte_perm(v, 0, 0x4342);
             }
         }
         int o[OW];
@@ -519,10 +527,8 @@ __device__ __forceinline__ void mc_cell(const uint8_t *win, int pitch, int col0,
         for (int r = 0; r < NR; r++) V[r] = hb[r][k];
         int oa[OH], ob[OH];
         fir_col<NT, OH>(V, FY0, FY1, oa, ob);
-        if (2 * k < ncol) {
 #pragma unroll
-            for (int r = 0; r < OH; r++) epi_pair(e, oa[r] >> 6, ob[r] >> 6, tw + r * tpitch + k);
-        }
+        for (int r = 0; r < OH; r++) epi_pair(e, oa[r] >> 6, ob[r] >> 6, tw + r * tpitch + k);
     }
 }
 
@@ -575,9 +581,11 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     int *rnd_cell = (int *)sp;                  sp += N_KINDS * MAX_ROUNDS;      // first sorted cell of each round
     int *rnd_bytes = (int *)sp;                 sp += N_KINDS * MAX_ROUNDS;      // TMA bytes of each round
     int *scan_tmp = (int *)sp;                  sp += 6 * RC_WARPS + 8;          // warp totals, then [24..29] totals
-    int *tu_cnt = (int *)sp;                    sp += 16;                         // [0..3] counts, [4..7] bases, [8..11] cursors
+    int *tu_cnt = (int *)sp;                    sp += 16;                         // [0..3] counts, [4..7] bases, [8..11] cursors, [12] coef lo, [13] coef hi
     uint16_t *tu_list = (uint16_t *)sp;         sp += MAX_CTB_TUS / 2;
-    uint64_t *mbar = (uint64_t *)(((uintptr_t)sp + 7) & ~(uintptr_t)7);
+    uint32_t *issue = sp;                       sp += N_KINDS * MAX_CTB_PUS * 2;  // TMA parameters per (kind, PU)
+    uint64_t *mbar = (uint64_t *)(((uintptr_t)sp + 7) & ~(uintptr_t)7);           sp += 4;
+    WarpScratch *scratch2 = f.cfi == 3 ? (WarpScratch *)(((uintptr_t)sp + 15) & ~(uintptr_t)15) : nullptr;   // cross-component
 
     const int2 prange = f.ctb_pu_range[ctb];
     const int p0 = prange.x, np = min(prange.y & 0xffffff, MAX_CTB_PUS);
@@ -608,10 +616,35 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         }
     }
     if (tid < 12) tu_cnt[tid] = 0;
+    if (tid == 12) { tu_cnt[12] = 0x7fffffff; tu_cnt[13] = 0; }
     if (tid < N_KINDS * MAX_ROUNDS) { rnd_pu[tid] = MAX_CTB_PUS; rnd_cell[tid] = MAX_CTB_CELLS; rnd_bytes[tid] = 0; }
     if (tid == 0) mbar_init(mbar, 1);
     __syncthreads();
 
+    // ---- TBs of the CTB sorted by size (counting sort) and the arena range their coefficients
+    //      occupy; done first so that its global-memory latency overlaps the prediction
+    if (nt > 0) {
+        for (int i = tid; i < nt; i += RC_THREADS) {
+            const ohcu_tu *tu = f.tus + t0 + i;
+            const int l2 = tu->log2_size;
+            const uint32_t off = tu->coeff_off;
+            atomicAdd(&tu_cnt[l2 - 2], 1);
+            atomicMin(&tu_cnt[12], (int)off);
+            atomicMax(&tu_cnt[13], (int)(off + (1u << (2 * l2))));
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int acc = 0;                                   // largest first: 32x32 batches are the long ones
+            for (int l = 3; l >= 0; l--) { tu_cnt[4 + l] = acc; acc += tu_cnt[l]; }
+        }
+        __syncthreads();
+        for (int i = tid; i < nt; i += RC_THREADS) {
+            const int l = f.tus[t0 + i].log2_size - 2;
+            tu_list[tu_cnt[4 + l] + atomicAdd(&tu_cnt[8 + l], 1)] = (uint16_t)i;
+        }
+    }
+
+    uint32_t parity = 0;                                   // phase of the (single) mbarrier
     // ================================================================ phase 1: prediction
     if (do_mc) {
         // ---- 1a. the thread that owns PU `tid` prepares its record
@@ -622,12 +655,12 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
             const ohcu_pu pu = load_pu(f.pus + p0 + tid);
             const ohcu_slice_tab &sl = f.slices[pu.slice];
             bi = pu.pred_flag == OHCU_PF_BI;
-            const int nx = (pu.w + 7) >> 3, ncell = nx * (pu.h >> 2);
+            const int ncell = (pu.w >> 2) * (pu.h >> 2);
             v[0] = ncell;
             v[1] = bi ? ncell : 0;
             PuRec &rc = recs[tid];
             rc.rect = (uint32_t)(((pu.x0 - cx0) >> 2) | (((pu.y0 - cy0) >> 2) << 4) | ((pu.w >> 2) << 8) | ((pu.h >> 2) << 13) |
-                                 ((bi ? 1 : 0) << 18) | (nx << 19));
+                                 ((bi ? 1 : 0) << 18));
             const int lA = (pu.pred_flag & 1) ? 0 : 1;
 #pragma unroll
             for (int s = 0; s < 2; s++) {
@@ -639,6 +672,11 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                     const WinGeom g = win_geom<HIGH>(f, pu, l, pt == 0);
                     const int pitch = box_w(HIGH, g.wcls) * (HIGH ? 2 : 1);
                     v[2 + 2 * pt + s] = pitch * box_h(g.hcls) * (pt ? 2 : 1);
+                    // what the TMA issue of this window needs (box of plane pt; Cr follows Cb)
+                    const int slot = sl.ref_slot[l][pu.ref_idx[l] & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1);
+                    uint32_t *iw = issue + ((2 * pt + s) * MAX_CTB_PUS + tid) * 2;
+                    iw[0] = (uint32_t)tmap_index(slot, pt, g.wcls, g.hcls) | ((uint32_t)(g.ax + PAD_X) << 12);
+                    iw[1] = (uint32_t)(g.y0 + PAD_Y) | ((uint32_t)((pitch * box_h(g.hcls)) >> 7) << 16);
                     gw[s][pt] = ((uint32_t)(pitch >> 4) << 12) | ((uint32_t)g.offx << 16) | ((uint32_t)g.mx << 20) |
                                 ((uint32_t)g.my << 23) | ((uint32_t)g.hcls << 26);
                 }
@@ -721,7 +759,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         __syncthreads();
         const int totA = scan_tmp[6 * RC_WARPS + 0], totB = scan_tmp[6 * RC_WARPS + 1];
         if (tid == 0) { cumA[np] = totA; cumB[np] = totB; }
-        // ---- 1c. cells sorted by PU: entry = PU | cell column << 7 | cell row << 10
+        // ---- 1c. cells sorted by PU: entry = PU | cell column << 7 | cell row << 11
 #pragma unroll 1
         for (int s = 0; s < 2; s++) {
             const int *cum = s ? cumB : cumA;
@@ -734,16 +772,15 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                     if (cum[mid] <= i) lo = mid; else hi = mid - 1;
                 }
                 const int local = i - cum[lo];
-                const int nx = (recs[lo].rect >> 19) & 15;
+                const int nx = (recs[lo].rect >> 8) & 31;
                 const int cy = fastdiv(local, fastinv(nx)), cx = local - cy * nx;
-                list[i] = (uint16_t)(lo | (cx << 7) | (cy << 10));
+                list[i] = (uint16_t)(lo | (cx << 7) | (cy << 11));
             }
         }
         __syncthreads();
 
         // ---- 1d. rounds: TMA the windows of a run of PUs into the pool, then one cell per thread
         const int sh1 = bd - 8;                            // first-stage shift (template :2486)
-        uint32_t parity = 0;
         const int nkinds = f.nplanes == 3 ? N_KINDS : 2;
 #pragma unroll 1
         for (int k = 0; k < nkinds; k++) {
@@ -761,27 +798,18 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                 if (tid == 0) mbar_expect_tx(mbar, (uint32_t)rnd_bytes[k * MAX_ROUNDS + r]);
                 if (pa + tid < pb) {
                     const int p = pa + tid;
-                    const ohcu_pu pu = load_pu(f.pus + p0 + p);
-                    const bool pbi = pu.pred_flag == OHCU_PF_BI;
-                    if (s == 0 || pbi) {
-                        const int l = s ? 1 : ((pu.pred_flag & 1) ? 0 : 1);
-                        const WinGeom g = win_geom<HIGH>(f, pu, l, pt == 0);
-                        const ohcu_slice_tab &sl = f.slices[pu.slice];
-                        const int slot = sl.ref_slot[l][pu.ref_idx[l] & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1);
-                        const uint32_t gword = recs[p].geom[s][pt];
-                        uint8_t *dst = pool + (gword & 0xfffu) * 16;
-                        const int bytes = box_bytes(HIGH, g.wcls, g.hcls);
-                        if (pt == 0) {
-                            const CUtensorMap *m = f.tmaps + tmap_index(slot, 0, g.wcls, g.hcls);
-                            tmap_acquire(m);
-                            tma_load_2d(dst, m, g.ax + PAD_X, g.y0 + PAD_Y, mbar);
-                        } else {
-#pragma unroll
-                            for (int c = 1; c < 3; c++) {
-                                const CUtensorMap *m = f.tmaps + tmap_index(slot, c, g.wcls, g.hcls);
-                                tmap_acquire(m);
-                                tma_load_2d(dst + (c - 1) * bytes, m, g.ax + PAD_X, g.y0 + PAD_Y, mbar);
-                            }
+                    const uint32_t *iw = issue + (k * MAX_CTB_PUS + p) * 2;
+                    const uint32_t w0 = iw[0], w1 = iw[1];
+                    const int bytes = (int)(w1 >> 16) << 7;
+                    if ((s == 0 || ((recs[p].rect >> 18) & 1)) && bytes > 0) {
+                        uint8_t *dst = pool + (recs[p].geom[s][pt] & 0xfffu) * 16;
+                        const CUtensorMap *m = f.tmaps + (w0 & 0xfffu);
+                        const int x = (int)(w0 >> 12), y = (int)(w1 & 0xffffu);
+                        tmap_acquire(m);
+                        tma_load_2d(dst, m, x, y, mbar);
+                        if (pt == 1) {
+                            tmap_acquire(m + N_WCLS * N_HCLS);
+                            tma_load_2d(dst + bytes, m + N_WCLS * N_HCLS, x, y, mbar);
                         }
                     }
                 }
@@ -793,10 +821,10 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
 #pragma unroll 1
                 for (int ci = clo + tid; ci < chi; ci += RC_THREADS) {
                     const int ent = list[ci];
-                    const int p = ent & 127, cx = (ent >> 7) & 7, cy = ent >> 10;
+                    const int p = ent & 127, cx = (ent >> 7) & 15, cy = ent >> 11;
                     const PuRec &rc = recs[p];
                     const uint32_t rect = rc.rect;
-                    const int x4 = rect & 15, y4 = (rect >> 4) & 15, w4 = (rect >> 8) & 31;
+                    const int x4 = rect & 15, y4 = (rect >> 4) & 15;
                     const bool pbi = (rect >> 18) & 1;
                     const uint32_t gword = rc.geom[s][pt];
                     const uint8_t *win = pool + (gword & 0xfffu) * 16;
@@ -806,29 +834,28 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                     if (pt == 0) {
                         const uint32_t ew[3] = {rc.epi[0][0], rc.epi[0][1], rc.epi[0][2]};
                         unpack_epi(ew, bd, pbi, pbi && s == 0, e);
-                        uint32_t *tp = tile.p[0] + (y4 * 4 + cy * 4) * tile.pitch[0] + ((x4 * 4 + cx * 8) >> 1);
-                        mc_cell<HIGH, 8, 8, 4>(win, pitch, offx + cx * 8, cy * 4, c_qpel4[mx][0], c_qpel4[mx][1], c_qpel4[my][0],
-                                               c_qpel4[my][1], sh1, e, tp, tile.pitch[0], w4 * 4 - cx * 8);
+                        uint32_t *tp = tile.p[0] + ((y4 + cy) * 4) * tile.pitch[0] + ((x4 + cx) * 2);
+                        mc_cell<HIGH, 8, 4, 4>(win, pitch, offx + cx * 4, cy * 4, c_qpel4[mx][0], c_qpel4[mx][1], c_qpel4[my][0],
+                                               c_qpel4[my][1], sh1, e, tp, tile.pitch[0]);
                     } else {
                         const int hs = f.hs, vs = f.vs;
-                        const int cw = 8 >> hs, ch = 4 >> vs;
+                        const int cw = 4 >> hs, ch = 4 >> vs;
                         const int bytes = pitch * box_h((gword >> 26) & 7);
 #pragma unroll 1
                         for (int c = 1; c < 3; c++) {
                             const uint32_t ew[3] = {rc.epi[c][0], rc.epi[c][1], rc.epi[c][2]};
                             unpack_epi(ew, bd, pbi, pbi && s == 0, e);
-                            uint32_t *tp = tile.p[c] + (((y4 * 4) >> vs) + cy * ch) * tile.pitch[c] + ((((x4 * 4) >> hs) + cx * cw) >> 1);
+                            uint32_t *tp = tile.p[c] + ((y4 + cy) * ch) * tile.pitch[c] + (((x4 + cx) * cw) >> 1);
                             const uint8_t *wc = win + (c - 1) * bytes;
-                            const int ncol = ((w4 * 4) >> hs) - cx * cw;
                             if (hs && vs)
-                                mc_cell<HIGH, 4, 4, 2>(wc, pitch, offx + cx * 4, cy * 2, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
-                                                       tp, tile.pitch[c], ncol);
+                                mc_cell<HIGH, 4, 2, 2>(wc, pitch, offx + cx * 2, cy * 2, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
+                                                       tp, tile.pitch[c]);
                             else if (hs)
-                                mc_cell<HIGH, 4, 4, 4>(wc, pitch, offx + cx * 4, cy * 4, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
-                                                       tp, tile.pitch[c], ncol);
+                                mc_cell<HIGH, 4, 2, 4>(wc, pitch, offx + cx * 2, cy * 4, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
+                                                       tp, tile.pitch[c]);
                             else
-                                mc_cell<HIGH, 4, 8, 4>(wc, pitch, offx + cx * 8, cy * 4, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
-                                                       tp, tile.pitch[c], ncol);
+                                mc_cell<HIGH, 4, 4, 4>(wc, pitch, offx + cx * 4, cy * 4, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
+                                                       tp, tile.pitch[c]);
                         }
                     }
                 }
@@ -837,23 +864,27 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     }
 
     // ================================================================ phase 2: residual
-    // Counting sort of the CTB's TBs by size, then batches of equal-size TBs per warp.
+    __syncthreads();          // prediction complete: the pool is free
     if (nt > 0) {
-        for (int i = tid; i < nt; i += RC_THREADS) atomicAdd(&tu_cnt[f.tus[t0 + i].log2_size - 2], 1);
-        __syncthreads();
-        if (tid == 0) {
-            int acc = 0;                                   // largest first: 32x32 batches are the long ones
-            for (int l = 3; l >= 0; l--) { tu_cnt[4 + l] = acc; acc += tu_cnt[l]; }
+        // the CTB's coefficients sit in one arena range (TBs are appended CTB by CTB): one bulk
+        // copy brings them next to the per-warp block buffers; ranges that do not fit are read
+        // from global memory block by block
+        int16_t *coef_sm = (int16_t *)(pool + RC_WARPS * sizeof(WarpScratch));
+        const uint32_t clo = (uint32_t)tu_cnt[12], chi = (uint32_t)tu_cnt[13];
+        const uint32_t cbytes = (chi - clo) * 2;
+        const bool staged = chi > clo && cbytes <= (uint32_t)(POOL_BYTES - RC_WARPS * sizeof(WarpScratch)) && !(cbytes & 15) && !(clo & 7);
+        if (staged) {
+            if (tid == 0) {
+                mbar_expect_tx(mbar, cbytes);
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             ::"r"(smem_u32(coef_sm)), "l"(f.coeffs + clo), "r"(cbytes), "r"(smem_u32(mbar)) : "memory");
+            }
+            mbar_wait(mbar, parity);
         }
-        __syncthreads();
-        for (int i = tid; i < nt; i += RC_THREADS) {
-            const int l = f.tus[t0 + i].log2_size - 2;
-            tu_list[tu_cnt[4 + l] + atomicAdd(&tu_cnt[8 + l], 1)] = (uint16_t)i;
-        }
-    }
-    __syncthreads();          // prediction complete (the pool is free), TB list sorted
-    if (nt > 0) {
+        CoefSrc cs;
+        cs.csm = staged ? coef_sm : nullptr; cs.clo = clo; cs.chi = chi; cs.glob = f.coeffs;
         WarpScratch &ws = ((WarpScratch *)pool)[warp];
+        WarpScratch *ws2 = scratch2 ? scratch2 + warp : nullptr;
         int b = 0;            // running batch number over all size classes
 #pragma unroll
         for (int l = 3; l >= 0; l--) {
@@ -861,10 +892,10 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
             const int per = 32 >> (l + 2);                 // TBs per batch
             const int nb = (cnt + per - 1) / per;
             for (int k = (warp - b) & (RC_WARPS - 1); k < nb; k += RC_WARPS) {
-                if (l == 3) tu_batch<5>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, lane);
-                if (l == 2) tu_batch<4>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, lane);
-                if (l == 1) tu_batch<3>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, lane);
-                if (l == 0) tu_batch<2>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, lane);
+                if (l == 3) tu_batch<5>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, ws2, cs, lane);
+                if (l == 2) tu_batch<4>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, ws2, cs, lane);
+                if (l == 1) tu_batch<3>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, ws2, cs, lane);
+                if (l == 0) tu_batch<2>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, ws2, cs, lane);
                 __syncwarp();
             }
             b = (b + nb) & (RC_WARPS - 1);
@@ -898,8 +929,8 @@ size_t recon_smem_bytes(const FrameDev &f)
         words += (size_t)(((cs >> hs) >> 1) + 2) * (cs >> vs);
     }
     words += MAX_CTB_PUS * (sizeof(PuRec) / 4) + 2 * (MAX_CTB_PUS + 4) + MAX_CTB_CELLS + 3 * N_KINDS * MAX_ROUNDS +
-             6 * RC_WARPS + 8 + 16 + MAX_CTB_TUS / 2 + 4;
-    return POOL_BYTES + words * 4;
+             6 * RC_WARPS + 8 + 16 + MAX_CTB_TUS / 2 + N_KINDS * MAX_CTB_PUS * 2 + 8;
+    return POOL_BYTES + words * 4 + (f.cfi == 3 ? RC_WARPS * sizeof(WarpScratch) + 16 : 0);
 }
 
 int launch_recon(const FrameDev &f, int flags, cudaStream_t st)
