@@ -8,7 +8,9 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <new>
+#include <utility>
 #include <vector>
 
 #include "ohcu_internal.h"
@@ -151,8 +153,21 @@ static int build_tensor_maps(ohcu_ctx *c)
                                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
                     if (r != CUDA_SUCCESS) return fail(OHCU_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
                 }
+    // Descriptor memory is never recycled for DIFFERENT content: the TMA unit caches
+    // descriptors by address and the kernels issue no per-use proxy fence (it costs about
+    // as much as the copy it guards, tools/ubench_tma.cu).  Blocks are kept for the life of
+    // the process and shared by contexts whose maps are byte-identical.
+    static std::mutex mu;
+    static std::vector<std::pair<CUtensorMap *, std::vector<CUtensorMap>>> cache;
+    std::lock_guard<std::mutex> lock(mu);
+    for (auto &e : cache)
+        if (e.second.size() == maps.size() && !memcmp(e.second.data(), maps.data(), maps.size() * sizeof(CUtensorMap))) {
+            c->tmaps_d = e.first;
+            return 0;
+        }
     CU(cudaMalloc((void **)&c->tmaps_d, maps.size() * sizeof(CUtensorMap)));
     CU(cudaMemcpy(c->tmaps_d, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
+    cache.emplace_back(c->tmaps_d, maps);
     return 0;
 }
 
@@ -219,7 +234,6 @@ extern "C" int ohcu_destroy(ohcu_ctx *c)
     }
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->l2_buf) cudaFree(c->l2_buf);
-    if (c->tmaps_d) cudaFree(c->tmaps_d);
     if (c->t0) cudaEventDestroy(c->t0);
     if (c->t1) cudaEventDestroy(c->t1);
     delete c;

@@ -92,29 +92,28 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *b, uint32_t bytes)
 __device__ __forceinline__ void mbar_wait(uint64_t *b, uint32_t parity)
 {
     uint32_t ok = 0;
-    const long long t0 = clock64();
-    while (!ok) {
-        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
-                     : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    long long t0 = 0;
+    for (int spin = 0; !ok; spin++) {
+        // try_wait suspends the warp until the phase completes or the hint (ns) runs out
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(smem_u32(b)), "r"(parity), "r"(20000) : "memory");
         // a transfer that never completes is a bug, not a reason to hang the GPU: fail the launch
-        if (!ok && clock64() - t0 > 2000000000ll) __trap();
+        if (!ok && (spin & 63) == 63) {
+            if (!t0) t0 = clock64();
+            else if (clock64() - t0 > 4000000000ll) __trap();
+        }
     }
 }
 // 2-D box at (x, y) of the tensor behind `map` -> dst (128-byte aligned); x*sizeof(sample) must
-// be a multiple of 16 (tools/ubench_tma.cu: anything else faults on this part)
+// be a multiple of 16 (tools/ubench_tma.cu: anything else faults on this part).  The maps live in
+// global memory that is written once and never reused for other content (api.cu), so no
+// tensormap proxy fence is issued here.
 __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, int x, int y, uint64_t *bar)
 {
     asm volatile(
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
         ::"r"(smem_u32(dst)), "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar)) : "memory");
 }
-// tensor maps live in global memory (written once by ohcu_create): make them visible to the
-// TMA unit's descriptor fetch
-__device__ __forceinline__ void tmap_acquire(const CUtensorMap *map)
-{
-    asm volatile("fence.proxy.tensormap::generic.acquire.sys [%0], 128;" ::"l"(map) : "memory");
-}
-
 // ---------------------------------------------------------------- dot-product helpers
 __device__ __forceinline__ int dp2lo(uint32_t a, uint32_t b, int c) { return __dp2a_lo((int)a, (int)b, c); }
 __device__ __forceinline__ int dp2hi(uint32_t a, uint32_t b, int c) { return __dp2a_hi((int)a, (int)b, c); }
@@ -581,7 +580,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     int *rnd_cell = (int *)sp;                  sp += N_KINDS * MAX_ROUNDS;      // first sorted cell of each round
     int *rnd_bytes = (int *)sp;                 sp += N_KINDS * MAX_ROUNDS;      // TMA bytes of each round
     int *scan_tmp = (int *)sp;                  sp += 6 * RC_WARPS + 8;          // warp totals, then [24..29] totals
-    int *tu_cnt = (int *)sp;                    sp += 16;                         // [0..3] counts, [4..7] bases, [8..11] cursors, [12] coef lo, [13] coef hi
+    int *tu_cnt = (int *)sp;                    sp += 16;                         // [0..3] counts, [4..7] bases, [8..11] cursors, [12] coef lo, [13] coef hi, [14] batch counter
     uint16_t *tu_list = (uint16_t *)sp;         sp += MAX_CTB_TUS / 2;
     uint32_t *issue = sp;                       sp += N_KINDS * MAX_CTB_PUS * 2;  // TMA parameters per (kind, PU)
     uint64_t *mbar = (uint64_t *)(((uintptr_t)sp + 7) & ~(uintptr_t)7);           sp += 4;
@@ -616,7 +615,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         }
     }
     if (tid < 12) tu_cnt[tid] = 0;
-    if (tid == 12) { tu_cnt[12] = 0x7fffffff; tu_cnt[13] = 0; }
+    if (tid == 12) { tu_cnt[12] = 0x7fffffff; tu_cnt[13] = 0; tu_cnt[14] = 0; }
     if (tid < N_KINDS * MAX_ROUNDS) { rnd_pu[tid] = MAX_CTB_PUS; rnd_cell[tid] = MAX_CTB_CELLS; rnd_bytes[tid] = 0; }
     if (tid == 0) mbar_init(mbar, 1);
     __syncthreads();
@@ -805,10 +804,8 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                         uint8_t *dst = pool + (recs[p].geom[s][pt] & 0xfffu) * 16;
                         const CUtensorMap *m = f.tmaps + (w0 & 0xfffu);
                         const int x = (int)(w0 >> 12), y = (int)(w1 & 0xffffu);
-                        tmap_acquire(m);
                         tma_load_2d(dst, m, x, y, mbar);
                         if (pt == 1) {
-                            tmap_acquire(m + N_WCLS * N_HCLS);
                             tma_load_2d(dst + bytes, m + N_WCLS * N_HCLS, x, y, mbar);
                         }
                     }
@@ -885,20 +882,19 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         cs.csm = staged ? coef_sm : nullptr; cs.clo = clo; cs.chi = chi; cs.glob = f.coeffs;
         WarpScratch &ws = ((WarpScratch *)pool)[warp];
         WarpScratch *ws2 = scratch2 ? scratch2 + warp : nullptr;
-        int b = 0;            // running batch number over all size classes
-#pragma unroll
-        for (int l = 3; l >= 0; l--) {
-            const int cnt = tu_cnt[l], base = tu_cnt[4 + l];
-            const int per = 32 >> (l + 2);                 // TBs per batch
-            const int nb = (cnt + per - 1) / per;
-            for (int k = (warp - b) & (RC_WARPS - 1); k < nb; k += RC_WARPS) {
-                if (l == 3) tu_batch<5>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, ws2, cs, lane);
-                if (l == 2) tu_batch<4>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, ws2, cs, lane);
-                if (l == 1) tu_batch<3>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, ws2, cs, lane);
-                if (l == 0) tu_batch<2>(f, tile, t0, tu_list + base, k * per, cnt, cx0, cy0, ws, ws2, cs, lane);
-                __syncwarp();
-            }
-            b = (b + nb) & (RC_WARPS - 1);
+        // batches (32/N TBs of one size) are handed out dynamically, largest blocks first
+        const int nb3 = tu_cnt[3], nb2 = (tu_cnt[2] + 1) >> 1, nb1 = (tu_cnt[1] + 3) >> 2, nb0 = (tu_cnt[0] + 7) >> 3;
+        const int nbatch = nb3 + nb2 + nb1 + nb0;
+        for (;;) {
+            int b = 0;
+            if (lane == 0) b = atomicAdd(&tu_cnt[14], 1);
+            b = __shfl_sync(0xffffffffu, b, 0);
+            if (b >= nbatch) break;
+            if (b < nb3) tu_batch<5>(f, tile, t0, tu_list + tu_cnt[4 + 3], b, tu_cnt[3], cx0, cy0, ws, ws2, cs, lane);
+            else if ((b -= nb3) < nb2) tu_batch<4>(f, tile, t0, tu_list + tu_cnt[4 + 2], b * 2, tu_cnt[2], cx0, cy0, ws, ws2, cs, lane);
+            else if ((b -= nb2) < nb1) tu_batch<3>(f, tile, t0, tu_list + tu_cnt[4 + 1], b * 4, tu_cnt[1], cx0, cy0, ws, ws2, cs, lane);
+            else tu_batch<2>(f, tile, t0, tu_list + tu_cnt[4 + 0], (b - nb1) * 8, tu_cnt[0], cx0, cy0, ws, ws2, cs, lane);
+            __syncwarp();
         }
     }
     __syncthreads();
