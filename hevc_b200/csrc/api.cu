@@ -65,6 +65,7 @@ struct Job {
     bool staged = false;
     int out_slot = -1, poc = 0;
     Picture recon;
+    LfMaps lf_maps{};                 // recon planes as the loop filter kernel fetches them
     // lists
     Arena<ohcu_pu> pus;      int n_pu = 0;
     Arena<int2> ctb_range;   // per CTB: first PU, count
@@ -128,6 +129,7 @@ static int alloc_picture(const ohcu_ctx *c, Picture *p, bool padded)
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static void fill_seq_dev(const ohcu_ctx *c, FrameDev *f);
 static int build_tensor_maps(ohcu_ctx *c)
 {
     EncodeTiledFn enc = nullptr;
@@ -153,6 +155,23 @@ static int build_tensor_maps(ohcu_ctx *c)
                                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
                     if (r != CUDA_SUCCESS) return fail(OHCU_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
                 }
+    // the loop filter reads each job's reconstructed picture through kernel-parameter maps
+    FrameDev fbox{};
+    fill_seq_dev(c, &fbox);
+    for (auto &j : c->jobs)
+        for (int pl = 0; pl < c->nplanes; pl++) {
+            int bw, bh;
+            loopfilter_box(fbox, pl, &bw, &bh);
+            cuuint64_t gdim[2] = {(cuuint64_t)c->pw[pl], (cuuint64_t)c->ph[pl]};
+            cuuint64_t gstr[1] = {(cuuint64_t)j.recon.ps.pitch[pl]};
+            cuuint32_t box[2] = {(cuuint32_t)bw, (cuuint32_t)bh};
+            cuuint32_t estr[2] = {1, 1};
+            CUresult r = enc(&j.lf_maps.m[pl], high ? CU_TENSOR_MAP_DATA_TYPE_UINT16 : CU_TENSOR_MAP_DATA_TYPE_UINT8, 2,
+                             j.recon.ps.p[pl], gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) return fail(OHCU_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+        }
     // Descriptor memory is never recycled for DIFFERENT content: the TMA unit caches
     // descriptors by address and the kernels issue no per-use proxy fence (it costs about
     // as much as the copy it guards, tools/ubench_tma.cu).  Blocks are kept for the life of
@@ -745,8 +764,11 @@ extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int 
     FrameDev f;
     fill_frame_dev(c, j, &f);
     const bool do_sao = c->sp.sao_enabled && j.has_sao && (stages & 8);
+    const int lf_flags = (((stages & 4) && j.has_deblock) ? 1 : 0) | (do_sao ? 2 : 0);
     f.out = os.pic.ps;
-    f.work = do_sao ? j.recon.ps : os.pic.ps;
+    // with a loop filter to follow, prediction + residual go to the job's own picture and the
+    // filter kernel writes the slot; otherwise they write the slot directly
+    f.work = lf_flags ? j.recon.ps : os.pic.ps;
     const bool timed = c->profiling;
     int n, total = 0;
 #define STAGE_EVENT(i) do { if (timed) CU(cudaEventRecord(j.ev[i], st)); } while (0)
@@ -754,14 +776,14 @@ extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int 
         CU(cudaGetLastError()); } while (0)
     STAGE_EVENT(0);
     // samples this launch does not predict keep the slot's current content
-    if ((!(stages & 1) || !j.all_covered) && do_sao) LAUNCHED(launch_copy_picture(f, f.work, f.out, st));
+    if ((!(stages & 1) || !j.all_covered) && lf_flags) LAUNCHED(launch_copy_picture(f, f.work, f.out, st));
     // MC and the residual run fused (recon.cu); stage 1 carries their time
     LAUNCHED(launch_recon(f, stages & 3, st));
     STAGE_EVENT(1);
     STAGE_EVENT(2);
-    if ((stages & 4) && j.has_deblock) LAUNCHED(launch_deblock(f, st));
+    // deblocking and SAO run fused (loopfilter.cu); stage 3 carries their time
+    if (lf_flags) LAUNCHED(launch_loopfilter(f, j.lf_maps, lf_flags, st));
     STAGE_EVENT(3);
-    if (do_sao) LAUNCHED(launch_sao(f, st));
     // the finished picture becomes a reference: replicate its borders into the halo
     LAUNCHED(launch_pad_picture(f, f.out, st));
     STAGE_EVENT(4);

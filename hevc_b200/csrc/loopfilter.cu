@@ -1,0 +1,457 @@
+// loopfilter.cu — deblocking + SAO of one picture in ONE pass: out = SAO(deblock(recon)).
+//
+// Replaces, per picture, ff_hevc_hls_filter / ff_hevc_hls_filters (hevc_filter.c:1211-1245):
+//   deblocking_filter_CTB (hevc_filter.c:525-762) and the table entries
+//     hevc_{h,v}_loop_filter_{luma,chroma}(_c)             hevcdsp_template.c:3377-3553
+//   sao_filter_CTB (hevc_filter.c:264-502), restore_tqb_pixels (:229-260) and
+//     sao_band_filter / sao_edge_filter / sao_edge_restore   hevcdsp_template.c:310-531
+//
+// One CTA owns a 64x64 luma region (and its chroma).  The region plus a halo is fetched
+// from the reconstructed picture into shared memory by TMA (one 2-D box per plane, zero
+// fill outside the picture), then
+//   1. every 4-line segment of every VERTICAL edge in the tile is filtered in place,
+//   2. every 4-line segment of every HORIZONTAL edge, on the result (the standard's order:
+//      all vertical edges of the picture before the horizontal ones; edges sit on an 8x8
+//      grid and touch at most 3 samples per side, so segments of one direction are
+//      independent and a 4-sample halo reproduces the picture-wide result),
+//   3. SAO reads the deblocked tile (+1 sample of halo) and writes the DPB slot with
+//      full-width stores.
+// The deblocked picture never goes to HBM: one read and one write per sample for both
+// filters.  tc / beta / pcm flags are derived on the device from the bs planes, qp_y_tab
+// and the per-CTB offsets exactly as the reference driver does, including its choice of
+// which CTB's offsets apply (hevc_filter.c:666, 699, 712, 721).
+#include "ohcu_internal.h"
+
+namespace ohcu {
+
+constexpr int LF_THREADS = 256;
+constexpr int LF_REGION = 64;                 // luma samples per side of a CTA's region
+
+__constant__ uint8_t c_tctable[54] = {
+    0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 1, 1, 1, 1, 2, 2, 2, 2, 3,
+    3, 3, 3, 4, 4, 4, 5, 5, 6, 6, 7, 8, 9, 10, 11, 13, 14, 16, 18, 20, 22, 24};
+__constant__ uint8_t c_betatable[52] = {
+    0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18,
+    20, 22, 24, 26, 28, 30, 32, 34, 36, 38, 40, 42, 44, 46, 48, 50, 52, 54, 56, 58, 60, 62, 64};
+__constant__ uint8_t c_qpc420[14] = {29, 30, 31, 32, 33, 33, 34, 34, 35, 35, 36, 36, 37, 37};
+
+// ---------------------------------------------------------------- TMA / mbarrier (as recon.cu)
+__device__ __forceinline__ uint32_t lf_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void lf_mbar_wait(uint64_t *b, uint32_t parity)
+{
+    uint32_t ok = 0;
+    long long t0 = 0;
+    for (int spin = 0; !ok; spin++) {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(lf_smem_u32(b)), "r"(parity), "r"(20000) : "memory");
+        if (!ok && (spin & 63) == 63) {
+            if (!t0) t0 = clock64();
+            else if (clock64() - t0 > 4000000000ll) __trap();
+        }
+    }
+}
+
+// ---------------------------------------------------------------- side information
+__device__ __forceinline__ int qpy_at(const FrameDev &f, int x, int y)
+{
+    return f.qp_y[(x >> f.log2_min_cb) + (y >> f.log2_min_cb) * f.min_cb_w];
+}
+__device__ __forceinline__ int pcm_at(const FrameDev &f, int x, int y)     // get_pcm, hevc_filter.c:504-518
+{
+    if (x < 0 || y < 0) return 2;
+    const int xp = x >> f.log2_min_pu, yp = y >> f.log2_min_pu;
+    if (xp >= f.min_pu_w || yp >= f.min_pu_h) return 2;
+    return f.is_pcm ? f.is_pcm[yp * f.min_pu_w + xp] : 0;
+}
+__device__ __forceinline__ int ctb_at(const FrameDev &f, int x, int y)
+{
+    return (x >> f.log2_ctb) + (y >> f.log2_ctb) * f.ctb_w;
+}
+__device__ __forceinline__ int chroma_tc(const FrameDev &f, int qp_y, int c, int tc_offset)   // hevc_filter.c:65-92
+{
+    const int qi = clip3i(qp_y + (c == 1 ? f.cb_qp_offset : f.cr_qp_offset), 0, 57);
+    int qp;
+    if (f.cfi == 1) qp = qi < 30 ? qi : (qi > 43 ? qi - 6 : c_qpc420[qi - 30]);
+    else qp = min(qi, 51);
+    return c_tctable[clip3i(qp + 2 + tc_offset, 0, 53)];
+}
+
+struct SegParam { int beta, tc, no_p, no_q; bool on; };
+
+// parameters of the 4-row segment starting at plane row ys of the VERTICAL edge at plane column ex
+__device__ __forceinline__ SegParam vseg_param(const FrameDev &f, int c, int ex, int ys)
+{
+    SegParam p = {0, 0, 0, 0, false};
+    const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
+    const int lx = ex << hs, ysl = ys << vs;
+    const int bs = f.vbs[(lx + ysl * f.bs_width) >> 2];
+    const int cb = ctb_at(f, lx, ysl);
+    if (c == 0) {
+        if (!bs) return p;
+        const int yu = ysl & ~7;                                   // 8-row unit, qp at its first row (:571)
+        const int qp = (qpy_at(f, lx - 1, yu) + qpy_at(f, lx, yu) + 1) >> 1;
+        p.beta = c_betatable[clip3i(qp + f.db[cb].beta_offset, 0, 51)];
+        const int tco = f.db[cb].tc_offset;
+        p.tc = c_tctable[clip3i(qp + 2 * (bs - 1) + (tco >> 1 << 1), 0, 53)];
+    } else {
+        if (bs != 2) return p;
+        const int qp = (qpy_at(f, lx - 1, ysl) + qpy_at(f, lx, ysl) + 1) >> 1;   // per segment (:614-615)
+        p.tc = chroma_tc(f, qp, c, f.db[cb].tc_offset);
+    }
+    if (f.pcm_or_bypass) { p.no_p = pcm_at(f, lx - 1, ysl); p.no_q = pcm_at(f, lx, ysl); }
+    p.on = true;
+    return p;
+}
+
+// parameters of the 4-column segment starting at plane column xs of the HORIZONTAL edge at plane row ey
+__device__ __forceinline__ SegParam hseg_param(const FrameDev &f, int c, int xs, int ey)
+{
+    SegParam p = {0, 0, 0, 0, false};
+    const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
+    const int xsl = xs << hs, ly = ey << vs;
+    const int bs = f.hbs[(xsl + ly * f.bs_width) >> 2];
+    const int unit = 8 << hs;                        // edge unit length in luma columns
+    const int xu = xsl & ~(unit - 1);
+    // CTB that runs this unit in the reference: the one owning column xu + unit, the last CTB
+    // column taking the remainder (hevc_filter.c:661-667, 715-718)
+    const int xproc = (xu + unit < f.width) ? xu + unit : xu;
+    const int cb_proc = ctb_at(f, xproc, ly), cb_here = ctb_at(f, xu, ly);
+    if (c == 0) {
+        if (!bs) return p;
+        const int qp = (qpy_at(f, xu, ly - 1) + qpy_at(f, xu, ly) + 1) >> 1;
+        p.beta = c_betatable[clip3i(qp + f.db[cb_here].beta_offset, 0, 51)];
+        const int tco = f.db[cb_proc].tc_offset;
+        p.tc = c_tctable[clip3i(qp + 2 * (bs - 1) + (tco >> 1 << 1), 0, 53)];
+    } else {
+        if (bs != 2) return p;
+        const int qp = (qpy_at(f, xsl, ly - 1) + qpy_at(f, xsl, ly) + 1) >> 1;
+        const bool first = xsl == xu;                // first segment of the unit
+        p.tc = chroma_tc(f, qp, c, f.db[first ? cb_here : cb_proc].tc_offset);
+    }
+    if (f.pcm_or_bypass) { p.no_p = pcm_at(f, xsl, ly - 1); p.no_q = pcm_at(f, xsl, ly); }
+    p.on = true;
+    return p;
+}
+
+// one 4-line luma segment: l[line][0..7] = P3 P2 P1 P0 Q0 Q1 Q2 Q3 (template :3390-3470)
+__device__ __forceinline__ void luma_segment(int (&l)[4][8], int bd, int beta, int tc, int no_p, int no_q)
+{
+    const int maxv = (1 << bd) - 1;
+    beta <<= bd - 8;
+    tc <<= bd - 8;
+    const int dp0 = abs(l[0][1] - 2 * l[0][2] + l[0][3]), dq0 = abs(l[0][6] - 2 * l[0][5] + l[0][4]);
+    const int dp3 = abs(l[3][1] - 2 * l[3][2] + l[3][3]), dq3 = abs(l[3][6] - 2 * l[3][5] + l[3][4]);
+    const int d0 = dp0 + dq0, d3 = dp3 + dq3;
+    if (d0 + d3 >= beta) return;
+    const int beta_3 = beta >> 3, beta_2 = beta >> 2, tc25 = (tc * 5 + 1) >> 1;
+    const bool strong =
+        abs(l[0][0] - l[0][3]) + abs(l[0][7] - l[0][4]) < beta_3 && abs(l[0][3] - l[0][4]) < tc25 &&
+        abs(l[3][0] - l[3][3]) + abs(l[3][7] - l[3][4]) < beta_3 && abs(l[3][3] - l[3][4]) < tc25 &&
+        (d0 << 1) < beta_2 && (d3 << 1) < beta_2;
+    if (strong) {
+        const int tc2 = tc << 1;
+#pragma unroll
+        for (int d = 0; d < 4; d++) {
+            const int p3 = l[d][0], p2 = l[d][1], p1 = l[d][2], p0 = l[d][3];
+            const int q0 = l[d][4], q1 = l[d][5], q2 = l[d][6], q3 = l[d][7];
+            if (!no_p) {
+                l[d][3] = p0 + clip3i(((p2 + 2 * p1 + 2 * p0 + 2 * q0 + q1 + 4) >> 3) - p0, -tc2, tc2);
+                l[d][2] = p1 + clip3i(((p2 + p1 + p0 + q0 + 2) >> 2) - p1, -tc2, tc2);
+                l[d][1] = p2 + clip3i(((2 * p3 + 3 * p2 + p1 + p0 + q0 + 4) >> 3) - p2, -tc2, tc2);
+            }
+            if (!no_q) {
+                l[d][4] = q0 + clip3i(((p1 + 2 * p0 + 2 * q0 + 2 * q1 + q2 + 4) >> 3) - q0, -tc2, tc2);
+                l[d][5] = q1 + clip3i(((p0 + q0 + q1 + q2 + 2) >> 2) - q1, -tc2, tc2);
+                l[d][6] = q2 + clip3i(((2 * q3 + 3 * q2 + q1 + q0 + p0 + 4) >> 3) - q2, -tc2, tc2);
+            }
+        }
+    } else {
+        const int side = (beta + (beta >> 1)) >> 3, tc_2 = tc >> 1;
+        const bool nd_p2 = dp0 + dp3 < side, nd_q2 = dq0 + dq3 < side;
+#pragma unroll
+        for (int d = 0; d < 4; d++) {
+            const int p2 = l[d][1], p1 = l[d][2], p0 = l[d][3];
+            const int q0 = l[d][4], q1 = l[d][5], q2 = l[d][6];
+            int delta0 = (9 * (q0 - p0) - 3 * (q1 - p1) + 8) >> 4;
+            if (abs(delta0) < 10 * tc) {
+                delta0 = clip3i(delta0, -tc, tc);
+                if (!no_p) l[d][3] = clip3i(p0 + delta0, 0, maxv);
+                if (!no_q) l[d][4] = clip3i(q0 - delta0, 0, maxv);
+                if (!no_p && nd_p2)
+                    l[d][2] = clip3i(p1 + clip3i((((p2 + p0 + 1) >> 1) - p1 + delta0) >> 1, -tc_2, tc_2), 0, maxv);
+                if (!no_q && nd_q2)
+                    l[d][5] = clip3i(q1 + clip3i((((q2 + q0 + 1) >> 1) - q1 - delta0) >> 1, -tc_2, tc_2), 0, maxv);
+            }
+        }
+    }
+}
+
+// one 4-line chroma segment: l[line][2..5] = P1 P0 Q0 Q1 (template :3473-3505)
+__device__ __forceinline__ void chroma_segment(int (&l)[4][8], int bd, int tc, int no_p, int no_q)
+{
+    const int maxv = (1 << bd) - 1;
+    tc <<= bd - 8;
+    if (tc <= 0) return;
+#pragma unroll
+    for (int d = 0; d < 4; d++) {
+        const int p1 = l[d][2], p0 = l[d][3], q0 = l[d][4], q1 = l[d][5];
+        const int delta0 = clip3i((((q0 - p0) * 4) + p1 - q1 + 4) >> 3, -tc, tc);
+        if (!no_p) l[d][3] = clip3i(p0 + delta0, 0, maxv);
+        if (!no_q) l[d][4] = clip3i(q0 - delta0, 0, maxv);
+    }
+}
+
+// four consecutive samples, aligned to 4 * sizeof(pixel)
+__device__ __forceinline__ void ld4(const uint16_t *p, int *v)
+{
+    const uint2 w = *(const uint2 *)p;
+    v[0] = w.x & 0xffff; v[1] = w.x >> 16; v[2] = w.y & 0xffff; v[3] = w.y >> 16;
+}
+__device__ __forceinline__ void ld4(const uint8_t *p, int *v)
+{
+    const uint32_t w = *(const uint32_t *)p;
+    v[0] = w & 0xff; v[1] = (w >> 8) & 0xff; v[2] = (w >> 16) & 0xff; v[3] = w >> 24;
+}
+__device__ __forceinline__ void st4(uint16_t *p, const int *v)
+{
+    *(uint2 *)p = make_uint2((uint32_t)v[0] | ((uint32_t)v[1] << 16), (uint32_t)v[2] | ((uint32_t)v[3] << 16));
+}
+__device__ __forceinline__ void st4(uint8_t *p, const int *v)
+{
+    *(uint32_t *)p = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24);
+}
+
+// ---------------------------------------------------------------- the kernel
+// flags: bit 0 deblock, bit 1 SAO.  Source f.work (the job's reconstructed picture, reached
+// through `maps`), destination f.out (the DPB slot).
+template <typename pixel>
+__global__ void __launch_bounds__(LF_THREADS) loopfilter_kernel(const __grid_constant__ FrameDev f,
+                                                                 const __grid_constant__ LfMaps maps, int flags)
+{
+    extern __shared__ __align__(128) uint8_t lf_smem[];
+    constexpr int AX = 16 / (int)sizeof(pixel);           // samples per 16 bytes: TMA boxes start on them
+    const int tid = threadIdx.x;
+    const int bd = f.bd;
+    int TW[3], TH[3], BW[3], BH[3], px0[3], py0[3];
+    pixel *tile[3];
+    uint32_t total = 0;
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
+        TW[c] = LF_REGION >> hs; TH[c] = LF_REGION >> vs;
+        BW[c] = TW[c] + 2 * AX;  BH[c] = TH[c] + 8;
+        px0[c] = (blockIdx.x * LF_REGION) >> hs;
+        py0[c] = (blockIdx.y * LF_REGION) >> vs;
+        tile[c] = (pixel *)(lf_smem + total);
+        if (c < f.nplanes) total += (uint32_t)(BW[c] * BH[c] * sizeof(pixel));
+    }
+    uint64_t *mbar = (uint64_t *)(lf_smem + total);
+
+    // ---- fetch: one box per plane, origin (px0 - AX, py0 - 4); outside the picture reads as zero
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(lf_smem_u32(mbar)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(lf_smem_u32(mbar)), "r"(total) : "memory");
+        for (int c = 0; c < f.nplanes; c++)
+            asm volatile(
+                "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                ::"r"(lf_smem_u32(tile[c])), "l"(&maps.m[c]), "r"(px0[c] - AX), "r"(py0[c] - 4), "r"(lf_smem_u32(mbar)) : "memory");
+    }
+    __syncthreads();
+    lf_mbar_wait(mbar, 0);
+
+    if ((flags & 1) && f.vbs) {
+        // ---- 1. vertical edges: segment = 4 rows x (P3..Q3); lines are rows
+        for (int c = 0; c < f.nplanes; c++) {
+            const int nE = TW[c] / 8 + 1, nS = BH[c] / 4, pw = f.pw[c], ph = f.ph[c];
+            for (int it = tid; it < nE * nS; it += LF_THREADS) {
+                const int s = it / nE, i = it - s * nE;
+                const int ex = px0[c] + 8 * i, ys = py0[c] - 4 + 4 * s;
+                if (ex <= 0 || ex >= pw || ys < 0 || ys >= ph) continue;
+                const SegParam p = vseg_param(f, c, ex, ys);
+                if (!p.on) continue;
+                pixel *base = tile[c] + (4 * s) * BW[c] + 8 * i + AX - 4;
+                int l[4][8];
+#pragma unroll
+                for (int d = 0; d < 4; d++) { ld4(base + d * BW[c], l[d]); ld4(base + d * BW[c] + 4, l[d] + 4); }
+                if (c == 0) luma_segment(l, bd, p.beta, p.tc, p.no_p, p.no_q);
+                else chroma_segment(l, bd, p.tc, p.no_p, p.no_q);
+#pragma unroll
+                for (int d = 0; d < 4; d++) { st4(base + d * BW[c], l[d]); st4(base + d * BW[c] + 4, l[d] + 4); }
+            }
+        }
+        __syncthreads();
+        // ---- 2. horizontal edges: segment = (P3..Q3) rows x 4 columns; lines are columns
+        for (int c = 0; c < f.nplanes; c++) {
+            const int nE = TH[c] / 8 + 1, nS = (TW[c] + 8) / 4, pw = f.pw[c], ph = f.ph[c];
+            for (int it = tid; it < nE * nS; it += LF_THREADS) {
+                const int j = it / nS, s = it - j * nS;
+                const int ey = py0[c] + 8 * j, xs = px0[c] - 4 + 4 * s;
+                if (ey <= 0 || ey >= ph || xs < 0 || xs >= pw) continue;
+                const SegParam p = hseg_param(f, c, xs, ey);
+                if (!p.on) continue;
+                pixel *base = tile[c] + (8 * j) * BW[c] + 4 * s + AX - 4;      // row py0 - 4 is tile row 0
+                int l[4][8];
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    int v[4];
+                    ld4(base + k * BW[c], v);
+#pragma unroll
+                    for (int d = 0; d < 4; d++) l[d][k] = v[d];
+                }
+                if (c == 0) luma_segment(l, bd, p.beta, p.tc, p.no_p, p.no_q);
+                else chroma_segment(l, bd, p.tc, p.no_p, p.no_q);
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    int v[4];
+#pragma unroll
+                    for (int d = 0; d < 4; d++) v[d] = l[d][k];
+                    st4(base + k * BW[c], v);
+                }
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- 3. SAO (or plain copy) of the region into the DPB slot, four samples per thread step
+    const int maxv = (1 << bd) - 1;
+    const bool tqb = f.pcm_or_bypass && f.is_pcm;
+    for (int c = 0; c < f.nplanes; c++) {
+        const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
+        const int pw = f.pw[c], ph = f.ph[c], bw = BW[c];
+        const int ucols = TW[c] / 4;
+        uint8_t *dst = f.out.p[c];
+        const int dpitch = f.out.pitch[c];
+        const int cw = (1 << f.log2_ctb) >> hs, chh = (1 << f.log2_ctb) >> vs;     // CTB size in this plane
+        for (int it = tid; it < ucols * TH[c]; it += LF_THREADS) {
+            const int r = it / ucols, u = it - r * ucols;
+            const int x0 = px0[c] + 4 * u, y = py0[c] + r;
+            if (x0 >= pw || y >= ph) continue;
+            const pixel *srow = tile[c] + (r + 4) * bw + (AX - px0[c]);           // srow[x] = deblocked sample (x, y)
+            pixel *drow = (pixel *)(dst + (size_t)y * dpitch);
+            int o[4];
+            ld4(srow + x0, o);
+            const int ctbx = x0 / cw, ctby = y / chh;
+            const int rs = ctby * f.ctb_w + ctbx;
+            const int type = ((flags & 2) && f.sao) ? f.sao[rs].type_idx[c] : OHCU_SAO_NOT_APPLIED;
+            if (type == OHCU_SAO_BAND || type == OHCU_SAO_EDGE) {
+                const ohcu_sao sp = f.sao[rs];
+                int off[5];
+#pragma unroll
+                for (int i = 0; i < 5; i++) off[i] = sp.offset_val[c][i];
+                const int cx0 = ctbx * cw, cy0 = ctby * chh;          // CTB origin in the plane
+                const int w = min(cw, pw - cx0), h = min(chh, ph - cy0);
+                const int ly = y - cy0;
+                // restore_tqb_pixels (:229-260): the min-PU range is taken from the LUMA origin of
+                // the CTB plus the PLANE's width/height, as in the reference
+                const int lx_ctb = ctbx << f.log2_ctb, ly_ctb = ctby << f.log2_ctb;
+                const int pu_xmax = (lx_ctb + w) >> f.log2_min_pu, pu_ymax = (ly_ctb + h) >> f.log2_min_pu;
+                if (type == OHCU_SAO_BAND) {                           // sao_band_filter_0, template :310-335
+                    const int pos = sp.band_position[c];
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const int x = x0 + i, v = o[i];
+                        const int k = ((v >> (bd - 5)) - pos) & 31;
+                        int q = clip3i(v + (k < 4 ? off[k + 1] : 0), 0, maxv);
+                        if (tqb) {
+                            const int pux = (x << hs) >> f.log2_min_pu, puy = (y << vs) >> f.log2_min_pu;
+                            if (pux < pu_xmax && puy < pu_ymax && f.is_pcm[puy * f.min_pu_w + pux]) q = v;
+                        }
+                        o[i] = q;
+                    }
+                } else {
+                    // ---- edge offset: sao_edge_filter (:342-378) then sao_edge_restore_{0,1} (:380-529)
+                    const int eo = sp.eo_class[c];
+                    const int dxa = (eo == 0 || eo == 2) ? -1 : (eo == 3 ? 1 : 0);
+                    const int dya = eo == 0 ? 0 : -1;
+                    const int fl = f.sao_ctb_flags[rs];
+                    const bool b0 = ctbx == 0, b1 = ctby == 0, b2 = ctbx == f.ctb_w - 1, b3 = ctby == f.ctb_h - 1;
+                    const bool notv = eo != OHCU_SAO_EO_VERT, noth = eo != OHCU_SAO_EO_HORIZ;
+                    const int wr = w - ((notv && b2) ? 1 : 0);             // width / height after the border
+                    const int hr = h - ((noth && b3) ? 1 : 0);             // columns / rows were peeled off
+                    const int init_x = (notv && b0) ? 1 : 0;
+                    const bool restore = fl & SAOF_RESTORE;
+                    const bool ve0 = fl & SAOF_VERT0, ve1 = fl & SAOF_VERT1;
+                    const bool he0 = fl & SAOF_HORIZ0, he1 = fl & SAOF_HORIZ1;
+                    const bool d0 = fl & SAOF_DIAG0, d1 = fl & SAOF_DIAG1, d2 = fl & SAOF_DIAG2, d3 = fl & SAOF_DIAG3;
+                    const int keep_ul = !d0 && eo == 2 && !b0 && !b1, keep_ur = !d1 && eo == 3 && !b1 && !b2;
+                    const int keep_lr = !d2 && eo == 2 && !b2 && !b3, keep_ll = !d3 && eo == 3 && !b0 && !b3;
+                    const int ya = y + dya, yb = y - dya;
+                    const bool ya_ok = ya >= 0 && ya < ph, yb_ok = yb >= 0 && yb < ph;
+                    const pixel *rowa = srow + dya * bw, *rowb = srow - dya * bw;
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const int x = x0 + i, lx = x - cx0, v = o[i];
+                        const int xa = x + dxa, xb = x - dxa;
+                        // out-of-picture neighbours only occur where the border rules below override the result
+                        const int a = (ya_ok && xa >= 0 && xa < pw) ? rowa[xa] : v;
+                        const int b = (yb_ok && xb >= 0 && xb < pw) ? rowb[xb] : v;
+                        const int sgn = ((v > a) - (v < a)) + ((v > b) - (v < b));   // -2..2
+                        // edge_idx[] = {1, 2, 0, 3, 4}
+                        const int cat = sgn == 0 ? 0 : (sgn == -2 ? 1 : (sgn == -1 ? 2 : (sgn == 1 ? 3 : 4)));
+                        int q = clip3i(v + off[cat], 0, maxv);
+                        const int keep = clip3i(v + off[0], 0, maxv);
+                        // picture borders (restore_0 part)
+                        if (notv && ((b0 && lx == 0) || (b2 && lx == w - 1))) q = keep;
+                        if (noth && ((b1 && ly == 0) || (b3 && ly == h - 1)) && lx >= init_x && lx < wr) q = keep;
+                        if (restore) {                                     // slice / tile boundaries (restore_1)
+                            if (ve0 && notv && lx == 0 && ly >= keep_ul && ly < hr - keep_ll) q = v;
+                            if (ve1 && notv && lx == wr - 1 && ly >= keep_ur && ly < hr - keep_lr) q = v;
+                            if (he0 && noth && ly == 0 && lx >= init_x + keep_ul && lx < wr - keep_ur) q = v;
+                            if (he1 && noth && ly == hr - 1 && lx >= init_x + keep_ll && lx < wr - keep_lr) q = v;
+                            if (d0 && eo == 2 && lx == 0 && ly == 0) q = v;
+                            if (d1 && eo == 3 && lx == wr - 1 && ly == 0) q = v;
+                            if (d2 && eo == 2 && lx == wr - 1 && ly == hr - 1) q = v;
+                            if (d3 && eo == 3 && lx == 0 && ly == hr - 1) q = v;
+                        }
+                        if (tqb) {
+                            const int pux = (x << hs) >> f.log2_min_pu, puy = (y << vs) >> f.log2_min_pu;
+                            if (pux < pu_xmax && puy < pu_ymax && f.is_pcm[puy * f.min_pu_w + pux]) q = v;
+                        }
+                        o[i] = q;
+                    }
+                }
+            }
+            st4(drow + x0, o);
+        }
+    }
+}
+
+size_t loopfilter_smem_bytes(const FrameDev &f)
+{
+    const int P = f.bd > 8 ? 2 : 1, AX = 16 / P;
+    size_t total = 0;
+    for (int c = 0; c < f.nplanes; c++) {
+        const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
+        total += (size_t)((LF_REGION >> hs) + 2 * AX) * ((LF_REGION >> vs) + 8) * P;
+    }
+    return total + 16;
+}
+
+// box of plane c that loopfilter_kernel fetches (api.cu encodes one tensor map per job and plane)
+void loopfilter_box(const FrameDev &f, int c, int *bw, int *bh)
+{
+    const int P = f.bd > 8 ? 2 : 1, AX = 16 / P;
+    const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
+    *bw = (LF_REGION >> hs) + 2 * AX;
+    *bh = (LF_REGION >> vs) + 8;
+}
+
+int launch_loopfilter(const FrameDev &f, const LfMaps &maps, int flags, cudaStream_t st)
+{
+    if (!(flags & 3)) return 0;
+    const size_t smem = loopfilter_smem_bytes(f);
+    static bool attr_set = false;
+    if (!attr_set) {
+        if (cudaFuncSetAttribute(loopfilter_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(loopfilter_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024) != cudaSuccess)
+            return -1;
+        attr_set = true;
+    }
+    dim3 grid((f.width + LF_REGION - 1) / LF_REGION, (f.height + LF_REGION - 1) / LF_REGION);
+    if (f.bd > 8) loopfilter_kernel<uint16_t><<<grid, LF_THREADS, smem, st>>>(f, maps, flags);
+    else          loopfilter_kernel<uint8_t><<<grid, LF_THREADS, smem, st>>>(f, maps, flags);
+    return 1;
+}
+
+}  // namespace ohcu

@@ -88,8 +88,9 @@ enum {
 int launch_recon(const FrameDev &f, int flags, cudaStream_t st);   // flags: 1 MC, 2 residual
 int upload_mc_taps();
 int upload_dct_table();
-int launch_deblock(const FrameDev &f, cudaStream_t st);
-int launch_sao(const FrameDev &f, cudaStream_t st);
+struct LfMaps { CUtensorMap m[3]; };        // the job's reconstructed picture, one box per plane
+int launch_loopfilter(const FrameDev &f, const LfMaps &maps, int flags, cudaStream_t st);   // flags: 1 deblock, 2 SAO
+void loopfilter_box(const FrameDev &f, int c, int *bw, int *bh);
 int launch_pad_picture(const FrameDev &f, const PlaneSet &pic, cudaStream_t st);   // fill the replicated halo
 int launch_copy_picture(const FrameDev &f, const PlaneSet &dst, const PlaneSet &src, cudaStream_t st);
 int launch_l2_flush(void *buf, size_t bytes, cudaStream_t st);
