@@ -221,9 +221,164 @@ __device__ __forceinline__ void st4(uint8_t *p, const int *v)
     *(uint32_t *)p = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24);
 }
 
+// eight consecutive samples, aligned to 8 * sizeof(pixel)
+__device__ __forceinline__ void ld8(const uint16_t *p, int *v)
+{
+    const uint4 w = *(const uint4 *)p;
+    v[0] = w.x & 0xffff; v[1] = w.x >> 16; v[2] = w.y & 0xffff; v[3] = w.y >> 16;
+    v[4] = w.z & 0xffff; v[5] = w.z >> 16; v[6] = w.w & 0xffff; v[7] = w.w >> 16;
+}
+__device__ __forceinline__ void ld8(const uint8_t *p, int *v)
+{
+    const uint2 w = *(const uint2 *)p;
+    v[0] = w.x & 0xff; v[1] = (w.x >> 8) & 0xff; v[2] = (w.x >> 16) & 0xff; v[3] = w.x >> 24;
+    v[4] = w.y & 0xff; v[5] = (w.y >> 8) & 0xff; v[6] = (w.y >> 16) & 0xff; v[7] = w.y >> 24;
+}
+__device__ __forceinline__ void st8(uint16_t *p, const int *v)
+{
+    *(uint4 *)p = make_uint4((uint32_t)v[0] | ((uint32_t)v[1] << 16), (uint32_t)v[2] | ((uint32_t)v[3] << 16),
+                             (uint32_t)v[4] | ((uint32_t)v[5] << 16), (uint32_t)v[6] | ((uint32_t)v[7] << 16));
+}
+__device__ __forceinline__ void st8(uint8_t *p, const int *v)
+{
+    *(uint2 *)p = make_uint2((uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24),
+                             (uint32_t)v[4] | ((uint32_t)v[5] << 8) | ((uint32_t)v[6] << 16) | ((uint32_t)v[7] << 24));
+}
+
+// ---------------------------------------------------------------- SAO of eight samples
+// Offsets of a CTB packed as signed bytes and picked with one PRMT (selector nibble bit 3
+// replicates the sign of the chosen byte, so bytes 1..3 of the result sign-extend byte 0):
+//   edge  byte[2 + sign(v-a) + sign(v-b)] = offset_val[edge_idx[..]],  edge_idx = {1,2,0,3,4}
+//   band  byte[k] = offset_val[k + 1] for k < 4, byte 4 = 0
+__device__ __forceinline__ int packed_offset(uint32_t lo, uint32_t hi, int idx)
+{
+    // prmt.b32 directly: __byte_perm() drops selector bit 3
+    int r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(lo), "r"(hi), "r"((uint32_t)idx * 0x1111u + 0x8880u));
+    return r;
+}
+
+// CTB away from every border rule: neighbours exist, nothing is restored.
+// rowa / rowb point at sample x0 of the rows holding neighbour a / b; DXA = column step to a.
+template <typename pixel, int DXA>
+__device__ __forceinline__ void sao_edge_fast(const pixel *rowa, const pixel *rowb, const int (&v)[8], uint32_t lo,
+                                              uint32_t hi, int maxv, int (&o)[8])
+{
+    int A[10], B[10];                                  // A[k] = rowa[k - 1]
+    ld8(rowa, A + 1);
+    ld8(rowb, B + 1);
+    if (DXA < 0) { A[0] = rowa[-1]; B[9] = rowb[8]; }
+    if (DXA > 0) { A[9] = rowa[8]; B[0] = rowb[-1]; }
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int a = A[i + 1 + DXA], b = B[i + 1 - DXA];
+        const int sgn = clip3i(v[i] - a, -1, 1) + clip3i(v[i] - b, -1, 1);
+        o[i] = clip3i(v[i] + packed_offset(lo, hi, sgn + 2), 0, maxv);
+    }
+}
+
+// per (plane, CTB of the region): what the SAO step needs, built once per CTA
+struct SaoRec {
+    uint32_t lo, hi;          // packed offsets (fast paths)
+    uint32_t misc;            // type | eo << 2 | fast << 4 | band_position << 8
+    uint32_t pad;
+};
+
+// Any CTB: picture borders, slice / tile restore flags, pcm / bypass restore, wide offsets.
+// Follows sao_edge_filter + sao_edge_restore_{0,1} (template :342-529), sao_band_filter_0
+// (:310-335) and restore_tqb_pixels (hevc_filter.c:229-260) sample by sample.
+// srow = tile row of plane row y, indexed by plane column; bw = tile pitch in samples.
+template <typename pixel>
+__device__ __noinline__ void sao_slow(const FrameDev &f, int c, int x0, int y, const pixel *srow, int bw, pixel *drow)
+{
+    const int bd = f.bd, maxv = (1 << bd) - 1;
+    const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
+    const int pw = f.pw[c], ph = f.ph[c];
+    const int lcw = f.log2_ctb - hs, lch = f.log2_ctb - vs;
+    const int cw = 1 << lcw, chh = 1 << lch;
+    const int ctbx = x0 >> lcw, ctby = y >> lch;
+    const int rs = ctby * f.ctb_w + ctbx;
+    const ohcu_sao sp = f.sao[rs];
+    const int type = sp.type_idx[c];
+    int off[5];
+#pragma unroll
+    for (int i = 0; i < 5; i++) off[i] = sp.offset_val[c][i];
+    const int cx0 = ctbx * cw, cy0 = ctby * chh;          // CTB origin in the plane
+    const int w = min(cw, pw - cx0), h = min(chh, ph - cy0);
+    const int ly = y - cy0;
+    const bool tqb = f.pcm_or_bypass && f.is_pcm;
+    // the min-PU range is taken from the LUMA origin of the CTB plus the PLANE's width/height, as in the reference
+    const int lx_ctb = ctbx << f.log2_ctb, ly_ctb = ctby << f.log2_ctb;
+    const int pu_xmax = (lx_ctb + w) >> f.log2_min_pu, pu_ymax = (ly_ctb + h) >> f.log2_min_pu;
+    const int eo = sp.eo_class[c];
+    const int dxa = (eo == 0 || eo == 2) ? -1 : (eo == 3 ? 1 : 0);
+    const int dya = eo == 0 ? 0 : -1;
+    const int fl = f.sao_ctb_flags[rs];
+    const bool b0 = ctbx == 0, b1 = ctby == 0, b2 = ctbx == f.ctb_w - 1, b3 = ctby == f.ctb_h - 1;
+    const bool notv = eo != OHCU_SAO_EO_VERT, noth = eo != OHCU_SAO_EO_HORIZ;
+    const int wr = w - ((notv && b2) ? 1 : 0);             // width / height after the border
+    const int hr = h - ((noth && b3) ? 1 : 0);             // columns / rows were peeled off
+    const int init_x = (notv && b0) ? 1 : 0;
+    const bool restore = fl & SAOF_RESTORE;
+    const bool ve0 = fl & SAOF_VERT0, ve1 = fl & SAOF_VERT1;
+    const bool he0 = fl & SAOF_HORIZ0, he1 = fl & SAOF_HORIZ1;
+    const bool d0 = fl & SAOF_DIAG0, d1 = fl & SAOF_DIAG1, d2 = fl & SAOF_DIAG2, d3 = fl & SAOF_DIAG3;
+    const int keep_ul = !d0 && eo == 2 && !b0 && !b1, keep_ur = !d1 && eo == 3 && !b1 && !b2;
+    const int keep_lr = !d2 && eo == 2 && !b2 && !b3, keep_ll = !d3 && eo == 3 && !b0 && !b3;
+    const int ya = y + dya, yb = y - dya;
+    const bool ya_ok = ya >= 0 && ya < ph, yb_ok = yb >= 0 && yb < ph;
+    const pixel *rowa = srow + dya * bw, *rowb = srow - dya * bw;
+#pragma unroll 1
+    for (int i = 0; i < 8; i++) {
+        const int x = x0 + i, lx = x - cx0, v = srow[x];
+        int q;
+        if (type == OHCU_SAO_BAND) {
+            const int k = ((v >> (bd - 5)) - sp.band_position[c]) & 31;
+            q = clip3i(v + (k < 4 ? off[k + 1] : 0), 0, maxv);
+        } else {
+            const int xa = x + dxa, xb = x - dxa;
+            // out-of-picture neighbours only occur where the border rules below override the result
+            const int a = (ya_ok && xa >= 0 && xa < pw) ? rowa[xa] : v;
+            const int b = (yb_ok && xb >= 0 && xb < pw) ? rowb[xb] : v;
+            const int sgn = ((v > a) - (v < a)) + ((v > b) - (v < b));   // -2..2
+            // edge_idx[] = {1, 2, 0, 3, 4}
+            const int cat = sgn == 0 ? 0 : (sgn == -2 ? 1 : (sgn == -1 ? 2 : (sgn == 1 ? 3 : 4)));
+            q = clip3i(v + off[cat], 0, maxv);
+            const int keep = clip3i(v + off[0], 0, maxv);
+            // picture borders (restore_0 part)
+            if (notv && ((b0 && lx == 0) || (b2 && lx == w - 1))) q = keep;
+            if (noth && ((b1 && ly == 0) || (b3 && ly == h - 1)) && lx >= init_x && lx < wr) q = keep;
+            if (restore) {                                     // slice / tile boundaries (restore_1)
+                if (ve0 && notv && lx == 0 && ly >= keep_ul && ly < hr - keep_ll) q = v;
+                if (ve1 && notv && lx == wr - 1 && ly >= keep_ur && ly < hr - keep_lr) q = v;
+                if (he0 && noth && ly == 0 && lx >= init_x + keep_ul && lx < wr - keep_ur) q = v;
+                if (he1 && noth && ly == hr - 1 && lx >= init_x + keep_ll && lx < wr - keep_lr) q = v;
+                if (d0 && eo == 2 && lx == 0 && ly == 0) q = v;
+                if (d1 && eo == 3 && lx == wr - 1 && ly == 0) q = v;
+                if (d2 && eo == 2 && lx == wr - 1 && ly == hr - 1) q = v;
+                if (d3 && eo == 3 && lx == 0 && ly == hr - 1) q = v;
+            }
+        }
+        if (tqb) {
+            const int pux = (x << hs) >> f.log2_min_pu, puy = (y << vs) >> f.log2_min_pu;
+            if (pux < pu_xmax && puy < pu_ymax && f.is_pcm[puy * f.min_pu_w + pux]) q = v;
+        }
+        drow[x] = (pixel)q;
+    }
+}
+
 // ---------------------------------------------------------------- the kernel
-// flags: bit 0 deblock, bit 1 SAO.  Source f.work (the job's reconstructed picture, reached
-// through `maps`), destination f.out (the DPB slot).
+// Edge segments that actually filter, found while the tile is in flight.
+//   w0  tile offset of the segment's first sample (P3 of line 0) | plane << 16 | no_p << 18 | no_q << 19
+//   w1  beta | tc << 16   (table values, scaled to the bit depth by the filter)
+constexpr int LF_MAX_SEGS = 512;               // per direction: 3 x 162 for 4:4:4
+
+struct LfGeom {
+    int TW, TH, BW, BH, px0, py0, lw;          // lw = log2(TW)
+};
+
+// flags: bit 0 deblock, bit 1 SAO.  Source: the job's reconstructed picture through `maps`
+// (= f.work); destination f.out (the DPB slot).
 template <typename pixel>
 __global__ void __launch_bounds__(LF_THREADS) loopfilter_kernel(const __grid_constant__ FrameDev f,
                                                                  const __grid_constant__ LfMaps maps, int flags)
@@ -232,189 +387,220 @@ __global__ void __launch_bounds__(LF_THREADS) loopfilter_kernel(const __grid_con
     constexpr int AX = 16 / (int)sizeof(pixel);           // samples per 16 bytes: TMA boxes start on them
     const int tid = threadIdx.x;
     const int bd = f.bd;
-    int TW[3], TH[3], BW[3], BH[3], px0[3], py0[3];
-    pixel *tile[3];
-    uint32_t total = 0;
+    const int np = f.nplanes;
+    LfGeom g[3];
+    uint32_t toff[3], total = 0;
 #pragma unroll
     for (int c = 0; c < 3; c++) {
         const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
-        TW[c] = LF_REGION >> hs; TH[c] = LF_REGION >> vs;
-        BW[c] = TW[c] + 2 * AX;  BH[c] = TH[c] + 8;
-        px0[c] = (blockIdx.x * LF_REGION) >> hs;
-        py0[c] = (blockIdx.y * LF_REGION) >> vs;
-        tile[c] = (pixel *)(lf_smem + total);
-        if (c < f.nplanes) total += (uint32_t)(BW[c] * BH[c] * sizeof(pixel));
+        g[c].lw = 6 - hs;
+        g[c].TW = LF_REGION >> hs; g[c].TH = LF_REGION >> vs;
+        g[c].BW = g[c].TW + 2 * AX; g[c].BH = g[c].TH + 8;
+        g[c].px0 = (blockIdx.x * LF_REGION) >> hs;
+        g[c].py0 = (blockIdx.y * LF_REGION) >> vs;
+        toff[c] = total;
+        if (c < np) total += (uint32_t)(g[c].BW * g[c].BH * sizeof(pixel));
     }
     uint64_t *mbar = (uint64_t *)(lf_smem + total);
+    int *cnt = (int *)(mbar + 1);                              // [dir][luma, chroma]
+    SaoRec *srec = (SaoRec *)(lf_smem + total + 32);           // [plane][CTB of the region], <= 3 x 16
+    uint2 *seg = (uint2 *)(srec + 48);                         // [dir][LF_MAX_SEGS]
+#define TILE(c) ((pixel *)(lf_smem + toff[c]))
 
     // ---- fetch: one box per plane, origin (px0 - AX, py0 - 4); outside the picture reads as zero
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(lf_smem_u32(mbar)));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(lf_smem_u32(mbar)), "r"(total) : "memory");
-        for (int c = 0; c < f.nplanes; c++)
-            asm volatile(
-                "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                ::"r"(lf_smem_u32(tile[c])), "l"(&maps.m[c]), "r"(px0[c] - AX), "r"(py0[c] - 4), "r"(lf_smem_u32(mbar)) : "memory");
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+            if (c < np)
+                asm volatile(
+                    "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                    ::"r"(lf_smem_u32(TILE(c))), "l"(&maps.m[c]), "r"(g[c].px0 - AX), "r"(g[c].py0 - 4), "r"(lf_smem_u32(mbar)) : "memory");
+    }
+    if (tid < 4) cnt[tid] = 0;
+    __syncthreads();
+
+    // ---- while the tile is in flight: side information -> segment lists and SAO records
+    const bool do_db = (flags & 1) && f.vbs;
+    if (do_db) {
+        // item space: [V: plane 0, 1, 2][H: plane 0, 1, 2]
+        int nV[3], nH[3], nvt = 0, nht = 0;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            nV[c] = c < np ? (g[c].TW / 8 + 1) * (g[c].BH / 4) : 0;
+            nH[c] = c < np ? (g[c].TH / 8 + 1) * ((g[c].TW + 8) / 4) : 0;
+            nvt += nV[c]; nht += nH[c];
+        }
+        for (int it = tid; it < nvt + nht; it += LF_THREADS) {
+            const int dir = it >= nvt;
+            int k = dir ? it - nvt : it, c = 0;
+#pragma unroll
+            for (int cc = 0; cc < 2; cc++) {
+                const int n = dir ? nH[cc] : nV[cc];
+                if (c == cc && k >= n) { k -= n; c = cc + 1; }
+            }
+            const LfGeom G = c == 0 ? g[0] : (c == 1 ? g[1] : g[2]);
+            SegParam p;
+            int base;
+            if (!dir) {
+                const int nE = G.TW / 8 + 1;
+                const int s = k / nE, i = k - s * nE;
+                const int ex = G.px0 + 8 * i, ys = G.py0 - 4 + 4 * s;
+                if (ex <= 0 || ex >= f.pw[c] || ys < 0 || ys >= f.ph[c]) continue;
+                p = vseg_param(f, c, ex, ys);
+                base = (4 * s) * G.BW + 8 * i + AX - 4;
+            } else {
+                const int nS = (G.TW + 8) / 4;
+                const int j = k / nS, s = k - j * nS;
+                const int ey = G.py0 + 8 * j, xs = G.px0 - 4 + 4 * s;
+                if (ey <= 0 || ey >= f.ph[c] || xs < 0 || xs >= f.pw[c]) continue;
+                p = hseg_param(f, c, xs, ey);
+                base = (8 * j) * G.BW + 4 * s + AX - 4;             // row py0 - 4 is tile row 0
+            }
+            if (!p.on || (c && p.tc == 0)) continue;
+            const int slot = atomicAdd(&cnt[dir * 2 + (c ? 1 : 0)], 1);
+            // luma segments from the front, chroma from the back: warps stay on one filter
+            seg[dir * LF_MAX_SEGS + (c ? LF_MAX_SEGS - 1 - slot : slot)] =
+                make_uint2((uint32_t)base | (uint32_t)c << 16 | (p.no_p ? 1u << 18 : 0u) | (p.no_q ? 1u << 19 : 0u),
+                           (uint32_t)p.beta | (uint32_t)p.tc << 16);
+        }
+    }
+    const int lctb = min(f.log2_ctb, 6);                       // CTBs of the region: nreg x nreg
+    const int nreg = LF_REGION >> lctb;
+    if (tid < np * nreg * nreg) {
+        const int c = tid / (nreg * nreg), k = tid - c * nreg * nreg;
+        const int ctbx = ((blockIdx.x * LF_REGION) >> f.log2_ctb) + (k % nreg);
+        const int ctby = ((blockIdx.y * LF_REGION) >> f.log2_ctb) + (k / nreg);
+        SaoRec r = {0, 0, OHCU_SAO_NOT_APPLIED, 0};
+        if ((flags & 2) && f.sao && ctbx < f.ctb_w && ctby < f.ctb_h) {
+            const int rs = ctby * f.ctb_w + ctbx;
+            const ohcu_sao sp = f.sao[rs];
+            const int type = sp.type_idx[c];
+            if (type == OHCU_SAO_BAND || type == OHCU_SAO_EDGE) {
+                int off[5];
+                bool fast = !(f.pcm_or_bypass && f.is_pcm);
+#pragma unroll
+                for (int i = 0; i < 5; i++) {
+                    off[i] = sp.offset_val[c][i];
+                    if (off[i] < -128 || off[i] > 127) fast = false;
+                }
+                const int eo = sp.eo_class[c];
+                if (type == OHCU_SAO_EDGE) {
+                    const bool notv = eo != OHCU_SAO_EO_VERT, noth = eo != OHCU_SAO_EO_HORIZ;
+                    const bool bx = ctbx == 0 || ctbx == f.ctb_w - 1, by = ctby == 0 || ctby == f.ctb_h - 1;
+                    const int fl = f.sao_ctb_flags[rs];
+                    if ((notv && bx) || (noth && by) || ((fl & SAOF_RESTORE) && (fl & ~SAOF_RESTORE))) fast = false;
+                    r.lo = (off[1] & 0xff) | (off[2] & 0xff) << 8 | (off[0] & 0xff) << 16 | (uint32_t)(off[3] & 0xff) << 24;
+                    r.hi = off[4] & 0xff;
+                } else {
+                    r.lo = (off[1] & 0xff) | (off[2] & 0xff) << 8 | (off[3] & 0xff) << 16 | (uint32_t)(off[4] & 0xff) << 24;
+                    r.hi = 0;
+                }
+                r.misc = (uint32_t)type | (uint32_t)eo << 2 | (fast ? 1u << 4 : 0u) | (uint32_t)sp.band_position[c] << 8;
+            }
+        }
+        srec[tid] = r;
     }
     __syncthreads();
     lf_mbar_wait(mbar, 0);
 
-    if ((flags & 1) && f.vbs) {
+    if (do_db) {
         // ---- 1. vertical edges: segment = 4 rows x (P3..Q3); lines are rows
-        for (int c = 0; c < f.nplanes; c++) {
-            const int nE = TW[c] / 8 + 1, nS = BH[c] / 4, pw = f.pw[c], ph = f.ph[c];
-            for (int it = tid; it < nE * nS; it += LF_THREADS) {
-                const int s = it / nE, i = it - s * nE;
-                const int ex = px0[c] + 8 * i, ys = py0[c] - 4 + 4 * s;
-                if (ex <= 0 || ex >= pw || ys < 0 || ys >= ph) continue;
-                const SegParam p = vseg_param(f, c, ex, ys);
-                if (!p.on) continue;
-                pixel *base = tile[c] + (4 * s) * BW[c] + 8 * i + AX - 4;
+        {
+            const int nl = cnt[0], n = nl + cnt[1];
+            for (int k = tid; k < n; k += LF_THREADS) {
+                const uint2 r = seg[k < nl ? k : LF_MAX_SEGS - 1 - (k - nl)];
+                const int c = (r.x >> 16) & 3;
+                const int bw = c == 0 ? g[0].BW : g[1].BW;
+                pixel *base = (pixel *)(lf_smem + (c == 0 ? toff[0] : (c == 1 ? toff[1] : toff[2]))) + (r.x & 0xffff);
                 int l[4][8];
 #pragma unroll
-                for (int d = 0; d < 4; d++) { ld4(base + d * BW[c], l[d]); ld4(base + d * BW[c] + 4, l[d] + 4); }
-                if (c == 0) luma_segment(l, bd, p.beta, p.tc, p.no_p, p.no_q);
-                else chroma_segment(l, bd, p.tc, p.no_p, p.no_q);
+                for (int d = 0; d < 4; d++) { ld4(base + d * bw, l[d]); ld4(base + d * bw + 4, l[d] + 4); }
+                if (c == 0) luma_segment(l, bd, r.y & 0xffff, r.y >> 16, (r.x >> 18) & 1, (r.x >> 19) & 1);
+                else chroma_segment(l, bd, r.y >> 16, (r.x >> 18) & 1, (r.x >> 19) & 1);
 #pragma unroll
-                for (int d = 0; d < 4; d++) { st4(base + d * BW[c], l[d]); st4(base + d * BW[c] + 4, l[d] + 4); }
+                for (int d = 0; d < 4; d++) { st4(base + d * bw, l[d]); st4(base + d * bw + 4, l[d] + 4); }
             }
         }
         __syncthreads();
         // ---- 2. horizontal edges: segment = (P3..Q3) rows x 4 columns; lines are columns
-        for (int c = 0; c < f.nplanes; c++) {
-            const int nE = TH[c] / 8 + 1, nS = (TW[c] + 8) / 4, pw = f.pw[c], ph = f.ph[c];
-            for (int it = tid; it < nE * nS; it += LF_THREADS) {
-                const int j = it / nS, s = it - j * nS;
-                const int ey = py0[c] + 8 * j, xs = px0[c] - 4 + 4 * s;
-                if (ey <= 0 || ey >= ph || xs < 0 || xs >= pw) continue;
-                const SegParam p = hseg_param(f, c, xs, ey);
-                if (!p.on) continue;
-                pixel *base = tile[c] + (8 * j) * BW[c] + 4 * s + AX - 4;      // row py0 - 4 is tile row 0
+        {
+            const int nl = cnt[2], n = nl + cnt[3];
+            for (int k = tid; k < n; k += LF_THREADS) {
+                const uint2 r = seg[LF_MAX_SEGS + (k < nl ? k : LF_MAX_SEGS - 1 - (k - nl))];
+                const int c = (r.x >> 16) & 3;
+                const int bw = c == 0 ? g[0].BW : g[1].BW;
+                pixel *base = (pixel *)(lf_smem + (c == 0 ? toff[0] : (c == 1 ? toff[1] : toff[2]))) + (r.x & 0xffff);
                 int l[4][8];
 #pragma unroll
-                for (int k = 0; k < 8; k++) {
+                for (int q = 0; q < 8; q++) {
                     int v[4];
-                    ld4(base + k * BW[c], v);
+                    ld4(base + q * bw, v);
 #pragma unroll
-                    for (int d = 0; d < 4; d++) l[d][k] = v[d];
+                    for (int d = 0; d < 4; d++) l[d][q] = v[d];
                 }
-                if (c == 0) luma_segment(l, bd, p.beta, p.tc, p.no_p, p.no_q);
-                else chroma_segment(l, bd, p.tc, p.no_p, p.no_q);
+                if (c == 0) luma_segment(l, bd, r.y & 0xffff, r.y >> 16, (r.x >> 18) & 1, (r.x >> 19) & 1);
+                else chroma_segment(l, bd, r.y >> 16, (r.x >> 18) & 1, (r.x >> 19) & 1);
 #pragma unroll
-                for (int k = 0; k < 8; k++) {
+                for (int q = 0; q < 8; q++) {
                     int v[4];
 #pragma unroll
-                    for (int d = 0; d < 4; d++) v[d] = l[d][k];
-                    st4(base + k * BW[c], v);
+                    for (int d = 0; d < 4; d++) v[d] = l[d][q];
+                    st4(base + q * bw, v);
                 }
             }
         }
+        __syncthreads();
     }
-    __syncthreads();
 
-    // ---- 3. SAO (or plain copy) of the region into the DPB slot, four samples per thread step
+    // ---- 3. SAO (or plain copy) of the region into the DPB slot, eight samples per thread step
     const int maxv = (1 << bd) - 1;
-    const bool tqb = f.pcm_or_bypass && f.is_pcm;
-    for (int c = 0; c < f.nplanes; c++) {
+    int nU[3], nut = 0;
+#pragma unroll
+    for (int c = 0; c < 3; c++) { nU[c] = c < np ? (g[c].TW >> 3) * g[c].TH : 0; nut += nU[c]; }
+    for (int it = tid; it < nut; it += LF_THREADS) {
+        int k = it, c = 0;
+        if (k >= nU[0]) { k -= nU[0]; c = 1; if (k >= nU[1]) { k -= nU[1]; c = 2; } }
+        const LfGeom G = c == 0 ? g[0] : (c == 1 ? g[1] : g[2]);
+        const int r = k >> (G.lw - 3), u = k & ((1 << (G.lw - 3)) - 1);
+        const int x0 = G.px0 + 8 * u, y = G.py0 + r;
+        if (x0 >= f.pw[c] || y >= f.ph[c]) continue;
+        const int bw = G.BW;
+        const pixel *trow = (const pixel *)(lf_smem + (c == 0 ? toff[0] : (c == 1 ? toff[1] : toff[2]))) + (r + 4) * bw + AX;
+        const pixel *sp8 = trow + 8 * u;                               // deblocked samples (x0.., y)
+        pixel *drow = (pixel *)(f.out.p[c] + (size_t)y * f.out.pitch[c]);
+        // CTB of the unit inside the region
         const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
-        const int pw = f.pw[c], ph = f.ph[c], bw = BW[c];
-        const int ucols = TW[c] / 4;
-        uint8_t *dst = f.out.p[c];
-        const int dpitch = f.out.pitch[c];
-        const int cw = (1 << f.log2_ctb) >> hs, chh = (1 << f.log2_ctb) >> vs;     // CTB size in this plane
-        for (int it = tid; it < ucols * TH[c]; it += LF_THREADS) {
-            const int r = it / ucols, u = it - r * ucols;
-            const int x0 = px0[c] + 4 * u, y = py0[c] + r;
-            if (x0 >= pw || y >= ph) continue;
-            const pixel *srow = tile[c] + (r + 4) * bw + (AX - px0[c]);           // srow[x] = deblocked sample (x, y)
-            pixel *drow = (pixel *)(dst + (size_t)y * dpitch);
-            int o[4];
-            ld4(srow + x0, o);
-            const int ctbx = x0 / cw, ctby = y / chh;
-            const int rs = ctby * f.ctb_w + ctbx;
-            const int type = ((flags & 2) && f.sao) ? f.sao[rs].type_idx[c] : OHCU_SAO_NOT_APPLIED;
-            if (type == OHCU_SAO_BAND || type == OHCU_SAO_EDGE) {
-                const ohcu_sao sp = f.sao[rs];
-                int off[5];
+        const int ci = (r >> (lctb - vs)) * nreg + ((8 * u) >> (lctb - hs));
+        const SaoRec rec = srec[c * nreg * nreg + ci];
+        const int type = rec.misc & 3;
+        int v[8], o[8];
+        if (type == OHCU_SAO_NOT_APPLIED) {
+            ld8(sp8, o);
+        } else if (!(rec.misc & 16)) {
+            sao_slow<pixel>(f, c, x0, y, trow - G.px0, bw, drow);
+            continue;
+        } else if (type == OHCU_SAO_BAND) {                            // sao_band_filter_0, template :310-335
+            ld8(sp8, v);
+            const int pos = (rec.misc >> 8) & 31, sh = bd - 5;
 #pragma unroll
-                for (int i = 0; i < 5; i++) off[i] = sp.offset_val[c][i];
-                const int cx0 = ctbx * cw, cy0 = ctby * chh;          // CTB origin in the plane
-                const int w = min(cw, pw - cx0), h = min(chh, ph - cy0);
-                const int ly = y - cy0;
-                // restore_tqb_pixels (:229-260): the min-PU range is taken from the LUMA origin of
-                // the CTB plus the PLANE's width/height, as in the reference
-                const int lx_ctb = ctbx << f.log2_ctb, ly_ctb = ctby << f.log2_ctb;
-                const int pu_xmax = (lx_ctb + w) >> f.log2_min_pu, pu_ymax = (ly_ctb + h) >> f.log2_min_pu;
-                if (type == OHCU_SAO_BAND) {                           // sao_band_filter_0, template :310-335
-                    const int pos = sp.band_position[c];
-#pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const int x = x0 + i, v = o[i];
-                        const int k = ((v >> (bd - 5)) - pos) & 31;
-                        int q = clip3i(v + (k < 4 ? off[k + 1] : 0), 0, maxv);
-                        if (tqb) {
-                            const int pux = (x << hs) >> f.log2_min_pu, puy = (y << vs) >> f.log2_min_pu;
-                            if (pux < pu_xmax && puy < pu_ymax && f.is_pcm[puy * f.min_pu_w + pux]) q = v;
-                        }
-                        o[i] = q;
-                    }
-                } else {
-                    // ---- edge offset: sao_edge_filter (:342-378) then sao_edge_restore_{0,1} (:380-529)
-                    const int eo = sp.eo_class[c];
-                    const int dxa = (eo == 0 || eo == 2) ? -1 : (eo == 3 ? 1 : 0);
-                    const int dya = eo == 0 ? 0 : -1;
-                    const int fl = f.sao_ctb_flags[rs];
-                    const bool b0 = ctbx == 0, b1 = ctby == 0, b2 = ctbx == f.ctb_w - 1, b3 = ctby == f.ctb_h - 1;
-                    const bool notv = eo != OHCU_SAO_EO_VERT, noth = eo != OHCU_SAO_EO_HORIZ;
-                    const int wr = w - ((notv && b2) ? 1 : 0);             // width / height after the border
-                    const int hr = h - ((noth && b3) ? 1 : 0);             // columns / rows were peeled off
-                    const int init_x = (notv && b0) ? 1 : 0;
-                    const bool restore = fl & SAOF_RESTORE;
-                    const bool ve0 = fl & SAOF_VERT0, ve1 = fl & SAOF_VERT1;
-                    const bool he0 = fl & SAOF_HORIZ0, he1 = fl & SAOF_HORIZ1;
-                    const bool d0 = fl & SAOF_DIAG0, d1 = fl & SAOF_DIAG1, d2 = fl & SAOF_DIAG2, d3 = fl & SAOF_DIAG3;
-                    const int keep_ul = !d0 && eo == 2 && !b0 && !b1, keep_ur = !d1 && eo == 3 && !b1 && !b2;
-                    const int keep_lr = !d2 && eo == 2 && !b2 && !b3, keep_ll = !d3 && eo == 3 && !b0 && !b3;
-                    const int ya = y + dya, yb = y - dya;
-                    const bool ya_ok = ya >= 0 && ya < ph, yb_ok = yb >= 0 && yb < ph;
-                    const pixel *rowa = srow + dya * bw, *rowb = srow - dya * bw;
-#pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const int x = x0 + i, lx = x - cx0, v = o[i];
-                        const int xa = x + dxa, xb = x - dxa;
-                        // out-of-picture neighbours only occur where the border rules below override the result
-                        const int a = (ya_ok && xa >= 0 && xa < pw) ? rowa[xa] : v;
-                        const int b = (yb_ok && xb >= 0 && xb < pw) ? rowb[xb] : v;
-                        const int sgn = ((v > a) - (v < a)) + ((v > b) - (v < b));   // -2..2
-                        // edge_idx[] = {1, 2, 0, 3, 4}
-                        const int cat = sgn == 0 ? 0 : (sgn == -2 ? 1 : (sgn == -1 ? 2 : (sgn == 1 ? 3 : 4)));
-                        int q = clip3i(v + off[cat], 0, maxv);
-                        const int keep = clip3i(v + off[0], 0, maxv);
-                        // picture borders (restore_0 part)
-                        if (notv && ((b0 && lx == 0) || (b2 && lx == w - 1))) q = keep;
-                        if (noth && ((b1 && ly == 0) || (b3 && ly == h - 1)) && lx >= init_x && lx < wr) q = keep;
-                        if (restore) {                                     // slice / tile boundaries (restore_1)
-                            if (ve0 && notv && lx == 0 && ly >= keep_ul && ly < hr - keep_ll) q = v;
-                            if (ve1 && notv && lx == wr - 1 && ly >= keep_ur && ly < hr - keep_lr) q = v;
-                            if (he0 && noth && ly == 0 && lx >= init_x + keep_ul && lx < wr - keep_ur) q = v;
-                            if (he1 && noth && ly == hr - 1 && lx >= init_x + keep_ll && lx < wr - keep_lr) q = v;
-                            if (d0 && eo == 2 && lx == 0 && ly == 0) q = v;
-                            if (d1 && eo == 3 && lx == wr - 1 && ly == 0) q = v;
-                            if (d2 && eo == 2 && lx == wr - 1 && ly == hr - 1) q = v;
-                            if (d3 && eo == 3 && lx == 0 && ly == hr - 1) q = v;
-                        }
-                        if (tqb) {
-                            const int pux = (x << hs) >> f.log2_min_pu, puy = (y << vs) >> f.log2_min_pu;
-                            if (pux < pu_xmax && puy < pu_ymax && f.is_pcm[puy * f.min_pu_w + pux]) q = v;
-                        }
-                        o[i] = q;
-                    }
-                }
+            for (int i = 0; i < 8; i++) {
+                const int kb = ((v[i] >> sh) - pos) & 31;
+                o[i] = clip3i(v[i] + packed_offset(rec.lo, rec.hi, min(kb, 4)), 0, maxv);
             }
-            st4(drow + x0, o);
+        } else {                                                       // sao_edge_filter, template :342-378
+            ld8(sp8, v);
+            const int eo = (rec.misc >> 2) & 3;
+            if (eo == 0) sao_edge_fast<pixel, -1>(sp8, sp8, v, rec.lo, rec.hi, maxv, o);
+            else if (eo == 1) sao_edge_fast<pixel, 0>(sp8 - bw, sp8 + bw, v, rec.lo, rec.hi, maxv, o);
+            else if (eo == 2) sao_edge_fast<pixel, -1>(sp8 - bw, sp8 + bw, v, rec.lo, rec.hi, maxv, o);
+            else sao_edge_fast<pixel, 1>(sp8 - bw, sp8 + bw, v, rec.lo, rec.hi, maxv, o);
         }
+        st8(drow + x0, o);
     }
+#undef TILE
 }
 
 size_t loopfilter_smem_bytes(const FrameDev &f)
@@ -425,7 +611,7 @@ size_t loopfilter_smem_bytes(const FrameDev &f)
         const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
         total += (size_t)((LF_REGION >> hs) + 2 * AX) * ((LF_REGION >> vs) + 8) * P;
     }
-    return total + 16;
+    return total + 32 + 48 * sizeof(SaoRec) + 2 * LF_MAX_SEGS * sizeof(uint2);
 }
 
 // box of plane c that loopfilter_kernel fetches (api.cu encodes one tensor map per job and plane)
