@@ -3,14 +3,14 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload 4k|1080p|8k]
 
-A step = one pass of the hot path (MC -> residual -> deblock -> SAO) over one batch of
-synthetic frames.  Default workload: BASELINE.json configs[2], 3840x2160 Main10 4:2:0 full
+A step = one pass of the hot path (MC + residual, then deblock + SAO: two fused kernels
+and the halo fill per frame) over one batch of synthetic frames.  Default workload: BASELINE.json configs[2], 3840x2160 Main10 4:2:0 full
 reconstruction with weighted prediction.
 
   value        whole-job Mpixel/s (luma W*H*frames / s), work lists resident in HBM
   e2e          same metric through the C ABI with HOST buffers: list upload from pinned
                memory, kernels, and the reconstructed picture copied back to pinned memory
-  roofline     the dominant kernel (motion compensation) against the measured HBM peak
+  roofline     the dominant kernel (recon_kernel: MC + residual) against the measured HBM peak
   cpu_baseline the reference's own C hevcdsp path (oracle/_ref) on the host cores
   --impl reference   times that CPU path alone, same metric / config
 
@@ -44,6 +44,10 @@ WORKLOAD_NAMES = {
     "8k": "7680x4320 Main10 4:2:0, 64 independent frames sharded across GPUs (BASELINE configs[4])",
 }
 N_DISTINCT = 4        # distinct synthetic frames; jobs reuse them round-robin
+# dram__bytes_read.sum + dram__bytes_write.sum of one recon_kernel launch, from the committed
+# `ncu --set full` capture of this same command (never measured inside a timed run)
+NCU_TRAFFIC = {"4k": 89697536}
+NCU_TRAFFIC_SOURCE = "profiles/r01_v4_ncu_kernels.txt"
 
 
 def peaks():
@@ -53,16 +57,23 @@ def peaks():
     return 6650.0, "fallback"
 
 
-def make_inputs(workload, rank):
-    from hevc_b200 import synth
+def make_inputs(workload, rank, world=1):
+    """The N_DISTINCT * world synthetic frames of the job are sharded frame i -> rank i mod world."""
+    from hevc_b200 import shard, synth
     w, h, bd, cf, kw, _ = WORKLOADS[workload]
-    jobs = [synth.make_job(w, h, bd, cf, seed=3000 + 17 * rank + i, **kw) for i in range(N_DISTINCT)]
+    mine = shard.frames_of_rank(N_DISTINCT * world, rank, world)
+    jobs = [synth.make_job(w, h, bd, cf, seed=shard.seed_of_frame(3000, i), **kw) for i in mine]
     refs = [synth.make_picture(jobs[0].sp, 7000 + s) for s in range(2)]
     return jobs, refs
 
 
 def algorithmic_bytes(job):
-    """per stage, bytes that must move once."""
+    """per kernel, bytes that must move once.
+    recon       every reference sample a PU needs read once + every sample written once
+                + the int16 coefficients of the coded blocks read once (fused: no RMW)
+    loopfilter  the reconstructed picture read once + the filtered picture written once
+    pipeline    recon + loopfilter.  pipeline_survey is SURVEY's figure for the layout it
+                assumed (MC, residual RMW, deblock and SAO as four passes)."""
     sp = job.sp
     P = 2 if sp.bit_depth > 8 else 1
     hs = 1 if sp.chroma_format_idc in (1, 2) else 0
@@ -74,9 +85,9 @@ def algorithmic_bytes(job):
     nref = np.where(job.pus["pred_flag"] == 3, 2, 1)
     mc = int((area * (1 + nref)).sum() * planes_factor * P)        # read each ref sample once + write pred
     coded = int((1 << (2 * job.tus["log2_size"].astype(np.int64))).sum())
-    residual = coded * 2 + coded * P * 2                            # int16 coeffs + RMW of the prediction
-    return {"mc": mc, "residual": residual, "deblock": 2 * S, "sao": 2 * S,
-            "pipeline": mc + residual + 4 * S, "S": S}
+    recon = mc + coded * 2
+    return {"recon": recon, "loopfilter": 2 * S, "pad": 0, "pipeline": recon + 2 * S,
+            "pipeline_survey": mc + coded * 2 + coded * P * 2 + 4 * S, "S": S}
 
 
 class ClockSampler:
@@ -148,8 +159,8 @@ def cpu_reference(jobs, refs, steps, warmup, max_threads=None):
 
 # ------------------------------------------------------------------ our arm
 def run_ours(args, rank, world):
-    from hevc_b200 import abi, backend
-    jobs, refs = make_inputs(args.workload, rank)
+    from hevc_b200 import abi, backend, shard
+    jobs, refs = make_inputs(args.workload, rank, world)
     sp = jobs[0].sp
     B = WORKLOADS[args.workload][5]
     if args.frames:
@@ -161,10 +172,7 @@ def run_ours(args, rank, world):
     for s in range(2):
         ctx.upload(s, refs[s])
 
-    def barrier():
-        if world > 1:
-            import torch.distributed as dist
-            dist.barrier()
+    barrier = shard.barrier
 
     # ---------------- resident leg: lists staged once, kernels only in the timed region
     for k in range(B):
@@ -232,12 +240,15 @@ def run_ours(args, rank, world):
                fj.vbs.nbytes + fj.hbs.nbytes + fj.qp_y_tab.nbytes + fj.deblock.nbytes + fj.sao.nbytes + 2 * nctb)
         d2h = sum(p.nbytes for p in outs[k])
 
+    # frames are submitted by a few host threads, one frame each at a time, the way the
+    # reference's frame threads (hevcdec.h:53) would drive their own jobs
+    from concurrent.futures import ThreadPoolExecutor
+    pool = ThreadPoolExecutor(max(1, min(args.host_threads, B)))
     for k in range(B):
         submit(k, copy_coeffs=True)
     ctx.sync()
     for _ in range(args.warmup):
-        for k in range(B):
-            submit(k)
+        list(pool.map(submit, range(B)))
     ctx.sync()
     for k in range(B):
         ctx.slot_sync(2 + k)
@@ -245,9 +256,9 @@ def run_ours(args, rank, world):
     ctx.timer_start()
     t_host = time.perf_counter()
     for _ in range(args.steps):
-        for k in range(B):
-            submit(k)
+        list(pool.map(submit, range(B)))
     ms_e2e = ctx.timer_stop()
+    pool.shutdown()
     t_host = (time.perf_counter() - t_host) * 1e3
     barrier()
 
@@ -262,12 +273,7 @@ def run_ours(args, rank, world):
 
     # ---------------- reduce over ranks
     frames_rank = args.steps * B
-    if world > 1:
-        import torch
-        import torch.distributed as dist
-        t = torch.tensor([ms_resident, ms_e2e], dtype=torch.float64, device=f"cuda:{device}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_resident, ms_e2e = t.tolist()
+    ms_resident, ms_e2e = shard.max_over_ranks([ms_resident, ms_e2e], device=f"cuda:{device}")
     ctx.close()
     if rank != 0:
         return
@@ -276,8 +282,13 @@ def run_ours(args, rank, world):
     value = total_frames * px / (ms_resident * 1e-3) / 1e6
     e2e_value = total_frames * px / (ms_e2e * 1e-3) / 1e6
     ab = algorithmic_bytes(jobs[0])
-    mc_ms = float(stage_ms[abi.STAGE_MC])
-    achieved = ab["mc"] / (mc_ms * 1e-3) / 1e9
+    # stage events: [1] after recon_kernel (MC + residual fused), [3] after loopfilter_kernel
+    # (deblock + SAO fused), [4] after the halo fill
+    rc_ms = float(stage_ms[abi.STAGE_MC] + stage_ms[abi.STAGE_RESIDUAL])
+    lf_ms = float(stage_ms[abi.STAGE_DEBLOCK])
+    pad_ms = float(stage_ms[abi.STAGE_SAO])
+    achieved = ab["recon"] / (rc_ms * 1e-3) / 1e9
+    kern = [("recon", rc_ms), ("loopfilter", lf_ms), ("pad", pad_ms)]
     line = {
         "metric": "Mpixel/s reconstructed per B200 (4K Main10); HBM GB/s vs peak", "value": round(value, 1),
         "unit": "Mpixel/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -294,17 +305,20 @@ def run_ours(args, rank, world):
         "clocks": clocks,
         "e2e": {"value": round(e2e_value, 1), "unit": "Mpixel/s", "h2d_bytes_per_step": int(h2d * B),
                 "d2h_bytes_per_step": int(d2h * B), "frames_per_s": round(total_frames / (ms_e2e * 1e-3), 1),
-                "host_ms_per_step": round(t_host / args.steps, 3)},
-        "roofline": {"bound": "hbm", "kernel": "mc_kernel (motion compensation)", "achieved": round(achieved, 1),
+                "host_ms_per_step": round(t_host / args.steps, 3), "host_threads": max(1, min(args.host_threads, B))},
+        "roofline": {"bound": "hbm", "kernel": "recon_kernel (motion compensation + residual, fused)",
+                     "achieved": round(achieved, 1),
                      "peak": hbm_peak, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "unit": "GB/s",
-                     "frac": round(achieved / hbm_peak, 4), "traffic": None,
-                     "algorithmic_bytes_per_launch": int(ab["mc"]), "ms_per_launch": round(mc_ms, 4)},
-        "stages": {name: {"ms": round(float(stage_ms[i]), 4), "algorithmic_mb": round(ab[key] / 1e6, 2),
-                          "gbs": round(ab[key] / (float(stage_ms[i]) * 1e-3) / 1e9, 1) if stage_ms[i] > 0 else None}
-                   for i, (name, key) in enumerate([("mc", "mc"), ("residual", "residual"), ("deblock", "deblock"),
-                                                    ("sao", "sao")])},
+                     "frac": round(achieved / hbm_peak, 4),
+                     "traffic": NCU_TRAFFIC.get(args.workload),
+                     "traffic_source": NCU_TRAFFIC_SOURCE if args.workload in NCU_TRAFFIC else None,
+                     "algorithmic_bytes_per_launch": int(ab["recon"]), "ms_per_launch": round(rc_ms, 4)},
+        "kernels": {name: {"ms": round(ms, 4), "algorithmic_mb": round(ab[name] / 1e6, 2),
+                           "gbs": round(ab[name] / (ms * 1e-3) / 1e9, 1) if ms > 0 and ab[name] else None}
+                    for name, ms in kern},
         "pipeline": {"ms_per_frame_single_stream": round(float(stage_ms[abi.STAGE_TOTAL]), 4),
                      "algorithmic_mb_per_frame": round(ab["pipeline"] / 1e6, 2),
+                     "algorithmic_mb_per_frame_survey_4pass": round(ab["pipeline_survey"] / 1e6, 2),
                      "gbs_at_value": round(ab["pipeline"] * total_frames / world / (ms_resident * 1e-3) / 1e9, 1),
                      "frac_of_peak_at_value": round(ab["pipeline"] * total_frames / world / (ms_resident * 1e-3) / 1e9 / hbm_peak, 4)},
         "parity_check": check,
@@ -347,6 +361,7 @@ def main():
     ap.add_argument("--workload", default="4k", choices=list(WORKLOADS))
     ap.add_argument("--frames", type=int, default=0, help="frames per step per GPU (default per workload)")
     ap.add_argument("--cpu-steps", type=int, default=2, help="steps of the cpu_baseline leg")
+    ap.add_argument("--host-threads", type=int, default=4, help="threads submitting frames in the e2e leg")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-check", action="store_true")
     args = ap.parse_args()

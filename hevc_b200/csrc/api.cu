@@ -76,6 +76,7 @@ struct Job {
     Arena<ohcu_tu> tus;      int n_tu = 0;
     Arena<int2> ctb_tu_range;    // per CTB: first TU, count
     bool tu_sorted = true;   int last_tu_ctb = -1;
+    bool has_cross = false;  int max_slice = -1;    // what frame_stage has to validate
     Arena<int16_t> coeffs;   size_t ncoeff = 0;
     Arena<uint8_t> vbs, hbs, is_pcm; Arena<int8_t> qp; Arena<ohcu_dbparams> db;
     Arena<ohcu_sao> sao;     Arena<uint16_t> sao_flags;
@@ -99,6 +100,10 @@ struct ohcu_ctx {
     size_t l2_bytes = 0;
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     CUtensorMap *tmaps_d = nullptr;
+    // Frame threads each drive their own job; the lists of a job are touched by one thread
+    // at a time (caller's contract).  What jobs share — the job ring, the slots' ordering
+    // events and reader masks, the launch counter — is guarded here.
+    std::mutex mu;
 };
 
 // ------------------------------------------------------------------ helpers
@@ -393,6 +398,7 @@ extern "C" int ohcu_slot_upload(ohcu_ctx *c, int slot, const uint8_t *const plan
     if (check_slot(c, slot)) return OHCU_EINVAL;
     if (!planes || !strides) return fail(OHCU_EINVAL, "null planes");
     Slot &s = c->slots[slot];
+    std::lock_guard<std::mutex> lock(c->mu);
     // anything still reading or writing this slot must finish first
     CU(cudaDeviceSynchronize());
     for (int i = 0; i < c->nplanes; i++)
@@ -416,12 +422,15 @@ static int download_impl(ohcu_ctx *c, int slot, uint8_t *const planes[3], const 
     if (check_slot(c, slot)) return OHCU_EINVAL;
     if (!planes || !strides) return fail(OHCU_EINVAL, "null planes");
     Slot &s = c->slots[slot];
-    if (s.has_ready) CU(cudaStreamWaitEvent(c->copy_stream, s.ready, 0));
-    for (int i = 0; i < c->nplanes; i++)
-        CU(cudaMemcpy2DAsync(planes[i], strides[i], s.pic.ps.p[i], s.pic.ps.pitch[i], (size_t)c->pw[i] * c->P,
-                             c->ph[i], cudaMemcpyDeviceToHost, c->copy_stream));
-    CU(cudaEventRecord(s.read_done, c->copy_stream));
-    s.has_read = true;
+    {
+        std::lock_guard<std::mutex> lock(c->mu);
+        if (s.has_ready) CU(cudaStreamWaitEvent(c->copy_stream, s.ready, 0));
+        for (int i = 0; i < c->nplanes; i++)
+            CU(cudaMemcpy2DAsync(planes[i], strides[i], s.pic.ps.p[i], s.pic.ps.pitch[i], (size_t)c->pw[i] * c->P,
+                                 c->ph[i], cudaMemcpyDeviceToHost, c->copy_stream));
+        CU(cudaEventRecord(s.read_done, c->copy_stream));
+        s.has_read = true;
+    }
     if (wait) CU(cudaEventSynchronize(s.read_done));
     return 0;
 }
@@ -438,8 +447,13 @@ extern "C" int ohcu_slot_sync(ohcu_ctx *c, int slot)
     ENTER(c);
     if (check_slot(c, slot)) return OHCU_EINVAL;
     Slot &s = c->slots[slot];
-    if (s.has_ready) CU(cudaEventSynchronize(s.ready));
-    if (s.has_read) CU(cudaEventSynchronize(s.read_done));
+    bool ready, read;
+    {
+        std::lock_guard<std::mutex> lock(c->mu);
+        ready = s.has_ready; read = s.has_read;
+    }
+    if (ready) CU(cudaEventSynchronize(s.ready));
+    if (read) CU(cudaEventSynchronize(s.read_done));
     return 0;
 }
 
@@ -448,8 +462,14 @@ extern "C" int ohcu_frame_begin(ohcu_ctx *c, int out_slot, int poc)
 {
     ENTER(c);
     if (check_slot(c, out_slot)) return OHCU_EINVAL;
-    const int id = c->next_job;
-    c->next_job = (c->next_job + 1) % (int)c->jobs.size();
+    int id;
+    {
+        std::lock_guard<std::mutex> lock(c->mu);
+        id = c->next_job;
+        if (c->jobs[id].open) return fail(OHCU_ESTATE, "job %d is still being filled: more frames begun than jobs", id);
+        c->next_job = (c->next_job + 1) % (int)c->jobs.size();
+        c->jobs[id].open = true;
+    }
     Job &j = c->jobs[id];
     // the arena's previous frame must have left the device before its pinned staging is reused
     if (j.has_done) CU(cudaEventSynchronize(j.done));
@@ -458,11 +478,20 @@ extern "C" int ohcu_frame_begin(ohcu_ctx *c, int out_slot, int poc)
     j.n_pu = 0; j.n_tu = 0; j.ncoeff = 0; j.n_slices = 0;
     j.pu_sorted = true; j.last_ctb = -1;
     j.tu_sorted = true; j.last_tu_ctb = -1;
+    j.has_cross = false; j.max_slice = -1;
     j.has_deblock = j.has_sao = j.has_pcm = false;
     memset(j.ctb_range.h, 0, sizeof(int2) * c->nctb);
     memset(j.ctb_tu_range.h, 0, sizeof(int2) * c->nctb);
     std::fill(j.ctb_area.begin(), j.ctb_area.end(), 0);
     return id;
+}
+
+extern "C" int ohcu_frame_abort(ohcu_ctx *c, int job)
+{
+    ENTER(c);
+    if (check_job(c, job)) return OHCU_EINVAL;
+    c->jobs[job].open = false;
+    return 0;
 }
 
 #define OPEN_JOB(c, job)                                                        \
@@ -485,24 +514,30 @@ extern "C" int ohcu_append_pu(ohcu_ctx *c, int job, const ohcu_pu *recs, int n)
     OPEN_JOB(c, job);
     if (n < 0 || (n && !recs)) return fail(OHCU_EINVAL, "bad PU list");
     if ((size_t)j.n_pu + n > j.pus.cap) return fail(OHCU_EOVERFLOW, "PU arena full (%zu)", j.pus.cap);
-    const int l2 = c->sp.log2_ctb_size;
-    int2 *range = j.ctb_range.h;
+    const int l2 = c->sp.log2_ctb_size, ctb_w = c->ctb_w, W = c->sp.width, H = c->sp.height, base = j.n_pu;
+    int2 *const range = j.ctb_range.h;
+    int *const area = j.ctb_area.data();
+    ohcu_pu *const dst = j.pus.h + j.n_pu;
+    int last = j.last_ctb, max_slice = j.max_slice;
+    bool sorted = j.pu_sorted;
     for (int i = 0; i < n; i++) {
-        const ohcu_pu &pu = recs[i];
+        const ohcu_pu pu = recs[i];
         if (pu.pred_flag < 1 || pu.pred_flag > 3 || pu.w < 4 || pu.h < 4 || pu.w > 64 || pu.h > 64 ||
-            pu.x0 + pu.w > c->sp.width || pu.y0 + pu.h > c->sp.height || pu.slice >= OHCU_MAX_SLICES ||
+            pu.x0 + pu.w > W || pu.y0 + pu.h > H || pu.slice >= OHCU_MAX_SLICES ||
             pu.ref_idx[0] >= OHCU_MAX_REFS || pu.ref_idx[1] >= OHCU_MAX_REFS)
-            return fail(OHCU_EINVAL, "PU record %d is malformed", j.n_pu + i);
-        const int ctb = (pu.x0 >> l2) + (pu.y0 >> l2) * c->ctb_w;
-        if (ctb != j.last_ctb) {
-            if (range[ctb].y != 0) j.pu_sorted = false;      // CTB seen before: lists not grouped
-            else range[ctb].x = j.n_pu + i;
-            j.last_ctb = ctb;
+            return fail(OHCU_EINVAL, "PU record %d is malformed", base + i);
+        const int ctb = (pu.x0 >> l2) + (pu.y0 >> l2) * ctb_w;
+        if (ctb != last) {
+            if (range[ctb].y != 0) sorted = false;           // CTB seen before: lists not grouped
+            else range[ctb].x = base + i;
+            last = ctb;
         }
         range[ctb].y++;
-        j.ctb_area[ctb] += pu.w * pu.h;
-        j.pus.h[j.n_pu + i] = pu;
+        area[ctb] += pu.w * pu.h;
+        max_slice = std::max(max_slice, (int)pu.slice);
+        dst[i] = pu;
     }
+    j.last_ctb = last; j.pu_sorted = sorted; j.max_slice = max_slice;
     j.n_pu += n;
     return 0;
 }
@@ -510,30 +545,39 @@ extern "C" int ohcu_append_pu(ohcu_ctx *c, int job, const ohcu_pu *recs, int n)
 static int add_tus(ohcu_ctx *c, Job &j, const ohcu_tu *recs, int n, uint32_t rebase)
 {
     if ((size_t)j.n_tu + n > j.tus.cap) return fail(OHCU_EOVERFLOW, "TU arena full (%zu)", j.tus.cap);
-    int2 *range = j.ctb_tu_range.h;
+    // everything the loop reads, in locals: the stores into the pinned arena could alias the context
+    int2 *const range = j.ctb_tu_range.h;
+    ohcu_tu *const dst = j.tus.h + j.n_tu;
+    const int l2 = c->sp.log2_ctb_size, ctb_w = c->ctb_w, base = j.n_tu;
+    const int pw[3] = {c->pw[0], c->pw[1], c->pw[2]}, ph[3] = {c->ph[0], c->ph[1], c->ph[2]};
+    const int ths[3] = {0, c->hs, c->hs}, tvs[3] = {0, c->vs, c->vs};
+    const int max_c = c->sp.chroma_format_idc ? 2 : 0;
+    const size_t ncoeff = j.ncoeff;
+    int last = j.last_tu_ctb;
+    bool sorted = j.tu_sorted, cross = j.has_cross;
     for (int i = 0; i < n; i++) {
         ohcu_tu tu = recs[i];
-        const int l = tu.log2_size - 2;
-        if (l < 0 || l > 3 || tu.c_idx > 2 || (tu.c_idx && !c->sp.chroma_format_idc) || tu.mode > OHCU_TU_BYPASS ||
-            (tu.mode == OHCU_TU_DST4 && l != 0))
-            return fail(OHCU_EINVAL, "TU record %d is malformed", j.n_tu + i);
+        const unsigned l = (unsigned)tu.log2_size - 2u;
+        if (l > 3u || tu.c_idx > max_c || tu.mode > OHCU_TU_BYPASS || (tu.mode == OHCU_TU_DST4 && l != 0))
+            return fail(OHCU_EINVAL, "TU record %d is malformed", base + i);
         const int n1 = 1 << tu.log2_size;
-        if (tu.x0 + n1 > c->pw[tu.c_idx] || tu.y0 + n1 > c->ph[tu.c_idx])
-            return fail(OHCU_EINVAL, "TU record %d lies outside plane %d", j.n_tu + i, tu.c_idx);
+        if (tu.x0 + n1 > pw[tu.c_idx] || tu.y0 + n1 > ph[tu.c_idx])
+            return fail(OHCU_EINVAL, "TU record %d lies outside plane %d", base + i, tu.c_idx);
         tu.coeff_off += rebase;
-        if ((size_t)tu.coeff_off + (size_t)n1 * n1 > j.ncoeff || (tu.coeff_off & 1))
-            return fail(OHCU_EINVAL, "TU record %d: coefficient block outside the arena", j.n_tu + i);
+        if ((size_t)tu.coeff_off + (size_t)(n1 * n1) > ncoeff || (tu.coeff_off & 1))
+            return fail(OHCU_EINVAL, "TU record %d: coefficient block outside the arena", base + i);
         // CTB of the block (plane samples -> luma samples)
-        const int ths = tu.c_idx ? c->hs : 0, tvs = tu.c_idx ? c->vs : 0;
-        const int ctb = ((tu.x0 << ths) >> c->sp.log2_ctb_size) + ((tu.y0 << tvs) >> c->sp.log2_ctb_size) * c->ctb_w;
-        if (ctb != j.last_tu_ctb) {
-            if (range[ctb].y != 0) j.tu_sorted = false;      // CTB seen before: list not grouped
-            else range[ctb].x = j.n_tu + i;
-            j.last_tu_ctb = ctb;
+        const int ctb = ((tu.x0 << ths[tu.c_idx]) >> l2) + ((tu.y0 << tvs[tu.c_idx]) >> l2) * ctb_w;
+        if (ctb != last) {
+            if (range[ctb].y != 0) sorted = false;           // CTB seen before: list not grouped
+            else range[ctb].x = base + i;
+            last = ctb;
         }
         range[ctb].y++;
-        j.tus.h[j.n_tu + i] = tu;
+        cross |= (tu.flags & OHCU_TUF_CROSS) != 0;
+        dst[i] = tu;
     }
+    j.last_tu_ctb = last; j.tu_sorted = sorted; j.has_cross = cross;
     j.n_tu += n;
     return 0;
 }
@@ -660,7 +704,15 @@ static void sort_tus_by_ctb(ohcu_ctx *c, Job &j)
     j.tu_sorted = true;
 }
 
+static int stage_impl(ohcu_ctx *c, int job);
+// A stage that fails discards the job's lists (the job can be begun again).
 extern "C" int ohcu_frame_stage(ohcu_ctx *c, int job)
+{
+    const int rc = stage_impl(c, job);
+    if (rc && c && job >= 0 && job < (int)c->jobs.size()) c->jobs[job].open = false;
+    return rc;
+}
+static int stage_impl(ohcu_ctx *c, int job)
 {
     OPEN_JOB(c, job);
     if (!j.pu_sorted) sort_pus_by_ctb(c, j);
@@ -682,9 +734,8 @@ extern "C" int ohcu_frame_stage(ohcu_ctx *c, int job)
                 else j.all_covered = false;
             }
     }
-    for (int i = 0; i < j.n_pu; i++)
-        if (j.pus.h[i].slice >= j.n_slices) return fail(OHCU_EINVAL, "PU %d uses slice %d which was never set", i, j.pus.h[i].slice);
-    for (int i = 0; i < j.n_tu; i++)
+    if (j.max_slice >= j.n_slices) return fail(OHCU_EINVAL, "a PU uses slice %d which was never set", j.max_slice);
+    for (int i = 0; j.has_cross && i < j.n_tu; i++)
         if ((j.tus.h[i].flags & OHCU_TUF_CROSS) &&
             (j.tus.h[i].cross_tu >= (uint32_t)j.n_tu || j.tus.h[j.tus.h[i].cross_tu].log2_size != j.tus.h[i].log2_size))
             return fail(OHCU_EINVAL, "TU %d: bad cross-component reference", i);
@@ -737,6 +788,7 @@ extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int 
     if (!stages) stages = 15;
     cudaStream_t st = j.stream;
     Slot &os = c->slots[out_slot];
+    std::lock_guard<std::mutex> lock(c->mu);
 
     // ---- ordering between frames: replaces ff_thread_await_progress (hevcdec.c:2051-2058).
     // Readers: every slot the slice tables name.  Writer: wait for earlier readers/downloads.

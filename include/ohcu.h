@@ -208,6 +208,13 @@ int ohcu_slot_sync(ohcu_ctx *ctx, int slot);   /* replaces ff_thread_await_progr
  * reconstructed picture is written to.                                        */
 int ohcu_frame_begin(ohcu_ctx *ctx, int out_slot, int poc);
 
+/* Threads: frame threads (the reference runs up to 16, hevcdec.h:53) may each drive
+ * their own job concurrently; the lists of ONE job are filled by one thread at a time.
+ * begin fails with OHCU_ESTATE when the ring's next job is still being filled (more
+ * frames begun than jobs).  A stage that fails discards the job's lists;
+ * ohcu_frame_abort does the same for a job whose appends failed.                  */
+int ohcu_frame_abort(ohcu_ctx *ctx, int job);
+
 int ohcu_set_slice(ohcu_ctx *ctx, int job, int slice_idx, const ohcu_slice_tab *tab);
 
 /* replaces the immediate put_hevc_{q,e}pel* calls of hevcdec.c:1781-1786,
@@ -239,7 +246,7 @@ int ohcu_set_sao(ohcu_ctx *ctx, int job, const ohcu_sao_in *in);
 
 /* End of frame (where ff_hevc_hls_filter ran per CTB, hevc_filter.c:1211-1245):
  * upload the job's lists (async, pinned) and enqueue the batched launches
- *   MC -> residual add -> deblock (all vertical, then all horizontal edges) -> SAO
+ *   MC + residual add (one kernel) -> deblock + SAO (one kernel) -> halo fill
  * on the job's stream.  Returns without waiting.                                 */
 int ohcu_frame_flush(ohcu_ctx *ctx, int job);
 
