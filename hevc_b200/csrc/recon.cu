@@ -48,7 +48,7 @@ constexpr int MAX_ROUNDS = 8;                // per kind
 constexpr int N_KINDS = 4;                   // list slot A luma, slot B luma, slot A chroma, slot B chroma
 
 // scratch of one warp in the residual phase (aliases the window pool): one 32x32 int16 block
-struct WarpScratch { uint32_t w[32 * 34 / 2]; };
+struct WarpScratch { uint32_t w[32 * 40 / 2]; };   // 32 x (32 + 8) int16: idct_mma's pass-1 output
 
 // ff_hevc_qpel_filters / ff_hevc_epel_filters (hevcdsp.c:181-195) packed four int8 taps
 // per word: [phase][0] = taps 0..3, [phase][1] = taps 4..7
@@ -207,6 +207,27 @@ __device__ __forceinline__ int fastinv(int d) { return c_inv[d]; }              
 // take them straight from the constant bank; filled at load time from the cosine index rule.
 __constant__ int c_dct[32][32];
 
+// constant mma fragments of the transform matrix, see idct_mma below
+__device__ uint32_t g_idct_frag[2][2][32][4];       // [N == 32][k-half][output index i][t]
+
+static void fill_idct_frag(const int (*t)[32], uint32_t (*out)[2][32][4])
+{
+    for (int big = 0; big < 2; big++) {
+        const int n = big ? 32 : 16, step = 32 / n;
+        for (int h = 0; h < 2; h++)
+            for (int i = 0; i < 32; i++)
+                for (int q = 0; q < 4; q++) {
+                    uint32_t w = 0;
+                    for (int s = 0; s < 4; s++) {
+                        const int j = 16 * h + (s < 2 ? 2 * q + s : 8 + 2 * q + s - 2);
+                        const int v = (j < n && i < n) ? t[j * step][i] : 0;
+                        w |= (uint32_t)(v & 0xff) << (8 * s);
+                    }
+                    out[big][h][i][q] = w;
+                }
+    }
+}
+
 int upload_dct_table()
 {
     static const int mag[33] = {64, 90, 90, 90, 89, 88, 87, 85, 83, 82, 80, 78, 75, 73, 70, 67, 64,
@@ -217,6 +238,9 @@ int upload_dct_table()
             int m = (r * (2 * c + 1)) & 127;
             t[r][c] = r == 0 ? 64 : (m <= 32 ? mag[m] : (m <= 64 ? -mag[64 - m] : (m <= 96 ? -mag[m - 64] : mag[128 - m])));
         }
+    static uint32_t frag[2][2][32][4];
+    fill_idct_frag(t, frag);
+    if (cudaMemcpyToSymbol(g_idct_frag, frag, sizeof(frag)) != cudaSuccess) return -1;
     return cudaMemcpyToSymbol(c_dct, t, sizeof(t)) == cudaSuccess ? 0 : -1;
 }
 
@@ -353,6 +377,174 @@ __device__ __noinline__ void tb_residual(int bd, const ohcu_tu &tu, const int16_
     __syncwarp(mask);
 }
 
+// ---------------------------------------------------------------- IDCT 16 / 32 on the tensor cores
+// The two passes of IDCT(16|32) (template :249-291) are matrix products with the int8
+// transform matrix: integer mma.sync (exact s32 accumulation) on the int16 data split into a
+// signed high and an unsigned low byte plane, v = 256 * hi + lo:
+//   pass 1   tmp[y][x] = clip16((sum_j T[j][y] * coef[j][x] + 64) >> 7)         A = T^T (constant), B = coef
+//   pass 2   res[y][m] = clip16((sum_x tmp[y][x] * T[x][m] + add) >> (20 - BD))  A = tmp, B = T (constant)
+// The contraction index must be contiguous in both fragments.  ldmatrix(.trans) delivers 16-bit
+// pairs, so the four bytes of a fragment register are data elements {2t, 2t+1, 8+2t, 9+2t} (+16
+// for the second k-half) of a column (pass 1, .trans on the row-major coefficient block) or of a
+// row (pass 2) — a fixed permutation of the contraction index that the constant fragments
+// repeat.  One table serves both passes: the pass-1 A fragment of output row i is the pass-2 B
+// fragment of output column i.
+// Zero skipping: the reference skips single inputs, not tiles — an input j of a butterfly called
+// with bound `end` is read iff idct_reads(j, end) (TR_8..TR_32, template :193-239), with
+// end = col_limit + 4 shrinking by 4 every 4 columns in pass 1 (:256-262) and end = col_limit in
+// pass 2.  Inputs it does not read are masked to zero here (registers of pass 1, the stored
+// pass-1 output for pass 2), so the result equals the reference's for ANY block content, not
+// only for blocks whose skipped coefficients are zero.
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], const void *p)
+{
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_u32(p)) : "memory");
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], const void *p)
+{
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_u32(p)) : "memory");
+}
+// d += A(16x16) * B(16x8); SA / SB: operand is signed
+template <bool SA, bool SB>
+__device__ __forceinline__ void imma16(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t b)
+{
+    if (SA && SB)
+        asm volatile("mma.sync.aligned.m16n8k16.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                     : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3]) : "r"(a0), "r"(a1), "r"(b));
+    else if (SA)
+        asm volatile("mma.sync.aligned.m16n8k16.row.col.s32.s8.u8.s32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                     : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3]) : "r"(a0), "r"(a1), "r"(b));
+    else
+        asm volatile("mma.sync.aligned.m16n8k16.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                     : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3]) : "r"(a0), "r"(a1), "r"(b));
+}
+__device__ __forceinline__ uint32_t pack_sat16(int lo, int hi)
+{
+    uint32_t d;
+    asm("cvt.pack.sat.s16.s32 %0, %1, %2;" : "=r"(d) : "r"(hi), "r"(lo));
+    return d;
+}
+// tile word (two samples) += two residuals, clipped to the pixel range: transform_add (template :45-84)
+__device__ __forceinline__ void tile_add_pair(uint32_t *w, int r0, int r1, int maxv)
+{
+    const uint32_t v = *w;
+    const int lo = min(max((int)(v & 0xffffu) + r0, 0), maxv), hi = min(max((int)(v >> 16) + r1, 0), maxv);
+    *w = (uint32_t)lo | ((uint32_t)hi << 16);
+}
+
+// One N x N block by the whole warp.  src: row-major coefficients in shared memory, 16-byte
+// aligned; t1: N x (N + 8) int16 of scratch; tw: tile word of the block's first sample.
+template <int LOG2>
+__device__ __noinline__ void idct_mma(const int16_t *src, int16_t *t1, uint32_t *tw, int tpitch, int col_limit, int bd, int lane)
+{
+    constexpr int N = 1 << LOG2, ST = N + 8, NQ = N / 8, NH = N / 16;
+    const int g = lane >> 2, t = lane & 3;
+    uint32_t F[NQ][NH];
+#pragma unroll
+    for (int q = 0; q < NQ; q++)
+#pragma unroll
+        for (int h = 0; h < NH; h++) F[q][h] = __ldg(&g_idct_frag[LOG2 - 4][h][g + 8 * q][t]);
+    const int limit = min(col_limit, N), lim2 = min(col_limit + 4, N);
+    // keep-masks of a 16-bit pair (even element e, odd element e + 1) under bound `end`
+    auto pair_mask = [](int e, int end) -> uint32_t {
+        const bool keep_even = (N == 32 && (e & 3) == 2) ? (e >> 1) < (end >> 1) : true;
+        return (keep_even ? 0xffffu : 0u) | (e + 1 < end ? 0xffff0000u : 0u);
+    };
+
+    // ---- pass 1: columns.  One ldmatrix.x4.trans per step: lane i supplies row (i & 7) of matrix (i >> 3).
+    //   N = 32: the four row tiles (j = 0..31) of column tile xt -> both k-halves
+    //   N = 16: the two row tiles of column tiles 0 and 1 -> the whole block in one step
+    constexpr int XSTEP = N == 16 ? 2 : 1;
+#pragma unroll 1
+    for (int xt0 = 0; xt0 < N / 8 / XSTEP; xt0++) {
+        uint32_t r[4];
+        if (N == 32) ldsm_x4_trans(r, src + lane * N + 8 * xt0);
+        else ldsm_x4_trans(r, src + (8 * ((lane >> 3) & 1) + (lane & 7)) * N + 8 * (lane >> 4));
+        if (lim2 < N) {                                    // inputs the reference's column pass skips
+#pragma unroll
+            for (int m = 0; m < 4; m++) {
+                const int x = 8 * (N == 32 ? xt0 : (m >> 1)) + g;
+                const int end = lim2 - (x ? 4 * ((x - 1) >> 2) : 0);
+                r[m] &= pair_mask(8 * (N == 32 ? m : (m & 1)) + 2 * t, end);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < XSTEP; u++) {
+            uint32_t bl[NH], bh[NH];
+            if (N == 32) {
+#pragma unroll
+                for (int h = 0; h < NH; h++) {
+                    bl[h] = __byte_perm(r[2 * h], r[2 * h + 1], 0x6420);
+                    bh[h] = __byte_perm(r[2 * h], r[2 * h + 1], 0x7531);
+                }
+            } else {
+                bl[0] = __byte_perm(r[2 * u], r[2 * u + 1], 0x6420);
+                bh[0] = __byte_perm(r[2 * u], r[2 * u + 1], 0x7531);
+            }
+            // pass 2 does not read every column: mask of this thread's output pair (x, x + 1)
+            const int x = 8 * (xt0 * XSTEP + u) + 2 * t;
+            const uint32_t keep = pair_mask(x, limit);
+#pragma unroll
+            for (int mt = 0; mt < NH; mt++) {
+                int acc[4] = {0, 0, 0, 0};
+#pragma unroll
+                for (int h = 0; h < NH; h++) imma16<true, true>(acc, F[2 * mt][h], F[2 * mt + 1][h], bh[h]);
+#pragma unroll
+                for (int k = 0; k < 4; k++) acc[k] = acc[k] * 256 + 64;
+#pragma unroll
+                for (int h = 0; h < NH; h++) imma16<true, false>(acc, F[2 * mt][h], F[2 * mt + 1][h], bl[h]);
+                const int y = 16 * mt + g;
+                *(uint32_t *)&t1[y * ST + x] = pack_sat16(acc[0] >> 7, acc[1] >> 7) & keep;
+                *(uint32_t *)&t1[(y + 8) * ST + x] = pack_sat16(acc[2] >> 7, acc[3] >> 7) & keep;
+            }
+        }
+    }
+    __syncwarp();
+
+    // ---- pass 2: rows, added into the tile
+    const int sh = 20 - bd, add = 1 << (sh - 1), maxv = (1 << bd) - 1;
+#pragma unroll 1
+    for (int mt = 0; mt < NH; mt++) {
+        uint32_t al[NH][2], ah[NH][2];
+#pragma unroll
+        for (int h = 0; h < NH; h++) {
+            {
+                uint32_t r[4];
+                // matrices: (rows 16mt.., cols 16h), (rows 16mt.., cols 16h + 8), (rows 16mt + 8.., cols 16h), (.., 16h + 8)
+                const int m = lane >> 3;
+                ldsm_x4(r, t1 + (16 * mt + 8 * (m >> 1) + (lane & 7)) * ST + 16 * h + 8 * (m & 1));
+                al[h][0] = __byte_perm(r[0], r[1], 0x6420); ah[h][0] = __byte_perm(r[0], r[1], 0x7531);
+                al[h][1] = __byte_perm(r[2], r[3], 0x6420); ah[h][1] = __byte_perm(r[2], r[3], 0x7531);
+            }
+        }
+#pragma unroll
+        for (int nt = 0; nt < NQ; nt++) {
+            int acc[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int h = 0; h < NH; h++)
+                imma16<true, true>(acc, ah[h][0], ah[h][1], F[nt][h]);
+#pragma unroll
+            for (int k = 0; k < 4; k++) acc[k] = acc[k] * 256 + add;
+#pragma unroll
+            for (int h = 0; h < NH; h++)
+                imma16<false, true>(acc, al[h][0], al[h][1], F[nt][h]);
+            const int y = 16 * mt + g, xw = 4 * nt + t;
+            tile_add_pair(tw + y * tpitch + xw, clip_s16(acc[0] >> sh), clip_s16(acc[1] >> sh), maxv);
+            tile_add_pair(tw + (y + 8) * tpitch + xw, clip_s16(acc[2] >> sh), clip_s16(acc[3] >> sh), maxv);
+        }
+    }
+    __syncwarp();
+}
+
+// IDCT_DC (template :273-286) of one N x N block by the whole warp
+__device__ __forceinline__ void dc_block(int log2, int c0, uint32_t *tw, int tpitch, int bd, int lane)
+{
+    const int v = (((c0 + 1) >> 1) + (1 << (13 - bd))) >> (14 - bd), maxv = (1 << bd) - 1;
+    const int n = 1 << log2, wl = log2 - 1;                // words per row = n / 2
+    for (int i = lane; i < (n << wl); i += 32) tile_add_pair(tw + (i >> wl) * tpitch + (i & ((1 << wl) - 1)), v, v, maxv);
+}
+
 // A warp takes 32/N TBs of one size class at a time (lane group = one TB) and adds their
 // residual into the CTB tile: transform_add (template :45-84).
 struct CtbTile {
@@ -377,34 +569,61 @@ __device__ void tu_batch(const FrameDev &f, const CtbTile &tile, int tu0, const 
                          int cx0, int cy0, WarpScratch &ws, WarpScratch *ws2, const CoefSrc &cs, int lane)
 {
     constexpr int N = 1 << LOG2, S = Stride<N>::S, GROUPS = 32 / N;
+    constexpr bool MMA = LOG2 >= 4;
     const int grp = lane >> LOG2, g = lane & (N - 1);
-    if (first + grp >= count) return;
+    const bool have = first + grp < count;
     const unsigned mask = N == 32 ? 0xffffffffu : (((1u << N) - 1u) << (lane & ~(N - 1)));
-    const ohcu_tu tu = f.tus[tu0 + list[first + grp]];
-    int16_t *blk = (int16_t *)&ws + (size_t)grp * N * S;
+    ohcu_tu tu = {};
+    if (have) tu = f.tus[tu0 + list[first + grp]];
     static_assert(GROUPS * N * S * 2 <= (int)sizeof(WarpScratch), "block buffers must fit the warp scratch");
-
-    tb_residual<LOG2>(f.bd, tu, cs.at(tu.coeff_off, N * N), blk, g, mask);
-    if ((tu.flags & OHCU_TUF_CROSS) && ws2) {                  // hevc_cabac.c:1810-1817
-        int16_t *by = (int16_t *)ws2 + (size_t)grp * N * S;
-        const ohcu_tu ty = f.tus[tu.cross_tu];
-        if (ty.log2_size == LOG2) {
-            tb_residual<LOG2>(f.bd, ty, cs.at(ty.coeff_off, N * N), by, g, mask);
-            const int scale = tu.res_scale_val;
+    // 16x16 / 32x32 IDCT and DC blocks go through the warp-wide paths below
+    bool wide = false;
+    if (MMA && have && !(tu.flags & OHCU_TUF_CROSS)) {
+        const bool in_smem = cs.csm && tu.coeff_off >= cs.clo && tu.coeff_off + N * N <= cs.chi && !((tu.coeff_off - cs.clo) & 7);
+        wide = tu.mode == OHCU_TU_DC || (tu.mode == OHCU_TU_IDCT && in_smem);
+    }
+    if (have && !wide) {
+        int16_t *blk = (int16_t *)&ws + (size_t)grp * N * S;
+        tb_residual<LOG2>(f.bd, tu, cs.at(tu.coeff_off, N * N), blk, g, mask);
+        if ((tu.flags & OHCU_TUF_CROSS) && ws2) {                  // hevc_cabac.c:1810-1817
+            int16_t *by = (int16_t *)ws2 + (size_t)grp * N * S;
+            const ohcu_tu ty = f.tus[tu.cross_tu];
+            if (ty.log2_size == LOG2) {
+                tb_residual<LOG2>(f.bd, ty, cs.at(ty.coeff_off, N * N), by, g, mask);
+                const int scale = tu.res_scale_val;
 #pragma unroll
-            for (int k = 0; k < N; k++)
-                blk[g * S + k] = (int16_t)(blk[g * S + k] + ((scale * by[g * S + k]) >> 3));
-            __syncwarp(mask);
+                for (int k = 0; k < N; k++)
+                    blk[g * S + k] = (int16_t)(blk[g * S + k] + ((scale * by[g * S + k]) >> 3));
+                __syncwarp(mask);
+            }
+        }
+        const int c = tu.c_idx;
+        const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
+        const int maxv = (1 << f.bd) - 1;
+        uint16_t *t = (uint16_t *)tile.p[c] + (tu.y0 - (cy0 >> vs)) * (2 * tile.pitch[c]) + (tu.x0 - (cx0 >> hs)) + g;
+#pragma unroll 4
+        for (int r = 0; r < N; r++) {
+            uint16_t *d = t + r * 2 * tile.pitch[c];
+            *d = (uint16_t)min(max((int)*d + blk[r * S + g], 0), maxv);
         }
     }
-    const int c = tu.c_idx;
-    const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
-    const int maxv = (1 << f.bd) - 1;
-    uint16_t *t = (uint16_t *)tile.p[c] + (tu.y0 - (cy0 >> vs)) * (2 * tile.pitch[c]) + (tu.x0 - (cx0 >> hs)) + g;
-#pragma unroll 4
-    for (int r = 0; r < N; r++) {
-        uint16_t *d = t + r * 2 * tile.pitch[c];
-        *d = (uint16_t)min(max((int)*d + blk[r * S + g], 0), maxv);
+    if constexpr (MMA) {
+        __syncwarp();
+#pragma unroll 1
+        for (int gi = 0; gi < GROUPS; gi++) {
+            const int sl = gi << LOG2;                                 // lane that holds this block's record
+            if (!__shfl_sync(0xffffffffu, (int)wide, sl)) continue;
+            const int c = __shfl_sync(0xffffffffu, (int)tu.c_idx, sl);
+            const int x0 = __shfl_sync(0xffffffffu, (int)tu.x0, sl), y0 = __shfl_sync(0xffffffffu, (int)tu.y0, sl);
+            const int mode = __shfl_sync(0xffffffffu, (int)tu.mode, sl);
+            const int col_limit = __shfl_sync(0xffffffffu, (int)tu.col_limit, sl);
+            const uint32_t off = __shfl_sync(0xffffffffu, tu.coeff_off, sl);
+            const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
+            uint32_t *tw = tile.p[c] + (y0 - (cy0 >> vs)) * tile.pitch[c] + ((x0 - (cx0 >> hs)) >> 1);
+            if (mode == OHCU_TU_DC) dc_block(LOG2, cs.at(off, 1)[0], tw, tile.pitch[c], f.bd, lane);
+            else idct_mma<LOG2>(cs.csm + (off - cs.clo), (int16_t *)&ws, tw, tile.pitch[c], col_limit, f.bd, lane);
+            __syncwarp();
+        }
     }
 }
 

@@ -22,18 +22,24 @@ for r in rows:
         hdr = r
         ii = hdr.index("Instructions Executed")
         ss = hdr.index("# Samples")
+        stall_cols = [(k, h[6:]) for k, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
         continue
     if hdr and len(r) > 8 and r[0].isdigit():
         try:
-            data.append((int(r[ii]), int(r[ss]), fname, int(r[0]), r[1].strip()[:100]))
+            st = sorted(((int(r[k] or 0), n) for k, n in stall_cols), reverse=True)[:3]
+            data.append((int(r[ii]), int(r[ss]), fname, int(r[0]), r[1].strip()[:70],
+                         " ".join(f"{n}:{v}" for v, n in st if v)))
         except ValueError:
             pass
 tot = sum(d[0] for d in data) or 1
 tots = sum(d[1] for d in data) or 1
 print(f"total warp instructions {tot}, samples {tots}")
 print(" inst%  smpl%  file:line  source")
-for d in sorted(data, reverse=True)[:top]:
-    print(f"{d[0] / tot * 100:5.1f}% {d[1] / tots * 100:5.1f}%  {d[2]}:{d[3]}  {d[4]}")
+by_samples = "--by-samples" in sys.argv
+if by_samples:
+    sys.argv.remove("--by-samples")
+for d in sorted(data, key=lambda d: d[1] if by_samples else d[0], reverse=True)[:top]:
+    print(f"{d[0] / tot * 100:5.1f}% {d[1] / tots * 100:5.1f}%  {d[2]}:{d[3]}  {d[4]}   [{d[5]}]")
 for rng in sys.argv[4:]:
     name, lo, hi = rng.split(":")[0], *map(int, rng.split(":")[1].split("-"))
     ins = sum(d[0] for d in data if lo <= d[3] <= hi and d[2].startswith(name))
