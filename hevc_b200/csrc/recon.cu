@@ -1,6 +1,6 @@
 // recon.cu — fused inter reconstruction of one picture: motion compensation + residual.
 //
-// One CTA (128 threads) owns one CTB.  It builds the CTB's prediction in a shared-memory
+// One CTA (256 threads) owns one CTB.  It builds the CTB's prediction in a shared-memory
 // tile (every inter PU: luma qpel 8-tap / chroma epel 4-tap, uni / bi / weighted), adds the
 // residual of every coded TB of the CTB into the same tile (inverse DCT 4..32 / DC / 4x4
 // DST / transform_skip / rdpcm / cross-component), and writes the CTB to the picture once
@@ -30,8 +30,9 @@
 //    dot-product pipe: IDP.2A does two 16x8-bit MACs per instruction at IMAD issue rate
 //    (profiles/r01_ubench_int_pipes.txt).  Horizontal pairs come straight from the window
 //    words (+ funnel shifts for odd positions), vertical pairs are built with PRMT.
-//  * The pool holds one ROUND of windows (<= 32 KB + one window); a CTB whose windows need
-//    more runs several rounds per (list, luma|chroma) kind.  Cells are sorted by PU, so a
+//  * The pool holds two ROUNDS of windows (22 KB each): while the cells of one round are
+//    filtered, the windows of the next are in flight.  Rounds are cut greedily per
+//    (list, luma|chroma) kind over the PUs in list order.  Cells are sorted by PU, so a
 //    round's cells are a contiguous range of the sorted list and lanes stay packed.
 #include "ohcu_internal.h"
 
@@ -42,9 +43,11 @@ constexpr int RC_THREADS = RC_WARPS * 32;
 constexpr int MAX_CTB_PUS = 128;             // 8x4 PUs of a 64x64 CTB
 constexpr int MAX_CTB_CELLS = 256;           // 4x4 cells of a 64x64 CTB
 constexpr int MAX_CTB_TUS = 768;             // 4x4 TBs of a 64x64 CTB, 3 full-size planes
-constexpr int POOL_ROUND = 32768;            // window bytes per round (before the last window's overhang)
-constexpr int POOL_BYTES = POOL_ROUND + 80 * 72 * 2;
-constexpr int MAX_ROUNDS = 8;                // per kind
+constexpr int POOL_UNIT = 128;               // every TMA box is a multiple of 128 bytes
+constexpr int HALF_UNITS = 180;              // one round of windows: 22.5 KB = the largest window pair (4:4:4 chroma, 2 x 80 x 72 x 2)
+constexpr int HALF_BYTES = HALF_UNITS * POOL_UNIT;
+constexpr int POOL_BYTES = 2 * HALF_BYTES;   // two rounds: one being filtered, one in flight
+constexpr int MAX_ROUNDS = 8;                // per kind (5 in the worst case: 128 8x4 PUs)
 constexpr int N_KINDS = 4;                   // list slot A luma, slot B luma, slot A chroma, slot B chroma
 
 // scratch of one warp in the residual phase (aliases the window pool): one 32x32 int16 block
@@ -795,14 +798,14 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     int *cumB = (int *)sp;                      sp += MAX_CTB_PUS + 4;
     uint16_t *listA = (uint16_t *)sp;           sp += MAX_CTB_CELLS / 2;
     uint16_t *listB = (uint16_t *)sp;           sp += MAX_CTB_CELLS / 2;
-    int *rnd_pu = (int *)sp;                    sp += N_KINDS * MAX_ROUNDS;      // first PU of each round
-    int *rnd_cell = (int *)sp;                  sp += N_KINDS * MAX_ROUNDS;      // first sorted cell of each round
-    int *rnd_bytes = (int *)sp;                 sp += N_KINDS * MAX_ROUNDS;      // TMA bytes of each round
-    int *scan_tmp = (int *)sp;                  sp += 6 * RC_WARPS + 8;          // warp totals, then [24..29] totals
+    uint16_t *cumW = (uint16_t *)sp;            sp += N_KINDS * (MAX_CTB_PUS + 2) / 2;   // [kind][PU] window units before this PU
+    uint8_t *nxt = (uint8_t *)sp;               sp += N_KINDS * MAX_CTB_PUS / 4;         // [kind][PU] first PU of the round after one starting here
+    uint8_t *rstart = (uint8_t *)sp;            sp += N_KINDS * (MAX_ROUNDS + 4) / 4;    // [kind][round] first PU, [kind][MAX_ROUNDS + 1] = count
+    int *scan_tmp = (int *)sp;                  sp += 2 * 4 * RC_WARPS;                  // [cells | units][class][warp]
     int *tu_cnt = (int *)sp;                    sp += 16;                         // [0..3] counts, [4..7] bases, [8..11] cursors, [12] coef lo, [13] coef hi, [14] batch counter
     uint16_t *tu_list = (uint16_t *)sp;         sp += MAX_CTB_TUS / 2;
     uint32_t *issue = sp;                       sp += N_KINDS * MAX_CTB_PUS * 2;  // TMA parameters per (kind, PU)
-    uint64_t *mbar = (uint64_t *)(((uintptr_t)sp + 7) & ~(uintptr_t)7);           sp += 4;
+    uint64_t *mbar = (uint64_t *)(((uintptr_t)sp + 7) & ~(uintptr_t)7);           sp += 6;     // one per pool half
     WarpScratch *scratch2 = f.cfi == 3 ? (WarpScratch *)(((uintptr_t)sp + 15) & ~(uintptr_t)15) : nullptr;   // cross-component
 
     const int2 prange = f.ctb_pu_range[ctb];
@@ -835,248 +838,278 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     }
     if (tid < 12) tu_cnt[tid] = 0;
     if (tid == 12) { tu_cnt[12] = 0x7fffffff; tu_cnt[13] = 0; tu_cnt[14] = 0; }
-    if (tid < N_KINDS * MAX_ROUNDS) { rnd_pu[tid] = MAX_CTB_PUS; rnd_cell[tid] = MAX_CTB_CELLS; rnd_bytes[tid] = 0; }
-    if (tid == 0) mbar_init(mbar, 1);
+    if (tid == 0) { mbar_init(mbar, 1); mbar_init(mbar + 1, 1); }
     __syncthreads();
 
     // ---- TBs of the CTB sorted by size (counting sort) and the arena range their coefficients
-    //      occupy; done first so that its global-memory latency overlaps the prediction
-    if (nt > 0) {
-        for (int i = tid; i < nt; i += RC_THREADS) {
-            const ohcu_tu *tu = f.tus + t0 + i;
-            const int l2 = tu->log2_size;
-            const uint32_t off = tu->coeff_off;
-            atomicAdd(&tu_cnt[l2 - 2], 1);
-            atomicMin(&tu_cnt[12], (int)off);
-            atomicMax(&tu_cnt[13], (int)(off + (1u << (2 * l2))));
+    //      occupy; runs while the first round of windows is in flight
+    auto sort_tus = [&]() {
+        if (nt > 0) {
+            for (int i = tid; i < nt; i += RC_THREADS) {
+                const ohcu_tu *tu = f.tus + t0 + i;
+                const int l2 = tu->log2_size;
+                const uint32_t off = tu->coeff_off;
+                atomicAdd(&tu_cnt[l2 - 2], 1);
+                atomicMin(&tu_cnt[12], (int)off);
+                atomicMax(&tu_cnt[13], (int)(off + (1u << (2 * l2))));
+            }
+            __syncthreads();
+            if (tid == 0) {
+                int acc = 0;                               // largest first: 32x32 batches are the long ones
+                for (int l = 3; l >= 0; l--) { tu_cnt[4 + l] = acc; acc += tu_cnt[l]; }
+            }
+            __syncthreads();
+            for (int i = tid; i < nt; i += RC_THREADS) {
+                const int l = f.tus[t0 + i].log2_size - 2;
+                tu_list[tu_cnt[4 + l] + atomicAdd(&tu_cnt[8 + l], 1)] = (uint16_t)i;
+            }
         }
-        __syncthreads();
-        if (tid == 0) {
-            int acc = 0;                                   // largest first: 32x32 batches are the long ones
-            for (int l = 3; l >= 0; l--) { tu_cnt[4 + l] = acc; acc += tu_cnt[l]; }
-        }
-        __syncthreads();
-        for (int i = tid; i < nt; i += RC_THREADS) {
-            const int l = f.tus[t0 + i].log2_size - 2;
-            tu_list[tu_cnt[4 + l] + atomicAdd(&tu_cnt[8 + l], 1)] = (uint16_t)i;
-        }
-    }
+    };
 
-    uint32_t parity = 0;                                   // phase of the (single) mbarrier
+    uint32_t par0 = 0, par1 = 0;                           // phases of the two mbarriers
     // ================================================================ phase 1: prediction
     if (do_mc) {
-        // ---- 1a. the thread that owns PU `tid` prepares its record
-        int v[6] = {0, 0, 0, 0, 0, 0};                 // cells A, cells B, bytes of the four kinds
-        uint32_t gw[2][2] = {{0, 0}, {0, 0}};
-        bool bi = false;
-        if (tid < np) {
-            const ohcu_pu pu = load_pu(f.pus + p0 + tid);
-            const ohcu_slice_tab &sl = f.slices[pu.slice];
-            bi = pu.pred_flag == OHCU_PF_BI;
-            const int ncell = (pu.w >> 2) * (pu.h >> 2);
-            v[0] = ncell;
-            v[1] = bi ? ncell : 0;
-            PuRec &rc = recs[tid];
-            rc.rect = (uint32_t)(((pu.x0 - cx0) >> 2) | (((pu.y0 - cy0) >> 2) << 4) | ((pu.w >> 2) << 8) | ((pu.h >> 2) << 13) |
-                                 ((bi ? 1 : 0) << 18));
-            const int lA = (pu.pred_flag & 1) ? 0 : 1;
-#pragma unroll
-            for (int s = 0; s < 2; s++) {
-                if (s == 1 && !bi) continue;
-                const int l = s ? 1 : lA;
-#pragma unroll
-                for (int pt = 0; pt < 2; pt++) {
-                    if (pt == 1 && f.nplanes != 3) continue;
-                    const WinGeom g = win_geom<HIGH>(f, pu, l, pt == 0);
-                    const int pitch = box_w(HIGH, g.wcls) * (HIGH ? 2 : 1);
-                    v[2 + 2 * pt + s] = pitch * box_h(g.hcls) * (pt ? 2 : 1);
-                    // what the TMA issue of this window needs (box of plane pt; Cr follows Cb)
-                    const int slot = sl.ref_slot[l][pu.ref_idx[l] & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1);
-                    uint32_t *iw = issue + ((2 * pt + s) * MAX_CTB_PUS + tid) * 2;
-                    iw[0] = (uint32_t)tmap_index(slot, pt, g.wcls, g.hcls) | ((uint32_t)(g.ax + PAD_X) << 12);
-                    iw[1] = (uint32_t)(g.y0 + PAD_Y) | ((uint32_t)((pitch * box_h(g.hcls)) >> 7) << 16);
-                    gw[s][pt] = ((uint32_t)(pitch >> 4) << 12) | ((uint32_t)g.offx << 16) | ((uint32_t)g.mx << 20) |
-                                ((uint32_t)g.my << 23) | ((uint32_t)g.hcls << 26);
-                }
-            }
-            // epilogue constants per plane (see Epi)
-            const bool wflag = sl.weight_flag != 0;
-#pragma unroll
-            for (int c = 0; c < 3; c++) {
-                const int denom = c ? sl.chroma_log2_weight_denom : sl.luma_log2_weight_denom;
-                int wx[2], ox[2];
-#pragma unroll
-                for (int l = 0; l < 2; l++) {
-                    const int ri = pu.ref_idx[l] & (OHCU_MAX_REFS - 1);
-                    wx[l] = c ? sl.chroma_weight[l][ri][c - 1] : sl.luma_weight[l][ri];
-                    ox[l] = (c ? sl.chroma_offset[l][ri][c - 1] : sl.luma_offset[l][ri]) * (1 << (bd - 8));
-                }
-                int wA, wB = 0, add, sh, post = 0;
-                if (!bi) {
-                    if (!wflag) { wA = 1; sh = 14 - bd; add = 1 << (13 - bd); }
-                    else { wA = wx[lA]; sh = denom + 14 - bd; add = 1 << (sh - 1); post = ox[lA]; }
-                } else {
-                    if (!wflag) { wA = 1; wB = 1; sh = 15 - bd; add = 1 << (14 - bd); }
-                    else {
-                        const int log2Wd = denom + 14 - bd;
-                        wA = wx[1]; wB = wx[0]; sh = log2Wd + 1; add = (ox[0] + ox[1] + 1) * (1 << log2Wd);
+        // ---- 1a. four threads per PU: thread `sub` prepares the window of kind `sub` (list slot
+        //      sub & 1, luma / chroma sub >> 1) and the epilogue constants of plane `sub`;
+        //      64 PUs per pass.  Class scans (stride-4 lanes) give, per kind, the window units
+        //      before each PU and, per list slot, the cells before each PU.
+        const int sub = tid & 3;
+        int carryW = 0, carryC = 0;
+#pragma unroll 1
+        for (int base = 0; base < np; base += RC_THREADS / 4) {
+            const int p = base + (tid >> 2);
+            int wu = 0, cc = 0;
+            if (p < np) {
+                const ohcu_pu pu = load_pu(f.pus + p0 + p);
+                const ohcu_slice_tab &sl = f.slices[pu.slice];
+                const bool bi = pu.pred_flag == OHCU_PF_BI;
+                const int ncell = (pu.w >> 2) * (pu.h >> 2);
+                PuRec &rc = recs[p];
+                const int lA = (pu.pred_flag & 1) ? 0 : 1;
+                if (sub == 0)
+                    rc.rect = (uint32_t)(((pu.x0 - cx0) >> 2) | (((pu.y0 - cy0) >> 2) << 4) | ((pu.w >> 2) << 8) |
+                                         ((pu.h >> 2) << 13) | ((bi ? 1 : 0) << 18));
+                cc = sub == 0 ? ncell : (sub == 1 && bi ? ncell : 0);
+                {
+                    const int s = sub & 1, pt = sub >> 1;
+                    uint32_t gw = 0;
+                    if ((s == 0 || bi) && (pt == 0 || f.nplanes == 3)) {
+                        const int l = s ? 1 : lA;
+                        const WinGeom g = win_geom<HIGH>(f, pu, l, pt == 0);
+                        const int pitch = box_w(HIGH, g.wcls) * (HIGH ? 2 : 1);
+                        const int bytes = pitch * box_h(g.hcls);
+                        wu = (bytes * (pt ? 2 : 1)) / POOL_UNIT;
+                        // what the TMA issue of this window needs (box of plane pt; Cr follows Cb)
+                        const int slot = sl.ref_slot[l][pu.ref_idx[l] & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1);
+                        uint32_t *iw = issue + (sub * MAX_CTB_PUS + p) * 2;
+                        iw[0] = (uint32_t)tmap_index(slot, pt, g.wcls, g.hcls) | ((uint32_t)(g.ax + PAD_X) << 12);
+                        iw[1] = (uint32_t)(g.y0 + PAD_Y) | ((uint32_t)(bytes >> 7) << 16);
+                        gw = ((uint32_t)(pitch >> 4) << 12) | ((uint32_t)g.offx << 16) | ((uint32_t)g.mx << 20) |
+                             ((uint32_t)g.my << 23) | ((uint32_t)g.hcls << 26);
                     }
+                    rc.geom[s][pt] = gw;
                 }
-                rc.epi[c][0] = ((uint32_t)wA & 0xffffu) | ((uint32_t)wB << 16);
-                rc.epi[c][1] = (uint32_t)add;
-                rc.epi[c][2] = ((uint32_t)sh & 0xffffu) | ((uint32_t)post << 16);
+                if (sub < 3) {                                 // epilogue constants of plane `sub` (see Epi)
+                    const int c = sub;
+                    const bool wflag = sl.weight_flag != 0;
+                    const int denom = c ? sl.chroma_log2_weight_denom : sl.luma_log2_weight_denom;
+                    int wx[2], ox[2];
+#pragma unroll
+                    for (int l = 0; l < 2; l++) {
+                        const int ri = pu.ref_idx[l] & (OHCU_MAX_REFS - 1);
+                        wx[l] = c ? sl.chroma_weight[l][ri][c - 1] : sl.luma_weight[l][ri];
+                        ox[l] = (c ? sl.chroma_offset[l][ri][c - 1] : sl.luma_offset[l][ri]) * (1 << (bd - 8));
+                    }
+                    int wA, wB = 0, add, sh, post = 0;
+                    if (!bi) {
+                        if (!wflag) { wA = 1; sh = 14 - bd; add = 1 << (13 - bd); }
+                        else { wA = wx[lA]; sh = denom + 14 - bd; add = 1 << (sh - 1); post = ox[lA]; }
+                    } else {
+                        if (!wflag) { wA = 1; wB = 1; sh = 15 - bd; add = 1 << (14 - bd); }
+                        else {
+                            const int log2Wd = denom + 14 - bd;
+                            wA = wx[1]; wB = wx[0]; sh = log2Wd + 1; add = (ox[0] + ox[1] + 1) * (1 << log2Wd);
+                        }
+                    }
+                    rc.epi[c][0] = ((uint32_t)wA & 0xffffu) | ((uint32_t)wB << 16);
+                    rc.epi[c][1] = (uint32_t)add;
+                    rc.epi[c][2] = ((uint32_t)sh & 0xffffu) | ((uint32_t)post << 16);
+                }
             }
-        }
-        // ---- 1b. exclusive scans over the PUs: sorted-cell positions and pool offsets
-        int excl[6];
+            // class scans inside the warp (lanes of one class are 4 apart), then across warps
+            int iw_ = wu, ic_ = cc;
 #pragma unroll
-        for (int q = 0; q < 6; q++) {
-            int x = v[q];
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const int y = __shfl_up_sync(0xffffffffu, x, d);
-                if (lane >= d) x += y;
+            for (int d = 4; d < 32; d <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, iw_, d), z = __shfl_up_sync(0xffffffffu, ic_, d);
+                if (lane >= d) { iw_ += y; ic_ += z; }
             }
-            excl[q] = x - v[q];
-            if (lane == 31) scan_tmp[q * RC_WARPS + warp] = x;
-        }
-        __syncthreads();
-#pragma unroll
-        for (int q = 0; q < 6; q++) {
-            int before = 0, total = 0;
+            if (lane >= 28) { scan_tmp[sub * RC_WARPS + warp] = ic_; scan_tmp[(4 + sub) * RC_WARPS + warp] = iw_; }
+            __syncthreads();
+            int beforeC = 0, totalC = 0, beforeW = 0, totalW = 0;
 #pragma unroll
             for (int w = 0; w < RC_WARPS; w++) {
-                const int t = scan_tmp[q * RC_WARPS + w];
-                if (w < warp) before += t;
-                total += t;
+                const int a = scan_tmp[sub * RC_WARPS + w], b = scan_tmp[(4 + sub) * RC_WARPS + w];
+                if (w < warp) { beforeC += a; beforeW += b; }
+                totalC += a; totalW += b;
             }
-            excl[q] += before;
-            if (tid == 0) scan_tmp[6 * RC_WARPS + q] = total;
+            if (p < np) {
+                cumW[sub * (MAX_CTB_PUS + 2) + p] = (uint16_t)(carryW + beforeW + iw_ - wu);
+                if (sub == 0) cumA[p] = carryC + beforeC + ic_ - cc;
+                if (sub == 1) cumB[p] = carryC + beforeC + ic_ - cc;
+            }
+            carryW += totalW; carryC += totalC;
+            __syncthreads();                               // scan_tmp is reused by the next pass
         }
-        if (tid < np) {
-            cumA[tid] = excl[0];
-            cumB[tid] = excl[1];
-            PuRec &rc = recs[tid];
-#pragma unroll
-            for (int k = 0; k < N_KINDS; k++) {
-                const int s = k & 1, pt = k >> 1;
-                const int bytes = v[2 + k];
-                uint32_t g = gw[s][pt];
-                if (bytes > 0) {
-                    const int r = excl[2 + k] >> 15;
-                    if (r < MAX_ROUNDS) {
-                        g |= (uint32_t)((excl[2 + k] - (r << 15)) >> 4);
-                        atomicMin(&rnd_pu[k * MAX_ROUNDS + r], tid);
-                        atomicMin(&rnd_cell[k * MAX_ROUNDS + r], excl[s]);
-                        atomicAdd(&rnd_bytes[k * MAX_ROUNDS + r], bytes);
-                    }
-                }
-                rc.geom[s][pt] = g;
-            }
+        if (tid < 4) {
+            cumW[tid * (MAX_CTB_PUS + 2) + np] = (uint16_t)carryW;
+            if (tid == 0) cumA[np] = carryC;
+            if (tid == 1) cumB[np] = carryC;
         }
         __syncthreads();
-        const int totA = scan_tmp[6 * RC_WARPS + 0], totB = scan_tmp[6 * RC_WARPS + 1];
-        if (tid == 0) { cumA[np] = totA; cumB[np] = totB; }
-        // ---- 1c. cells sorted by PU: entry = PU | cell column << 7 | cell row << 11
+        const int totA = cumA[np], totB = cumB[np];
+
+        // ---- 1b. greedy rounds: nxt[kind][p] = first PU that no longer fits a round starting at p
+        const int nkinds = f.nplanes == 3 ? N_KINDS : 2;
+        for (int i = tid; i < nkinds * np; i += RC_THREADS) {
+            const int k = i / np, p = i - k * np;
+            const uint16_t *cw = cumW + k * (MAX_CTB_PUS + 2);
+            const int target = cw[p] + HALF_UNITS;
+            int lo = p + 1, hi = np;                       // largest e with cw[e] <= target (every window fits: e > p)
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (cw[mid] <= target) lo = mid; else hi = mid - 1;
+            }
+            nxt[k * MAX_CTB_PUS + p] = (uint8_t)lo;
+        }
+        __syncthreads();
+        // one thread per kind walks its rounds; the others build the cell lists meanwhile
+        if (tid < nkinds) {
+            const int k = tid;
+            uint8_t *rs = rstart + k * (MAX_ROUNDS + 4);
+            int n = 0;
+            if (cumW[k * (MAX_CTB_PUS + 2) + np] > 0)
+                for (int s = 0; s < np && n < MAX_ROUNDS; s = nxt[k * MAX_CTB_PUS + s]) rs[n++] = (uint8_t)s;
+            rs[n] = (uint8_t)np;
+            rs[MAX_ROUNDS + 1] = (uint8_t)n;
+        } else if (tid >= 32) {
+            // ---- 1c. cells sorted by PU: entry = PU | cell column << 7 | cell row << 11
 #pragma unroll 1
-        for (int s = 0; s < 2; s++) {
-            const int *cum = s ? cumB : cumA;
-            uint16_t *list = s ? listB : listA;
-            const int tot = min(s ? totB : totA, MAX_CTB_CELLS);
-            for (int i = tid; i < tot; i += RC_THREADS) {
-                int lo = 0, hi = np - 1;                   // largest p with cum[p] <= i
-                while (lo < hi) {
-                    const int mid = (lo + hi + 1) >> 1;
-                    if (cum[mid] <= i) lo = mid; else hi = mid - 1;
+            for (int s = 0; s < 2; s++) {
+                const int *cum = s ? cumB : cumA;
+                uint16_t *list = s ? listB : listA;
+                const int tot = min(s ? totB : totA, MAX_CTB_CELLS);
+                for (int i = tid - 32; i < tot; i += RC_THREADS - 32) {
+                    int lo = 0, hi = np - 1;               // largest p with cum[p] <= i
+                    while (lo < hi) {
+                        const int mid = (lo + hi + 1) >> 1;
+                        if (cum[mid] <= i) lo = mid; else hi = mid - 1;
+                    }
+                    const int local = i - cum[lo];
+                    const int nx = (recs[lo].rect >> 8) & 31;
+                    const int cy = fastdiv(local, fastinv(nx)), cx = local - cy * nx;
+                    list[i] = (uint16_t)(lo | (cx << 7) | (cy << 11));
                 }
-                const int local = i - cum[lo];
-                const int nx = (recs[lo].rect >> 8) & 31;
-                const int cy = fastdiv(local, fastinv(nx)), cx = local - cy * nx;
-                list[i] = (uint16_t)(lo | (cx << 7) | (cy << 11));
             }
         }
         __syncthreads();
 
-        // ---- 1d. rounds: TMA the windows of a run of PUs into the pool, then one cell per thread
+        // ---- 1d. rounds, double buffered: the windows of round i + 1 fly while round i is filtered
         const int sh1 = bd - 8;                            // first-stage shift (template :2486)
-        const int nkinds = f.nplanes == 3 ? N_KINDS : 2;
-#pragma unroll 1
-        for (int k = 0; k < nkinds; k++) {
-            const int s = k & 1, pt = k >> 1;
-            // rounds of this kind: a round exists iff some window STARTS in its 32 KB slice
-            int nr = 0;
-            while (nr < MAX_ROUNDS && rnd_bytes[k * MAX_ROUNDS + nr] > 0) nr++;
-            const uint16_t *list = s ? listB : listA;
-            const int ncells = min(s ? totB : totA, MAX_CTB_CELLS);
-#pragma unroll 1
-            for (int r = 0; r < nr; r++) {
-                __syncthreads();                           // everyone is done with the pool's previous content
-                const int pa = rnd_pu[k * MAX_ROUNDS + r];
-                const int pb = r + 1 < nr ? min(rnd_pu[k * MAX_ROUNDS + r + 1], np) : np;
-                if (tid == 0) mbar_expect_tx(mbar, (uint32_t)rnd_bytes[k * MAX_ROUNDS + r]);
-                if (pa + tid < pb) {
-                    const int p = pa + tid;
-                    const uint32_t *iw = issue + (k * MAX_CTB_PUS + p) * 2;
+        int nrk[N_KINDS], R = 0;
+#pragma unroll
+        for (int k = 0; k < N_KINDS; k++) { nrk[k] = k < nkinds ? rstart[k * (MAX_ROUNDS + 4) + MAX_ROUNDS + 1] : 0; R += nrk[k]; }
+        // flat round index -> (kind, round of the kind)
+        auto locate = [&](int i, int &k, int &r) {
+            k = 0; r = i;
+#pragma unroll
+            for (int q = 0; q < N_KINDS - 1; q++)
+                if (k == q && r >= nrk[q]) { r -= nrk[q]; k = q + 1; }
+        };
+        auto issue_round = [&](int i) {
+            int k, r;
+            locate(i, k, r);
+            const uint8_t *rs = rstart + k * (MAX_ROUNDS + 4);
+            const int pa = rs[r], pb = rs[r + 1];
+            const uint16_t *cw = cumW + k * (MAX_CTB_PUS + 2);
+            uint64_t *bar = mbar + (i & 1);
+            uint8_t *buf = pool + (i & 1) * HALF_BYTES;
+            if (tid == 0) mbar_expect_tx(bar, (uint32_t)(cw[pb] - cw[pa]) * POOL_UNIT);
+            for (int p = pa + tid; p < pb; p += RC_THREADS) {
+                const uint32_t *iw = issue + (k * MAX_CTB_PUS + p) * 2;
+                const int units = cw[p + 1] - cw[p];
+                if (units > 0) {
                     const uint32_t w0 = iw[0], w1 = iw[1];
                     const int bytes = (int)(w1 >> 16) << 7;
-                    if ((s == 0 || ((recs[p].rect >> 18) & 1)) && bytes > 0) {
-                        uint8_t *dst = pool + (recs[p].geom[s][pt] & 0xfffu) * 16;
-                        const CUtensorMap *m = f.tmaps + (w0 & 0xfffu);
-                        const int x = (int)(w0 >> 12), y = (int)(w1 & 0xffffu);
-                        tma_load_2d(dst, m, x, y, mbar);
-                        if (pt == 1) {
-                            tma_load_2d(dst + bytes, m + N_WCLS * N_HCLS, x, y, mbar);
-                        }
-                    }
+                    uint8_t *dst = buf + (cw[p] - cw[pa]) * POOL_UNIT;
+                    const CUtensorMap *m = f.tmaps + (w0 & 0xfffu);
+                    const int x = (int)(w0 >> 12), y = (int)(w1 & 0xffffu);
+                    tma_load_2d(dst, m, x, y, bar);
+                    if (k >> 1) tma_load_2d(dst + bytes, m + N_WCLS * N_HCLS, x, y, bar);
                 }
-                mbar_wait(mbar, parity);
-                parity ^= 1;
-
-                const int clo = rnd_cell[k * MAX_ROUNDS + r];
-                const int chi = r + 1 < nr ? rnd_cell[k * MAX_ROUNDS + r + 1] : ncells;
+            }
+        };
+        if (R > 0) issue_round(0);
+        sort_tus();
 #pragma unroll 1
-                for (int ci = clo + tid; ci < chi; ci += RC_THREADS) {
-                    const int ent = list[ci];
-                    const int p = ent & 127, cx = (ent >> 7) & 15, cy = ent >> 11;
-                    const PuRec &rc = recs[p];
-                    const uint32_t rect = rc.rect;
-                    const int x4 = rect & 15, y4 = (rect >> 4) & 15;
-                    const bool pbi = (rect >> 18) & 1;
-                    const uint32_t gword = rc.geom[s][pt];
-                    const uint8_t *win = pool + (gword & 0xfffu) * 16;
-                    const int pitch = ((gword >> 12) & 15) * 16, offx = (gword >> 16) & 15;
-                    const int mx = (gword >> 20) & 7, my = (gword >> 23) & 7;
-                    Epi e;
-                    if (pt == 0) {
-                        const uint32_t ew[3] = {rc.epi[0][0], rc.epi[0][1], rc.epi[0][2]};
+        for (int i = 0; i < R; i++) {
+            __syncthreads();                               // round i - 1 is done with the other half
+            if (i + 1 < R) issue_round(i + 1);
+            int k, r;
+            locate(i, k, r);
+            const int s = k & 1, pt = k >> 1;
+            const uint8_t *rs = rstart + k * (MAX_ROUNDS + 4);
+            const int pa = rs[r], pb = rs[r + 1];
+            const uint16_t *cw = cumW + k * (MAX_CTB_PUS + 2);
+            const uint8_t *buf = pool + (i & 1) * HALF_BYTES - cw[pa] * POOL_UNIT;
+            const uint16_t *list = s ? listB : listA;
+            const int *cum = s ? cumB : cumA;
+            const int clo = cum[pa], chi = min(cum[pb], MAX_CTB_CELLS);
+            mbar_wait(mbar + (i & 1), (i & 1) ? par1 : par0);
+            if (i & 1) par1 ^= 1; else par0 ^= 1;
+#pragma unroll 1
+            for (int ci = clo + tid; ci < chi; ci += RC_THREADS) {
+                const int ent = list[ci];
+                const int p = ent & 127, cx = (ent >> 7) & 15, cy = ent >> 11;
+                const PuRec &rc = recs[p];
+                const uint32_t rect = rc.rect;
+                const int x4 = rect & 15, y4 = (rect >> 4) & 15;
+                const bool pbi = (rect >> 18) & 1;
+                const uint32_t gword = rc.geom[s][pt];
+                const uint8_t *win = buf + cw[p] * POOL_UNIT;
+                const int pitch = ((gword >> 12) & 15) * 16, offx = (gword >> 16) & 15;
+                const int mx = (gword >> 20) & 7, my = (gword >> 23) & 7;
+                Epi e;
+                if (pt == 0) {
+                    const uint32_t ew[3] = {rc.epi[0][0], rc.epi[0][1], rc.epi[0][2]};
+                    unpack_epi(ew, bd, pbi, pbi && s == 0, e);
+                    uint32_t *tp = tile.p[0] + ((y4 + cy) * 4) * tile.pitch[0] + ((x4 + cx) * 2);
+                    mc_cell<HIGH, 8, 4, 4>(win, pitch, offx + cx * 4, cy * 4, c_qpel4[mx][0], c_qpel4[mx][1], c_qpel4[my][0],
+                                           c_qpel4[my][1], sh1, e, tp, tile.pitch[0]);
+                } else {
+                    const int hs = f.hs, vs = f.vs;
+                    const int cw_ = 4 >> hs, ch = 4 >> vs;
+                    const int bytes = pitch * box_h((gword >> 26) & 7);
+#pragma unroll 1
+                    for (int c = 1; c < 3; c++) {
+                        const uint32_t ew[3] = {rc.epi[c][0], rc.epi[c][1], rc.epi[c][2]};
                         unpack_epi(ew, bd, pbi, pbi && s == 0, e);
-                        uint32_t *tp = tile.p[0] + ((y4 + cy) * 4) * tile.pitch[0] + ((x4 + cx) * 2);
-                        mc_cell<HIGH, 8, 4, 4>(win, pitch, offx + cx * 4, cy * 4, c_qpel4[mx][0], c_qpel4[mx][1], c_qpel4[my][0],
-                                               c_qpel4[my][1], sh1, e, tp, tile.pitch[0]);
-                    } else {
-                        const int hs = f.hs, vs = f.vs;
-                        const int cw = 4 >> hs, ch = 4 >> vs;
-                        const int bytes = pitch * box_h((gword >> 26) & 7);
-#pragma unroll 1
-                        for (int c = 1; c < 3; c++) {
-                            const uint32_t ew[3] = {rc.epi[c][0], rc.epi[c][1], rc.epi[c][2]};
-                            unpack_epi(ew, bd, pbi, pbi && s == 0, e);
-                            uint32_t *tp = tile.p[c] + ((y4 + cy) * ch) * tile.pitch[c] + (((x4 + cx) * cw) >> 1);
-                            const uint8_t *wc = win + (c - 1) * bytes;
-                            if (hs && vs)
-                                mc_cell<HIGH, 4, 2, 2>(wc, pitch, offx + cx * 2, cy * 2, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
-                                                       tp, tile.pitch[c]);
-                            else if (hs)
-                                mc_cell<HIGH, 4, 2, 4>(wc, pitch, offx + cx * 2, cy * 4, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
-                                                       tp, tile.pitch[c]);
-                            else
-                                mc_cell<HIGH, 4, 4, 4>(wc, pitch, offx + cx * 4, cy * 4, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
-                                                       tp, tile.pitch[c]);
-                        }
+                        uint32_t *tp = tile.p[c] + ((y4 + cy) * ch) * tile.pitch[c] + (((x4 + cx) * cw_) >> 1);
+                        const uint8_t *wc = win + (c - 1) * bytes;
+                        if (hs && vs)
+                            mc_cell<HIGH, 4, 2, 2>(wc, pitch, offx + cx * 2, cy * 2, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
+                                                   tp, tile.pitch[c]);
+                        else if (hs)
+                            mc_cell<HIGH, 4, 2, 4>(wc, pitch, offx + cx * 2, cy * 4, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
+                                                   tp, tile.pitch[c]);
+                        else
+                            mc_cell<HIGH, 4, 4, 4>(wc, pitch, offx + cx * 4, cy * 4, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
+                                                   tp, tile.pitch[c]);
                     }
                 }
             }
         }
+    } else {
+        sort_tus();
     }
 
     // ================================================================ phase 2: residual
@@ -1095,7 +1128,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                 asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                              ::"r"(smem_u32(coef_sm)), "l"(f.coeffs + clo), "r"(cbytes), "r"(smem_u32(mbar)) : "memory");
             }
-            mbar_wait(mbar, parity);
+            mbar_wait(mbar, par0);
         }
         CoefSrc cs;
         cs.csm = staged ? coef_sm : nullptr; cs.clo = clo; cs.chi = chi; cs.glob = f.coeffs;
@@ -1143,8 +1176,9 @@ size_t recon_smem_bytes(const FrameDev &f)
         const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
         words += (size_t)(((cs >> hs) >> 1) + 2) * (cs >> vs);
     }
-    words += MAX_CTB_PUS * (sizeof(PuRec) / 4) + 2 * (MAX_CTB_PUS + 4) + MAX_CTB_CELLS + 3 * N_KINDS * MAX_ROUNDS +
-             6 * RC_WARPS + 8 + 16 + MAX_CTB_TUS / 2 + N_KINDS * MAX_CTB_PUS * 2 + 8;
+    words += MAX_CTB_PUS * (sizeof(PuRec) / 4) + 2 * (MAX_CTB_PUS + 4) + MAX_CTB_CELLS + N_KINDS * (MAX_CTB_PUS + 2) / 2 +
+             N_KINDS * MAX_CTB_PUS / 4 + N_KINDS * (MAX_ROUNDS + 4) / 4 + 2 * 4 * RC_WARPS + 16 + MAX_CTB_TUS / 2 +
+             N_KINDS * MAX_CTB_PUS * 2 + 8;
     return POOL_BYTES + words * 4 + (f.cfi == 3 ? RC_WARPS * sizeof(WarpScratch) + 16 : 0);
 }
 
