@@ -173,25 +173,16 @@ __device__ __forceinline__ void fir_col(const uint32_t (&V)[R + NT - 1], uint32_
 //   uni_w   (template :2733)  wA wx         add 1<<(shift-1)          sh shift      post ox
 //   bi      (template :2570)  wA 1   wB 1   add 1<<(14-BD)            sh 15-BD      post 0
 //   bi_w    (template :2760)  wA wx1 wB wx0 add (ox0+ox1+1)<<log2Wd   sh log2Wd+1   post 0
-// store_tmp: the first list of a bi PU parks its intermediate in the tile (the reference's
-// lc->tmp, hevcdec.c:1854), the second list picks it up.
 struct Epi {
     int wA, wB, add, sh, post, maxv;
-    bool store_tmp, bi;
 };
 
-__device__ __forceinline__ void epi_pair(const Epi &e, int va, int vb, uint32_t *tw)
+// val / tmp: two 14-bit intermediates each (int16 pairs); tmp = first list of a bi PU (the
+// reference's lc->tmp, hevcdec.c:1854), 0 otherwise
+__device__ __forceinline__ void epi_pair(const Epi &e, uint32_t val, uint32_t tmp, uint32_t *tw)
 {
-    if (e.store_tmp) {
-        *tw = __byte_perm((uint32_t)va, (uint32_t)vb, 0x5410);
-        return;
-    }
-    int ta = 0, tb = 0;
-    if (e.bi) {
-        const uint32_t t = *tw;
-        ta = (int)(int16_t)(t & 0xffffu);
-        tb = (int)t >> 16;
-    }
+    const int va = (int)(int16_t)(val & 0xffffu), vb = (int)val >> 16;
+    const int ta = (int)(int16_t)(tmp & 0xffffu), tb = (int)tmp >> 16;
     int oa = ((va * e.wA + ta * e.wB + e.add) >> e.sh) + e.post;
     int ob = ((vb * e.wA + tb * e.wB + e.add) >> e.sh) + e.post;
     oa = min(max(oa, 0), e.maxv);
@@ -699,12 +690,13 @@ __device__ __forceinline__ int box_bytes(bool high, int wcls, int hcls) { return
 // ---------------------------------------------------------------- one cell
 // OW x OH output samples of one plane from the window at `win` (row pitch in bytes):
 // horizontal pass over OH + NT - 1 rows into packed int16 registers (the reference's
-// tmp_array, template :2522), vertical pass, epilogue into the CTB tile.
+// tmp_array, template :2522), vertical pass; res[r][k] = the 14-bit intermediates of output
+// row r, columns 2k and 2k + 1 as an int16 pair.
 //   col0  first output column of the cell relative to the window's first needed column
 //   row0  first output row of the cell relative to the window's first row
 template <bool HIGH, int NT, int OW, int OH>
-__device__ __forceinline__ void mc_cell(const uint8_t *win, int pitch, int col0, int row0, uint32_t FX0, uint32_t FX1,
-                                        uint32_t FY0, uint32_t FY1, int sh1, const Epi &e, uint32_t *tw, int tpitch)
+__device__ __forceinline__ void mc_filter(const uint8_t *win, int pitch, int col0, int row0, uint32_t FX0, uint32_t FX1,
+                                          uint32_t FY0, uint32_t FY1, int sh1, uint32_t (&res)[OH][OW / 2])
 {
     constexpr int NW = (OW + NT) / 2, NR = OH + NT - 1;
     uint32_t hb[NR][OW / 2];
@@ -749,12 +741,47 @@ __device__ __forceinline__ void mc_cell(const uint8_t *win, int pitch, int col0,
         int oa[OH], ob[OH];
         fir_col<NT, OH>(V, FY0, FY1, oa, ob);
 #pragma unroll
-        for (int r = 0; r < OH; r++) epi_pair(e, oa[r] >> 6, ob[r] >> 6, tw + r * tpitch + k);
+        for (int r = 0; r < OH; r++) res[r][k] = __byte_perm((uint32_t)(oa[r] >> 6), (uint32_t)(ob[r] >> 6), 0x5410);
     }
 }
 
+// One cell of one plane: list slot A, then (bi) slot B, then the epilogue into the CTB tile.
+// One copy of the filter code: the lists run through the same loop body.
+//   gA / gB: geometry words of the two windows (PuRec::geom), winA / winB: their pool addresses
+template <bool HIGH, int NT, int OW, int OH>
+__device__ __forceinline__ void mc_cell(const uint8_t *winA, uint32_t gA, const uint8_t *winB, uint32_t gB, bool bi, int ccol,
+                                        int crow, int sh1, const Epi &e, uint32_t *tw, int tpitch)
+{
+    uint32_t cur[OH][OW / 2], prev[OH][OW / 2];
+#pragma unroll
+    for (int r = 0; r < OH; r++)
+#pragma unroll
+        for (int k = 0; k < OW / 2; k++) prev[r][k] = 0;
+#pragma unroll 1
+    for (int s = 0; s < (bi ? 2 : 1); s++) {
+        const uint32_t gword = s ? gB : gA;
+        const int pitch = ((gword >> 12) & 15) * 16, offx = (gword >> 16) & 15;
+        const int mx = (gword >> 20) & 7, my = (gword >> 23) & 7;
+        if (s) {
+#pragma unroll
+            for (int r = 0; r < OH; r++)
+#pragma unroll
+                for (int k = 0; k < OW / 2; k++) prev[r][k] = cur[r][k];
+        }
+        if (NT == 8)
+            mc_filter<HIGH, NT, OW, OH>(s ? winB : winA, pitch, offx + ccol, crow, c_qpel4[mx][0], c_qpel4[mx][1], c_qpel4[my][0],
+                                        c_qpel4[my][1], sh1, cur);
+        else
+            mc_filter<HIGH, NT, OW, OH>(s ? winB : winA, pitch, offx + ccol, crow, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, cur);
+    }
+#pragma unroll
+    for (int r = 0; r < OH; r++)
+#pragma unroll
+        for (int k = 0; k < OW / 2; k++) epi_pair(e, cur[r][k], prev[r][k], tw + r * tpitch + k);
+}
+
 // ================================================================= the kernel
-__device__ __forceinline__ void unpack_epi(const uint32_t (&w)[3], int bd, bool bi, bool first_of_bi, Epi &e)
+__device__ __forceinline__ void unpack_epi(const uint32_t (&w)[3], int bd, Epi &e)
 {
     e.wA = (int)(int16_t)(w[0] & 0xffffu);
     e.wB = (int)w[0] >> 16;
@@ -762,8 +789,6 @@ __device__ __forceinline__ void unpack_epi(const uint32_t (&w)[3], int bd, bool 
     e.sh = (int)(w[2] & 0xffffu);
     e.post = (int)w[2] >> 16;
     e.maxv = (1 << bd) - 1;
-    e.bi = bi;
-    e.store_tmp = first_of_bi;
 }
 
 // flags: bit 0 run MC, bit 1 run the residual
@@ -795,12 +820,11 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     }
     PuRec *recs = (PuRec *)sp;                  sp += MAX_CTB_PUS * (sizeof(PuRec) / 4);
     int *cumA = (int *)sp;                      sp += MAX_CTB_PUS + 4;
-    int *cumB = (int *)sp;                      sp += MAX_CTB_PUS + 4;
     uint16_t *listA = (uint16_t *)sp;           sp += MAX_CTB_CELLS / 2;
-    uint16_t *listB = (uint16_t *)sp;           sp += MAX_CTB_CELLS / 2;
-    uint16_t *cumW = (uint16_t *)sp;            sp += N_KINDS * (MAX_CTB_PUS + 2) / 2;   // [kind][PU] window units before this PU
-    uint8_t *nxt = (uint8_t *)sp;               sp += N_KINDS * MAX_CTB_PUS / 4;         // [kind][PU] first PU of the round after one starting here
-    uint8_t *rstart = (uint8_t *)sp;            sp += N_KINDS * (MAX_ROUNDS + 4) / 4;    // [kind][round] first PU, [kind][MAX_ROUNDS + 1] = count
+    uint16_t *cumW = (uint16_t *)sp;            sp += 2 * (MAX_CTB_PUS + 2) / 2;         // [luma | chroma plane][PU] window units (128 B) before this PU
+    uint8_t *nxt = (uint8_t *)sp;               sp += 2 * MAX_CTB_PUS / 4;               // [..][PU] first PU of the round after one starting here
+    uint8_t *rstart = (uint8_t *)sp;            sp += 2 * (MAX_ROUNDS + 4) / 4;          // [..][round] first PU, [..][MAX_ROUNDS + 1] = count
+    int *done = (int *)sp;                      sp += 2;                                 // warps finished with each pool half
     int *scan_tmp = (int *)sp;                  sp += 2 * 4 * RC_WARPS;                  // [cells | units][class][warp]
     int *tu_cnt = (int *)sp;                    sp += 16;                         // [0..3] counts, [4..7] bases, [8..11] cursors, [12] coef lo, [13] coef hi, [14] batch counter
     uint16_t *tu_list = (uint16_t *)sp;         sp += MAX_CTB_TUS / 2;
@@ -838,7 +862,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     }
     if (tid < 12) tu_cnt[tid] = 0;
     if (tid == 12) { tu_cnt[12] = 0x7fffffff; tu_cnt[13] = 0; tu_cnt[14] = 0; }
-    if (tid == 0) { mbar_init(mbar, 1); mbar_init(mbar + 1, 1); }
+    if (tid == 0) { mbar_init(mbar, 1); mbar_init(mbar + 1, 1); done[0] = 0; done[1] = 0; }
     __syncthreads();
 
     // ---- TBs of the CTB sorted by size (counting sort) and the arena range their coefficients
@@ -889,7 +913,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                 if (sub == 0)
                     rc.rect = (uint32_t)(((pu.x0 - cx0) >> 2) | (((pu.y0 - cy0) >> 2) << 4) | ((pu.w >> 2) << 8) |
                                          ((pu.h >> 2) << 13) | ((bi ? 1 : 0) << 18));
-                cc = sub == 0 ? ncell : (sub == 1 && bi ? ncell : 0);
+                cc = sub == 0 ? ncell : 0;
                 {
                     const int s = sub & 1, pt = sub >> 1;
                     uint32_t gw = 0;
@@ -898,7 +922,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                         const WinGeom g = win_geom<HIGH>(f, pu, l, pt == 0);
                         const int pitch = box_w(HIGH, g.wcls) * (HIGH ? 2 : 1);
                         const int bytes = pitch * box_h(g.hcls);
-                        wu = (bytes * (pt ? 2 : 1)) / POOL_UNIT;
+                        wu = bytes / POOL_UNIT;                // one plane: Cb and Cr run in separate rounds
                         // what the TMA issue of this window needs (box of plane pt; Cr follows Cb)
                         const int slot = sl.ref_slot[l][pu.ref_idx[l] & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1);
                         uint32_t *iw = issue + (sub * MAX_CTB_PUS + p) * 2;
@@ -952,29 +976,31 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                 if (w < warp) { beforeC += a; beforeW += b; }
                 totalC += a; totalW += b;
             }
+            // the windows of a PU sit together (slot A, then slot B): units before the PU = both classes
+            const int exW = carryW + beforeW + iw_ - wu;
+            const int exBoth = exW + __shfl_xor_sync(0xffffffffu, exW, 1);
             if (p < np) {
-                cumW[sub * (MAX_CTB_PUS + 2) + p] = (uint16_t)(carryW + beforeW + iw_ - wu);
+                if (!(sub & 1)) cumW[(sub >> 1) * (MAX_CTB_PUS + 2) + p] = (uint16_t)exBoth;
                 if (sub == 0) cumA[p] = carryC + beforeC + ic_ - cc;
-                if (sub == 1) cumB[p] = carryC + beforeC + ic_ - cc;
             }
             carryW += totalW; carryC += totalC;
             __syncthreads();                               // scan_tmp is reused by the next pass
         }
-        if (tid < 4) {
-            cumW[tid * (MAX_CTB_PUS + 2) + np] = (uint16_t)carryW;
+        {
+            const int both = carryW + __shfl_xor_sync(0xffffffffu, carryW, 1);
+            if (tid < 4 && !(tid & 1)) cumW[(tid >> 1) * (MAX_CTB_PUS + 2) + np] = (uint16_t)both;
             if (tid == 0) cumA[np] = carryC;
-            if (tid == 1) cumB[np] = carryC;
         }
         __syncthreads();
-        const int totA = cumA[np], totB = cumB[np];
+        const int totA = cumA[np];
 
-        // ---- 1b. greedy rounds: nxt[kind][p] = first PU that no longer fits a round starting at p
-        const int nkinds = f.nplanes == 3 ? N_KINDS : 2;
-        for (int i = tid; i < nkinds * np; i += RC_THREADS) {
-            const int k = i / np, p = i - k * np;
+        // ---- 1b. greedy rounds per plane type: nxt[pt][p] = first PU that no longer fits a round starting at p
+        const int npt = f.nplanes == 3 ? 2 : 1;
+        for (int i = tid; i < npt * np; i += RC_THREADS) {
+            const int k = i >= np, p = i - k * np;
             const uint16_t *cw = cumW + k * (MAX_CTB_PUS + 2);
             const int target = cw[p] + HALF_UNITS;
-            int lo = p + 1, hi = np;                       // largest e with cw[e] <= target (every window fits: e > p)
+            int lo = p + 1, hi = np;                       // largest e with cw[e] <= target (a PU's windows always fit: e > p)
             while (lo < hi) {
                 const int mid = (lo + hi + 1) >> 1;
                 if (cw[mid] <= target) lo = mid; else hi = mid - 1;
@@ -982,129 +1008,115 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
             nxt[k * MAX_CTB_PUS + p] = (uint8_t)lo;
         }
         __syncthreads();
-        // one thread per kind walks its rounds; the others build the cell lists meanwhile
-        if (tid < nkinds) {
+        // one thread per plane type walks its rounds; the other warps build the cell list meanwhile
+        if (tid < npt) {
             const int k = tid;
             uint8_t *rs = rstart + k * (MAX_ROUNDS + 4);
             int n = 0;
-            if (cumW[k * (MAX_CTB_PUS + 2) + np] > 0)
-                for (int s = 0; s < np && n < MAX_ROUNDS; s = nxt[k * MAX_CTB_PUS + s]) rs[n++] = (uint8_t)s;
+            for (int q = 0; q < np && n < MAX_ROUNDS; q = nxt[k * MAX_CTB_PUS + q]) rs[n++] = (uint8_t)q;
             rs[n] = (uint8_t)np;
             rs[MAX_ROUNDS + 1] = (uint8_t)n;
         } else if (tid >= 32) {
             // ---- 1c. cells sorted by PU: entry = PU | cell column << 7 | cell row << 11
-#pragma unroll 1
-            for (int s = 0; s < 2; s++) {
-                const int *cum = s ? cumB : cumA;
-                uint16_t *list = s ? listB : listA;
-                const int tot = min(s ? totB : totA, MAX_CTB_CELLS);
-                for (int i = tid - 32; i < tot; i += RC_THREADS - 32) {
-                    int lo = 0, hi = np - 1;               // largest p with cum[p] <= i
-                    while (lo < hi) {
-                        const int mid = (lo + hi + 1) >> 1;
-                        if (cum[mid] <= i) lo = mid; else hi = mid - 1;
-                    }
-                    const int local = i - cum[lo];
-                    const int nx = (recs[lo].rect >> 8) & 31;
-                    const int cy = fastdiv(local, fastinv(nx)), cx = local - cy * nx;
-                    list[i] = (uint16_t)(lo | (cx << 7) | (cy << 11));
+            const int tot = min(totA, MAX_CTB_CELLS);
+            for (int i = tid - 32; i < tot; i += RC_THREADS - 32) {
+                int lo = 0, hi = np - 1;                   // largest p with cumA[p] <= i
+                while (lo < hi) {
+                    const int mid = (lo + hi + 1) >> 1;
+                    if (cumA[mid] <= i) lo = mid; else hi = mid - 1;
                 }
+                const int local = i - cumA[lo];
+                const int nx = (recs[lo].rect >> 8) & 31;
+                const int cy = fastdiv(local, fastinv(nx)), cx = local - cy * nx;
+                listA[i] = (uint16_t)(lo | (cx << 7) | (cy << 11));
             }
         }
         __syncthreads();
 
-        // ---- 1d. rounds, double buffered: the windows of round i + 1 fly while round i is filtered
+        // ---- 1d. rounds, plane by plane, through the two pool halves.  No block barrier in the
+        //      loop: a warp that has filtered its cells of round i goes on to round i + 1 (already
+        //      resident); the LAST warp to leave round i refills that half with round i + 2.
         const int sh1 = bd - 8;                            // first-stage shift (template :2486)
-        int nrk[N_KINDS], R = 0;
-#pragma unroll
-        for (int k = 0; k < N_KINDS; k++) { nrk[k] = k < nkinds ? rstart[k * (MAX_ROUNDS + 4) + MAX_ROUNDS + 1] : 0; R += nrk[k]; }
-        // flat round index -> (kind, round of the kind)
-        auto locate = [&](int i, int &k, int &r) {
-            k = 0; r = i;
-#pragma unroll
-            for (int q = 0; q < N_KINDS - 1; q++)
-                if (k == q && r >= nrk[q]) { r -= nrk[q]; k = q + 1; }
+        const int nr0 = rstart[MAX_ROUNDS + 1], nr1 = npt == 2 ? rstart[(MAX_ROUNDS + 4) + MAX_ROUNDS + 1] : 0;
+        const int R = nr0 + 2 * nr1;
+        auto locate = [&](int i, int &c, int &r) {        // flat round -> (plane, round of its plane type)
+            if (i < nr0) { c = 0; r = i; }
+            else if (i < nr0 + nr1) { c = 1; r = i - nr0; }
+            else { c = 2; r = i - nr0 - nr1; }
         };
-        auto issue_round = [&](int i) {
-            int k, r;
-            locate(i, k, r);
-            const uint8_t *rs = rstart + k * (MAX_ROUNDS + 4);
+        auto issue_round = [&](int i, int t, int n) {     // by threads t, t + n, ...
+            int c, r;
+            locate(i, c, r);
+            const int pt = c > 0;
+            const uint8_t *rs = rstart + pt * (MAX_ROUNDS + 4);
             const int pa = rs[r], pb = rs[r + 1];
-            const uint16_t *cw = cumW + k * (MAX_CTB_PUS + 2);
+            const uint16_t *cw = cumW + pt * (MAX_CTB_PUS + 2);
             uint64_t *bar = mbar + (i & 1);
             uint8_t *buf = pool + (i & 1) * HALF_BYTES;
-            if (tid == 0) mbar_expect_tx(bar, (uint32_t)(cw[pb] - cw[pa]) * POOL_UNIT);
-            for (int p = pa + tid; p < pb; p += RC_THREADS) {
-                const uint32_t *iw = issue + (k * MAX_CTB_PUS + p) * 2;
-                const int units = cw[p + 1] - cw[p];
-                if (units > 0) {
+            if (t == 0) mbar_expect_tx(bar, (uint32_t)(cw[pb] - cw[pa]) * POOL_UNIT);
+            for (int p = pa + t; p < pb; p += n) {
+                uint8_t *dst = buf + (cw[p] - cw[pa]) * POOL_UNIT;
+                const bool bi = (recs[p].rect >> 18) & 1;
+#pragma unroll 1
+                for (int sl = 0; sl < (bi ? 2 : 1); sl++) {
+                    const uint32_t *iw = issue + ((2 * pt + sl) * MAX_CTB_PUS + p) * 2;
                     const uint32_t w0 = iw[0], w1 = iw[1];
-                    const int bytes = (int)(w1 >> 16) << 7;
-                    uint8_t *dst = buf + (cw[p] - cw[pa]) * POOL_UNIT;
-                    const CUtensorMap *m = f.tmaps + (w0 & 0xfffu);
-                    const int x = (int)(w0 >> 12), y = (int)(w1 & 0xffffu);
-                    tma_load_2d(dst, m, x, y, bar);
-                    if (k >> 1) tma_load_2d(dst + bytes, m + N_WCLS * N_HCLS, x, y, bar);
+                    const CUtensorMap *m = f.tmaps + (w0 & 0xfffu) + (c == 2 ? N_WCLS * N_HCLS : 0);
+                    tma_load_2d(dst, m, (int)(w0 >> 12), (int)(w1 & 0xffffu), bar);
+                    dst += (w1 >> 16) * POOL_UNIT;
                 }
             }
         };
-        if (R > 0) issue_round(0);
+        if (R > 0) issue_round(0, tid, RC_THREADS);
+        if (R > 1) issue_round(1, tid, RC_THREADS);
         sort_tus();
 #pragma unroll 1
         for (int i = 0; i < R; i++) {
-            __syncthreads();                               // round i - 1 is done with the other half
-            if (i + 1 < R) issue_round(i + 1);
-            int k, r;
-            locate(i, k, r);
-            const int s = k & 1, pt = k >> 1;
-            const uint8_t *rs = rstart + k * (MAX_ROUNDS + 4);
+            int c, r;
+            locate(i, c, r);
+            const int pt = c > 0;
+            const uint8_t *rs = rstart + pt * (MAX_ROUNDS + 4);
             const int pa = rs[r], pb = rs[r + 1];
-            const uint16_t *cw = cumW + k * (MAX_CTB_PUS + 2);
+            const uint16_t *cw = cumW + pt * (MAX_CTB_PUS + 2);
             const uint8_t *buf = pool + (i & 1) * HALF_BYTES - cw[pa] * POOL_UNIT;
-            const uint16_t *list = s ? listB : listA;
-            const int *cum = s ? cumB : cumA;
-            const int clo = cum[pa], chi = min(cum[pb], MAX_CTB_CELLS);
+            const int clo = cumA[pa], chi = min(cumA[pb], MAX_CTB_CELLS);
             mbar_wait(mbar + (i & 1), (i & 1) ? par1 : par0);
             if (i & 1) par1 ^= 1; else par0 ^= 1;
 #pragma unroll 1
             for (int ci = clo + tid; ci < chi; ci += RC_THREADS) {
-                const int ent = list[ci];
+                const int ent = listA[ci];
                 const int p = ent & 127, cx = (ent >> 7) & 15, cy = ent >> 11;
                 const PuRec &rc = recs[p];
                 const uint32_t rect = rc.rect;
                 const int x4 = rect & 15, y4 = (rect >> 4) & 15;
                 const bool pbi = (rect >> 18) & 1;
-                const uint32_t gword = rc.geom[s][pt];
-                const uint8_t *win = buf + cw[p] * POOL_UNIT;
-                const int pitch = ((gword >> 12) & 15) * 16, offx = (gword >> 16) & 15;
-                const int mx = (gword >> 20) & 7, my = (gword >> 23) & 7;
+                const uint32_t gA = rc.geom[0][pt], gB = rc.geom[1][pt];
+                const uint8_t *winA = buf + cw[p] * POOL_UNIT;
+                const uint8_t *winB = winA + (issue[((2 * pt) * MAX_CTB_PUS + p) * 2 + 1] >> 16) * POOL_UNIT;
                 Epi e;
+                const uint32_t ew[3] = {rc.epi[c][0], rc.epi[c][1], rc.epi[c][2]};
+                unpack_epi(ew, bd, e);
                 if (pt == 0) {
-                    const uint32_t ew[3] = {rc.epi[0][0], rc.epi[0][1], rc.epi[0][2]};
-                    unpack_epi(ew, bd, pbi, pbi && s == 0, e);
                     uint32_t *tp = tile.p[0] + ((y4 + cy) * 4) * tile.pitch[0] + ((x4 + cx) * 2);
-                    mc_cell<HIGH, 8, 4, 4>(win, pitch, offx + cx * 4, cy * 4, c_qpel4[mx][0], c_qpel4[mx][1], c_qpel4[my][0],
-                                           c_qpel4[my][1], sh1, e, tp, tile.pitch[0]);
+                    mc_cell<HIGH, 8, 4, 4>(winA, gA, winB, gB, pbi, cx * 4, cy * 4, sh1, e, tp, tile.pitch[0]);
                 } else {
                     const int hs = f.hs, vs = f.vs;
                     const int cw_ = 4 >> hs, ch = 4 >> vs;
-                    const int bytes = pitch * box_h((gword >> 26) & 7);
-#pragma unroll 1
-                    for (int c = 1; c < 3; c++) {
-                        const uint32_t ew[3] = {rc.epi[c][0], rc.epi[c][1], rc.epi[c][2]};
-                        unpack_epi(ew, bd, pbi, pbi && s == 0, e);
-                        uint32_t *tp = tile.p[c] + ((y4 + cy) * ch) * tile.pitch[c] + (((x4 + cx) * cw_) >> 1);
-                        const uint8_t *wc = win + (c - 1) * bytes;
-                        if (hs && vs)
-                            mc_cell<HIGH, 4, 2, 2>(wc, pitch, offx + cx * 2, cy * 2, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
-                                                   tp, tile.pitch[c]);
-                        else if (hs)
-                            mc_cell<HIGH, 4, 2, 4>(wc, pitch, offx + cx * 2, cy * 4, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
-                                                   tp, tile.pitch[c]);
-                        else
-                            mc_cell<HIGH, 4, 4, 4>(wc, pitch, offx + cx * 4, cy * 4, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, e,
-                                                   tp, tile.pitch[c]);
-                    }
+                    uint32_t *tp = tile.p[c] + ((y4 + cy) * ch) * tile.pitch[c] + (((x4 + cx) * cw_) >> 1);
+                    if (hs && vs) mc_cell<HIGH, 4, 2, 2>(winA, gA, winB, gB, pbi, cx * 2, cy * 2, sh1, e, tp, tile.pitch[c]);
+                    else if (hs) mc_cell<HIGH, 4, 2, 4>(winA, gA, winB, gB, pbi, cx * 2, cy * 4, sh1, e, tp, tile.pitch[c]);
+                    else mc_cell<HIGH, 4, 4, 4>(winA, gA, winB, gB, pbi, cx * 4, cy * 4, sh1, e, tp, tile.pitch[c]);
+                }
+            }
+            __syncwarp();
+            if (i + 2 < R) {
+                int old = 0;
+                if (lane == 0) old = atomicAdd(&done[i & 1], 1);
+                old = __shfl_sync(0xffffffffu, old, 0);
+                if (old == RC_WARPS - 1) {                 // every warp has left this half
+                    if (lane == 0) done[i & 1] = 0;
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    issue_round(i + 2, lane, 32);
                 }
             }
         }
@@ -1176,8 +1188,8 @@ size_t recon_smem_bytes(const FrameDev &f)
         const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
         words += (size_t)(((cs >> hs) >> 1) + 2) * (cs >> vs);
     }
-    words += MAX_CTB_PUS * (sizeof(PuRec) / 4) + 2 * (MAX_CTB_PUS + 4) + MAX_CTB_CELLS + N_KINDS * (MAX_CTB_PUS + 2) / 2 +
-             N_KINDS * MAX_CTB_PUS / 4 + N_KINDS * (MAX_ROUNDS + 4) / 4 + 2 * 4 * RC_WARPS + 16 + MAX_CTB_TUS / 2 +
+    words += MAX_CTB_PUS * (sizeof(PuRec) / 4) + (MAX_CTB_PUS + 4) + MAX_CTB_CELLS / 2 + 2 * (MAX_CTB_PUS + 2) / 2 +
+             2 * MAX_CTB_PUS / 4 + 2 * (MAX_ROUNDS + 4) / 4 + 2 + 2 * 4 * RC_WARPS + 16 + MAX_CTB_TUS / 2 +
              N_KINDS * MAX_CTB_PUS * 2 + 8;
     return POOL_BYTES + words * 4 + (f.cfi == 3 ? RC_WARPS * sizeof(WarpScratch) + 16 : 0);
 }
