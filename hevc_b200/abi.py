@@ -115,6 +115,7 @@ SYMBOLS = {
     "ohcu_set_sao": (C.c_int, [_P, C.c_int, C.POINTER(SaoIn)]),
     "ohcu_frame_flush": (C.c_int, [_P, C.c_int]),
     "ohcu_frame_abort": (C.c_int, [_P, C.c_int]),
+    "ohcu_slot_pitch": (C.c_int, [_P, C.c_int, C.POINTER(C.c_ssize_t)]),
     "ohcu_frame_stage": (C.c_int, [_P, C.c_int]),
     "ohcu_frame_launch": (C.c_int, [_P, C.c_int, C.c_int]),
     "ohcu_frame_launch_stages": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),

@@ -129,16 +129,22 @@ class Context:
         check(self.lib.ohcu_timer_stop(self.handle, C.byref(ms)), "ohcu_timer_stop")
         return ms.value
 
-    def pinned_picture(self):
-        """Output picture in pinned host memory (for download_async)."""
+    def pinned_picture(self, slot_pitch=False):
+        """Output picture in pinned host memory (for download_async).  With slot_pitch the rows
+        are spaced like the device planes (ohcu_slot_pitch), which makes the download one
+        linear copy per plane; the returned arrays are views of the picture columns."""
         planes = []
+        item = np.dtype(self.dtype).itemsize
         for c in range(self.nplanes):
             h, w = self.plane_shape(c)
-            nbytes = h * w * np.dtype(self.dtype).itemsize
+            pitch = C.c_ssize_t(w * item)
+            if slot_pitch:
+                check(self.lib.ohcu_slot_pitch(self.handle, c, C.byref(pitch)), "ohcu_slot_pitch")
+            nbytes = h * pitch.value
             p = C.c_void_p()
             check(self.lib.ohcu_host_alloc(nbytes, C.byref(p)), "ohcu_host_alloc")
             buf = (C.c_char * nbytes).from_address(p.value)
-            planes.append(np.frombuffer(buf, dtype=self.dtype).reshape(h, w))
+            planes.append(np.frombuffer(buf, dtype=self.dtype).reshape(h, pitch.value // item)[:, :w])
         return planes
 
     # ---- convenience: one frame, synchronously (tests, smoke) -----------------

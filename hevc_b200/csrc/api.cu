@@ -416,6 +416,13 @@ extern "C" int ohcu_slot_upload(ohcu_ctx *c, int slot, const uint8_t *const plan
     return 0;
 }
 
+extern "C" int ohcu_slot_pitch(const ohcu_ctx *c, int plane, ptrdiff_t *pitch)
+{
+    if (!c || !pitch || plane < 0 || plane >= c->nplanes) return fail(OHCU_EINVAL, "bad plane");
+    *pitch = c->slots[0].pic.ps.pitch[plane];
+    return 0;
+}
+
 static int download_impl(ohcu_ctx *c, int slot, uint8_t *const planes[3], const ptrdiff_t strides[3], bool wait)
 {
     ENTER(c);
@@ -425,9 +432,16 @@ static int download_impl(ohcu_ctx *c, int slot, uint8_t *const planes[3], const 
     {
         std::lock_guard<std::mutex> lock(c->mu);
         if (s.has_ready) CU(cudaStreamWaitEvent(c->copy_stream, s.ready, 0));
-        for (int i = 0; i < c->nplanes; i++)
-            CU(cudaMemcpy2DAsync(planes[i], strides[i], s.pic.ps.p[i], s.pic.ps.pitch[i], (size_t)c->pw[i] * c->P,
-                                 c->ph[i], cudaMemcpyDeviceToHost, c->copy_stream));
+        for (int i = 0; i < c->nplanes; i++) {
+            // a host plane with the slot's own pitch (ohcu_slot_pitch) is one linear copy: the row
+            // tails carry halo bytes, and the copy engine runs at full rate
+            if (strides[i] == (ptrdiff_t)s.pic.ps.pitch[i])
+                CU(cudaMemcpyAsync(planes[i], s.pic.ps.p[i], (size_t)(c->ph[i] - 1) * s.pic.ps.pitch[i] + (size_t)c->pw[i] * c->P,
+                                   cudaMemcpyDeviceToHost, c->copy_stream));
+            else
+                CU(cudaMemcpy2DAsync(planes[i], strides[i], s.pic.ps.p[i], s.pic.ps.pitch[i], (size_t)c->pw[i] * c->P,
+                                     c->ph[i], cudaMemcpyDeviceToHost, c->copy_stream));
+        }
         CU(cudaEventRecord(s.read_done, c->copy_stream));
         s.has_read = true;
     }

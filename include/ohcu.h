@@ -198,6 +198,12 @@ int ohcu_slot_download(ohcu_ctx *ctx, int slot, uint8_t *const planes[3],
 int ohcu_slot_download_async(ohcu_ctx *ctx, int slot, uint8_t *const planes[3],
                              const ptrdiff_t strides[3]);
 int ohcu_slot_sync(ohcu_ctx *ctx, int slot);   /* replaces ff_thread_await_progress */
+/* Row pitch in bytes of the slots' device planes.  A host plane passed to the download
+ * calls with exactly this stride (an AVFrame whose linesize the decoder's get_buffer chose
+ * that way) is fetched as ONE linear copy per plane, which runs at the link rate next to
+ * concurrent uploads; other strides take a pitched 2-D copy.  The bytes between the end
+ * of a row and the start of the next then hold halo samples.                          */
+int ohcu_slot_pitch(const ohcu_ctx *ctx, int plane, ptrdiff_t *pitch);
 
 /* ======================================================================== */
 /* Per-frame work lists                                                     */
