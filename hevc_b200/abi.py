@@ -94,6 +94,8 @@ assert C.sizeof(PU) == 20 and C.sizeof(TU) == 20 and C.sizeof(SAO) == 40 and C.s
 
 # name -> (restype, argtypes); every symbol include/ohcu.h declares
 _P = C.c_void_p
+_I = C.c_int
+_S = C.c_ssize_t
 SYMBOLS = {
     "ohcu_abi_version": (C.c_int, []),
     "ohcu_last_error": (C.c_char_p, []),
@@ -130,6 +132,22 @@ SYMBOLS = {
     "ohcu_timer_stop": (C.c_int, [_P, C.POINTER(C.c_float)]),
     "ohcu_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
     "ohcu_host_free": (C.c_int, [_P]),
+    # per-entry test shims: same argument lists as the checkers' leaves (tests/oracle_lib.py)
+    "ohcu_dsp_mc_put": (C.c_int, [_I, _I, _P, _P, _S, _I, _I, _I, _I]),
+    "ohcu_dsp_mc_uni": (C.c_int, [_I, _I, _P, _S, _P, _S, _I, _I, _I, _I]),
+    "ohcu_dsp_mc_uni_w": (C.c_int, [_I, _I, _P, _S, _P, _S, _I, _I, _I, _I, _I, _I, _I]),
+    "ohcu_dsp_mc_bi": (C.c_int, [_I, _I, _P, _S, _P, _S, _P, _I, _I, _I, _I]),
+    "ohcu_dsp_mc_bi_w": (C.c_int, [_I, _I, _P, _S, _P, _S, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I]),
+    "ohcu_dsp_idct": (C.c_int, [_I, _P, _I, _I]),
+    "ohcu_dsp_idct_dc": (C.c_int, [_I, _P, _I]),
+    "ohcu_dsp_idct_4x4_luma": (C.c_int, [_I, _P]),
+    "ohcu_dsp_transform_skip": (C.c_int, [_I, _P, _I]),
+    "ohcu_dsp_transform_rdpcm": (C.c_int, [_I, _P, _I, _I]),
+    "ohcu_dsp_transform_add": (C.c_int, [_I, _P, _P, _S, _I]),
+    "ohcu_dsp_loop_filter_luma": (C.c_int, [_I, _I, _P, _S, _I, _P, _P, _P]),
+    "ohcu_dsp_loop_filter_chroma": (C.c_int, [_I, _I, _P, _S, _P, _P, _P]),
+    "ohcu_dsp_sao_band_filter": (C.c_int, [_I, _P, _P, _S, _S, _P, _I, _I, _I]),
+    "ohcu_dsp_sao_edge_filter": (C.c_int, [_I, _P, _P, _S, _S, _P, _I, _I, _I]),
 }
 
 _lib = None

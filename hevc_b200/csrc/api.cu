@@ -969,3 +969,97 @@ extern "C" int ohcu_host_free(void *ptr)
     if (ptr) CU(cudaFreeHost(ptr));
     return 0;
 }
+
+// ------------------------------------------------------------------ per-entry test shims
+// One block through the device code of the frame kernels, with the argument meaning of the
+// HEVCDSPContext entries (hevcdsp.h:51-166).  Host pointers; synchronous; tests only.
+#define DSP_ENTER()                                                                      \
+    do {                                                                                 \
+        int n_ = 0;                                                                      \
+        if (cudaGetDeviceCount(&n_) != cudaSuccess || n_ < 1) return fail(OHCU_ENODEV, "no CUDA device"); \
+    } while (0)
+#define DSP_RC(call) ((call) == 0 ? 0 : fail(OHCU_ECUDA, "per-entry shim failed: %s", cudaGetErrorString(cudaGetLastError())))
+
+extern "C" int ohcu_dsp_mc_put(int bd, int luma, int16_t *dst, const uint8_t *src, ptrdiff_t srcstride, int height, int mx, int my, int width)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_mc(bd, luma, 0, nullptr, 0, src, srcstride, nullptr, dst, height, 0, 0, 0, 0, 0, mx, my, width));
+}
+extern "C" int ohcu_dsp_mc_uni(int bd, int luma, uint8_t *dst, ptrdiff_t dststride, const uint8_t *src, ptrdiff_t srcstride, int height,
+                               int mx, int my, int width)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_mc(bd, luma, 1, dst, dststride, src, srcstride, nullptr, nullptr, height, 0, 0, 0, 0, 0, mx, my, width));
+}
+extern "C" int ohcu_dsp_mc_uni_w(int bd, int luma, uint8_t *dst, ptrdiff_t dststride, const uint8_t *src, ptrdiff_t srcstride, int height,
+                                 int denom, int wx, int ox, int mx, int my, int width)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_mc(bd, luma, 2, dst, dststride, src, srcstride, nullptr, nullptr, height, denom, wx, 0, ox, 0, mx, my, width));
+}
+extern "C" int ohcu_dsp_mc_bi(int bd, int luma, uint8_t *dst, ptrdiff_t dststride, const uint8_t *src, ptrdiff_t srcstride,
+                              const int16_t *src2, int height, int mx, int my, int width)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_mc(bd, luma, 3, dst, dststride, src, srcstride, src2, nullptr, height, 0, 0, 0, 0, 0, mx, my, width));
+}
+extern "C" int ohcu_dsp_mc_bi_w(int bd, int luma, uint8_t *dst, ptrdiff_t dststride, const uint8_t *src, ptrdiff_t srcstride,
+                                const int16_t *src2, int height, int denom, int wx0, int wx1, int ox0, int ox1, int mx, int my, int width)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_mc(bd, luma, 4, dst, dststride, src, srcstride, src2, nullptr, height, denom, wx0, wx1, ox0, ox1, mx, my, width));
+}
+extern "C" int ohcu_dsp_idct(int bd, int16_t *coeffs, int log2_size, int col_limit)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_residual(bd, OHCU_TU_IDCT, 0, coeffs, log2_size, col_limit, 1));
+}
+extern "C" int ohcu_dsp_idct_dc(int bd, int16_t *coeffs, int log2_size)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_residual(bd, OHCU_TU_DC, 0, coeffs, log2_size, 0, 0));
+}
+extern "C" int ohcu_dsp_idct_4x4_luma(int bd, int16_t *coeffs)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_residual(bd, OHCU_TU_DST4, 0, coeffs, 2, 0, 0));
+}
+extern "C" int ohcu_dsp_transform_skip(int bd, int16_t *coeffs, int log2_size)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_residual(bd, OHCU_TU_SKIP, 0, coeffs, log2_size, 0, 0));
+}
+extern "C" int ohcu_dsp_transform_rdpcm(int bd, int16_t *coeffs, int log2_size, int mode)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_residual(bd, OHCU_TU_BYPASS, OHCU_TUF_RDPCM | (mode ? OHCU_TUF_RDPCM_VERT : 0), coeffs, log2_size, 0, 0));
+}
+extern "C" int ohcu_dsp_transform_add(int bd, uint8_t *dst, const int16_t *coeffs, ptrdiff_t stride, int n)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_transform_add(bd, dst, coeffs, stride, n));
+}
+extern "C" int ohcu_dsp_loop_filter_luma(int bd, int vertical, uint8_t *pix, ptrdiff_t stride, int beta, const int *tc, const uint8_t *no_p,
+                                         const uint8_t *no_q)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_loop_filter(bd, 1, vertical, pix, stride, beta, tc, no_p, no_q));
+}
+extern "C" int ohcu_dsp_loop_filter_chroma(int bd, int vertical, uint8_t *pix, ptrdiff_t stride, const int *tc, const uint8_t *no_p,
+                                           const uint8_t *no_q)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_loop_filter(bd, 0, vertical, pix, stride, 0, tc, no_p, no_q));
+}
+extern "C" int ohcu_dsp_sao_band_filter(int bd, uint8_t *dst, const uint8_t *src, ptrdiff_t stride_dst, ptrdiff_t stride_src,
+                                        const int16_t *offset_val, int band_position, int width, int height)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_sao(bd, 0, dst, src, stride_dst, stride_src, offset_val, band_position, width, height));
+}
+extern "C" int ohcu_dsp_sao_edge_filter(int bd, uint8_t *dst, const uint8_t *src, ptrdiff_t stride_dst, ptrdiff_t stride_src,
+                                        const int16_t *offset_val, int eo, int width, int height)
+{
+    DSP_ENTER();
+    return DSP_RC(dsp_sao(bd, 1, dst, src, stride_dst, stride_src, offset_val, eo, width, height));
+}

@@ -277,6 +277,16 @@ __device__ __forceinline__ void sao_edge_fast(const pixel *rowa, const pixel *ro
     }
 }
 
+// sao_band_filter_0 (template :310-335) on eight samples; lo = offsets of bands 0..3 packed, hi = 0
+__device__ __forceinline__ void sao_band_fast(const int (&v)[8], uint32_t lo, uint32_t hi, int pos, int sh, int maxv, int (&o)[8])
+{
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int kb = ((v[i] >> sh) - pos) & 31;
+        o[i] = clip3i(v[i] + packed_offset(lo, hi, min(kb, 4)), 0, maxv);
+    }
+}
+
 // per (plane, CTB of the region): what the SAO step needs, built once per CTA
 struct SaoRec {
     uint32_t lo, hi;          // packed offsets (fast paths)
@@ -584,12 +594,7 @@ __global__ void __launch_bounds__(LF_THREADS) loopfilter_kernel(const __grid_con
             continue;
         } else if (type == OHCU_SAO_BAND) {                            // sao_band_filter_0, template :310-335
             ld8(sp8, v);
-            const int pos = (rec.misc >> 8) & 31, sh = bd - 5;
-#pragma unroll
-            for (int i = 0; i < 8; i++) {
-                const int kb = ((v[i] >> sh) - pos) & 31;
-                o[i] = clip3i(v[i] + packed_offset(rec.lo, rec.hi, min(kb, 4)), 0, maxv);
-            }
+            sao_band_fast(v, rec.lo, rec.hi, (rec.misc >> 8) & 31, bd - 5, maxv, o);
         } else {                                                       // sao_edge_filter, template :342-378
             ld8(sp8, v);
             const int eo = (rec.misc >> 2) & 3;
@@ -638,6 +643,101 @@ int launch_loopfilter(const FrameDev &f, const LfMaps &maps, int flags, cudaStre
     if (f.bd > 8) loopfilter_kernel<uint16_t><<<grid, LF_THREADS, smem, st>>>(f, maps, flags);
     else          loopfilter_kernel<uint8_t><<<grid, LF_THREADS, smem, st>>>(f, maps, flags);
     return 1;
+}
+
+// ================================================================= per-entry test shims
+// hevc_{h,v}_loop_filter_{luma,chroma} (template :3377-3553): 8 lines = two 4-line segments
+// through luma_segment / chroma_segment; pix = first Q sample.
+template <typename pixel>
+__global__ void dsp_deblock_kernel(pixel *pix, int stride, int luma, int vertical, int bd, int beta, int tc0, int tc1, int nop0,
+                                   int nop1, int noq0, int noq1)
+{
+    const int s = threadIdx.x;                    // segment
+    if (s >= 2) return;
+    const int xs = vertical ? 1 : stride, ys = vertical ? stride : 1;      // along the line / to the next line
+    pixel *base = pix + 4 * s * ys - 4 * xs;
+    int l[4][8];
+    for (int d = 0; d < 4; d++)
+        for (int k = 0; k < 8; k++) l[d][k] = base[d * ys + k * xs];
+    const int tc = s ? tc1 : tc0, no_p = s ? nop1 : nop0, no_q = s ? noq1 : noq0;
+    if (luma) luma_segment(l, bd, beta, tc, no_p, no_q);
+    else chroma_segment(l, bd, tc, no_p, no_q);
+    for (int d = 0; d < 4; d++)
+        for (int k = 0; k < 8; k++) base[d * ys + k * xs] = (pixel)l[d][k];
+}
+
+int dsp_loop_filter(int bd, int luma, int vertical, uint8_t *pix, ptrdiff_t stride, int beta, const int *tc, const uint8_t *no_p,
+                    const uint8_t *no_q)
+{
+    const int P = bd > 8 ? 2 : 1;
+    // 8 samples across the edge x 8 lines along it, copied as a 8 x 8 patch whose centre is pix
+    uint8_t *d = nullptr;
+    if (cudaMalloc((void **)&d, 16 * 16 * 2) != cudaSuccess) return -1;
+    uint8_t *h0 = vertical ? pix - 4 * P : pix - 4 * stride;
+    const int rows = 8, wbytes = 8 * P;
+    int rc = -1;
+    if (cudaMemcpy2D(d, 32, h0, stride, wbytes, rows, cudaMemcpyHostToDevice) == cudaSuccess) {
+        // device patch: pitch 32 bytes; pix sits at column 4 (vertical) or row 4 (horizontal)
+        uint8_t *dp = vertical ? d + 4 * P : d + 4 * 32;
+        if (bd > 8) dsp_deblock_kernel<uint16_t><<<1, 32>>>((uint16_t *)dp, 16, luma, vertical, bd, beta, tc[0], tc[1], no_p[0], no_p[1], no_q[0], no_q[1]);
+        else dsp_deblock_kernel<uint8_t><<<1, 32>>>(dp, 32, luma, vertical, bd, beta, tc[0], tc[1], no_p[0], no_p[1], no_q[0], no_q[1]);
+        if (cudaDeviceSynchronize() == cudaSuccess &&
+            cudaMemcpy2D(h0, stride, d, 32, wbytes, rows, cudaMemcpyDeviceToHost) == cudaSuccess) rc = 0;
+    }
+    cudaFree(d);
+    return rc;
+}
+
+// sao_band_filter / sao_edge_filter (template :310-378) on a w x h block through the 8-sample
+// fast paths of the frame kernel.  src carries a 1-sample halo (edge); tile pitch TP samples.
+template <typename pixel>
+__global__ void dsp_sao_kernel(const pixel *tile, int tp, pixel *dst, int dp, int w, int h, int bd, int edge, int eo, int pos,
+                               uint32_t lo, uint32_t hi)
+{
+    const int maxv = (1 << bd) - 1, units = (w + 7) >> 3;
+    for (int it = threadIdx.x; it < units * h; it += blockDim.x) {
+        const int y = it / units, u = it - y * units;
+        const pixel *sp8 = tile + (y + 1) * tp + 8 + 8 * u;       // block origin at tile (1, 8): aligned, halo around
+        int v[8], o[8];
+        ld8(sp8, v);
+        if (!edge) sao_band_fast(v, lo, hi, pos, bd - 5, maxv, o);
+        else if (eo == 0) sao_edge_fast<pixel, -1>(sp8, sp8, v, lo, hi, maxv, o);
+        else if (eo == 1) sao_edge_fast<pixel, 0>(sp8 - tp, sp8 + tp, v, lo, hi, maxv, o);
+        else if (eo == 2) sao_edge_fast<pixel, -1>(sp8 - tp, sp8 + tp, v, lo, hi, maxv, o);
+        else sao_edge_fast<pixel, 1>(sp8 - tp, sp8 + tp, v, lo, hi, maxv, o);
+        for (int i = 0; i < 8 && 8 * u + i < w; i++) dst[y * dp + 8 * u + i] = (pixel)o[i];
+    }
+}
+
+int dsp_sao(int bd, int edge, uint8_t *dst, const uint8_t *src, ptrdiff_t stride_dst, ptrdiff_t stride_src, const int16_t *offset_val,
+            int eo_or_band, int w, int h)
+{
+    const int P = bd > 8 ? 2 : 1;
+    if (w < 1 || w > 64 || h < 1 || h > 64) return -1;
+    for (int i = 0; i < 5; i++) if (offset_val[i] < -128 || offset_val[i] > 127) return -1;
+    uint32_t lo, hi;
+    const int16_t *ov = offset_val;
+    if (edge) { lo = (ov[1] & 0xff) | (ov[2] & 0xff) << 8 | (ov[0] & 0xff) << 16 | (uint32_t)(ov[3] & 0xff) << 24; hi = ov[4] & 0xff; }
+    else { lo = (ov[1] & 0xff) | (ov[2] & 0xff) << 8 | (ov[3] & 0xff) << 16 | (uint32_t)(ov[4] & 0xff) << 24; hi = 0; }
+    const int tp = 96;                                   // samples per tile row: 8 + 64 + slack, rows 16-byte aligned
+    const size_t tbytes = (size_t)tp * P * (h + 2), dbytes = (size_t)64 * P * h;
+    uint8_t *d = nullptr;
+    if (cudaMalloc((void **)&d, tbytes + dbytes + 256) != cudaSuccess) return -1;
+    uint8_t *d_dst = d + ((tbytes + 255) & ~(size_t)255);
+    cudaMemset(d, 0, tbytes);
+    int rc = -1;
+    // edge: rows -1..h and columns -1..w of src exist (the caller's halo); band: the block only
+    const int halo = edge ? 1 : 0;
+    const uint8_t *s0 = src - halo * stride_src - halo * P;
+    uint8_t *t0 = d + ((size_t)(1 - halo) * tp + (8 - halo)) * P;
+    if (cudaMemcpy2D(t0, (size_t)tp * P, s0, stride_src, (size_t)(w + 2 * halo) * P, h + 2 * halo, cudaMemcpyHostToDevice) == cudaSuccess) {
+        if (bd > 8) dsp_sao_kernel<uint16_t><<<1, 256>>>((const uint16_t *)d, tp, (uint16_t *)d_dst, 64, w, h, bd, edge, eo_or_band, eo_or_band, lo, hi);
+        else dsp_sao_kernel<uint8_t><<<1, 256>>>(d, tp, d_dst, 64, w, h, bd, edge, eo_or_band, eo_or_band, lo, hi);
+        if (cudaDeviceSynchronize() == cudaSuccess &&
+            cudaMemcpy2D(dst, stride_dst, d_dst, (size_t)64 * P, (size_t)w * P, h, cudaMemcpyDeviceToHost) == cudaSuccess) rc = 0;
+    }
+    cudaFree(d);
+    return rc;
 }
 
 }  // namespace ohcu

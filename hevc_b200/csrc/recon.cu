@@ -429,8 +429,10 @@ __device__ __forceinline__ void tile_add_pair(uint32_t *w, int r0, int r1, int m
 
 // One N x N block by the whole warp.  src: row-major coefficients in shared memory, 16-byte
 // aligned; t1: N x (N + 8) int16 of scratch; tw: tile word of the block's first sample.
+// raw: store the residual pairs instead of adding them (per-entry test shim ohcu_dsp_idct).
 template <int LOG2>
-__device__ __noinline__ void idct_mma(const int16_t *src, int16_t *t1, uint32_t *tw, int tpitch, int col_limit, int bd, int lane)
+__device__ __noinline__ void idct_mma(const int16_t *src, int16_t *t1, uint32_t *tw, int tpitch, int col_limit, int bd, int lane,
+                                      bool raw = false)
 {
     constexpr int N = 1 << LOG2, ST = N + 8, NQ = N / 8, NH = N / 16;
     const int g = lane >> 2, t = lane & 3;
@@ -524,8 +526,13 @@ __device__ __noinline__ void idct_mma(const int16_t *src, int16_t *t1, uint32_t 
             for (int h = 0; h < NH; h++)
                 imma16<false, true>(acc, al[h][0], al[h][1], F[nt][h]);
             const int y = 16 * mt + g, xw = 4 * nt + t;
-            tile_add_pair(tw + y * tpitch + xw, clip_s16(acc[0] >> sh), clip_s16(acc[1] >> sh), maxv);
-            tile_add_pair(tw + (y + 8) * tpitch + xw, clip_s16(acc[2] >> sh), clip_s16(acc[3] >> sh), maxv);
+            if (raw) {
+                tw[y * tpitch + xw] = pack_sat16(acc[0] >> sh, acc[1] >> sh);
+                tw[(y + 8) * tpitch + xw] = pack_sat16(acc[2] >> sh, acc[3] >> sh);
+            } else {
+                tile_add_pair(tw + y * tpitch + xw, clip_s16(acc[0] >> sh), clip_s16(acc[1] >> sh), maxv);
+                tile_add_pair(tw + (y + 8) * tpitch + xw, clip_s16(acc[2] >> sh), clip_s16(acc[3] >> sh), maxv);
+            }
         }
     }
     __syncwarp();
@@ -1210,6 +1217,198 @@ int launch_recon(const FrameDev &f, int flags, cudaStream_t st)
     if (f.bd > 8) recon_kernel<true><<<nctb, RC_THREADS, smem, st>>>(f, flags);
     else          recon_kernel<false><<<nctb, RC_THREADS, smem, st>>>(f, flags);
     return 1;
+}
+
+// ================================================================= per-entry test shims
+// One block through the SAME device code as the frame kernels (mc_filter + epi_pair,
+// tb_residual, idct_mma, tile_add_pair), behind entry points with the argument meaning of
+// the reference's table (ohcu.h: ohcu_dsp_*).  Test infrastructure for tests/test_gpu_leaves.py.
+struct DspMc {
+    const uint8_t *win;       // device copy of the source window: rows h + NT - 1, first needed sample at column 0
+    int pitch;                // bytes, multiple of 16
+    int w, h, mx, my, luma, family, bd;        // family: 0 put, 1 uni, 2 uni_w, 3 bi, 4 bi_w
+    Epi e;
+    const int16_t *src2;      // bi: first list's intermediates, stride 64 (MAX_PB_SIZE, hevcdec.h:51)
+    int16_t *out16;           // put: stride 64
+    uint8_t *dst;             // w x h pixels, pitch dpitch bytes
+    int dpitch;
+};
+
+template <bool HIGH, int NT, int OW, int OH>
+__device__ __forceinline__ void dsp_mc_cell(const DspMc &a, int cx, int cy)
+{
+    uint32_t res[OH][OW / 2];
+    const int sh1 = a.bd - 8;
+    if (NT == 8)
+        mc_filter<HIGH, NT, OW, OH>(a.win, a.pitch, cx * OW, cy * OH, c_qpel4[a.mx][0], c_qpel4[a.mx][1], c_qpel4[a.my][0],
+                                    c_qpel4[a.my][1], sh1, res);
+    else
+        mc_filter<HIGH, NT, OW, OH>(a.win, a.pitch, cx * OW, cy * OH, c_epel4[a.mx][0], 0, c_epel4[a.my][0], 0, sh1, res);
+#pragma unroll
+    for (int r = 0; r < OH; r++)
+#pragma unroll
+        for (int k = 0; k < OW / 2; k++) {
+            const int x = cx * OW + 2 * k, y = cy * OH + r;
+            if (x >= a.w || y >= a.h) continue;
+            if (a.family == 0) {
+                *(uint32_t *)&a.out16[y * 64 + x] = res[r][k];
+                continue;
+            }
+            const uint32_t prev = a.family >= 3 ? *(const uint32_t *)&a.src2[y * 64 + x] : 0u;
+            uint32_t o;
+            epi_pair(a.e, res[r][k], prev, &o);
+            if (HIGH) *(uint32_t *)(a.dst + (size_t)y * a.dpitch + 2 * x) = o;
+            else *(uint16_t *)(a.dst + (size_t)y * a.dpitch + x) = (uint16_t)((o & 0xffu) | ((o >> 8) & 0xff00u));
+        }
+}
+
+template <bool HIGH>
+__global__ void dsp_mc_kernel(const DspMc a)
+{
+    const int ow = a.luma ? 4 : 2, oh = a.luma ? 4 : 2;
+    const int ncx = (a.w + ow - 1) / ow, ncy = (a.h + oh - 1) / oh;
+    for (int i = threadIdx.x; i < ncx * ncy; i += blockDim.x) {
+        const int cy = i / ncx, cx = i - cy * ncx;
+        if (a.luma) dsp_mc_cell<HIGH, 8, 4, 4>(a, cx, cy);
+        else dsp_mc_cell<HIGH, 4, 2, 2>(a, cx, cy);
+    }
+}
+
+// scratch shared by the shim entry points (tests are single-threaded)
+static uint8_t *dsp_scratch(size_t bytes)
+{
+    static uint8_t *buf = nullptr;
+    static size_t cap = 0;
+    if (bytes > cap) {
+        if (buf) cudaFree(buf);
+        cap = bytes < (1u << 20) ? (1u << 20) : bytes;
+        if (cudaMalloc((void **)&buf, cap) != cudaSuccess) { buf = nullptr; cap = 0; }
+    }
+    return buf;
+}
+static int dsp_tables()
+{
+    static bool done = false;
+    if (!done) {
+        if (upload_mc_taps() || upload_dct_table()) return -1;
+        done = true;
+    }
+    return 0;
+}
+
+int dsp_mc(int bd, int luma, int family, uint8_t *dst, ptrdiff_t dststride, const uint8_t *src, ptrdiff_t srcstride,
+           const int16_t *src2, int16_t *out16, int h, int denom, int wx0, int wx1, int ox0, int ox1, int mx, int my, int w)
+{
+    if (dsp_tables()) return -1;
+    const int P = bd > 8 ? 2 : 1, NT = luma ? 8 : 4, BEFORE = luma ? 3 : 1;
+    if (w < 2 || w > 64 || h < 2 || h > 64 || (w & 1) || (h & 1) || mx < 0 || my < 0 || mx > (luma ? 3 : 7) || my > (luma ? 3 : 7)) return -1;
+    const int rows = h + NT - 1, pitch = (((w + NT + 8) * P) + 15) & ~15;
+    const size_t win_bytes = (size_t)rows * pitch, dpitch = (size_t)((w * P + 15) & ~15);
+    uint8_t *base = dsp_scratch(win_bytes + 64 * 64 * 2 * 2 + dpitch * h + 256);
+    if (!base) return -1;
+    uint8_t *d_win = base, *d_src2 = base + ((win_bytes + 255) & ~(size_t)255), *d_out16 = d_src2 + 64 * 64 * 2, *d_dst = d_out16 + 64 * 64 * 2;
+    cudaMemset(d_win, 0, win_bytes);
+    // the window as the reference reads it: BEFORE rows / columns ahead of src, NT - 1 - BEFORE behind
+    const uint8_t *s0 = src - (ptrdiff_t)BEFORE * srcstride - BEFORE * P;
+    if (cudaMemcpy2D(d_win, pitch, s0, srcstride, (size_t)(w + NT - 1) * P, rows, cudaMemcpyHostToDevice) != cudaSuccess) return -1;
+    if (family >= 3 && cudaMemcpy(d_src2, src2, 64 * 64 * 2, cudaMemcpyHostToDevice) != cudaSuccess) return -1;
+    DspMc a{};
+    a.win = d_win; a.pitch = pitch; a.w = w; a.h = h; a.mx = mx; a.my = my; a.luma = luma; a.family = family; a.bd = bd;
+    a.src2 = (const int16_t *)d_src2; a.out16 = (int16_t *)d_out16; a.dst = d_dst; a.dpitch = (int)dpitch;
+    Epi &e = a.e;                                  // the table of `Epi` above
+    e.maxv = (1 << bd) - 1; e.wB = 0; e.post = 0;
+    const int sc = 1 << (bd - 8);
+    if (family == 1) { e.wA = 1; e.sh = 14 - bd; e.add = 1 << (13 - bd); }
+    else if (family == 2) { e.wA = wx0; e.sh = denom + 14 - bd; e.add = 1 << (e.sh - 1); e.post = ox0 * sc; }
+    else if (family == 3) { e.wA = 1; e.wB = 1; e.sh = 15 - bd; e.add = 1 << (14 - bd); }
+    else if (family == 4) {
+        const int log2Wd = denom + 14 - bd;
+        e.wA = wx1; e.wB = wx0; e.sh = log2Wd + 1; e.add = (ox0 * sc + ox1 * sc + 1) * (1 << log2Wd);
+    } else { e.wA = 1; e.sh = 0; e.add = 0; }
+    if (bd > 8) dsp_mc_kernel<true><<<1, 256>>>(a);
+    else dsp_mc_kernel<false><<<1, 256>>>(a);
+    if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+    if (family == 0) {
+        // rows of 64 int16; only the block is defined
+        return cudaMemcpy2D(out16, 64 * 2, d_out16, 64 * 2, (size_t)w * 2, h, cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -1;
+    }
+    return cudaMemcpy2D(dst, dststride, d_dst, dpitch, (size_t)w * P, h, cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -1;
+}
+
+// residual entries: idct[], idct_dc[], idct_4x4_luma, transform_skip, transform_rdpcm (in place on coeffs)
+template <int LOG2>
+__global__ void dsp_residual_kernel(int16_t *coef, ohcu_tu tu, int bd, int use_mma)
+{
+    constexpr int N = 1 << LOG2, S = Stride<N>::S;
+    __shared__ __align__(16) int16_t src[N * N];
+    __shared__ __align__(16) int16_t t1[N * (N + 8)];
+    __shared__ __align__(16) int16_t blk[N * S];
+    __shared__ uint32_t outw[N * N / 2];
+    const int lane = threadIdx.x;
+    if constexpr (LOG2 >= 4) {
+        if (use_mma) {
+            for (int i = lane; i < N * N; i += 32) src[i] = coef[i];
+            __syncwarp();
+            idct_mma<LOG2>(src, t1, outw, N / 2, tu.col_limit, bd, lane, true);
+            __syncwarp();
+            for (int i = lane; i < N * N / 2; i += 32) ((uint32_t *)coef)[i] = outw[i];
+            return;
+        }
+    }
+    if (lane < N) {
+        const unsigned mask = N == 32 ? 0xffffffffu : ((1u << N) - 1u);
+        tb_residual<LOG2>(bd, tu, coef, blk, lane, mask);
+        for (int k = 0; k < N; k++) coef[lane * N + k] = blk[lane * S + k];
+    }
+}
+
+int dsp_residual(int bd, int mode, int flags, int16_t *coeffs, int log2, int col_limit, int use_mma)
+{
+    if (dsp_tables() || log2 < 2 || log2 > 5) return -1;
+    const size_t bytes = (size_t)2 << (2 * log2);
+    int16_t *d = (int16_t *)dsp_scratch(bytes);
+    if (!d || cudaMemcpy(d, coeffs, bytes, cudaMemcpyHostToDevice) != cudaSuccess) return -1;
+    ohcu_tu tu{};
+    tu.log2_size = (uint8_t)log2; tu.mode = (uint8_t)mode; tu.flags = (uint8_t)flags; tu.col_limit = (int8_t)col_limit;
+    switch (log2) {
+    case 2: dsp_residual_kernel<2><<<1, 32>>>(d, tu, bd, 0); break;
+    case 3: dsp_residual_kernel<3><<<1, 32>>>(d, tu, bd, 0); break;
+    case 4: dsp_residual_kernel<4><<<1, 32>>>(d, tu, bd, use_mma); break;
+    default: dsp_residual_kernel<5><<<1, 32>>>(d, tu, bd, use_mma); break;
+    }
+    if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+    return cudaMemcpy(coeffs, d, bytes, cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -1;
+}
+
+// transform_add[] (template :45-84): dst block += coeffs, clipped
+template <bool HIGH>
+__global__ void dsp_transform_add_kernel(uint8_t *dst, int dpitch, const int16_t *coef, int n, int bd)
+{
+    const int maxv = (1 << bd) - 1;
+    for (int i = threadIdx.x; i < n * n / 2; i += blockDim.x) {
+        const int y = i / (n / 2), x = 2 * (i - y * (n / 2));
+        uint8_t *p = dst + (size_t)y * dpitch + x * (HIGH ? 2 : 1);
+        uint32_t w = HIGH ? *(uint32_t *)p : ((uint32_t)p[0] | ((uint32_t)p[1] << 16));
+        tile_add_pair(&w, coef[y * n + x], coef[y * n + x + 1], maxv);
+        if (HIGH) *(uint32_t *)p = w;
+        else { p[0] = (uint8_t)w; p[1] = (uint8_t)(w >> 16); }
+    }
+}
+
+int dsp_transform_add(int bd, uint8_t *dst, const int16_t *coeffs, ptrdiff_t stride, int n)
+{
+    const int P = bd > 8 ? 2 : 1;
+    if (n != 4 && n != 8 && n != 16 && n != 32) return -1;
+    const size_t dpitch = (size_t)((n * P + 15) & ~15);
+    uint8_t *base = dsp_scratch(dpitch * n + (size_t)n * n * 2 + 256);
+    if (!base) return -1;
+    int16_t *d_c = (int16_t *)(base + ((dpitch * n + 255) & ~(size_t)255));
+    if (cudaMemcpy2D(base, dpitch, dst, stride, (size_t)n * P, n, cudaMemcpyHostToDevice) != cudaSuccess) return -1;
+    if (cudaMemcpy(d_c, coeffs, (size_t)n * n * 2, cudaMemcpyHostToDevice) != cudaSuccess) return -1;
+    if (bd > 8) dsp_transform_add_kernel<true><<<1, 128>>>(base, (int)dpitch, d_c, n, bd);
+    else dsp_transform_add_kernel<false><<<1, 128>>>(base, (int)dpitch, d_c, n, bd);
+    if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+    return cudaMemcpy2D(dst, stride, base, dpitch, (size_t)n * P, n, cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -1;
 }
 
 }  // namespace ohcu

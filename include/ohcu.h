@@ -297,6 +297,57 @@ int ohcu_timer_stop(ohcu_ctx *ctx, float *ms);
 int ohcu_host_alloc(size_t bytes, void **ptr);
 int ohcu_host_free(void *ptr);
 
+/* ======================================================================== */
+/* Per-entry test shims                                                     */
+/* ======================================================================== */
+/* One block through the device code of the frame kernels, with the argument meaning of the
+ * reference's table entries (hevcdsp.h:51-166), so that the table semantics can be tested
+ * 1:1 against ff_hevc_dsp_init (tests/test_gpu_leaves.py, same cases as the oracle-vs-
+ * reference test).  bd = bit depth; luma: 1 = put_hevc_qpel* (mx, my in quarter samples),
+ * 0 = put_hevc_epel* (eighths).  Host pointers, synchronous, NOT a production path.
+ *   put_hevc_{q,e}pel[idx][my][mx]        hevcdsp.h:97-98, :112-113   int16 dst, stride 64    */
+int ohcu_dsp_mc_put(int bd, int luma, int16_t *dst, const uint8_t *src, ptrdiff_t srcstride,
+                    int height, int mx, int my, int width);
+/*  put_hevc_{q,e}pel_uni                  hevcdsp.h:99-100, :115-116                          */
+int ohcu_dsp_mc_uni(int bd, int luma, uint8_t *dst, ptrdiff_t dststride, const uint8_t *src,
+                    ptrdiff_t srcstride, int height, int mx, int my, int width);
+/*  put_hevc_{q,e}pel_uni_w                hevcdsp.h:101-102, :117-118                         */
+int ohcu_dsp_mc_uni_w(int bd, int luma, uint8_t *dst, ptrdiff_t dststride, const uint8_t *src,
+                      ptrdiff_t srcstride, int height, int denom, int wx, int ox, int mx, int my,
+                      int width);
+/*  put_hevc_{q,e}pel_bi (src2: int16, stride 64)   hevcdsp.h:104-106, :119-121               */
+int ohcu_dsp_mc_bi(int bd, int luma, uint8_t *dst, ptrdiff_t dststride, const uint8_t *src,
+                   ptrdiff_t srcstride, const int16_t *src2, int height, int mx, int my, int width);
+/*  put_hevc_{q,e}pel_bi_w, parameters in the order the implementation takes them
+ *  (denom, wx0, wx1, ox0, ox1 — hevcdsp_template.c:3202-3205)   hevcdsp.h:107-110, :122-125   */
+int ohcu_dsp_mc_bi_w(int bd, int luma, uint8_t *dst, ptrdiff_t dststride, const uint8_t *src,
+                     ptrdiff_t srcstride, const int16_t *src2, int height, int denom, int wx0,
+                     int wx1, int ox0, int ox1, int mx, int my, int width);
+/*  idct[log2-2], idct_dc[log2-2], idct_4x4_luma, transform_skip, transform_rdpcm (in place),
+ *  transform_add[log2-2]                                       hevcdsp.h:55-65               */
+int ohcu_dsp_idct(int bd, int16_t *coeffs, int log2_size, int col_limit);
+int ohcu_dsp_idct_dc(int bd, int16_t *coeffs, int log2_size);
+int ohcu_dsp_idct_4x4_luma(int bd, int16_t *coeffs);
+int ohcu_dsp_transform_skip(int bd, int16_t *coeffs, int log2_size);
+int ohcu_dsp_transform_rdpcm(int bd, int16_t *coeffs, int log2_size, int mode);
+int ohcu_dsp_transform_add(int bd, uint8_t *dst, const int16_t *coeffs, ptrdiff_t stride, int n);
+/*  hevc_{h,v}_loop_filter_{luma,chroma}: pix = first Q sample, tc / no_p / no_q per 4-line
+ *  segment                                                     hevcdsp.h:128-131             */
+int ohcu_dsp_loop_filter_luma(int bd, int vertical, uint8_t *pix, ptrdiff_t stride, int beta,
+                              const int *tc, const uint8_t *no_p, const uint8_t *no_q);
+int ohcu_dsp_loop_filter_chroma(int bd, int vertical, uint8_t *pix, ptrdiff_t stride,
+                                const int *tc, const uint8_t *no_p, const uint8_t *no_q);
+/*  sao_band_filter / sao_edge_filter with SAOParams reduced to offset_val[5] and
+ *  band_position / eo_class of the plane (src carries the 1-sample halo the edge classes
+ *  read).  sao_edge_restore has no per-entry shim: the frame kernel applies the border rules
+ *  per CTB (tests/test_gpu_parity.py covers every flag).      hevcdsp.h:67-71               */
+int ohcu_dsp_sao_band_filter(int bd, uint8_t *dst, const uint8_t *src, ptrdiff_t stride_dst,
+                             ptrdiff_t stride_src, const int16_t *offset_val, int band_position,
+                             int width, int height);
+int ohcu_dsp_sao_edge_filter(int bd, uint8_t *dst, const uint8_t *src, ptrdiff_t stride_dst,
+                             ptrdiff_t stride_src, const int16_t *offset_val, int eo, int width,
+                             int height);
+
 #ifdef __cplusplus
 }
 #endif
