@@ -168,7 +168,10 @@ def run_ours(args, rank, world):
     device = int(os.environ.get("LOCAL_RANK", 0))
     hbm_peak, peak_kind = peaks()
     # the e2e leg keeps 2B frames in flight (B being filled / uploaded while B run and drain)
-    ctx = backend.Context(sp, device=device, dpb_slots=2 + 2 * B, jobs=2 * B)
+    if B % N_DISTINCT:
+        raise SystemExit(f"--frames must be a multiple of {N_DISTINCT} (the job ring is revisited with the same frame contents)")
+    E = min(2 * B, 28)                       # ring depth of the e2e leg (2 reference slots + E <= 32 DPB slots)
+    ctx = backend.Context(sp, device=device, dpb_slots=2 + max(B, E), jobs=max(B, E))
     lib, h = ctx.lib, ctx.handle
     for s in range(2):
         ctx.upload(s, refs[s])
@@ -212,12 +215,12 @@ def run_ours(args, rank, world):
     ctx.set_profiling(False)
 
     # ---------------- e2e leg: host buffers -> H2D -> kernels -> D2H, through the C ABI
-    outs = [ctx.pinned_picture() for _ in range(2 * B)]
+    outs = [ctx.pinned_picture() for _ in range(E)]
     h2d = d2h = 0
 
     def submit(i, copy_coeffs=False):
         nonlocal h2d, d2h
-        k = i % (2 * B)                      # output slot / pinned output buffer of this frame
+        k = i % E                            # output slot / pinned output buffer of this frame
         fj = jobs[k % len(jobs)]
         j = ctx.begin(2 + k)
         for i in range(len(fj.slices)):
@@ -248,13 +251,13 @@ def run_ours(args, rank, world):
     pool = ThreadPoolExecutor(max(1, min(args.host_threads, B)))
     # untimed first pass over every job arena of the ring (puts the coefficients in place);
     # the resident leg left the ring at job B, so 2B submissions visit each arena once
-    for i in range(2 * B):
+    for i in range(max(B, E)):
         ctx.sync()
         submit(i, copy_coeffs=True)
     ctx.sync()
     list(pool.map(submit, range(args.warmup * B)))
     ctx.sync()
-    for k in range(2 * B):
+    for k in range(E):
         ctx.slot_sync(2 + k)
     barrier()
     ctx.timer_start()
@@ -300,7 +303,7 @@ def run_ours(args, rank, world):
         "vs_baseline": None, "dtype": "int32 accumulate on u16 samples / int16 coefficients" if sp.bit_depth > 8
         else "int32 accumulate on u8 samples / int16 coefficients", "data": "synthetic",
         "config": {"workload": WORKLOAD_NAMES[args.workload], "frames_per_step_per_gpu": B,
-                   "frames_in_flight": B, "frames_in_flight_e2e": 2 * B, "distinct_frames": len(jobs), "sharding": "independent frames per GPU, no collective",
+                   "frames_in_flight": B, "frames_in_flight_e2e": E, "distinct_frames": len(jobs), "sharding": "independent frames per GPU, no collective",
                    "l2": f"inputs larger than L2: {B} frames x ~{(ab['pipeline']) / 1e6:.0f} MB algorithmic traffic per step",
                    "pus_per_frame": int(len(jobs[0].pus)), "tus_per_frame": int(len(jobs[0].tus)),
                    "coded_fraction": round(len(jobs[0].coeffs) / (ab['S'] / (2 if sp.bit_depth > 8 else 1)), 3)},

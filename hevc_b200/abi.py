@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libohcu.so")
+# OHCU_LIB selects another build of the same library (A/B measurements of kernel variants)
+LIB_PATH = os.environ.get("OHCU_LIB") or os.path.join(HERE, "libohcu.so")
 
 OHCU_ABI_VERSION = 1
 MAX_REFS = 16

@@ -534,6 +534,9 @@ extern "C" int ohcu_append_pu(ohcu_ctx *c, int job, const ohcu_pu *recs, int n)
     ohcu_pu *const dst = j.pus.h + j.n_pu;
     int last = j.last_ctb, max_slice = j.max_slice;
     bool sorted = j.pu_sorted;
+    // PUs wider or taller than 32 are cut into <= 32x32 pieces with the same motion: prediction is
+    // per sample, so the result is the same, and the kernel's window pool can work in small slots
+    int o = 0;                                             // records written
     for (int i = 0; i < n; i++) {
         const ohcu_pu pu = recs[i];
         if (pu.pred_flag < 1 || pu.pred_flag > 3 || pu.w < 4 || pu.h < 4 || pu.w > 64 || pu.h > 64 ||
@@ -541,16 +544,29 @@ extern "C" int ohcu_append_pu(ohcu_ctx *c, int job, const ohcu_pu *recs, int n)
             pu.ref_idx[0] >= OHCU_MAX_REFS || pu.ref_idx[1] >= OHCU_MAX_REFS)
             return fail(OHCU_EINVAL, "PU record %d is malformed", base + i);
         const int ctb = (pu.x0 >> l2) + (pu.y0 >> l2) * ctb_w;
+        const int pieces = ((pu.w + 31) >> 5) * ((pu.h + 31) >> 5);
+        if ((size_t)base + o + pieces > j.pus.cap) return fail(OHCU_EOVERFLOW, "PU arena full (%zu)", j.pus.cap);
         if (ctb != last) {
             if (range[ctb].y != 0) sorted = false;           // CTB seen before: lists not grouped
-            else range[ctb].x = base + i;
+            else range[ctb].x = base + o;
             last = ctb;
         }
-        range[ctb].y++;
+        range[ctb].y += pieces;
         area[ctb] += pu.w * pu.h;
         max_slice = std::max(max_slice, (int)pu.slice);
-        dst[i] = pu;
+        if (pieces == 1) {
+            dst[o++] = pu;
+        } else {
+            for (int yy = 0; yy < pu.h; yy += 32)
+                for (int xx = 0; xx < pu.w; xx += 32) {
+                    ohcu_pu sub = pu;
+                    sub.x0 = (uint16_t)(pu.x0 + xx); sub.y0 = (uint16_t)(pu.y0 + yy);
+                    sub.w = (uint8_t)std::min(32, pu.w - xx); sub.h = (uint8_t)std::min(32, pu.h - yy);
+                    dst[o++] = sub;
+                }
+        }
     }
+    n = o;
     j.last_ctb = last; j.pu_sorted = sorted; j.max_slice = max_slice;
     j.n_pu += n;
     return 0;

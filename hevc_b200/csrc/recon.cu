@@ -44,10 +44,14 @@ constexpr int MAX_CTB_PUS = 128;             // 8x4 PUs of a 64x64 CTB
 constexpr int MAX_CTB_CELLS = 256;           // 4x4 cells of a 64x64 CTB
 constexpr int MAX_CTB_TUS = 768;             // 4x4 TBs of a 64x64 CTB, 3 full-size planes
 constexpr int POOL_UNIT = 128;               // every TMA box is a multiple of 128 bytes
-constexpr int HALF_UNITS = 180;              // one round of windows: 22.5 KB = the largest window pair (4:4:4 chroma, 2 x 80 x 72 x 2)
+constexpr int ROUND_ROTATE = 128;            // threads by which the cell assignment shifts from round to round
+constexpr int POOL_SLOTS = 2;                // rounds resident at a time: one being filtered, one in flight
+                                             // (measured: 2 x 22 KB 0.191 ms, 3 x 15 KB 0.199 ms, 4 x 11 KB 0.207 ms per 4K frame)
+constexpr int HALF_UNITS = 176;              // one round of windows: 22 KB; the largest PU the kernel sees is 32x32
+                                             // (split at append time), both windows 2 x 48 x 40 x 2 B = 60 units
 constexpr int HALF_BYTES = HALF_UNITS * POOL_UNIT;
-constexpr int POOL_BYTES = 2 * HALF_BYTES;   // two rounds: one being filtered, one in flight
-constexpr int MAX_ROUNDS = 8;                // per kind (5 in the worst case: 128 8x4 PUs)
+constexpr int POOL_BYTES = POOL_SLOTS * HALF_BYTES;
+constexpr int MAX_ROUNDS = 24;               // per plane type (18 in the worst case: 128 bi-predicted 8x4 PUs)
 constexpr int N_KINDS = 4;                   // list slot A luma, slot B luma, slot A chroma, slot B chroma
 
 // scratch of one warp in the residual phase (aliases the window pool): one 32x32 int16 block
@@ -278,7 +282,8 @@ template <int N> struct Stride { static constexpr int S = N + 2; };   // int16 r
 // one TB: coefficients -> residual, in place in blk[N][S]; N lanes (g = 0..N-1) cooperate
 // coef: the TB's N*N coefficients (shared-memory copy of the CTB's arena range, or global)
 template <int LOG2>
-__device__ __noinline__ void tb_residual(int bd, const ohcu_tu &tu, const int16_t *coef, int16_t *blk, int g, unsigned mask)
+__device__ __noinline__ void tb_residual(int bd, int mode, int tuflags, int col_limit, const int16_t *coef, int16_t *blk, int g,
+                                         unsigned mask)
 {
     constexpr int N = 1 << LOG2, S = Stride<N>::S;
     {
@@ -291,9 +296,7 @@ __device__ __noinline__ void tb_residual(int bd, const ohcu_tu &tu, const int16_
     }
     __syncwarp(mask);
 
-    const int mode = tu.mode;
     if (mode == OHCU_TU_IDCT) {
-        const int col_limit = tu.col_limit;
         int in[N], out[N];
         // columns (shift 7); zero-skip bound shrinks by 4 every 4 columns (template :256-262)
         {
@@ -340,7 +343,7 @@ __device__ __noinline__ void tb_residual(int bd, const ohcu_tu &tu, const int16_
         // OHCU_TU_SKIP / OHCU_TU_BYPASS (hevc_cabac.c:1727-1757)
         if (mode == OHCU_TU_SKIP) {
             if constexpr (N == 4) {
-                if (tu.flags & OHCU_TUF_ROTATE) {              // coeffs[i] <-> coeffs[15 - i]
+                if (tuflags & OHCU_TUF_ROTATE) {              // coeffs[i] <-> coeffs[15 - i]
                     int16_t v[4];
 #pragma unroll
                     for (int k = 0; k < 4; k++) v[k] = blk[(3 - g) * S + (3 - k)];
@@ -358,8 +361,8 @@ __device__ __noinline__ void tb_residual(int bd, const ohcu_tu &tu, const int16_
             }
             __syncwarp(mask);
         }
-        if (tu.flags & OHCU_TUF_RDPCM) {                       // transform_rdpcm, template :87-107
-            if (tu.flags & OHCU_TUF_RDPCM_VERT) {
+        if (tuflags & OHCU_TUF_RDPCM) {                       // transform_rdpcm, template :87-107
+            if (tuflags & OHCU_TUF_RDPCM_VERT) {
                 int16_t acc = blk[g];
                 for (int y = 1; y < N; y++) { acc = (int16_t)(acc + blk[y * S + g]); blk[y * S + g] = acc; }
             } else {
@@ -549,8 +552,12 @@ __device__ __forceinline__ void dc_block(int log2, int c0, uint32_t *tw, int tpi
 // A warp takes 32/N TBs of one size class at a time (lane group = one TB) and adds their
 // residual into the CTB tile: transform_add (template :45-84).
 struct CtbTile {
-    uint32_t *p[3];       // tile words of each plane
-    int pitch[3];         // words per tile row
+    uint32_t *base;       // plane 0; planes 1 and 2 follow (same geometry)
+    int size0, sizec;     // words of plane 0 / of one chroma plane
+    int pitch0, pitchc;   // words per tile row
+    // no arrays: a run-time plane index into a local array would go through local memory
+    __device__ __forceinline__ uint32_t *p(int c) const { return base + (c > 0 ? size0 : 0) + (c > 1 ? sizec : 0); }
+    __device__ __forceinline__ int pitch(int c) const { return c ? pitchc : pitch0; }
 };
 
 // Where the coefficients of this CTB are: csm != nullptr -> arena range [clo, ...) copied to
@@ -585,12 +592,12 @@ __device__ void tu_batch(const FrameDev &f, const CtbTile &tile, int tu0, const 
     }
     if (have && !wide) {
         int16_t *blk = (int16_t *)&ws + (size_t)grp * N * S;
-        tb_residual<LOG2>(f.bd, tu, cs.at(tu.coeff_off, N * N), blk, g, mask);
+        tb_residual<LOG2>(f.bd, tu.mode, tu.flags, tu.col_limit, cs.at(tu.coeff_off, N * N), blk, g, mask);
         if ((tu.flags & OHCU_TUF_CROSS) && ws2) {                  // hevc_cabac.c:1810-1817
             int16_t *by = (int16_t *)ws2 + (size_t)grp * N * S;
             const ohcu_tu ty = f.tus[tu.cross_tu];
             if (ty.log2_size == LOG2) {
-                tb_residual<LOG2>(f.bd, ty, cs.at(ty.coeff_off, N * N), by, g, mask);
+                tb_residual<LOG2>(f.bd, ty.mode, ty.flags, ty.col_limit, cs.at(ty.coeff_off, N * N), by, g, mask);
                 const int scale = tu.res_scale_val;
 #pragma unroll
                 for (int k = 0; k < N; k++)
@@ -601,10 +608,10 @@ __device__ void tu_batch(const FrameDev &f, const CtbTile &tile, int tu0, const 
         const int c = tu.c_idx;
         const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
         const int maxv = (1 << f.bd) - 1;
-        uint16_t *t = (uint16_t *)tile.p[c] + (tu.y0 - (cy0 >> vs)) * (2 * tile.pitch[c]) + (tu.x0 - (cx0 >> hs)) + g;
+        uint16_t *t = (uint16_t *)tile.p(c) + (tu.y0 - (cy0 >> vs)) * (2 * tile.pitch(c)) + (tu.x0 - (cx0 >> hs)) + g;
 #pragma unroll 4
         for (int r = 0; r < N; r++) {
-            uint16_t *d = t + r * 2 * tile.pitch[c];
+            uint16_t *d = t + r * 2 * tile.pitch(c);
             *d = (uint16_t)min(max((int)*d + blk[r * S + g], 0), maxv);
         }
     }
@@ -620,9 +627,9 @@ __device__ void tu_batch(const FrameDev &f, const CtbTile &tile, int tu0, const 
             const int col_limit = __shfl_sync(0xffffffffu, (int)tu.col_limit, sl);
             const uint32_t off = __shfl_sync(0xffffffffu, tu.coeff_off, sl);
             const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
-            uint32_t *tw = tile.p[c] + (y0 - (cy0 >> vs)) * tile.pitch[c] + ((x0 - (cx0 >> hs)) >> 1);
-            if (mode == OHCU_TU_DC) dc_block(LOG2, cs.at(off, 1)[0], tw, tile.pitch[c], f.bd, lane);
-            else idct_mma<LOG2>(cs.csm + (off - cs.clo), (int16_t *)&ws, tw, tile.pitch[c], col_limit, f.bd, lane);
+            uint32_t *tw = tile.p(c) + (y0 - (cy0 >> vs)) * tile.pitch(c) + ((x0 - (cx0 >> hs)) >> 1);
+            if (mode == OHCU_TU_DC) dc_block(LOG2, cs.at(off, 1)[0], tw, tile.pitch(c), f.bd, lane);
+            else idct_mma<LOG2>(cs.csm + (off - cs.clo), (int16_t *)&ws, tw, tile.pitch(c), col_limit, f.bd, lane);
             __syncwarp();
         }
     }
@@ -670,7 +677,8 @@ __device__ __forceinline__ WinGeom win_geom(const FrameDev &f, const ohcu_pu &pu
     const int bw = pu.w >> hs, bh = pu.h >> vs;
     const int xo = pu.x0 >> hs, yo = pu.y0 >> vs;
     const int pw = f.pw[luma ? 0 : 1], ph = f.ph[luma ? 0 : 1];
-    const int mvx = pu.mv[l][0], mvy = pu.mv[l][1];
+    // explicit selects: a run-time index into the record would push it to local memory
+    const int mvx = l ? pu.mv[1][0] : pu.mv[0][0], mvy = l ? pu.mv[1][1] : pu.mv[0][1];
     int sx, sy;
     if (luma) {                                            // hevcdec.c:1753-1760
         g.mx = mvx & 3; g.my = mvy & 3;
@@ -799,9 +807,20 @@ __device__ __forceinline__ void unpack_epi(const uint32_t (&w)[3], int bd, Epi &
 }
 
 // flags: bit 0 run MC, bit 1 run the residual
+// -DRC_PROFILE: thread 0 of every CTA adds the cycles between phase marks to g_rc_prof (tools/rc_phases.py)
+#ifdef RC_PROFILE
+__device__ unsigned long long g_rc_prof[16];
+#define RC_MARK(i) do { if (threadIdx.x == 0) { const long long t_ = clock64(); atomicAdd(&g_rc_prof[i], (unsigned long long)(t_ - rc_t)); rc_t = t_; } } while (0)
+#else
+#define RC_MARK(i) do { } while (0)
+#endif
+
 template <bool HIGH>
 __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_constant__ FrameDev f, int flags)
 {
+#ifdef RC_PROFILE
+    long long rc_t = clock64();
+#endif
     extern __shared__ __align__(128) uint8_t smem_raw[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int ctb = blockIdx.x;
@@ -813,30 +832,29 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     // ---- shared memory carve-up
     uint8_t *pool = smem_raw;
     CtbTile tile;
-    int vw[3], vh[3];
     uint32_t *sp = (uint32_t *)(smem_raw + POOL_BYTES);
-#pragma unroll
-    for (int c = 0; c < 3; c++) {
-        const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
-        const int tw = cs >> hs, th = cs >> vs;
-        vw[c] = min(tw, f.pw[c] - (cx0 >> hs));
-        vh[c] = min(th, f.ph[c] - (cy0 >> vs));
-        tile.pitch[c] = (tw >> 1) + 2;
-        tile.p[c] = sp;
-        if (c < f.nplanes) sp += tile.pitch[c] * th;
-    }
+    // valid samples of this CTB per plane type (the picture may end inside it)
+    const int vw0 = min(cs, f.pw[0] - cx0), vh0 = min(cs, f.ph[0] - cy0);
+    const int vwc = f.nplanes == 3 ? min(cs >> f.hs, f.pw[1] - (cx0 >> f.hs)) : 0;
+    const int vhc = f.nplanes == 3 ? min(cs >> f.vs, f.ph[1] - (cy0 >> f.vs)) : 0;
+    tile.base = sp;
+    tile.pitch0 = (cs >> 1) + 2;
+    tile.pitchc = ((cs >> f.hs) >> 1) + 2;
+    tile.size0 = tile.pitch0 * cs;
+    tile.sizec = f.nplanes == 3 ? tile.pitchc * (cs >> f.vs) : 0;
+    sp += tile.size0 + 2 * tile.sizec;
     PuRec *recs = (PuRec *)sp;                  sp += MAX_CTB_PUS * (sizeof(PuRec) / 4);
     int *cumA = (int *)sp;                      sp += MAX_CTB_PUS + 4;
     uint16_t *listA = (uint16_t *)sp;           sp += MAX_CTB_CELLS / 2;
     uint16_t *cumW = (uint16_t *)sp;            sp += 2 * (MAX_CTB_PUS + 2) / 2;         // [luma | chroma plane][PU] window units (128 B) before this PU
     uint8_t *nxt = (uint8_t *)sp;               sp += 2 * MAX_CTB_PUS / 4;               // [..][PU] first PU of the round after one starting here
     uint8_t *rstart = (uint8_t *)sp;            sp += 2 * (MAX_ROUNDS + 4) / 4;          // [..][round] first PU, [..][MAX_ROUNDS + 1] = count
-    int *done = (int *)sp;                      sp += 2;                                 // warps finished with each pool half
+    int *done = (int *)sp;                      sp += POOL_SLOTS;                        // warps finished with each pool slot
     int *scan_tmp = (int *)sp;                  sp += 2 * 4 * RC_WARPS;                  // [cells | units][class][warp]
     int *tu_cnt = (int *)sp;                    sp += 16;                         // [0..3] counts, [4..7] bases, [8..11] cursors, [12] coef lo, [13] coef hi, [14] batch counter
     uint16_t *tu_list = (uint16_t *)sp;         sp += MAX_CTB_TUS / 2;
     uint32_t *issue = sp;                       sp += N_KINDS * MAX_CTB_PUS * 2;  // TMA parameters per (kind, PU)
-    uint64_t *mbar = (uint64_t *)(((uintptr_t)sp + 7) & ~(uintptr_t)7);           sp += 6;     // one per pool half
+    uint64_t *mbar = (uint64_t *)(((uintptr_t)sp + 7) & ~(uintptr_t)7);           sp += 2 * POOL_SLOTS + 2;   // one per pool slot
     WarpScratch *scratch2 = f.cfi == 3 ? (WarpScratch *)(((uintptr_t)sp + 15) & ~(uintptr_t)15) : nullptr;   // cross-component
 
     const int2 prange = f.ctb_pu_range[ctb];
@@ -852,7 +870,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         for (int c = 0; c < f.nplanes; c++) {
             const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
             const uint8_t *plane = f.work.p[c] + (size_t)(cy0 >> vs) * f.work.pitch[c];
-            const int units = vw[c] >> 2, items = units * vh[c], inv = fastinv(units);
+            const int units = (c ? vwc : vw0) >> 2, items = units * (c ? vhc : vh0), inv = fastinv(units);
             for (int it = tid; it < items; it += RC_THREADS) {
                 const int r = fastdiv(it, inv), u = it - r * units;
                 uint2 o;
@@ -863,14 +881,15 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                     o.x = __byte_perm(v, 0, 0x4140);
                     o.y = __byte_perm(v, 0, 0x4342);
                 }
-                *(uint2 *)&tile.p[c][r * tile.pitch[c] + 2 * u] = o;
+                *(uint2 *)&tile.p(c)[r * tile.pitch(c) + 2 * u] = o;
             }
         }
     }
     if (tid < 12) tu_cnt[tid] = 0;
     if (tid == 12) { tu_cnt[12] = 0x7fffffff; tu_cnt[13] = 0; tu_cnt[14] = 0; }
-    if (tid == 0) { mbar_init(mbar, 1); mbar_init(mbar + 1, 1); done[0] = 0; done[1] = 0; }
+    if (tid < POOL_SLOTS) { mbar_init(mbar + tid, 1); done[tid] = 0; }
     __syncthreads();
+    RC_MARK(1);
 
     // ---- TBs of the CTB sorted by size (counting sort) and the arena range their coefficients
     //      occupy; runs while the first round of windows is in flight
@@ -897,7 +916,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         }
     };
 
-    uint32_t par0 = 0, par1 = 0;                           // phases of the two mbarriers
+    int rounds_done = 0;                                   // rounds that went through the pool (phase of mbar[0] afterwards)
     // ================================================================ phase 1: prediction
     if (do_mc) {
         // ---- 1a. four threads per PU: thread `sub` prepares the window of kind `sub` (list slot
@@ -931,7 +950,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                         const int bytes = pitch * box_h(g.hcls);
                         wu = bytes / POOL_UNIT;                // one plane: Cb and Cr run in separate rounds
                         // what the TMA issue of this window needs (box of plane pt; Cr follows Cb)
-                        const int slot = sl.ref_slot[l][pu.ref_idx[l] & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1);
+                        const int slot = sl.ref_slot[l][(l ? pu.ref_idx[1] : pu.ref_idx[0]) & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1);
                         uint32_t *iw = issue + (sub * MAX_CTB_PUS + p) * 2;
                         iw[0] = (uint32_t)tmap_index(slot, pt, g.wcls, g.hcls) | ((uint32_t)(g.ax + PAD_X) << 12);
                         iw[1] = (uint32_t)(g.y0 + PAD_Y) | ((uint32_t)(bytes >> 7) << 16);
@@ -947,7 +966,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                     int wx[2], ox[2];
 #pragma unroll
                     for (int l = 0; l < 2; l++) {
-                        const int ri = pu.ref_idx[l] & (OHCU_MAX_REFS - 1);
+                        const int ri = (l ? pu.ref_idx[1] : pu.ref_idx[0]) & (OHCU_MAX_REFS - 1);
                         wx[l] = c ? sl.chroma_weight[l][ri][c - 1] : sl.luma_weight[l][ri];
                         ox[l] = (c ? sl.chroma_offset[l][ri][c - 1] : sl.luma_offset[l][ri]) * (1 << (bd - 8));
                     }
@@ -999,6 +1018,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
             if (tid == 0) cumA[np] = carryC;
         }
         __syncthreads();
+        RC_MARK(2);
         const int totA = cumA[np];
 
         // ---- 1b. greedy rounds per plane type: nxt[pt][p] = first PU that no longer fits a round starting at p
@@ -1039,6 +1059,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
             }
         }
         __syncthreads();
+        RC_MARK(3);
 
         // ---- 1d. rounds, plane by plane, through the two pool halves.  No block barrier in the
         //      loop: a warp that has filtered its cells of round i goes on to round i + 1 (already
@@ -1046,6 +1067,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         const int sh1 = bd - 8;                            // first-stage shift (template :2486)
         const int nr0 = rstart[MAX_ROUNDS + 1], nr1 = npt == 2 ? rstart[(MAX_ROUNDS + 4) + MAX_ROUNDS + 1] : 0;
         const int R = nr0 + 2 * nr1;
+        rounds_done = R;
         auto locate = [&](int i, int &c, int &r) {        // flat round -> (plane, round of its plane type)
             if (i < nr0) { c = 0; r = i; }
             else if (i < nr0 + nr1) { c = 1; r = i - nr0; }
@@ -1058,8 +1080,8 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
             const uint8_t *rs = rstart + pt * (MAX_ROUNDS + 4);
             const int pa = rs[r], pb = rs[r + 1];
             const uint16_t *cw = cumW + pt * (MAX_CTB_PUS + 2);
-            uint64_t *bar = mbar + (i & 1);
-            uint8_t *buf = pool + (i & 1) * HALF_BYTES;
+            uint64_t *bar = mbar + (i % POOL_SLOTS);
+            uint8_t *buf = pool + (i % POOL_SLOTS) * HALF_BYTES;
             if (t == 0) mbar_expect_tx(bar, (uint32_t)(cw[pb] - cw[pa]) * POOL_UNIT);
             for (int p = pa + t; p < pb; p += n) {
                 uint8_t *dst = buf + (cw[p] - cw[pa]) * POOL_UNIT;
@@ -1074,9 +1096,10 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                 }
             }
         };
-        if (R > 0) issue_round(0, tid, RC_THREADS);
-        if (R > 1) issue_round(1, tid, RC_THREADS);
+#pragma unroll 1
+        for (int i = 0; i < min(R, POOL_SLOTS); i++) issue_round(i, tid, RC_THREADS);
         sort_tus();
+        RC_MARK(4);
 #pragma unroll 1
         for (int i = 0; i < R; i++) {
             int c, r;
@@ -1085,12 +1108,16 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
             const uint8_t *rs = rstart + pt * (MAX_ROUNDS + 4);
             const int pa = rs[r], pb = rs[r + 1];
             const uint16_t *cw = cumW + pt * (MAX_CTB_PUS + 2);
-            const uint8_t *buf = pool + (i & 1) * HALF_BYTES - cw[pa] * POOL_UNIT;
+            const int slot = i % POOL_SLOTS;
+            const uint8_t *buf = pool + slot * HALF_BYTES - cw[pa] * POOL_UNIT;
             const int clo = cumA[pa], chi = min(cumA[pb], MAX_CTB_CELLS);
-            mbar_wait(mbar + (i & 1), (i & 1) ? par1 : par0);
-            if (i & 1) par1 ^= 1; else par0 ^= 1;
+            RC_MARK(11);                                   // round bookkeeping
+            mbar_wait(mbar + slot, (i / POOL_SLOTS) & 1);
+            RC_MARK(12);                                   // waiting for the windows
 #pragma unroll 1
-            for (int ci = clo + tid; ci < chi; ci += RC_THREADS) {
+            // consecutive rounds start on different warps: with no barrier between rounds, the
+            // warps of a CTA then work on the resident rounds side by side
+            for (int ci = clo + ((tid - i * ROUND_ROTATE) & (RC_THREADS - 1)); ci < chi; ci += RC_THREADS) {
                 const int ent = listA[ci];
                 const int p = ent & 127, cx = (ent >> 7) & 15, cy = ent >> 11;
                 const PuRec &rc = recs[p];
@@ -1104,26 +1131,27 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                 const uint32_t ew[3] = {rc.epi[c][0], rc.epi[c][1], rc.epi[c][2]};
                 unpack_epi(ew, bd, e);
                 if (pt == 0) {
-                    uint32_t *tp = tile.p[0] + ((y4 + cy) * 4) * tile.pitch[0] + ((x4 + cx) * 2);
-                    mc_cell<HIGH, 8, 4, 4>(winA, gA, winB, gB, pbi, cx * 4, cy * 4, sh1, e, tp, tile.pitch[0]);
+                    uint32_t *tp = tile.p(0) + ((y4 + cy) * 4) * tile.pitch(0) + ((x4 + cx) * 2);
+                    mc_cell<HIGH, 8, 4, 4>(winA, gA, winB, gB, pbi, cx * 4, cy * 4, sh1, e, tp, tile.pitch(0));
                 } else {
                     const int hs = f.hs, vs = f.vs;
                     const int cw_ = 4 >> hs, ch = 4 >> vs;
-                    uint32_t *tp = tile.p[c] + ((y4 + cy) * ch) * tile.pitch[c] + (((x4 + cx) * cw_) >> 1);
-                    if (hs && vs) mc_cell<HIGH, 4, 2, 2>(winA, gA, winB, gB, pbi, cx * 2, cy * 2, sh1, e, tp, tile.pitch[c]);
-                    else if (hs) mc_cell<HIGH, 4, 2, 4>(winA, gA, winB, gB, pbi, cx * 2, cy * 4, sh1, e, tp, tile.pitch[c]);
-                    else mc_cell<HIGH, 4, 4, 4>(winA, gA, winB, gB, pbi, cx * 4, cy * 4, sh1, e, tp, tile.pitch[c]);
+                    uint32_t *tp = tile.p(c) + ((y4 + cy) * ch) * tile.pitch(c) + (((x4 + cx) * cw_) >> 1);
+                    if (hs && vs) mc_cell<HIGH, 4, 2, 2>(winA, gA, winB, gB, pbi, cx * 2, cy * 2, sh1, e, tp, tile.pitch(c));
+                    else if (hs) mc_cell<HIGH, 4, 2, 4>(winA, gA, winB, gB, pbi, cx * 2, cy * 4, sh1, e, tp, tile.pitch(c));
+                    else mc_cell<HIGH, 4, 4, 4>(winA, gA, winB, gB, pbi, cx * 4, cy * 4, sh1, e, tp, tile.pitch(c));
                 }
             }
             __syncwarp();
-            if (i + 2 < R) {
+            RC_MARK(13);                                   // cells
+            if (i + POOL_SLOTS < R) {
                 int old = 0;
-                if (lane == 0) old = atomicAdd(&done[i & 1], 1);
+                if (lane == 0) old = atomicAdd(&done[slot], 1);
                 old = __shfl_sync(0xffffffffu, old, 0);
-                if (old == RC_WARPS - 1) {                 // every warp has left this half
-                    if (lane == 0) done[i & 1] = 0;
+                if (old == RC_WARPS - 1) {                 // every warp has left this slot
+                    if (lane == 0) done[slot] = 0;
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    issue_round(i + 2, lane, 32);
+                    issue_round(i + POOL_SLOTS, lane, 32);
                 }
             }
         }
@@ -1131,8 +1159,10 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         sort_tus();
     }
 
+    RC_MARK(5);
     // ================================================================ phase 2: residual
     __syncthreads();          // prediction complete: the pool is free
+    RC_MARK(6);
     if (nt > 0) {
         // the CTB's coefficients sit in one arena range (TBs are appended CTB by CTB): one bulk
         // copy brings them next to the per-warp block buffers; ranges that do not fit are read
@@ -1147,7 +1177,8 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
                 asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                              ::"r"(smem_u32(coef_sm)), "l"(f.coeffs + clo), "r"(cbytes), "r"(smem_u32(mbar)) : "memory");
             }
-            mbar_wait(mbar, par0);
+            mbar_wait(mbar, ((rounds_done + POOL_SLOTS - 1) / POOL_SLOTS) & 1);
+            RC_MARK(7);
         }
         CoefSrc cs;
         cs.csm = staged ? coef_sm : nullptr; cs.clo = clo; cs.chi = chi; cs.glob = f.coeffs;
@@ -1156,6 +1187,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         // batches (32/N TBs of one size) are handed out dynamically, largest blocks first
         const int nb3 = tu_cnt[3], nb2 = (tu_cnt[2] + 1) >> 1, nb1 = (tu_cnt[1] + 3) >> 2, nb0 = (tu_cnt[0] + 7) >> 3;
         const int nbatch = nb3 + nb2 + nb1 + nb0;
+        RC_MARK(8);
         for (;;) {
             int b = 0;
             if (lane == 0) b = atomicAdd(&tu_cnt[14], 1);
@@ -1169,23 +1201,35 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         }
     }
     __syncthreads();
+    RC_MARK(9);
 
     // ================================================================ phase 3: the CTB leaves the SM once
     for (int c = 0; c < f.nplanes; c++) {
         const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
         uint8_t *plane = f.work.p[c] + (size_t)(cy0 >> vs) * f.work.pitch[c];
-        const int units = vw[c] >> 2, items = units * vh[c];
+        const int units = (c ? vwc : vw0) >> 2, items = units * (c ? vhc : vh0);
         const int inv = fastinv(units);
         for (int it = tid; it < items; it += RC_THREADS) {
             const int r = fastdiv(it, inv), u = it - r * units;
-            const uint2 v = *(const uint2 *)&tile.p[c][r * tile.pitch[c] + 2 * u];
+            const uint2 v = *(const uint2 *)&tile.p(c)[r * tile.pitch(c) + 2 * u];
             if (HIGH)
                 *(uint2 *)(plane + (size_t)r * f.work.pitch[c] + (size_t)((cx0 >> hs) + 4 * u) * 2) = v;
             else
                 *(uint32_t *)(plane + (size_t)r * f.work.pitch[c] + (cx0 >> hs) + 4 * u) = __byte_perm(v.x, v.y, 0x6420);
         }
     }
+    RC_MARK(10);
 }
+
+#ifdef RC_PROFILE
+int rc_profile_read(unsigned long long *out, int reset)
+{
+    if (cudaMemcpyFromSymbol(out, g_rc_prof, sizeof(g_rc_prof)) != cudaSuccess) return -1;
+    if (reset) { unsigned long long z[16] = {}; cudaMemcpyToSymbol(g_rc_prof, z, sizeof(z)); }
+    return 0;
+}
+extern "C" int ohcu_rc_profile(unsigned long long *out, int reset) { return rc_profile_read(out, reset); }
+#endif
 
 size_t recon_smem_bytes(const FrameDev &f)
 {
@@ -1196,8 +1240,8 @@ size_t recon_smem_bytes(const FrameDev &f)
         words += (size_t)(((cs >> hs) >> 1) + 2) * (cs >> vs);
     }
     words += MAX_CTB_PUS * (sizeof(PuRec) / 4) + (MAX_CTB_PUS + 4) + MAX_CTB_CELLS / 2 + 2 * (MAX_CTB_PUS + 2) / 2 +
-             2 * MAX_CTB_PUS / 4 + 2 * (MAX_ROUNDS + 4) / 4 + 2 + 2 * 4 * RC_WARPS + 16 + MAX_CTB_TUS / 2 +
-             N_KINDS * MAX_CTB_PUS * 2 + 8;
+             2 * MAX_CTB_PUS / 4 + 2 * (MAX_ROUNDS + 4) / 4 + POOL_SLOTS + 2 * 4 * RC_WARPS + 16 + MAX_CTB_TUS / 2 +
+             N_KINDS * MAX_CTB_PUS * 2 + 2 * POOL_SLOTS + 4;
     return POOL_BYTES + words * 4 + (f.cfi == 3 ? RC_WARPS * sizeof(WarpScratch) + 16 : 0);
 }
 
@@ -1357,7 +1401,7 @@ __global__ void dsp_residual_kernel(int16_t *coef, ohcu_tu tu, int bd, int use_m
     }
     if (lane < N) {
         const unsigned mask = N == 32 ? 0xffffffffu : ((1u << N) - 1u);
-        tb_residual<LOG2>(bd, tu, coef, blk, lane, mask);
+        tb_residual<LOG2>(bd, tu.mode, tu.flags, tu.col_limit, coef, blk, lane, mask);
         for (int k = 0; k < N; k++) coef[lane * N + k] = blk[lane * S + k];
     }
 }
