@@ -9,6 +9,7 @@ import numpy as np
 
 from . import abi
 from .abi import check
+from .sparse import to_sparse
 
 
 def _plane_args(planes):
@@ -75,14 +76,27 @@ class Context:
     def begin(self, out_slot, poc=0):
         return check(self.lib.ohcu_frame_begin(self.handle, out_slot, poc), "ohcu_frame_begin")
 
-    def append(self, job_id, fj, use_deblock=True, use_sao=True):
-        """Append every list of a synth.FrameJob (or anything with the same arrays)."""
+    def sparse_lists(self, fj):
+        """(recs, pairs) of a FrameJob for ohcu_append_tu_sparse (hevc_b200.sparse.to_sparse)."""
+        sp = self.sp
+        hs = 1 if sp.chroma_format_idc in (1, 2) else 0
+        vs = 1 if sp.chroma_format_idc == 1 else 0
+        ctb_w = (sp.width + (1 << sp.log2_ctb_size) - 1) >> sp.log2_ctb_size
+        return to_sparse(fj.tus, fj.coeffs, sp.log2_ctb_size, hs, vs, ctb_w)
+
+    def append(self, job_id, fj, use_deblock=True, use_sao=True, sparse=False):
+        """Append every list of a synth.FrameJob (or anything with the same arrays); sparse = the
+        coefficients go as (position, level) pairs (True, or the lists sparse_lists() returned)."""
         lib, h = self.lib, self.handle
         for i in range(len(fj.slices)):
             tab = abi.SliceTab.from_buffer_copy(fj.slices[i].tobytes())
             check(lib.ohcu_set_slice(h, job_id, i, C.byref(tab)), "ohcu_set_slice")
         check(lib.ohcu_append_pu(h, job_id, fj.pus.ctypes.data, len(fj.pus)), "ohcu_append_pu")
-        if len(fj.tus):
+        if len(fj.tus) and sparse:
+            recs, pairs = sparse if isinstance(sparse, tuple) else self.sparse_lists(fj)
+            check(lib.ohcu_append_tu_sparse(h, job_id, recs.ctypes.data, len(recs), pairs.ctypes.data, len(pairs)),
+                  "ohcu_append_tu_sparse")
+        elif len(fj.tus):
             check(lib.ohcu_append_tu(h, job_id, fj.tus.ctypes.data, len(fj.tus), fj.coeffs.ctypes.data,
                                      len(fj.coeffs)), "ohcu_append_tu")
         if use_deblock:
@@ -148,7 +162,7 @@ class Context:
         return planes
 
     # ---- convenience: one frame, synchronously (tests, smoke) -----------------
-    def reconstruct(self, fj, refs, out_slot=None, out_init=None, stages=0, use_deblock=True, use_sao=True):
+    def reconstruct(self, fj, refs, out_slot=None, out_init=None, stages=0, use_deblock=True, use_sao=True, sparse=False):
         """Upload refs to slots 0.., run one frame job, return the reconstructed planes."""
         if out_slot is None:
             out_slot = self.sp.dpb_slots - 1
@@ -158,7 +172,7 @@ class Context:
         if out_init is not None:
             self.upload(out_slot, out_init)
         j = self.begin(out_slot)
-        self.append(j, fj, use_deblock=use_deblock, use_sao=use_sao)
+        self.append(j, fj, use_deblock=use_deblock, use_sao=use_sao, sparse=sparse)
         self.stage(j)
         self.launch(j, out_slot, stages)
         self.sync(j)

@@ -54,6 +54,7 @@ template <typename T> struct Arena {      // pinned host staging + device copy
     T *h = nullptr;
     T *d = nullptr;
     size_t cap = 0;
+    bool carved = false;                  // lives inside the job's table block (Job::tab_h / tab_d)
 };
 
 struct Job {
@@ -78,6 +79,12 @@ struct Job {
     bool tu_sorted = true;   int last_tu_ctb = -1;
     bool has_cross = false;  int max_slice = -1;    // what frame_stage has to validate
     Arena<int16_t> coeffs;   size_t ncoeff = 0;
+    uint8_t *tab_h = nullptr, *tab_d = nullptr;      // block the table arenas are carved from
+    size_t tab_end[4] = {0, 0, 0, 0};                // bytes up to and including: CTB ranges + slices, SAO, deblock, is_pcm
+    // sparse form (ohcu_append_tu_sparse): the arena holds ohcu_coef pairs, ncoeff counts int16
+    Arena<int2> ctb_coef_range;  // per CTB: first pair, number of pairs
+    int coef_form = 0;           // 0 none yet, 1 dense, 2 sparse
+    std::vector<uint32_t> ctb_seen; uint32_t seen_epoch = 0;   // CTBs met by the current sparse append
     Arena<uint8_t> vbs, hbs, is_pcm; Arena<int8_t> qp; Arena<ohcu_dbparams> db;
     Arena<ohcu_sao> sao;     Arena<uint16_t> sao_flags;
     bool has_deblock = false, has_sao = false, has_pcm = false;
@@ -202,10 +209,20 @@ template <typename T> static int alloc_arena(Arena<T> *a, size_t n)
     CU(cudaMalloc((void **)&a->d, a->cap * sizeof(T)));
     return 0;
 }
+// The per-CTB / per-edge tables of a frame are carved out of one pinned block and one device
+// block in upload order, so that a frame's tables go up in ONE copy: 13 separate copies per
+// frame cost 11% of the link when uploads and downloads overlap (tools/pcie_probe3.py).
+template <typename T> static void carve_arena(Arena<T> *a, size_t n, uint8_t *hbase, uint8_t *dbase, size_t *off)
+{
+    a->cap = n ? n : 1;
+    a->carved = true;
+    if (hbase) { a->h = (T *)(hbase + *off); a->d = (T *)(dbase + *off); }
+    *off += (a->cap * sizeof(T) + 255) & ~(size_t)255;
+}
 template <typename T> static void free_arena(Arena<T> *a)
 {
-    if (a->h) cudaFreeHost(a->h);
-    if (a->d) cudaFree(a->d);
+    if (a->h && !a->carved) cudaFreeHost(a->h);
+    if (a->d && !a->carved) cudaFree(a->d);
     a->h = nullptr; a->d = nullptr; a->cap = 0;
 }
 template <typename T> static cudaError_t push_arena(const Arena<T> &a, size_t n, cudaStream_t st)
@@ -249,9 +266,11 @@ extern "C" int ohcu_destroy(ohcu_ctx *c)
     for (auto &j : c->jobs) {
         if (j.recon.base) cudaFree(j.recon.base);
         free_arena(&j.pus); free_arena(&j.ctb_range); free_arena(&j.slices); free_arena(&j.tus);
-        free_arena(&j.coeffs); free_arena(&j.ctb_tu_range);
+        free_arena(&j.coeffs); free_arena(&j.ctb_tu_range); free_arena(&j.ctb_coef_range);
         free_arena(&j.vbs); free_arena(&j.hbs); free_arena(&j.is_pcm); free_arena(&j.qp); free_arena(&j.db);
         free_arena(&j.sao); free_arena(&j.sao_flags);
+        if (j.tab_h) cudaFreeHost(j.tab_h);
+        if (j.tab_d) cudaFree(j.tab_d);
         if (j.done) cudaEventDestroy(j.done);
         for (auto &e : j.ev) if (e) cudaEventDestroy(e);
         if (j.stream) cudaStreamDestroy(j.stream);
@@ -338,19 +357,33 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
         for (auto &e : j.ev) TRYCU(cudaEventCreate(&e));
         TRY(alloc_picture(c, &j.recon, false));
         TRY(alloc_arena(&j.pus, c->sp.max_pus));
-        TRY(alloc_arena(&j.ctb_range, c->nctb));
-        TRY(alloc_arena(&j.slices, OHCU_MAX_SLICES));
         TRY(alloc_arena(&j.tus, c->sp.max_tus));
-        TRY(alloc_arena(&j.coeffs, (size_t)c->sp.max_coeffs));
-        TRY(alloc_arena(&j.ctb_tu_range, c->nctb));
+        // twice max_coeffs int16: the sparse form of a frame whose coefficients are all significant
+        TRY(alloc_arena(&j.coeffs, 2 * (size_t)c->sp.max_coeffs));
         j.ctb_area.assign(c->nctb, 0);
-        TRY(alloc_arena(&j.vbs, (size_t)c->bs_w * c->bs_h));
-        TRY(alloc_arena(&j.hbs, (size_t)c->bs_w * c->bs_h));
-        TRY(alloc_arena(&j.qp, (size_t)c->min_cb_w * c->min_cb_h));
-        TRY(alloc_arena(&j.db, c->nctb));
-        TRY(alloc_arena(&j.is_pcm, (size_t)c->min_pu_w * c->min_pu_h));
-        TRY(alloc_arena(&j.sao, c->nctb));
-        TRY(alloc_arena(&j.sao_flags, c->nctb));
+        for (int pass = 0; pass < 2; pass++) {            // pass 0 sizes the table block, pass 1 carves it
+            size_t off = 0;
+            carve_arena(&j.ctb_range, c->nctb, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.ctb_tu_range, c->nctb, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.ctb_coef_range, c->nctb, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.slices, OHCU_MAX_SLICES, j.tab_h, j.tab_d, &off);
+            j.tab_end[0] = off;
+            carve_arena(&j.sao, c->nctb, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.sao_flags, c->nctb, j.tab_h, j.tab_d, &off);
+            j.tab_end[1] = off;
+            carve_arena(&j.vbs, (size_t)c->bs_w * c->bs_h, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.hbs, (size_t)c->bs_w * c->bs_h, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.qp, (size_t)c->min_cb_w * c->min_cb_h, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.db, c->nctb, j.tab_h, j.tab_d, &off);
+            j.tab_end[2] = off;
+            carve_arena(&j.is_pcm, (size_t)c->min_pu_w * c->min_pu_h, j.tab_h, j.tab_d, &off);
+            j.tab_end[3] = off;
+            if (pass == 0) {
+                TRYCU(cudaHostAlloc((void **)&j.tab_h, off, cudaHostAllocDefault));
+                TRYCU(cudaMalloc((void **)&j.tab_d, off));
+                memset(j.tab_h, 0, off);
+            }
+        }
     }
     TRYCU(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     TRY(build_tensor_maps(c));
@@ -496,6 +529,7 @@ extern "C" int ohcu_frame_begin(ohcu_ctx *c, int out_slot, int poc)
     j.has_deblock = j.has_sao = j.has_pcm = false;
     memset(j.ctb_range.h, 0, sizeof(int2) * c->nctb);
     memset(j.ctb_tu_range.h, 0, sizeof(int2) * c->nctb);
+    j.coef_form = 0;
     std::fill(j.ctb_area.begin(), j.ctb_area.end(), 0);
     return id;
 }
@@ -616,6 +650,8 @@ extern "C" int ohcu_append_tu(ohcu_ctx *c, int job, const ohcu_tu *recs, int n, 
 {
     OPEN_JOB(c, job);
     if (n < 0 || (n && (!recs || !coeffs))) return fail(OHCU_EINVAL, "bad TU list");
+    if (j.coef_form == 2) return fail(OHCU_ESTATE, "job %d already holds sparse coefficients", job);
+    j.coef_form = 1;
     if (j.ncoeff + ncoeff > j.coeffs.cap) return fail(OHCU_EOVERFLOW, "coefficient arena full (%zu)", j.coeffs.cap);
     if (j.ncoeff + ncoeff > 0xffffffffull) return fail(OHCU_EOVERFLOW, "coefficient offsets exceed 32 bits");
     const uint32_t base = (uint32_t)j.ncoeff;
@@ -628,6 +664,8 @@ extern "C" int ohcu_reserve_coeffs(ohcu_ctx *c, int job, size_t ncoeff, int16_t 
 {
     OPEN_JOB(c, job);
     if (!ptr || !arena_off) return fail(OHCU_EINVAL, "null argument");
+    if (j.coef_form == 2) return fail(OHCU_ESTATE, "job %d already holds sparse coefficients", job);
+    j.coef_form = 1;
     ncoeff = (ncoeff + 7) & ~(size_t)7;              // keep blocks 16-byte aligned
     if (j.ncoeff + ncoeff > j.coeffs.cap) return fail(OHCU_EOVERFLOW, "coefficient arena full (%zu)", j.coeffs.cap);
     *ptr = j.coeffs.h + j.ncoeff;
@@ -640,7 +678,81 @@ extern "C" int ohcu_append_tu_inplace(ohcu_ctx *c, int job, const ohcu_tu *recs,
 {
     OPEN_JOB(c, job);
     if (n < 0 || (n && !recs)) return fail(OHCU_EINVAL, "bad TU list");
+    if (j.coef_form == 2) return fail(OHCU_ESTATE, "job %d already holds sparse coefficients", job);
+    j.coef_form = 1;
     return add_tus(c, j, recs, n, 0);
+}
+
+// ---- sparse form: (position, level) pairs, dense blocks rebuilt per CTB in shared memory
+extern "C" int ohcu_reserve_coefs(ohcu_ctx *c, int job, size_t n, ohcu_coef **ptr)
+{
+    OPEN_JOB(c, job);
+    if (!ptr) return fail(OHCU_EINVAL, "null argument");
+    if (j.coef_form == 1) return fail(OHCU_ESTATE, "job %d already holds dense coefficients", job);
+    if (j.ncoeff + 2 * n > j.coeffs.cap) return fail(OHCU_EOVERFLOW, "coefficient arena full (%zu pairs)", j.coeffs.cap / 2);
+    *ptr = (ohcu_coef *)(j.coeffs.h + j.ncoeff);
+    return 0;
+}
+
+extern "C" int ohcu_append_tu_sparse(ohcu_ctx *c, int job, const ohcu_tu *recs, int n, const ohcu_coef *coefs, size_t ncoefs)
+{
+    OPEN_JOB(c, job);
+    if (n < 0 || (n && !recs) || (ncoefs && !coefs)) return fail(OHCU_EINVAL, "bad TU list");
+    if (j.coef_form == 1) return fail(OHCU_ESTATE, "job %d already holds dense coefficients", job);
+    if ((size_t)j.n_tu + n > j.tus.cap) return fail(OHCU_EOVERFLOW, "TU arena full (%zu)", j.tus.cap);
+    if (j.ncoeff + 2 * ncoefs > j.coeffs.cap) return fail(OHCU_EOVERFLOW, "coefficient arena full (%zu pairs)", j.coeffs.cap / 2);
+    int2 *const range = j.ctb_tu_range.h, *const crange = j.ctb_coef_range.h;
+    ohcu_tu *const dst = j.tus.h + j.n_tu;
+    const int l2 = c->sp.log2_ctb_size, ctb_w = c->ctb_w, base = j.n_tu;
+    const int pw[3] = {c->pw[0], c->pw[1], c->pw[2]}, ph[3] = {c->ph[0], c->ph[1], c->ph[2]};
+    const int ths[3] = {0, c->hs, c->hs}, tvs[3] = {0, c->vs, c->vs};
+    const int max_c = c->sp.chroma_format_idc ? 2 : 0;
+    const uint32_t area = (uint32_t)recon_sparse_ctb_coefs();
+    const size_t first_pair = j.ncoeff / 2;
+    size_t cursor = 0;
+    int last = j.last_tu_ctb;
+    bool cross = j.has_cross;
+    // validate everything before the lists change
+    if (j.ctb_seen.size() != (size_t)c->nctb) j.ctb_seen.assign(c->nctb, 0);
+    j.seen_epoch++;
+    for (int i = 0; i < n; i++) {
+        const ohcu_tu &tu = recs[i];
+        const unsigned l = (unsigned)tu.log2_size - 2u;
+        if (l > 3u || tu.c_idx > max_c || tu.mode > OHCU_TU_BYPASS || (tu.mode == OHCU_TU_DST4 && l != 0))
+            return fail(OHCU_EINVAL, "TU record %d is malformed", base + i);
+        const int n1 = 1 << tu.log2_size;
+        if (tu.x0 + n1 > pw[tu.c_idx] || tu.y0 + n1 > ph[tu.c_idx])
+            return fail(OHCU_EINVAL, "TU record %d lies outside plane %d", base + i, tu.c_idx);
+        if ((tu.coeff_off & 7) || tu.coeff_off + (uint32_t)(n1 * n1) > area || tu.pad > n1 * n1)
+            return fail(OHCU_EINVAL, "TU record %d: block outside the CTB's coefficient area (%u)", base + i, area);
+        const int ctb = ((tu.x0 << ths[tu.c_idx]) >> l2) + ((tu.y0 << tvs[tu.c_idx]) >> l2) * ctb_w;
+        if (ctb != last) {
+            if (range[ctb].y != 0 || j.ctb_seen[ctb] == j.seen_epoch)
+                return fail(OHCU_EINVAL, "TU record %d: the sparse form needs the blocks of a CTB appended contiguously", base + i);
+            j.ctb_seen[ctb] = j.seen_epoch;
+        }
+        last = ctb;
+        cursor += tu.pad;
+    }
+    if (cursor != ncoefs) return fail(OHCU_EINVAL, "the records count %zu coefficients, %zu given", cursor, ncoefs);
+    ohcu_coef *const arena = (ohcu_coef *)(j.coeffs.h + j.ncoeff);
+    if (ncoefs && coefs != arena) memcpy(arena, coefs, ncoefs * sizeof(ohcu_coef));
+    cursor = first_pair;
+    last = j.last_tu_ctb;
+    for (int i = 0; i < n; i++) {
+        const ohcu_tu &tu = recs[i];
+        const int ctb = ((tu.x0 << ths[tu.c_idx]) >> l2) + ((tu.y0 << tvs[tu.c_idx]) >> l2) * ctb_w;
+        if (ctb != last) { range[ctb].x = base + i; crange[ctb].x = (int)cursor; crange[ctb].y = 0; last = ctb; }
+        range[ctb].y++;
+        crange[ctb].y += tu.pad;
+        cursor += tu.pad;
+        cross |= (tu.flags & OHCU_TUF_CROSS) != 0;
+        dst[i] = tu;
+    }
+    j.last_tu_ctb = last; j.has_cross = cross; j.coef_form = 2;
+    j.ncoeff += 2 * ncoefs;
+    j.n_tu += n;
+    return 0;
 }
 
 extern "C" int ohcu_set_deblock(ohcu_ctx *c, int job, const ohcu_deblock_in *in)
@@ -771,22 +883,11 @@ static int stage_impl(ohcu_ctx *c, int job)
             return fail(OHCU_EINVAL, "TU %d: bad cross-component reference", i);
     cudaStream_t st = j.stream;
     CU(push_arena(j.pus, j.n_pu, st));
-    CU(push_arena(j.ctb_range, c->nctb, st));
-    CU(push_arena(j.slices, j.n_slices, st));
     CU(push_arena(j.tus, j.n_tu, st));
     CU(push_arena(j.coeffs, j.ncoeff, st));
-    CU(push_arena(j.ctb_tu_range, c->nctb, st));
-    if (j.has_deblock) {
-        CU(push_arena(j.vbs, (size_t)c->bs_w * c->bs_h, st));
-        CU(push_arena(j.hbs, (size_t)c->bs_w * c->bs_h, st));
-        CU(push_arena(j.qp, (size_t)c->min_cb_w * c->min_cb_h, st));
-        CU(push_arena(j.db, c->nctb, st));
-    }
-    if (j.has_pcm) CU(push_arena(j.is_pcm, (size_t)c->min_pu_w * c->min_pu_h, st));
-    if (j.has_sao) {
-        CU(push_arena(j.sao, c->nctb, st));
-        CU(push_arena(j.sao_flags, c->nctb, st));
-    }
+    // the tables: one copy up to the last group this frame uses
+    const size_t tab_bytes = j.tab_end[j.has_pcm ? 3 : j.has_deblock ? 2 : j.has_sao ? 1 : 0];
+    CU(cudaMemcpyAsync(j.tab_d, j.tab_h, tab_bytes, cudaMemcpyHostToDevice, st));
     j.open = false;
     j.staged = true;
     // the pinned staging is reusable once this event has fired
@@ -800,6 +901,7 @@ static void fill_frame_dev(const ohcu_ctx *c, const Job &j, FrameDev *f)
     fill_seq_dev(c, f);
     f->pus = j.pus.d; f->n_pu = j.n_pu; f->ctb_pu_range = j.ctb_range.d; f->slices = j.slices.d;
     f->tus = j.tus.d; f->n_tu = j.n_tu; f->coeffs = j.coeffs.d; f->ctb_tu_range = j.ctb_tu_range.d;
+    f->ctb_coef_range = j.coef_form == 2 ? j.ctb_coef_range.d : nullptr;
     f->vbs = j.has_deblock ? j.vbs.d : nullptr; f->hbs = j.hbs.d; f->qp_y = j.qp.d; f->db = j.db.d;
     f->is_pcm = j.has_pcm ? j.is_pcm.d : nullptr;
     f->sao = j.has_sao ? j.sao.d : nullptr; f->sao_ctb_flags = j.sao_flags.d;

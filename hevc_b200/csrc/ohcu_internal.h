@@ -62,6 +62,7 @@ struct FrameDev {
     int n_tu;
     const int16_t *coeffs;
     const int2 *ctb_tu_range;     // per CTB (raster): first TU, number of TUs
+    const int2 *ctb_coef_range;   // sparse coefficients: per CTB first (pos, level) pair in `coeffs`, number of pairs; nullptr = dense blocks
     // deblock
     const uint8_t *vbs, *hbs;
     const int8_t *qp_y;
@@ -86,6 +87,7 @@ enum {
 
 // kernel launchers (each returns the number of kernels it enqueued, < 0 on error)
 int launch_recon(const FrameDev &f, int flags, cudaStream_t st);   // flags: 1 MC, 2 residual
+int recon_sparse_ctb_coefs();   // int16 a CTB's rebuilt coefficient area may hold (sparse form)
 int upload_mc_taps();
 int upload_dct_table();
 struct LfMaps { CUtensorMap m[3]; };        // the job's reconstructed picture, one box per plane

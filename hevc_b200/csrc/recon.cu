@@ -56,6 +56,8 @@ constexpr int N_KINDS = 4;                   // list slot A luma, slot B luma, s
 
 // scratch of one warp in the residual phase (aliases the window pool): one 32x32 int16 block
 struct WarpScratch { uint32_t w[32 * 40 / 2]; };   // 32 x (32 + 8) int16: idct_mma's pass-1 output
+// int16 coefficients of one CTB staged next to the per-warp scratch: 12288 = a 64x64 4:4:4 CTB
+constexpr int SPARSE_CTB_COEFS = (POOL_BYTES - RC_WARPS * (int)sizeof(WarpScratch)) / 2;
 
 // ff_hevc_qpel_filters / ff_hevc_epel_filters (hevcdsp.c:181-195) packed four int8 taps
 // per word: [phase][0] = taps 0..3, [phase][1] = taps 4..7
@@ -851,7 +853,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     uint8_t *rstart = (uint8_t *)sp;            sp += 2 * (MAX_ROUNDS + 4) / 4;          // [..][round] first PU, [..][MAX_ROUNDS + 1] = count
     int *done = (int *)sp;                      sp += POOL_SLOTS;                        // warps finished with each pool slot
     int *scan_tmp = (int *)sp;                  sp += 2 * 4 * RC_WARPS;                  // [cells | units][class][warp]
-    int *tu_cnt = (int *)sp;                    sp += 16;                         // [0..3] counts, [4..7] bases, [8..11] cursors, [12] coef lo, [13] coef hi, [14] batch counter
+    int *tu_cnt = (int *)sp;                    sp += 18;                         // [0..3] counts, [4..7] bases, [8..11] cursors, [12] coef lo, [13] coef hi, [14] batch counter, [15..16] sparse pair range
     uint16_t *tu_list = (uint16_t *)sp;         sp += MAX_CTB_TUS / 2;
     uint32_t *issue = sp;                       sp += N_KINDS * MAX_CTB_PUS * 2;  // TMA parameters per (kind, PU)
     uint64_t *mbar = (uint64_t *)(((uintptr_t)sp + 7) & ~(uintptr_t)7);           sp += 2 * POOL_SLOTS + 2;   // one per pool slot
@@ -895,6 +897,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     //      occupy; runs while the first round of windows is in flight
     auto sort_tus = [&]() {
         if (nt > 0) {
+            if (tid == RC_THREADS - 1 && f.ctb_coef_range) { const int2 cr = f.ctb_coef_range[ctb]; tu_cnt[15] = cr.x; tu_cnt[16] = cr.y; }
             for (int i = tid; i < nt; i += RC_THREADS) {
                 const ohcu_tu *tu = f.tus + t0 + i;
                 const int l2 = tu->log2_size;
@@ -1161,6 +1164,17 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
 
     RC_MARK(5);
     // ================================================================ phase 2: residual
+    // sparse coefficients: the first (position, level) pairs of the CTB are fetched while the
+    // other warps finish their cells
+    const bool sparse = nt > 0 && f.ctb_coef_range != nullptr;
+    uint32_t pr[4] = {0xffffu, 0xffffu, 0xffffu, 0xffffu};
+    if (sparse) {
+        const uint32_t *src = (const uint32_t *)f.coeffs + tu_cnt[15];
+        const int npair = tu_cnt[16];
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (k * RC_THREADS + tid < npair) pr[k] = __ldg(src + k * RC_THREADS + tid);
+    }
     __syncthreads();          // prediction complete: the pool is free
     RC_MARK(6);
     if (nt > 0) {
@@ -1168,10 +1182,33 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         // copy brings them next to the per-warp block buffers; ranges that do not fit are read
         // from global memory block by block
         int16_t *coef_sm = (int16_t *)(pool + RC_WARPS * sizeof(WarpScratch));
-        const uint32_t clo = (uint32_t)tu_cnt[12], chi = (uint32_t)tu_cnt[13];
+        const uint32_t clo = sparse ? 0u : (uint32_t)tu_cnt[12], chi = (uint32_t)tu_cnt[13];
         const uint32_t cbytes = (chi - clo) * 2;
-        const bool staged = chi > clo && cbytes <= (uint32_t)(POOL_BYTES - RC_WARPS * sizeof(WarpScratch)) && !(cbytes & 15) && !(clo & 7);
-        if (staged) {
+        const bool staged = sparse || (chi > clo && cbytes <= (uint32_t)SPARSE_CTB_COEFS * 2 && !(cbytes & 15) && !(clo & 7));
+        if (sparse) {
+            // pairs -> dense blocks: clear the CTB's coefficient area, then scatter
+            const uint32_t *src = (const uint32_t *)f.coeffs + tu_cnt[15];
+            const int npair = tu_cnt[16];
+            const uint32_t area = min(chi, (uint32_t)SPARSE_CTB_COEFS);
+            for (uint32_t o = tid * 8; o < area; o += RC_THREADS * 8) *(uint4 *)(coef_sm + o) = make_uint4(0, 0, 0, 0);
+            __syncthreads();
+            for (int base = 0;;) {
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t pos = pr[k] & 0xffffu;
+                    if (pos < area) coef_sm[pos] = (int16_t)(pr[k] >> 16);
+                }
+                base += 4 * RC_THREADS;
+                if (base >= npair) break;
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const int q = base + k * RC_THREADS + tid;
+                    pr[k] = q < npair ? __ldg(src + q) : 0xffffu;
+                }
+            }
+            __syncthreads();
+            RC_MARK(7);
+        } else if (staged) {
             if (tid == 0) {
                 mbar_expect_tx(mbar, cbytes);
                 asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -1240,10 +1277,12 @@ size_t recon_smem_bytes(const FrameDev &f)
         words += (size_t)(((cs >> hs) >> 1) + 2) * (cs >> vs);
     }
     words += MAX_CTB_PUS * (sizeof(PuRec) / 4) + (MAX_CTB_PUS + 4) + MAX_CTB_CELLS / 2 + 2 * (MAX_CTB_PUS + 2) / 2 +
-             2 * MAX_CTB_PUS / 4 + 2 * (MAX_ROUNDS + 4) / 4 + POOL_SLOTS + 2 * 4 * RC_WARPS + 16 + MAX_CTB_TUS / 2 +
+             2 * MAX_CTB_PUS / 4 + 2 * (MAX_ROUNDS + 4) / 4 + POOL_SLOTS + 2 * 4 * RC_WARPS + 18 + MAX_CTB_TUS / 2 +
              N_KINDS * MAX_CTB_PUS * 2 + 2 * POOL_SLOTS + 4;
     return POOL_BYTES + words * 4 + (f.cfi == 3 ? RC_WARPS * sizeof(WarpScratch) + 16 : 0);
 }
+
+int recon_sparse_ctb_coefs() { return SPARSE_CTB_COEFS; }
 
 int launch_recon(const FrameDev &f, int flags, cudaStream_t st)
 {

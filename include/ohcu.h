@@ -129,8 +129,9 @@ typedef struct ohcu_tu {
     uint8_t  flags;           /* OHCU_TUF_*                                       */
     int8_t   col_limit;       /* idct only, as hevc_cabac.c:1793-1805             */
     int8_t   res_scale_val;   /* OHCU_TUF_CROSS only (lc->tu.res_scale_val)       */
-    uint16_t pad;
-    uint32_t coeff_off;       /* int16 offset of the N*N block in the arena       */
+    uint16_t pad;             /* sparse form: number of ohcu_coef of the block    */
+    uint32_t coeff_off;       /* int16 offset of the N*N block in the arena
+                                 (sparse form: inside the CTB's area)             */
     uint32_t cross_tu;        /* OHCU_TUF_CROSS: index (in this frame's TU list)
                                  of the luma TB whose residual is coeffs_y        */
 } ohcu_tu;                    /* 20 bytes */
@@ -240,6 +241,30 @@ int ohcu_append_tu(ohcu_ctx *ctx, int job, const ohcu_tu *recs, int n,
 int ohcu_reserve_coeffs(ohcu_ctx *ctx, int job, size_t ncoeff, int16_t **ptr,
                         uint32_t *arena_off);
 int ohcu_append_tu_inplace(ohcu_ctx *ctx, int job, const ohcu_tu *recs, int n);
+
+/* Sparse variant: only the significant coefficients cross the bus.  The residual
+ * parser zeroes an N x N block and then writes one coefficient per significant
+ * position (memset at hevc_cabac.c:2120, stores at :2352, :2398, :2693, :2740);
+ * here it appends one ohcu_coef per such store instead and the kernel rebuilds
+ * the dense blocks in shared memory.  The coefficient area of a CTB is the
+ * concatenation of its blocks in append order:
+ *   recs[i].coeff_off = block base inside the CTB's area = sum of N*N of the
+ *                       CTB's earlier blocks (a multiple of 16, < 12288)
+ *   recs[i].pad       = number of ohcu_coef of this block
+ *   coef.pos          = recs[i].coeff_off + y * N + x
+ * coefs holds the pairs of the n blocks back to back, in record order.  The
+ * blocks of one CTB must be appended contiguously (as hls_coding_quadtree
+ * emits them), and a frame uses either the dense or the sparse form.
+ * ohcu_reserve_coefs returns room for n pairs at the end of the job's pinned
+ * arena (capacity max_coeffs pairs); passing that pointer as coefs appends
+ * without a copy.                                                               */
+typedef struct ohcu_coef {
+    uint16_t pos;
+    int16_t  level;
+} ohcu_coef;                  /* 4 bytes */
+int ohcu_reserve_coefs(ohcu_ctx *ctx, int job, size_t n, ohcu_coef **ptr);
+int ohcu_append_tu_sparse(ohcu_ctx *ctx, int job, const ohcu_tu *recs, int n,
+                          const ohcu_coef *coefs, size_t ncoefs);
 
 /* replaces the per-edge calls of deblocking_filter_CTB (hevc_filter.c:588-599,
  * 634-654, 686-697, 735-755).  Arrays are copied before return.  Not calling it

@@ -93,3 +93,60 @@ def test_frames_in_flight_and_reference_chain(oracle):
         want = oracle.replay(jb, dpb)
         assert _diff(outs[k], want) is None, f"frame {k}: {_diff(outs[k], want)}"
         chain.append(want)
+
+
+@pytest.mark.parametrize("name", list(frame_cases.FRAME_CASES))
+def test_sparse_coefficients_parity(name):
+    """The same frames with the coefficients sent as (position, level) pairs
+    (ohcu_append_tu_sparse): identical pictures, checked against the reference fixtures."""
+    gold = json.load(open(os.path.join(GOLDEN, "frames.json")))["cases"][name]
+    job, refs = frame_cases.build_case(name)
+    init = refs[-1]
+    with backend.Context(job.sp) as ctx:
+        for key in ("mc_res", "all"):
+            got = ctx.reconstruct(job, refs, out_init=init, stages=STAGE_SETS[key], sparse=True)
+            assert frame_cases.picture_digest(got) == gold[key], f"{name}/{key} (sparse) differs from the reference fixture"
+
+
+def test_sparse_residual_only_and_ungrouped_list(oracle):
+    """Residual alone on a given picture; a TU list that is not grouped by CTB is grouped by the
+    harness (the library itself refuses it, see test_sparse_append_errors)."""
+    job, refs = frame_cases.build_case("rext_10b_444")
+    init = refs[-1]
+    want = oracle.replay(job, refs, out_init=init, stages=2)
+    with backend.Context(job.sp) as ctx:
+        got = ctx.reconstruct(job, refs, out_init=init, stages=2, sparse=True)
+        assert _diff(got, want) is None, _diff(got, want)
+        no_cross = (job.tus["flags"] & 8) == 0
+        if no_cross.all():
+            rng = np.random.default_rng(5)
+            job.tus = job.tus[rng.permutation(len(job.tus))].copy()
+            got = ctx.reconstruct(job, refs, out_init=init, stages=2, sparse=True)
+            assert _diff(got, want) is None, _diff(got, want)
+
+
+def test_sparse_append_errors():
+    from hevc_b200 import abi
+    job, refs = frame_cases.build_case("cfg1_416x240_8b_420")
+    with backend.Context(job.sp) as ctx:
+        lib, h = ctx.lib, ctx.handle
+        recs, pairs = ctx.sparse_lists(job)
+        j = ctx.begin(ctx.sp.dpb_slots - 1)
+        # pair count that does not match the records
+        assert lib.ohcu_append_tu_sparse(h, j, recs.ctypes.data, len(recs), pairs.ctypes.data, len(pairs) - 1) == -1
+        # a CTB met twice
+        twice = np.concatenate([recs[:1], recs[-1:], recs[:1]])
+        n = int(twice["pad"].sum())
+        assert lib.ohcu_append_tu_sparse(h, j, twice.ctypes.data, 3, pairs.ctypes.data, n) == -1
+        # block outside the CTB's coefficient area
+        bad = recs[:1].copy()
+        bad["coeff_off"] = 12288
+        assert lib.ohcu_append_tu_sparse(h, j, bad.ctypes.data, 1, pairs.ctypes.data, int(bad["pad"][0])) == -1
+        # nothing was appended by the failed calls; dense and sparse do not mix
+        assert lib.ohcu_append_tu_sparse(h, j, recs.ctypes.data, len(recs), pairs.ctypes.data, len(pairs)) == 0
+        assert lib.ohcu_append_tu(h, j, job.tus.ctypes.data, len(job.tus), job.coeffs.ctypes.data, len(job.coeffs)) == -4
+        assert lib.ohcu_frame_abort(h, j) == 0
+        j = ctx.begin(ctx.sp.dpb_slots - 1)
+        assert lib.ohcu_append_tu(h, j, job.tus.ctypes.data, len(job.tus), job.coeffs.ctypes.data, len(job.coeffs)) == 0
+        assert lib.ohcu_append_tu_sparse(h, j, recs.ctypes.data, len(recs), pairs.ctypes.data, len(pairs)) == -4
+        assert lib.ohcu_frame_abort(h, j) == 0
