@@ -707,7 +707,7 @@ extern "C" int ohcu_append_tu_sparse(ohcu_ctx *c, int job, const ohcu_tu *recs, 
     const int pw[3] = {c->pw[0], c->pw[1], c->pw[2]}, ph[3] = {c->ph[0], c->ph[1], c->ph[2]};
     const int ths[3] = {0, c->hs, c->hs}, tvs[3] = {0, c->vs, c->vs};
     const int max_c = c->sp.chroma_format_idc ? 2 : 0;
-    const uint32_t area = (uint32_t)recon_sparse_ctb_coefs();
+    const uint32_t area = (uint32_t)recon_sparse_ctb_coefs(c->sp.log2_ctb_size, c->nplanes, c->hs, c->vs, c->sp.chroma_format_idc);
     const size_t first_pair = j.ncoeff / 2;
     size_t cursor = 0;
     int last = j.last_tu_ctb;

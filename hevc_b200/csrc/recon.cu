@@ -47,17 +47,37 @@ constexpr int POOL_UNIT = 128;               // every TMA box is a multiple of 1
 constexpr int ROUND_ROTATE = 128;            // threads by which the cell assignment shifts from round to round
 constexpr int POOL_SLOTS = 2;                // rounds resident at a time: one being filtered, one in flight
                                              // (measured: 2 x 22 KB 0.191 ms, 3 x 15 KB 0.199 ms, 4 x 11 KB 0.207 ms per 4K frame)
-constexpr int HALF_UNITS = 176;              // one round of windows: 22 KB; the largest PU the kernel sees is 32x32
-                                             // (split at append time), both windows 2 x 48 x 40 x 2 B = 60 units
-constexpr int HALF_BYTES = HALF_UNITS * POOL_UNIT;
-constexpr int POOL_BYTES = POOL_SLOTS * HALF_BYTES;
-constexpr int MAX_ROUNDS = 24;               // per plane type (18 in the worst case: 128 bi-predicted 8x4 PUs)
+// One round of windows is `half_units` x 128 B, chosen per launch (rc_half_units below) so that
+// the CTA's shared memory lets 4 CTAs share an SM where the picture format allows it.  The
+// largest PU the kernel sees is 32x32 (split at append time): both windows 2 x 48 x 40 x 2 B
+// = 60 units.  Measured at 3 CTAs/SM: 2 x 22 KB 0.191 ms, 3 x 15 KB 0.199 ms, 4 x 11 KB 0.207 ms.
+constexpr int MIN_HALF_UNITS = 60, MAX_HALF_UNITS = 176;
+// RC_DIRECT 1: the cells read their reference windows straight from the halo-padded DPB planes
+// through L1 (no window pool, no rounds); 0: TMA windows in a shared-memory pool.
+#ifndef RC_DIRECT
+#define RC_DIRECT 1
+#endif
+#ifndef RC_MINB
+#define RC_MINB 3
+#endif
+constexpr int MAX_ROUNDS = 28;               // per plane type (26 in the worst case: 128 bi-predicted 8x4 PUs, 60-unit rounds)
 constexpr int N_KINDS = 4;                   // list slot A luma, slot B luma, slot A chroma, slot B chroma
 
 // scratch of one warp in the residual phase (aliases the window pool): one 32x32 int16 block
 struct WarpScratch { uint32_t w[32 * 40 / 2]; };   // 32 x (32 + 8) int16: idct_mma's pass-1 output
-// int16 coefficients of one CTB staged next to the per-warp scratch: 12288 = a 64x64 4:4:4 CTB
-constexpr int SPARSE_CTB_COEFS = (POOL_BYTES - RC_WARPS * (int)sizeof(WarpScratch)) / 2;
+// shared-memory words that only the prediction phase uses (PU records, scans, round tables, cell
+// list, TMA parameters): they follow the pool, and in the residual phase pool + these words hold
+// the per-warp scratch and the int16 coefficients of the CTB (a 64x64 4:2:0 CTB has 6144)
+constexpr int PUREC_WORDS = 14;              // sizeof(PuRec) / 4
+constexpr int MCONLY_WORDS = MAX_CTB_PUS * PUREC_WORDS + (MAX_CTB_PUS + 4) + MAX_CTB_CELLS / 2 + 2 * (MAX_CTB_PUS + 2) / 2 +
+                             2 * MAX_CTB_PUS / 4 + 2 * (MAX_ROUNDS + 4) / 4 + 2 * 4 * RC_WARPS + N_KINDS * MAX_CTB_PUS * 2;
+__host__ __device__ constexpr int coef_area(int half_units)     // int16, multiple of 8
+{
+#if RC_DIRECT
+    return ((half_units * POOL_UNIT - RC_WARPS * (int)sizeof(WarpScratch)) / 2) & ~7;
+#endif
+    return ((POOL_SLOTS * half_units * POOL_UNIT + MCONLY_WORDS * 4 - RC_WARPS * (int)sizeof(WarpScratch)) / 2) & ~7;
+}
 
 // ff_hevc_qpel_filters / ff_hevc_epel_filters (hevcdsp.c:181-195) packed four int8 taps
 // per word: [phase][0] = taps 0..3, [phase][1] = taps 4..7
@@ -657,6 +677,7 @@ struct PuRec {
     uint32_t geom[2][2];
     uint32_t epi[3][3];
 };
+static_assert(sizeof(PuRec) == PUREC_WORDS * 4, "PUREC_WORDS");
 
 // One reference window: the samples list `l` of the PU reads in plane type luma / chroma
 // (both chroma planes share it).  Always the full separable window (NT-1 extra rows and
@@ -711,6 +732,11 @@ __device__ __forceinline__ int box_bytes(bool high, int wcls, int hcls) { return
 // row r, columns 2k and 2k + 1 as an int16 pair.
 //   col0  first output column of the cell relative to the window's first needed column
 //   row0  first output row of the cell relative to the window's first row
+#if RC_DIRECT
+#define RC_LD(ptr) __ldg(ptr)          // windows are read from the DPB planes (global memory, L1-cached)
+#else
+#define RC_LD(ptr) (*(ptr))            // windows sit in the shared-memory pool (or, for the shims, in global memory)
+#endif
 template <bool HIGH, int NT, int OW, int OH>
 __device__ __forceinline__ void mc_filter(const uint8_t *win, int pitch, int col0, int row0, uint32_t FX0, uint32_t FX1,
                                           uint32_t FY0, uint32_t FY1, int sh1, uint32_t (&res)[OH][OW / 2])
@@ -726,7 +752,7 @@ __device__ __forceinline__ void mc_filter(const uint8_t *win, int pitch, int col
             const int sh = (col0 & 1) * 16;
             uint32_t T[NW];
 #pragma unroll
-            for (int j = 0; j < NW; j++) T[j] = p[j];
+            for (int j = 0; j < NW; j++) T[j] = RC_LD(p + j);
 #pragma unroll
             for (int j = 0; j < NW; j++) W[j] = __funnelshift_r(T[j], T[j + 1 < NW ? j + 1 : j], sh);
         } else {
@@ -735,7 +761,7 @@ __device__ __forceinline__ void mc_filter(const uint8_t *win, int pitch, int col
             const int sh = (col0 & 3) * 8;
             uint32_t T[NB];
 #pragma unroll
-            for (int j = 0; j < NB; j++) T[j] = p[j];
+            for (int j = 0; j < NB; j++) T[j] = RC_LD(p + j);
 #pragma unroll
             for (int j = 0; j < NB - 1; j++) {
                 const uint32_t v = __funnelshift_r(T[j], T[j + 1], sh);
@@ -797,6 +823,55 @@ __device__ __forceinline__ void mc_cell(const uint8_t *winA, uint32_t gA, const 
         for (int k = 0; k < OW / 2; k++) epi_pair(e, cur[r][k], prev[r][k], tw + r * tpitch + k);
 }
 
+#if RC_DIRECT
+// ---- direct form: a cell reads its windows from the DPB planes ---------------------------
+//   rect  as PuRec
+//   org   [list slot A,B][luma, chroma]: window origin (first needed sample) in plane coordinates, x | y << 16 (int16 each;
+//         negative = inside the replicated halo)
+//   par   [..][..]: DPB slot | mx << 8 | my << 11
+struct PuRecD {
+    uint32_t rect;
+    uint32_t org[2][2];
+    uint32_t par[2][2];
+    uint32_t epi[3][3];
+};
+constexpr int CMAP_STRIDE = 16;              // 4x4 cells per CTB row (64x64 CTB)
+
+template <bool HIGH, int NT, int OW, int OH>
+__device__ __forceinline__ void mc_cell_d(const FrameDev &f, int c, uint32_t orgA, uint32_t parA, uint32_t orgB, uint32_t parB, bool bi,
+                                          int ccol, int crow, int sh1, const Epi &e, uint32_t *tw, int tpitch)
+{
+    uint32_t cur[OH][OW / 2], prev[OH][OW / 2];
+#pragma unroll
+    for (int r = 0; r < OH; r++)
+#pragma unroll
+        for (int k = 0; k < OW / 2; k++) prev[r][k] = 0;
+#pragma unroll 1
+    for (int s = 0; s < (bi ? 2 : 1); s++) {
+        const uint32_t org = s ? orgB : orgA, par = s ? parB : parA;
+        const int slot = par & 0xff, mx = (par >> 8) & 7, my = (par >> 11) & 7;
+        const int x0 = (int)(int16_t)(org & 0xffffu), y0 = (int)org >> 16;
+        const uint8_t *plane = f.dpb[slot].p[c];
+        const int pitch = f.dpb[slot].pitch[c];
+        if (s) {
+#pragma unroll
+            for (int r = 0; r < OH; r++)
+#pragma unroll
+                for (int k = 0; k < OW / 2; k++) prev[r][k] = cur[r][k];
+        }
+        if (NT == 8)
+            mc_filter<HIGH, NT, OW, OH>(plane, pitch, x0 + ccol, y0 + crow, c_qpel4[mx][0], c_qpel4[mx][1], c_qpel4[my][0],
+                                        c_qpel4[my][1], sh1, cur);
+        else
+            mc_filter<HIGH, NT, OW, OH>(plane, pitch, x0 + ccol, y0 + crow, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, cur);
+    }
+#pragma unroll
+    for (int r = 0; r < OH; r++)
+#pragma unroll
+        for (int k = 0; k < OW / 2; k++) epi_pair(e, cur[r][k], prev[r][k], tw + r * tpitch + k);
+}
+#endif
+
 // ================================================================= the kernel
 __device__ __forceinline__ void unpack_epi(const uint32_t (&w)[3], int bd, Epi &e)
 {
@@ -818,7 +893,7 @@ __device__ unsigned long long g_rc_prof[16];
 #endif
 
 template <bool HIGH>
-__global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_constant__ FrameDev f, int flags)
+__global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid_constant__ FrameDev f, int flags, int half_units)
 {
 #ifdef RC_PROFILE
     long long rc_t = clock64();
@@ -831,10 +906,32 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     const int cx0 = ctbx << f.log2_ctb, cy0 = ctby << f.log2_ctb;      // luma origin of the CTB
     const int bd = f.bd;
 
-    // ---- shared memory carve-up
+#if RC_DIRECT
+    // ---- shared memory carve-up: [residual area | tile, TB lists, barrier].  The residual area (per-warp
+    //      scratch + the CTB's coefficients, `half_units` x 128 B) holds the PU records and the cell map
+    //      during the prediction phase.
     uint8_t *pool = smem_raw;
+    const int pool_bytes = half_units * POOL_UNIT;
     CtbTile tile;
-    uint32_t *sp = (uint32_t *)(smem_raw + POOL_BYTES);
+    PuRecD *recs = (PuRecD *)smem_raw;
+    uint8_t *cmap = smem_raw + MAX_CTB_PUS * sizeof(PuRecD);                            // PU of every 4x4 cell, 0xff = none
+    uint32_t *sp = (uint32_t *)(smem_raw + pool_bytes);
+#else
+    // ---- shared memory carve-up: [window pool | prediction-only words | tile, TB lists, barriers]
+    uint8_t *pool = smem_raw;
+    const int half_bytes = half_units * POOL_UNIT, pool_bytes = POOL_SLOTS * half_bytes;
+    CtbTile tile;
+    uint32_t *sp = (uint32_t *)(smem_raw + pool_bytes);
+    PuRec *recs = (PuRec *)sp;                  sp += MAX_CTB_PUS * PUREC_WORDS;
+    int *cumA = (int *)sp;                      sp += MAX_CTB_PUS + 4;
+    uint16_t *listA = (uint16_t *)sp;           sp += MAX_CTB_CELLS / 2;
+    uint16_t *cumW = (uint16_t *)sp;            sp += 2 * (MAX_CTB_PUS + 2) / 2;         // [luma | chroma plane][PU] window units (128 B) before this PU
+    uint8_t *nxt = (uint8_t *)sp;               sp += 2 * MAX_CTB_PUS / 4;               // [..][PU] first PU of the round after one starting here
+    uint8_t *rstart = (uint8_t *)sp;            sp += 2 * (MAX_ROUNDS + 4) / 4;          // [..][round] first PU, [..][MAX_ROUNDS + 1] = count
+    int *scan_tmp = (int *)sp;                  sp += 2 * 4 * RC_WARPS;                  // [cells | units][class][warp]
+    uint32_t *issue = sp;                       sp += N_KINDS * MAX_CTB_PUS * 2;         // TMA parameters per (kind, PU)
+#endif
+    // ---- end of the prediction-only words (MCONLY_WORDS)
     // valid samples of this CTB per plane type (the picture may end inside it)
     const int vw0 = min(cs, f.pw[0] - cx0), vh0 = min(cs, f.ph[0] - cy0);
     const int vwc = f.nplanes == 3 ? min(cs >> f.hs, f.pw[1] - (cx0 >> f.hs)) : 0;
@@ -845,17 +942,9 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     tile.size0 = tile.pitch0 * cs;
     tile.sizec = f.nplanes == 3 ? tile.pitchc * (cs >> f.vs) : 0;
     sp += tile.size0 + 2 * tile.sizec;
-    PuRec *recs = (PuRec *)sp;                  sp += MAX_CTB_PUS * (sizeof(PuRec) / 4);
-    int *cumA = (int *)sp;                      sp += MAX_CTB_PUS + 4;
-    uint16_t *listA = (uint16_t *)sp;           sp += MAX_CTB_CELLS / 2;
-    uint16_t *cumW = (uint16_t *)sp;            sp += 2 * (MAX_CTB_PUS + 2) / 2;         // [luma | chroma plane][PU] window units (128 B) before this PU
-    uint8_t *nxt = (uint8_t *)sp;               sp += 2 * MAX_CTB_PUS / 4;               // [..][PU] first PU of the round after one starting here
-    uint8_t *rstart = (uint8_t *)sp;            sp += 2 * (MAX_ROUNDS + 4) / 4;          // [..][round] first PU, [..][MAX_ROUNDS + 1] = count
     int *done = (int *)sp;                      sp += POOL_SLOTS;                        // warps finished with each pool slot
-    int *scan_tmp = (int *)sp;                  sp += 2 * 4 * RC_WARPS;                  // [cells | units][class][warp]
     int *tu_cnt = (int *)sp;                    sp += 18;                         // [0..3] counts, [4..7] bases, [8..11] cursors, [12] coef lo, [13] coef hi, [14] batch counter, [15..16] sparse pair range
     uint16_t *tu_list = (uint16_t *)sp;         sp += MAX_CTB_TUS / 2;
-    uint32_t *issue = sp;                       sp += N_KINDS * MAX_CTB_PUS * 2;  // TMA parameters per (kind, PU)
     uint64_t *mbar = (uint64_t *)(((uintptr_t)sp + 7) & ~(uintptr_t)7);           sp += 2 * POOL_SLOTS + 2;   // one per pool slot
     WarpScratch *scratch2 = f.cfi == 3 ? (WarpScratch *)(((uintptr_t)sp + 15) & ~(uintptr_t)15) : nullptr;   // cross-component
 
@@ -889,7 +978,13 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
     }
     if (tid < 12) tu_cnt[tid] = 0;
     if (tid == 12) { tu_cnt[12] = 0x7fffffff; tu_cnt[13] = 0; tu_cnt[14] = 0; }
+#if RC_DIRECT
+    if (tid == 0) mbar_init(mbar, 1);
+    if (tid < CMAP_STRIDE * CMAP_STRIDE / 4) ((uint32_t *)cmap)[tid] = 0xffffffffu;
+    (void)done;
+#else
     if (tid < POOL_SLOTS) { mbar_init(mbar + tid, 1); done[tid] = 0; }
+#endif
     __syncthreads();
     RC_MARK(1);
 
@@ -921,6 +1016,115 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
 
     int rounds_done = 0;                                   // rounds that went through the pool (phase of mbar[0] afterwards)
     // ================================================================ phase 1: prediction
+#if RC_DIRECT
+    if (do_mc) {
+        // ---- 1a. four threads per PU: thread `sub` prepares the window of kind `sub` (list slot
+        //      sub & 1, luma / chroma sub >> 1) and the epilogue constants of plane `sub`, and
+        //      enters the PU into a quarter of its cells of the cell map; 64 PUs per pass.
+        const int sub = tid & 3;
+#pragma unroll 1
+        for (int base = 0; base < np; base += RC_THREADS / 4) {
+            const int p = base + (tid >> 2);
+            if (p < np) {
+                const ohcu_pu pu = load_pu(f.pus + p0 + p);
+                const ohcu_slice_tab &sl = f.slices[pu.slice];
+                const bool bi = pu.pred_flag == OHCU_PF_BI;
+                PuRecD &rc = recs[p];
+                const int lA = (pu.pred_flag & 1) ? 0 : 1;
+                const int x4 = (pu.x0 - cx0) >> 2, y4 = (pu.y0 - cy0) >> 2, w4 = pu.w >> 2, h4 = pu.h >> 2;
+                if (sub == 0)
+                    rc.rect = (uint32_t)(x4 | (y4 << 4) | (w4 << 8) | (h4 << 13) | ((bi ? 1 : 0) << 18));
+                {
+                    const int s = sub & 1, pt = sub >> 1;
+                    uint32_t org = 0, par = 0;
+                    if ((s == 0 || bi) && (pt == 0 || f.nplanes == 3)) {
+                        const int l = s ? 1 : lA;
+                        const WinGeom g = win_geom<HIGH>(f, pu, l, pt == 0);
+                        const int slot = sl.ref_slot[l][(l ? pu.ref_idx[1] : pu.ref_idx[0]) & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1);
+                        org = ((uint32_t)(g.ax + g.offx) & 0xffffu) | ((uint32_t)g.y0 << 16);
+                        par = (uint32_t)slot | ((uint32_t)g.mx << 8) | ((uint32_t)g.my << 11);
+                    }
+                    rc.org[s][pt] = org;
+                    rc.par[s][pt] = par;
+                }
+                if (sub < 3) {                                 // epilogue constants of plane `sub` (see Epi)
+                    const int c = sub;
+                    const bool wflag = sl.weight_flag != 0;
+                    const int denom = c ? sl.chroma_log2_weight_denom : sl.luma_log2_weight_denom;
+                    int wx[2], ox[2];
+#pragma unroll
+                    for (int l = 0; l < 2; l++) {
+                        const int ri = (l ? pu.ref_idx[1] : pu.ref_idx[0]) & (OHCU_MAX_REFS - 1);
+                        wx[l] = c ? sl.chroma_weight[l][ri][c - 1] : sl.luma_weight[l][ri];
+                        ox[l] = (c ? sl.chroma_offset[l][ri][c - 1] : sl.luma_offset[l][ri]) * (1 << (bd - 8));
+                    }
+                    int wA, wB = 0, add, sh, post = 0;
+                    if (!bi) {
+                        if (!wflag) { wA = 1; sh = 14 - bd; add = 1 << (13 - bd); }
+                        else { wA = wx[lA]; sh = denom + 14 - bd; add = 1 << (sh - 1); post = ox[lA]; }
+                    } else {
+                        if (!wflag) { wA = 1; wB = 1; sh = 15 - bd; add = 1 << (14 - bd); }
+                        else {
+                            const int log2Wd = denom + 14 - bd;
+                            wA = wx[1]; wB = wx[0]; sh = log2Wd + 1; add = (ox[0] + ox[1] + 1) * (1 << log2Wd);
+                        }
+                    }
+                    rc.epi[c][0] = ((uint32_t)wA & 0xffffu) | ((uint32_t)wB << 16);
+                    rc.epi[c][1] = (uint32_t)add;
+                    rc.epi[c][2] = ((uint32_t)sh & 0xffffu) | ((uint32_t)post << 16);
+                }
+                const int inv = fastinv(w4);
+                for (int i = sub; i < w4 * h4; i += 4) {
+                    const int yy = fastdiv(i, inv), xx = i - yy * w4;
+                    cmap[(y4 + yy) * CMAP_STRIDE + x4 + xx] = (uint8_t)p;
+                }
+            }
+        }
+        __syncthreads();
+        RC_MARK(2);
+        sort_tus();
+        RC_MARK(4);
+
+        // ---- 1b. one thread per 4x4 cell (and its chroma).  A warp covers 8 x 4 cells of a 64x64 CTB.
+        int cx, cy;
+        if (f.log2_ctb == 6) { cx = (warp & 1) * 8 + (lane & 7); cy = (warp >> 1) * 4 + (lane >> 3); }
+        else { const int n4 = cs >> 2; cy = tid >> (f.log2_ctb - 2); cx = tid & (n4 - 1); }
+        const int p = (cy << 2) < cs ? cmap[cy * CMAP_STRIDE + cx] : 0xff;
+        if (p != 0xff) {
+            const int sh1 = bd - 8;                        // first-stage shift (template :2486)
+            const PuRecD &rc = recs[p];
+            const uint32_t rect = rc.rect;
+            const int ccx = cx - (int)(rect & 15), ccy = cy - (int)((rect >> 4) & 15);
+            const bool pbi = (rect >> 18) & 1;
+            {
+                Epi e;
+                const uint32_t ew[3] = {rc.epi[0][0], rc.epi[0][1], rc.epi[0][2]};
+                unpack_epi(ew, bd, e);
+                uint32_t *tp = tile.p(0) + (cy * 4) * tile.pitch(0) + cx * 2;
+                mc_cell_d<HIGH, 8, 4, 4>(f, 0, rc.org[0][0], rc.par[0][0], rc.org[1][0], rc.par[1][0], pbi, ccx * 4, ccy * 4, sh1, e, tp,
+                                         tile.pitch(0));
+            }
+            if (f.nplanes == 3) {
+                const int hs = f.hs, vs = f.vs;
+                const int cw_ = 4 >> hs, ch = 4 >> vs;
+#pragma unroll 1
+                for (int c = 1; c <= 2; c++) {
+                    Epi e;
+                    const uint32_t ew[3] = {rc.epi[c][0], rc.epi[c][1], rc.epi[c][2]};
+                    unpack_epi(ew, bd, e);
+                    uint32_t *tp = tile.p(c) + (cy * ch) * tile.pitch(c) + ((cx * cw_) >> 1);
+                    const uint32_t oA = rc.org[0][1], pA = rc.par[0][1], oB = rc.org[1][1], pB = rc.par[1][1];
+                    if (hs && vs) mc_cell_d<HIGH, 4, 2, 2>(f, c, oA, pA, oB, pB, pbi, ccx * 2, ccy * 2, sh1, e, tp, tile.pitch(c));
+                    else if (hs) mc_cell_d<HIGH, 4, 2, 4>(f, c, oA, pA, oB, pB, pbi, ccx * 2, ccy * 4, sh1, e, tp, tile.pitch(c));
+                    else mc_cell_d<HIGH, 4, 4, 4>(f, c, oA, pA, oB, pB, pbi, ccx * 4, ccy * 4, sh1, e, tp, tile.pitch(c));
+                }
+            }
+        }
+        RC_MARK(13);
+    } else {
+        sort_tus();
+    }
+#else
     if (do_mc) {
         // ---- 1a. four threads per PU: thread `sub` prepares the window of kind `sub` (list slot
         //      sub & 1, luma / chroma sub >> 1) and the epilogue constants of plane `sub`;
@@ -1029,7 +1233,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         for (int i = tid; i < npt * np; i += RC_THREADS) {
             const int k = i >= np, p = i - k * np;
             const uint16_t *cw = cumW + k * (MAX_CTB_PUS + 2);
-            const int target = cw[p] + HALF_UNITS;
+            const int target = cw[p] + half_units;
             int lo = p + 1, hi = np;                       // largest e with cw[e] <= target (a PU's windows always fit: e > p)
             while (lo < hi) {
                 const int mid = (lo + hi + 1) >> 1;
@@ -1084,7 +1288,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
             const int pa = rs[r], pb = rs[r + 1];
             const uint16_t *cw = cumW + pt * (MAX_CTB_PUS + 2);
             uint64_t *bar = mbar + (i % POOL_SLOTS);
-            uint8_t *buf = pool + (i % POOL_SLOTS) * HALF_BYTES;
+            uint8_t *buf = pool + (i % POOL_SLOTS) * half_bytes;
             if (t == 0) mbar_expect_tx(bar, (uint32_t)(cw[pb] - cw[pa]) * POOL_UNIT);
             for (int p = pa + t; p < pb; p += n) {
                 uint8_t *dst = buf + (cw[p] - cw[pa]) * POOL_UNIT;
@@ -1112,7 +1316,7 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
             const int pa = rs[r], pb = rs[r + 1];
             const uint16_t *cw = cumW + pt * (MAX_CTB_PUS + 2);
             const int slot = i % POOL_SLOTS;
-            const uint8_t *buf = pool + slot * HALF_BYTES - cw[pa] * POOL_UNIT;
+            const uint8_t *buf = pool + slot * half_bytes - cw[pa] * POOL_UNIT;
             const int clo = cumA[pa], chi = min(cumA[pb], MAX_CTB_CELLS);
             RC_MARK(11);                                   // round bookkeeping
             mbar_wait(mbar + slot, (i / POOL_SLOTS) & 1);
@@ -1162,6 +1366,8 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         sort_tus();
     }
 
+#endif
+
     RC_MARK(5);
     // ================================================================ phase 2: residual
     // sparse coefficients: the first (position, level) pairs of the CTB are fetched while the
@@ -1184,12 +1390,12 @@ __global__ void __launch_bounds__(RC_THREADS, 3) recon_kernel(const __grid_const
         int16_t *coef_sm = (int16_t *)(pool + RC_WARPS * sizeof(WarpScratch));
         const uint32_t clo = sparse ? 0u : (uint32_t)tu_cnt[12], chi = (uint32_t)tu_cnt[13];
         const uint32_t cbytes = (chi - clo) * 2;
-        const bool staged = sparse || (chi > clo && cbytes <= (uint32_t)SPARSE_CTB_COEFS * 2 && !(cbytes & 15) && !(clo & 7));
+        const bool staged = sparse || (chi > clo && cbytes <= (uint32_t)coef_area(half_units) * 2 && !(cbytes & 15) && !(clo & 7));
         if (sparse) {
             // pairs -> dense blocks: clear the CTB's coefficient area, then scatter
             const uint32_t *src = (const uint32_t *)f.coeffs + tu_cnt[15];
             const int npair = tu_cnt[16];
-            const uint32_t area = min(chi, (uint32_t)SPARSE_CTB_COEFS);
+            const uint32_t area = min(chi, (uint32_t)coef_area(half_units));
             for (uint32_t o = tid * 8; o < area; o += RC_THREADS * 8) *(uint4 *)(coef_sm + o) = make_uint4(0, 0, 0, 0);
             __syncthreads();
             for (int base = 0;;) {
@@ -1268,37 +1474,69 @@ int rc_profile_read(unsigned long long *out, int reset)
 extern "C" int ohcu_rc_profile(unsigned long long *out, int reset) { return rc_profile_read(out, reset); }
 #endif
 
-size_t recon_smem_bytes(const FrameDev &f)
+// shared memory of one CTA without the window pool
+static size_t recon_fixed_smem(int log2_ctb, int nplanes, int hs, int vs, int cfi)
 {
-    const int cs = 1 << f.log2_ctb;
-    size_t words = 0;
-    for (int c = 0; c < f.nplanes; c++) {
-        const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
-        words += (size_t)(((cs >> hs) >> 1) + 2) * (cs >> vs);
+    const int cs = 1 << log2_ctb;
+    size_t words = RC_DIRECT ? 0 : MCONLY_WORDS;
+    for (int c = 0; c < nplanes; c++) {
+        const int h = c ? hs : 0, v = c ? vs : 0;
+        words += (size_t)(((cs >> h) >> 1) + 2) * (cs >> v);
     }
-    words += MAX_CTB_PUS * (sizeof(PuRec) / 4) + (MAX_CTB_PUS + 4) + MAX_CTB_CELLS / 2 + 2 * (MAX_CTB_PUS + 2) / 2 +
-             2 * MAX_CTB_PUS / 4 + 2 * (MAX_ROUNDS + 4) / 4 + POOL_SLOTS + 2 * 4 * RC_WARPS + 18 + MAX_CTB_TUS / 2 +
-             N_KINDS * MAX_CTB_PUS * 2 + 2 * POOL_SLOTS + 4;
-    return POOL_BYTES + words * 4 + (f.cfi == 3 ? RC_WARPS * sizeof(WarpScratch) + 16 : 0);
+    words += POOL_SLOTS + 18 + MAX_CTB_TUS / 2 + 2 * POOL_SLOTS + 4;
+    return words * 4 + (cfi == 3 ? RC_WARPS * sizeof(WarpScratch) + 16 : 0);
 }
 
-int recon_sparse_ctb_coefs() { return SPARSE_CTB_COEFS; }
+// Units (128 B) of one round of windows: the largest pool with which RC_MINB CTAs still share an
+// SM (228 KB, 1 KB reserved per CTA); formats whose tile leaves no room for that (4:4:4) fall back
+// to one CTA fewer.  -DRC_HALF_UNITS=n fixes it (A/B measurements).
+int rc_half_units(int log2_ctb, int nplanes, int hs, int vs, int cfi)
+{
+#ifdef RC_HALF_UNITS
+    return RC_HALF_UNITS;
+#elif RC_DIRECT
+    // the residual area: per-warp scratch + a full CTB of coefficients (it also holds the PU records
+    // and the cell map of the prediction phase, which are smaller)
+    const int need = (1 << (2 * log2_ctb)) + (nplanes == 3 ? 2 * ((1 << (2 * log2_ctb)) >> (hs + vs)) : 0);
+    (void)cfi; (void)recon_fixed_smem;
+    return (RC_WARPS * (int)sizeof(WarpScratch) + 2 * need + POOL_UNIT - 1) / POOL_UNIT;
+#else
+    const size_t fixed = recon_fixed_smem(log2_ctb, nplanes, hs, vs, cfi);
+    for (int ctas = RC_MINB; ctas >= 1; ctas--) {
+        const long room = (long)(228 * 1024 / ctas - 1024) - (long)fixed;
+        const int hu = (int)(room / (POOL_SLOTS * POOL_UNIT));
+        // the residual phase needs the per-warp scratch and a full CTB of coefficients in pool + prediction-only words
+        const int need = (1 << (2 * log2_ctb)) + (nplanes == 3 ? 2 * ((1 << (2 * log2_ctb)) >> (hs + vs)) : 0);
+        if (hu >= MIN_HALF_UNITS && coef_area(hu < MAX_HALF_UNITS ? hu : MAX_HALF_UNITS) >= need)
+            return hu < MAX_HALF_UNITS ? hu : MAX_HALF_UNITS;
+    }
+    return MAX_HALF_UNITS;
+#endif
+}
+
+size_t recon_smem_bytes(const FrameDev &f, int half_units)
+{
+    return (size_t)(RC_DIRECT ? 1 : POOL_SLOTS) * half_units * POOL_UNIT + recon_fixed_smem(f.log2_ctb, f.nplanes, f.hs, f.vs, f.cfi);
+}
+
+int recon_sparse_ctb_coefs(int log2_ctb, int nplanes, int hs, int vs, int cfi) { return coef_area(rc_half_units(log2_ctb, nplanes, hs, vs, cfi)); }
 
 int launch_recon(const FrameDev &f, int flags, cudaStream_t st)
 {
     if (!(flags & 3)) return 0;
     if (!((flags & 1) && f.n_pu > 0) && !((flags & 2) && f.n_tu > 0)) return 0;
-    const size_t smem = recon_smem_bytes(f);
+    const int hu = rc_half_units(f.log2_ctb, f.nplanes, f.hs, f.vs, f.cfi);
+    const size_t smem = recon_smem_bytes(f, hu);
     static bool attr_set = false;
     if (!attr_set) {
-        if (cudaFuncSetAttribute(recon_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024) != cudaSuccess ||
-            cudaFuncSetAttribute(recon_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024) != cudaSuccess)
+        if (cudaFuncSetAttribute(recon_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(recon_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024) != cudaSuccess)
             return -1;
         attr_set = true;
     }
     const int nctb = f.ctb_w * f.ctb_h;
-    if (f.bd > 8) recon_kernel<true><<<nctb, RC_THREADS, smem, st>>>(f, flags);
-    else          recon_kernel<false><<<nctb, RC_THREADS, smem, st>>>(f, flags);
+    if (f.bd > 8) recon_kernel<true><<<nctb, RC_THREADS, smem, st>>>(f, flags, hu);
+    else          recon_kernel<false><<<nctb, RC_THREADS, smem, st>>>(f, flags, hu);
     return 1;
 }
 
