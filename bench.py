@@ -46,8 +46,8 @@ WORKLOAD_NAMES = {
 N_DISTINCT = 4        # distinct synthetic frames; jobs reuse them round-robin
 # dram__bytes_read.sum + dram__bytes_write.sum of one recon_kernel launch, from the committed
 # `ncu --set full` capture of this same command (never measured inside a timed run)
-NCU_TRAFFIC = {"4k": 90825216}
-NCU_TRAFFIC_SOURCE = "profiles/r01_v7_ncu_kernels.txt (75.65 MB read + 15.17 MB write)"
+NCU_TRAFFIC = {"4k": 70551552}
+NCU_TRAFFIC_SOURCE = "profiles/r01_v10_ncu_kernels.txt (61.54 MB read + 9.01 MB write; the reference pictures stay in L2)"
 
 
 def peaks():

@@ -106,7 +106,6 @@ struct ohcu_ctx {
     void *l2_buf = nullptr;
     size_t l2_bytes = 0;
     cudaEvent_t t0 = nullptr, t1 = nullptr;
-    CUtensorMap *tmaps_d = nullptr;
     // Frame threads each drive their own job; the lists of a job are touched by one thread
     // at a time (caller's contract).  What jobs share — the job ring, the slots' ordering
     // events and reader masks, the launch counter — is guarded here.
@@ -135,9 +134,9 @@ static int alloc_picture(const ohcu_ctx *c, Picture *p, bool padded)
     return 0;
 }
 
-// One tensor map per (DPB slot, plane, box class): the MC kernel fetches each PU's
-// reference window with one cp.async.bulk.tensor.2d.  The driver entry point is looked up
-// at run time so that the library has no link-time dependency on libcuda.
+// The loop filter fetches its tiles with cp.async.bulk.tensor.2d through one tensor map per
+// (job, plane), passed as kernel parameters.  The driver entry point is looked up at run time
+// so that the library has no link-time dependency on libcuda.
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -149,24 +148,6 @@ static int build_tensor_maps(ohcu_ctx *c)
     CU(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", (void **)&enc, cudaEnableDefault, &qr));
     if (!enc || qr != cudaDriverEntryPointSuccess) return fail(OHCU_ECUDA, "cuTensorMapEncodeTiled is not available");
     const bool high = c->P == 2;
-    std::vector<CUtensorMap> maps(c->slots.size() * 3 * N_WCLS * N_HCLS);
-    memset(maps.data(), 0, maps.size() * sizeof(CUtensorMap));
-    for (size_t s = 0; s < c->slots.size(); s++)
-        for (int pl = 0; pl < c->nplanes; pl++)
-            for (int wc = 0; wc < N_WCLS; wc++)
-                for (int hc = 0; hc < N_HCLS; hc++) {
-                    const Picture &p = c->slots[s].pic;
-                    cuuint64_t gdim[2] = {(cuuint64_t)(c->pw[pl] + 2 * PAD_X), (cuuint64_t)(c->ph[pl] + 2 * PAD_Y)};
-                    cuuint64_t gstr[1] = {(cuuint64_t)p.ps.pitch[pl]};
-                    cuuint32_t box[2] = {(cuuint32_t)box_w(high, wc), (cuuint32_t)box_h(hc)};
-                    cuuint32_t estr[2] = {1, 1};
-                    CUresult r = enc(&maps[tmap_index((int)s, pl, wc, hc)],
-                                     high ? CU_TENSOR_MAP_DATA_TYPE_UINT16 : CU_TENSOR_MAP_DATA_TYPE_UINT8, 2,
-                                     p.padded_base[pl], gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-                    if (r != CUDA_SUCCESS) return fail(OHCU_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
-                }
     // the loop filter reads each job's reconstructed picture through kernel-parameter maps
     FrameDev fbox{};
     fill_seq_dev(c, &fbox);
@@ -184,21 +165,6 @@ static int build_tensor_maps(ohcu_ctx *c)
                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
             if (r != CUDA_SUCCESS) return fail(OHCU_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
         }
-    // Descriptor memory is never recycled for DIFFERENT content: the TMA unit caches
-    // descriptors by address and the kernels issue no per-use proxy fence (it costs about
-    // as much as the copy it guards, tools/ubench_tma.cu).  Blocks are kept for the life of
-    // the process and shared by contexts whose maps are byte-identical.
-    static std::mutex mu;
-    static std::vector<std::pair<CUtensorMap *, std::vector<CUtensorMap>>> cache;
-    std::lock_guard<std::mutex> lock(mu);
-    for (auto &e : cache)
-        if (e.second.size() == maps.size() && !memcmp(e.second.data(), maps.data(), maps.size() * sizeof(CUtensorMap))) {
-            c->tmaps_d = e.first;
-            return 0;
-        }
-    CU(cudaMalloc((void **)&c->tmaps_d, maps.size() * sizeof(CUtensorMap)));
-    CU(cudaMemcpy(c->tmaps_d, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
-    cache.emplace_back(c->tmaps_d, maps);
     return 0;
 }
 
@@ -415,7 +381,6 @@ static void fill_seq_dev(const ohcu_ctx *c, FrameDev *f)
     f->nplanes = c->nplanes;
     for (int i = 0; i < 3; i++) { f->pw[i] = c->pw[i]; f->ph[i] = c->ph[i]; }
     for (size_t i = 0; i < c->slots.size(); i++) f->dpb[i] = c->slots[i].pic.ps;
-    f->tmaps = c->tmaps_d;
 }
 
 // ------------------------------------------------------------------ device DPB
@@ -707,7 +672,7 @@ extern "C" int ohcu_append_tu_sparse(ohcu_ctx *c, int job, const ohcu_tu *recs, 
     const int pw[3] = {c->pw[0], c->pw[1], c->pw[2]}, ph[3] = {c->ph[0], c->ph[1], c->ph[2]};
     const int ths[3] = {0, c->hs, c->hs}, tvs[3] = {0, c->vs, c->vs};
     const int max_c = c->sp.chroma_format_idc ? 2 : 0;
-    const uint32_t area = (uint32_t)recon_sparse_ctb_coefs(c->sp.log2_ctb_size, c->nplanes, c->hs, c->vs, c->sp.chroma_format_idc);
+    const uint32_t area = (uint32_t)recon_sparse_ctb_coefs(c->sp.log2_ctb_size, c->nplanes, c->hs, c->vs);
     const size_t first_pair = j.ncoeff / 2;
     size_t cursor = 0;
     int last = j.last_tu_ctb;

@@ -15,26 +15,14 @@ struct PlaneSet {
     int pitch[3];          // bytes
 };
 
-// ---- halo-padded DPB planes and the TMA box classes of motion compensation ------------
+// ---- halo-padded DPB planes ------------------------------------------------------------
 // Every DPB plane is allocated with PAD_X samples left/right and PAD_Y rows above/below
 // that replicate the border sample (the reference's ff_emulated_edge_mc, done once per
-// picture instead of once per block).  MC windows are fetched by TMA as 2-D boxes whose
-// inner coordinate must be 16-byte aligned (measured: tools/ubench_tma.cu), so a window
-// starts at the aligned column at or left of the first sample it needs.
-constexpr int PAD_X = 96;                  // samples; >= 71 needed + 15 alignment slack
+// picture instead of once per block).  Motion compensation reads its windows straight from
+// these planes; a window is clamped so that it starts at most one window size outside the
+// picture, and the 8-byte loads of the filter may begin up to 3 samples left of it.
+constexpr int PAD_X = 96;                  // samples; >= 71 needed + alignment slack of the loads
 constexpr int PAD_Y = 80;                  // rows;    >= 71 needed
-constexpr int N_WCLS = 5, N_HCLS = 5;      // box width / height classes
-// box widths in samples (inner box bytes are multiples of 16 for both sample sizes)
-__host__ __device__ constexpr int box_w(bool high, int cls)
-{
-    return high ? (cls == 0 ? 16 : cls == 1 ? 24 : cls == 2 ? 32 : cls == 3 ? 48 : 80)
-                : (cls == 0 ? 16 : cls == 1 ? 32 : cls == 2 ? 48 : cls == 3 ? 64 : 96);
-}
-__host__ __device__ constexpr int box_h(int cls) { return cls == 0 ? 8 : cls == 1 ? 16 : cls == 2 ? 24 : cls == 3 ? 40 : 72; }
-__host__ __device__ inline int tmap_index(int slot, int plane, int wcls, int hcls)
-{
-    return ((slot * 3 + plane) * N_WCLS + wcls) * N_HCLS + hcls;
-}
 
 // Everything a launch needs, passed by value as one kernel parameter.
 struct FrameDev {
@@ -51,7 +39,6 @@ struct FrameDev {
     PlaneSet work;         // picture being reconstructed (pre-SAO)
     PlaneSet out;          // SAO destination (the DPB slot)
     PlaneSet dpb[OHCU_MAX_DPB];
-    const CUtensorMap *tmaps;     // [slot][plane][width class][height class], see tmap_index()
     // MC
     const ohcu_pu *pus;
     int n_pu;
@@ -87,7 +74,7 @@ enum {
 
 // kernel launchers (each returns the number of kernels it enqueued, < 0 on error)
 int launch_recon(const FrameDev &f, int flags, cudaStream_t st);   // flags: 1 MC, 2 residual
-int recon_sparse_ctb_coefs(int log2_ctb, int nplanes, int hs, int vs, int cfi);   // int16 a CTB's rebuilt coefficient area may hold (sparse form)
+int recon_sparse_ctb_coefs(int log2_ctb, int nplanes, int hs, int vs);   // int16 a CTB's rebuilt coefficient area may hold (sparse form)
 int upload_mc_taps();
 int upload_dct_table();
 struct LfMaps { CUtensorMap m[3]; };        // the job's reconstructed picture, one box per plane

@@ -15,25 +15,26 @@
 //                                                               hevcdsp_template.c:45-296
 //
 // Motion compensation.
-//  * Reference windows come from HALO-PADDED DPB planes (PAD_X / PAD_Y replicated samples,
-//    written once per picture by pad_kernel) through TMA: one cp.async.bulk.tensor.2d per
-//    (PU, list, plane) into a shared-memory pool, issued by the thread that owns the PU,
-//    all landing on one mbarrier.  Window positions outside the halo are clamped to it,
-//    which is bit-identical to the reference's per-block edge emulation.
-//  * Work is then re-cut into CELLS of 4x4 luma samples (and their chroma): one thread per
-//    cell, every thread running the same straight-line code, so a CTB of 64 tiny PUs keeps
-//    the lanes as busy as a CTB with one 64x64 PU.  The [my][mx] table dispatch is gone:
-//    every cell runs the separable h+v path with the phase-0 taps {0,0,0,64,0,0,0,0}
-//    standing in for "no filter", which gives the reference's results exactly
-//    (64*x >> 6 == x, and (x << (14-BD)) is what (64*x) >> (BD-8) computes).
+//  * Reference samples come from HALO-PADDED DPB planes (PAD_X / PAD_Y replicated samples,
+//    written once per picture by pad_kernel).  Window positions outside the halo are clamped to
+//    it, which is bit-identical to the reference's per-block edge emulation.
+//  * Work is cut into CELLS of 4x4 luma samples (and their chroma): one thread per cell,
+//    every thread running the same straight-line code, so a CTB of 64 tiny PUs keeps the
+//    lanes as busy as a CTB with one 64x64 PU.  A 16x16 map of the CTB says which PU owns a
+//    cell; the PUs enter themselves into it, so there is no sorting and no scan.  The
+//    [my][mx] table dispatch is gone: every cell runs the separable h+v path with the phase-0
+//    taps {0,0,0,64,0,0,0,0} standing in for "no filter", which gives the reference's results
+//    exactly (64*x >> 6 == x, and (x << (14-BD)) is what (64*x) >> (BD-8) computes).
+//  * A cell reads its window STRAIGHT FROM THE DPB PLANE through L1 (ld.global.nc, 8-byte
+//    loads): neighbouring cells of a PU share their rows in L1, which here is the ~90 KB the
+//    CTAs' shared memory leaves.  The earlier form (one TMA box per PU and list into a
+//    shared-memory pool, cells run in rounds as the boxes land) spent more time on window
+//    geometry, scans, round bookkeeping and mbarrier waits than on filtering: 0.205 ms per 4K
+//    frame against 0.137 ms for this one (profiles/README.md, r01 v9 -> v10).
 //  * Samples are 16-bit lanes, two per 32-bit word, so the taps run on the integer
 //    dot-product pipe: IDP.2A does two 16x8-bit MACs per instruction at IMAD issue rate
 //    (profiles/r01_ubench_int_pipes.txt).  Horizontal pairs come straight from the window
 //    words (+ funnel shifts for odd positions), vertical pairs are built with PRMT.
-//  * The pool holds two ROUNDS of windows (22 KB each): while the cells of one round are
-//    filtered, the windows of the next are in flight.  Rounds are cut greedily per
-//    (list, luma|chroma) kind over the PUs in list order.  Cells are sorted by PU, so a
-//    round's cells are a contiguous range of the sorted list and lanes stay packed.
 #include "ohcu_internal.h"
 
 namespace ohcu {
@@ -41,42 +42,20 @@ namespace ohcu {
 constexpr int RC_WARPS = 8;
 constexpr int RC_THREADS = RC_WARPS * 32;
 constexpr int MAX_CTB_PUS = 128;             // 8x4 PUs of a 64x64 CTB
-constexpr int MAX_CTB_CELLS = 256;           // 4x4 cells of a 64x64 CTB
 constexpr int MAX_CTB_TUS = 768;             // 4x4 TBs of a 64x64 CTB, 3 full-size planes
-constexpr int POOL_UNIT = 128;               // every TMA box is a multiple of 128 bytes
-constexpr int ROUND_ROTATE = 128;            // threads by which the cell assignment shifts from round to round
-constexpr int POOL_SLOTS = 2;                // rounds resident at a time: one being filtered, one in flight
-                                             // (measured: 2 x 22 KB 0.191 ms, 3 x 15 KB 0.199 ms, 4 x 11 KB 0.207 ms per 4K frame)
-// One round of windows is `half_units` x 128 B, chosen per launch (rc_half_units below) so that
-// the CTA's shared memory lets 4 CTAs share an SM where the picture format allows it.  The
-// largest PU the kernel sees is 32x32 (split at append time): both windows 2 x 48 x 40 x 2 B
-// = 60 units.  Measured at 3 CTAs/SM: 2 x 22 KB 0.191 ms, 3 x 15 KB 0.199 ms, 4 x 11 KB 0.207 ms.
-constexpr int MIN_HALF_UNITS = 60, MAX_HALF_UNITS = 176;
-// RC_DIRECT 1: the cells read their reference windows straight from the halo-padded DPB planes
-// through L1 (no window pool, no rounds); 0: TMA windows in a shared-memory pool.
-#ifndef RC_DIRECT
-#define RC_DIRECT 1
-#endif
+constexpr int POOL_UNIT = 128;               // granule of the residual area
 #ifndef RC_MINB
-#define RC_MINB 3
+#define RC_MINB 3                            // CTAs per SM the register budget is set for (4 was measured: no gain, L1 shrinks)
 #endif
-constexpr int MAX_ROUNDS = 28;               // per plane type (26 in the worst case: 128 bi-predicted 8x4 PUs, 60-unit rounds)
-constexpr int N_KINDS = 4;                   // list slot A luma, slot B luma, slot A chroma, slot B chroma
 
-// scratch of one warp in the residual phase (aliases the window pool): one 32x32 int16 block
+// scratch of one warp in the residual phase: one 32x32 int16 block
 struct WarpScratch { uint32_t w[32 * 40 / 2]; };   // 32 x (32 + 8) int16: idct_mma's pass-1 output
-// shared-memory words that only the prediction phase uses (PU records, scans, round tables, cell
-// list, TMA parameters): they follow the pool, and in the residual phase pool + these words hold
-// the per-warp scratch and the int16 coefficients of the CTB (a 64x64 4:2:0 CTB has 6144)
-constexpr int PUREC_WORDS = 14;              // sizeof(PuRec) / 4
-constexpr int MCONLY_WORDS = MAX_CTB_PUS * PUREC_WORDS + (MAX_CTB_PUS + 4) + MAX_CTB_CELLS / 2 + 2 * (MAX_CTB_PUS + 2) / 2 +
-                             2 * MAX_CTB_PUS / 4 + 2 * (MAX_ROUNDS + 4) / 4 + 2 * 4 * RC_WARPS + N_KINDS * MAX_CTB_PUS * 2;
-__host__ __device__ constexpr int coef_area(int half_units)     // int16, multiple of 8
+// The residual area of a CTA: per-warp scratch, then the int16 coefficients of the CTB
+// (`units` x 128 B in all; a 64x64 4:2:0 CTB has 6144 coefficients).  During the prediction
+// phase the same bytes hold the PU records and the cell map.
+__host__ __device__ constexpr int coef_area(int units)          // int16, multiple of 8
 {
-#if RC_DIRECT
-    return ((half_units * POOL_UNIT - RC_WARPS * (int)sizeof(WarpScratch)) / 2) & ~7;
-#endif
-    return ((POOL_SLOTS * half_units * POOL_UNIT + MCONLY_WORDS * 4 - RC_WARPS * (int)sizeof(WarpScratch)) / 2) & ~7;
+    return ((units * POOL_UNIT - RC_WARPS * (int)sizeof(WarpScratch)) / 2) & ~7;
 }
 
 // ff_hevc_qpel_filters / ff_hevc_epel_filters (hevcdsp.c:181-195) packed four int8 taps
@@ -132,16 +111,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t *b, uint32_t parity)
             else if (clock64() - t0 > 4000000000ll) __trap();
         }
     }
-}
-// 2-D box at (x, y) of the tensor behind `map` -> dst (128-byte aligned); x*sizeof(sample) must
-// be a multiple of 16 (tools/ubench_tma.cu: anything else faults on this part).  The maps live in
-// global memory that is written once and never reused for other content (api.cu), so no
-// tensormap proxy fence is issued here.
-__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, int x, int y, uint64_t *bar)
-{
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-        ::"r"(smem_u32(dst)), "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar)) : "memory");
 }
 // ---------------------------------------------------------------- dot-product helpers
 __device__ __forceinline__ int dp2lo(uint32_t a, uint32_t b, int c) { return __dp2a_lo((int)a, (int)b, c); }
@@ -668,16 +637,19 @@ __device__ __forceinline__ ohcu_pu load_pu(const ohcu_pu *p)
     return u.pu;
 }
 
-// What the cells of a PU need, prepared once by the thread that owns the PU.
+// What the cells of a PU need, prepared once by the four threads that own the PU.
 //   rect  x/4 | y/4 << 4 | w/4 << 8 | h/4 << 13 | bi << 18                        (position inside the CTB)
-//   geom  [list slot A,B][luma, chroma]: pool offset / 16 | pitch / 16 << 12 | offx << 16 | mx << 20 | my << 23 | hcls << 26
+//   org   [list slot A,B][luma, chroma]: window origin (first needed sample) in plane coordinates,
+//         x | y << 16 (int16 each; negative = inside the replicated halo)
+//   par   [..][..]: DPB slot | mx << 8 | my << 11
 //   epi   per plane: (wA & 0xffff) | wB << 16,  add,  sh | post << 16
 struct PuRec {
     uint32_t rect;
-    uint32_t geom[2][2];
+    uint32_t org[2][2];
+    uint32_t par[2][2];
     uint32_t epi[3][3];
 };
-static_assert(sizeof(PuRec) == PUREC_WORDS * 4, "PUREC_WORDS");
+constexpr int CMAP_STRIDE = 16;              // 4x4 cells per CTB row (64x64 CTB)
 
 // One reference window: the samples list `l` of the PU reads in plane type luma / chroma
 // (both chroma planes share it).  Always the full separable window (NT-1 extra rows and
@@ -685,13 +657,10 @@ static_assert(sizeof(PuRec) == PUREC_WORDS * 4, "PUREC_WORDS");
 // fetched from the nearest part of the replicated halo — same samples as
 // ff_emulated_edge_mc would build (videodsp_template.c:37-83).
 struct WinGeom {
-    int ax, y0;           // plane coordinates of the box origin (ax is 16-byte aligned)
-    int offx;             // first needed column inside the box
-    int wcls, hcls;       // box class
+    int x0, y0;           // plane coordinates of the first needed sample
     int mx, my;           // fractional phase: qpel 0..3 / epel 0..7
 };
 
-template <bool HIGH>
 __device__ __forceinline__ WinGeom win_geom(const FrameDev &f, const ohcu_pu &pu, int l, bool luma)
 {
     WinGeom g;
@@ -711,19 +680,10 @@ __device__ __forceinline__ WinGeom win_geom(const FrameDev &f, const ohcu_pu &pu
         g.my = (mvy & ((1 << (2 + vs)) - 1)) << (1 - vs);
         sx = xo + (mvx >> (2 + hs)); sy = yo + (mvy >> (2 + vs));
     }
-    const int needw = bw + NT - 1, needh = bh + NT - 1;
-    const int x0 = clip3i(sx - BEFORE, -needw, pw);
-    g.y0 = clip3i(sy - BEFORE, -needh, ph);
-    constexpr int A = HIGH ? 8 : 16;                       // samples per 16 bytes
-    g.ax = x0 & ~(A - 1);
-    g.offx = x0 - g.ax;
-    const int readw = g.offx + needw;
-    g.wcls = readw <= box_w(HIGH, 0) ? 0 : readw <= box_w(HIGH, 1) ? 1 : readw <= box_w(HIGH, 2) ? 2 : readw <= box_w(HIGH, 3) ? 3 : 4;
-    g.hcls = needh <= box_h(0) ? 0 : needh <= box_h(1) ? 1 : needh <= box_h(2) ? 2 : needh <= box_h(3) ? 3 : 4;
+    g.x0 = clip3i(sx - BEFORE, -(bw + NT - 1), pw);
+    g.y0 = clip3i(sy - BEFORE, -(bh + NT - 1), ph);
     return g;
 }
-
-__device__ __forceinline__ int box_bytes(bool high, int wcls, int hcls) { return box_w(high, wcls) * (high ? 2 : 1) * box_h(hcls); }
 
 // ---------------------------------------------------------------- one cell
 // OW x OH output samples of one plane from the window at `win` (row pitch in bytes):
@@ -732,11 +692,6 @@ __device__ __forceinline__ int box_bytes(bool high, int wcls, int hcls) { return
 // row r, columns 2k and 2k + 1 as an int16 pair.
 //   col0  first output column of the cell relative to the window's first needed column
 //   row0  first output row of the cell relative to the window's first row
-#if RC_DIRECT
-#define RC_LD(ptr) __ldg(ptr)          // windows are read from the DPB planes (global memory, L1-cached)
-#else
-#define RC_LD(ptr) (*(ptr))            // windows sit in the shared-memory pool (or, for the shims, in global memory)
-#endif
 template <bool HIGH, int NT, int OW, int OH>
 __device__ __forceinline__ void mc_filter(const uint8_t *win, int pitch, int col0, int row0, uint32_t FX0, uint32_t FX1,
                                           uint32_t FY0, uint32_t FY1, int sh1, uint32_t (&res)[OH][OW / 2])
@@ -748,11 +703,17 @@ __device__ __forceinline__ void mc_filter(const uint8_t *win, int pitch, int col
     for (int r = 0; r < NR; r++) {
         uint32_t W[NW];
         if (HIGH) {
-            const uint32_t *p = (const uint32_t *)rowp + (col0 >> 1);
             const int sh = (col0 & 1) * 16;
             uint32_t T[NW];
+            // 8-byte loads from the aligned pair of words at or left of the first one needed
+            constexpr int NQ = NW / 2 + 1;
+            const uint2 *q = (const uint2 *)rowp + (col0 >> 2);
+            const bool odd = (col0 >> 1) & 1;
+            uint32_t U[2 * NQ];
 #pragma unroll
-            for (int j = 0; j < NW; j++) T[j] = RC_LD(p + j);
+            for (int j = 0; j < NQ; j++) { const uint2 v = __ldg(q + j); U[2 * j] = v.x; U[2 * j + 1] = v.y; }
+#pragma unroll
+            for (int j = 0; j < NW; j++) T[j] = odd ? U[j + 1] : U[j];
 #pragma unroll
             for (int j = 0; j < NW; j++) W[j] = __funnelshift_r(T[j], T[j + 1 < NW ? j + 1 : j], sh);
         } else {
@@ -761,7 +722,7 @@ __device__ __forceinline__ void mc_filter(const uint8_t *win, int pitch, int col
             const int sh = (col0 & 3) * 8;
             uint32_t T[NB];
 #pragma unroll
-            for (int j = 0; j < NB; j++) T[j] = RC_LD(p + j);
+            for (int j = 0; j < NB; j++) T[j] = __ldg(p + j);
 #pragma unroll
             for (int j = 0; j < NB - 1; j++) {
                 const uint32_t v = __funnelshift_r(T[j], T[j + 1], sh);
@@ -789,56 +750,10 @@ __device__ __forceinline__ void mc_filter(const uint8_t *win, int pitch, int col
 }
 
 // One cell of one plane: list slot A, then (bi) slot B, then the epilogue into the CTB tile.
-// One copy of the filter code: the lists run through the same loop body.
-//   gA / gB: geometry words of the two windows (PuRec::geom), winA / winB: their pool addresses
+// One copy of the filter code: the lists run through the same loop body.  The windows are read
+// from the DPB plane of the list's reference picture (org / par: PuRec).
 template <bool HIGH, int NT, int OW, int OH>
-__device__ __forceinline__ void mc_cell(const uint8_t *winA, uint32_t gA, const uint8_t *winB, uint32_t gB, bool bi, int ccol,
-                                        int crow, int sh1, const Epi &e, uint32_t *tw, int tpitch)
-{
-    uint32_t cur[OH][OW / 2], prev[OH][OW / 2];
-#pragma unroll
-    for (int r = 0; r < OH; r++)
-#pragma unroll
-        for (int k = 0; k < OW / 2; k++) prev[r][k] = 0;
-#pragma unroll 1
-    for (int s = 0; s < (bi ? 2 : 1); s++) {
-        const uint32_t gword = s ? gB : gA;
-        const int pitch = ((gword >> 12) & 15) * 16, offx = (gword >> 16) & 15;
-        const int mx = (gword >> 20) & 7, my = (gword >> 23) & 7;
-        if (s) {
-#pragma unroll
-            for (int r = 0; r < OH; r++)
-#pragma unroll
-                for (int k = 0; k < OW / 2; k++) prev[r][k] = cur[r][k];
-        }
-        if (NT == 8)
-            mc_filter<HIGH, NT, OW, OH>(s ? winB : winA, pitch, offx + ccol, crow, c_qpel4[mx][0], c_qpel4[mx][1], c_qpel4[my][0],
-                                        c_qpel4[my][1], sh1, cur);
-        else
-            mc_filter<HIGH, NT, OW, OH>(s ? winB : winA, pitch, offx + ccol, crow, c_epel4[mx][0], 0, c_epel4[my][0], 0, sh1, cur);
-    }
-#pragma unroll
-    for (int r = 0; r < OH; r++)
-#pragma unroll
-        for (int k = 0; k < OW / 2; k++) epi_pair(e, cur[r][k], prev[r][k], tw + r * tpitch + k);
-}
-
-#if RC_DIRECT
-// ---- direct form: a cell reads its windows from the DPB planes ---------------------------
-//   rect  as PuRec
-//   org   [list slot A,B][luma, chroma]: window origin (first needed sample) in plane coordinates, x | y << 16 (int16 each;
-//         negative = inside the replicated halo)
-//   par   [..][..]: DPB slot | mx << 8 | my << 11
-struct PuRecD {
-    uint32_t rect;
-    uint32_t org[2][2];
-    uint32_t par[2][2];
-    uint32_t epi[3][3];
-};
-constexpr int CMAP_STRIDE = 16;              // 4x4 cells per CTB row (64x64 CTB)
-
-template <bool HIGH, int NT, int OW, int OH>
-__device__ __forceinline__ void mc_cell_d(const FrameDev &f, int c, uint32_t orgA, uint32_t parA, uint32_t orgB, uint32_t parB, bool bi,
+__device__ __forceinline__ void mc_cell(const FrameDev &f, int c, uint32_t orgA, uint32_t parA, uint32_t orgB, uint32_t parB, bool bi,
                                           int ccol, int crow, int sh1, const Epi &e, uint32_t *tw, int tpitch)
 {
     uint32_t cur[OH][OW / 2], prev[OH][OW / 2];
@@ -870,7 +785,6 @@ __device__ __forceinline__ void mc_cell_d(const FrameDev &f, int c, uint32_t org
 #pragma unroll
         for (int k = 0; k < OW / 2; k++) epi_pair(e, cur[r][k], prev[r][k], tw + r * tpitch + k);
 }
-#endif
 
 // ================================================================= the kernel
 __device__ __forceinline__ void unpack_epi(const uint32_t (&w)[3], int bd, Epi &e)
@@ -893,7 +807,7 @@ __device__ unsigned long long g_rc_prof[16];
 #endif
 
 template <bool HIGH>
-__global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid_constant__ FrameDev f, int flags, int half_units)
+__global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid_constant__ FrameDev f, int flags, int area_units)
 {
 #ifdef RC_PROFILE
     long long rc_t = clock64();
@@ -906,32 +820,15 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
     const int cx0 = ctbx << f.log2_ctb, cy0 = ctby << f.log2_ctb;      // luma origin of the CTB
     const int bd = f.bd;
 
-#if RC_DIRECT
     // ---- shared memory carve-up: [residual area | tile, TB lists, barrier].  The residual area (per-warp
-    //      scratch + the CTB's coefficients, `half_units` x 128 B) holds the PU records and the cell map
+    //      scratch + the CTB's coefficients, `area_units` x 128 B) holds the PU records and the cell map
     //      during the prediction phase.
     uint8_t *pool = smem_raw;
-    const int pool_bytes = half_units * POOL_UNIT;
+    const int pool_bytes = area_units * POOL_UNIT;
     CtbTile tile;
-    PuRecD *recs = (PuRecD *)smem_raw;
-    uint8_t *cmap = smem_raw + MAX_CTB_PUS * sizeof(PuRecD);                            // PU of every 4x4 cell, 0xff = none
+    PuRec *recs = (PuRec *)smem_raw;
+    uint8_t *cmap = smem_raw + MAX_CTB_PUS * sizeof(PuRec);                            // PU of every 4x4 cell, 0xff = none
     uint32_t *sp = (uint32_t *)(smem_raw + pool_bytes);
-#else
-    // ---- shared memory carve-up: [window pool | prediction-only words | tile, TB lists, barriers]
-    uint8_t *pool = smem_raw;
-    const int half_bytes = half_units * POOL_UNIT, pool_bytes = POOL_SLOTS * half_bytes;
-    CtbTile tile;
-    uint32_t *sp = (uint32_t *)(smem_raw + pool_bytes);
-    PuRec *recs = (PuRec *)sp;                  sp += MAX_CTB_PUS * PUREC_WORDS;
-    int *cumA = (int *)sp;                      sp += MAX_CTB_PUS + 4;
-    uint16_t *listA = (uint16_t *)sp;           sp += MAX_CTB_CELLS / 2;
-    uint16_t *cumW = (uint16_t *)sp;            sp += 2 * (MAX_CTB_PUS + 2) / 2;         // [luma | chroma plane][PU] window units (128 B) before this PU
-    uint8_t *nxt = (uint8_t *)sp;               sp += 2 * MAX_CTB_PUS / 4;               // [..][PU] first PU of the round after one starting here
-    uint8_t *rstart = (uint8_t *)sp;            sp += 2 * (MAX_ROUNDS + 4) / 4;          // [..][round] first PU, [..][MAX_ROUNDS + 1] = count
-    int *scan_tmp = (int *)sp;                  sp += 2 * 4 * RC_WARPS;                  // [cells | units][class][warp]
-    uint32_t *issue = sp;                       sp += N_KINDS * MAX_CTB_PUS * 2;         // TMA parameters per (kind, PU)
-#endif
-    // ---- end of the prediction-only words (MCONLY_WORDS)
     // valid samples of this CTB per plane type (the picture may end inside it)
     const int vw0 = min(cs, f.pw[0] - cx0), vh0 = min(cs, f.ph[0] - cy0);
     const int vwc = f.nplanes == 3 ? min(cs >> f.hs, f.pw[1] - (cx0 >> f.hs)) : 0;
@@ -942,10 +839,9 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
     tile.size0 = tile.pitch0 * cs;
     tile.sizec = f.nplanes == 3 ? tile.pitchc * (cs >> f.vs) : 0;
     sp += tile.size0 + 2 * tile.sizec;
-    int *done = (int *)sp;                      sp += POOL_SLOTS;                        // warps finished with each pool slot
     int *tu_cnt = (int *)sp;                    sp += 18;                         // [0..3] counts, [4..7] bases, [8..11] cursors, [12] coef lo, [13] coef hi, [14] batch counter, [15..16] sparse pair range
     uint16_t *tu_list = (uint16_t *)sp;         sp += MAX_CTB_TUS / 2;
-    uint64_t *mbar = (uint64_t *)(((uintptr_t)sp + 7) & ~(uintptr_t)7);           sp += 2 * POOL_SLOTS + 2;   // one per pool slot
+    uint64_t *mbar = (uint64_t *)(((uintptr_t)sp + 7) & ~(uintptr_t)7);           sp += 4;                     // coefficient bulk copy
     WarpScratch *scratch2 = f.cfi == 3 ? (WarpScratch *)(((uintptr_t)sp + 15) & ~(uintptr_t)15) : nullptr;   // cross-component
 
     const int2 prange = f.ctb_pu_range[ctb];
@@ -978,13 +874,8 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
     }
     if (tid < 12) tu_cnt[tid] = 0;
     if (tid == 12) { tu_cnt[12] = 0x7fffffff; tu_cnt[13] = 0; tu_cnt[14] = 0; }
-#if RC_DIRECT
     if (tid == 0) mbar_init(mbar, 1);
     if (tid < CMAP_STRIDE * CMAP_STRIDE / 4) ((uint32_t *)cmap)[tid] = 0xffffffffu;
-    (void)done;
-#else
-    if (tid < POOL_SLOTS) { mbar_init(mbar + tid, 1); done[tid] = 0; }
-#endif
     __syncthreads();
     RC_MARK(1);
 
@@ -1014,9 +905,7 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
         }
     };
 
-    int rounds_done = 0;                                   // rounds that went through the pool (phase of mbar[0] afterwards)
     // ================================================================ phase 1: prediction
-#if RC_DIRECT
     if (do_mc) {
         // ---- 1a. four threads per PU: thread `sub` prepares the window of kind `sub` (list slot
         //      sub & 1, luma / chroma sub >> 1) and the epilogue constants of plane `sub`, and
@@ -1029,7 +918,7 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
                 const ohcu_pu pu = load_pu(f.pus + p0 + p);
                 const ohcu_slice_tab &sl = f.slices[pu.slice];
                 const bool bi = pu.pred_flag == OHCU_PF_BI;
-                PuRecD &rc = recs[p];
+                PuRec &rc = recs[p];
                 const int lA = (pu.pred_flag & 1) ? 0 : 1;
                 const int x4 = (pu.x0 - cx0) >> 2, y4 = (pu.y0 - cy0) >> 2, w4 = pu.w >> 2, h4 = pu.h >> 2;
                 if (sub == 0)
@@ -1039,9 +928,9 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
                     uint32_t org = 0, par = 0;
                     if ((s == 0 || bi) && (pt == 0 || f.nplanes == 3)) {
                         const int l = s ? 1 : lA;
-                        const WinGeom g = win_geom<HIGH>(f, pu, l, pt == 0);
+                        const WinGeom g = win_geom(f, pu, l, pt == 0);
                         const int slot = sl.ref_slot[l][(l ? pu.ref_idx[1] : pu.ref_idx[0]) & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1);
-                        org = ((uint32_t)(g.ax + g.offx) & 0xffffu) | ((uint32_t)g.y0 << 16);
+                        org = ((uint32_t)g.x0 & 0xffffu) | ((uint32_t)g.y0 << 16);
                         par = (uint32_t)slot | ((uint32_t)g.mx << 8) | ((uint32_t)g.my << 11);
                     }
                     rc.org[s][pt] = org;
@@ -1092,7 +981,7 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
         const int p = (cy << 2) < cs ? cmap[cy * CMAP_STRIDE + cx] : 0xff;
         if (p != 0xff) {
             const int sh1 = bd - 8;                        // first-stage shift (template :2486)
-            const PuRecD &rc = recs[p];
+            const PuRec &rc = recs[p];
             const uint32_t rect = rc.rect;
             const int ccx = cx - (int)(rect & 15), ccy = cy - (int)((rect >> 4) & 15);
             const bool pbi = (rect >> 18) & 1;
@@ -1101,7 +990,7 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
                 const uint32_t ew[3] = {rc.epi[0][0], rc.epi[0][1], rc.epi[0][2]};
                 unpack_epi(ew, bd, e);
                 uint32_t *tp = tile.p(0) + (cy * 4) * tile.pitch(0) + cx * 2;
-                mc_cell_d<HIGH, 8, 4, 4>(f, 0, rc.org[0][0], rc.par[0][0], rc.org[1][0], rc.par[1][0], pbi, ccx * 4, ccy * 4, sh1, e, tp,
+                mc_cell<HIGH, 8, 4, 4>(f, 0, rc.org[0][0], rc.par[0][0], rc.org[1][0], rc.par[1][0], pbi, ccx * 4, ccy * 4, sh1, e, tp,
                                          tile.pitch(0));
             }
             if (f.nplanes == 3) {
@@ -1114,9 +1003,9 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
                     unpack_epi(ew, bd, e);
                     uint32_t *tp = tile.p(c) + (cy * ch) * tile.pitch(c) + ((cx * cw_) >> 1);
                     const uint32_t oA = rc.org[0][1], pA = rc.par[0][1], oB = rc.org[1][1], pB = rc.par[1][1];
-                    if (hs && vs) mc_cell_d<HIGH, 4, 2, 2>(f, c, oA, pA, oB, pB, pbi, ccx * 2, ccy * 2, sh1, e, tp, tile.pitch(c));
-                    else if (hs) mc_cell_d<HIGH, 4, 2, 4>(f, c, oA, pA, oB, pB, pbi, ccx * 2, ccy * 4, sh1, e, tp, tile.pitch(c));
-                    else mc_cell_d<HIGH, 4, 4, 4>(f, c, oA, pA, oB, pB, pbi, ccx * 4, ccy * 4, sh1, e, tp, tile.pitch(c));
+                    if (hs && vs) mc_cell<HIGH, 4, 2, 2>(f, c, oA, pA, oB, pB, pbi, ccx * 2, ccy * 2, sh1, e, tp, tile.pitch(c));
+                    else if (hs) mc_cell<HIGH, 4, 2, 4>(f, c, oA, pA, oB, pB, pbi, ccx * 2, ccy * 4, sh1, e, tp, tile.pitch(c));
+                    else mc_cell<HIGH, 4, 4, 4>(f, c, oA, pA, oB, pB, pbi, ccx * 4, ccy * 4, sh1, e, tp, tile.pitch(c));
                 }
             }
         }
@@ -1124,249 +1013,6 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
     } else {
         sort_tus();
     }
-#else
-    if (do_mc) {
-        // ---- 1a. four threads per PU: thread `sub` prepares the window of kind `sub` (list slot
-        //      sub & 1, luma / chroma sub >> 1) and the epilogue constants of plane `sub`;
-        //      64 PUs per pass.  Class scans (stride-4 lanes) give, per kind, the window units
-        //      before each PU and, per list slot, the cells before each PU.
-        const int sub = tid & 3;
-        int carryW = 0, carryC = 0;
-#pragma unroll 1
-        for (int base = 0; base < np; base += RC_THREADS / 4) {
-            const int p = base + (tid >> 2);
-            int wu = 0, cc = 0;
-            if (p < np) {
-                const ohcu_pu pu = load_pu(f.pus + p0 + p);
-                const ohcu_slice_tab &sl = f.slices[pu.slice];
-                const bool bi = pu.pred_flag == OHCU_PF_BI;
-                const int ncell = (pu.w >> 2) * (pu.h >> 2);
-                PuRec &rc = recs[p];
-                const int lA = (pu.pred_flag & 1) ? 0 : 1;
-                if (sub == 0)
-                    rc.rect = (uint32_t)(((pu.x0 - cx0) >> 2) | (((pu.y0 - cy0) >> 2) << 4) | ((pu.w >> 2) << 8) |
-                                         ((pu.h >> 2) << 13) | ((bi ? 1 : 0) << 18));
-                cc = sub == 0 ? ncell : 0;
-                {
-                    const int s = sub & 1, pt = sub >> 1;
-                    uint32_t gw = 0;
-                    if ((s == 0 || bi) && (pt == 0 || f.nplanes == 3)) {
-                        const int l = s ? 1 : lA;
-                        const WinGeom g = win_geom<HIGH>(f, pu, l, pt == 0);
-                        const int pitch = box_w(HIGH, g.wcls) * (HIGH ? 2 : 1);
-                        const int bytes = pitch * box_h(g.hcls);
-                        wu = bytes / POOL_UNIT;                // one plane: Cb and Cr run in separate rounds
-                        // what the TMA issue of this window needs (box of plane pt; Cr follows Cb)
-                        const int slot = sl.ref_slot[l][(l ? pu.ref_idx[1] : pu.ref_idx[0]) & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1);
-                        uint32_t *iw = issue + (sub * MAX_CTB_PUS + p) * 2;
-                        iw[0] = (uint32_t)tmap_index(slot, pt, g.wcls, g.hcls) | ((uint32_t)(g.ax + PAD_X) << 12);
-                        iw[1] = (uint32_t)(g.y0 + PAD_Y) | ((uint32_t)(bytes >> 7) << 16);
-                        gw = ((uint32_t)(pitch >> 4) << 12) | ((uint32_t)g.offx << 16) | ((uint32_t)g.mx << 20) |
-                             ((uint32_t)g.my << 23) | ((uint32_t)g.hcls << 26);
-                    }
-                    rc.geom[s][pt] = gw;
-                }
-                if (sub < 3) {                                 // epilogue constants of plane `sub` (see Epi)
-                    const int c = sub;
-                    const bool wflag = sl.weight_flag != 0;
-                    const int denom = c ? sl.chroma_log2_weight_denom : sl.luma_log2_weight_denom;
-                    int wx[2], ox[2];
-#pragma unroll
-                    for (int l = 0; l < 2; l++) {
-                        const int ri = (l ? pu.ref_idx[1] : pu.ref_idx[0]) & (OHCU_MAX_REFS - 1);
-                        wx[l] = c ? sl.chroma_weight[l][ri][c - 1] : sl.luma_weight[l][ri];
-                        ox[l] = (c ? sl.chroma_offset[l][ri][c - 1] : sl.luma_offset[l][ri]) * (1 << (bd - 8));
-                    }
-                    int wA, wB = 0, add, sh, post = 0;
-                    if (!bi) {
-                        if (!wflag) { wA = 1; sh = 14 - bd; add = 1 << (13 - bd); }
-                        else { wA = wx[lA]; sh = denom + 14 - bd; add = 1 << (sh - 1); post = ox[lA]; }
-                    } else {
-                        if (!wflag) { wA = 1; wB = 1; sh = 15 - bd; add = 1 << (14 - bd); }
-                        else {
-                            const int log2Wd = denom + 14 - bd;
-                            wA = wx[1]; wB = wx[0]; sh = log2Wd + 1; add = (ox[0] + ox[1] + 1) * (1 << log2Wd);
-                        }
-                    }
-                    rc.epi[c][0] = ((uint32_t)wA & 0xffffu) | ((uint32_t)wB << 16);
-                    rc.epi[c][1] = (uint32_t)add;
-                    rc.epi[c][2] = ((uint32_t)sh & 0xffffu) | ((uint32_t)post << 16);
-                }
-            }
-            // class scans inside the warp (lanes of one class are 4 apart), then across warps
-            int iw_ = wu, ic_ = cc;
-#pragma unroll
-            for (int d = 4; d < 32; d <<= 1) {
-                const int y = __shfl_up_sync(0xffffffffu, iw_, d), z = __shfl_up_sync(0xffffffffu, ic_, d);
-                if (lane >= d) { iw_ += y; ic_ += z; }
-            }
-            if (lane >= 28) { scan_tmp[sub * RC_WARPS + warp] = ic_; scan_tmp[(4 + sub) * RC_WARPS + warp] = iw_; }
-            __syncthreads();
-            int beforeC = 0, totalC = 0, beforeW = 0, totalW = 0;
-#pragma unroll
-            for (int w = 0; w < RC_WARPS; w++) {
-                const int a = scan_tmp[sub * RC_WARPS + w], b = scan_tmp[(4 + sub) * RC_WARPS + w];
-                if (w < warp) { beforeC += a; beforeW += b; }
-                totalC += a; totalW += b;
-            }
-            // the windows of a PU sit together (slot A, then slot B): units before the PU = both classes
-            const int exW = carryW + beforeW + iw_ - wu;
-            const int exBoth = exW + __shfl_xor_sync(0xffffffffu, exW, 1);
-            if (p < np) {
-                if (!(sub & 1)) cumW[(sub >> 1) * (MAX_CTB_PUS + 2) + p] = (uint16_t)exBoth;
-                if (sub == 0) cumA[p] = carryC + beforeC + ic_ - cc;
-            }
-            carryW += totalW; carryC += totalC;
-            __syncthreads();                               // scan_tmp is reused by the next pass
-        }
-        {
-            const int both = carryW + __shfl_xor_sync(0xffffffffu, carryW, 1);
-            if (tid < 4 && !(tid & 1)) cumW[(tid >> 1) * (MAX_CTB_PUS + 2) + np] = (uint16_t)both;
-            if (tid == 0) cumA[np] = carryC;
-        }
-        __syncthreads();
-        RC_MARK(2);
-        const int totA = cumA[np];
-
-        // ---- 1b. greedy rounds per plane type: nxt[pt][p] = first PU that no longer fits a round starting at p
-        const int npt = f.nplanes == 3 ? 2 : 1;
-        for (int i = tid; i < npt * np; i += RC_THREADS) {
-            const int k = i >= np, p = i - k * np;
-            const uint16_t *cw = cumW + k * (MAX_CTB_PUS + 2);
-            const int target = cw[p] + half_units;
-            int lo = p + 1, hi = np;                       // largest e with cw[e] <= target (a PU's windows always fit: e > p)
-            while (lo < hi) {
-                const int mid = (lo + hi + 1) >> 1;
-                if (cw[mid] <= target) lo = mid; else hi = mid - 1;
-            }
-            nxt[k * MAX_CTB_PUS + p] = (uint8_t)lo;
-        }
-        __syncthreads();
-        // one thread per plane type walks its rounds; the other warps build the cell list meanwhile
-        if (tid < npt) {
-            const int k = tid;
-            uint8_t *rs = rstart + k * (MAX_ROUNDS + 4);
-            int n = 0;
-            for (int q = 0; q < np && n < MAX_ROUNDS; q = nxt[k * MAX_CTB_PUS + q]) rs[n++] = (uint8_t)q;
-            rs[n] = (uint8_t)np;
-            rs[MAX_ROUNDS + 1] = (uint8_t)n;
-        } else if (tid >= 32) {
-            // ---- 1c. cells sorted by PU: entry = PU | cell column << 7 | cell row << 11
-            const int tot = min(totA, MAX_CTB_CELLS);
-            for (int i = tid - 32; i < tot; i += RC_THREADS - 32) {
-                int lo = 0, hi = np - 1;                   // largest p with cumA[p] <= i
-                while (lo < hi) {
-                    const int mid = (lo + hi + 1) >> 1;
-                    if (cumA[mid] <= i) lo = mid; else hi = mid - 1;
-                }
-                const int local = i - cumA[lo];
-                const int nx = (recs[lo].rect >> 8) & 31;
-                const int cy = fastdiv(local, fastinv(nx)), cx = local - cy * nx;
-                listA[i] = (uint16_t)(lo | (cx << 7) | (cy << 11));
-            }
-        }
-        __syncthreads();
-        RC_MARK(3);
-
-        // ---- 1d. rounds, plane by plane, through the two pool halves.  No block barrier in the
-        //      loop: a warp that has filtered its cells of round i goes on to round i + 1 (already
-        //      resident); the LAST warp to leave round i refills that half with round i + 2.
-        const int sh1 = bd - 8;                            // first-stage shift (template :2486)
-        const int nr0 = rstart[MAX_ROUNDS + 1], nr1 = npt == 2 ? rstart[(MAX_ROUNDS + 4) + MAX_ROUNDS + 1] : 0;
-        const int R = nr0 + 2 * nr1;
-        rounds_done = R;
-        auto locate = [&](int i, int &c, int &r) {        // flat round -> (plane, round of its plane type)
-            if (i < nr0) { c = 0; r = i; }
-            else if (i < nr0 + nr1) { c = 1; r = i - nr0; }
-            else { c = 2; r = i - nr0 - nr1; }
-        };
-        auto issue_round = [&](int i, int t, int n) {     // by threads t, t + n, ...
-            int c, r;
-            locate(i, c, r);
-            const int pt = c > 0;
-            const uint8_t *rs = rstart + pt * (MAX_ROUNDS + 4);
-            const int pa = rs[r], pb = rs[r + 1];
-            const uint16_t *cw = cumW + pt * (MAX_CTB_PUS + 2);
-            uint64_t *bar = mbar + (i % POOL_SLOTS);
-            uint8_t *buf = pool + (i % POOL_SLOTS) * half_bytes;
-            if (t == 0) mbar_expect_tx(bar, (uint32_t)(cw[pb] - cw[pa]) * POOL_UNIT);
-            for (int p = pa + t; p < pb; p += n) {
-                uint8_t *dst = buf + (cw[p] - cw[pa]) * POOL_UNIT;
-                const bool bi = (recs[p].rect >> 18) & 1;
-#pragma unroll 1
-                for (int sl = 0; sl < (bi ? 2 : 1); sl++) {
-                    const uint32_t *iw = issue + ((2 * pt + sl) * MAX_CTB_PUS + p) * 2;
-                    const uint32_t w0 = iw[0], w1 = iw[1];
-                    const CUtensorMap *m = f.tmaps + (w0 & 0xfffu) + (c == 2 ? N_WCLS * N_HCLS : 0);
-                    tma_load_2d(dst, m, (int)(w0 >> 12), (int)(w1 & 0xffffu), bar);
-                    dst += (w1 >> 16) * POOL_UNIT;
-                }
-            }
-        };
-#pragma unroll 1
-        for (int i = 0; i < min(R, POOL_SLOTS); i++) issue_round(i, tid, RC_THREADS);
-        sort_tus();
-        RC_MARK(4);
-#pragma unroll 1
-        for (int i = 0; i < R; i++) {
-            int c, r;
-            locate(i, c, r);
-            const int pt = c > 0;
-            const uint8_t *rs = rstart + pt * (MAX_ROUNDS + 4);
-            const int pa = rs[r], pb = rs[r + 1];
-            const uint16_t *cw = cumW + pt * (MAX_CTB_PUS + 2);
-            const int slot = i % POOL_SLOTS;
-            const uint8_t *buf = pool + slot * half_bytes - cw[pa] * POOL_UNIT;
-            const int clo = cumA[pa], chi = min(cumA[pb], MAX_CTB_CELLS);
-            RC_MARK(11);                                   // round bookkeeping
-            mbar_wait(mbar + slot, (i / POOL_SLOTS) & 1);
-            RC_MARK(12);                                   // waiting for the windows
-#pragma unroll 1
-            // consecutive rounds start on different warps: with no barrier between rounds, the
-            // warps of a CTA then work on the resident rounds side by side
-            for (int ci = clo + ((tid - i * ROUND_ROTATE) & (RC_THREADS - 1)); ci < chi; ci += RC_THREADS) {
-                const int ent = listA[ci];
-                const int p = ent & 127, cx = (ent >> 7) & 15, cy = ent >> 11;
-                const PuRec &rc = recs[p];
-                const uint32_t rect = rc.rect;
-                const int x4 = rect & 15, y4 = (rect >> 4) & 15;
-                const bool pbi = (rect >> 18) & 1;
-                const uint32_t gA = rc.geom[0][pt], gB = rc.geom[1][pt];
-                const uint8_t *winA = buf + cw[p] * POOL_UNIT;
-                const uint8_t *winB = winA + (issue[((2 * pt) * MAX_CTB_PUS + p) * 2 + 1] >> 16) * POOL_UNIT;
-                Epi e;
-                const uint32_t ew[3] = {rc.epi[c][0], rc.epi[c][1], rc.epi[c][2]};
-                unpack_epi(ew, bd, e);
-                if (pt == 0) {
-                    uint32_t *tp = tile.p(0) + ((y4 + cy) * 4) * tile.pitch(0) + ((x4 + cx) * 2);
-                    mc_cell<HIGH, 8, 4, 4>(winA, gA, winB, gB, pbi, cx * 4, cy * 4, sh1, e, tp, tile.pitch(0));
-                } else {
-                    const int hs = f.hs, vs = f.vs;
-                    const int cw_ = 4 >> hs, ch = 4 >> vs;
-                    uint32_t *tp = tile.p(c) + ((y4 + cy) * ch) * tile.pitch(c) + (((x4 + cx) * cw_) >> 1);
-                    if (hs && vs) mc_cell<HIGH, 4, 2, 2>(winA, gA, winB, gB, pbi, cx * 2, cy * 2, sh1, e, tp, tile.pitch(c));
-                    else if (hs) mc_cell<HIGH, 4, 2, 4>(winA, gA, winB, gB, pbi, cx * 2, cy * 4, sh1, e, tp, tile.pitch(c));
-                    else mc_cell<HIGH, 4, 4, 4>(winA, gA, winB, gB, pbi, cx * 4, cy * 4, sh1, e, tp, tile.pitch(c));
-                }
-            }
-            __syncwarp();
-            RC_MARK(13);                                   // cells
-            if (i + POOL_SLOTS < R) {
-                int old = 0;
-                if (lane == 0) old = atomicAdd(&done[slot], 1);
-                old = __shfl_sync(0xffffffffu, old, 0);
-                if (old == RC_WARPS - 1) {                 // every warp has left this slot
-                    if (lane == 0) done[slot] = 0;
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    issue_round(i + POOL_SLOTS, lane, 32);
-                }
-            }
-        }
-    } else {
-        sort_tus();
-    }
-
-#endif
 
     RC_MARK(5);
     // ================================================================ phase 2: residual
@@ -1390,12 +1036,12 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
         int16_t *coef_sm = (int16_t *)(pool + RC_WARPS * sizeof(WarpScratch));
         const uint32_t clo = sparse ? 0u : (uint32_t)tu_cnt[12], chi = (uint32_t)tu_cnt[13];
         const uint32_t cbytes = (chi - clo) * 2;
-        const bool staged = sparse || (chi > clo && cbytes <= (uint32_t)coef_area(half_units) * 2 && !(cbytes & 15) && !(clo & 7));
+        const bool staged = sparse || (chi > clo && cbytes <= (uint32_t)coef_area(area_units) * 2 && !(cbytes & 15) && !(clo & 7));
         if (sparse) {
             // pairs -> dense blocks: clear the CTB's coefficient area, then scatter
             const uint32_t *src = (const uint32_t *)f.coeffs + tu_cnt[15];
             const int npair = tu_cnt[16];
-            const uint32_t area = min(chi, (uint32_t)coef_area(half_units));
+            const uint32_t area = min(chi, (uint32_t)coef_area(area_units));
             for (uint32_t o = tid * 8; o < area; o += RC_THREADS * 8) *(uint4 *)(coef_sm + o) = make_uint4(0, 0, 0, 0);
             __syncthreads();
             for (int base = 0;;) {
@@ -1420,7 +1066,7 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
                 asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                              ::"r"(smem_u32(coef_sm)), "l"(f.coeffs + clo), "r"(cbytes), "r"(smem_u32(mbar)) : "memory");
             }
-            mbar_wait(mbar, ((rounds_done + POOL_SLOTS - 1) / POOL_SLOTS) & 1);
+            mbar_wait(mbar, 0);
             RC_MARK(7);
         }
         CoefSrc cs;
@@ -1474,58 +1120,41 @@ int rc_profile_read(unsigned long long *out, int reset)
 extern "C" int ohcu_rc_profile(unsigned long long *out, int reset) { return rc_profile_read(out, reset); }
 #endif
 
-// shared memory of one CTA without the window pool
+// shared memory of one CTA without the residual area
 static size_t recon_fixed_smem(int log2_ctb, int nplanes, int hs, int vs, int cfi)
 {
     const int cs = 1 << log2_ctb;
-    size_t words = RC_DIRECT ? 0 : MCONLY_WORDS;
+    size_t words = 0;
     for (int c = 0; c < nplanes; c++) {
         const int h = c ? hs : 0, v = c ? vs : 0;
         words += (size_t)(((cs >> h) >> 1) + 2) * (cs >> v);
     }
-    words += POOL_SLOTS + 18 + MAX_CTB_TUS / 2 + 2 * POOL_SLOTS + 4;
+    words += 18 + MAX_CTB_TUS / 2 + 4 + 4;
     return words * 4 + (cfi == 3 ? RC_WARPS * sizeof(WarpScratch) + 16 : 0);
 }
 
-// Units (128 B) of one round of windows: the largest pool with which RC_MINB CTAs still share an
-// SM (228 KB, 1 KB reserved per CTA); formats whose tile leaves no room for that (4:4:4) fall back
-// to one CTA fewer.  -DRC_HALF_UNITS=n fixes it (A/B measurements).
-int rc_half_units(int log2_ctb, int nplanes, int hs, int vs, int cfi)
+// Units (128 B) of the residual area: per-warp scratch + a full CTB of coefficients (it also holds
+// the PU records and the cell map of the prediction phase, which are smaller).
+static int rc_area_units(int log2_ctb, int nplanes, int hs, int vs)
 {
-#ifdef RC_HALF_UNITS
-    return RC_HALF_UNITS;
-#elif RC_DIRECT
-    // the residual area: per-warp scratch + a full CTB of coefficients (it also holds the PU records
-    // and the cell map of the prediction phase, which are smaller)
     const int need = (1 << (2 * log2_ctb)) + (nplanes == 3 ? 2 * ((1 << (2 * log2_ctb)) >> (hs + vs)) : 0);
-    (void)cfi; (void)recon_fixed_smem;
+    static_assert(MAX_CTB_PUS * sizeof(PuRec) + CMAP_STRIDE * CMAP_STRIDE <= RC_WARPS * sizeof(WarpScratch),
+                  "PU records + cell map must fit the residual area");
     return (RC_WARPS * (int)sizeof(WarpScratch) + 2 * need + POOL_UNIT - 1) / POOL_UNIT;
-#else
-    const size_t fixed = recon_fixed_smem(log2_ctb, nplanes, hs, vs, cfi);
-    for (int ctas = RC_MINB; ctas >= 1; ctas--) {
-        const long room = (long)(228 * 1024 / ctas - 1024) - (long)fixed;
-        const int hu = (int)(room / (POOL_SLOTS * POOL_UNIT));
-        // the residual phase needs the per-warp scratch and a full CTB of coefficients in pool + prediction-only words
-        const int need = (1 << (2 * log2_ctb)) + (nplanes == 3 ? 2 * ((1 << (2 * log2_ctb)) >> (hs + vs)) : 0);
-        if (hu >= MIN_HALF_UNITS && coef_area(hu < MAX_HALF_UNITS ? hu : MAX_HALF_UNITS) >= need)
-            return hu < MAX_HALF_UNITS ? hu : MAX_HALF_UNITS;
-    }
-    return MAX_HALF_UNITS;
-#endif
 }
 
-size_t recon_smem_bytes(const FrameDev &f, int half_units)
+size_t recon_smem_bytes(const FrameDev &f, int area_units)
 {
-    return (size_t)(RC_DIRECT ? 1 : POOL_SLOTS) * half_units * POOL_UNIT + recon_fixed_smem(f.log2_ctb, f.nplanes, f.hs, f.vs, f.cfi);
+    return (size_t)area_units * POOL_UNIT + recon_fixed_smem(f.log2_ctb, f.nplanes, f.hs, f.vs, f.cfi);
 }
 
-int recon_sparse_ctb_coefs(int log2_ctb, int nplanes, int hs, int vs, int cfi) { return coef_area(rc_half_units(log2_ctb, nplanes, hs, vs, cfi)); }
+int recon_sparse_ctb_coefs(int log2_ctb, int nplanes, int hs, int vs) { return coef_area(rc_area_units(log2_ctb, nplanes, hs, vs)); }
 
 int launch_recon(const FrameDev &f, int flags, cudaStream_t st)
 {
     if (!(flags & 3)) return 0;
     if (!((flags & 1) && f.n_pu > 0) && !((flags & 2) && f.n_tu > 0)) return 0;
-    const int hu = rc_half_units(f.log2_ctb, f.nplanes, f.hs, f.vs, f.cfi);
+    const int hu = rc_area_units(f.log2_ctb, f.nplanes, f.hs, f.vs);
     const size_t smem = recon_smem_bytes(f, hu);
     static bool attr_set = false;
     if (!attr_set) {

@@ -249,7 +249,9 @@ int ohcu_append_tu_inplace(ohcu_ctx *ctx, int job, const ohcu_tu *recs, int n);
  * the dense blocks in shared memory.  The coefficient area of a CTB is the
  * concatenation of its blocks in append order:
  *   recs[i].coeff_off = block base inside the CTB's area = sum of N*N of the
- *                       CTB's earlier blocks (a multiple of 16, < 12288)
+ *                       CTB's earlier blocks (a multiple of 16, below the number
+ *                       of samples of a CTB over all planes: 6144 for a 64x64
+ *                       4:2:0 CTB, 12288 for 4:4:4)
  *   recs[i].pad       = number of ohcu_coef of this block
  *   coef.pos          = recs[i].coeff_off + y * N + x
  * coefs holds the pairs of the n blocks back to back, in record order.  The
