@@ -18,44 +18,76 @@ __global__ void copy_picture_kernel(uint8_t *dst, int dpitch, const uint8_t *src
         for (int i = x; i < wbytes; i++) dst[(size_t)y * dpitch + i] = src[(size_t)y * spitch + i];
 }
 
-// Replicated halo of a DPB picture (PAD_X / PAD_Y, ohcu_internal.h): one CTA per padded row.
-// Rows inside the picture only get their left/right margins; rows above/below copy the
-// first/last picture row with its margins.  Equivalent of ff_emulated_edge_mc
-// (videodsp_template.c:22-100) applied once to the whole picture.
+// Replicated halo of a DPB picture (PAD_X / PAD_Y, ohcu_internal.h).  Equivalent of
+// ff_emulated_edge_mc (videodsp_template.c:22-100) applied once to the whole picture.
+// 16-byte stores throughout (plane origins, PAD_X samples and the pitches are multiples of
+// 16 bytes).  Work items of one plane: first the rows above / below the picture, one CTA each
+// (the border row repeated with its own margins), then the picture's rows, one WARP each
+// (left and right margin only).
+struct PadPlane { uint8_t *p; int pitch, pw, ph; };
+struct PadArgs { PadPlane pl[3]; int nplanes; int cta0[4]; };     // cta0[c]: first CTA of plane c
+
 template <typename pixel>
-__global__ void __launch_bounds__(256) pad_kernel(uint8_t *p0, uint8_t *p1, uint8_t *p2, int pitch0, int pitch1, int pitch2,
-                                                   int pw0, int ph0, int pwc, int phc)
+__device__ __forceinline__ uint4 splat16(pixel v)
 {
-    int row = blockIdx.x;
-    const int rows0 = ph0 + 2 * PAD_Y, rowsc = phc + 2 * PAD_Y;
-    uint8_t *plane; int pitch, pw, ph;
-    if (row < rows0) { plane = p0; pitch = pitch0; pw = pw0; ph = ph0; }
-    else if (row < rows0 + rowsc) { row -= rows0; plane = p1; pitch = pitch1; pw = pwc; ph = phc; }
-    else { row -= rows0 + rowsc; plane = p2; pitch = pitch2; pw = pwc; ph = phc; }
-    const int y = row - PAD_Y;
-    const int ys = min(max(y, 0), ph - 1);
-    const pixel *src = (const pixel *)(plane + (ptrdiff_t)ys * pitch);
-    pixel *dst = (pixel *)(plane + (ptrdiff_t)y * pitch);
-    if (y >= 0 && y < ph) {
-        const pixel l = src[0], r = src[pw - 1];
-        for (int t = threadIdx.x; t < 2 * PAD_X; t += blockDim.x) {
-            if (t < PAD_X) dst[t - PAD_X] = l;
-            else dst[pw + t - PAD_X] = r;
+    uint32_t w = sizeof(pixel) == 2 ? (uint32_t)v * 0x00010001u : (uint32_t)v * 0x01010101u;
+    return make_uint4(w, w, w, w);
+}
+
+template <typename pixel>
+__global__ void __launch_bounds__(256) pad_kernel(const PadArgs a)
+{
+    constexpr int P = sizeof(pixel), MARGIN16 = PAD_X * P / 16;          // 16-byte stores per margin
+    int c = 0;
+    while (c + 1 < a.nplanes && (int)blockIdx.x >= a.cta0[c + 1]) c++;
+    const PadPlane pl = a.pl[c];
+    const int cta = blockIdx.x - a.cta0[c];
+    const int tid = threadIdx.x;
+    if (cta < 2 * PAD_Y) {
+        // a row above (cta < PAD_Y) or below the picture
+        const int y = cta < PAD_Y ? cta - PAD_Y : pl.ph + cta - PAD_Y;
+        const pixel *src = (const pixel *)(pl.p + (ptrdiff_t)(cta < PAD_Y ? 0 : pl.ph - 1) * pl.pitch);
+        uint8_t *dst = pl.p + (ptrdiff_t)y * pl.pitch;
+        const int wbytes = pl.pw * P, mid16 = wbytes / 16;
+        const uint4 l = splat16<pixel>(src[0]), r = splat16<pixel>(src[pl.pw - 1]);
+        for (int i = tid; i < MARGIN16; i += 256) *(uint4 *)(dst - PAD_X * P + 16 * i) = l;
+        for (int i = tid; i < mid16; i += 256) *(uint4 *)(dst + 16 * i) = *(const uint4 *)((const uint8_t *)src + 16 * i);
+        // a picture row that does not end on a 16-byte boundary: the tail and the right margin sample by sample
+        if (wbytes & 15) {
+            for (int x = mid16 * (16 / P) + tid; x < pl.pw + PAD_X; x += 256) ((pixel *)dst)[x] = src[min(x, pl.pw - 1)];
+        } else {
+            for (int i = tid; i < MARGIN16; i += 256) *(uint4 *)(dst + wbytes + 16 * i) = r;
         }
     } else {
-        for (int x = -PAD_X + (int)threadIdx.x; x < pw + PAD_X; x += blockDim.x) dst[x] = src[min(max(x, 0), pw - 1)];
+        // eight picture rows, one per warp: lanes store the two margins
+        const int y = (cta - 2 * PAD_Y) * 8 + (tid >> 5), lane = tid & 31;
+        if (y >= pl.ph) return;
+        uint8_t *row = pl.p + (ptrdiff_t)y * pl.pitch;
+        const int wbytes = pl.pw * P;
+        const pixel lv = ((const pixel *)row)[0], rv = ((const pixel *)row)[pl.pw - 1];
+        for (int i = lane; i < MARGIN16; i += 32) *(uint4 *)(row - PAD_X * P + 16 * i) = splat16<pixel>(lv);
+        if (wbytes & 15) {
+            for (int x = lane; x < PAD_X; x += 32) ((pixel *)row)[pl.pw + x] = rv;
+        } else {
+            for (int i = lane; i < MARGIN16; i += 32) *(uint4 *)(row + wbytes + 16 * i) = splat16<pixel>(rv);
+        }
     }
 }
 
 int launch_pad_picture(const FrameDev &f, const PlaneSet &pic, cudaStream_t st)
 {
-    const int rows = f.ph[0] + 2 * PAD_Y + (f.nplanes == 3 ? 2 * (f.ph[1] + 2 * PAD_Y) : 0);
-    if (f.bd > 8)
-        pad_kernel<uint16_t><<<rows, 256, 0, st>>>(pic.p[0], pic.p[1], pic.p[2], pic.pitch[0], pic.pitch[1], pic.pitch[2],
-                                                   f.pw[0], f.ph[0], f.pw[1], f.ph[1]);
-    else
-        pad_kernel<uint8_t><<<rows, 256, 0, st>>>(pic.p[0], pic.p[1], pic.p[2], pic.pitch[0], pic.pitch[1], pic.pitch[2],
-                                                  f.pw[0], f.ph[0], f.pw[1], f.ph[1]);
+    static_assert((PAD_X % 16) == 0, "margins are whole 16-byte stores for 8- and 16-bit samples");
+    PadArgs a{};
+    a.nplanes = f.nplanes;
+    int n = 0;
+    for (int c = 0; c < f.nplanes; c++) {
+        a.pl[c].p = pic.p[c]; a.pl[c].pitch = pic.pitch[c]; a.pl[c].pw = f.pw[c]; a.pl[c].ph = f.ph[c];
+        a.cta0[c] = n;
+        n += 2 * PAD_Y + (f.ph[c] + 7) / 8;
+    }
+    a.cta0[f.nplanes] = n;
+    if (f.bd > 8) pad_kernel<uint16_t><<<n, 256, 0, st>>>(a);
+    else          pad_kernel<uint8_t><<<n, 256, 0, st>>>(a);
     return 1;
 }
 
