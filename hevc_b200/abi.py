@@ -116,6 +116,8 @@ SYMBOLS = {
     "ohcu_append_tu_inplace": (C.c_int, [_P, C.c_int, _P, C.c_int]),
     "ohcu_reserve_coefs": (C.c_int, [_P, C.c_int, C.c_size_t, C.POINTER(_P)]),
     "ohcu_append_tu_sparse": (C.c_int, [_P, C.c_int, _P, C.c_int, _P, C.c_size_t]),
+    "ohcu_append_tu_levels": (C.c_int, [_P, C.c_int, _P, _P, C.c_int, _P, C.c_size_t]),
+    "ohcu_set_scaling_list": (C.c_int, [_P, C.c_int, _P, _P]),
     "ohcu_set_deblock": (C.c_int, [_P, C.c_int, C.POINTER(DeblockIn)]),
     "ohcu_set_sao": (C.c_int, [_P, C.c_int, C.POINTER(SaoIn)]),
     "ohcu_frame_flush": (C.c_int, [_P, C.c_int]),

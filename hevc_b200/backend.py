@@ -9,7 +9,7 @@ import numpy as np
 
 from . import abi
 from .abi import check
-from .sparse import to_sparse
+from .sparse import to_levels, to_sparse
 
 
 def _plane_args(planes):
@@ -84,15 +84,30 @@ class Context:
         ctb_w = (sp.width + (1 << sp.log2_ctb_size) - 1) >> sp.log2_ctb_size
         return to_sparse(fj.tus, fj.coeffs, sp.log2_ctb_size, hs, vs, ctb_w)
 
-    def append(self, job_id, fj, use_deblock=True, use_sao=True, sparse=False):
+    def append(self, job_id, fj, use_deblock=True, use_sao=True, sparse=False, levels=None):
         """Append every list of a synth.FrameJob (or anything with the same arrays); sparse = the
-        coefficients go as (position, level) pairs (True, or the lists sparse_lists() returned)."""
+        coefficients go as (position, level) pairs (True, or the lists sparse_lists() returned);
+        levels = (quant, scaling) : fj.coeffs holds UN-scaled levels, quant one QUANT_DTYPE record per
+        TU, scaling None or (sl[4][6][64], sl_dc[2][6]) uint8 arrays - the device dequantises."""
         lib, h = self.lib, self.handle
         for i in range(len(fj.slices)):
             tab = abi.SliceTab.from_buffer_copy(fj.slices[i].tobytes())
             check(lib.ohcu_set_slice(h, job_id, i, C.byref(tab)), "ohcu_set_slice")
         check(lib.ohcu_append_pu(h, job_id, fj.pus.ctypes.data, len(fj.pus)), "ohcu_append_pu")
-        if len(fj.tus) and sparse:
+        if len(fj.tus) and levels is not None:
+            quant, scaling = levels
+            sp = self.sp
+            hs = 1 if sp.chroma_format_idc in (1, 2) else 0
+            vs = 1 if sp.chroma_format_idc == 1 else 0
+            ctb_w = (sp.width + (1 << sp.log2_ctb_size) - 1) >> sp.log2_ctb_size
+            recs, q, pairs = to_levels(fj.tus, quant, fj.coeffs, sp.log2_ctb_size, hs, vs, ctb_w)
+            if scaling is not None:
+                sl, sl_dc = (np.ascontiguousarray(a, dtype=np.uint8) for a in scaling)
+                assert sl.shape == (4, 6, 64) and sl_dc.shape == (2, 6)
+                check(lib.ohcu_set_scaling_list(h, job_id, sl.ctypes.data, sl_dc.ctypes.data), "ohcu_set_scaling_list")
+            check(lib.ohcu_append_tu_levels(h, job_id, recs.ctypes.data, q.ctypes.data, len(recs), pairs.ctypes.data,
+                                            len(pairs)), "ohcu_append_tu_levels")
+        elif len(fj.tus) and sparse:
             recs, pairs = sparse if isinstance(sparse, tuple) else self.sparse_lists(fj)
             check(lib.ohcu_append_tu_sparse(h, job_id, recs.ctypes.data, len(recs), pairs.ctypes.data, len(pairs)),
                   "ohcu_append_tu_sparse")
@@ -162,7 +177,8 @@ class Context:
         return planes
 
     # ---- convenience: one frame, synchronously (tests, smoke) -----------------
-    def reconstruct(self, fj, refs, out_slot=None, out_init=None, stages=0, use_deblock=True, use_sao=True, sparse=False):
+    def reconstruct(self, fj, refs, out_slot=None, out_init=None, stages=0, use_deblock=True, use_sao=True, sparse=False,
+                    levels=None):
         """Upload refs to slots 0.., run one frame job, return the reconstructed planes."""
         if out_slot is None:
             out_slot = self.sp.dpb_slots - 1
@@ -172,7 +188,7 @@ class Context:
         if out_init is not None:
             self.upload(out_slot, out_init)
         j = self.begin(out_slot)
-        self.append(j, fj, use_deblock=use_deblock, use_sao=use_sao, sparse=sparse)
+        self.append(j, fj, use_deblock=use_deblock, use_sao=use_sao, sparse=sparse, levels=levels)
         self.stage(j)
         self.launch(j, out_slot, stages)
         self.sync(j)

@@ -57,6 +57,8 @@ template <typename T> struct Arena {      // pinned host staging + device copy
     bool carved = false;                  // lives inside the job's table block (Job::tab_h / tab_d)
 };
 
+constexpr size_t SL_BYTES = 4 * 6 * 64 + 2 * 6;      // ScalingList, hevc_ps.h:605-610
+
 struct Job {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
@@ -83,7 +85,10 @@ struct Job {
     size_t tab_end[4] = {0, 0, 0, 0};                // bytes up to and including: CTB ranges + slices, SAO, deblock, is_pcm
     // sparse form (ohcu_append_tu_sparse): the arena holds ohcu_coef pairs, ncoeff counts int16
     Arena<int2> ctb_coef_range;  // per CTB: first pair, number of pairs
-    int coef_form = 0;           // 0 none yet, 1 dense, 2 sparse
+    int coef_form = 0;           // 0 none yet, 1 dense, 2 sparse, 3 sparse un-scaled levels + per-TU quantiser
+    Arena<ohcu_tu_quant> tuq;    // levels form: parallel to tus
+    uint8_t *sl_h = nullptr, *sl_d = nullptr;   // ScalingList (sl[4][6][64], sl_dc[2][6])
+    bool has_sl = false;
     std::vector<uint32_t> ctb_seen; uint32_t seen_epoch = 0;   // CTBs met by the current sparse append
     Arena<uint8_t> vbs, hbs, is_pcm; Arena<int8_t> qp; Arena<ohcu_dbparams> db;
     Arena<ohcu_sao> sao;     Arena<uint16_t> sao_flags;
@@ -234,7 +239,9 @@ extern "C" int ohcu_destroy(ohcu_ctx *c)
         free_arena(&j.pus); free_arena(&j.ctb_range); free_arena(&j.slices); free_arena(&j.tus);
         free_arena(&j.coeffs); free_arena(&j.ctb_tu_range); free_arena(&j.ctb_coef_range);
         free_arena(&j.vbs); free_arena(&j.hbs); free_arena(&j.is_pcm); free_arena(&j.qp); free_arena(&j.db);
-        free_arena(&j.sao); free_arena(&j.sao_flags);
+        free_arena(&j.sao); free_arena(&j.sao_flags); free_arena(&j.tuq);
+        if (j.sl_h) cudaFreeHost(j.sl_h);
+        if (j.sl_d) cudaFree(j.sl_d);
         if (j.tab_h) cudaFreeHost(j.tab_h);
         if (j.tab_d) cudaFree(j.tab_d);
         if (j.done) cudaEventDestroy(j.done);
@@ -324,6 +331,9 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
         TRY(alloc_picture(c, &j.recon, false));
         TRY(alloc_arena(&j.pus, c->sp.max_pus));
         TRY(alloc_arena(&j.tus, c->sp.max_tus));
+        TRY(alloc_arena(&j.tuq, c->sp.max_tus));
+        TRYCU(cudaHostAlloc((void **)&j.sl_h, SL_BYTES, cudaHostAllocDefault));
+        TRYCU(cudaMalloc((void **)&j.sl_d, SL_BYTES));
         // twice max_coeffs int16: the sparse form of a frame whose coefficients are all significant
         TRY(alloc_arena(&j.coeffs, 2 * (size_t)c->sp.max_coeffs));
         j.ctb_area.assign(c->nctb, 0);
@@ -494,7 +504,7 @@ extern "C" int ohcu_frame_begin(ohcu_ctx *c, int out_slot, int poc)
     j.has_deblock = j.has_sao = j.has_pcm = false;
     memset(j.ctb_range.h, 0, sizeof(int2) * c->nctb);
     memset(j.ctb_tu_range.h, 0, sizeof(int2) * c->nctb);
-    j.coef_form = 0;
+    j.coef_form = 0; j.has_sl = false;
     std::fill(j.ctb_area.begin(), j.ctb_area.end(), 0);
     return id;
 }
@@ -615,7 +625,7 @@ extern "C" int ohcu_append_tu(ohcu_ctx *c, int job, const ohcu_tu *recs, int n, 
 {
     OPEN_JOB(c, job);
     if (n < 0 || (n && (!recs || !coeffs))) return fail(OHCU_EINVAL, "bad TU list");
-    if (j.coef_form == 2) return fail(OHCU_ESTATE, "job %d already holds sparse coefficients", job);
+    if (j.coef_form >= 2) return fail(OHCU_ESTATE, "job %d already holds sparse coefficients", job);
     j.coef_form = 1;
     if (j.ncoeff + ncoeff > j.coeffs.cap) return fail(OHCU_EOVERFLOW, "coefficient arena full (%zu)", j.coeffs.cap);
     if (j.ncoeff + ncoeff > 0xffffffffull) return fail(OHCU_EOVERFLOW, "coefficient offsets exceed 32 bits");
@@ -629,7 +639,7 @@ extern "C" int ohcu_reserve_coeffs(ohcu_ctx *c, int job, size_t ncoeff, int16_t 
 {
     OPEN_JOB(c, job);
     if (!ptr || !arena_off) return fail(OHCU_EINVAL, "null argument");
-    if (j.coef_form == 2) return fail(OHCU_ESTATE, "job %d already holds sparse coefficients", job);
+    if (j.coef_form >= 2) return fail(OHCU_ESTATE, "job %d already holds sparse coefficients", job);
     j.coef_form = 1;
     ncoeff = (ncoeff + 7) & ~(size_t)7;              // keep blocks 16-byte aligned
     if (j.ncoeff + ncoeff > j.coeffs.cap) return fail(OHCU_EOVERFLOW, "coefficient arena full (%zu)", j.coeffs.cap);
@@ -643,7 +653,7 @@ extern "C" int ohcu_append_tu_inplace(ohcu_ctx *c, int job, const ohcu_tu *recs,
 {
     OPEN_JOB(c, job);
     if (n < 0 || (n && !recs)) return fail(OHCU_EINVAL, "bad TU list");
-    if (j.coef_form == 2) return fail(OHCU_ESTATE, "job %d already holds sparse coefficients", job);
+    if (j.coef_form >= 2) return fail(OHCU_ESTATE, "job %d already holds sparse coefficients", job);
     j.coef_form = 1;
     return add_tus(c, j, recs, n, 0);
 }
@@ -659,11 +669,18 @@ extern "C" int ohcu_reserve_coefs(ohcu_ctx *c, int job, size_t n, ohcu_coef **pt
     return 0;
 }
 
-extern "C" int ohcu_append_tu_sparse(ohcu_ctx *c, int job, const ohcu_tu *recs, int n, const ohcu_coef *coefs, size_t ncoefs)
+// form: 2 = the pairs are coefficients, 3 = un-scaled levels with one ohcu_tu_quant per record
+static int append_pairs(ohcu_ctx *c, int job, const ohcu_tu *recs, const ohcu_tu_quant *quant, int n, const ohcu_coef *coefs,
+                        size_t ncoefs, int form)
 {
     OPEN_JOB(c, job);
-    if (n < 0 || (n && !recs) || (ncoefs && !coefs)) return fail(OHCU_EINVAL, "bad TU list");
+    if (n < 0 || (n && !recs) || (ncoefs && !coefs) || (form == 3 && n && !quant)) return fail(OHCU_EINVAL, "bad TU list");
     if (j.coef_form == 1) return fail(OHCU_ESTATE, "job %d already holds dense coefficients", job);
+    if (j.coef_form && j.coef_form != form)
+        return fail(OHCU_ESTATE, "job %d already holds %s", job, j.coef_form == 3 ? "un-scaled levels" : "scaled coefficients");
+    for (int i = 0; form == 3 && i < n; i++)
+        if (quant[i].qp >= 76 || (quant[i].matrix_id > 5 && quant[i].matrix_id != OHCU_QM_FLAT))
+            return fail(OHCU_EINVAL, "quantiser of TU record %d is malformed", j.n_tu + i);
     if ((size_t)j.n_tu + n > j.tus.cap) return fail(OHCU_EOVERFLOW, "TU arena full (%zu)", j.tus.cap);
     if (j.ncoeff + 2 * ncoefs > j.coeffs.cap) return fail(OHCU_EOVERFLOW, "coefficient arena full (%zu pairs)", j.coeffs.cap / 2);
     int2 *const range = j.ctb_tu_range.h, *const crange = j.ctb_coef_range.h;
@@ -714,9 +731,32 @@ extern "C" int ohcu_append_tu_sparse(ohcu_ctx *c, int job, const ohcu_tu *recs, 
         cross |= (tu.flags & OHCU_TUF_CROSS) != 0;
         dst[i] = tu;
     }
-    j.last_tu_ctb = last; j.has_cross = cross; j.coef_form = 2;
+    if (form == 3 && n) memcpy(j.tuq.h + j.n_tu, quant, (size_t)n * sizeof(ohcu_tu_quant));
+    j.last_tu_ctb = last; j.has_cross = cross; j.coef_form = form;
     j.ncoeff += 2 * ncoefs;
     j.n_tu += n;
+    return 0;
+}
+
+extern "C" int ohcu_append_tu_sparse(ohcu_ctx *c, int job, const ohcu_tu *recs, int n, const ohcu_coef *coefs, size_t ncoefs)
+{
+    return append_pairs(c, job, recs, nullptr, n, coefs, ncoefs, 2);
+}
+
+// scale_and_clip_coeff (hevc_cabac.c:2030-2055) moves to the device: see recon.cu, "levels"
+extern "C" int ohcu_append_tu_levels(ohcu_ctx *c, int job, const ohcu_tu *recs, const ohcu_tu_quant *quant, int n,
+                                     const ohcu_coef *levels, size_t nlevels)
+{
+    return append_pairs(c, job, recs, quant, n, levels, nlevels, 3);
+}
+
+extern "C" int ohcu_set_scaling_list(ohcu_ctx *c, int job, const uint8_t sl[4][6][64], const uint8_t sl_dc[2][6])
+{
+    OPEN_JOB(c, job);
+    if (!sl || !sl_dc) return fail(OHCU_EINVAL, "null scaling list");
+    memcpy(j.sl_h, sl, 4 * 6 * 64);
+    memcpy(j.sl_h + 4 * 6 * 64, sl_dc, 2 * 6);
+    j.has_sl = true;
     return 0;
 }
 
@@ -850,6 +890,12 @@ static int stage_impl(ohcu_ctx *c, int job)
     CU(push_arena(j.pus, j.n_pu, st));
     CU(push_arena(j.tus, j.n_tu, st));
     CU(push_arena(j.coeffs, j.ncoeff, st));
+    if (j.coef_form == 3) {
+        for (int i = 0; !j.has_sl && i < j.n_tu; i++)
+            if (j.tuq.h[i].matrix_id != OHCU_QM_FLAT) return fail(OHCU_EINVAL, "TU %d names a scaling list but none was set", i);
+        CU(push_arena(j.tuq, j.n_tu, st));
+        if (j.has_sl) CU(cudaMemcpyAsync(j.sl_d, j.sl_h, SL_BYTES, cudaMemcpyHostToDevice, st));
+    }
     // the tables: one copy up to the last group this frame uses
     const size_t tab_bytes = j.tab_end[j.has_pcm ? 3 : j.has_deblock ? 2 : j.has_sao ? 1 : 0];
     CU(cudaMemcpyAsync(j.tab_d, j.tab_h, tab_bytes, cudaMemcpyHostToDevice, st));
@@ -866,7 +912,9 @@ static void fill_frame_dev(const ohcu_ctx *c, const Job &j, FrameDev *f)
     fill_seq_dev(c, f);
     f->pus = j.pus.d; f->n_pu = j.n_pu; f->ctb_pu_range = j.ctb_range.d; f->slices = j.slices.d;
     f->tus = j.tus.d; f->n_tu = j.n_tu; f->coeffs = j.coeffs.d; f->ctb_tu_range = j.ctb_tu_range.d;
-    f->ctb_coef_range = j.coef_form == 2 ? j.ctb_coef_range.d : nullptr;
+    f->ctb_coef_range = j.coef_form >= 2 ? j.ctb_coef_range.d : nullptr;
+    f->tu_quant = j.coef_form == 3 ? j.tuq.d : nullptr;
+    f->scaling = j.coef_form == 3 && j.has_sl ? j.sl_d : nullptr;
     f->vbs = j.has_deblock ? j.vbs.d : nullptr; f->hbs = j.hbs.d; f->qp_y = j.qp.d; f->db = j.db.d;
     f->is_pcm = j.has_pcm ? j.is_pcm.d : nullptr;
     f->sao = j.has_sao ? j.sao.d : nullptr; f->sao_ctb_flags = j.sao_flags.d;

@@ -389,8 +389,11 @@ struct LfGeom {
 
 // flags: bit 0 deblock, bit 1 SAO.  Source: the job's reconstructed picture through `maps`
 // (= f.work); destination f.out (the DPB slot).
+#ifndef LF_MINB
+#define LF_MINB 4
+#endif
 template <typename pixel>
-__global__ void __launch_bounds__(LF_THREADS) loopfilter_kernel(const __grid_constant__ FrameDev f,
+__global__ void __launch_bounds__(LF_THREADS, LF_MINB) loopfilter_kernel(const __grid_constant__ FrameDev f,
                                                                  const __grid_constant__ LfMaps maps, int flags)
 {
     extern __shared__ __align__(128) uint8_t lf_smem[];

@@ -50,6 +50,8 @@ struct FrameDev {
     const int16_t *coeffs;
     const int2 *ctb_tu_range;     // per CTB (raster): first TU, number of TUs
     const int2 *ctb_coef_range;   // sparse coefficients: per CTB first (pos, level) pair in `coeffs`, number of pairs; nullptr = dense blocks
+    const ohcu_tu_quant *tu_quant; // levels form: dequantisation parameters per TU (the pairs carry un-scaled levels); else nullptr
+    const uint8_t *scaling;        // ScalingList: sl[4][6][64] then sl_dc[2][6]; nullptr = none set
     // deblock
     const uint8_t *vbs, *hbs;
     const int8_t *qp_y;

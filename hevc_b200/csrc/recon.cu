@@ -626,6 +626,56 @@ __device__ void tu_batch(const FrameDev &f, const CtbTile &tile, int tu0, const 
     }
 }
 
+// ---------------------------------------------------------------- levels -> coefficients
+// The "levels" form of the sparse upload (ohcu_append_tu_levels): the pairs carry the un-scaled
+// trans_coeff_level and the kernel scales them once the CTB's dense blocks are rebuilt, in
+// place: scale_and_clip_coeff (hevc_cabac.c:2030-2055) with the parameters of
+// derive_quant_parameters{,_c} (:1472-1557).  A zero stays zero ((0 + add) >> shift == 0), so
+// scaling the dense block equals scaling the pairs.  Eight lanes of a warp fetch the records of
+// eight TBs, then the warp goes through those blocks one by one.
+__constant__ int c_level_scale[6] = {40, 45, 51, 57, 64, 72};                 // hevc_cabac.c:1470
+
+__device__ __noinline__ void dequant_ctb(const FrameDev &f, int t0, int nt, int16_t *coef_sm, uint32_t area, int warp, int lane)
+{
+    for (int base = warp * 8; base < nt; base += RC_WARPS * 8) {
+        uint32_t off = 0, par = 0;         // par: log2 | qp << 8 | matrix_id << 16 | bypass << 24 | valid << 25
+        if (lane < 8 && base + lane < nt) {
+            const ohcu_tu *tu = f.tus + t0 + base + lane;
+            const ohcu_tu_quant q = f.tu_quant[t0 + base + lane];
+            off = tu->coeff_off;
+            par = (uint32_t)tu->log2_size | (uint32_t)q.qp << 8 | (uint32_t)q.matrix_id << 16 |
+                  (tu->mode == OHCU_TU_BYPASS ? 1u << 24 : 0u) | 1u << 25;
+        }
+#pragma unroll 1
+        for (int k = 0; k < 8; k++) {
+            const uint32_t p = __shfl_sync(0xffffffffu, par, k), o = __shfl_sync(0xffffffffu, off, k);
+            if (!((p >> 25) & 1)) break;
+            const int log2 = p & 0xff, qp = (p >> 8) & 0xff, mid = (p >> 16) & 0xff, n2 = 1 << (2 * log2);
+            if (((p >> 24) & 1) || o + n2 > area) continue;                  // cu_transquant_bypass: levels are the residual
+            const int shift = f.bd + log2 - 5;                              // bit_depth + log2 + 10 - log2_transform_range (15)
+            const long long add = 1ll << (shift - 1);
+            // rem6[] / div6[] of the reference hold zeros at qp 74 and 75 (76 entries declared, 74 initialised,
+            // hevc_cabac.c:1456-1468): reproduced, parity is against the reference
+            const int scale = qp < 74 ? c_level_scale[qp % 6] << (qp / 6) : c_level_scale[0];
+            const uint8_t *m = (mid != OHCU_QM_FLAT && f.scaling) ? f.scaling + ((log2 - 2) * 6 + mid) * 64 : nullptr;
+            const int dc = (m && log2 >= 4) ? f.scaling[4 * 6 * 64 + (log2 - 4) * 6 + mid] : 16;
+            const int ds = log2 > 3 ? log2 - 3 : 0, lw = log2 == 2 ? 2 : 3;  // 16x16 / 32x32 share an 8x8 list
+            int16_t *blk = coef_sm + o;
+            for (int e = lane; e < n2; e += 32) {
+                const int v = blk[e];
+                if (!v) continue;
+                int sm = 16;
+                if (m) {
+                    const int x = e & ((1 << log2) - 1), y = e >> log2;
+                    sm = (log2 >= 4 && !(x | y)) ? dc : (int)__ldg(m + ((y >> ds) << lw) + (x >> ds));
+                }
+                const long long t = ((long long)(v * sm) * scale + add) >> shift;
+                blk[e] = (int16_t)(t < -32768 ? -32768 : (t > 32767 ? 32767 : t));
+            }
+        }
+    }
+}
+
 // ---------------------------------------------------------------- per-PU records
 __device__ __forceinline__ ohcu_pu load_pu(const ohcu_pu *p)
 {
@@ -1059,6 +1109,10 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
                 }
             }
             __syncthreads();
+            if (f.tu_quant) {
+                dequant_ctb(f, t0, nt, coef_sm, area, warp, lane);
+                __syncthreads();
+            }
             RC_MARK(7);
         } else if (staged) {
             if (tid == 0) {

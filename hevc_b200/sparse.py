@@ -16,15 +16,18 @@ def ctb_of_tus(tus, log2_ctb, hs, vs, ctb_w):
     return (x >> log2_ctb) + (y >> log2_ctb) * ctb_w
 
 
-def to_sparse(tus, coeffs, log2_ctb, hs, vs, ctb_w):
+def to_sparse(tus, coeffs, log2_ctb, hs, vs, ctb_w, return_order=False):
     """Return (recs, pairs): recs = the TU records with coeff_off = block base inside the
     CTB's coefficient area and pad = pairs of the block; pairs = COEF_DTYPE array in record
-    order.  Lists that are not grouped by CTB are grouped first (stable), cross_tu follows."""
+    order.  Lists that are not grouped by CTB are grouped first (stable), cross_tu follows;
+    return_order adds the permutation (recs[i] came from tus[order[i]])."""
     tus = np.asarray(tus)
     n_tu = len(tus)
     if n_tu == 0:
-        return tus.copy(), np.zeros(0, COEF_DTYPE)
+        empty = (tus.copy(), np.zeros(0, COEF_DTYPE))
+        return empty + (np.zeros(0, np.int64),) if return_order else empty
     ctb = ctb_of_tus(tus, log2_ctb, hs, vs, ctb_w)
+    order = np.arange(n_tu)
     if len(np.unique(ctb)) != 1 + np.count_nonzero(np.diff(ctb)):        # a CTB appears in more than one run
         order = np.argsort(ctb, kind="stable")
         new_index = np.empty(n_tu, np.int64)
@@ -48,4 +51,15 @@ def to_sparse(tus, coeffs, log2_ctb, hs, vs, ctb_w):
     recs = tus.copy()
     recs["coeff_off"] = base
     recs["pad"] = np.bincount(np.repeat(np.arange(n_tu), nn)[nz], minlength=n_tu)
-    return recs, pairs
+    return (recs, pairs, order) if return_order else (recs, pairs)
+
+
+# ---- the levels form (ohcu_append_tu_levels): un-scaled levels + one quantiser per block
+QUANT_DTYPE = np.dtype([("qp", "u1"), ("matrix_id", "u1")])
+QM_FLAT = 0xff
+
+
+def to_levels(tus, quant, levels, log2_ctb, hs, vs, ctb_w):
+    """(recs, quant_in_record_order, pairs) of a dense arena of un-scaled levels."""
+    recs, pairs, order = to_sparse(tus, levels, log2_ctb, hs, vs, ctb_w, return_order=True)
+    return recs, np.ascontiguousarray(np.asarray(quant)[order]), pairs

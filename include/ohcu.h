@@ -268,6 +268,39 @@ int ohcu_reserve_coefs(ohcu_ctx *ctx, int job, size_t n, ohcu_coef **ptr);
 int ohcu_append_tu_sparse(ohcu_ctx *ctx, int job, const ohcu_tu *recs, int n,
                           const ohcu_coef *coefs, size_t ncoefs);
 
+/* Levels variant (dequantisation on the device).  The residual
+ * parser scales every decoded level before it stores it: scale_and_clip_coeff
+ * (hevc_cabac.c:2030-2055, called at :2349, :2395, :2690, :2737 unless
+ * cu_transquant_bypass) with the per-block parameters of derive_quant_parameters /
+ * derive_quant_parameters_c (:1472-1557).  Here the pairs carry the UN-scaled
+ * trans_coeff_level and each record comes with those parameters; the kernel computes
+ *   coeff = clip_int16((level * scale * scale_m + add) >> shift)       (64-bit product)
+ *   shift = bit_depth + log2_size + 10 - 15,  add = 1 << (shift - 1)   (:1481-1482;
+ *           log2_transform_range 15: no extended_precision_processing)
+ *   scale = level_scale[qp % 6] << (qp / 6)                            (:1470, :1483)
+ *   scale_m = 16, or the scaling-list entry of the position (dc entry for the DC
+ *           of 16x16 / 32x32 blocks), :2031-2044
+ * while it rebuilds the CTB's dense blocks.  OHCU_TU_BYPASS blocks are not scaled.
+ * Same layout rules as ohcu_append_tu_sparse; a frame uses one of the three forms.      */
+#define OHCU_QM_FLAT 0xff     /* no scaling list for this block (scale_m = 16): list
+                                 disabled, or transform_skip with log2_size > 2 (:1487)  */
+typedef struct ohcu_tu_quant {
+    uint8_t qp;               /* quant_ctx->qp: qp_y, or the mapped chroma qp, plus
+                                 qp_bd_offset (:1479, :1511-1527); < 76, the size of
+                                 the reference's rem6[] / div6[] (whose last two
+                                 entries are zero: qp 74, 75 scale with 40 << 0)       */
+    uint8_t matrix_id;        /* 3 * (pred_mode != MODE_INTRA) + c_idx (:1491-1494,
+                                 :1546-1550), or OHCU_QM_FLAT                           */
+} ohcu_tu_quant;              /* 2 bytes */
+int ohcu_append_tu_levels(ohcu_ctx *ctx, int job, const ohcu_tu *recs,
+                          const ohcu_tu_quant *quant, int n,
+                          const ohcu_coef *levels, size_t nlevels);
+/* ScalingList of the active SPS / PPS (hevc_ps.h:605-610): sl[size_id][matrix_id][64],
+ * sl_dc[size_id - 2][matrix_id].  Copied before return; needed only when a record's
+ * matrix_id is not OHCU_QM_FLAT.                                                        */
+int ohcu_set_scaling_list(ohcu_ctx *ctx, int job, const uint8_t sl[4][6][64],
+                          const uint8_t sl_dc[2][6]);
+
 /* replaces the per-edge calls of deblocking_filter_CTB (hevc_filter.c:588-599,
  * 634-654, 686-697, 735-755).  Arrays are copied before return.  Not calling it
  * for a frame = no deblocking (all bs zero).                                    */

@@ -536,3 +536,55 @@ void or_loop_filter_chroma(int bd, int vertical, uint8_t *pix, ptrdiff_t stride,
         }
     }
 }
+
+/* ---------------------------------------------------------------- dequantisation
+ * derive_quant_parameters{,_c} (hevc_cabac.c:1472-1557): shift = bit_depth + log2 + 10 -
+ * log2_transform_range (15 without extended_precision_processing), add = 1 << (shift - 1),
+ * scale = level_scale[qp % 6] << (qp / 6); scale_and_clip_coeff (:2030-2055): scale_m from
+ * the scaling list by position (8x8 lists sub-sampled for 16x16 / 32x32, dc_scale for their
+ * DC), 64-bit product, clip to int16. */
+#include "../include/ohcu.h"
+
+void or_dequant_block(int16_t *blk, int log2_size, int bd, int qp, const uint8_t *matrix, int dc_scale)
+{
+    static const int level_scale[6] = {40, 45, 51, 57, 64, 72};
+    const int n = 1 << log2_size, shift = bd + log2_size + 10 - 15;
+    /* rem6[] / div6[] (hevc_cabac.c:1456-1468) are declared with 76 entries but initialised with
+     * 74: for qp 74 and 75 (12-bit video, qp_y >= 50) the reference reads zeros, i.e. scales with
+     * level_scale[0] << 0.  Reproduced: parity is against the reference, not the standard. */
+    const int rem = qp < 74 ? qp % 6 : 0, div = qp < 74 ? qp / 6 : 0;
+    const int64_t add = (int64_t)1 << (shift - 1), scale = (int64_t)level_scale[rem] << div;
+    for (int y = 0; y < n; y++)
+        for (int x = 0; x < n; x++) {
+            const int64_t level = blk[y * n + x];
+            int64_t m = 16, t;
+            if (!level) continue;
+            if (matrix) {
+                if (x || y || log2_size < 4) {
+                    int pos;
+                    switch (log2_size) {
+                    case 3: pos = (y << 3) + x; break;
+                    case 4: pos = ((y >> 1) << 3) + (x >> 1); break;
+                    case 5: pos = ((y >> 2) << 3) + (x >> 2); break;
+                    default: pos = (y << 2) + x; break;
+                    }
+                    m = matrix[pos];
+                } else {
+                    m = dc_scale;
+                }
+            }
+            t = (level * scale * m + add) >> shift;
+            blk[y * n + x] = (int16_t)(t < -32768 ? -32768 : t > 32767 ? 32767 : t);
+        }
+}
+
+void or_dequant_tus(const struct ohcu_tu *tus, const struct ohcu_tu_quant *quant, int n, int16_t *arena,
+                    int bd, const uint8_t *sl, const uint8_t *sl_dc)
+{
+    for (int i = 0; i < n; i++) {
+        const int l2 = tus[i].log2_size, id = quant[i].matrix_id;
+        const uint8_t *m = (id != OHCU_QM_FLAT && sl) ? sl + ((l2 - 2) * 6 + id) * 64 : 0;
+        if (tus[i].mode == OHCU_TU_BYPASS) continue;          /* cu_transquant_bypass: not scaled */
+        or_dequant_block(arena + tus[i].coeff_off, l2, bd, quant[i].qp, m, (m && l2 >= 4) ? sl_dc[(l2 - 4) * 6 + id] : 16);
+    }
+}

@@ -79,6 +79,19 @@ void or_loop_filter_luma(int bd, int vertical, uint8_t *pix, ptrdiff_t stride, i
 void or_loop_filter_chroma(int bd, int vertical, uint8_t *pix, ptrdiff_t stride,
                            const int tc[2], const uint8_t no_p[2], const uint8_t no_q[2]);
 
+/* ---- dequantisation (hevc_cabac.c:1470-1557, :2030-2055): the device-side step of
+ *      ohcu_append_tu_levels.  blk: N x N un-scaled levels, scaled in place (zeros stay
+ *      zero, as the reference only scales the levels it decodes).  matrix: the 64-entry
+ *      scaling list of the block's size and matrix id, or NULL for the flat 16; dc_scale
+ *      is used for the DC of 16x16 / 32x32 blocks when matrix != NULL. ---- */
+void or_dequant_block(int16_t *blk, int log2_size, int bd, int qp, const uint8_t *matrix, int dc_scale);
+/* every block of a TU list whose records carry arena offsets (dense layout): what the
+ * device does for a levels frame.  sl = ScalingList.sl[4][6][64], sl_dc = .sl_dc[2][6]
+ * (hevc_ps.h:605-610), both may be NULL when every matrix_id is OHCU_QM_FLAT. */
+struct ohcu_tu; struct ohcu_tu_quant;
+void or_dequant_tus(const struct ohcu_tu *tus, const struct ohcu_tu_quant *quant, int n, int16_t *arena,
+                    int bd, const uint8_t *sl, const uint8_t *sl_dc);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,6 +20,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 
 import frame_cases  # noqa: E402
 import leaf_cases  # noqa: E402
+import levels_cases  # noqa: E402
 import oracle_lib  # noqa: E402
 
 STAGE_SETS = {"mc": 1, "mc_res": 3, "mc_res_db": 7, "all": 15}
@@ -47,7 +48,18 @@ def main():
     with open(os.path.join(HERE, "frames.json"), "w") as f:
         json.dump({"source": "ohref_replay_frame (reference drivers + table)", "cases": frames}, f,
                   indent=1, sort_keys=True)
-    print(f"{len(leaves)} leaf digests, {len(frames)} frame cases written")
+    # dequantisation (the levels form): the reference's own scale_and_clip_coeff on seeded blocks
+    sl, sl_dc, cases = levels_cases.leaf_cases()
+    outs = []
+    for p, blk in cases:
+        b = blk.copy()
+        ref._dequant_block(p["bd"], p["cfi"], p["c_idx"], p["log2"], p["qp_y"], p["qp_offset"], p["intra"],
+                           p["transform_skip"], p["sl_enabled"], sl.ctypes.data, sl_dc.ctypes.data, b.ctypes.data)
+        outs.append(b)
+    with open(os.path.join(HERE, "levels_digest.json"), "w") as f:
+        json.dump({"source": "ohref_dequant_block (hevc_cabac.c derive_quant_parameters{,_c} + scale_and_clip_coeff)",
+                   "cases": len(outs), "sha256": levels_cases.digest(outs)}, f, indent=1)
+    print(f"{len(leaves)} leaf digests, {len(frames)} frame cases, {len(outs)} dequantisation cases written")
 
 
 if __name__ == "__main__":

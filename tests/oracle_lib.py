@@ -98,6 +98,17 @@ class Lib:
             if args is not None:
                 fn.argtypes = args
             setattr(self, "_" + name, fn)
+        # dequantisation (the levels form): the two libraries take different arguments, see dequant_block()
+        fn = getattr(self.lib, prefix + "dequant_block")
+        if which == "oracle":
+            fn.restype = None
+            fn.argtypes = [_P, _I, _I, _I, _P, _I]
+            self.lib.or_dequant_tus.restype = None
+            self.lib.or_dequant_tus.argtypes = [_P, _P, _I, _P, _I, _P, _P]
+        else:
+            fn.restype = _I
+            fn.argtypes = [_I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P]
+        self._dequant_block = fn
         self._replay = getattr(self.lib, prefix + "replay_frame")
         self._replay.restype = C.c_int
         self._replay.argtypes = [C.POINTER(FrameJobC)]
@@ -112,6 +123,16 @@ class Lib:
             self._transform_rdpcm(C.c_void_p(coeffs_ptr), C.c_int(log2_size), C.c_int(mode))
         else:
             self._transform_rdpcm(C.c_int(bd), C.c_void_p(coeffs_ptr), C.c_int(log2_size), C.c_int(mode))
+
+    def dequant_tus(self, tus, quant, levels, bd, scaling=None):
+        """oracle only: the dense arena of un-scaled levels -> coefficients (a copy)."""
+        out = np.ascontiguousarray(levels).copy()
+        sl = sl_dc = None
+        if scaling is not None:
+            sl, sl_dc = (np.ascontiguousarray(a, dtype=np.uint8) for a in scaling)
+        self.lib.or_dequant_tus(tus.ctypes.data, np.ascontiguousarray(quant).ctypes.data, len(tus), out.ctypes.data, bd,
+                                sl.ctypes.data if sl is not None else None, sl_dc.ctypes.data if sl_dc is not None else None)
+        return out
 
     def replay(self, job, refs, out_init=None, stages=0, use_deblock=True, use_sao=True):
         """Run one frame job.  refs = list (DPB slots) of pictures (lists of 2-D arrays).
