@@ -628,52 +628,39 @@ __device__ void tu_batch(const FrameDev &f, const CtbTile &tile, int tu0, const 
 
 // ---------------------------------------------------------------- levels -> coefficients
 // The "levels" form of the sparse upload (ohcu_append_tu_levels): the pairs carry the un-scaled
-// trans_coeff_level and the kernel scales them once the CTB's dense blocks are rebuilt, in
-// place: scale_and_clip_coeff (hevc_cabac.c:2030-2055) with the parameters of
-// derive_quant_parameters{,_c} (:1472-1557).  A zero stays zero ((0 + add) >> shift == 0), so
-// scaling the dense block equals scaling the pairs.  Eight lanes of a warp fetch the records of
-// eight TBs, then the warp goes through those blocks one by one.
-__constant__ int c_level_scale[6] = {40, 45, 51, 57, 64, 72};                 // hevc_cabac.c:1470
+// trans_coeff_level and are scaled while they are scattered into the CTB's dense blocks:
+// scale_and_clip_coeff (hevc_cabac.c:2030-2055) with the parameters of
+// derive_quant_parameters{,_c} (:1472-1557).  The reference scales exactly the levels it decodes,
+// i.e. the pairs.  A pair only knows its position in the CTB's coefficient area, so a table with
+// one word per 16 coefficients (blocks are 16-aligned multiples of 16) says which block it is in:
+//   block base / 16 | (log2 - 2) << 10 | qp << 12 | matrix id << 19 (7 = flat) | bypass << 22
+constexpr int QTAB_FLAT = 7;
 
-__device__ __noinline__ void dequant_ctb(const FrameDev &f, int t0, int nt, int16_t *coef_sm, uint32_t area, int warp, int lane)
+__device__ __forceinline__ uint32_t qtab_word(const ohcu_tu &tu, const ohcu_tu_quant q)
 {
-    for (int base = warp * 8; base < nt; base += RC_WARPS * 8) {
-        uint32_t off = 0, par = 0;         // par: log2 | qp << 8 | matrix_id << 16 | bypass << 24 | valid << 25
-        if (lane < 8 && base + lane < nt) {
-            const ohcu_tu *tu = f.tus + t0 + base + lane;
-            const ohcu_tu_quant q = f.tu_quant[t0 + base + lane];
-            off = tu->coeff_off;
-            par = (uint32_t)tu->log2_size | (uint32_t)q.qp << 8 | (uint32_t)q.matrix_id << 16 |
-                  (tu->mode == OHCU_TU_BYPASS ? 1u << 24 : 0u) | 1u << 25;
-        }
-#pragma unroll 1
-        for (int k = 0; k < 8; k++) {
-            const uint32_t p = __shfl_sync(0xffffffffu, par, k), o = __shfl_sync(0xffffffffu, off, k);
-            if (!((p >> 25) & 1)) break;
-            const int log2 = p & 0xff, qp = (p >> 8) & 0xff, mid = (p >> 16) & 0xff, n2 = 1 << (2 * log2);
-            if (((p >> 24) & 1) || o + n2 > area) continue;                  // cu_transquant_bypass: levels are the residual
-            const int shift = f.bd + log2 - 5;                              // bit_depth + log2 + 10 - log2_transform_range (15)
-            const long long add = 1ll << (shift - 1);
-            // rem6[] / div6[] of the reference hold zeros at qp 74 and 75 (76 entries declared, 74 initialised,
-            // hevc_cabac.c:1456-1468): reproduced, parity is against the reference
-            const int scale = qp < 74 ? c_level_scale[qp % 6] << (qp / 6) : c_level_scale[0];
-            const uint8_t *m = (mid != OHCU_QM_FLAT && f.scaling) ? f.scaling + ((log2 - 2) * 6 + mid) * 64 : nullptr;
-            const int dc = (m && log2 >= 4) ? f.scaling[4 * 6 * 64 + (log2 - 4) * 6 + mid] : 16;
-            const int ds = log2 > 3 ? log2 - 3 : 0, lw = log2 == 2 ? 2 : 3;  // 16x16 / 32x32 share an 8x8 list
-            int16_t *blk = coef_sm + o;
-            for (int e = lane; e < n2; e += 32) {
-                const int v = blk[e];
-                if (!v) continue;
-                int sm = 16;
-                if (m) {
-                    const int x = e & ((1 << log2) - 1), y = e >> log2;
-                    sm = (log2 >= 4 && !(x | y)) ? dc : (int)__ldg(m + ((y >> ds) << lw) + (x >> ds));
-                }
-                const long long t = ((long long)(v * sm) * scale + add) >> shift;
-                blk[e] = (int16_t)(t < -32768 ? -32768 : (t > 32767 ? 32767 : t));
-            }
-        }
+    return (tu.coeff_off >> 4) | (uint32_t)(tu.log2_size - 2) << 10 | (uint32_t)q.qp << 12 |
+           (uint32_t)(q.matrix_id == OHCU_QM_FLAT ? QTAB_FLAT : q.matrix_id) << 19 | (tu.mode == OHCU_TU_BYPASS ? 1u << 22 : 0u);
+}
+
+__device__ __forceinline__ int dequant_level(int v, uint32_t pos, uint32_t w, const uint8_t *scaling, int bd)
+{
+    if ((w >> 22) & 1) return v;                                      // cu_transquant_bypass: levels are the residual
+    const int log2 = 2 + ((w >> 10) & 3), qp = (w >> 12) & 127, mid = (w >> 19) & 7;
+    const int e = (int)pos - (int)((w & 1023u) << 4);
+    const int shift = bd + log2 - 5;                                  // bit_depth + log2 + 10 - log2_transform_range (15)
+    int sm = 16;
+    if (mid != QTAB_FLAT && scaling) {
+        const int x = e & ((1 << log2) - 1), y = e >> log2;
+        const int ds = log2 > 3 ? log2 - 3 : 0, lw = log2 == 2 ? 2 : 3;  // 16x16 / 32x32 share an 8x8 list
+        sm = (log2 >= 4 && !(x | y)) ? scaling[4 * 6 * 64 + (log2 - 4) * 6 + mid]
+                                     : scaling[((log2 - 2) * 6 + mid) * 64 + ((y >> ds) << lw) + (x >> ds)];
     }
+    // level_scale[] = {40, 45, 51, 57, 64, 72} (hevc_cabac.c:1470) as bytes of two words; rem6[] / div6[] of the
+    // reference hold zeros at qp 74 and 75 (76 entries declared, 74 initialised, :1456-1468): reproduced
+    const int rem = qp < 74 ? qp % 6 : 0, div = qp < 74 ? qp / 6 : 0;
+    const int scale = (int)(((rem < 4 ? 0x39332d28u >> (8 * rem) : 0x00004840u >> (8 * (rem - 4))) & 0xffu) << div);
+    const long long t = ((long long)(v * sm) * scale + (1ll << (shift - 1))) >> shift;
+    return (int)(t < -32768 ? -32768 : (t > 32767 ? 32767 : t));
 }
 
 // ---------------------------------------------------------------- per-PU records
@@ -1093,12 +1080,27 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
             const int npair = tu_cnt[16];
             const uint32_t area = min(chi, (uint32_t)coef_area(area_units));
             for (uint32_t o = tid * 8; o < area; o += RC_THREADS * 8) *(uint4 *)(coef_sm + o) = make_uint4(0, 0, 0, 0);
+            // levels form: which block a position belongs to (the per-warp scratch is free until the batches)
+            uint32_t *qtab = (uint32_t *)pool;
+            const bool levels = f.tu_quant != nullptr;
+            if (levels) {
+                for (int i = tid; i < nt; i += RC_THREADS) {
+                    const ohcu_tu tu = f.tus[t0 + i];
+                    const uint32_t w = qtab_word(tu, f.tu_quant[t0 + i]), n16 = 1u << (2 * tu.log2_size - 4);
+                    if (tu.coeff_off + 16 * n16 <= area)
+                        for (uint32_t k = 0; k < n16; k++) qtab[(tu.coeff_off >> 4) + k] = w;
+                }
+            }
             __syncthreads();
             for (int base = 0;;) {
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
                     const uint32_t pos = pr[k] & 0xffffu;
-                    if (pos < area) coef_sm[pos] = (int16_t)(pr[k] >> 16);
+                    if (pos < area) {
+                        int v = (int)(int16_t)(pr[k] >> 16);
+                        if (levels) v = dequant_level(v, pos, qtab[pos >> 4], f.scaling, bd);
+                        coef_sm[pos] = (int16_t)v;
+                    }
                 }
                 base += 4 * RC_THREADS;
                 if (base >= npair) break;
@@ -1109,10 +1111,6 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
                 }
             }
             __syncthreads();
-            if (f.tu_quant) {
-                dequant_ctb(f, t0, nt, coef_sm, area, warp, lane);
-                __syncthreads();
-            }
             RC_MARK(7);
         } else if (staged) {
             if (tid == 0) {
