@@ -67,6 +67,28 @@ def make_inputs(workload, rank, world=1):
     return jobs, refs
 
 
+def levels_inputs(jobs):
+    """--coeffs levels: the frames' coefficient arenas become UN-scaled levels with a random quantiser
+    per block and random scaling lists (tests/levels_cases.py); job.coeffs is replaced by the scaled
+    coefficients (CPU restatement of scale_and_clip_coeff), which is what the parity check and the CPU
+    arms consume - the GPU arm is handed the levels (ohcu_append_tu_levels) and scales them itself.
+    Returns per job (recs, quant, pairs, (sl, sl_dc))."""
+    import levels_cases
+    import oracle_lib
+    from hevc_b200.sparse import to_levels
+    orc = oracle_lib.Lib("oracle")
+    out = []
+    for i, fj in enumerate(jobs):
+        sp = fj.sp
+        hs = 1 if sp.chroma_format_idc in (1, 2) else 0
+        vs = 1 if sp.chroma_format_idc == 1 else 0
+        ctb_w = (sp.width + (1 << sp.log2_ctb_size) - 1) >> sp.log2_ctb_size
+        lv, quant, scaling = levels_cases.frame_levels(fj, seed=900 + i)
+        fj.coeffs = orc.dequant_tus(fj.tus, quant, lv, sp.bit_depth, scaling)
+        out.append(to_levels(fj.tus, quant, lv, sp.log2_ctb_size, hs, vs, ctb_w) + (scaling,))
+    return out
+
+
 def algorithmic_bytes(job):
     """per kernel, bytes that must move once.
     recon       every reference sample a PU needs read once + every sample written once
@@ -179,12 +201,18 @@ def run_ours(args, rank, world):
     barrier = shard.barrier
     # --coeffs sparse: significant coefficients as (position, level) pairs (ohcu_append_tu_sparse)
     sparse_lists = [ctx.sparse_lists(fj) for fj in jobs] if args.coeffs == "sparse" else None
+    # --coeffs levels: the pairs carry un-scaled levels, the kernel dequantises (ohcu_append_tu_levels)
+    level_lists = levels_inputs(jobs) if args.coeffs == "levels" else None
 
     # ---------------- resident leg: lists staged once, kernels only in the timed region
     for k in range(B):
         j = ctx.begin(2 + k)
         assert j == k
-        ctx.append(j, jobs[k % len(jobs)], sparse=sparse_lists[k % len(jobs)] if sparse_lists else False)
+        if level_lists:
+            recs, q, pairs, scaling = level_lists[k % len(jobs)]
+            ctx.append(j, jobs[k % len(jobs)], levels=(q, scaling, (recs, q, pairs)))
+        else:
+            ctx.append(j, jobs[k % len(jobs)], sparse=sparse_lists[k % len(jobs)] if sparse_lists else False)
         ctx.stage(j)
     ctx.sync()
     l0 = ctx.kernel_launches()
@@ -233,7 +261,15 @@ def run_ours(args, rank, world):
         # (ohcu_reserve_coeffs, lc->tu.coeffs of hevcdec.h:333); the untimed first pass puts
         # them there, later passes find them in place like a decoder that just parsed them
         ptr = C.c_void_p(); off = C.c_uint32()
-        if sparse_lists:
+        if level_lists:
+            recs, q, pairs, (sl, sl_dc) = level_lists[k % len(jobs)]
+            abi.check(lib.ohcu_reserve_coefs(h, j, len(pairs), C.byref(ptr)))
+            if copy_coeffs:
+                C.memmove(ptr.value, pairs.ctypes.data, pairs.nbytes)
+            abi.check(lib.ohcu_set_scaling_list(h, j, sl.ctypes.data, sl_dc.ctypes.data))
+            abi.check(lib.ohcu_append_tu_levels(h, j, recs.ctypes.data, q.ctypes.data, len(recs), ptr, len(pairs)))
+            coef_bytes = pairs.nbytes + 8 * len(fj.sao) + q.nbytes + sl.nbytes + sl_dc.nbytes
+        elif sparse_lists:
             recs, pairs = sparse_lists[k % len(jobs)]
             abi.check(lib.ohcu_reserve_coefs(h, j, len(pairs), C.byref(ptr)))
             if copy_coeffs:
@@ -354,6 +390,8 @@ def run_reference(args, rank, world):
     if rank != 0:
         return
     jobs, refs = make_inputs(args.workload, 0)
+    if args.coeffs == "levels":
+        levels_inputs(jobs)               # same coefficient values as the GPU arm reconstructs from
     cb = cpu_reference(jobs, refs, steps=args.steps, warmup=args.warmup)
     sp = jobs[0].sp
     line = {
@@ -382,9 +420,10 @@ def main():
     ap.add_argument("--frames", type=int, default=0, help="frames per step per GPU (default per workload)")
     ap.add_argument("--cpu-steps", type=int, default=2, help="steps of the cpu_baseline leg")
     ap.add_argument("--host-threads", type=int, default=4, help="threads submitting frames in the e2e leg")
-    ap.add_argument("--coeffs", default="sparse", choices=["dense", "sparse"],
+    ap.add_argument("--coeffs", default="sparse", choices=["dense", "sparse", "levels"],
                     help="coefficient form handed to the library: (position, level) pairs of the significant "
-                         "coefficients (ohcu_append_tu_sparse, what the residual parser produces) or zero-filled N x N blocks")
+                         "coefficients (ohcu_append_tu_sparse, what the residual parser produces), zero-filled N x N blocks, or "
+                         "un-scaled levels + a quantiser per block (ohcu_append_tu_levels: dequantisation on the device)")
     ap.add_argument("--slot-pitch", action="store_true",
                     help="e2e leg: host pictures with the device planes' row pitch (one linear copy per plane)")
     ap.add_argument("--no-cpu", action="store_true")

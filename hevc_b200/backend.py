@@ -95,12 +95,13 @@ class Context:
             check(lib.ohcu_set_slice(h, job_id, i, C.byref(tab)), "ohcu_set_slice")
         check(lib.ohcu_append_pu(h, job_id, fj.pus.ctypes.data, len(fj.pus)), "ohcu_append_pu")
         if len(fj.tus) and levels is not None:
-            quant, scaling = levels
+            quant, scaling = levels[:2]
             sp = self.sp
             hs = 1 if sp.chroma_format_idc in (1, 2) else 0
             vs = 1 if sp.chroma_format_idc == 1 else 0
             ctb_w = (sp.width + (1 << sp.log2_ctb_size) - 1) >> sp.log2_ctb_size
-            recs, q, pairs = to_levels(fj.tus, quant, fj.coeffs, sp.log2_ctb_size, hs, vs, ctb_w)
+            # a third element = the lists to_levels() already made (fj.coeffs is then not read)
+            recs, q, pairs = levels[2] if len(levels) > 2 else to_levels(fj.tus, quant, fj.coeffs, sp.log2_ctb_size, hs, vs, ctb_w)
             if scaling is not None:
                 sl, sl_dc = (np.ascontiguousarray(a, dtype=np.uint8) for a in scaling)
                 assert sl.shape == (4, 6, 64) and sl_dc.shape == (2, 6)
