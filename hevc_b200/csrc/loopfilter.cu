@@ -24,7 +24,10 @@
 
 namespace ohcu {
 
-constexpr int LF_THREADS = 256;
+#ifndef LF_NTHREADS
+#define LF_NTHREADS 256
+#endif
+constexpr int LF_THREADS = LF_NTHREADS;
 constexpr int LF_REGION = 64;                 // luma samples per side of a CTA's region
 
 __constant__ uint8_t c_tctable[54] = {

@@ -27,6 +27,7 @@ SLICE_DTYPE = np.dtype([("ref_slot", "u1", (2, 16)), ("weight_flag", "u1"), ("lu
                         ("chroma_log2_weight_denom", "u1"), ("pad", "u1"),
                         ("luma_weight", "<i2", (2, 16)), ("luma_offset", "<i2", (2, 16)),
                         ("chroma_weight", "<i2", (2, 16, 2)), ("chroma_offset", "<i2", (2, 16, 2))])
+LEAF_DTYPE = np.dtype([("x0", "<u2"), ("y0", "<u2"), ("log2_size", "u1"), ("cbf_luma", "u1"), ("pad", "u1", (2,))])
 assert PU_DTYPE.itemsize == 20 and TU_DTYPE.itemsize == 20 and SAO_DTYPE.itemsize == 40
 assert SLICE_DTYPE.itemsize == C.sizeof(abi.SliceTab)
 
@@ -54,6 +55,7 @@ class _SynthFrame(C.Structure):
         ("min_pu_width", C.c_int32), ("min_pu_height", C.c_int32), ("is_pcm", C.c_void_p),
         ("sao", C.c_void_p), ("filter_slice_edges", C.c_void_p),
         ("tab_slice_address", C.c_void_p), ("tile_id", C.c_void_p),
+        ("n_leaf", C.c_int32), ("leaves", C.c_void_p),
     ]
 
 
@@ -166,6 +168,7 @@ class FrameJob:
             self.filter_slice_edges = _copy(f.filter_slice_edges, np.uint8, nctb)
             self.tab_slice_address = _copy(f.tab_slice_address, np.int32, nctb)
             self.tile_id = _copy(f.tile_id, np.int32, nctb)
+            self.leaves = _copy(f.leaves, LEAF_DTYPE, f.n_leaf)     # transform-tree leaves, coded or not
             self.ctb_width, self.ctb_height = f.ctb_width, f.ctb_height
         finally:
             lib.ohsynth_free(fp)

@@ -49,6 +49,15 @@ typedef struct ohsynth_params {
     int32_t n_refs;          /* reference pictures used (DPB slots 0..n_refs-1), <= 4 */
 } ohsynth_params;
 
+/* one leaf of a transform tree (hls_transform_tree, hevcdec.c:1549): what
+ * ff_hevc_deblocking_boundary_strengths is called with, coded or not */
+typedef struct ohsynth_leaf {
+    uint16_t x0, y0;
+    uint8_t  log2_size;
+    uint8_t  cbf_luma;
+    uint8_t  pad[2];
+} ohsynth_leaf;
+
 typedef struct ohsynth_frame {
     int32_t n_slices;  ohcu_slice_tab *slices;
     int32_t n_pu;      ohcu_pu *pus;
@@ -62,6 +71,7 @@ typedef struct ohsynth_frame {
     uint8_t *filter_slice_edges;
     int32_t *tab_slice_address;
     int32_t *tile_id;
+    int32_t n_leaf;    ohsynth_leaf *leaves;    /* transform-tree leaves in decoding order */
 } ohsynth_frame;
 
 void ohsynth_default_params(ohsynth_params *p, int width, int height, int bit_depth,

@@ -265,8 +265,10 @@ static void gen_tt(gen *g, int x, int y, int log2, int bypass)
     paint_bs(g, x, y, 1 << log2, 1 << log2);
     {
         int luma_idx = -1;
+        ohsynth_leaf *lf = &g->f->leaves[g->f->n_leaf++];
         if (rnd_pct(&g->r, g->p->cbf_pct))
             luma_idx = emit_tb(g, 0, x, y, log2, bypass, -1);
+        lf->x0 = (uint16_t)x; lf->y0 = (uint16_t)y; lf->log2_size = (uint8_t)log2; lf->cbf_luma = luma_idx >= 0;
         if (log2 > 2 || g->cfi == 3)
             emit_chroma(g, x, y, log2, bypass, luma_idx);
     }
@@ -426,6 +428,8 @@ ohsynth_frame *ohsynth_generate(const ohsynth_params *p)
     f->filter_slice_edges = calloc(nctb, 1);
     f->tab_slice_address = calloc(nctb, sizeof(int32_t));
     f->tile_id = calloc(nctb, sizeof(int32_t));
+    /* at most one leaf per 4x4 luma block */
+    f->leaves = calloc((size_t)((sp->width + 3) >> 2) * ((sp->height + 3) >> 2) + 1, sizeof(ohsynth_leaf));
 
     /* slices: n_slices-1 random cut points in CTB raster order */
     f->n_slices = imin(imin(p->n_slices, OHCU_MAX_SLICES), nctb);
@@ -461,7 +465,7 @@ void ohsynth_free(ohsynth_frame *f)
     if (!f) return;
     free(f->slices); free(f->pus); free(f->tus); free(f->coeffs); free(f->vbs); free(f->hbs);
     free(f->qp_y_tab); free(f->deblock); free(f->is_pcm); free(f->sao);
-    free(f->filter_slice_edges); free(f->tab_slice_address); free(f->tile_id);
+    free(f->filter_slice_edges); free(f->tab_slice_address); free(f->tile_id); free(f->leaves);
     free(f);
 }
 
