@@ -444,3 +444,101 @@ int ohref_replay_frame(const oh_frame_job *job)
     free(st);
     return 0;
 }
+
+/* ------------------------------------------------------------------ boundary strengths
+ * The reference's own ff_hevc_deblocking_boundary_strengths (hevc_filter.c:1006-1125), called
+ * once per transform-tree leaf as hls_transform_tree / hls_coding_unit do (hevcdec.c), with
+ * lc->boundary_flags from its own hls_decode_neighbour (hevcdec.c:2796-2843).  tab_mvf is
+ * filled from the PU list the way hls_prediction_unit leaves it (MvField, hevcdec.h:302-311;
+ * poc[] = the DPB slot of the referenced picture: one picture per slot). */
+int ohref_boundary_strengths(const oh_bs_job *job)
+{
+    const ohcu_seq_params *sp = &job->sp;
+    ref_state *st = zalloc(sizeof(*st));
+    HEVCContext *s = &st->s;
+    HEVCSPS *sps = &st->sps;
+    HEVCPPS *pps = &st->pps;
+    HEVCFrame *fr = zalloc(sizeof(*fr));
+    int ctb_size = 1 << sp->log2_ctb_size, nctb, last_ctb = -1;
+    size_t bsn;
+
+    sps->width = sp->width;   sps->height = sp->height;
+    sps->log2_ctb_size = sp->log2_ctb_size;
+    sps->log2_min_cb_size = sp->log2_min_cb_size;
+    sps->log2_min_pu_size = sp->log2_min_pu_size;
+    sps->log2_min_tb_size = 2;
+    sps->ctb_width  = (sp->width  + ctb_size - 1) >> sp->log2_ctb_size;
+    sps->ctb_height = (sp->height + ctb_size - 1) >> sp->log2_ctb_size;
+    sps->ctb_size = sps->ctb_width * sps->ctb_height;
+    sps->min_pu_width  = sp->width  >> sp->log2_min_pu_size;
+    sps->min_pu_height = sp->height >> sp->log2_min_pu_size;
+    sps->min_tb_width  = sp->width  >> 2;
+    sps->min_tb_height = sp->height >> 2;
+    nctb = sps->ctb_size;
+    pps->tiles_enabled_flag = !!sp->no_tile_filter;
+    pps->loop_filter_across_tiles_enabled_flag = 0;
+    pps->ctb_addr_rs_to_ts = zalloc(sizeof(int) * nctb);
+    pps->ctb_addr_ts_to_rs = zalloc(sizeof(int) * nctb);
+    pps->tile_id = zalloc(sizeof(int) * nctb);
+    pps->col_idxX = zalloc(sizeof(int) * (sps->ctb_width + 1));
+    pps->column_width = zalloc(sizeof(int) * 2);
+    pps->column_width[0] = sps->ctb_width;
+    for (int i = 0; i < nctb; i++) {
+        pps->ctb_addr_rs_to_ts[i] = pps->ctb_addr_ts_to_rs[i] = i;
+        pps->tile_id[i] = job->tile_id ? job->tile_id[i] : 0;
+    }
+    s->ps.sps = sps;
+    s->ps.pps = pps;
+    s->HEVClc = &st->lc;
+    s->bs_width  = (sp->width  >> 2) + 1;
+    s->bs_height = (sp->height >> 2) + 1;
+    bsn = (size_t)s->bs_width * s->bs_height;
+    s->vertical_bs = zalloc(bsn);
+    s->horizontal_bs = zalloc(bsn);
+    s->cbf_luma = zalloc((size_t)sps->min_tb_width * sps->min_tb_height);
+    s->tab_slice_address = zalloc(sizeof(int32_t) * nctb);
+    fr->tab_mvf = zalloc(sizeof(MvField) * (size_t)sps->min_pu_width * sps->min_pu_height);   /* pred_flag 0 = PF_INTRA */
+    s->ref = fr;
+
+    for (int i = 0; i < job->n_pu; i++) {
+        const ohcu_pu *pu = &job->pus[i];
+        const ohcu_slice_tab *sl = &job->slices[pu->slice];
+        MvField mvf;
+        memset(&mvf, 0, sizeof(mvf));
+        for (int l = 0; l < 2; l++) {
+            mvf.mv[l].x = pu->mv[l][0]; mvf.mv[l].y = pu->mv[l][1];
+            mvf.ref_idx[l] = pu->ref_idx[l];
+            mvf.poc[l] = sl->ref_slot[l][pu->ref_idx[l] & (OHCU_MAX_REFS - 1)];
+        }
+        mvf.pred_flag = pu->pred_flag;
+        for (int y = pu->y0 >> sp->log2_min_pu_size; y < (pu->y0 + pu->h) >> sp->log2_min_pu_size; y++)
+            for (int x = pu->x0 >> sp->log2_min_pu_size; x < (pu->x0 + pu->w) >> sp->log2_min_pu_size; x++)
+                fr->tab_mvf[y * sps->min_pu_width + x] = mvf;
+    }
+    for (int i = 0; i < job->n_leaf; i++) {
+        const oh_leaf *lf = &job->leaves[i];
+        if (lf->cbf_luma)
+            for (int y = lf->y0 >> 2; y < (lf->y0 >> 2) + (1 << (lf->log2_size - 2)); y++)
+                memset(s->cbf_luma + y * sps->min_tb_width + (lf->x0 >> 2), 1, 1 << (lf->log2_size - 2));
+    }
+    for (int i = 0; i < job->n_leaf; i++) {
+        const oh_leaf *lf = &job->leaves[i];
+        int rs = (lf->y0 >> sp->log2_ctb_size) * sps->ctb_width + (lf->x0 >> sp->log2_ctb_size);
+        if (rs != last_ctb) {                              /* CTB loop of hls_decode_entry, hevcdec.c:2868-2890 */
+            s->sh.slice_addr = job->tab_slice_address ? job->tab_slice_address[rs] : 0;
+            s->sh.slice_loop_filter_across_slices_enabled_flag = job->filter_slice_edges ? job->filter_slice_edges[rs] : 1;
+            s->sh.disable_deblocking_filter_flag = job->deblock_disabled ? job->deblock_disabled[rs] : 0;
+            hls_decode_neighbour(s, (rs % sps->ctb_width) << sp->log2_ctb_size, (rs / sps->ctb_width) << sp->log2_ctb_size, rs);
+            last_ctb = rs;
+        }
+        if (!s->sh.disable_deblocking_filter_flag)         /* hevcdec.c: the call sites' condition */
+            ff_hevc_deblocking_boundary_strengths(s, lf->x0, lf->y0, lf->log2_size);
+    }
+    memcpy(job->vbs, s->vertical_bs, bsn);
+    memcpy(job->hbs, s->horizontal_bs, bsn);
+    free(s->vertical_bs); free(s->horizontal_bs); free(s->cbf_luma); free(s->tab_slice_address);
+    free(fr->tab_mvf); free(fr);
+    free(pps->ctb_addr_rs_to_ts); free(pps->ctb_addr_ts_to_rs); free(pps->tile_id); free(pps->col_idxX); free(pps->column_width);
+    free(st);
+    return 0;
+}

@@ -439,3 +439,97 @@ int or_replay_frame(const oh_frame_job *job)
     }
     return 0;
 }
+
+/* ================================================================== boundary strengths
+ * Restatement of ff_hevc_deblocking_boundary_strengths (hevc_filter.c:1006-1125) +
+ * boundary_strength (:764-880, TEST_MV_POC variant) in terms of the lists the C ABI carries.
+ * The reference visits every edge unit (4 samples on the 8x8 grid) exactly once, from the
+ * leaf on its Q side (the current block):
+ *   - on the leaf's own left / top boundary (:1020-1086): 2 if either side is intra, else 1 if
+ *     the transform block on either side has cbf_luma, else the motion rule;
+ *   - inside the leaf (:1088-1124): the motion rule only.
+ * An edge unit is "a transform-block boundary with cbf_luma on a side" exactly when it lies on
+ * the perimeter of a CODED luma TB, so the coded TBs the ABI already has are enough: the edge
+ * separates two 4x4 cells that do not belong to the same coded TB and one of them belongs to
+ * one.  Cells no PU covers count as intra.  The motion rule compares reference PICTURES (the
+ * reference compares POCs; here DPB slots, one picture per slot). */
+typedef struct bs_cell { int32_t pu, tb; } bs_cell;
+
+static int bs_far(const int16_t a[2], const int16_t b[2])
+{
+    return abs(a[0] - b[0]) >= 4 || abs(a[1] - b[1]) >= 4;
+}
+
+static int bs_motion(const oh_bs_job *job, const ohcu_pu *c, const ohcu_pu *n)
+{
+    const ohcu_slice_tab *sc = &job->slices[c->slice], *sn = &job->slices[n->slice];
+    int pc[2], pn[2];
+    for (int l = 0; l < 2; l++) {
+        pc[l] = sc->ref_slot[l][c->ref_idx[l] & (OHCU_MAX_REFS - 1)];
+        pn[l] = sn->ref_slot[l][n->ref_idx[l] & (OHCU_MAX_REFS - 1)];
+    }
+    if (c->pred_flag == OHCU_PF_BI && n->pred_flag == OHCU_PF_BI) {
+        if (pc[0] == pn[0] && pc[0] == pc[1] && pn[0] == pn[1])
+            return (bs_far(n->mv[0], c->mv[0]) || bs_far(n->mv[1], c->mv[1])) &&
+                   (bs_far(n->mv[1], c->mv[0]) || bs_far(n->mv[0], c->mv[1]));
+        if (pn[0] == pc[0] && pn[1] == pc[1])
+            return bs_far(n->mv[0], c->mv[0]) || bs_far(n->mv[1], c->mv[1]);
+        if (pn[1] == pc[0] && pn[0] == pc[1])
+            return bs_far(n->mv[1], c->mv[0]) || bs_far(n->mv[0], c->mv[1]);
+        return 1;
+    }
+    if (c->pred_flag != OHCU_PF_BI && n->pred_flag != OHCU_PF_BI) {
+        const int lc = (c->pred_flag & 1) ? 0 : 1, ln = (n->pred_flag & 1) ? 0 : 1;
+        return pc[lc] == pn[ln] ? bs_far(c->mv[lc], n->mv[ln]) : 1;
+    }
+    return 1;
+}
+
+static int bs_unit(const oh_bs_job *job, const bs_cell *q, const bs_cell *p)
+{
+    if (q->pu < 0 || p->pu < 0) return 2;
+    if (q->tb != p->tb && (q->tb >= 0 || p->tb >= 0)) return 1;
+    if (q->pu == p->pu) return 0;
+    return bs_motion(job, &job->pus[q->pu], &job->pus[p->pu]);
+}
+
+int or_boundary_strengths(const oh_bs_job *job)
+{
+    const ohcu_seq_params *sp = &job->sp;
+    const int W = sp->width, H = sp->height, gw = W >> 2, gh = H >> 2, bsw = gw + 1, bsh = gh + 1;
+    const int l2 = sp->log2_ctb_size, ctb_w = (W + (1 << l2) - 1) >> l2, cmask = (1 << l2) - 1;
+    bs_cell *g = malloc(sizeof(bs_cell) * (size_t)gw * gh);
+    if (!g) return OHCU_ENOMEM;
+    for (int i = 0; i < gw * gh; i++) g[i].pu = g[i].tb = -1;
+    for (int i = 0; i < job->n_pu; i++) {
+        const ohcu_pu *pu = &job->pus[i];
+        for (int y = pu->y0 >> 2; y < (pu->y0 + pu->h) >> 2 && y < gh; y++)
+            for (int x = pu->x0 >> 2; x < (pu->x0 + pu->w) >> 2 && x < gw; x++) g[y * gw + x].pu = i;
+    }
+    for (int i = 0; i < job->n_tu; i++) {
+        const ohcu_tu *tu = &job->tus[i];
+        const int n4 = 1 << (tu->log2_size - 2);
+        if (tu->c_idx) continue;
+        for (int y = tu->y0 >> 2; y < (tu->y0 >> 2) + n4 && y < gh; y++)
+            for (int x = tu->x0 >> 2; x < (tu->x0 >> 2) + n4 && x < gw; x++) g[y * gw + x].tb = i;
+    }
+    memset(job->vbs, 0, (size_t)bsw * bsh);
+    memset(job->hbs, 0, (size_t)bsw * bsh);
+    for (int dir = 0; dir < 2; dir++)                      /* 0: vertical edges (left neighbour), 1: horizontal (upper) */
+        for (int y = dir ? 8 : 0; y < H; y += dir ? 8 : 4)
+            for (int x = dir ? 0 : 8; x < W; x += dir ? 4 : 8) {
+                const int cq = (y >> l2) * ctb_w + (x >> l2);
+                const int cp = dir ? cq - ctb_w : cq - 1;
+                const bs_cell *q = &g[(y >> 2) * gw + (x >> 2)];
+                const bs_cell *p = dir ? q - gw : q - 1;
+                if (job->deblock_disabled && job->deblock_disabled[cq]) continue;      /* the leaf's call is not made */
+                if (!((dir ? y : x) & cmask)) {            /* a CTB boundary: slice / tile conditions, :1010-1016, :1052-1058 */
+                    const int across = job->filter_slice_edges ? job->filter_slice_edges[cq] : 1;
+                    if (job->tab_slice_address && job->tab_slice_address[cq] != job->tab_slice_address[cp] && !across) continue;
+                    if (sp->no_tile_filter && job->tile_id && job->tile_id[cq] != job->tile_id[cp]) continue;
+                }
+                (dir ? job->hbs : job->vbs)[(x + y * bsw) >> 2] = (uint8_t)bs_unit(job, q, p);
+            }
+    free(g);
+    return 0;
+}

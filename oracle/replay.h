@@ -50,6 +50,34 @@ typedef struct oh_frame_job {
 #define OH_STAGE_DEBLOCK  4
 #define OH_STAGE_SAO      8
 
+/* ---- boundary strengths (bs derivation on the device) ----
+ * ff_hevc_deblocking_boundary_strengths (hevc_filter.c:1006-1125) with boundary_strength
+ * (:764-880, the TEST_MV_POC variant hevc.h:33 selects) fills vertical_bs / horizontal_bs
+ * per transform-tree leaf.  or_boundary_strengths() derives the same planes from what the
+ * C ABI already carries - the PU list, the coded luma TBs, the slice tables and the per-CTB
+ * slice / tile tables; ohref_boundary_strengths() drives the reference's own function over
+ * the transform-tree leaves (which only it reads). */
+typedef struct oh_leaf {          /* one leaf of hls_transform_tree (hevcdec.c:1549), coded or not */
+    uint16_t x0, y0;
+    uint8_t  log2_size, cbf_luma, pad[2];
+} oh_leaf;
+
+typedef struct oh_bs_job {
+    ohcu_seq_params sp;
+    int32_t n_slices;  const ohcu_slice_tab *slices;
+    int32_t n_pu;      const ohcu_pu *pus;
+    int32_t n_tu;      const ohcu_tu *tus;        /* coded TBs; the luma ones count */
+    int32_t n_leaf;    const oh_leaf *leaves;     /* decoding order */
+    const uint8_t *filter_slice_edges;            /* per CTB: slice_loop_filter_across_slices_enabled_flag; NULL = 1 */
+    const int32_t *tab_slice_address;             /* per CTB; NULL = one slice */
+    const int32_t *tile_id;                       /* per CTB; NULL = one tile  */
+    const uint8_t *deblock_disabled;              /* per CTB: slice_deblocking_filter_disabled_flag; NULL = 0 */
+    uint8_t *vbs, *hbs;                           /* out: ((width >> 2) + 1) * ((height >> 2) + 1) each */
+} oh_bs_job;
+
+int or_boundary_strengths(const oh_bs_job *job);
+int ohref_boundary_strengths(const oh_bs_job *job);
+
 /* returns 0, or a negative OHCU_E* code for malformed jobs */
 int or_replay_frame(const oh_frame_job *job);
 int ohref_replay_frame(const oh_frame_job *job);

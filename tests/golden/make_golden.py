@@ -21,6 +21,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 import frame_cases  # noqa: E402
 import leaf_cases  # noqa: E402
 import levels_cases  # noqa: E402
+import bs_cases  # noqa: E402
 import oracle_lib  # noqa: E402
 
 STAGE_SETS = {"mc": 1, "mc_res": 3, "mc_res_db": 7, "all": 15}
@@ -59,6 +60,15 @@ def main():
     with open(os.path.join(HERE, "levels_digest.json"), "w") as f:
         json.dump({"source": "ohref_dequant_block (hevc_cabac.c derive_quant_parameters{,_c} + scale_and_clip_coeff)",
                    "cases": len(outs), "sha256": levels_cases.digest(outs)}, f, indent=1)
+    # boundary strengths: the reference's ff_hevc_deblocking_boundary_strengths over the transform-tree leaves
+    bs = {}
+    for name in bs_cases.BS_CASES:
+        job, disabled = bs_cases.build_case(name)
+        vbs, hbs = ref.boundary_strengths(job, disabled)
+        bs[name] = hashlib.sha256(vbs.tobytes() + hbs.tobytes()).hexdigest()[:16]
+    with open(os.path.join(HERE, "bs_digests.json"), "w") as f:
+        json.dump({"source": "ohref_boundary_strengths (hevc_filter.c ff_hevc_deblocking_boundary_strengths per leaf)",
+                   "cases": bs}, f, indent=1, sort_keys=True)
     print(f"{len(leaves)} leaf digests, {len(frames)} frame cases, {len(outs)} dequantisation cases written")
 
 

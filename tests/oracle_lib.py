@@ -37,6 +37,18 @@ class FrameJobC(C.Structure):
     ]
 
 
+class BsJobC(C.Structure):
+    _fields_ = [
+        ("sp", abi.SeqParams),
+        ("n_slices", C.c_int32), ("slices", C.c_void_p),
+        ("n_pu", C.c_int32), ("pus", C.c_void_p),
+        ("n_tu", C.c_int32), ("tus", C.c_void_p),
+        ("n_leaf", C.c_int32), ("leaves", C.c_void_p),
+        ("filter_slice_edges", C.c_void_p), ("tab_slice_address", C.c_void_p), ("tile_id", C.c_void_p),
+        ("deblock_disabled", C.c_void_p), ("vbs", C.c_void_p), ("hbs", C.c_void_p),
+    ]
+
+
 STAGE_MC, STAGE_RESIDUAL, STAGE_DEBLOCK, STAGE_SAO = 1, 2, 4, 8
 
 
@@ -109,6 +121,9 @@ class Lib:
             fn.restype = _I
             fn.argtypes = [_I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P]
         self._dequant_block = fn
+        self._bs = getattr(self.lib, prefix + "boundary_strengths")
+        self._bs.restype = C.c_int
+        self._bs.argtypes = [C.POINTER(BsJobC)]
         self._replay = getattr(self.lib, prefix + "replay_frame")
         self._replay.restype = C.c_int
         self._replay.argtypes = [C.POINTER(FrameJobC)]
@@ -133,6 +148,30 @@ class Lib:
         self.lib.or_dequant_tus(tus.ctypes.data, np.ascontiguousarray(quant).ctypes.data, len(tus), out.ctypes.data, bd,
                                 sl.ctypes.data if sl is not None else None, sl_dc.ctypes.data if sl_dc is not None else None)
         return out
+
+    def boundary_strengths(self, job, deblock_disabled=None):
+        """(vbs, hbs) of a synth.FrameJob: derived from its PU / coded-TB lists (oracle) or by the
+        reference's ff_hevc_deblocking_boundary_strengths over its transform-tree leaves (ref)."""
+        sp = job.sp
+        n = ((sp.width >> 2) + 1) * ((sp.height >> 2) + 1)
+        vbs, hbs = np.zeros(n, np.uint8), np.zeros(n, np.uint8)
+        bj = BsJobC()
+        bj.sp = sp
+        bj.n_slices = len(job.slices); bj.slices = job.slices.ctypes.data
+        bj.n_pu = len(job.pus); bj.pus = job.pus.ctypes.data
+        bj.n_tu = len(job.tus); bj.tus = job.tus.ctypes.data
+        bj.n_leaf = len(job.leaves); bj.leaves = job.leaves.ctypes.data
+        bj.filter_slice_edges = job.filter_slice_edges.ctypes.data
+        bj.tab_slice_address = job.tab_slice_address.ctypes.data
+        bj.tile_id = job.tile_id.ctypes.data
+        if deblock_disabled is not None:
+            deblock_disabled = np.ascontiguousarray(deblock_disabled, dtype=np.uint8)
+            bj.deblock_disabled = deblock_disabled.ctypes.data
+        bj.vbs = vbs.ctypes.data; bj.hbs = hbs.ctypes.data
+        rc = self._bs(C.byref(bj))
+        if rc != 0:
+            raise RuntimeError(f"{self.which} boundary_strengths failed: {rc}")
+        return vbs, hbs
 
     def replay(self, job, refs, out_init=None, stages=0, use_deblock=True, use_sao=True):
         """Run one frame job.  refs = list (DPB slots) of pictures (lists of 2-D arrays).
