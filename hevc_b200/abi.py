@@ -84,6 +84,14 @@ class DeblockIn(C.Structure):
     ]
 
 
+class DeblockDeriveIn(C.Structure):
+    _fields_ = [
+        ("qp_y_tab", C.c_void_p), ("deblock", C.c_void_p), ("is_pcm", C.c_void_p),
+        ("filter_slice_edges", C.c_void_p), ("tab_slice_address", C.c_void_p), ("tile_id", C.c_void_p),
+        ("deblock_disabled", C.c_void_p),
+    ]
+
+
 class SaoIn(C.Structure):
     _fields_ = [
         ("sao", C.c_void_p), ("filter_slice_edges", C.c_void_p),
@@ -119,6 +127,7 @@ SYMBOLS = {
     "ohcu_append_tu_levels": (C.c_int, [_P, C.c_int, _P, _P, C.c_int, _P, C.c_size_t]),
     "ohcu_set_scaling_list": (C.c_int, [_P, C.c_int, _P, _P]),
     "ohcu_set_deblock": (C.c_int, [_P, C.c_int, C.POINTER(DeblockIn)]),
+    "ohcu_set_deblock_derived": (C.c_int, [_P, C.c_int, C.POINTER(DeblockDeriveIn)]),
     "ohcu_set_sao": (C.c_int, [_P, C.c_int, C.POINTER(SaoIn)]),
     "ohcu_frame_flush": (C.c_int, [_P, C.c_int]),
     "ohcu_frame_abort": (C.c_int, [_P, C.c_int]),
@@ -128,6 +137,7 @@ SYMBOLS = {
     "ohcu_frame_launch_stages": (C.c_int, [_P, C.c_int, C.c_int, C.c_int]),
     "ohcu_frame_sync": (C.c_int, [_P, C.c_int]),
     "ohcu_sync_all": (C.c_int, [_P]),
+    "ohcu_job_read_bs": (C.c_int, [_P, C.c_int, _P, _P]),
     "ohcu_set_profiling": (C.c_int, [_P, C.c_int]),
     "ohcu_job_stage_ms": (C.c_int, [_P, C.c_int, C.POINTER(C.c_float * NUM_STAGES)]),
     "ohcu_kernel_launches": (C.c_int64, [_P]),

@@ -84,11 +84,13 @@ class Context:
         ctb_w = (sp.width + (1 << sp.log2_ctb_size) - 1) >> sp.log2_ctb_size
         return to_sparse(fj.tus, fj.coeffs, sp.log2_ctb_size, hs, vs, ctb_w)
 
-    def append(self, job_id, fj, use_deblock=True, use_sao=True, sparse=False, levels=None):
+    def append(self, job_id, fj, use_deblock=True, use_sao=True, sparse=False, levels=None, derive_bs=None):
         """Append every list of a synth.FrameJob (or anything with the same arrays); sparse = the
         coefficients go as (position, level) pairs (True, or the lists sparse_lists() returned);
         levels = (quant, scaling) : fj.coeffs holds UN-scaled levels, quant one QUANT_DTYPE record per
-        TU, scaling None or (sl[4][6][64], sl_dc[2][6]) uint8 arrays - the device dequantises."""
+        TU, scaling None or (sl[4][6][64], sl_dc[2][6]) uint8 arrays - the device dequantises;
+        derive_bs = True or a per-CTB uint8 array of slice_deblocking_filter_disabled flags: fj.vbs / fj.hbs
+        are NOT sent, the device derives the boundary strengths from the lists (ohcu_set_deblock_derived)."""
         lib, h = self.lib, self.handle
         for i in range(len(fj.slices)):
             tab = abi.SliceTab.from_buffer_copy(fj.slices[i].tobytes())
@@ -115,7 +117,20 @@ class Context:
         elif len(fj.tus):
             check(lib.ohcu_append_tu(h, job_id, fj.tus.ctypes.data, len(fj.tus), fj.coeffs.ctypes.data,
                                      len(fj.coeffs)), "ohcu_append_tu")
-        if use_deblock:
+        if use_deblock and derive_bs is not None and derive_bs is not False:
+            d = abi.DeblockDeriveIn()
+            d.qp_y_tab = fj.qp_y_tab.ctypes.data
+            d.deblock = fj.deblock.ctypes.data
+            d.is_pcm = fj.is_pcm.ctypes.data if self.sp.pcm_or_bypass else None
+            d.filter_slice_edges = fj.filter_slice_edges.ctypes.data
+            d.tab_slice_address = fj.tab_slice_address.ctypes.data
+            d.tile_id = fj.tile_id.ctypes.data
+            dis = None
+            if derive_bs is not True:
+                dis = np.ascontiguousarray(derive_bs, dtype=np.uint8)
+                d.deblock_disabled = dis.ctypes.data
+            check(lib.ohcu_set_deblock_derived(h, job_id, C.byref(d)), "ohcu_set_deblock_derived")
+        elif use_deblock:
             d = fj.deblock_in()
             check(lib.ohcu_set_deblock(h, job_id, C.byref(d)), "ohcu_set_deblock")
         if use_sao:
@@ -179,7 +194,7 @@ class Context:
 
     # ---- convenience: one frame, synchronously (tests, smoke) -----------------
     def reconstruct(self, fj, refs, out_slot=None, out_init=None, stages=0, use_deblock=True, use_sao=True, sparse=False,
-                    levels=None):
+                    levels=None, derive_bs=None):
         """Upload refs to slots 0.., run one frame job, return the reconstructed planes."""
         if out_slot is None:
             out_slot = self.sp.dpb_slots - 1
@@ -189,7 +204,7 @@ class Context:
         if out_init is not None:
             self.upload(out_slot, out_init)
         j = self.begin(out_slot)
-        self.append(j, fj, use_deblock=use_deblock, use_sao=use_sao, sparse=sparse, levels=levels)
+        self.append(j, fj, use_deblock=use_deblock, use_sao=use_sao, sparse=sparse, levels=levels, derive_bs=derive_bs)
         self.stage(j)
         self.launch(j, out_slot, stages)
         self.sync(j)

@@ -82,7 +82,9 @@ struct Job {
     bool has_cross = false;  int max_slice = -1;    // what frame_stage has to validate
     Arena<int16_t> coeffs;   size_t ncoeff = 0;
     uint8_t *tab_h = nullptr, *tab_d = nullptr;      // block the table arenas are carved from
-    size_t tab_end[4] = {0, 0, 0, 0};                // bytes up to and including: CTB ranges + slices, SAO, deblock, is_pcm
+    size_t tab_end[5] = {0, 0, 0, 0, 0};             // bytes up to and including: CTB ranges + slices, SAO, qp + DBParams + bs flags, bs planes, is_pcm
+    Arena<uint8_t> bs_flags;     // per CTB BSF_*, bs derived on the device
+    bool bs_derived = false;
     // sparse form (ohcu_append_tu_sparse): the arena holds ohcu_coef pairs, ncoeff counts int16
     Arena<int2> ctb_coef_range;  // per CTB: first pair, number of pairs
     int coef_form = 0;           // 0 none yet, 1 dense, 2 sparse, 3 sparse un-scaled levels + per-TU quantiser
@@ -347,13 +349,15 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
             carve_arena(&j.sao, c->nctb, j.tab_h, j.tab_d, &off);
             carve_arena(&j.sao_flags, c->nctb, j.tab_h, j.tab_d, &off);
             j.tab_end[1] = off;
-            carve_arena(&j.vbs, (size_t)c->bs_w * c->bs_h, j.tab_h, j.tab_d, &off);
-            carve_arena(&j.hbs, (size_t)c->bs_w * c->bs_h, j.tab_h, j.tab_d, &off);
             carve_arena(&j.qp, (size_t)c->min_cb_w * c->min_cb_h, j.tab_h, j.tab_d, &off);
             carve_arena(&j.db, c->nctb, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.bs_flags, c->nctb, j.tab_h, j.tab_d, &off);
             j.tab_end[2] = off;
-            carve_arena(&j.is_pcm, (size_t)c->min_pu_w * c->min_pu_h, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.vbs, (size_t)c->bs_w * c->bs_h, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.hbs, (size_t)c->bs_w * c->bs_h, j.tab_h, j.tab_d, &off);
             j.tab_end[3] = off;
+            carve_arena(&j.is_pcm, (size_t)c->min_pu_w * c->min_pu_h, j.tab_h, j.tab_d, &off);
+            j.tab_end[4] = off;
             if (pass == 0) {
                 TRYCU(cudaHostAlloc((void **)&j.tab_h, off, cudaHostAllocDefault));
                 TRYCU(cudaMalloc((void **)&j.tab_d, off));
@@ -772,6 +776,36 @@ extern "C" int ohcu_set_deblock(ohcu_ctx *c, int job, const ohcu_deblock_in *in)
     j.has_pcm = c->sp.pcm_or_bypass && in->is_pcm;
     if (j.has_pcm) memcpy(j.is_pcm.h, in->is_pcm, (size_t)c->min_pu_w * c->min_pu_h);
     j.has_deblock = true;
+    j.bs_derived = false;
+    return 0;
+}
+
+// ff_hevc_deblocking_boundary_strengths moves to the device (bs.cu); here only the per-CTB
+// conditions of lc->boundary_flags (hevcdec.c:2822-2837) are folded into one byte per CTB
+extern "C" int ohcu_set_deblock_derived(ohcu_ctx *c, int job, const ohcu_deblock_derive_in *in)
+{
+    OPEN_JOB(c, job);
+    if (!in || !in->qp_y_tab || !in->deblock) return fail(OHCU_EINVAL, "null deblock input");
+    memcpy(j.qp.h, in->qp_y_tab, (size_t)c->min_cb_w * c->min_cb_h);
+    memcpy(j.db.h, in->deblock, sizeof(ohcu_dbparams) * c->nctb);
+    j.has_pcm = c->sp.pcm_or_bypass && in->is_pcm;
+    if (j.has_pcm) memcpy(j.is_pcm.h, in->is_pcm, (size_t)c->min_pu_w * c->min_pu_h);
+    const int cw = c->ctb_w;
+    for (int rs = 0; rs < c->nctb; rs++) {
+        const int x = rs % cw, y = rs / cw;
+        const bool across = in->filter_slice_edges ? in->filter_slice_edges[rs] != 0 : true;
+        auto differs = [&](int other) {
+            return (in->tab_slice_address && in->tab_slice_address[rs] != in->tab_slice_address[other] && !across) ||
+                   (c->sp.no_tile_filter && in->tile_id && in->tile_id[rs] != in->tile_id[other]);
+        };
+        unsigned fl = 0;
+        if (x > 0 && differs(rs - 1)) fl |= BSF_NO_LEFT;
+        if (y > 0 && differs(rs - cw)) fl |= BSF_NO_UP;
+        if (in->deblock_disabled && in->deblock_disabled[rs]) fl |= BSF_DISABLED;
+        j.bs_flags.h[rs] = (uint8_t)fl;
+    }
+    j.has_deblock = true;
+    j.bs_derived = true;
     return 0;
 }
 
@@ -897,7 +931,7 @@ static int stage_impl(ohcu_ctx *c, int job)
         if (j.has_sl) CU(cudaMemcpyAsync(j.sl_d, j.sl_h, SL_BYTES, cudaMemcpyHostToDevice, st));
     }
     // the tables: one copy up to the last group this frame uses
-    const size_t tab_bytes = j.tab_end[j.has_pcm ? 3 : j.has_deblock ? 2 : j.has_sao ? 1 : 0];
+    const size_t tab_bytes = j.tab_end[j.has_pcm ? 4 : j.has_deblock ? (j.bs_derived ? 2 : 3) : j.has_sao ? 1 : 0];
     CU(cudaMemcpyAsync(j.tab_d, j.tab_h, tab_bytes, cudaMemcpyHostToDevice, st));
     j.open = false;
     j.staged = true;
@@ -917,6 +951,7 @@ static void fill_frame_dev(const ohcu_ctx *c, const Job &j, FrameDev *f)
     f->scaling = j.coef_form == 3 && j.has_sl ? j.sl_d : nullptr;
     f->vbs = j.has_deblock ? j.vbs.d : nullptr; f->hbs = j.hbs.d; f->qp_y = j.qp.d; f->db = j.db.d;
     f->is_pcm = j.has_pcm ? j.is_pcm.d : nullptr;
+    f->bs_ctb_flags = j.has_deblock && j.bs_derived ? j.bs_flags.d : nullptr;
     f->sao = j.has_sao ? j.sao.d : nullptr; f->sao_ctb_flags = j.sao_flags.d;
 }
 
@@ -978,7 +1013,8 @@ extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int 
     LAUNCHED(launch_recon(f, stages & 3, st));
     STAGE_EVENT(1);
     STAGE_EVENT(2);
-    // deblocking and SAO run fused (loopfilter.cu); stage 3 carries their time
+    // deblocking and SAO run fused (loopfilter.cu); stage 3 carries their time (and the bs derivation's, bs.cu)
+    if ((lf_flags & 1) && f.bs_ctb_flags) LAUNCHED(launch_bs_derive(f, st));
     if (lf_flags) LAUNCHED(launch_loopfilter(f, j.lf_maps, lf_flags, st));
     STAGE_EVENT(3);
     // the finished picture becomes a reference: replicate its borders into the halo
@@ -1039,6 +1075,19 @@ extern "C" int ohcu_job_stage_ms(ohcu_ctx *c, int job, float ms[OHCU_NUM_STAGES]
     CU(cudaEventSynchronize(j.ev[4]));
     for (int i = 0; i < 4; i++) CU(cudaEventElapsedTime(&ms[i], j.ev[i], j.ev[i + 1]));
     CU(cudaEventElapsedTime(&ms[OHCU_STAGE_TOTAL], j.ev[0], j.ev[4]));
+    return 0;
+}
+
+extern "C" int ohcu_job_read_bs(ohcu_ctx *c, int job, uint8_t *vertical_bs, uint8_t *horizontal_bs)
+{
+    ENTER(c);
+    if (check_job(c, job)) return OHCU_EINVAL;
+    Job &j = c->jobs[job];
+    if (!vertical_bs || !horizontal_bs) return fail(OHCU_EINVAL, "null argument");
+    if (!j.staged || !j.has_deblock) return fail(OHCU_ESTATE, "job %d holds no deblocking input", job);
+    CU(cudaStreamSynchronize(j.stream));
+    CU(cudaMemcpy(vertical_bs, j.vbs.d, (size_t)c->bs_w * c->bs_h, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(horizontal_bs, j.hbs.d, (size_t)c->bs_w * c->bs_h, cudaMemcpyDeviceToHost));
     return 0;
 }
 

@@ -57,6 +57,7 @@ struct FrameDev {
     const int8_t *qp_y;
     const ohcu_dbparams *db;
     const uint8_t *is_pcm;
+    const uint8_t *bs_ctb_flags;     // bs derived on the device: per CTB, BSF_* below; nullptr = the planes came from the host
     // SAO
     const ohcu_sao *sao;
     const uint16_t *sao_ctb_flags;   // per CTB, see SAOF_* below
@@ -74,6 +75,9 @@ enum {
     SAOF_DIAG0 = 1 << 5, SAOF_DIAG1 = 1 << 6, SAOF_DIAG2 = 1 << 7, SAOF_DIAG3 = 1 << 8,
 };
 
+// per-CTB flags of the bs derivation (ohcu_set_deblock_derived), from the slice / tile tables
+enum { BSF_NO_LEFT = 1, BSF_NO_UP = 2, BSF_DISABLED = 4 };
+
 // kernel launchers (each returns the number of kernels it enqueued, < 0 on error)
 int launch_recon(const FrameDev &f, int flags, cudaStream_t st);   // flags: 1 MC, 2 residual
 int recon_sparse_ctb_coefs(int log2_ctb, int nplanes, int hs, int vs);   // int16 a CTB's rebuilt coefficient area may hold (sparse form)
@@ -81,6 +85,7 @@ int upload_mc_taps();
 int upload_dct_table();
 struct LfMaps { CUtensorMap m[3]; };        // the job's reconstructed picture, one box per plane
 int launch_loopfilter(const FrameDev &f, const LfMaps &maps, int flags, cudaStream_t st);   // flags: 1 deblock, 2 SAO
+int launch_bs_derive(const FrameDev &f, cudaStream_t st);      // vbs / hbs from the PU and TU lists (bs.cu)
 // per-entry test shims (recon.cu, loopfilter.cu)
 int dsp_mc(int bd, int luma, int family, uint8_t *dst, ptrdiff_t dststride, const uint8_t *src, ptrdiff_t srcstride,
            const int16_t *src2, int16_t *out16, int h, int denom, int wx0, int wx1, int ox0, int ox1, int mx, int my, int w);

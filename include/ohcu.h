@@ -163,6 +163,30 @@ typedef struct ohcu_deblock_in {
                                       seq.pcm_or_bypass == 0                       */
 } ohcu_deblock_in;
 
+/* ---- deblocking with the boundary strengths DERIVED ON THE DEVICE (SURVEY section 8f
+ *      rank 2).  Replaces ff_hevc_deblocking_boundary_strengths (hevc_filter.c:989-1125,
+ *      called per transform-tree leaf at hevcdec.c:1677, :1707, :2603, :2687) and its
+ *      boundary_strength (:764-880): vertical_bs / horizontal_bs are computed at flush from
+ *      the frame's own lists -
+ *        PU list + slice tables  ->  MvField of every 4x4 block and the picture each list
+ *                                    refers to (the reference compares POCs; here DPB slots)
+ *        coded luma TBs          ->  cbf_luma: an edge unit lies on a transform-block
+ *                                    boundary with cbf_luma on a side exactly when it lies
+ *                                    on the perimeter of a coded luma TB
+ *      4x4 blocks no PU covers count as intra (bs 2).  The per-CTB tables say where the
+ *      reference suppresses CTB-boundary edges (lc->boundary_flags, hevcdec.c:2822-2837, with
+ *      slice_loop_filter_across_slices_enabled_flag of the CTB's slice and
+ *      seq.no_tile_filter) and which slices have slice_deblocking_filter_disabled_flag. */
+typedef struct ohcu_deblock_derive_in {
+    const int8_t  *qp_y_tab;           /* as ohcu_deblock_in                          */
+    const ohcu_dbparams *deblock;
+    const uint8_t *is_pcm;             /* may be NULL                                 */
+    const uint8_t *filter_slice_edges; /* per CTB, NULL = 1 everywhere                */
+    const int32_t *tab_slice_address;  /* per CTB, NULL = one slice                   */
+    const int32_t *tile_id;            /* per CTB, NULL = one tile                    */
+    const uint8_t *deblock_disabled;   /* per CTB, NULL = 0 everywhere                */
+} ohcu_deblock_derive_in;
+
 /* ---- SAO side inputs (sao_filter_CTB, hevc_filter.c:264-325) ------------ */
 typedef struct ohcu_sao_in {
     const ohcu_sao *sao;               /* ctb_width*ctb_height, raster             */
@@ -305,6 +329,9 @@ int ohcu_set_scaling_list(ohcu_ctx *ctx, int job, const uint8_t sl[4][6][64],
  * 634-654, 686-697, 735-755).  Arrays are copied before return.  Not calling it
  * for a frame = no deblocking (all bs zero).                                    */
 int ohcu_set_deblock(ohcu_ctx *ctx, int job, const ohcu_deblock_in *in);
+/* same, with the bs planes derived on the device from this job's PU and TU lists
+ * (whatever is appended before the flush)                                          */
+int ohcu_set_deblock_derived(ohcu_ctx *ctx, int job, const ohcu_deblock_derive_in *in);
 
 /* replaces the per-CTB calls of sao_filter_CTB (hevc_filter.c:349-353, 486-494).
  * Not calling it for a frame = SAO not applied.                                 */
@@ -329,6 +356,11 @@ int ohcu_frame_launch_stages(ohcu_ctx *ctx, int job, int out_slot, int stages);
 
 int ohcu_frame_sync(ohcu_ctx *ctx, int job);
 int ohcu_sync_all(ohcu_ctx *ctx);
+
+/* Test hook: the boundary-strength planes the job's last launch filtered with (the
+ * host's, or the ones derived on the device), bs_width*bs_height bytes each; waits for
+ * the job.                                                                         */
+int ohcu_job_read_bs(ohcu_ctx *ctx, int job, uint8_t *vertical_bs, uint8_t *horizontal_bs);
 
 /* ---- measurement hooks (bench.py; CUDA events on the job's own stream) ---- */
 #define OHCU_STAGE_MC       0

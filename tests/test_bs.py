@@ -43,3 +43,46 @@ def test_oracle_bs_vs_reference(name):
         far.pus["mv"][:, :, 0] += (np.arange(len(far.pus)) % 7 * 64)[:, None].astype(np.int16)
         all_far = int(np.count_nonzero(np.concatenate(oracle_lib.Lib("ref").boundary_strengths(far, disabled)) == 1))
         assert 0 < ones < all_far * 0.9, (ones, all_far)
+
+
+def _grid_units(sp):
+    """indices of the plane entries the filters read: vertical edges x % 8 == 0, horizontal y % 8 == 0"""
+    bsw = (sp.width >> 2) + 1
+    ys, xs = np.meshgrid(np.arange(0, sp.height, 4), np.arange(8, sp.width, 8), indexing="ij")
+    v = ((xs + ys * bsw) >> 2).ravel()
+    ys, xs = np.meshgrid(np.arange(8, sp.height, 8), np.arange(0, sp.width, 4), indexing="ij")
+    h = ((xs + ys * bsw) >> 2).ravel()
+    return v, h
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(bs_cases.BS_CASES))
+def test_device_bs_matches_oracle_and_filters_with_it(name):
+    from hevc_b200 import backend
+    job, disabled = bs_cases.build_case(name)
+    base = bs_cases.BS_CASES[name][0]
+    import frame_cases
+    _, refs = frame_cases.build_case(base)
+    orc = oracle_lib.Lib("oracle")
+    vbs, hbs = orc.boundary_strengths(job, disabled)
+    # the oracle replay filters with the derived planes ...
+    job.vbs, job.hbs = vbs, hbs
+    want = orc.replay(job, refs)
+    # ... and so must the device, which is given none
+    with backend.Context(job.sp) as ctx:
+        out_slot = job.sp.dpb_slots - 1
+        for i, r in enumerate(refs):
+            if i != out_slot:
+                ctx.upload(i, r)
+        j = ctx.begin(out_slot)
+        ctx.append(j, job, sparse=True, derive_bs=True if disabled is None else disabled)
+        ctx.flush(j)
+        ctx.sync(j)
+        got = ctx.download(out_slot)
+        gv, gh = np.zeros_like(vbs), np.zeros_like(hbs)
+        backend.check(ctx.lib.ohcu_job_read_bs(ctx.handle, j, gv.ctypes.data, gh.ctypes.data), "ohcu_job_read_bs")
+    iv, ih = _grid_units(job.sp)
+    assert np.array_equal(gv[iv], vbs[iv]), f"{name}: vertical_bs differs at {np.flatnonzero(gv[iv] != vbs[iv])[:5].tolist()}"
+    assert np.array_equal(gh[ih], hbs[ih]), f"{name}: horizontal_bs differs at {np.flatnonzero(gh[ih] != hbs[ih])[:5].tolist()}"
+    for c, (g, w) in enumerate(zip(got, want)):
+        assert np.array_equal(g, w), f"{name} plane {c}"
