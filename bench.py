@@ -89,6 +89,16 @@ def levels_inputs(jobs):
     return out
 
 
+def derived_bs_inputs(jobs):
+    """--bs derived: the frames' bs planes are replaced by the ones the work lists imply (CPU restatement of
+    ff_hevc_deblocking_boundary_strengths, oracle/replay.c) - what the parity check and the CPU arms filter
+    with; the GPU arm is handed no planes and derives them itself (ohcu_set_deblock_derived)."""
+    import oracle_lib
+    orc = oracle_lib.Lib("oracle")
+    for fj in jobs:
+        fj.vbs, fj.hbs = orc.boundary_strengths(fj)
+
+
 def algorithmic_bytes(job):
     """per kernel, bytes that must move once.
     recon       every reference sample a PU needs read once + every sample written once
@@ -203,6 +213,9 @@ def run_ours(args, rank, world):
     sparse_lists = [ctx.sparse_lists(fj) for fj in jobs] if args.coeffs == "sparse" else None
     # --coeffs levels: the pairs carry un-scaled levels, the kernel dequantises (ohcu_append_tu_levels)
     level_lists = levels_inputs(jobs) if args.coeffs == "levels" else None
+    derive = args.bs == "derived"
+    if derive:
+        derived_bs_inputs(jobs)
 
     # ---------------- resident leg: lists staged once, kernels only in the timed region
     for k in range(B):
@@ -210,9 +223,9 @@ def run_ours(args, rank, world):
         assert j == k
         if level_lists:
             recs, q, pairs, scaling = level_lists[k % len(jobs)]
-            ctx.append(j, jobs[k % len(jobs)], levels=(q, scaling, (recs, q, pairs)))
+            ctx.append(j, jobs[k % len(jobs)], levels=(q, scaling, (recs, q, pairs)), derive_bs=derive)
         else:
-            ctx.append(j, jobs[k % len(jobs)], sparse=sparse_lists[k % len(jobs)] if sparse_lists else False)
+            ctx.append(j, jobs[k % len(jobs)], sparse=sparse_lists[k % len(jobs)] if sparse_lists else False, derive_bs=derive)
         ctx.stage(j)
     ctx.sync()
     l0 = ctx.kernel_launches()
@@ -282,14 +295,23 @@ def run_ours(args, rank, world):
                 C.memmove(ptr.value, fj.coeffs.ctypes.data, fj.coeffs.nbytes)
             abi.check(lib.ohcu_append_tu_inplace(h, j, fj.tus.ctypes.data, len(fj.tus)))
             coef_bytes = fj.coeffs.nbytes
-        d = fj.deblock_in(); s = fj.sao_in()
-        abi.check(lib.ohcu_set_deblock(h, j, C.byref(d)))
+        s = fj.sao_in()
+        if derive:
+            d = abi.DeblockDeriveIn()
+            d.qp_y_tab = fj.qp_y_tab.ctypes.data; d.deblock = fj.deblock.ctypes.data
+            d.is_pcm = fj.is_pcm.ctypes.data if sp.pcm_or_bypass else None
+            d.filter_slice_edges = fj.filter_slice_edges.ctypes.data
+            d.tab_slice_address = fj.tab_slice_address.ctypes.data; d.tile_id = fj.tile_id.ctypes.data
+            abi.check(lib.ohcu_set_deblock_derived(h, j, C.byref(d)))
+        else:
+            d = fj.deblock_in()
+            abi.check(lib.ohcu_set_deblock(h, j, C.byref(d)))
         abi.check(lib.ohcu_set_sao(h, j, C.byref(s)))
         ctx.flush(j)
         ctx.download_async(2 + k, outs[k])
         nctb = len(fj.sao)
         h2d = (fj.pus.nbytes + 8 * nctb + fj.slices.nbytes + fj.tus.nbytes + coef_bytes + 8 * nctb +
-               fj.vbs.nbytes + fj.hbs.nbytes + fj.qp_y_tab.nbytes + fj.deblock.nbytes + fj.sao.nbytes + 2 * nctb)
+               (nctb if derive else fj.vbs.nbytes + fj.hbs.nbytes) + fj.qp_y_tab.nbytes + fj.deblock.nbytes + fj.sao.nbytes + 2 * nctb)
         d2h = sum(p.strides[0] * (p.shape[0] - 1) + p.shape[1] * p.itemsize for p in outs[k])   # bytes the copies move
 
     # frames are submitted by a few host threads, one frame each at a time, the way the
@@ -354,7 +376,7 @@ def run_ours(args, rank, world):
                    "l2": f"inputs larger than L2: {B} frames x ~{(ab['pipeline']) / 1e6:.0f} MB algorithmic traffic per step",
                    "pus_per_frame": int(len(jobs[0].pus)), "tus_per_frame": int(len(jobs[0].tus)),
                    "coded_fraction": round(len(jobs[0].coeffs) / (ab['S'] / (2 if sp.bit_depth > 8 else 1)), 3),
-                   "coeffs": args.coeffs,
+                   "coeffs": args.coeffs, "bs": args.bs,
                    "significant_fraction": round(float(np.count_nonzero(jobs[0].coeffs)) / max(1, len(jobs[0].coeffs)), 3)},
         "frames_per_s": round(total_frames / (ms_resident * 1e-3), 1),
         "gpu_launches": int(launches),
@@ -392,6 +414,8 @@ def run_reference(args, rank, world):
     jobs, refs = make_inputs(args.workload, 0)
     if args.coeffs == "levels":
         levels_inputs(jobs)               # same coefficient values as the GPU arm reconstructs from
+    if args.bs == "derived":
+        derived_bs_inputs(jobs)           # same bs planes as the GPU arm derives
     cb = cpu_reference(jobs, refs, steps=args.steps, warmup=args.warmup)
     sp = jobs[0].sp
     line = {
@@ -424,6 +448,9 @@ def main():
                     help="coefficient form handed to the library: (position, level) pairs of the significant "
                          "coefficients (ohcu_append_tu_sparse, what the residual parser produces), zero-filled N x N blocks, or "
                          "un-scaled levels + a quantiser per block (ohcu_append_tu_levels: dequantisation on the device)")
+    ap.add_argument("--bs", default="host", choices=["host", "derived"],
+                    help="boundary strengths: planes uploaded by the host (ohcu_set_deblock) or derived on the device from the "
+                         "PU / TU lists (ohcu_set_deblock_derived)")
     ap.add_argument("--slot-pitch", action="store_true",
                     help="e2e leg: host pictures with the device planes' row pitch (one linear copy per plane)")
     ap.add_argument("--no-cpu", action="store_true")

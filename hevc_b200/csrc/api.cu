@@ -61,6 +61,8 @@ constexpr size_t SL_BYTES = 4 * 6 * 64 + 2 * 6;      // ScalingList, hevc_ps.h:6
 
 struct Job {
     cudaStream_t stream = nullptr;
+    cudaStream_t side = nullptr;      // the bs derivation runs beside recon_kernel (it needs only the lists)
+    cudaEvent_t fork = nullptr, join = nullptr;
     cudaEvent_t done = nullptr;
     cudaEvent_t ev[OHCU_NUM_STAGES + 1] = {};
     bool has_done = false, timed = false;
@@ -248,6 +250,9 @@ extern "C" int ohcu_destroy(ohcu_ctx *c)
         if (j.tab_d) cudaFree(j.tab_d);
         if (j.done) cudaEventDestroy(j.done);
         for (auto &e : j.ev) if (e) cudaEventDestroy(e);
+        if (j.fork) cudaEventDestroy(j.fork);
+        if (j.join) cudaEventDestroy(j.join);
+        if (j.side) cudaStreamDestroy(j.side);
         if (j.stream) cudaStreamDestroy(j.stream);
     }
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
@@ -329,6 +334,9 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
     for (auto &j : c->jobs) {
         TRYCU(cudaStreamCreateWithFlags(&j.stream, cudaStreamNonBlocking));
         TRYCU(cudaEventCreateWithFlags(&j.done, cudaEventDisableTiming));
+        TRYCU(cudaStreamCreateWithFlags(&j.side, cudaStreamNonBlocking));
+        TRYCU(cudaEventCreateWithFlags(&j.fork, cudaEventDisableTiming));
+        TRYCU(cudaEventCreateWithFlags(&j.join, cudaEventDisableTiming));
         for (auto &e : j.ev) TRYCU(cudaEventCreate(&e));
         TRY(alloc_picture(c, &j.recon, false));
         TRY(alloc_arena(&j.pus, c->sp.max_pus));
@@ -1007,14 +1015,23 @@ extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int 
 #define LAUNCHED(call) do { n = (call); if (n < 0) return fail(OHCU_EINVAL, "launch refused"); total += n; \
         CU(cudaGetLastError()); } while (0)
     STAGE_EVENT(0);
+    // boundary strengths derived from the lists (bs.cu): on the job's side stream, beside recon_kernel;
+    // it starts after everything already queued on the job's stream (staging copies, the previous launch)
+    const bool derive = (lf_flags & 1) && f.bs_ctb_flags;
+    if (derive) {
+        CU(cudaEventRecord(j.fork, st));
+        CU(cudaStreamWaitEvent(j.side, j.fork, 0));
+        LAUNCHED(launch_bs_derive(f, j.side));
+        CU(cudaEventRecord(j.join, j.side));
+    }
     // samples this launch does not predict keep the slot's current content
     if ((!(stages & 1) || !j.all_covered) && lf_flags) LAUNCHED(launch_copy_picture(f, f.work, f.out, st));
     // MC and the residual run fused (recon.cu); stage 1 carries their time
     LAUNCHED(launch_recon(f, stages & 3, st));
     STAGE_EVENT(1);
     STAGE_EVENT(2);
-    // deblocking and SAO run fused (loopfilter.cu); stage 3 carries their time (and the bs derivation's, bs.cu)
-    if ((lf_flags & 1) && f.bs_ctb_flags) LAUNCHED(launch_bs_derive(f, st));
+    // deblocking and SAO run fused (loopfilter.cu); stage 3 carries their time
+    if (derive) CU(cudaStreamWaitEvent(st, j.join, 0));
     if (lf_flags) LAUNCHED(launch_loopfilter(f, j.lf_maps, lf_flags, st));
     STAGE_EVENT(3);
     // the finished picture becomes a reference: replicate its borders into the halo

@@ -15,13 +15,16 @@
 //
 // One CTA per CTB.  The PUs and coded luma TBs of the CTB, of its left and of its upper neighbour
 // enter a (cells + 1)^2 map of 4x4 cells in shared memory (PU index, TB index); then one thread
-// per edge unit: 16 x 8 vertical and 8 x 16 horizontal units of a 64x64 CTB = 256 threads.
+// per edge unit (16 x 8 vertical and 8 x 16 horizontal units of a 64x64 CTB).
 // The planes are the ones loopfilter_kernel reads (index (x + y * bs_width) >> 2, hevcdec.c:127).
 #include "ohcu_internal.h"
 
 namespace ohcu {
 
-constexpr int BS_THREADS = 256;
+#ifndef BS_NTHREADS
+#define BS_NTHREADS 128
+#endif
+constexpr int BS_THREADS = BS_NTHREADS;      // 128: all CTBs of a 4K picture are resident at once (16 CTAs per SM)
 constexpr int BS_CELLS = 17;                 // 16 cells of a 64x64 CTB + the neighbour's column / row
 
 struct BsCell { int pu, tb; };
@@ -75,21 +78,22 @@ __global__ void __launch_bounds__(BS_THREADS) bs_kernel(const __grid_constant__ 
                 if (is_tb) c.tb = idx; else c.pu = idx;
             }
     };
-#pragma unroll 1
+    int2 pr[3], tr[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {                          // the six ranges first: independent loads
+        pr[k] = nb[k] >= 0 ? f.ctb_pu_range[nb[k]] : make_int2(0, 0);
+        tr[k] = nb[k] >= 0 && f.n_tu > 0 ? f.ctb_tu_range[nb[k]] : make_int2(0, 0);
+    }
+#pragma unroll
     for (int k = 0; k < 3; k++) {
-        if (nb[k] < 0) continue;
-        const int2 pr = f.ctb_pu_range[nb[k]];
-        const int np = min(pr.y & 0xffffff, 128);
+        const int np = min(pr[k].y & 0xffffff, 128);
         for (int i = tid; i < np; i += BS_THREADS) {
-            const ohcu_pu &pu = f.pus[pr.x + i];
-            paint(pu.x0 >> 2, pu.y0 >> 2, pu.w >> 2, pu.h >> 2, pr.x + i, false);
+            const ohcu_pu &pu = f.pus[pr[k].x + i];
+            paint(pu.x0 >> 2, pu.y0 >> 2, pu.w >> 2, pu.h >> 2, pr[k].x + i, false);
         }
-        if (f.n_tu > 0) {
-            const int2 tr = f.ctb_tu_range[nb[k]];
-            for (int i = tid; i < tr.y; i += BS_THREADS) {
-                const ohcu_tu &tu = f.tus[tr.x + i];
-                if (tu.c_idx == 0) paint(tu.x0 >> 2, tu.y0 >> 2, 1 << (tu.log2_size - 2), 1 << (tu.log2_size - 2), tr.x + i, true);
-            }
+        for (int i = tid; i < tr[k].y; i += BS_THREADS) {
+            const ohcu_tu &tu = f.tus[tr[k].x + i];
+            if (tu.c_idx == 0) paint(tu.x0 >> 2, tu.y0 >> 2, 1 << (tu.log2_size - 2), 1 << (tu.log2_size - 2), tr[k].x + i, true);
         }
     }
     __syncthreads();
