@@ -258,7 +258,11 @@ def run_ours(args, rank, world):
     ctx.set_profiling(False)
 
     # ---------------- e2e leg: host buffers -> H2D -> kernels -> D2H, through the C ABI
-    outs = [ctx.pinned_picture(slot_pitch=args.slot_pitch) for _ in range(E)]
+    full = (0, 0, sp.width, sp.height)
+    if args.copy_out == "packed":
+        outs = [ctx.pinned_cropped(full) for _ in range(E)]
+    else:
+        outs = [ctx.pinned_picture(slot_pitch=args.slot_pitch or args.copy_out == "pitch") for _ in range(E)]
     h2d = d2h = 0
 
     def submit(i, copy_coeffs=False):
@@ -308,7 +312,10 @@ def run_ours(args, rank, world):
             abi.check(lib.ohcu_set_deblock(h, j, C.byref(d)))
         abi.check(lib.ohcu_set_sao(h, j, C.byref(s)))
         ctx.flush(j)
-        ctx.download_async(2 + k, outs[k])
+        if args.copy_out == "packed":
+            ctx.output_cropped(2 + k, full, out=outs[k], wait=False)
+        else:
+            ctx.download_async(2 + k, outs[k])
         nctb = len(fj.sao)
         h2d = (fj.pus.nbytes + 8 * nctb + fj.slices.nbytes + fj.tus.nbytes + coef_bytes + 8 * nctb +
                (nctb if derive else fj.vbs.nbytes + fj.hbs.nbytes) + fj.qp_y_tab.nbytes + fj.deblock.nbytes + fj.sao.nbytes + 2 * nctb)
@@ -376,7 +383,7 @@ def run_ours(args, rank, world):
                    "l2": f"inputs larger than L2: {B} frames x ~{(ab['pipeline']) / 1e6:.0f} MB algorithmic traffic per step",
                    "pus_per_frame": int(len(jobs[0].pus)), "tus_per_frame": int(len(jobs[0].tus)),
                    "coded_fraction": round(len(jobs[0].coeffs) / (ab['S'] / (2 if sp.bit_depth > 8 else 1)), 3),
-                   "coeffs": args.coeffs, "bs": args.bs,
+                   "coeffs": args.coeffs, "bs": args.bs, "copy_out": args.copy_out,
                    "significant_fraction": round(float(np.count_nonzero(jobs[0].coeffs)) / max(1, len(jobs[0].coeffs)), 3)},
         "frames_per_s": round(total_frames / (ms_resident * 1e-3), 1),
         "gpu_launches": int(launches),
@@ -451,6 +458,9 @@ def main():
     ap.add_argument("--bs", default="host", choices=["host", "derived"],
                     help="boundary strengths: planes uploaded by the host (ohcu_set_deblock) or derived on the device from the "
                          "PU / TU lists (ohcu_set_deblock_derived)")
+    ap.add_argument("--copy-out", choices=["2d", "pitch", "packed"], default="2d",
+                    help="e2e leg, device -> host: pitched 2-D copies into tight planes (2d), linear copies into planes with "
+                         "the device pitch (pitch), or ohcu_slot_output_cropped: pack kernel + one linear copy (packed)")
     ap.add_argument("--slot-pitch", action="store_true",
                     help="e2e leg: host pictures with the device planes' row pitch (one linear copy per plane)")
     ap.add_argument("--no-cpu", action="store_true")

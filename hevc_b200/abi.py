@@ -92,6 +92,10 @@ class DeblockDeriveIn(C.Structure):
     ]
 
 
+class Crop(C.Structure):
+    _fields_ = [("left", C.c_int32), ("top", C.c_int32), ("width", C.c_int32), ("height", C.c_int32)]
+
+
 class SaoIn(C.Structure):
     _fields_ = [
         ("sao", C.c_void_p), ("filter_slice_edges", C.c_void_p),
@@ -115,6 +119,8 @@ SYMBOLS = {
     "ohcu_slot_upload": (C.c_int, [_P, C.c_int, C.POINTER(_P * 3), C.POINTER(C.c_ssize_t * 3)]),
     "ohcu_slot_download": (C.c_int, [_P, C.c_int, C.POINTER(_P * 3), C.POINTER(C.c_ssize_t * 3)]),
     "ohcu_slot_download_async": (C.c_int, [_P, C.c_int, C.POINTER(_P * 3), C.POINTER(C.c_ssize_t * 3)]),
+    "ohcu_slot_output_cropped": (C.c_int, [_P, C.c_int, C.POINTER(Crop), C.POINTER(_P * 3)]),
+    "ohcu_slot_output_cropped_async": (C.c_int, [_P, C.c_int, C.POINTER(Crop), C.POINTER(_P * 3)]),
     "ohcu_slot_sync": (C.c_int, [_P, C.c_int]),
     "ohcu_frame_begin": (C.c_int, [_P, C.c_int, C.c_int]),
     "ohcu_set_slice": (C.c_int, [_P, C.c_int, C.c_int, C.POINTER(SliceTab)]),

@@ -69,6 +69,39 @@ class Context:
         check(self.lib.ohcu_slot_download_async(self.handle, slot, C.byref(ptrs), C.byref(strides)),
               "ohcu_slot_download_async")
 
+    def crop_shape(self, c, crop):
+        hs = 1 if (c and self.sp.chroma_format_idc in (1, 2)) else 0
+        vs = 1 if (c and self.sp.chroma_format_idc == 1) else 0
+        return (crop[3] >> vs, crop[2] >> hs)
+
+    def output_cropped(self, slot, crop, out=None, wait=True):
+        """ohcu_slot_output_cropped: the (left, top, width, height) window of the slot's planes,
+        packed on the device, into tight host planes (oh_output_cropped_cpy, openhevc.c:662-742)."""
+        if out is None:
+            out = [np.empty(self.crop_shape(c, crop), dtype=self.dtype) for c in range(self.nplanes)]
+        ptrs = (C.c_void_p * 3)()
+        for i, p in enumerate(out):
+            assert p.flags["C_CONTIGUOUS"] and p.shape == self.crop_shape(i, crop) and p.dtype == self.dtype
+            ptrs[i] = p.ctypes.data
+        cr = abi.Crop(*[int(v) for v in crop])
+        fn = self.lib.ohcu_slot_output_cropped if wait else self.lib.ohcu_slot_output_cropped_async
+        check(fn(self.handle, slot, C.byref(cr), C.byref(ptrs)), "ohcu_slot_output_cropped")
+        return out
+
+    def pinned_cropped(self, crop):
+        """Tight output planes for output_cropped(wait=False), following each other in one pinned
+        block at 16-byte boundaries (they then leave the device as one copy)."""
+        item = np.dtype(self.dtype).itemsize
+        shapes = [self.crop_shape(c, crop) for c in range(self.nplanes)]
+        offs, total = [], 0
+        for h, w in shapes:
+            offs.append(total)
+            total += (h * w * item + 15) & ~15
+        p = C.c_void_p()
+        check(self.lib.ohcu_host_alloc(total, C.byref(p)), "ohcu_host_alloc")
+        buf = (C.c_char * total).from_address(p.value)
+        return [np.frombuffer(buf, dtype=self.dtype, count=h * w, offset=o).reshape(h, w) for (h, w), o in zip(shapes, offs)]
+
     def slot_sync(self, slot):
         check(self.lib.ohcu_slot_sync(self.handle, slot), "ohcu_slot_sync")
 

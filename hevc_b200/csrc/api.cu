@@ -48,6 +48,7 @@ struct Slot {
     cudaEvent_t read_done = nullptr;  // last async download finished
     bool has_ready = false, has_read = false;
     uint64_t readers = 0;             // jobs that read this slot since its last write
+    uint8_t *out_d = nullptr;         // tight staging of ohcu_slot_output_cropped (allocated on first use)
 };
 
 template <typename T> struct Arena {      // pinned host staging + device copy
@@ -235,6 +236,7 @@ extern "C" int ohcu_destroy(ohcu_ctx *c)
     cudaDeviceSynchronize();
     for (auto &s : c->slots) {
         if (s.pic.base) cudaFree(s.pic.base);
+        if (s.out_d) cudaFree(s.out_d);
         if (s.ready) cudaEventDestroy(s.ready);
         if (s.read_done) cudaEventDestroy(s.read_done);
     }
@@ -475,6 +477,62 @@ extern "C" int ohcu_slot_download(ohcu_ctx *c, int slot, uint8_t *const planes[3
 extern "C" int ohcu_slot_download_async(ohcu_ctx *c, int slot, uint8_t *const planes[3], const ptrdiff_t strides[3])
 {
     return download_impl(c, slot, planes, strides, false);
+}
+// Cropped copy-out: pack kernel into the slot's tight staging buffer, then linear copies.
+static int output_cropped_impl(ohcu_ctx *c, int slot, const ohcu_crop *crop, uint8_t *const planes[3], bool wait)
+{
+    ENTER(c);
+    if (check_slot(c, slot)) return OHCU_EINVAL;
+    if (!crop || !planes) return fail(OHCU_EINVAL, "null crop or planes");
+    const int mx = (1 << c->hs) - 1, my = (1 << c->vs) - 1;
+    if (crop->left < 0 || crop->top < 0 || crop->width <= 0 || crop->height <= 0 ||
+        crop->left + crop->width > c->sp.width || crop->top + crop->height > c->sp.height)
+        return fail(OHCU_EINVAL, "crop window outside the picture");
+    if (c->nplanes > 1 && (((crop->left | crop->width) & mx) || ((crop->top | crop->height) & my)))
+        return fail(OHCU_EINVAL, "crop window not a multiple of the chroma subsampling");
+    int left[3], top[3], w[3], h[3];
+    size_t off[3], total = 0, full = 0;
+    for (int i = 0; i < c->nplanes; i++) {
+        if (!planes[i]) return fail(OHCU_EINVAL, "null plane");
+        const int hs = i ? c->hs : 0, vs = i ? c->vs : 0;
+        left[i] = crop->left >> hs; top[i] = crop->top >> vs; w[i] = crop->width >> hs; h[i] = crop->height >> vs;
+        off[i] = total;
+        total += ((size_t)w[i] * h[i] * c->P + 15) & ~(size_t)15;     // planes start on 16-byte boundaries
+        full += ((size_t)c->pw[i] * c->ph[i] * c->P + 15) & ~(size_t)15;
+    }
+    Slot &s = c->slots[slot];
+    {
+        std::lock_guard<std::mutex> lock(c->mu);
+        if (!s.out_d) CU(cudaMalloc(&s.out_d, full));
+        if (s.has_ready) CU(cudaStreamWaitEvent(c->copy_stream, s.ready, 0));
+        uint8_t *dst[3] = {nullptr, nullptr, nullptr};
+        for (int i = 0; i < c->nplanes; i++) dst[i] = s.out_d + off[i];
+        c->launches += launch_crop_pack(s.pic.ps, c->nplanes, c->P, left, top, w, h, dst, c->copy_stream);
+        CU(cudaGetLastError());
+        // planes that follow each other in the caller's memory the way they do in the staging
+        // buffer leave as one copy
+        bool one = true;
+        for (int i = 1; i < c->nplanes; i++) one = one && planes[i] == planes[0] + off[i];
+        if (one) {
+            CU(cudaMemcpyAsync(planes[0], s.out_d, off[c->nplanes - 1] + (size_t)w[c->nplanes - 1] * h[c->nplanes - 1] * c->P,
+                               cudaMemcpyDeviceToHost, c->copy_stream));
+        } else {
+            for (int i = 0; i < c->nplanes; i++)
+                CU(cudaMemcpyAsync(planes[i], dst[i], (size_t)w[i] * h[i] * c->P, cudaMemcpyDeviceToHost, c->copy_stream));
+        }
+        CU(cudaEventRecord(s.read_done, c->copy_stream));
+        s.has_read = true;
+    }
+    if (wait) CU(cudaEventSynchronize(s.read_done));
+    return 0;
+}
+extern "C" int ohcu_slot_output_cropped(ohcu_ctx *c, int slot, const ohcu_crop *crop, uint8_t *const planes[3])
+{
+    return output_cropped_impl(c, slot, crop, planes, true);
+}
+extern "C" int ohcu_slot_output_cropped_async(ohcu_ctx *c, int slot, const ohcu_crop *crop, uint8_t *const planes[3])
+{
+    return output_cropped_impl(c, slot, crop, planes, false);
 }
 extern "C" int ohcu_slot_sync(ohcu_ctx *c, int slot)
 {

@@ -98,6 +98,9 @@ int dsp_sao(int bd, int edge, uint8_t *dst, const uint8_t *src, ptrdiff_t stride
 void loopfilter_box(const FrameDev &f, int c, int *bw, int *bh);
 int launch_pad_picture(const FrameDev &f, const PlaneSet &pic, cudaStream_t st);   // fill the replicated halo
 int launch_copy_picture(const FrameDev &f, const PlaneSet &dst, const PlaneSet &src, cudaStream_t st);
+// the window of every plane packed without row gaps (ohcu_slot_output_cropped)
+int launch_crop_pack(const PlaneSet &pic, int nplanes, int P, const int left[3], const int top[3], const int w[3],
+                     const int h[3], uint8_t *const dst[3], cudaStream_t st);
 int launch_l2_flush(void *buf, size_t bytes, cudaStream_t st);
 
 // ---- small device helpers -------------------------------------------------------

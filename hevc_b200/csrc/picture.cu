@@ -102,6 +102,60 @@ int launch_copy_picture(const FrameDev &f, const PlaneSet &dst, const PlaneSet &
     return f.nplanes;
 }
 
+// Cropped copy-out (ohcu_slot_output_cropped): the window of every plane, packed without row
+// gaps into one device buffer that crosses the bus as linear copies.  What the reference does
+// with a pointer offset (hevc_refs.c:335-341) and one memcpy per row (openhevc.c:722-735).
+// One CTA per 4 rows of a plane, a warp per row; 16-byte loads and stores when the source
+// window and the row length allow it, else sample by sample.
+struct CropPlane { const uint8_t *src; uint8_t *dst; int pitch, wbytes, rows; };
+struct CropArgs { CropPlane pl[3]; int nplanes; int cta0[4]; };
+
+__global__ void __launch_bounds__(128) crop_pack_kernel(const CropArgs a)
+{
+    int c = 0;
+    while (c + 1 < a.nplanes && (int)blockIdx.x >= a.cta0[c + 1]) c++;
+    const CropPlane pl = a.pl[c];
+    const int y = (blockIdx.x - a.cta0[c]) * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (y >= pl.rows) return;
+    const uint8_t *s = pl.src + (size_t)y * pl.pitch;
+    uint8_t *d = pl.dst + (size_t)y * pl.wbytes;
+    if ((((uintptr_t)s | (uintptr_t)d | (uintptr_t)pl.wbytes) & 15) == 0) {
+        for (int i = lane; i < pl.wbytes / 16; i += 32) ((uint4 *)d)[i] = __ldcs((const uint4 *)s + i);
+    } else {
+        // bytes up to the first 4-byte boundary of the destination, whole words after that
+        // (funnel-shifted from the two source words they straddle), then the tail
+        int i = min((int)(-(uintptr_t)d & 3), pl.wbytes);
+        if (lane < i) d[lane] = s[lane];
+        const int nw = (pl.wbytes - i) >> 2;
+        const uint8_t *sw = s + i;
+        const int sh = (int)((uintptr_t)sw & 3) * 8;
+        const uint32_t *sa = (const uint32_t *)(sw - ((uintptr_t)sw & 3));
+        for (int k = lane; k < nw; k += 32) {
+            const uint32_t lo = sa[k], hi = sh ? sa[k + 1] : 0;
+            ((uint32_t *)(d + i))[k] = __funnelshift_r(lo, hi, sh);
+        }
+        const int t0 = i + 4 * nw;
+        if (t0 + lane < pl.wbytes) d[t0 + lane] = s[t0 + lane];
+    }
+}
+
+int launch_crop_pack(const PlaneSet &pic, int nplanes, int P, const int left[3], const int top[3], const int w[3],
+                     const int h[3], uint8_t *const dst[3], cudaStream_t st)
+{
+    CropArgs a{};
+    a.nplanes = nplanes;
+    int n = 0;
+    for (int c = 0; c < nplanes; c++) {
+        a.pl[c].src = pic.p[c] + (ptrdiff_t)top[c] * pic.pitch[c] + (ptrdiff_t)left[c] * P;
+        a.pl[c].dst = dst[c]; a.pl[c].pitch = pic.pitch[c]; a.pl[c].wbytes = w[c] * P; a.pl[c].rows = h[c];
+        a.cta0[c] = n;
+        n += (h[c] + 3) / 4;
+    }
+    a.cta0[nplanes] = n;
+    if (n) crop_pack_kernel<<<n, 128, 0, st>>>(a);
+    return n ? 1 : 0;
+}
+
 __global__ void l2_flush_kernel(uint4 *buf, size_t n)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -230,6 +230,21 @@ int ohcu_slot_sync(ohcu_ctx *ctx, int slot);   /* replaces ff_thread_await_progr
  * of a row and the start of the next then hold halo samples.                          */
 int ohcu_slot_pitch(const ohcu_ctx *ctx, int plane, ptrdiff_t *pitch);
 
+/* ---- output: cropped copy-out.
+ * Replaces the conformance-window offset of ff_hevc_output_frame (hevc_refs.c:335-341:
+ * data[i] += (left >> hshift << pixel_shift) + (top >> vshift) * linesize[i]) followed by
+ * oh_output_cropped_cpy (openhevc.c:662-742: one memcpy per row into the caller's TIGHT
+ * planes, row length = cropped width in bytes).  A kernel packs the window of the three
+ * planes into one tight device buffer, which then crosses the bus as one linear copy per
+ * plane (one in all when the caller's planes follow each other in memory) instead of a
+ * pitched 2-D copy.  left/top/width/height are luma samples; chroma uses them shifted by the
+ * format's subsampling, so they must be multiples of it.  planes[c] receives
+ * (height >> vs) rows of (width >> hs) samples with no gap between rows.               */
+typedef struct { int32_t left, top, width, height; } ohcu_crop;
+int ohcu_slot_output_cropped(ohcu_ctx *ctx, int slot, const ohcu_crop *crop, uint8_t *const planes[3]);
+/* Asynchronous variant into caller-pinned memory; completes at ohcu_slot_sync. */
+int ohcu_slot_output_cropped_async(ohcu_ctx *ctx, int slot, const ohcu_crop *crop, uint8_t *const planes[3]);
+
 /* ======================================================================== */
 /* Per-frame work lists                                                     */
 /* ======================================================================== */

@@ -533,3 +533,19 @@ int or_boundary_strengths(const oh_bs_job *job)
     free(g);
     return 0;
 }
+
+/* ---------------------------------------------------------------- cropped copy-out
+ * hevc_refs.c:335-341: data[i] += (left >> hshift << pixel_shift) + (top >> vshift) * linesize[i];
+ * openhevc.c:722-735: for every row, memcpy(dst + y * dst_stride, src + y * src_stride, dst_stride)
+ * with dst_stride = the cropped width in bytes (set_cropped_dim_from_avframe, openhevc.c:463). */
+void or_output_cropped(const uint8_t *const src[3], const ptrdiff_t stride[3], int nplanes, int pixel_shift,
+                       int hshift, int vshift, int left, int top, int width, int height, uint8_t *const dst[3])
+{
+    for (int i = 0; i < nplanes; i++) {
+        const int hs = i ? hshift : 0, vs = i ? vshift : 0;
+        const uint8_t *s = src[i] + ((ptrdiff_t)(left >> hs) << pixel_shift) + (ptrdiff_t)(top >> vs) * stride[i];
+        const size_t row = (size_t)(width >> hs) << pixel_shift;
+        for (int y = 0; y < height >> vs; y++)
+            memcpy(dst[i] + y * row, s + y * stride[i], row);
+    }
+}

@@ -78,6 +78,14 @@ typedef struct oh_bs_job {
 int or_boundary_strengths(const oh_bs_job *job);
 int ohref_boundary_strengths(const oh_bs_job *job);
 
+/* Cropped copy-out: the conformance-window offset of ff_hevc_output_frame (hevc_refs.c:335-341)
+ * and the row-by-row memcpy into tight planes of oh_output_cropped_cpy_from_layer
+ * (openhevc.c:722-735).  Parity unpinned: openhevc.c needs a whole opened decoder to call; the
+ * restatement is a pointer offset and a memcpy per row and is also checked against array
+ * slicing in tests/test_output.py.  src strides in bytes; dst planes tight. */
+void or_output_cropped(const uint8_t *const src[3], const ptrdiff_t stride[3], int nplanes, int pixel_shift,
+                       int hshift, int vshift, int left, int top, int width, int height, uint8_t *const dst[3]);
+
 /* returns 0, or a negative OHCU_E* code for malformed jobs */
 int or_replay_frame(const oh_frame_job *job);
 int ohref_replay_frame(const oh_frame_job *job);

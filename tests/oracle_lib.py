@@ -173,6 +173,25 @@ class Lib:
             raise RuntimeError(f"{self.which} boundary_strengths failed: {rc}")
         return vbs, hbs
 
+    def output_cropped(self, planes, crop, hshift, vshift):
+        """or_output_cropped: the (left, top, width, height) window of a picture as tight planes
+        (hevc_refs.c:335-341 + openhevc.c:722-735).  Oracle only (openhevc.c needs a decoder)."""
+        fn = self.lib.or_output_cropped
+        fn.restype = None
+        fn.argtypes = [C.POINTER(C.c_void_p * 3), C.POINTER(C.c_ssize_t * 3)] + [_I] * 8 + [C.POINTER(C.c_void_p * 3)]
+        left, top, width, height = [int(v) for v in crop]
+        src, strides, dst = (C.c_void_p * 3)(), (C.c_ssize_t * 3)(), (C.c_void_p * 3)()
+        out = []
+        for i, p in enumerate(planes):
+            assert p.strides[1] == p.itemsize
+            hs, vs = (hshift, vshift) if i else (0, 0)
+            src[i] = p.ctypes.data; strides[i] = p.strides[0]
+            out.append(np.zeros((height >> vs, width >> hs), p.dtype))
+            dst[i] = out[-1].ctypes.data
+        fn(C.byref(src), C.byref(strides), len(planes), planes[0].itemsize - 1, hshift, vshift, left, top, width, height,
+           C.byref(dst))
+        return out
+
     def replay(self, job, refs, out_init=None, stages=0, use_deblock=True, use_sao=True):
         """Run one frame job.  refs = list (DPB slots) of pictures (lists of 2-D arrays).
         Returns the reconstructed picture as a list of arrays."""
