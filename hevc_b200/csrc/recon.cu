@@ -824,6 +824,74 @@ __device__ __forceinline__ void mc_cell(const FrameDev &f, int c, uint32_t orgA,
         for (int k = 0; k < OW / 2; k++) epi_pair(e, cur[r][k], prev[r][k], tw + r * tpitch + k);
 }
 
+// ---- PU records and the cell map of one CTB (phase 1a of recon_kernel; the preparation of mc_kernel):
+// four threads per PU: thread `sub` prepares the window of kind `sub` (list slot sub & 1, luma / chroma
+// sub >> 1) and the epilogue constants of plane `sub`, and enters the PU into a quarter of its cells of
+// the cell map; 64 PUs per pass.
+__device__ __forceinline__ void build_pu_records(const FrameDev &f, PuRec *recs, uint8_t *cmap, int p0, int np, int cx0, int cy0,
+                                                 int bd, int tid)
+{
+    const int sub = tid & 3;
+#pragma unroll 1
+    for (int base = 0; base < np; base += RC_THREADS / 4) {
+        const int p = base + (tid >> 2);
+        if (p < np) {
+            const ohcu_pu pu = load_pu(f.pus + p0 + p);
+            const ohcu_slice_tab &sl = f.slices[pu.slice];
+            const bool bi = pu.pred_flag == OHCU_PF_BI;
+            PuRec &rc = recs[p];
+            const int lA = (pu.pred_flag & 1) ? 0 : 1;
+            const int x4 = (pu.x0 - cx0) >> 2, y4 = (pu.y0 - cy0) >> 2, w4 = pu.w >> 2, h4 = pu.h >> 2;
+            if (sub == 0)
+                rc.rect = (uint32_t)(x4 | (y4 << 4) | (w4 << 8) | (h4 << 13) | ((bi ? 1 : 0) << 18));
+            {
+                const int s = sub & 1, pt = sub >> 1;
+                uint32_t org = 0, par = 0;
+                if ((s == 0 || bi) && (pt == 0 || f.nplanes == 3)) {
+                    const int l = s ? 1 : lA;
+                    const WinGeom g = win_geom(f, pu, l, pt == 0);
+                    const int slot = sl.ref_slot[l][(l ? pu.ref_idx[1] : pu.ref_idx[0]) & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1);
+                    org = ((uint32_t)g.x0 & 0xffffu) | ((uint32_t)g.y0 << 16);
+                    par = (uint32_t)slot | ((uint32_t)g.mx << 8) | ((uint32_t)g.my << 11);
+                }
+                rc.org[s][pt] = org;
+                rc.par[s][pt] = par;
+            }
+            if (sub < 3) {                                 // epilogue constants of plane `sub` (see Epi)
+                const int c = sub;
+                const bool wflag = sl.weight_flag != 0;
+                const int denom = c ? sl.chroma_log2_weight_denom : sl.luma_log2_weight_denom;
+                int wx[2], ox[2];
+#pragma unroll
+                for (int l = 0; l < 2; l++) {
+                    const int ri = (l ? pu.ref_idx[1] : pu.ref_idx[0]) & (OHCU_MAX_REFS - 1);
+                    wx[l] = c ? sl.chroma_weight[l][ri][c - 1] : sl.luma_weight[l][ri];
+                    ox[l] = (c ? sl.chroma_offset[l][ri][c - 1] : sl.luma_offset[l][ri]) * (1 << (bd - 8));
+                }
+                int wA, wB = 0, add, sh, post = 0;
+                if (!bi) {
+                    if (!wflag) { wA = 1; sh = 14 - bd; add = 1 << (13 - bd); }
+                    else { wA = wx[lA]; sh = denom + 14 - bd; add = 1 << (sh - 1); post = ox[lA]; }
+                } else {
+                    if (!wflag) { wA = 1; wB = 1; sh = 15 - bd; add = 1 << (14 - bd); }
+                    else {
+                        const int log2Wd = denom + 14 - bd;
+                        wA = wx[1]; wB = wx[0]; sh = log2Wd + 1; add = (ox[0] + ox[1] + 1) * (1 << log2Wd);
+                    }
+                }
+                rc.epi[c][0] = ((uint32_t)wA & 0xffffu) | ((uint32_t)wB << 16);
+                rc.epi[c][1] = (uint32_t)add;
+                rc.epi[c][2] = ((uint32_t)sh & 0xffffu) | ((uint32_t)post << 16);
+            }
+            const int inv = fastinv(w4);
+            for (int i = sub; i < w4 * h4; i += 4) {
+                const int yy = fastdiv(i, inv), xx = i - yy * w4;
+                cmap[(y4 + yy) * CMAP_STRIDE + x4 + xx] = (uint8_t)p;
+            }
+        }
+    }
+}
+
 // ================================================================= the kernel
 __device__ __forceinline__ void unpack_epi(const uint32_t (&w)[3], int bd, Epi &e)
 {
@@ -890,6 +958,7 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
     const int2 trange = do_res ? f.ctb_tu_range[ctb] : make_int2(0, 0);
     const int t0 = trange.x, nt = min(trange.y, MAX_CTB_TUS);
 
+    if (!do_mc && nt == 0) return;            // nothing to add to this CTB
     // ---- phase 0: start from the current picture where this launch does not produce every sample
     if (!do_mc || !covered) {
         for (int c = 0; c < f.nplanes; c++) {
@@ -948,65 +1017,7 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
         // ---- 1a. four threads per PU: thread `sub` prepares the window of kind `sub` (list slot
         //      sub & 1, luma / chroma sub >> 1) and the epilogue constants of plane `sub`, and
         //      enters the PU into a quarter of its cells of the cell map; 64 PUs per pass.
-        const int sub = tid & 3;
-#pragma unroll 1
-        for (int base = 0; base < np; base += RC_THREADS / 4) {
-            const int p = base + (tid >> 2);
-            if (p < np) {
-                const ohcu_pu pu = load_pu(f.pus + p0 + p);
-                const ohcu_slice_tab &sl = f.slices[pu.slice];
-                const bool bi = pu.pred_flag == OHCU_PF_BI;
-                PuRec &rc = recs[p];
-                const int lA = (pu.pred_flag & 1) ? 0 : 1;
-                const int x4 = (pu.x0 - cx0) >> 2, y4 = (pu.y0 - cy0) >> 2, w4 = pu.w >> 2, h4 = pu.h >> 2;
-                if (sub == 0)
-                    rc.rect = (uint32_t)(x4 | (y4 << 4) | (w4 << 8) | (h4 << 13) | ((bi ? 1 : 0) << 18));
-                {
-                    const int s = sub & 1, pt = sub >> 1;
-                    uint32_t org = 0, par = 0;
-                    if ((s == 0 || bi) && (pt == 0 || f.nplanes == 3)) {
-                        const int l = s ? 1 : lA;
-                        const WinGeom g = win_geom(f, pu, l, pt == 0);
-                        const int slot = sl.ref_slot[l][(l ? pu.ref_idx[1] : pu.ref_idx[0]) & (OHCU_MAX_REFS - 1)] & (OHCU_MAX_DPB - 1);
-                        org = ((uint32_t)g.x0 & 0xffffu) | ((uint32_t)g.y0 << 16);
-                        par = (uint32_t)slot | ((uint32_t)g.mx << 8) | ((uint32_t)g.my << 11);
-                    }
-                    rc.org[s][pt] = org;
-                    rc.par[s][pt] = par;
-                }
-                if (sub < 3) {                                 // epilogue constants of plane `sub` (see Epi)
-                    const int c = sub;
-                    const bool wflag = sl.weight_flag != 0;
-                    const int denom = c ? sl.chroma_log2_weight_denom : sl.luma_log2_weight_denom;
-                    int wx[2], ox[2];
-#pragma unroll
-                    for (int l = 0; l < 2; l++) {
-                        const int ri = (l ? pu.ref_idx[1] : pu.ref_idx[0]) & (OHCU_MAX_REFS - 1);
-                        wx[l] = c ? sl.chroma_weight[l][ri][c - 1] : sl.luma_weight[l][ri];
-                        ox[l] = (c ? sl.chroma_offset[l][ri][c - 1] : sl.luma_offset[l][ri]) * (1 << (bd - 8));
-                    }
-                    int wA, wB = 0, add, sh, post = 0;
-                    if (!bi) {
-                        if (!wflag) { wA = 1; sh = 14 - bd; add = 1 << (13 - bd); }
-                        else { wA = wx[lA]; sh = denom + 14 - bd; add = 1 << (sh - 1); post = ox[lA]; }
-                    } else {
-                        if (!wflag) { wA = 1; wB = 1; sh = 15 - bd; add = 1 << (14 - bd); }
-                        else {
-                            const int log2Wd = denom + 14 - bd;
-                            wA = wx[1]; wB = wx[0]; sh = log2Wd + 1; add = (ox[0] + ox[1] + 1) * (1 << log2Wd);
-                        }
-                    }
-                    rc.epi[c][0] = ((uint32_t)wA & 0xffffu) | ((uint32_t)wB << 16);
-                    rc.epi[c][1] = (uint32_t)add;
-                    rc.epi[c][2] = ((uint32_t)sh & 0xffffu) | ((uint32_t)post << 16);
-                }
-                const int inv = fastinv(w4);
-                for (int i = sub; i < w4 * h4; i += 4) {
-                    const int yy = fastdiv(i, inv), xx = i - yy * w4;
-                    cmap[(y4 + yy) * CMAP_STRIDE + x4 + xx] = (uint8_t)p;
-                }
-            }
-        }
+        build_pu_records(f, recs, cmap, p0, np, cx0, cy0, bd, tid);
         __syncthreads();
         RC_MARK(2);
         sort_tus();
@@ -1173,6 +1184,89 @@ int rc_profile_read(unsigned long long *out, int reset)
 extern "C" int ohcu_rc_profile(unsigned long long *out, int reset) { return rc_profile_read(out, reset); }
 #endif
 
+// ================================================================= prediction alone
+// mc_kernel: the prediction samples of one CTB written straight to the job's picture.  Same
+// records, cell map and cell code as phase 1 of recon_kernel, without the CTB tile, the TB
+// lists and the barriers around them: 7.4 KB of static shared memory per CTA, so the L1 the
+// windows are read through keeps most of the SM's 256 KB, and only the filter code is resident
+// in the instruction caches.  launch_recon runs it ahead of recon_kernel(flags = residual),
+// which then starts from the picture (its phase 0) in the CTBs that hold coded blocks.
+#ifndef MC_MINB
+#define MC_MINB 4
+#endif
+template <bool HIGH, int OW, int OH>
+__device__ __forceinline__ void store_cell(uint8_t *dst, int pitch, const uint32_t (&o)[OH][OW / 2])
+{
+#pragma unroll
+    for (int r = 0; r < OH; r++) {
+        uint8_t *row = dst + (size_t)r * pitch;
+        if (HIGH) {
+            if (OW == 4) *(uint2 *)row = make_uint2(o[r][0], o[r][1]);
+            else *(uint32_t *)row = o[r][0];
+        } else {
+            if (OW == 4) *(uint32_t *)row = __byte_perm(o[r][0], o[r][1], 0x6420);
+            else *(uint16_t *)row = (uint16_t)__byte_perm(o[r][0], 0, 0x4420);
+        }
+    }
+}
+
+template <bool HIGH, int NT, int OW, int OH>
+__device__ __forceinline__ void mc_cell_out(const FrameDev &f, int c, const PuRec &rc, int pt, bool bi, int ccol, int crow, int bd,
+                                            uint8_t *dst, int pitch)
+{
+    Epi e;
+    const uint32_t ew[3] = {rc.epi[c][0], rc.epi[c][1], rc.epi[c][2]};
+    unpack_epi(ew, bd, e);
+    uint32_t o[OH][OW / 2];
+    mc_cell<HIGH, NT, OW, OH>(f, c, rc.org[0][pt], rc.par[0][pt], rc.org[1][pt], rc.par[1][pt], bi, ccol, crow, bd - 8, e, &o[0][0],
+                              OW / 2);
+    store_cell<HIGH, OW, OH>(dst, pitch, o);
+}
+
+template <bool HIGH>
+__global__ void __launch_bounds__(RC_THREADS, MC_MINB) mc_kernel(const __grid_constant__ FrameDev f)
+{
+    __shared__ __align__(16) PuRec recs[MAX_CTB_PUS];
+    __shared__ __align__(16) uint8_t cmap[CMAP_STRIDE * CMAP_STRIDE];
+    constexpr int P = HIGH ? 2 : 1;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int ctb = blockIdx.x;
+    const int ctbx = ctb % f.ctb_w, ctby = ctb / f.ctb_w;
+    const int cs = 1 << f.log2_ctb;
+    const int cx0 = ctbx << f.log2_ctb, cy0 = ctby << f.log2_ctb;
+    const int bd = f.bd;
+    const int2 prange = f.ctb_pu_range[ctb];
+    const int p0 = prange.x, np = min(prange.y & 0xffffff, MAX_CTB_PUS);
+    if (np == 0) return;
+    if (tid < CMAP_STRIDE * CMAP_STRIDE / 4) ((uint32_t *)cmap)[tid] = 0xffffffffu;
+    __syncthreads();
+    build_pu_records(f, recs, cmap, p0, np, cx0, cy0, bd, tid);
+    __syncthreads();
+    // one thread per 4x4 cell (and its chroma); a warp covers 8 x 4 cells of a 64x64 CTB
+    int cx, cy;
+    if (f.log2_ctb == 6) { cx = (warp & 1) * 8 + (lane & 7); cy = (warp >> 1) * 4 + (lane >> 3); }
+    else { const int n4 = cs >> 2; cy = tid >> (f.log2_ctb - 2); cx = tid & (n4 - 1); }
+    const int p = (cy << 2) < cs ? cmap[cy * CMAP_STRIDE + cx] : 0xff;
+    if (p == 0xff) return;
+    const PuRec &rc = recs[p];
+    const uint32_t rect = rc.rect;
+    const int ccx = cx - (int)(rect & 15), ccy = cy - (int)((rect >> 4) & 15);
+    const bool pbi = (rect >> 18) & 1;
+    const int x = cx0 + 4 * cx, y = cy0 + 4 * cy;                                   // luma position of the cell
+    mc_cell_out<HIGH, 8, 4, 4>(f, 0, rc, 0, pbi, ccx * 4, ccy * 4, bd, f.work.p[0] + (size_t)y * f.work.pitch[0] + (size_t)x * P,
+                               f.work.pitch[0]);
+    if (f.nplanes == 3) {
+        const int hs = f.hs, vs = f.vs;
+#pragma unroll 1
+        for (int c = 1; c <= 2; c++) {
+            uint8_t *dst = f.work.p[c] + (size_t)(y >> vs) * f.work.pitch[c] + (size_t)(x >> hs) * P;
+            if (hs && vs) mc_cell_out<HIGH, 4, 2, 2>(f, c, rc, 1, pbi, ccx * 2, ccy * 2, bd, dst, f.work.pitch[c]);
+            else if (hs) mc_cell_out<HIGH, 4, 2, 4>(f, c, rc, 1, pbi, ccx * 2, ccy * 4, bd, dst, f.work.pitch[c]);
+            else mc_cell_out<HIGH, 4, 4, 4>(f, c, rc, 1, pbi, ccx * 4, ccy * 4, bd, dst, f.work.pitch[c]);
+        }
+    }
+}
+
 // shared memory of one CTA without the residual area
 static size_t recon_fixed_smem(int log2_ctb, int nplanes, int hs, int vs, int cfi)
 {
@@ -1217,6 +1311,23 @@ int launch_recon(const FrameDev &f, int flags, cudaStream_t st)
         attr_set = true;
     }
     const int nctb = f.ctb_w * f.ctb_h;
+    // prediction and residual as two launches (mc_kernel, then recon_kernel from its phase 0);
+    // OHCU_FUSED=1 keeps both in recon_kernel (measurement)
+    static const bool fused = getenv("OHCU_FUSED") && atoi(getenv("OHCU_FUSED")) != 0;
+    if (!fused) {
+        int n = 0;
+        if ((flags & 1) && f.n_pu > 0) {
+            if (f.bd > 8) mc_kernel<true><<<nctb, RC_THREADS, 0, st>>>(f);
+            else          mc_kernel<false><<<nctb, RC_THREADS, 0, st>>>(f);
+            n++;
+        }
+        if ((flags & 2) && f.n_tu > 0) {
+            if (f.bd > 8) recon_kernel<true><<<nctb, RC_THREADS, smem, st>>>(f, 2, hu);
+            else          recon_kernel<false><<<nctb, RC_THREADS, smem, st>>>(f, 2, hu);
+            n++;
+        }
+        return n;
+    }
     if (f.bd > 8) recon_kernel<true><<<nctb, RC_THREADS, smem, st>>>(f, flags, hu);
     else          recon_kernel<false><<<nctb, RC_THREADS, smem, st>>>(f, flags, hu);
     return 1;
