@@ -10,7 +10,7 @@ reconstruction with weighted prediction.
   value        whole-job Mpixel/s (luma W*H*frames / s), work lists resident in HBM
   e2e          same metric through the C ABI with HOST buffers: list upload from pinned
                memory, kernels, and the reconstructed picture copied back to pinned memory
-  roofline     the dominant kernel (recon_kernel: MC + residual) against the measured HBM peak
+  roofline     the dominant kernel (mc_kernel: motion compensation) against the measured HBM peak
   cpu_baseline the reference's own C hevcdsp path (oracle/_ref) on the host cores
   --impl reference   times that CPU path alone, same metric / config
 
@@ -44,7 +44,7 @@ WORKLOAD_NAMES = {
     "8k": "7680x4320 Main10 4:2:0, 64 independent frames sharded across GPUs (BASELINE configs[4])",
 }
 N_DISTINCT = 4        # distinct synthetic frames; jobs reuse them round-robin
-# dram__bytes_read.sum + dram__bytes_write.sum of one recon_kernel launch, from the committed
+# dram__bytes_read.sum + dram__bytes_write.sum of one mc_kernel launch, from the committed
 # `ncu --set full` capture of this same command (never measured inside a timed run)
 NCU_TRAFFIC = {"4k": 70551552}
 NCU_TRAFFIC_SOURCE = "profiles/r01_v10_ncu_kernels.txt (61.54 MB read + 9.01 MB write; the reference pictures stay in L2)"
@@ -101,10 +101,11 @@ def derived_bs_inputs(jobs):
 
 def algorithmic_bytes(job):
     """per kernel, bytes that must move once.
-    recon       every reference sample a PU needs read once + every sample written once
-                + the int16 coefficients of the coded blocks read once (fused: no RMW)
+    mc          every reference sample a PU needs read once + every predicted sample written once
+    residual    the int16 coefficients of the coded blocks read once + the samples of the coded
+                blocks read and written once
     loopfilter  the reconstructed picture read once + the filtered picture written once
-    pipeline    recon + loopfilter.  pipeline_survey is SURVEY's figure for the layout it
+    pipeline    mc + residual + loopfilter.  pipeline_survey is SURVEY's figure for the layout it
                 assumed (MC, residual RMW, deblock and SAO as four passes)."""
     sp = job.sp
     P = 2 if sp.bit_depth > 8 else 1
@@ -117,8 +118,8 @@ def algorithmic_bytes(job):
     nref = np.where(job.pus["pred_flag"] == 3, 2, 1)
     mc = int((area * (1 + nref)).sum() * planes_factor * P)        # read each ref sample once + write pred
     coded = int((1 << (2 * job.tus["log2_size"].astype(np.int64))).sum())
-    recon = mc + coded * 2
-    return {"recon": recon, "loopfilter": 2 * S, "pad": 0, "pipeline": recon + 2 * S,
+    residual = coded * 2 + coded * P * 2
+    return {"mc": mc, "residual": residual, "loopfilter": 2 * S, "pad": 0, "pipeline": mc + residual + 2 * S,
             "pipeline_survey": mc + coded * 2 + coded * P * 2 + 4 * S, "S": S}
 
 
@@ -365,13 +366,14 @@ def run_ours(args, rank, world):
     value = total_frames * px / (ms_resident * 1e-3) / 1e6
     e2e_value = total_frames * px / (ms_e2e * 1e-3) / 1e6
     ab = algorithmic_bytes(jobs[0])
-    # stage events: [1] after recon_kernel (MC + residual fused), [3] after loopfilter_kernel
+    # stage events: [1] after mc_kernel, [2] after residual_kernel, [3] after loopfilter_kernel
     # (deblock + SAO fused), [4] after the halo fill
-    rc_ms = float(stage_ms[abi.STAGE_MC] + stage_ms[abi.STAGE_RESIDUAL])
+    mc_ms = float(stage_ms[abi.STAGE_MC])
+    res_ms = float(stage_ms[abi.STAGE_RESIDUAL])
     lf_ms = float(stage_ms[abi.STAGE_DEBLOCK])
     pad_ms = float(stage_ms[abi.STAGE_SAO])
-    achieved = ab["recon"] / (rc_ms * 1e-3) / 1e9
-    kern = [("recon", rc_ms), ("loopfilter", lf_ms), ("pad", pad_ms)]
+    achieved = ab["mc"] / (mc_ms * 1e-3) / 1e9
+    kern = [("mc", mc_ms), ("residual", res_ms), ("loopfilter", lf_ms), ("pad", pad_ms)]
     line = {
         "metric": "Mpixel/s reconstructed per B200 (4K Main10); HBM GB/s vs peak", "value": round(value, 1),
         "unit": "Mpixel/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -391,13 +393,13 @@ def run_ours(args, rank, world):
         "e2e": {"value": round(e2e_value, 1), "unit": "Mpixel/s", "h2d_bytes_per_step": int(h2d * B),
                 "d2h_bytes_per_step": int(d2h * B), "frames_per_s": round(total_frames / (ms_e2e * 1e-3), 1),
                 "host_ms_per_step": round(t_host / args.steps, 3), "host_threads": max(1, min(args.host_threads, B))},
-        "roofline": {"bound": "hbm", "kernel": "recon_kernel (motion compensation + residual, fused)",
+        "roofline": {"bound": "hbm", "kernel": "mc_kernel (motion compensation: qpel / epel, uni / bi / weighted)",
                      "achieved": round(achieved, 1),
                      "peak": hbm_peak, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "unit": "GB/s",
                      "frac": round(achieved / hbm_peak, 4),
                      "traffic": NCU_TRAFFIC.get(args.workload),
                      "traffic_source": NCU_TRAFFIC_SOURCE if args.workload in NCU_TRAFFIC else None,
-                     "algorithmic_bytes_per_launch": int(ab["recon"]), "ms_per_launch": round(rc_ms, 4)},
+                     "algorithmic_bytes_per_launch": int(ab["mc"]), "ms_per_launch": round(mc_ms, 4)},
         "kernels": {name: {"ms": round(ms, 4), "algorithmic_mb": round(ab[name] / 1e6, 2),
                            "gbs": round(ab[name] / (ms * 1e-3) / 1e9, 1) if ms > 0 and ab[name] else None}
                     for name, ms in kern},

@@ -62,7 +62,7 @@ constexpr size_t SL_BYTES = 4 * 6 * 64 + 2 * 6;      // ScalingList, hevc_ps.h:6
 
 struct Job {
     cudaStream_t stream = nullptr;
-    cudaStream_t side = nullptr;      // the bs derivation runs beside recon_kernel (it needs only the lists)
+    cudaStream_t side = nullptr;      // the bs derivation runs beside mc_kernel and residual_kernel (it needs only the lists)
     cudaEvent_t fork = nullptr, join = nullptr;
     cudaEvent_t done = nullptr;
     cudaEvent_t ev[OHCU_NUM_STAGES + 1] = {};
@@ -1073,7 +1073,7 @@ extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int 
 #define LAUNCHED(call) do { n = (call); if (n < 0) return fail(OHCU_EINVAL, "launch refused"); total += n; \
         CU(cudaGetLastError()); } while (0)
     STAGE_EVENT(0);
-    // boundary strengths derived from the lists (bs.cu): on the job's side stream, beside recon_kernel;
+    // boundary strengths derived from the lists (bs.cu): on the job's side stream, beside mc_kernel and residual_kernel;
     // it starts after everything already queued on the job's stream (staging copies, the previous launch)
     const bool derive = (lf_flags & 1) && f.bs_ctb_flags;
     if (derive) {
@@ -1084,9 +1084,10 @@ extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int 
     }
     // samples this launch does not predict keep the slot's current content
     if ((!(stages & 1) || !j.all_covered) && lf_flags) LAUNCHED(launch_copy_picture(f, f.work, f.out, st));
-    // MC and the residual run fused (recon.cu); stage 1 carries their time
-    LAUNCHED(launch_recon(f, stages & 3, st));
+    // prediction (mc_kernel), then the coded blocks on top of it (residual_kernel), recon.cu
+    LAUNCHED(launch_recon(f, stages & 1, st));
     STAGE_EVENT(1);
+    LAUNCHED(launch_recon(f, stages & 2, st));
     STAGE_EVENT(2);
     // deblocking and SAO run fused (loopfilter.cu); stage 3 carries their time
     if (derive) CU(cudaStreamWaitEvent(st, j.join, 0));

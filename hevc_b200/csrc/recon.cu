@@ -1,11 +1,15 @@
-// recon.cu — fused inter reconstruction of one picture: motion compensation + residual.
+// recon.cu — inter reconstruction of one picture: motion compensation, then the residual.
 //
-// One CTA (256 threads) owns one CTB.  It builds the CTB's prediction in a shared-memory
-// tile (every inter PU: luma qpel 8-tap / chroma epel 4-tap, uni / bi / weighted), adds the
-// residual of every coded TB of the CTB into the same tile (inverse DCT 4..32 / DC / 4x4
-// DST / transform_skip / rdpcm / cross-component), and writes the CTB to the picture once
-// with full-line stores.  The prediction is never written to HBM and read back (the
-// transform_add RMW of the reference disappears).
+// Two kernels, one CTA (256 threads) per CTB in both.  mc_kernel writes the prediction of
+// every inter PU (luma qpel 8-tap / chroma epel 4-tap, uni / bi / weighted) straight to the
+// job's picture.  residual_kernel then takes the CTBs that hold coded blocks: the CTB enters
+// a shared-memory tile (the prediction was just written: L2 hits), the residual of every coded
+// TB is added into the tile (inverse DCT 4..32 / DC / 4x4 DST / transform_skip / rdpcm /
+// cross-component), and the CTB is written back once with full-line stores; the per-block
+// transform_add RMW of the reference disappears.  Until r01 v11 both lived in one kernel whose
+// tile never left the SM; its 170 KB of code thrashed the 32 KB instruction cache (26 % of
+// the warp stalls) and its shared memory took the L1 the windows are read through, and the two
+// launches are 10 % faster per picture (profiles/README.md, r01 v12).
 //
 // Replaces, per picture:
 //   hls_prediction_unit -> luma_mc_uni/bi, chroma_mc_uni/bi     hevcdec.c:1744-2049, 2250-2306
@@ -26,8 +30,8 @@
 //    taps {0,0,0,64,0,0,0,0} standing in for "no filter", which gives the reference's results
 //    exactly (64*x >> 6 == x, and (x << (14-BD)) is what (64*x) >> (BD-8) computes).
 //  * A cell reads its window STRAIGHT FROM THE DPB PLANE through L1 (ld.global.nc, 8-byte
-//    loads): neighbouring cells of a PU share their rows in L1, which here is the ~90 KB the
-//    CTAs' shared memory leaves.  The earlier form (one TMA box per PU and list into a
+//    loads): neighbouring cells of a PU share their rows in L1 (mc_kernel's CTAs hold 10 KB of
+//    shared memory each, so L1 keeps most of the SM's 256 KB).  The earlier form (one TMA box per PU and list into a
 //    shared-memory pool, cells run in rounds as the boxes land) spent more time on window
 //    geometry, scans, round bookkeeping and mbarrier waits than on filtering: 0.205 ms per 4K
 //    frame against 0.137 ms for this one (profiles/README.md, r01 v9 -> v10).
@@ -52,8 +56,7 @@ constexpr int POOL_UNIT = 128;               // granule of the residual area
 // scratch of one warp in the residual phase: one 32x32 int16 block
 struct WarpScratch { uint32_t w[32 * 40 / 2]; };   // 32 x (32 + 8) int16: idct_mma's pass-1 output
 // The residual area of a CTA: per-warp scratch, then the int16 coefficients of the CTB
-// (`units` x 128 B in all; a 64x64 4:2:0 CTB has 6144 coefficients).  During the prediction
-// phase the same bytes hold the PU records and the cell map.
+// (`units` x 128 B in all; a 64x64 4:2:0 CTB has 6144 coefficients).
 __host__ __device__ constexpr int coef_area(int units)          // int16, multiple of 8
 {
     return ((units * POOL_UNIT - RC_WARPS * (int)sizeof(WarpScratch)) / 2) & ~7;
@@ -824,7 +827,7 @@ __device__ __forceinline__ void mc_cell(const FrameDev &f, int c, uint32_t orgA,
         for (int k = 0; k < OW / 2; k++) epi_pair(e, cur[r][k], prev[r][k], tw + r * tpitch + k);
 }
 
-// ---- PU records and the cell map of one CTB (phase 1a of recon_kernel; the preparation of mc_kernel):
+// ---- PU records and the cell map of one CTB (the preparation of mc_kernel):
 // four threads per PU: thread `sub` prepares the window of kind `sub` (list slot sub & 1, luma / chroma
 // sub >> 1) and the epilogue constants of plane `sub`, and enters the PU into a quarter of its cells of
 // the cell map; 64 PUs per pass.
@@ -903,7 +906,8 @@ __device__ __forceinline__ void unpack_epi(const uint32_t (&w)[3], int bd, Epi &
     e.maxv = (1 << bd) - 1;
 }
 
-// flags: bit 0 run MC, bit 1 run the residual
+// residual_kernel: the coded blocks of one CTB added to the prediction mc_kernel left in the job's
+// picture.  CTBs without coded blocks leave at once.
 // -DRC_PROFILE: thread 0 of every CTA adds the cycles between phase marks to g_rc_prof (tools/rc_phases.py)
 #ifdef RC_PROFILE
 __device__ unsigned long long g_rc_prof[16];
@@ -913,7 +917,7 @@ __device__ unsigned long long g_rc_prof[16];
 #endif
 
 template <bool HIGH>
-__global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid_constant__ FrameDev f, int flags, int area_units)
+__global__ void __launch_bounds__(RC_THREADS, RC_MINB) residual_kernel(const __grid_constant__ FrameDev f, int area_units)
 {
 #ifdef RC_PROFILE
     long long rc_t = clock64();
@@ -926,14 +930,11 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
     const int cx0 = ctbx << f.log2_ctb, cy0 = ctby << f.log2_ctb;      // luma origin of the CTB
     const int bd = f.bd;
 
-    // ---- shared memory carve-up: [residual area | tile, TB lists, barrier].  The residual area (per-warp
-    //      scratch + the CTB's coefficients, `area_units` x 128 B) holds the PU records and the cell map
-    //      during the prediction phase.
+    // ---- shared memory carve-up: [residual area | tile, TB lists, barrier].  The residual area: per-warp
+    //      scratch + the CTB's coefficients, `area_units` x 128 B.
     uint8_t *pool = smem_raw;
     const int pool_bytes = area_units * POOL_UNIT;
     CtbTile tile;
-    PuRec *recs = (PuRec *)smem_raw;
-    uint8_t *cmap = smem_raw + MAX_CTB_PUS * sizeof(PuRec);                            // PU of every 4x4 cell, 0xff = none
     uint32_t *sp = (uint32_t *)(smem_raw + pool_bytes);
     // valid samples of this CTB per plane type (the picture may end inside it)
     const int vw0 = min(cs, f.pw[0] - cx0), vh0 = min(cs, f.ph[0] - cy0);
@@ -950,17 +951,12 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
     uint64_t *mbar = (uint64_t *)(((uintptr_t)sp + 7) & ~(uintptr_t)7);           sp += 4;                     // coefficient bulk copy
     WarpScratch *scratch2 = f.cfi == 3 ? (WarpScratch *)(((uintptr_t)sp + 15) & ~(uintptr_t)15) : nullptr;   // cross-component
 
-    const int2 prange = f.ctb_pu_range[ctb];
-    const int p0 = prange.x, np = min(prange.y & 0xffffff, MAX_CTB_PUS);
-    const bool covered = (prange.y >> 30) & 1;
-    const bool do_mc = (flags & 1) && np > 0;
-    const bool do_res = (flags & 2) && f.n_tu > 0;
-    const int2 trange = do_res ? f.ctb_tu_range[ctb] : make_int2(0, 0);
+    const int2 trange = f.ctb_tu_range[ctb];
     const int t0 = trange.x, nt = min(trange.y, MAX_CTB_TUS);
+    if (nt == 0) return;                      // nothing to add to this CTB
 
-    if (!do_mc && nt == 0) return;            // nothing to add to this CTB
-    // ---- phase 0: start from the current picture where this launch does not produce every sample
-    if (!do_mc || !covered) {
+    // ---- phase 0: the CTB's samples (the prediction, or whatever the picture holds) enter the tile
+    {
         for (int c = 0; c < f.nplanes; c++) {
             const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
             const uint8_t *plane = f.work.p[c] + (size_t)(cy0 >> vs) * f.work.pitch[c];
@@ -982,7 +978,6 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
     if (tid < 12) tu_cnt[tid] = 0;
     if (tid == 12) { tu_cnt[12] = 0x7fffffff; tu_cnt[13] = 0; tu_cnt[14] = 0; }
     if (tid == 0) mbar_init(mbar, 1);
-    if (tid < CMAP_STRIDE * CMAP_STRIDE / 4) ((uint32_t *)cmap)[tid] = 0xffffffffu;
     __syncthreads();
     RC_MARK(1);
 
@@ -1012,61 +1007,11 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
         }
     };
 
-    // ================================================================ phase 1: prediction
-    if (do_mc) {
-        // ---- 1a. four threads per PU: thread `sub` prepares the window of kind `sub` (list slot
-        //      sub & 1, luma / chroma sub >> 1) and the epilogue constants of plane `sub`, and
-        //      enters the PU into a quarter of its cells of the cell map; 64 PUs per pass.
-        build_pu_records(f, recs, cmap, p0, np, cx0, cy0, bd, tid);
-        __syncthreads();
-        RC_MARK(2);
-        sort_tus();
-        RC_MARK(4);
-
-        // ---- 1b. one thread per 4x4 cell (and its chroma).  A warp covers 8 x 4 cells of a 64x64 CTB.
-        int cx, cy;
-        if (f.log2_ctb == 6) { cx = (warp & 1) * 8 + (lane & 7); cy = (warp >> 1) * 4 + (lane >> 3); }
-        else { const int n4 = cs >> 2; cy = tid >> (f.log2_ctb - 2); cx = tid & (n4 - 1); }
-        const int p = (cy << 2) < cs ? cmap[cy * CMAP_STRIDE + cx] : 0xff;
-        if (p != 0xff) {
-            const int sh1 = bd - 8;                        // first-stage shift (template :2486)
-            const PuRec &rc = recs[p];
-            const uint32_t rect = rc.rect;
-            const int ccx = cx - (int)(rect & 15), ccy = cy - (int)((rect >> 4) & 15);
-            const bool pbi = (rect >> 18) & 1;
-            {
-                Epi e;
-                const uint32_t ew[3] = {rc.epi[0][0], rc.epi[0][1], rc.epi[0][2]};
-                unpack_epi(ew, bd, e);
-                uint32_t *tp = tile.p(0) + (cy * 4) * tile.pitch(0) + cx * 2;
-                mc_cell<HIGH, 8, 4, 4>(f, 0, rc.org[0][0], rc.par[0][0], rc.org[1][0], rc.par[1][0], pbi, ccx * 4, ccy * 4, sh1, e, tp,
-                                         tile.pitch(0));
-            }
-            if (f.nplanes == 3) {
-                const int hs = f.hs, vs = f.vs;
-                const int cw_ = 4 >> hs, ch = 4 >> vs;
-#pragma unroll 1
-                for (int c = 1; c <= 2; c++) {
-                    Epi e;
-                    const uint32_t ew[3] = {rc.epi[c][0], rc.epi[c][1], rc.epi[c][2]};
-                    unpack_epi(ew, bd, e);
-                    uint32_t *tp = tile.p(c) + (cy * ch) * tile.pitch(c) + ((cx * cw_) >> 1);
-                    const uint32_t oA = rc.org[0][1], pA = rc.par[0][1], oB = rc.org[1][1], pB = rc.par[1][1];
-                    if (hs && vs) mc_cell<HIGH, 4, 2, 2>(f, c, oA, pA, oB, pB, pbi, ccx * 2, ccy * 2, sh1, e, tp, tile.pitch(c));
-                    else if (hs) mc_cell<HIGH, 4, 2, 4>(f, c, oA, pA, oB, pB, pbi, ccx * 2, ccy * 4, sh1, e, tp, tile.pitch(c));
-                    else mc_cell<HIGH, 4, 4, 4>(f, c, oA, pA, oB, pB, pbi, ccx * 4, ccy * 4, sh1, e, tp, tile.pitch(c));
-                }
-            }
-        }
-        RC_MARK(13);
-    } else {
-        sort_tus();
-    }
+    sort_tus();
 
     RC_MARK(5);
     // ================================================================ phase 2: residual
-    // sparse coefficients: the first (position, level) pairs of the CTB are fetched while the
-    // other warps finish their cells
+    // sparse coefficients: the first (position, level) pairs of the CTB are fetched ahead of the barrier
     const bool sparse = nt > 0 && f.ctb_coef_range != nullptr;
     uint32_t pr[4] = {0xffffu, 0xffffu, 0xffffu, 0xffffu};
     if (sparse) {
@@ -1076,7 +1021,7 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) recon_kernel(const __grid
         for (int k = 0; k < 4; k++)
             if (k * RC_THREADS + tid < npair) pr[k] = __ldg(src + k * RC_THREADS + tid);
     }
-    __syncthreads();          // prediction complete: the pool is free
+    __syncthreads();
     RC_MARK(6);
     if (nt > 0) {
         // the CTB's coefficients sit in one arena range (TBs are appended CTB by CTB): one bulk
@@ -1185,12 +1130,13 @@ extern "C" int ohcu_rc_profile(unsigned long long *out, int reset) { return rc_p
 #endif
 
 // ================================================================= prediction alone
-// mc_kernel: the prediction samples of one CTB written straight to the job's picture.  Same
-// records, cell map and cell code as phase 1 of recon_kernel, without the CTB tile, the TB
-// lists and the barriers around them: 7.4 KB of static shared memory per CTA, so the L1 the
-// windows are read through keeps most of the SM's 256 KB, and only the filter code is resident
-// in the instruction caches.  launch_recon runs it ahead of recon_kernel(flags = residual),
-// which then starts from the picture (its phase 0) in the CTBs that hold coded blocks.
+// mc_kernel: the prediction samples of one CTB written straight to the job's picture.  PU records
+// and the cell map (build_pu_records), then one thread per 4x4 luma cell and its chroma; no tile, no
+// TB lists: 10 KB of static shared memory per CTA, so the L1 the windows are read through keeps
+// most of the SM's 256 KB and only the filter code is resident in the instruction caches (fused
+// with the residual in one kernel, 26 % of the warp stalls were instruction fetches).
+// launch_recon runs it ahead of residual_kernel, which starts from the picture (its phase 0) in
+// the CTBs that hold coded blocks.
 #ifndef MC_MINB
 #define MC_MINB 4
 #endif
@@ -1280,13 +1226,10 @@ static size_t recon_fixed_smem(int log2_ctb, int nplanes, int hs, int vs, int cf
     return words * 4 + (cfi == 3 ? RC_WARPS * sizeof(WarpScratch) + 16 : 0);
 }
 
-// Units (128 B) of the residual area: per-warp scratch + a full CTB of coefficients (it also holds
-// the PU records and the cell map of the prediction phase, which are smaller).
+// Units (128 B) of the residual area: per-warp scratch + a full CTB of coefficients.
 static int rc_area_units(int log2_ctb, int nplanes, int hs, int vs)
 {
     const int need = (1 << (2 * log2_ctb)) + (nplanes == 3 ? 2 * ((1 << (2 * log2_ctb)) >> (hs + vs)) : 0);
-    static_assert(MAX_CTB_PUS * sizeof(PuRec) + CMAP_STRIDE * CMAP_STRIDE <= RC_WARPS * sizeof(WarpScratch),
-                  "PU records + cell map must fit the residual area");
     return (RC_WARPS * (int)sizeof(WarpScratch) + 2 * need + POOL_UNIT - 1) / POOL_UNIT;
 }
 
@@ -1299,38 +1242,28 @@ int recon_sparse_ctb_coefs(int log2_ctb, int nplanes, int hs, int vs) { return c
 
 int launch_recon(const FrameDev &f, int flags, cudaStream_t st)
 {
-    if (!(flags & 3)) return 0;
-    if (!((flags & 1) && f.n_pu > 0) && !((flags & 2) && f.n_tu > 0)) return 0;
-    const int hu = rc_area_units(f.log2_ctb, f.nplanes, f.hs, f.vs);
-    const size_t smem = recon_smem_bytes(f, hu);
-    static bool attr_set = false;
-    if (!attr_set) {
-        if (cudaFuncSetAttribute(recon_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024) != cudaSuccess ||
-            cudaFuncSetAttribute(recon_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024) != cudaSuccess)
-            return -1;
-        attr_set = true;
-    }
     const int nctb = f.ctb_w * f.ctb_h;
-    // prediction and residual as two launches (mc_kernel, then recon_kernel from its phase 0);
-    // OHCU_FUSED=1 keeps both in recon_kernel (measurement)
-    static const bool fused = getenv("OHCU_FUSED") && atoi(getenv("OHCU_FUSED")) != 0;
-    if (!fused) {
-        int n = 0;
-        if ((flags & 1) && f.n_pu > 0) {
-            if (f.bd > 8) mc_kernel<true><<<nctb, RC_THREADS, 0, st>>>(f);
-            else          mc_kernel<false><<<nctb, RC_THREADS, 0, st>>>(f);
-            n++;
-        }
-        if ((flags & 2) && f.n_tu > 0) {
-            if (f.bd > 8) recon_kernel<true><<<nctb, RC_THREADS, smem, st>>>(f, 2, hu);
-            else          recon_kernel<false><<<nctb, RC_THREADS, smem, st>>>(f, 2, hu);
-            n++;
-        }
-        return n;
+    int n = 0;
+    if ((flags & 1) && f.n_pu > 0) {
+        if (f.bd > 8) mc_kernel<true><<<nctb, RC_THREADS, 0, st>>>(f);
+        else          mc_kernel<false><<<nctb, RC_THREADS, 0, st>>>(f);
+        n++;
     }
-    if (f.bd > 8) recon_kernel<true><<<nctb, RC_THREADS, smem, st>>>(f, flags, hu);
-    else          recon_kernel<false><<<nctb, RC_THREADS, smem, st>>>(f, flags, hu);
-    return 1;
+    if ((flags & 2) && f.n_tu > 0) {
+        const int hu = rc_area_units(f.log2_ctb, f.nplanes, f.hs, f.vs);
+        const size_t smem = recon_smem_bytes(f, hu);
+        static bool attr_set = false;
+        if (!attr_set) {
+            if (cudaFuncSetAttribute(residual_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024) != cudaSuccess ||
+                cudaFuncSetAttribute(residual_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024) != cudaSuccess)
+                return -1;
+            attr_set = true;
+        }
+        if (f.bd > 8) residual_kernel<true><<<nctb, RC_THREADS, smem, st>>>(f, hu);
+        else          residual_kernel<false><<<nctb, RC_THREADS, smem, st>>>(f, hu);
+        n++;
+    }
+    return n;
 }
 
 // ================================================================= per-entry test shims

@@ -6,5 +6,5 @@ for lib in "$@"; do
   OHCU_LIB=$lib python bench.py "${args[@]}" --no-cpu 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.readline()); k=d['kernels']
-print('$lib', 'frames/s', d['frames_per_s'], 'e2e', d['e2e']['frames_per_s'], 'recon', k['recon']['ms'], 'lf', k['loopfilter']['ms'], 'pad', k['pad']['ms'], d['parity_check'])"
+print('$lib', 'frames/s', d['frames_per_s'], 'e2e', d['e2e']['frames_per_s'], 'mc', k['mc']['ms'], 'res', k['residual']['ms'], 'lf', k['loopfilter']['ms'], 'pad', k['pad']['ms'], d['parity_check'])"
 done

@@ -13,7 +13,7 @@ python bench.py --coeffs levels --bs derived --copy-out packed --no-cpu 2>/dev/n
 cmd="python bench.py --steps 2 --warmup 1 --no-cpu --no-check --frames 4 --bs derived"
 $cmd > /dev/null 2>&1 || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $o/${tag}_launches.csv $cmd > $o/ncu1.log 2>&1
-for k in recon_kernel loopfilter_kernel bs_kernel; do
+for k in mc_kernel residual_kernel loopfilter_kernel bs_kernel; do
   ncu --set full --clock-control none --import-source on -k regex:$k -s 6 -c 1 -f -o $o/${tag}_$k $cmd > $o/ncu_$k.log 2>&1
 done
 ls -la $o | tail -20

@@ -1,4 +1,4 @@
-"""recon_kernel time per 4K frame with only MC, only the residual, both (CUDA events of the job's stream)."""
+"""mc_kernel + residual_kernel time per 4K frame with only MC, only the residual, both (CUDA events of the job's stream)."""
 import sys
 sys.path.insert(0, "."); sys.path.insert(0, "tests")
 import numpy as np
@@ -14,4 +14,4 @@ for stages in (1, 2, 3, 15):
     for i in range(12):
         ctx.launch(j, 2, stages=stages); ctx.sync(j)
         if i >= 2: acc += np.array(ctx.stage_ms(j))
-    print("stages", stages, "recon %.4f ms  loopfilter %.4f  pad %.4f  total %.4f" % tuple((acc / 10)[[0, 2, 3, 4]]))
+    print("stages", stages, "mc %.4f ms  residual %.4f  loopfilter %.4f  pad %.4f  total %.4f" % tuple((acc / 10)[[0, 1, 2, 3, 4]]))
