@@ -965,6 +965,13 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) residual_kernel(const __g
                 const int r = fastdiv(it, inv), u = it - r * units;
                 uint2 o;
                 if (HIGH) {
+#ifndef RC_NO_LDGSTS
+                    // same format in the picture and in the tile: asynchronous copies, awaited ahead of the
+                    // batches (the TB sort and the coefficient scatter run meanwhile)
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(&tile.p(c)[r * tile.pitch(c) + 2 * u])),
+                                 "l"(plane + (size_t)r * f.work.pitch[c] + (size_t)((cx0 >> hs) + 4 * u) * 2) : "memory");
+                    continue;
+#endif
                     o = *(const uint2 *)(plane + (size_t)r * f.work.pitch[c] + (size_t)((cx0 >> hs) + 4 * u) * 2);
                 } else {
                     const uint32_t v = *(const uint32_t *)(plane + (size_t)r * f.work.pitch[c] + (cx0 >> hs) + 4 * u);
@@ -1067,6 +1074,7 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) residual_kernel(const __g
                     pr[k] = q < npair ? __ldg(src + q) : 0xffffu;
                 }
             }
+            asm volatile("cp.async.wait_all;" ::: "memory");         // the tile (phase 0)
             __syncthreads();
             RC_MARK(7);
         } else if (staged) {
@@ -1077,6 +1085,10 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) residual_kernel(const __g
             }
             mbar_wait(mbar, 0);
             RC_MARK(7);
+        }
+        if (!sparse) {
+            asm volatile("cp.async.wait_all;" ::: "memory");         // the tile (phase 0)
+            __syncthreads();
         }
         CoefSrc cs;
         cs.csm = staged ? coef_sm : nullptr; cs.clo = clo; cs.chi = chi; cs.glob = f.coeffs;
