@@ -395,11 +395,24 @@ struct LfGeom {
 #ifndef LF_MINB
 #define LF_MINB 4
 #endif
+// -DLF_PROFILE: thread LF_PROF_TID of every CTA adds the cycles between phase marks to g_lf_prof (tools/lf_phases.py)
+#ifdef LF_PROFILE
+#ifndef LF_PROF_TID
+#define LF_PROF_TID 0
+#endif
+__device__ unsigned long long g_lf_prof[16];
+#define LF_MARK(i) do { if (threadIdx.x == LF_PROF_TID) { const long long t_ = clock64(); atomicAdd(&g_lf_prof[i], (unsigned long long)(t_ - lf_t)); lf_t = t_; } } while (0)
+#else
+#define LF_MARK(i) do { } while (0)
+#endif
 template <typename pixel>
 __global__ void __launch_bounds__(LF_THREADS, LF_MINB) loopfilter_kernel(const __grid_constant__ FrameDev f,
                                                                  const __grid_constant__ LfMaps maps, int flags)
 {
     extern __shared__ __align__(128) uint8_t lf_smem[];
+#ifdef LF_PROFILE
+    long long lf_t = clock64();
+#endif
     constexpr int AX = 16 / (int)sizeof(pixel);           // samples per 16 bytes: TMA boxes start on them
     const int tid = threadIdx.x;
     const int bd = f.bd;
@@ -437,6 +450,7 @@ __global__ void __launch_bounds__(LF_THREADS, LF_MINB) loopfilter_kernel(const _
     }
     if (tid < 4) cnt[tid] = 0;
     __syncthreads();
+    LF_MARK(0);
 
     // ---- while the tile is in flight: side information -> segment lists and SAO records
     const bool do_db = (flags & 1) && f.vbs;
@@ -483,6 +497,7 @@ __global__ void __launch_bounds__(LF_THREADS, LF_MINB) loopfilter_kernel(const _
                            (uint32_t)p.beta | (uint32_t)p.tc << 16);
         }
     }
+    LF_MARK(9);
     const int lctb = min(f.log2_ctb, 6);                       // CTBs of the region: nreg x nreg
     const int nreg = LF_REGION >> lctb;
     if (tid < np * nreg * nreg) {
@@ -519,8 +534,11 @@ __global__ void __launch_bounds__(LF_THREADS, LF_MINB) loopfilter_kernel(const _
         }
         srec[tid] = r;
     }
+    LF_MARK(1);
     __syncthreads();
+    LF_MARK(2);
     lf_mbar_wait(mbar, 0);
+    LF_MARK(3);
 
     if (do_db) {
         // ---- 1. vertical edges: segment = 4 rows x (P3..Q3); lines are rows
@@ -540,7 +558,9 @@ __global__ void __launch_bounds__(LF_THREADS, LF_MINB) loopfilter_kernel(const _
                 for (int d = 0; d < 4; d++) { st4(base + d * bw, l[d]); st4(base + d * bw + 4, l[d] + 4); }
             }
         }
+        LF_MARK(4);
         __syncthreads();
+        LF_MARK(5);
         // ---- 2. horizontal edges: segment = (P3..Q3) rows x 4 columns; lines are columns
         {
             const int nl = cnt[2], n = nl + cnt[3];
@@ -568,7 +588,9 @@ __global__ void __launch_bounds__(LF_THREADS, LF_MINB) loopfilter_kernel(const _
                 }
             }
         }
+        LF_MARK(6);
         __syncthreads();
+        LF_MARK(7);
     }
 
     // ---- 3. SAO (or plain copy) of the region into the DPB slot, eight samples per thread step
@@ -611,8 +633,18 @@ __global__ void __launch_bounds__(LF_THREADS, LF_MINB) loopfilter_kernel(const _
         }
         st8(drow + x0, o);
     }
+    LF_MARK(8);
 #undef TILE
 }
+
+#ifdef LF_PROFILE
+extern "C" int ohcu_lf_profile(unsigned long long *out, int reset)
+{
+    if (cudaMemcpyFromSymbol(out, g_lf_prof, sizeof(g_lf_prof)) != cudaSuccess) return -1;
+    if (reset) { unsigned long long z[16] = {}; cudaMemcpyToSymbol(g_lf_prof, z, sizeof(z)); }
+    return 0;
+}
+#endif
 
 size_t loopfilter_smem_bytes(const FrameDev &f)
 {
