@@ -380,11 +380,93 @@ __device__ __noinline__ void sao_slow(const FrameDev &f, int c, int x0, int y, c
     }
 }
 
+constexpr int LF_MAX_SEGS = 512;               // per direction: 3 x 162 for 4:4:4
+
+// ---------------------------------------------------------------- one edge pass, a thread per LINE
+// The four lines of a segment sit on four neighbouring lanes.  The decisions of the reference
+// (template :3390-3420) read lines 0 and 3 only: every lane computes dp, dq and the strong-filter
+// test of its own line, the quad's lanes 0 and 3 hand theirs out by shuffle / ballot, and each
+// lane then filters its line.  All 256 threads work on 4 n lines instead of n threads on n
+// segments (n is 130-190 per pass of a 64x64 region: half the CTA used to wait at the barrier).
+template <typename pixel, bool HORIZ>
+__device__ __forceinline__ void edge_pass(uint8_t *smem, uint32_t toff0, uint32_t toff1, uint32_t toff2, int bw0, int bwc,
+                                          const uint2 *list, int nl, int nch, int bd, int tid)
+{
+    const int n = nl + nch, n4 = 4 * n;
+    const int q0 = tid & 28;                                   // first lane of this quad within the warp
+    const int maxv = (1 << bd) - 1;
+    for (int base = 0; base < n4; base += LF_THREADS) {
+        const int k4 = base + tid, k = k4 >> 2, d = k4 & 3;
+        const bool act = k < n;
+        const uint2 r = act ? list[k < nl ? k : LF_MAX_SEGS - 1 - (k - nl)] : make_uint2(0u, 0u);
+        const int c = (r.x >> 16) & 3;
+        const int bw = c == 0 ? bw0 : bwc;
+        pixel *p = (pixel *)(smem + (c == 0 ? toff0 : (c == 1 ? toff1 : toff2))) + (r.x & 0xffff);
+        int l[8];
+        if (act) {
+            if (!HORIZ) { ld4(p + d * bw, l); ld4(p + d * bw + 4, l + 4); }
+            else {
+#pragma unroll
+                for (int q = 0; q < 8; q++) l[q] = p[q * bw + d];
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < 8; q++) l[q] = 0;
+        }
+        const int beta = (int)(r.y & 0xffff) << (bd - 8), tc = (int)(r.y >> 16) << (bd - 8);
+        const int dp = abs(l[1] - 2 * l[2] + l[3]), dq = abs(l[6] - 2 * l[5] + l[4]);
+        const int ds = dp + dq;
+        const bool sline = abs(l[0] - l[3]) + abs(l[7] - l[4]) < (beta >> 3) && abs(l[3] - l[4]) < ((tc * 5 + 1) >> 1) &&
+                           (ds << 1) < (beta >> 2);
+        const int ds0 = __shfl_sync(0xffffffffu, ds, q0), ds3 = __shfl_sync(0xffffffffu, ds, q0 + 3);
+        const int dp0 = __shfl_sync(0xffffffffu, dp, q0), dp3 = __shfl_sync(0xffffffffu, dp, q0 + 3);
+        const unsigned sb = __ballot_sync(0xffffffffu, sline);
+        if (!act) continue;
+        const int no_p = (r.x >> 18) & 1, no_q = (r.x >> 19) & 1;
+        if (c == 0) {
+            if (ds0 + ds3 >= beta) continue;
+            const int p3 = l[0], p2 = l[1], p1 = l[2], p0 = l[3], q0_ = l[4], q1 = l[5], q2 = l[6], q3 = l[7];
+            if (((sb >> q0) & 1u) && ((sb >> (q0 + 3)) & 1u)) {
+                const int tc2 = tc << 1;
+                if (!no_p) {
+                    l[3] = p0 + clip3i(((p2 + 2 * p1 + 2 * p0 + 2 * q0_ + q1 + 4) >> 3) - p0, -tc2, tc2);
+                    l[2] = p1 + clip3i(((p2 + p1 + p0 + q0_ + 2) >> 2) - p1, -tc2, tc2);
+                    l[1] = p2 + clip3i(((2 * p3 + 3 * p2 + p1 + p0 + q0_ + 4) >> 3) - p2, -tc2, tc2);
+                }
+                if (!no_q) {
+                    l[4] = q0_ + clip3i(((p1 + 2 * p0 + 2 * q0_ + 2 * q1 + q2 + 4) >> 3) - q0_, -tc2, tc2);
+                    l[5] = q1 + clip3i(((p0 + q0_ + q1 + q2 + 2) >> 2) - q1, -tc2, tc2);
+                    l[6] = q2 + clip3i(((2 * q3 + 3 * q2 + q1 + q0_ + p0 + 4) >> 3) - q2, -tc2, tc2);
+                }
+            } else {
+                const int side = (beta + (beta >> 1)) >> 3, tc_2 = tc >> 1;
+                const bool nd_p2 = dp0 + dp3 < side, nd_q2 = (ds0 - dp0) + (ds3 - dp3) < side;
+                int delta0 = (9 * (q0_ - p0) - 3 * (q1 - p1) + 8) >> 4;
+                if (abs(delta0) >= 10 * tc) continue;
+                delta0 = clip3i(delta0, -tc, tc);
+                if (!no_p) l[3] = clip3i(p0 + delta0, 0, maxv);
+                if (!no_q) l[4] = clip3i(q0_ - delta0, 0, maxv);
+                if (!no_p && nd_p2) l[2] = clip3i(p1 + clip3i((((p2 + p0 + 1) >> 1) - p1 + delta0) >> 1, -tc_2, tc_2), 0, maxv);
+                if (!no_q && nd_q2) l[5] = clip3i(q1 + clip3i((((q2 + q0_ + 1) >> 1) - q1 - delta0) >> 1, -tc_2, tc_2), 0, maxv);
+            }
+        } else {
+            const int p1 = l[2], p0 = l[3], q0_ = l[4], q1 = l[5];
+            const int delta0 = clip3i((((q0_ - p0) * 4) + p1 - q1 + 4) >> 3, -tc, tc);
+            if (!no_p) l[3] = clip3i(p0 + delta0, 0, maxv);
+            if (!no_q) l[4] = clip3i(q0_ - delta0, 0, maxv);
+        }
+        if (!HORIZ) { st4(p + d * bw, l); st4(p + d * bw + 4, l + 4); }
+        else {
+#pragma unroll
+            for (int q = 1; q < 7; q++) p[q * bw + d] = (pixel)l[q];
+        }
+    }
+}
+
 // ---------------------------------------------------------------- the kernel
 // Edge segments that actually filter, found while the tile is in flight.
 //   w0  tile offset of the segment's first sample (P3 of line 0) | plane << 16 | no_p << 18 | no_q << 19
 //   w1  beta | tc << 16   (table values, scaled to the bit depth by the filter)
-constexpr int LF_MAX_SEGS = 512;               // per direction: 3 x 162 for 4:4:4
 
 struct LfGeom {
     int TW, TH, BW, BH, px0, py0, lw;          // lw = log2(TW)
@@ -542,52 +624,12 @@ __global__ void __launch_bounds__(LF_THREADS, LF_MINB) loopfilter_kernel(const _
 
     if (do_db) {
         // ---- 1. vertical edges: segment = 4 rows x (P3..Q3); lines are rows
-        {
-            const int nl = cnt[0], n = nl + cnt[1];
-            for (int k = tid; k < n; k += LF_THREADS) {
-                const uint2 r = seg[k < nl ? k : LF_MAX_SEGS - 1 - (k - nl)];
-                const int c = (r.x >> 16) & 3;
-                const int bw = c == 0 ? g[0].BW : g[1].BW;
-                pixel *base = (pixel *)(lf_smem + (c == 0 ? toff[0] : (c == 1 ? toff[1] : toff[2]))) + (r.x & 0xffff);
-                int l[4][8];
-#pragma unroll
-                for (int d = 0; d < 4; d++) { ld4(base + d * bw, l[d]); ld4(base + d * bw + 4, l[d] + 4); }
-                if (c == 0) luma_segment(l, bd, r.y & 0xffff, r.y >> 16, (r.x >> 18) & 1, (r.x >> 19) & 1);
-                else chroma_segment(l, bd, r.y >> 16, (r.x >> 18) & 1, (r.x >> 19) & 1);
-#pragma unroll
-                for (int d = 0; d < 4; d++) { st4(base + d * bw, l[d]); st4(base + d * bw + 4, l[d] + 4); }
-            }
-        }
+        edge_pass<pixel, false>(lf_smem, toff[0], toff[1], toff[2], g[0].BW, g[1].BW, seg, cnt[0], cnt[1], bd, tid);
         LF_MARK(4);
         __syncthreads();
         LF_MARK(5);
         // ---- 2. horizontal edges: segment = (P3..Q3) rows x 4 columns; lines are columns
-        {
-            const int nl = cnt[2], n = nl + cnt[3];
-            for (int k = tid; k < n; k += LF_THREADS) {
-                const uint2 r = seg[LF_MAX_SEGS + (k < nl ? k : LF_MAX_SEGS - 1 - (k - nl))];
-                const int c = (r.x >> 16) & 3;
-                const int bw = c == 0 ? g[0].BW : g[1].BW;
-                pixel *base = (pixel *)(lf_smem + (c == 0 ? toff[0] : (c == 1 ? toff[1] : toff[2]))) + (r.x & 0xffff);
-                int l[4][8];
-#pragma unroll
-                for (int q = 0; q < 8; q++) {
-                    int v[4];
-                    ld4(base + q * bw, v);
-#pragma unroll
-                    for (int d = 0; d < 4; d++) l[d][q] = v[d];
-                }
-                if (c == 0) luma_segment(l, bd, r.y & 0xffff, r.y >> 16, (r.x >> 18) & 1, (r.x >> 19) & 1);
-                else chroma_segment(l, bd, r.y >> 16, (r.x >> 18) & 1, (r.x >> 19) & 1);
-#pragma unroll
-                for (int q = 0; q < 8; q++) {
-                    int v[4];
-#pragma unroll
-                    for (int d = 0; d < 4; d++) v[d] = l[d][q];
-                    st4(base + q * bw, v);
-                }
-            }
-        }
+        edge_pass<pixel, true>(lf_smem, toff[0], toff[1], toff[2], g[0].BW, g[1].BW, seg + LF_MAX_SEGS, cnt[2], cnt[3], bd, tid);
         LF_MARK(6);
         __syncthreads();
         LF_MARK(7);
