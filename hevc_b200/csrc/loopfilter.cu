@@ -582,8 +582,11 @@ __global__ void __launch_bounds__(LF_THREADS, LF_MINB) loopfilter_kernel(const _
     LF_MARK(9);
     const int lctb = min(f.log2_ctb, 6);                       // CTBs of the region: nreg x nreg
     const int nreg = LF_REGION >> lctb;
-    if (tid < np * nreg * nreg) {
-        const int c = tid / (nreg * nreg), k = tid - c * nreg * nreg;
+    // the SAO records go to the LAST threads: the first ones carry one segment item more (524 items on
+    // 256 threads at 4:2:0) and were the CTA's critical path with the records on top
+    const int stid = LF_THREADS - 1 - tid;
+    if (stid < np * nreg * nreg) {
+        const int c = stid / (nreg * nreg), k = stid - c * nreg * nreg;
         const int ctbx = ((blockIdx.x * LF_REGION) >> f.log2_ctb) + (k % nreg);
         const int ctby = ((blockIdx.y * LF_REGION) >> f.log2_ctb) + (k / nreg);
         SaoRec r = {0, 0, OHCU_SAO_NOT_APPLIED, 0};
@@ -614,7 +617,7 @@ __global__ void __launch_bounds__(LF_THREADS, LF_MINB) loopfilter_kernel(const _
                 r.misc = (uint32_t)type | (uint32_t)eo << 2 | (fast ? 1u << 4 : 0u) | (uint32_t)sp.band_position[c] << 8;
             }
         }
-        srec[tid] = r;
+        srec[stid] = r;
     }
     LF_MARK(1);
     __syncthreads();
