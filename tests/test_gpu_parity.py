@@ -150,3 +150,47 @@ def test_sparse_append_errors():
         assert lib.ohcu_append_tu(h, j, job.tus.ctypes.data, len(job.tus), job.coeffs.ctypes.data, len(job.coeffs)) == 0
         assert lib.ohcu_append_tu_sparse(h, j, recs.ctypes.data, len(recs), pairs.ctypes.data, len(pairs)) == -4
         assert lib.ohcu_frame_abort(h, j) == 0
+
+
+def test_threaded_submission_ring(oracle):
+    """Four host threads submit 96 frames through a ring of 8 jobs / 8 slots with asynchronous
+    downloads (the flow of bench.py's e2e leg); every downloaded picture is compared."""
+    from concurrent.futures import ThreadPoolExecutor
+    jobs = [synth.make_job(256, 128, 10, 1, seed=40 + k) for k in range(4)]
+    sp = jobs[0].sp
+    refs = [synth.make_picture(sp, 70 + s) for s in range(2)]
+    E = 8
+    want = []
+    for jb in jobs:
+        jb.sp.dpb_slots = 2 + E
+        want.append(oracle.replay(jb, list(refs) + [None] * E))
+    bad = []
+    with backend.Context(sp, dpb_slots=2 + E, jobs=E) as ctx:
+        ctx.upload(0, refs[0]); ctx.upload(1, refs[1])
+        outs = [ctx.pinned_picture() for _ in range(E)]
+        sparse = [ctx.sparse_lists(jb) for jb in jobs]
+        pending = [None] * E
+
+        def submit(i):
+            k = i % E
+            if pending[k] is not None:
+                ctx.slot_sync(2 + k)
+                d = _diff(outs[k], want[pending[k] % len(jobs)])
+                if d is not None:
+                    bad.append((pending[k], d))
+            j = ctx.begin(2 + k)
+            ctx.append(j, jobs[i % len(jobs)], sparse=sparse[i % len(jobs)] if i & 1 else False)
+            ctx.flush(j)
+            ctx.download_async(2 + k, outs[k])
+            pending[k] = i
+
+        # frames that share a slot must not be in flight together on the host side: E frames per wave
+        with ThreadPoolExecutor(4) as pool:
+            for wave in range(12):
+                list(pool.map(submit, range(wave * E, (wave + 1) * E)))
+        for k in range(E):
+            ctx.slot_sync(2 + k)
+            d = _diff(outs[k], want[pending[k] % len(jobs)])
+            if d is not None:
+                bad.append((pending[k], d))
+    assert not bad, bad[:3]
