@@ -46,8 +46,8 @@ WORKLOAD_NAMES = {
 N_DISTINCT = 4        # distinct synthetic frames; jobs reuse them round-robin
 # dram__bytes_read.sum + dram__bytes_write.sum of one mc_kernel launch, from the committed
 # `ncu --set full` capture of this same command (never measured inside a timed run)
-NCU_TRAFFIC = {"4k": 59126272}
-NCU_TRAFFIC_SOURCE = "profiles/r01_v12_ncu_kernels.txt (53.63 MB read + 5.49 MB write; the reference pictures and part of the written prediction stay in L2)"
+NCU_TRAFFIC = {"4k": 59145984}
+NCU_TRAFFIC_SOURCE = "profiles/r01_v13_ncu_kernels.txt (53.62 MB read + 5.53 MB write; the reference pictures and part of the written prediction stay in L2)"
 
 
 def peaks():
