@@ -553,23 +553,24 @@ __global__ void __launch_bounds__(LF_THREADS, LF_MINB) loopfilter_kernel(const _
                 const int n = dir ? nH[cc] : nV[cc];
                 if (c == cc && k >= n) { k -= n; c = cc + 1; }
             }
-            const LfGeom G = c == 0 ? g[0] : (c == 1 ? g[1] : g[2]);
+            // planes 1 and 2 share their geometry; the two grid widths are 64 and 32 samples, so the
+            // divisions are by constants (9, 5 edges per row of items; 18, 10 segments per edge row)
+            const int TW = c == 0 ? g[0].TW : g[1].TW, BW = c == 0 ? g[0].BW : g[1].BW;
+            const int px0 = c == 0 ? g[0].px0 : g[1].px0, py0 = c == 0 ? g[0].py0 : g[1].py0;
             SegParam p;
             int base;
             if (!dir) {
-                const int nE = G.TW / 8 + 1;
-                const int s = k / nE, i = k - s * nE;
-                const int ex = G.px0 + 8 * i, ys = G.py0 - 4 + 4 * s;
+                const int s = TW == 64 ? k / 9 : k / 5, i = k - s * (TW / 8 + 1);
+                const int ex = px0 + 8 * i, ys = py0 - 4 + 4 * s;
                 if (ex <= 0 || ex >= f.pw[c] || ys < 0 || ys >= f.ph[c]) continue;
                 p = vseg_param(f, c, ex, ys);
-                base = (4 * s) * G.BW + 8 * i + AX - 4;
+                base = (4 * s) * BW + 8 * i + AX - 4;
             } else {
-                const int nS = (G.TW + 8) / 4;
-                const int j = k / nS, s = k - j * nS;
-                const int ey = G.py0 + 8 * j, xs = G.px0 - 4 + 4 * s;
+                const int j = TW == 64 ? k / 18 : k / 10, s = k - j * ((TW + 8) / 4);
+                const int ey = py0 + 8 * j, xs = px0 - 4 + 4 * s;
                 if (ey <= 0 || ey >= f.ph[c] || xs < 0 || xs >= f.pw[c]) continue;
                 p = hseg_param(f, c, xs, ey);
-                base = (8 * j) * G.BW + 4 * s + AX - 4;             // row py0 - 4 is tile row 0
+                base = (8 * j) * BW + 4 * s + AX - 4;             // row py0 - 4 is tile row 0
             }
             if (!p.on || (c && p.tc == 0)) continue;
             const int slot = atomicAdd(&cnt[dir * 2 + (c ? 1 : 0)], 1);
