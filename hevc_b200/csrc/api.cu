@@ -271,8 +271,9 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
     *out = nullptr;
     if (sp->width <= 0 || sp->height <= 0 || sp->width > 16384 || sp->height > 16384)
         return fail(OHCU_EINVAL, "bad picture size %dx%d", sp->width, sp->height);
-    if (sp->bit_depth != 8 && sp->bit_depth != 9 && sp->bit_depth != 10 && sp->bit_depth != 12)
-        return fail(OHCU_EINVAL, "unsupported bit depth %d (8, 9, 10, 12)", sp->bit_depth);
+    // the depths ff_hevc_dsp_init instantiates (hevcdsp.c:514-545)
+    if (sp->bit_depth != 8 && sp->bit_depth != 9 && sp->bit_depth != 10 && sp->bit_depth != 12 && sp->bit_depth != 14)
+        return fail(OHCU_EINVAL, "unsupported bit depth %d (8, 9, 10, 12, 14)", sp->bit_depth);
     if (sp->chroma_format_idc < 0 || sp->chroma_format_idc > 3)
         return fail(OHCU_EINVAL, "bad chroma_format_idc %d", sp->chroma_format_idc);
     if (sp->log2_ctb_size < 4 || sp->log2_ctb_size > 6 || sp->log2_min_cb_size < 3 ||
@@ -326,6 +327,7 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
 #define TRYCU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { ohcu_destroy(c); \
         return fail(e_ == cudaErrorMemoryAllocation ? OHCU_ENOMEM : OHCU_ECUDA, "%s -> %s", #x, cudaGetErrorString(e_)); } } while (0)
     if (upload_dct_table() || upload_mc_taps()) { ohcu_destroy(c); return fail(OHCU_ECUDA, "constant upload failed"); }
+    if (recon_set_attrs() || loopfilter_set_attrs()) { ohcu_destroy(c); return fail(OHCU_ECUDA, "cudaFuncSetAttribute failed"); }
     c->slots.resize(sp->dpb_slots);
     for (auto &s : c->slots) {
         TRY(alloc_picture(c, &s.pic, true));

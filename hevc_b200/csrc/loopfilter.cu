@@ -712,17 +712,19 @@ void loopfilter_box(const FrameDev &f, int c, int *bw, int *bh)
     *bh = (LF_REGION >> vs) + 8;
 }
 
+// per device, from ohcu_create (see recon_set_attrs)
+int loopfilter_set_attrs()
+{
+    if (cudaFuncSetAttribute(loopfilter_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024) != cudaSuccess ||
+        cudaFuncSetAttribute(loopfilter_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024) != cudaSuccess)
+        return -1;
+    return 0;
+}
+
 int launch_loopfilter(const FrameDev &f, const LfMaps &maps, int flags, cudaStream_t st)
 {
     if (!(flags & 3)) return 0;
     const size_t smem = loopfilter_smem_bytes(f);
-    static bool attr_set = false;
-    if (!attr_set) {
-        if (cudaFuncSetAttribute(loopfilter_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024) != cudaSuccess ||
-            cudaFuncSetAttribute(loopfilter_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024) != cudaSuccess)
-            return -1;
-        attr_set = true;
-    }
     dim3 grid((f.width + LF_REGION - 1) / LF_REGION, (f.height + LF_REGION - 1) / LF_REGION);
     if (f.bd > 8) loopfilter_kernel<uint16_t><<<grid, LF_THREADS, smem, st>>>(f, maps, flags);
     else          loopfilter_kernel<uint8_t><<<grid, LF_THREADS, smem, st>>>(f, maps, flags);

@@ -81,6 +81,8 @@ enum { BSF_NO_LEFT = 1, BSF_NO_UP = 2, BSF_DISABLED = 4 };
 // kernel launchers (each returns the number of kernels it enqueued, < 0 on error)
 int launch_recon(const FrameDev &f, int flags, cudaStream_t st);   // flags: 1 MC, 2 residual
 int recon_sparse_ctb_coefs(int log2_ctb, int nplanes, int hs, int vs);   // int16 a CTB's rebuilt coefficient area may hold (sparse form)
+int recon_set_attrs();                     // per-device function attributes (dynamic shared memory opt-in)
+int loopfilter_set_attrs();
 int upload_mc_taps();
 int upload_dct_table();
 struct LfMaps { CUtensorMap m[3]; };        // the job's reconstructed picture, one box per plane

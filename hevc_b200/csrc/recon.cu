@@ -873,10 +873,11 @@ __device__ __forceinline__ void build_pu_records(const FrameDev &f, PuRec *recs,
                 }
                 int wA, wB = 0, add, sh, post = 0;
                 if (!bi) {
-                    if (!wflag) { wA = 1; sh = 14 - bd; add = 1 << (13 - bd); }
-                    else { wA = wx[lA]; sh = denom + 14 - bd; add = 1 << (sh - 1); post = ox[lA]; }
+                    // rounding offsets are 0 at 14 bits (#if BIT_DEPTH < 14, template :2381, :2400, :2427)
+                    if (!wflag) { wA = 1; sh = 14 - bd; add = bd < 14 ? 1 << (13 - bd) : 0; }
+                    else { wA = wx[lA]; sh = denom + 14 - bd; add = bd < 14 ? 1 << (sh - 1) : 0; post = ox[lA]; }
                 } else {
-                    if (!wflag) { wA = 1; wB = 1; sh = 15 - bd; add = 1 << (14 - bd); }
+                    if (!wflag) { wA = 1; wB = 1; sh = 15 - bd; add = bd < 14 ? 1 << (14 - bd) : 0; }
                     else {
                         const int log2Wd = denom + 14 - bd;
                         wA = wx[1]; wB = wx[0]; sh = log2Wd + 1; add = (ox[0] + ox[1] + 1) * (1 << log2Wd);
@@ -1252,6 +1253,16 @@ size_t recon_smem_bytes(const FrameDev &f, int area_units)
 
 int recon_sparse_ctb_coefs(int log2_ctb, int nplanes, int hs, int vs) { return coef_area(rc_area_units(log2_ctb, nplanes, hs, vs)); }
 
+// Function attributes are per DEVICE: ohcu_create calls this after cudaSetDevice, once per context
+// (a process-wide flag left the second GPU of a process without the > 48 KB opt-in).
+int recon_set_attrs()
+{
+    if (cudaFuncSetAttribute(residual_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024) != cudaSuccess ||
+        cudaFuncSetAttribute(residual_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024) != cudaSuccess)
+        return -1;
+    return 0;
+}
+
 int launch_recon(const FrameDev &f, int flags, cudaStream_t st)
 {
     const int nctb = f.ctb_w * f.ctb_h;
@@ -1264,13 +1275,6 @@ int launch_recon(const FrameDev &f, int flags, cudaStream_t st)
     if ((flags & 2) && f.n_tu > 0) {
         const int hu = rc_area_units(f.log2_ctb, f.nplanes, f.hs, f.vs);
         const size_t smem = recon_smem_bytes(f, hu);
-        static bool attr_set = false;
-        if (!attr_set) {
-            if (cudaFuncSetAttribute(residual_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024) != cudaSuccess ||
-                cudaFuncSetAttribute(residual_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024) != cudaSuccess)
-                return -1;
-            attr_set = true;
-        }
         if (f.bd > 8) residual_kernel<true><<<nctb, RC_THREADS, smem, st>>>(f, hu);
         else          residual_kernel<false><<<nctb, RC_THREADS, smem, st>>>(f, hu);
         n++;
@@ -1377,9 +1381,9 @@ int dsp_mc(int bd, int luma, int family, uint8_t *dst, ptrdiff_t dststride, cons
     Epi &e = a.e;                                  // the table of `Epi` above
     e.maxv = (1 << bd) - 1; e.wB = 0; e.post = 0;
     const int sc = 1 << (bd - 8);
-    if (family == 1) { e.wA = 1; e.sh = 14 - bd; e.add = 1 << (13 - bd); }
-    else if (family == 2) { e.wA = wx0; e.sh = denom + 14 - bd; e.add = 1 << (e.sh - 1); e.post = ox0 * sc; }
-    else if (family == 3) { e.wA = 1; e.wB = 1; e.sh = 15 - bd; e.add = 1 << (14 - bd); }
+    if (family == 1) { e.wA = 1; e.sh = 14 - bd; e.add = bd < 14 ? 1 << (13 - bd) : 0; }
+    else if (family == 2) { e.wA = wx0; e.sh = denom + 14 - bd; e.add = bd < 14 ? 1 << (e.sh - 1) : 0; e.post = ox0 * sc; }
+    else if (family == 3) { e.wA = 1; e.wB = 1; e.sh = 15 - bd; e.add = bd < 14 ? 1 << (14 - bd) : 0; }
     else if (family == 4) {
         const int log2Wd = denom + 14 - bd;
         e.wA = wx1; e.wB = wx0; e.sh = log2Wd + 1; e.add = (ox0 * sc + ox1 * sc + 1) * (1 << log2Wd);

@@ -60,7 +60,7 @@ typedef struct ohcu_ctx ohcu_ctx;
 /* ---- sequence-level parameters (what set_sps() derives, hevcdec.c:428-476) */
 typedef struct ohcu_seq_params {
     int32_t width, height;        /* luma samples; multiples of the min CB size   */
-    int32_t bit_depth;            /* 8, 9, 10 or 12. One depth for luma+chroma:
+    int32_t bit_depth;            /* 8, 9, 10, 12 or 14 (hevcdsp.c:514-545). One depth for luma+chroma:
                                      ff_hevc_dsp_init(&s->hevcdsp, bit_depth[LUMA]),
                                      hevcdec.c:447                                 */
     int32_t chroma_format_idc;    /* 0 mono, 1 4:2:0, 2 4:2:2, 3 4:4:4            */

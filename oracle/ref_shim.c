@@ -25,7 +25,7 @@ static pthread_once_t g_once = PTHREAD_ONCE_INIT;
 
 static void init_tables(void)
 {
-    static const int depths[] = { 8, 9, 10, 12 };
+    static const int depths[] = { 8, 9, 10, 12, 14 };
     for (unsigned i = 0; i < sizeof(depths) / sizeof(depths[0]); i++) {
         ff_hevc_dsp_init(&g_tab[depths[i]], depths[i]);      /* hevcdsp.c:311 */
         ff_videodsp_init(&g_vdsp[depths[i]], depths[i]);     /* videodsp.c    */

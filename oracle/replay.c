@@ -396,7 +396,7 @@ int or_replay_frame(const oh_frame_job *job)
     r.min_pu_w = sp->width >> sp->log2_min_pu_size;
     r.min_pu_h = sp->height >> sp->log2_min_pu_size;
     r.cur = job->out;
-    if (sp->bit_depth < 8 || sp->bit_depth > 12 || sp->chroma_format_idc < 0 || sp->chroma_format_idc > 3)
+    if (sp->bit_depth < 8 || sp->bit_depth > 14 || sp->chroma_format_idc < 0 || sp->chroma_format_idc > 3)
         return OHCU_EINVAL;
     /* Not supported (documented in DESIGN.md, parity hazards): with 16x16 CTBs and
      * horizontally subsampled chroma the reference defers a whole CTB of horizontal

@@ -23,6 +23,8 @@ FRAME_CASES = {
     "mono_8b": (192, 128, 8, 0, 6001, {}),
     "main12_420": (256, 136, 12, 1, 6002, dict(weighted=1)),
     "bd9_420": (256, 136, 9, 1, 6003, {}),
+    "main14_420": (256, 136, 14, 1, 6004, {}),
+    "main14_444_weighted": (192, 128, 14, 3, 6005, dict(weighted=1, rext=1)),
     "dense_coeffs_8b": (256, 128, 8, 1, 7001, dict(dense_coeffs=1)),
     "dense_coeffs_10b_444": (192, 128, 10, 3, 7002, dict(dense_coeffs=1, rext=1)),
     "far_mv_8b": (320, 176, 8, 1, 7003, dict(far_mv_pct=60)),
@@ -34,9 +36,19 @@ FRAME_CASES = {
     "cfg2_small_1080like": (480, 272, 8, 1, 2001, {}),
 }
 
+# BASELINE.json configs[1..4] at their named sizes (one picture each): grids of 510 - 8160 CTBs,
+# pitches beyond 8 KB, coordinates up to 7680, lists of 10^5 - 10^6 records.
+FULLSIZE_CASES = {
+    "cfg2_1920x1080_8b_420": (1920, 1080, 8, 1, 2002, {}),
+    "cfg3_3840x2160_10b_420_weighted": (3840, 2160, 10, 1, 3002, dict(weighted=1)),
+    "cfg4a_1920x1080_10b_422": (1920, 1080, 10, 2, 4004, dict(rext=1, weighted=1)),
+    "cfg4b_1920x1080_10b_444": (1920, 1080, 10, 3, 4005, dict(rext=1)),
+    "cfg5_7680x4320_10b_420_weighted": (7680, 4320, 10, 1, 5005, dict(weighted=1)),
+}
+
 
 def build_case(name):
-    w, h, bd, cf, seed, kw = FRAME_CASES[name]
+    w, h, bd, cf, seed, kw = (FRAME_CASES.get(name) or FULLSIZE_CASES[name])
     job = synth.make_job(w, h, bd, cf, seed=seed, **kw)
     refs = [synth.make_picture(job.sp, seed * 10 + s) for s in range(job.sp.dpb_slots)]
     return job, refs

@@ -5,6 +5,8 @@ Run in the build container (needs /root/reference):  python tests/golden/make_go
   leaf_digests.json   sha256[:16] of every output of every leaf case (tests/leaf_cases.py)
   frames.json         sha256 of the reconstructed picture of every frame case
                       (tests/frame_cases.py) after MC, MC+residual, and the full pipeline
+  frames_fullsize.json  the same for BASELINE configs[1..4] at their named sizes (1080p 8-bit, 4K Main10,
+                      1080p 10-bit 4:2:2 / 4:4:4, 8K Main10), MC+residual and the full pipeline
   cfg1_416x240.npz    the full golden picture of BASELINE.json configs[0]
 """
 import hashlib
@@ -49,6 +51,15 @@ def main():
     with open(os.path.join(HERE, "frames.json"), "w") as f:
         json.dump({"source": "ohref_replay_frame (reference drivers + table)", "cases": frames}, f,
                   indent=1, sort_keys=True)
+    # BASELINE configs at their named sizes: the reference's picture after MC + residual and after the full pipeline
+    full = {}
+    for name in frame_cases.FULLSIZE_CASES:
+        job, refs = frame_cases.build_case(name)
+        full[name] = {"n_pu": int(len(job.pus)), "n_tu": int(len(job.tus)), "ncoeff": int(len(job.coeffs))}
+        for key in ("mc_res", "all"):
+            full[name][key] = frame_cases.picture_digest(ref.replay(job, refs, out_init=refs[-1], stages=STAGE_SETS[key]))
+    with open(os.path.join(HERE, "frames_fullsize.json"), "w") as f:
+        json.dump({"source": "ohref_replay_frame (reference drivers + table)", "cases": full}, f, indent=1, sort_keys=True)
     # dequantisation (the levels form): the reference's own scale_and_clip_coeff on seeded blocks
     sl, sl_dc, cases = levels_cases.leaf_cases()
     outs = []

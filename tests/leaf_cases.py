@@ -8,7 +8,7 @@ Inputs come from numpy default_rng(seed) so every consumer sees the same bytes.
 import numpy as np
 
 WIDTHS = [2, 4, 6, 8, 12, 16, 24, 32, 48, 64]      # ff_hevc_pel_weight domain, hevcdec.c:49
-DEPTHS = [8, 10, 12, 9]
+DEPTHS = [8, 10, 12, 9, 14]      # every depth ff_hevc_dsp_init instantiates (hevcdsp.c:514-545)
 
 
 def _pix_dtype(bd):

@@ -39,6 +39,17 @@ def test_frame_goldens(name, oracle):
         assert frame_cases.picture_digest(out) == gold[key], f"{name}/{key}"
 
 
+@pytest.mark.parametrize("name", list(frame_cases.FULLSIZE_CASES))
+def test_fullsize_goldens(name, oracle):
+    """BASELINE.json configs[1..4] at their named sizes: the restatement against the reference's digests."""
+    gold = _load("frames_fullsize.json")[name]
+    job, refs = frame_cases.build_case(name)
+    assert (len(job.pus), len(job.tus), len(job.coeffs)) == (gold["n_pu"], gold["n_tu"], gold["ncoeff"]), \
+        "generator output changed: rerun make_golden.py"
+    out = oracle.replay(job, refs, out_init=refs[-1], stages=15)
+    assert frame_cases.picture_digest(out) == gold["all"], name
+
+
 def test_cfg1_golden_picture(oracle):
     """BASELINE.json configs[0]: the 416x240 8-bit 4:2:0 golden frame, byte for byte."""
     z = np.load(os.path.join(GOLDEN, "cfg1_416x240.npz"))

@@ -35,6 +35,24 @@ def test_frame_parity(name, oracle):
             assert frame_cases.picture_digest(got) == gold[key], f"{name}/{key} differs from the reference fixture"
 
 
+@pytest.mark.parametrize("name", list(frame_cases.FULLSIZE_CASES))
+def test_fullsize_parity(name, oracle):
+    """BASELINE.json configs[1..4] at their NAMED sizes (1080p 8-bit, 4K Main10 weighted, 1080p 10-bit 4:2:2 and
+    4:4:4, 8K Main10), one picture each: plane for plane against the oracle replay, and the digests the compiled
+    reference wrote (tests/golden/frames_fullsize.json).  Dense blocks for MC + residual, sparse pairs for the
+    full pipeline, so both coefficient forms run at size."""
+    gold = json.load(open(os.path.join(GOLDEN, "frames_fullsize.json")))["cases"][name]
+    job, refs = frame_cases.build_case(name)
+    init = refs[-1]
+    with backend.Context(job.sp) as ctx:
+        got = ctx.reconstruct(job, refs, out_init=init, stages=3)
+        assert frame_cases.picture_digest(got) == gold["mc_res"], f"{name}/mc_res differs from the reference fixture"
+        got = ctx.reconstruct(job, refs, out_init=init, stages=15, sparse=True)
+        want = oracle.replay(job, refs, out_init=init, stages=15)
+        assert _diff(got, want) is None, f"{name}/all: {_diff(got, want)}"
+        assert frame_cases.picture_digest(got) == gold["all"], f"{name}/all differs from the reference fixture"
+
+
 @pytest.mark.parametrize("name", ["main10_416x240_420_weighted", "rext_10b_422", "rext_8b_444_bypass",
                                   "slices_tiles_8b_420", "slices_10b_420_bypass", "mono_8b"])
 @pytest.mark.parametrize("stage", [2, 4, 8, 12])
