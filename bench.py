@@ -11,7 +11,8 @@ reconstruction with weighted prediction.
   e2e          same metric through the C ABI with HOST buffers: list upload from pinned
                memory, kernels, and the reconstructed picture copied back to pinned memory
   roofline     the dominant kernel (mc_kernel: motion compensation) against the measured HBM peak
-  cpu_baseline the reference's own C hevcdsp path (oracle/_ref) on the host cores
+  cpu_baseline the reference's own CPU path on the host cores: its C drivers + its SSE intrinsics (oracle/_ref/
+               liboh_ref_simd.so, the fastest reference path buildable here), with the pure-C arms beside it
   --impl reference   times that CPU path alone, same metric / config
 
 One process per GPU (torchrun for N > 1), frames sharded across ranks, no collective on
@@ -160,34 +161,60 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------ reference arm
-def cpu_reference(jobs, refs, steps, warmup, max_threads=None):
-    """The reference's own C path (oracle/_ref, else the oracle port) on the host cores.
-    A step = one frame replayed per thread, all threads in parallel."""
+def cpu_arm(jobs, refs, steps, warmup, which, threads):
+    """One CPU arm: `threads` host threads, each replaying one frame per step through the library `which`
+    (ref_simd: the reference's C drivers + its SSE intrinsics, -O3; ref: its pure C table, -O2; oracle: the port)."""
     import oracle_lib
     from concurrent.futures import ThreadPoolExecutor
-    kind = "reference" if os.path.exists(oracle_lib.REF_SO) or os.path.isdir(oracle_lib.REFERENCE_ROOT) else "port"
-    lib = oracle_lib.Lib("ref" if kind == "reference" else "oracle")
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
-    if max_threads:
-        cores = min(cores, max_threads)
+    lib = oracle_lib.Lib(which)
     dpb = list(refs) + [None] * (jobs[0].sp.dpb_slots - len(refs))
 
     def one(i):
         lib.replay(jobs[i % len(jobs)], dpb)
 
-    pool = ThreadPoolExecutor(cores)
+    pool = ThreadPoolExecutor(threads)
     for _ in range(warmup):
-        list(pool.map(one, range(cores)))
+        list(pool.map(one, range(threads)))
     t0 = time.perf_counter()
     for _ in range(steps):
-        list(pool.map(one, range(cores)))
+        list(pool.map(one, range(threads)))
     dt = time.perf_counter() - t0
     pool.shutdown()
     sp = jobs[0].sp
-    frames = steps * cores
-    return {"value": frames * sp.width * sp.height / dt / 1e6, "unit": "Mpixel/s", "cores": cores, "kind": kind,
-            "sample": f"{frames} frames ({cores} threads x {steps} steps, one frame per thread per step)",
-            "ms_per_step": dt / steps * 1e3, "seconds": dt}
+    frames = steps * threads
+    return {"value": frames * sp.width * sp.height / dt / 1e6, "frames": frames, "seconds": dt, "ms_per_step": dt / steps * 1e3}
+
+
+def cpu_reference(jobs, refs, steps, warmup, max_threads=None, all_arms=False):
+    """The reference's own CPU path on the host cores.  The headline arm is the FASTEST reference path this box can
+    build: its C drivers with its SSE intrinsics (x86/hevc_mc_sse.c, hevc_idct_sse.c, hevc_sao_sse.c) wired into the
+    table, -O3, one frame per host thread on all cores ("reference-simd").  The yasm sources of the reference are
+    unavailable on this box (no yasm / nasm), so deblocking runs its C entries.  all_arms adds the pure-C table on one
+    thread and on all threads."""
+    import oracle_lib
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
+    if max_threads:
+        cores = min(cores, max_threads)
+    have = lambda so: os.path.exists(so) or os.path.isdir(oracle_lib.REFERENCE_ROOT)
+    if have(oracle_lib.REF_SIMD_SO):
+        kind, which = "reference-simd", "ref_simd"
+    elif have(oracle_lib.REF_SO):
+        kind, which = "reference", "ref"
+    else:
+        kind, which = "port", "oracle"
+    main = cpu_arm(jobs, refs, steps, warmup, which, cores)
+    out = {"value": main["value"], "unit": "Mpixel/s", "cores": cores, "kind": kind,
+           "sample": f"{main['frames']} frames ({cores} threads x {steps} steps, one frame per thread per step)",
+           "ms_per_step": main["ms_per_step"], "seconds": main["seconds"]}
+    if all_arms:
+        arms = {f"{kind}_{cores}t": round(main["value"], 2)}
+        if which == "ref_simd":
+            arms["reference-simd_1t"] = round(cpu_arm(jobs, refs, max(1, steps), 1, "ref_simd", 1)["value"], 2)
+        if have(oracle_lib.REF_SO):
+            arms[f"reference-c_{cores}t"] = round(cpu_arm(jobs, refs, max(1, steps // 2), 1, "ref", cores)["value"], 2)
+            arms["reference-c_1t"] = round(cpu_arm(jobs, refs, 1, 1, "ref", 1)["value"], 2)
+        out["arms"] = arms
+    return out
 
 
 # ------------------------------------------------------------------ our arm
@@ -423,9 +450,9 @@ def run_ours(args, rank, world):
         "parity_check": check,
     }
     if world == 1 and not args.no_cpu:
-        cb = cpu_reference(jobs, refs, steps=args.cpu_steps, warmup=1)
+        cb = cpu_reference(jobs, refs, steps=args.cpu_steps, warmup=1, all_arms=True)
         line["cpu_baseline"] = {k: (round(v, 2) if isinstance(v, float) else v) for k, v in cb.items()
-                                if k in ("value", "unit", "cores", "kind", "sample")}
+                                if k in ("value", "unit", "cores", "kind", "sample", "arms")}
     print(json.dumps(line))
 
 
@@ -463,7 +490,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="4k", choices=list(WORKLOADS))
     ap.add_argument("--frames", type=int, default=0, help="frames per step per GPU (default per workload)")
-    ap.add_argument("--cpu-steps", type=int, default=2, help="steps of the cpu_baseline leg")
+    ap.add_argument("--cpu-steps", type=int, default=4, help="steps of the cpu_baseline leg")
     ap.add_argument("--host-threads", type=int, default=4, help="threads submitting frames in the e2e leg")
     ap.add_argument("--coeffs", default="sparse", choices=["dense", "sparse", "levels"],
                     help="coefficient form handed to the library: (position, level) pairs of the significant "

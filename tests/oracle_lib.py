@@ -14,6 +14,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 ORACLE_SO = os.path.join(ORACLE_DIR, "liboracle.so")
 REF_SO = os.path.join(ORACLE_DIR, "_ref", "liboh_ref.so")
+REF_SIMD_SO = os.path.join(ORACLE_DIR, "_ref", "liboh_ref_simd.so")     # reference C + its SSE intrinsics, -O3
 REFERENCE_ROOT = "/root/reference"
 
 import sys
@@ -63,8 +64,19 @@ def build_ref():
     return True
 
 
+def build_ref_simd():
+    if not os.path.isdir(REFERENCE_ROOT):
+        return False
+    subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "ref_simd", "-j8"])
+    return True
+
+
 def have_ref():
     return os.path.exists(REF_SO) or os.path.isdir(REFERENCE_ROOT)
+
+
+def have_ref_simd():
+    return os.path.exists(REF_SIMD_SO) or os.path.isdir(REFERENCE_ROOT)
 
 
 _P = C.c_void_p
@@ -101,6 +113,11 @@ class Lib:
             if not os.path.exists(REF_SO) and not build_ref():
                 raise FileNotFoundError(REF_SO)
             self.lib = C.CDLL(REF_SO)
+            prefix = "ohref_"
+        elif which == "ref_simd":
+            if not os.path.exists(REF_SIMD_SO) and not build_ref_simd():
+                raise FileNotFoundError(REF_SIMD_SO)
+            self.lib = C.CDLL(REF_SIMD_SO)
             prefix = "ohref_"
         else:
             raise ValueError(which)
