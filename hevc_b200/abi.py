@@ -103,7 +103,57 @@ class SaoIn(C.Structure):
     ]
 
 
+class Coef(C.Structure):
+    _fields_ = [("pos", C.c_uint16), ("level", C.c_int16)]
+
+
+class TuQuant(C.Structure):
+    _fields_ = [("qp", C.c_uint8), ("matrix_id", C.c_uint8)]
+
+
+class CtbIndex(C.Structure):
+    _fields_ = [("first_pu", C.c_uint32), ("n_pu", C.c_uint32), ("first_tu", C.c_uint32), ("n_tu", C.c_uint32),
+                ("first_coef", C.c_uint32), ("n_coef", C.c_uint32)]
+
+
+class FrameArenas(C.Structure):
+    _fields_ = [
+        ("pus", C.c_void_p), ("max_pus", C.c_uint32), ("max_tus", C.c_uint32), ("tus", C.c_void_p),
+        ("quant", C.c_void_p), ("coefs", C.c_void_p), ("coeffs", C.c_void_p), ("max_coefs", C.c_uint64),
+        ("ctbs", C.c_void_p), ("slices", C.c_void_p), ("vertical_bs", C.c_void_p), ("horizontal_bs", C.c_void_p),
+        ("qp_y_tab", C.c_void_p), ("deblock", C.c_void_p), ("is_pcm", C.c_void_p), ("sao", C.c_void_p),
+        ("filter_slice_edges", C.c_void_p), ("tab_slice_address", C.c_void_p), ("tile_id", C.c_void_p),
+        ("deblock_disabled", C.c_void_p), ("scaling_list", C.c_void_p),
+    ]
+
+
+class FrameCounts(C.Structure):
+    _fields_ = [
+        ("n_pu", C.c_uint32), ("n_tu", C.c_uint32), ("n_coef", C.c_uint64), ("n_slices", C.c_int32),
+        ("coef_form", C.c_int32), ("deblock", C.c_int32), ("sao", C.c_int32), ("pcm", C.c_int32),
+        ("scaling_list", C.c_int32), ("all_inter", C.c_int32),
+    ]
+
+
+class PicParams(C.Structure):
+    _fields_ = [("pcm_or_bypass", C.c_int32), ("cb_qp_offset", C.c_int32), ("cr_qp_offset", C.c_int32),
+                ("no_tile_filter", C.c_int32)]
+
+
+NO_REF = 0xff
+COEF_DENSE, COEF_SPARSE, COEF_LEVELS = 1, 2, 3
+DEBLOCK_NONE, DEBLOCK_PLANES, DEBLOCK_DERIVED = 0, 1, 2
+
+# every struct of include/ohcu.h by its C name: tests/test_abi.py compares sizeof / offsetof with a C program
+STRUCTS = {
+    "ohcu_seq_params": SeqParams, "ohcu_slice_tab": SliceTab, "ohcu_pu": PU, "ohcu_tu": TU, "ohcu_dbparams": DBParams,
+    "ohcu_sao": SAO, "ohcu_deblock_in": DeblockIn, "ohcu_deblock_derive_in": DeblockDeriveIn, "ohcu_sao_in": SaoIn,
+    "ohcu_crop": Crop, "ohcu_coef": Coef, "ohcu_tu_quant": TuQuant, "ohcu_ctb_index": CtbIndex,
+    "ohcu_frame_arenas": FrameArenas, "ohcu_frame_counts": FrameCounts, "ohcu_pic_params": PicParams,
+}
+
 assert C.sizeof(PU) == 20 and C.sizeof(TU) == 20 and C.sizeof(SAO) == 40 and C.sizeof(DBParams) == 2
+assert C.sizeof(CtbIndex) == 24 and C.sizeof(Coef) == 4
 
 # name -> (restype, argtypes); every symbol include/ohcu.h declares
 _P = C.c_void_p
@@ -135,6 +185,11 @@ SYMBOLS = {
     "ohcu_set_deblock": (C.c_int, [_P, C.c_int, C.POINTER(DeblockIn)]),
     "ohcu_set_deblock_derived": (C.c_int, [_P, C.c_int, C.POINTER(DeblockDeriveIn)]),
     "ohcu_set_sao": (C.c_int, [_P, C.c_int, C.POINTER(SaoIn)]),
+    "ohcu_frame_arenas_get": (C.c_int, [_P, C.c_int, C.POINTER(FrameArenas)]),
+    "ohcu_frame_commit_lists": (C.c_int, [_P, C.c_int, C.POINTER(FrameCounts)]),
+    "ohcu_set_pic_params": (C.c_int, [_P, C.c_int, C.POINTER(PicParams)]),
+    "ohcu_append_pcm": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
+    "ohcu_slot_release": (C.c_int, [_P, C.c_int]),
     "ohcu_frame_flush": (C.c_int, [_P, C.c_int]),
     "ohcu_frame_abort": (C.c_int, [_P, C.c_int]),
     "ohcu_slot_pitch": (C.c_int, [_P, C.c_int, C.POINTER(C.c_ssize_t)]),

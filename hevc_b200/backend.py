@@ -9,7 +9,7 @@ import numpy as np
 
 from . import abi
 from .abi import check
-from .sparse import to_levels, to_sparse
+from .sparse import ctb_index, to_levels, to_sparse
 
 
 def _plane_args(planes):
@@ -170,6 +170,70 @@ class Context:
             s = fj.sao_in()
             check(lib.ohcu_set_sao(h, job_id, C.byref(s)), "ohcu_set_sao")
 
+    def append_inplace(self, job_id, fj, coeffs="sparse", levels=None, use_deblock=True, use_sao=True, derive_bs=None,
+                       all_inter=None, commit=True):
+        """The same lists through the ZERO-COPY path: ohcu_frame_arenas_get, records and tables written straight into
+        the job's pinned arenas (what the patched parser does), ohcu_frame_commit_lists.  Nothing is validated on
+        the host; prepare_kernel does it on the device.  coeffs = 'sparse' | 'dense'; levels as in append().
+        commit=False returns (arenas, counts) without committing (tests tamper with them first)."""
+        lib, h, sp = self.lib, self.handle, self.sp
+        hs = 1 if sp.chroma_format_idc in (1, 2) else 0
+        vs = 1 if sp.chroma_format_idc == 1 else 0
+        ctb_w = (sp.width + (1 << sp.log2_ctb_size) - 1) >> sp.log2_ctb_size
+        ctb_h = (sp.height + (1 << sp.log2_ctb_size) - 1) >> sp.log2_ctb_size
+        nctb = ctb_w * ctb_h
+        a = abi.FrameArenas()
+        check(lib.ohcu_frame_arenas_get(h, job_id, C.byref(a)), "ohcu_frame_arenas_get")
+
+        def put(dst, arr):
+            arr = np.ascontiguousarray(arr)
+            if arr.nbytes:
+                C.memmove(dst, arr.ctypes.data, arr.nbytes)
+
+        n = abi.FrameCounts()
+        quant = None
+        if len(fj.tus) and levels is not None:
+            recs, quant, pairs = levels[2] if len(levels) > 2 else to_levels(fj.tus, levels[0], fj.coeffs, sp.log2_ctb_size, hs, vs, ctb_w)
+            form = abi.COEF_LEVELS
+        elif len(fj.tus) and coeffs == "sparse":
+            recs, pairs = self.sparse_lists(fj)
+            form = abi.COEF_SPARSE
+        else:
+            recs, pairs, form = fj.tus, fj.coeffs, abi.COEF_DENSE if len(fj.tus) else 0
+        idx = ctb_index(fj.pus, recs, sp.log2_ctb_size, hs, vs, ctb_w, nctb,
+                        recs["pad"].astype(np.int64) if form >= abi.COEF_SPARSE else None)
+        assert len(fj.pus) <= a.max_pus and len(recs) <= a.max_tus
+        put(a.pus, fj.pus); put(a.tus, recs); put(a.coefs, pairs); put(a.ctbs, idx); put(a.slices, fj.slices)
+        if quant is not None:
+            put(a.quant, quant)
+        if levels is not None and levels[1] is not None:
+            sl, sl_dc = (np.ascontiguousarray(x, dtype=np.uint8) for x in levels[1])
+            put(a.scaling_list, sl); put(a.scaling_list + sl.nbytes, sl_dc)
+            n.scaling_list = 1
+        n.n_pu, n.n_tu, n.n_coef, n.n_slices, n.coef_form = len(fj.pus), len(recs), len(pairs), len(fj.slices), form
+        if use_deblock:
+            put(a.qp_y_tab, fj.qp_y_tab); put(a.deblock, fj.deblock)
+            if sp.pcm_or_bypass:
+                put(a.is_pcm, fj.is_pcm); n.pcm = 1
+            if derive_bs is not None and derive_bs is not False:
+                n.deblock = abi.DEBLOCK_DERIVED
+                dis = np.zeros(nctb, np.uint8) if derive_bs is True else np.ascontiguousarray(derive_bs, dtype=np.uint8)
+                put(a.deblock_disabled, dis)
+            else:
+                n.deblock = abi.DEBLOCK_PLANES
+                put(a.vertical_bs, fj.vbs); put(a.horizontal_bs, fj.hbs)
+        if use_sao or n.deblock == abi.DEBLOCK_DERIVED:
+            put(a.filter_slice_edges, fj.filter_slice_edges); put(a.tab_slice_address, fj.tab_slice_address)
+            put(a.tile_id, fj.tile_id)
+        if use_sao:
+            put(a.sao, fj.sao); n.sao = 1
+        if all_inter is None:
+            all_inter = int((fj.pus["w"].astype(np.int64) * fj.pus["h"]).sum()) == sp.width * sp.height
+        n.all_inter = int(bool(all_inter))
+        if not commit:
+            return a, n
+        check(lib.ohcu_frame_commit_lists(h, job_id, C.byref(n)), "ohcu_frame_commit_lists")
+
     def stage(self, job_id):
         check(self.lib.ohcu_frame_stage(self.handle, job_id), "ohcu_frame_stage")
 
@@ -227,7 +291,7 @@ class Context:
 
     # ---- convenience: one frame, synchronously (tests, smoke) -----------------
     def reconstruct(self, fj, refs, out_slot=None, out_init=None, stages=0, use_deblock=True, use_sao=True, sparse=False,
-                    levels=None, derive_bs=None):
+                    levels=None, derive_bs=None, inplace=False):
         """Upload refs to slots 0.., run one frame job, return the reconstructed planes."""
         if out_slot is None:
             out_slot = self.sp.dpb_slots - 1
@@ -237,7 +301,11 @@ class Context:
         if out_init is not None:
             self.upload(out_slot, out_init)
         j = self.begin(out_slot)
-        self.append(j, fj, use_deblock=use_deblock, use_sao=use_sao, sparse=sparse, levels=levels, derive_bs=derive_bs)
+        if inplace:
+            self.append_inplace(j, fj, coeffs="sparse" if sparse else "dense", levels=levels, use_deblock=use_deblock,
+                                use_sao=use_sao, derive_bs=derive_bs)
+        else:
+            self.append(j, fj, use_deblock=use_deblock, use_sao=use_sao, sparse=sparse, levels=levels, derive_bs=derive_bs)
         self.stage(j)
         self.launch(j, out_slot, stages)
         self.sync(j)

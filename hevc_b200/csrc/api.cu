@@ -49,6 +49,9 @@ struct Slot {
     bool has_ready = false, has_read = false;
     uint64_t readers = 0;             // jobs that read this slot since its last write
     uint8_t *out_d = nullptr;         // tight staging of ohcu_slot_output_cropped (allocated on first use)
+    int producer = -1;                // job that wrote the slot last (its error word is the slot's)
+    bool released = false;            // ohcu_slot_release: no picture to read until the slot is written again
+    int copy_lane = 0;                // which copy stream the slot's downloads use
 };
 
 template <typename T> struct Arena {      // pinned host staging + device copy
@@ -59,6 +62,7 @@ template <typename T> struct Arena {      // pinned host staging + device copy
 };
 
 constexpr size_t SL_BYTES = 4 * 6 * 64 + 2 * 6;      // ScalingList, hevc_ps.h:605-610
+constexpr int COPY_LANES = 4;
 
 struct Job {
     cudaStream_t stream = nullptr;
@@ -98,6 +102,17 @@ struct Job {
     Arena<uint8_t> vbs, hbs, is_pcm; Arena<int8_t> qp; Arena<ohcu_dbparams> db;
     Arena<ohcu_sao> sao;     Arena<uint16_t> sao_flags;
     bool has_deblock = false, has_sao = false, has_pcm = false;
+    ohcu_pic_params pp{};             // picture-level PPS fields of this frame (default: the context's)
+    // in-place lists (ohcu_frame_arenas_get / ohcu_frame_commit_lists): the parser wrote into the pinned arenas,
+    // prepare_kernel validates and indexes them on the device
+    Arena<ohcu_ctb_index> ctbs;
+    Arena<uint8_t> fse, dbk_disabled; Arena<int32_t> tsa, tile;
+    bool inplace = false; int all_inter = 0;
+    uint64_t n_coef_units = 0;        // pairs (sparse / levels) or int16 (dense) committed
+    int *err_d = nullptr, *err_h = nullptr;      // the job's error word (device) and its copy (pinned)
+    // PCM blocks (ohcu_append_pcm): allocated on first use
+    PcmRec *pcm_h = nullptr, *pcm_d = nullptr; int n_pcm = 0, pcm_cap = 0;
+    uint8_t *pcms_h = nullptr, *pcms_d = nullptr; size_t pcm_bytes = 0, pcms_cap = 0;
 };
 
 struct ohcu_ctx {
@@ -111,6 +126,7 @@ struct ohcu_ctx {
     std::vector<Job> jobs;
     int next_job = 0;
     cudaStream_t copy_stream = nullptr;
+    cudaStream_t copy_lanes[COPY_LANES] = {};    // downloads of different slots overlap (lane 0 = copy_stream)
     bool profiling = false;
     int64_t launches = 0;
     void *l2_buf = nullptr;
@@ -248,6 +264,12 @@ extern "C" int ohcu_destroy(ohcu_ctx *c)
         free_arena(&j.sao); free_arena(&j.sao_flags); free_arena(&j.tuq);
         if (j.sl_h) cudaFreeHost(j.sl_h);
         if (j.sl_d) cudaFree(j.sl_d);
+        if (j.err_h) cudaFreeHost(j.err_h);
+        if (j.err_d) cudaFree(j.err_d);
+        if (j.pcm_h) cudaFreeHost(j.pcm_h);
+        if (j.pcm_d) cudaFree(j.pcm_d);
+        if (j.pcms_h) cudaFreeHost(j.pcms_h);
+        if (j.pcms_d) cudaFree(j.pcms_d);
         if (j.tab_h) cudaFreeHost(j.tab_h);
         if (j.tab_d) cudaFree(j.tab_d);
         if (j.done) cudaEventDestroy(j.done);
@@ -257,6 +279,7 @@ extern "C" int ohcu_destroy(ohcu_ctx *c)
         if (j.side) cudaStreamDestroy(j.side);
         if (j.stream) cudaStreamDestroy(j.stream);
     }
+    for (int i = 1; i < COPY_LANES; i++) if (c->copy_lanes[i]) cudaStreamDestroy(c->copy_lanes[i]);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->l2_buf) cudaFree(c->l2_buf);
     if (c->t0) cudaEventDestroy(c->t0);
@@ -348,6 +371,10 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
         TRY(alloc_arena(&j.tuq, c->sp.max_tus));
         TRYCU(cudaHostAlloc((void **)&j.sl_h, SL_BYTES, cudaHostAllocDefault));
         TRYCU(cudaMalloc((void **)&j.sl_d, SL_BYTES));
+        TRYCU(cudaHostAlloc((void **)&j.err_h, sizeof(int), cudaHostAllocDefault));
+        TRYCU(cudaMalloc((void **)&j.err_d, sizeof(int)));
+        TRYCU(cudaMemset(j.err_d, 0, sizeof(int)));
+        *j.err_h = 0;
         // twice max_coeffs int16: the sparse form of a frame whose coefficients are all significant
         TRY(alloc_arena(&j.coeffs, 2 * (size_t)c->sp.max_coeffs));
         j.ctb_area.assign(c->nctb, 0);
@@ -357,6 +384,11 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
             carve_arena(&j.ctb_tu_range, c->nctb, j.tab_h, j.tab_d, &off);
             carve_arena(&j.ctb_coef_range, c->nctb, j.tab_h, j.tab_d, &off);
             carve_arena(&j.slices, OHCU_MAX_SLICES, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.ctbs, c->nctb, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.fse, c->nctb, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.dbk_disabled, c->nctb, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.tsa, c->nctb, j.tab_h, j.tab_d, &off);
+            carve_arena(&j.tile, c->nctb, j.tab_h, j.tab_d, &off);
             j.tab_end[0] = off;
             carve_arena(&j.sao, c->nctb, j.tab_h, j.tab_d, &off);
             carve_arena(&j.sao_flags, c->nctb, j.tab_h, j.tab_d, &off);
@@ -378,6 +410,9 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
         }
     }
     TRYCU(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    c->copy_lanes[0] = c->copy_stream;
+    for (int i = 1; i < COPY_LANES; i++) TRYCU(cudaStreamCreateWithFlags(&c->copy_lanes[i], cudaStreamNonBlocking));
+    for (size_t i = 0; i < c->slots.size(); i++) c->slots[i].copy_lane = (int)(i % COPY_LANES);
     TRY(build_tensor_maps(c));
 #undef TRY
 #undef TRYCU
@@ -416,6 +451,24 @@ static int check_slot(ohcu_ctx *c, int slot)
     return 0;
 }
 
+// The error word prepare_kernel left for a job (valid once the job's stream has drained).
+static int job_list_error(const ohcu_ctx *c, int job)
+{
+    const int e = *c->jobs[job].err_h;
+    if (!e) return 0;
+    return fail(OHCU_EINVAL, "job %d: %s %d); the frame was not reconstructed", job, prepare_error_text(e), (int)((unsigned)e >> 8));
+}
+static int slot_list_error(ohcu_ctx *c, int slot)
+{
+    int prod;
+    {
+        std::lock_guard<std::mutex> lock(c->mu);
+        prod = c->slots[slot].producer;
+        if (prod >= 0 && c->jobs[prod].out_slot != slot) prod = -1;      // the job moved on to another picture
+    }
+    return prod >= 0 ? job_list_error(c, prod) : 0;
+}
+
 extern "C" int ohcu_slot_upload(ohcu_ctx *c, int slot, const uint8_t *const planes[3], const ptrdiff_t strides[3])
 {
     ENTER(c);
@@ -437,6 +490,8 @@ extern "C" int ohcu_slot_upload(ohcu_ctx *c, int slot, const uint8_t *const plan
     c->launches++;
     s.has_ready = false;
     s.readers = 0;
+    s.producer = -1;
+    s.released = false;
     return 0;
 }
 
@@ -455,18 +510,20 @@ static int download_impl(ohcu_ctx *c, int slot, uint8_t *const planes[3], const 
     Slot &s = c->slots[slot];
     {
         std::lock_guard<std::mutex> lock(c->mu);
-        if (s.has_ready) CU(cudaStreamWaitEvent(c->copy_stream, s.ready, 0));
+        if (s.released) return fail(OHCU_ESTATE, "DPB slot %d was released and not written since", slot);
+        cudaStream_t cs = c->copy_lanes[s.copy_lane];       // downloads of one slot stay ordered on its lane
+        if (s.has_ready) CU(cudaStreamWaitEvent(cs, s.ready, 0));
         for (int i = 0; i < c->nplanes; i++) {
             // a host plane with the slot's own pitch (ohcu_slot_pitch) is one linear copy: the row
             // tails carry halo bytes, and the copy engine runs at full rate
             if (strides[i] == (ptrdiff_t)s.pic.ps.pitch[i])
                 CU(cudaMemcpyAsync(planes[i], s.pic.ps.p[i], (size_t)(c->ph[i] - 1) * s.pic.ps.pitch[i] + (size_t)c->pw[i] * c->P,
-                                   cudaMemcpyDeviceToHost, c->copy_stream));
+                                   cudaMemcpyDeviceToHost, cs));
             else
                 CU(cudaMemcpy2DAsync(planes[i], strides[i], s.pic.ps.p[i], s.pic.ps.pitch[i], (size_t)c->pw[i] * c->P,
-                                     c->ph[i], cudaMemcpyDeviceToHost, c->copy_stream));
+                                     c->ph[i], cudaMemcpyDeviceToHost, cs));
         }
-        CU(cudaEventRecord(s.read_done, c->copy_stream));
+        CU(cudaEventRecord(s.read_done, cs));
         s.has_read = true;
     }
     if (wait) CU(cudaEventSynchronize(s.read_done));
@@ -505,11 +562,13 @@ static int output_cropped_impl(ohcu_ctx *c, int slot, const ohcu_crop *crop, uin
     Slot &s = c->slots[slot];
     {
         std::lock_guard<std::mutex> lock(c->mu);
+        if (s.released) return fail(OHCU_ESTATE, "DPB slot %d was released and not written since", slot);
+        cudaStream_t cs = c->copy_lanes[s.copy_lane];
         if (!s.out_d) CU(cudaMalloc(&s.out_d, full));
-        if (s.has_ready) CU(cudaStreamWaitEvent(c->copy_stream, s.ready, 0));
+        if (s.has_ready) CU(cudaStreamWaitEvent(cs, s.ready, 0));
         uint8_t *dst[3] = {nullptr, nullptr, nullptr};
         for (int i = 0; i < c->nplanes; i++) dst[i] = s.out_d + off[i];
-        c->launches += launch_crop_pack(s.pic.ps, c->nplanes, c->P, left, top, w, h, dst, c->copy_stream);
+        c->launches += launch_crop_pack(s.pic.ps, c->nplanes, c->P, left, top, w, h, dst, cs);
         CU(cudaGetLastError());
         // planes that follow each other in the caller's memory the way they do in the staging
         // buffer leave as one copy
@@ -517,12 +576,12 @@ static int output_cropped_impl(ohcu_ctx *c, int slot, const ohcu_crop *crop, uin
         for (int i = 1; i < c->nplanes; i++) one = one && planes[i] == planes[0] + off[i];
         if (one) {
             CU(cudaMemcpyAsync(planes[0], s.out_d, off[c->nplanes - 1] + (size_t)w[c->nplanes - 1] * h[c->nplanes - 1] * c->P,
-                               cudaMemcpyDeviceToHost, c->copy_stream));
+                               cudaMemcpyDeviceToHost, cs));
         } else {
             for (int i = 0; i < c->nplanes; i++)
-                CU(cudaMemcpyAsync(planes[i], dst[i], (size_t)w[i] * h[i] * c->P, cudaMemcpyDeviceToHost, c->copy_stream));
+                CU(cudaMemcpyAsync(planes[i], dst[i], (size_t)w[i] * h[i] * c->P, cudaMemcpyDeviceToHost, cs));
         }
-        CU(cudaEventRecord(s.read_done, c->copy_stream));
+        CU(cudaEventRecord(s.read_done, cs));
         s.has_read = true;
     }
     if (wait) CU(cudaEventSynchronize(s.read_done));
@@ -548,6 +607,16 @@ extern "C" int ohcu_slot_sync(ohcu_ctx *c, int slot)
     }
     if (ready) CU(cudaEventSynchronize(s.ready));
     if (read) CU(cudaEventSynchronize(s.read_done));
+    return slot_list_error(c, slot);
+}
+
+// hevc_refs.c:131-166: the decoder is done with the picture in `slot`
+extern "C" int ohcu_slot_release(ohcu_ctx *c, int slot)
+{
+    ENTER(c);
+    if (check_slot(c, slot)) return OHCU_EINVAL;
+    std::lock_guard<std::mutex> lock(c->mu);
+    c->slots[slot].released = true;
     return 0;
 }
 
@@ -578,7 +647,23 @@ extern "C" int ohcu_frame_begin(ohcu_ctx *c, int out_slot, int poc)
     memset(j.ctb_tu_range.h, 0, sizeof(int2) * c->nctb);
     j.coef_form = 0; j.has_sl = false;
     std::fill(j.ctb_area.begin(), j.ctb_area.end(), 0);
+    j.pp.pcm_or_bypass = c->sp.pcm_or_bypass; j.pp.cb_qp_offset = c->sp.cb_qp_offset;
+    j.pp.cr_qp_offset = c->sp.cr_qp_offset; j.pp.no_tile_filter = c->sp.no_tile_filter;
+    j.inplace = false; j.all_inter = 0; j.n_coef_units = 0; j.n_pcm = 0; j.pcm_bytes = 0;
+    memset(j.ctbs.h, 0, sizeof(ohcu_ctb_index) * c->nctb);
+    *j.err_h = 0;
     return id;
+}
+
+extern "C" int ohcu_set_pic_params(ohcu_ctx *c, int job, const ohcu_pic_params *pp)
+{
+    ENTER(c);
+    if (check_job(c, job)) return OHCU_EINVAL;
+    Job &j = c->jobs[job];
+    if (!j.open) return fail(OHCU_ESTATE, "job %d is not open (call ohcu_frame_begin)", job);
+    if (!pp) return fail(OHCU_EINVAL, "null picture parameters");
+    j.pp = *pp;
+    return 0;
 }
 
 extern "C" int ohcu_frame_abort(ohcu_ctx *c, int job)
@@ -615,39 +700,25 @@ extern "C" int ohcu_append_pu(ohcu_ctx *c, int job, const ohcu_pu *recs, int n)
     ohcu_pu *const dst = j.pus.h + j.n_pu;
     int last = j.last_ctb, max_slice = j.max_slice;
     bool sorted = j.pu_sorted;
-    // PUs wider or taller than 32 are cut into <= 32x32 pieces with the same motion: prediction is
-    // per sample, so the result is the same, and the kernel's window pool can work in small slots
-    int o = 0;                                             // records written
     for (int i = 0; i < n; i++) {
         const ohcu_pu pu = recs[i];
+        // a block that is not 4-aligned or crosses a CTB boundary would leave the CTB's 16x16 cell map (mc_kernel)
         if (pu.pred_flag < 1 || pu.pred_flag > 3 || pu.w < 4 || pu.h < 4 || pu.w > 64 || pu.h > 64 ||
-            pu.x0 + pu.w > W || pu.y0 + pu.h > H || pu.slice >= OHCU_MAX_SLICES ||
-            pu.ref_idx[0] >= OHCU_MAX_REFS || pu.ref_idx[1] >= OHCU_MAX_REFS)
+            ((pu.x0 | pu.y0 | pu.w | pu.h) & 3) || pu.x0 + pu.w > W || pu.y0 + pu.h > H ||
+            (pu.x0 >> l2) != ((pu.x0 + pu.w - 1) >> l2) || (pu.y0 >> l2) != ((pu.y0 + pu.h - 1) >> l2) ||
+            pu.slice >= OHCU_MAX_SLICES || pu.ref_idx[0] >= OHCU_MAX_REFS || pu.ref_idx[1] >= OHCU_MAX_REFS)
             return fail(OHCU_EINVAL, "PU record %d is malformed", base + i);
         const int ctb = (pu.x0 >> l2) + (pu.y0 >> l2) * ctb_w;
-        const int pieces = ((pu.w + 31) >> 5) * ((pu.h + 31) >> 5);
-        if ((size_t)base + o + pieces > j.pus.cap) return fail(OHCU_EOVERFLOW, "PU arena full (%zu)", j.pus.cap);
         if (ctb != last) {
             if (range[ctb].y != 0) sorted = false;           // CTB seen before: lists not grouped
-            else range[ctb].x = base + o;
+            else range[ctb].x = base + i;
             last = ctb;
         }
-        range[ctb].y += pieces;
+        range[ctb].y++;
         area[ctb] += pu.w * pu.h;
         max_slice = std::max(max_slice, (int)pu.slice);
-        if (pieces == 1) {
-            dst[o++] = pu;
-        } else {
-            for (int yy = 0; yy < pu.h; yy += 32)
-                for (int xx = 0; xx < pu.w; xx += 32) {
-                    ohcu_pu sub = pu;
-                    sub.x0 = (uint16_t)(pu.x0 + xx); sub.y0 = (uint16_t)(pu.y0 + yy);
-                    sub.w = (uint8_t)std::min(32, pu.w - xx); sub.h = (uint8_t)std::min(32, pu.h - yy);
-                    dst[o++] = sub;
-                }
-        }
+        dst[i] = pu;
     }
-    n = o;
     j.last_ctb = last; j.pu_sorted = sorted; j.max_slice = max_slice;
     j.n_pu += n;
     return 0;
@@ -672,8 +743,10 @@ static int add_tus(ohcu_ctx *c, Job &j, const ohcu_tu *recs, int n, uint32_t reb
         if (l > 3u || tu.c_idx > max_c || tu.mode > OHCU_TU_BYPASS || (tu.mode == OHCU_TU_DST4 && l != 0))
             return fail(OHCU_EINVAL, "TU record %d is malformed", base + i);
         const int n1 = 1 << tu.log2_size;
-        if (tu.x0 + n1 > pw[tu.c_idx] || tu.y0 + n1 > ph[tu.c_idx])
-            return fail(OHCU_EINVAL, "TU record %d lies outside plane %d", base + i, tu.c_idx);
+        if (tu.x0 + n1 > pw[tu.c_idx] || tu.y0 + n1 > ph[tu.c_idx] || ((tu.x0 | tu.y0) & 3) ||
+            ((tu.x0 << ths[tu.c_idx]) >> l2) != (((tu.x0 + n1 - 1) << ths[tu.c_idx]) >> l2) ||
+            ((tu.y0 << tvs[tu.c_idx]) >> l2) != (((tu.y0 + n1 - 1) << tvs[tu.c_idx]) >> l2))
+            return fail(OHCU_EINVAL, "TU record %d lies outside plane %d, is not 4-aligned or crosses a CTB boundary", base + i, tu.c_idx);
         tu.coeff_off += rebase;
         if ((size_t)tu.coeff_off + (size_t)(n1 * n1) > ncoeff || (tu.coeff_off & 1))
             return fail(OHCU_EINVAL, "TU record %d: coefficient block outside the arena", base + i);
@@ -775,8 +848,10 @@ static int append_pairs(ohcu_ctx *c, int job, const ohcu_tu *recs, const ohcu_tu
         if (l > 3u || tu.c_idx > max_c || tu.mode > OHCU_TU_BYPASS || (tu.mode == OHCU_TU_DST4 && l != 0))
             return fail(OHCU_EINVAL, "TU record %d is malformed", base + i);
         const int n1 = 1 << tu.log2_size;
-        if (tu.x0 + n1 > pw[tu.c_idx] || tu.y0 + n1 > ph[tu.c_idx])
-            return fail(OHCU_EINVAL, "TU record %d lies outside plane %d", base + i, tu.c_idx);
+        if (tu.x0 + n1 > pw[tu.c_idx] || tu.y0 + n1 > ph[tu.c_idx] || ((tu.x0 | tu.y0) & 3) ||
+            ((tu.x0 << ths[tu.c_idx]) >> l2) != (((tu.x0 + n1 - 1) << ths[tu.c_idx]) >> l2) ||
+            ((tu.y0 << tvs[tu.c_idx]) >> l2) != (((tu.y0 + n1 - 1) << tvs[tu.c_idx]) >> l2))
+            return fail(OHCU_EINVAL, "TU record %d lies outside plane %d, is not 4-aligned or crosses a CTB boundary", base + i, tu.c_idx);
         if ((tu.coeff_off & 7) || tu.coeff_off + (uint32_t)(n1 * n1) > area || tu.pad > n1 * n1)
             return fail(OHCU_EINVAL, "TU record %d: block outside the CTB's coefficient area (%u)", base + i, area);
         const int ctb = ((tu.x0 << ths[tu.c_idx]) >> l2) + ((tu.y0 << tvs[tu.c_idx]) >> l2) * ctb_w;
@@ -841,7 +916,7 @@ extern "C" int ohcu_set_deblock(ohcu_ctx *c, int job, const ohcu_deblock_in *in)
     memcpy(j.hbs.h, in->horizontal_bs, (size_t)c->bs_w * c->bs_h);
     memcpy(j.qp.h, in->qp_y_tab, (size_t)c->min_cb_w * c->min_cb_h);
     memcpy(j.db.h, in->deblock, sizeof(ohcu_dbparams) * c->nctb);
-    j.has_pcm = c->sp.pcm_or_bypass && in->is_pcm;
+    j.has_pcm = j.pp.pcm_or_bypass && in->is_pcm;
     if (j.has_pcm) memcpy(j.is_pcm.h, in->is_pcm, (size_t)c->min_pu_w * c->min_pu_h);
     j.has_deblock = true;
     j.bs_derived = false;
@@ -856,7 +931,7 @@ extern "C" int ohcu_set_deblock_derived(ohcu_ctx *c, int job, const ohcu_deblock
     if (!in || !in->qp_y_tab || !in->deblock) return fail(OHCU_EINVAL, "null deblock input");
     memcpy(j.qp.h, in->qp_y_tab, (size_t)c->min_cb_w * c->min_cb_h);
     memcpy(j.db.h, in->deblock, sizeof(ohcu_dbparams) * c->nctb);
-    j.has_pcm = c->sp.pcm_or_bypass && in->is_pcm;
+    j.has_pcm = j.pp.pcm_or_bypass && in->is_pcm;
     if (j.has_pcm) memcpy(j.is_pcm.h, in->is_pcm, (size_t)c->min_pu_w * c->min_pu_h);
     const int cw = c->ctb_w;
     for (int rs = 0; rs < c->nctb; rs++) {
@@ -864,7 +939,7 @@ extern "C" int ohcu_set_deblock_derived(ohcu_ctx *c, int job, const ohcu_deblock
         const bool across = in->filter_slice_edges ? in->filter_slice_edges[rs] != 0 : true;
         auto differs = [&](int other) {
             return (in->tab_slice_address && in->tab_slice_address[rs] != in->tab_slice_address[other] && !across) ||
-                   (c->sp.no_tile_filter && in->tile_id && in->tile_id[rs] != in->tile_id[other]);
+                   (j.pp.no_tile_filter && in->tile_id && in->tile_id[rs] != in->tile_id[other]);
         };
         unsigned fl = 0;
         if (x > 0 && differs(rs - 1)) fl |= BSF_NO_LEFT;
@@ -884,7 +959,7 @@ extern "C" int ohcu_set_sao(ohcu_ctx *c, int job, const ohcu_sao_in *in)
     if (!in || !in->sao) return fail(OHCU_EINVAL, "null SAO input");
     memcpy(j.sao.h, in->sao, sizeof(ohcu_sao) * c->nctb);
     const int cw = c->ctb_w, chh = c->ctb_h;
-    const bool no_tile = c->sp.no_tile_filter != 0;
+    const bool no_tile = j.pp.no_tile_filter != 0;
     for (int y = 0; y < chh; y++)
         for (int x = 0; x < cw; x++) {
             const int rs = y * cw + x;
@@ -910,6 +985,72 @@ extern "C" int ohcu_set_sao(ohcu_ctx *c, int job, const ohcu_sao_in *in)
             j.sao_flags.h[rs] = (uint16_t)fl;
         }
     j.has_sao = true;
+    return 0;
+}
+
+// ------------------------------------------------------------------ in-place lists
+extern "C" int ohcu_frame_arenas_get(ohcu_ctx *c, int job, ohcu_frame_arenas *out)
+{
+    OPEN_JOB(c, job);
+    if (!out) return fail(OHCU_EINVAL, "null argument");
+    memset(out, 0, sizeof(*out));
+    out->pus = j.pus.h;       out->max_pus = (uint32_t)j.pus.cap;
+    out->tus = j.tus.h;       out->max_tus = (uint32_t)j.tus.cap;
+    out->quant = j.tuq.h;
+    out->coefs = (ohcu_coef *)j.coeffs.h;  out->coeffs = j.coeffs.h;  out->max_coefs = j.coeffs.cap / 2;
+    out->ctbs = j.ctbs.h;     out->slices = j.slices.h;
+    out->vertical_bs = j.vbs.h; out->horizontal_bs = j.hbs.h; out->qp_y_tab = j.qp.h; out->deblock = j.db.h;
+    out->is_pcm = j.is_pcm.h; out->sao = j.sao.h; out->filter_slice_edges = j.fse.h;
+    out->tab_slice_address = j.tsa.h; out->tile_id = j.tile.h; out->deblock_disabled = j.dbk_disabled.h;
+    out->scaling_list = j.sl_h;
+    return 0;
+}
+
+extern "C" int ohcu_frame_commit_lists(ohcu_ctx *c, int job, const ohcu_frame_counts *n)
+{
+    OPEN_JOB(c, job);
+    if (!n) return fail(OHCU_EINVAL, "null argument");
+    if (j.n_pu || j.n_tu) return fail(OHCU_ESTATE, "job %d already holds appended lists", job);
+    if (n->n_pu > j.pus.cap || n->n_tu > j.tus.cap) return fail(OHCU_EOVERFLOW, "lists larger than the job's arenas");
+    if (n->coef_form < 0 || n->coef_form > 3 || (n->n_tu && !n->coef_form)) return fail(OHCU_EINVAL, "bad coef_form %d", n->coef_form);
+    const uint64_t n16 = n->coef_form >= 2 ? 2 * n->n_coef : n->n_coef;
+    if (n16 > j.coeffs.cap || n16 > 0xffffffffull) return fail(OHCU_EOVERFLOW, "coefficient arena full (%zu int16)", j.coeffs.cap);
+    if (n->n_slices < 0 || n->n_slices > OHCU_MAX_SLICES || (n->n_pu && !n->n_slices)) return fail(OHCU_EINVAL, "bad n_slices %d", n->n_slices);
+    if (n->deblock < 0 || n->deblock > 2) return fail(OHCU_EINVAL, "bad deblock mode %d", n->deblock);
+    j.n_pu = (int)n->n_pu; j.n_tu = (int)n->n_tu; j.n_slices = n->n_slices;
+    j.ncoeff = (size_t)n16; j.n_coef_units = n->n_coef; j.coef_form = n->n_tu ? n->coef_form : 0;
+    j.has_sl = n->scaling_list != 0;
+    j.has_deblock = n->deblock != 0; j.bs_derived = n->deblock == OHCU_DEBLOCK_DERIVED;
+    j.has_sao = n->sao != 0; j.has_pcm = j.pp.pcm_or_bypass && n->pcm;
+    j.all_inter = n->all_inter != 0; j.all_covered = j.all_inter && n->n_pu > 0;
+    j.inplace = true;
+    return 0;
+}
+
+// ---- PCM samples (hls_pcm_sample -> put_pcm): arenas allocated when a stream first uses PCM
+extern "C" int ohcu_append_pcm(ohcu_ctx *c, int job, int x0, int y0, int log2_size, int c_idx, const void *samples)
+{
+    OPEN_JOB(c, job);
+    const int n = 1 << log2_size;
+    if (!samples || log2_size < 2 || log2_size > 5 || c_idx < 0 || c_idx >= c->nplanes || x0 < 0 || y0 < 0 ||
+        x0 + n > c->pw[c_idx] || y0 + n > c->ph[c_idx])
+        return fail(OHCU_EINVAL, "PCM block %dx%d at (%d, %d) of plane %d is malformed", n, n, x0, y0, c_idx);
+    if (!j.pcm_h) {
+        const size_t nsamp = (size_t)c->pw[0] * c->ph[0] + (c->nplanes == 3 ? 2 * (size_t)c->pw[1] * c->ph[1] : 0);
+        j.pcm_cap = (int)(nsamp / 16 + 1);
+        j.pcms_cap = nsamp * c->P;
+        CU(cudaHostAlloc((void **)&j.pcm_h, sizeof(PcmRec) * j.pcm_cap, cudaHostAllocDefault));
+        CU(cudaMalloc((void **)&j.pcm_d, sizeof(PcmRec) * j.pcm_cap));
+        CU(cudaHostAlloc((void **)&j.pcms_h, j.pcms_cap, cudaHostAllocDefault));
+        CU(cudaMalloc((void **)&j.pcms_d, j.pcms_cap));
+    }
+    const size_t bytes = (size_t)n * n * c->P;
+    if (j.n_pcm >= j.pcm_cap || j.pcm_bytes + bytes > j.pcms_cap) return fail(OHCU_EOVERFLOW, "PCM arena full");
+    PcmRec r{};
+    r.x0 = (uint16_t)x0; r.y0 = (uint16_t)y0; r.log2_size = (uint8_t)log2_size; r.c_idx = (uint8_t)c_idx; r.off = (uint32_t)j.pcm_bytes;
+    j.pcm_h[j.n_pcm++] = r;
+    memcpy(j.pcms_h + j.pcm_bytes, samples, bytes);
+    j.pcm_bytes += (bytes + 15) & ~(size_t)15;
     return 0;
 }
 
@@ -954,6 +1095,7 @@ static void sort_tus_by_ctb(ohcu_ctx *c, Job &j)
 }
 
 static int stage_impl(ohcu_ctx *c, int job);
+static void fill_frame_dev(const ohcu_ctx *c, const Job &j, FrameDev *f);
 // A stage that fails discards the job's lists (the job can be begun again).
 extern "C" int ohcu_frame_stage(ohcu_ctx *c, int job)
 {
@@ -964,10 +1106,10 @@ extern "C" int ohcu_frame_stage(ohcu_ctx *c, int job)
 static int stage_impl(ohcu_ctx *c, int job)
 {
     OPEN_JOB(c, job);
-    if (!j.pu_sorted) sort_pus_by_ctb(c, j);
-    if (!j.tu_sorted) sort_tus_by_ctb(c, j);
+    if (!j.inplace && !j.pu_sorted) sort_pus_by_ctb(c, j);
+    if (!j.inplace && !j.tu_sorted) sort_tus_by_ctb(c, j);
     // CTBs whose PUs cover all of their samples need no read of the picture before MC
-    {
+    if (!j.inplace) {
         const int cs = 1 << c->sp.log2_ctb_size;
         j.all_covered = j.n_pu > 0;
         for (int y = 0; y < c->ctb_h; y++)
@@ -983,8 +1125,18 @@ static int stage_impl(ohcu_ctx *c, int job)
                 else j.all_covered = false;
             }
     }
-    if (j.max_slice >= j.n_slices) return fail(OHCU_EINVAL, "a PU uses slice %d which was never set", j.max_slice);
-    for (int i = 0; j.has_cross && i < j.n_tu; i++)
+    if (!j.inplace && j.max_slice >= j.n_slices) return fail(OHCU_EINVAL, "a PU uses slice %d which was never set", j.max_slice);
+    // every reference a PU names must be a DPB slot
+    for (int i = 0; !j.inplace && i < j.n_pu; i++) {
+        const ohcu_pu &pu = j.pus.h[i];
+        for (int l = 0; l < 2; l++)
+            if (pu.pred_flag & (1 << l)) {
+                const int slot = j.slices.h[pu.slice].ref_slot[l][pu.ref_idx[l]];
+                if (slot >= (int)c->slots.size())
+                    return fail(OHCU_EINVAL, "PU record %d: list %d, ref_idx %d names DPB slot %d (of %zu)", i, l, pu.ref_idx[l], slot, c->slots.size());
+            }
+    }
+    for (int i = 0; !j.inplace && j.has_cross && i < j.n_tu; i++)
         if ((j.tus.h[i].flags & OHCU_TUF_CROSS) &&
             (j.tus.h[i].cross_tu >= (uint32_t)j.n_tu || j.tus.h[j.tus.h[i].cross_tu].log2_size != j.tus.h[i].log2_size))
             return fail(OHCU_EINVAL, "TU %d: bad cross-component reference", i);
@@ -993,7 +1145,7 @@ static int stage_impl(ohcu_ctx *c, int job)
     CU(push_arena(j.tus, j.n_tu, st));
     CU(push_arena(j.coeffs, j.ncoeff, st));
     if (j.coef_form == 3) {
-        for (int i = 0; !j.has_sl && i < j.n_tu; i++)
+        for (int i = 0; !j.inplace && !j.has_sl && i < j.n_tu; i++)
             if (j.tuq.h[i].matrix_id != OHCU_QM_FLAT) return fail(OHCU_EINVAL, "TU %d names a scaling list but none was set", i);
         CU(push_arena(j.tuq, j.n_tu, st));
         if (j.has_sl) CU(cudaMemcpyAsync(j.sl_d, j.sl_h, SL_BYTES, cudaMemcpyHostToDevice, st));
@@ -1001,6 +1153,29 @@ static int stage_impl(ohcu_ctx *c, int job)
     // the tables: one copy up to the last group this frame uses
     const size_t tab_bytes = j.tab_end[j.has_pcm ? 4 : j.has_deblock ? (j.bs_derived ? 2 : 3) : j.has_sao ? 1 : 0];
     CU(cudaMemcpyAsync(j.tab_d, j.tab_h, tab_bytes, cudaMemcpyHostToDevice, st));
+    if (j.n_pcm) {
+        CU(cudaMemcpyAsync(j.pcm_d, j.pcm_h, sizeof(PcmRec) * j.n_pcm, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(j.pcms_d, j.pcms_h, j.pcm_bytes, cudaMemcpyHostToDevice, st));
+    }
+    CU(cudaMemsetAsync(j.err_d, 0, sizeof(int), st));
+    if (j.inplace) {
+        // validation, per-CTB ranges and flags on the device (prepare.cu)
+        FrameDev f;
+        fill_frame_dev(c, j, &f);
+        PrepDev p{};
+        p.idx = j.ctbs.d; p.pu_range = j.ctb_range.d; p.tu_range = j.ctb_tu_range.d; p.coef_range = j.ctb_coef_range.d;
+        p.sao_flags = j.sao_flags.d; p.bs_flags = j.bs_flags.d;
+        p.fse = j.fse.d; p.tsa = j.tsa.d; p.tile = j.tile.d; p.dbk_disabled = j.dbk_disabled.d;
+        p.err = j.err_d;
+        p.n_pu = (uint32_t)j.n_pu; p.n_tu = (uint32_t)j.n_tu; p.n_coef = j.n_coef_units;
+        p.n_slices = j.n_slices; p.coef_form = j.coef_form; p.dpb_slots = (int)c->slots.size(); p.out_slot = j.out_slot;
+        p.all_inter = j.all_inter; p.no_tile_filter = j.pp.no_tile_filter; p.has_sao = j.has_sao; p.derive = j.bs_derived;
+        p.area = recon_sparse_ctb_coefs(c->sp.log2_ctb_size, c->nplanes, c->hs, c->vs); p.has_sl = j.has_sl;
+        launch_prepare(f, p, st);
+        CU(cudaGetLastError());
+        std::lock_guard<std::mutex> lock(c->mu);
+        c->launches++;
+    }
     j.open = false;
     j.staged = true;
     // the pinned staging is reusable once this event has fired
@@ -1021,6 +1196,8 @@ static void fill_frame_dev(const ohcu_ctx *c, const Job &j, FrameDev *f)
     f->is_pcm = j.has_pcm ? j.is_pcm.d : nullptr;
     f->bs_ctb_flags = j.has_deblock && j.bs_derived ? j.bs_flags.d : nullptr;
     f->sao = j.has_sao ? j.sao.d : nullptr; f->sao_ctb_flags = j.sao_flags.d;
+    f->pcm_or_bypass = j.pp.pcm_or_bypass; f->cb_qp_offset = j.pp.cb_qp_offset; f->cr_qp_offset = j.pp.cr_qp_offset;
+    f->err = j.err_d;
 }
 
 // stages: bit mask 1 MC, 2 residual, 4 deblock, 8 SAO (0 = all).  Test / bench hook behind
@@ -1090,6 +1267,8 @@ extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int 
     LAUNCHED(launch_recon(f, stages & 1, st));
     STAGE_EVENT(1);
     LAUNCHED(launch_recon(f, stages & 2, st));
+    // PCM blocks replace prediction + residual of their samples (put_pcm), ahead of the loop filters
+    if ((stages & 2) && j.n_pcm) LAUNCHED(launch_pcm(f, j.pcm_d, j.n_pcm, j.pcms_d, st));
     STAGE_EVENT(2);
     // deblocking and SAO run fused (loopfilter.cu); stage 3 carries their time
     if (derive) CU(cudaStreamWaitEvent(st, j.join, 0));
@@ -1102,6 +1281,9 @@ extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int 
 #undef LAUNCHED
     j.timed = timed;
     c->launches += total;
+    // the job's error word travels back with its results (read by ohcu_frame_sync / ohcu_slot_sync)
+    if (j.inplace) CU(cudaMemcpyAsync(j.err_h, j.err_d, sizeof(int), cudaMemcpyDeviceToHost, st));
+    os.producer = job; os.released = false;
     CU(cudaEventRecord(j.done, st));
     j.has_done = true;
     CU(cudaEventRecord(os.ready, st));
@@ -1126,7 +1308,7 @@ extern "C" int ohcu_frame_sync(ohcu_ctx *c, int job)
     ENTER(c);
     if (check_job(c, job)) return OHCU_EINVAL;
     CU(cudaStreamSynchronize(c->jobs[job].stream));
-    return 0;
+    return job_list_error(c, job);
 }
 
 extern "C" int ohcu_sync_all(ohcu_ctx *c)
@@ -1209,6 +1391,8 @@ extern "C" int ohcu_timer_stop(ohcu_ctx *c, float *ms)
     if (!c->t0 || !ms) return fail(OHCU_ESTATE, "timer not started");
     for (auto &j : c->jobs)
         if (j.has_done) CU(cudaStreamWaitEvent(c->copy_stream, j.done, 0));
+    for (auto &s : c->slots)
+        if (s.has_read) CU(cudaStreamWaitEvent(c->copy_stream, s.read_done, 0));
     CU(cudaEventRecord(c->t1, c->copy_stream));
     CU(cudaEventSynchronize(c->t1));
     CU(cudaEventElapsedTime(ms, c->t0, c->t1));

@@ -60,6 +60,7 @@ __device__ int bs_motion(const FrameDev &f, const ohcu_pu &c, const ohcu_pu &n)
 __global__ void __launch_bounds__(BS_THREADS) bs_kernel(const __grid_constant__ FrameDev f, uint8_t *vbs, uint8_t *hbs)
 {
     __shared__ BsCell cell[BS_CELLS * BS_CELLS];          // [1 + y][1 + x], row / column 0 = the neighbours' last cells
+    if (f.err && *f.err) return;                          // malformed lists (prepare.cu)
     const int tid = threadIdx.x;
     const int ctb = blockIdx.x, ctbx = ctb % f.ctb_w, ctby = ctb / f.ctb_w;
     const int cs = 1 << f.log2_ctb, n4 = cs >> 2;

@@ -496,6 +496,7 @@ __global__ void __launch_bounds__(LF_THREADS, LF_MINB) loopfilter_kernel(const _
     long long lf_t = clock64();
 #endif
     constexpr int AX = 16 / (int)sizeof(pixel);           // samples per 16 bytes: TMA boxes start on them
+    if (f.err && *f.err) return;                          // malformed lists (prepare.cu)
     const int tid = threadIdx.x;
     const int bd = f.bd;
     const int np = f.nplanes;

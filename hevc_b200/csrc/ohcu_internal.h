@@ -61,7 +61,31 @@ struct FrameDev {
     // SAO
     const ohcu_sao *sao;
     const uint16_t *sao_ctb_flags;   // per CTB, see SAOF_* below
+    // the job's error word (prepare.cu): non-zero = the lists are malformed, every kernel of the frame returns at once
+    const int *err;
 };
+
+// ---- in-place lists: what prepare_kernel reads and writes besides FrameDev (prepare.cu)
+struct PrepDev {
+    const ohcu_ctb_index *idx;       // per CTB: where its records sit (written by the parser)
+    int2 *pu_range, *tu_range, *coef_range;      // out: FrameDev::ctb_pu_range / ctb_tu_range / ctb_coef_range
+    uint16_t *sao_flags;             // out: FrameDev::sao_ctb_flags
+    uint8_t *bs_flags;               // out: FrameDev::bs_ctb_flags
+    const uint8_t *fse;              // slice_loop_filter_across_slices_enabled_flag per CTB (nullptr = 1)
+    const int32_t *tsa, *tile;       // tab_slice_address / tile id per CTB (nullptr = one slice / tile)
+    const uint8_t *dbk_disabled;     // slice_deblocking_filter_disabled_flag per CTB (nullptr = 0)
+    int *err;
+    uint32_t n_pu, n_tu;
+    uint64_t n_coef;
+    int n_slices, coef_form, dpb_slots, out_slot, all_inter, no_tile_filter, has_sao, derive, area, has_sl;
+};
+enum { PE_INDEX = 1, PE_PU, PE_TU, PE_OVERLAP, PE_NOT_COVERED, PE_PAIRS };
+int launch_prepare(const FrameDev &f, const PrepDev &p, cudaStream_t st);
+const char *prepare_error_text(int code);
+
+// PCM samples of one block (ohcu_append_pcm): plane coordinates, byte offset of its samples in the job's arena
+struct PcmRec { uint16_t x0, y0; uint8_t log2_size, c_idx; uint16_t pad; uint32_t off; };
+int launch_pcm(const FrameDev &f, const PcmRec *recs, int n, const uint8_t *samples, cudaStream_t st);
 
 // set in ctb_pu_range[].y when the CTB's PUs cover every sample of it
 constexpr int CTB_COVERED = 1 << 30;

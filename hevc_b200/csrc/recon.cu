@@ -955,6 +955,7 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) residual_kernel(const __g
     const int2 trange = f.ctb_tu_range[ctb];
     const int t0 = trange.x, nt = min(trange.y, MAX_CTB_TUS);
     if (nt == 0) return;                      // nothing to add to this CTB
+    if (f.err && *f.err) return;              // malformed lists (prepare.cu)
 
     // ---- phase 0: the CTB's samples (the prediction, or whatever the picture holds) enter the tile
     {
@@ -1197,6 +1198,7 @@ __global__ void __launch_bounds__(RC_THREADS, MC_MINB) mc_kernel(const __grid_co
     const int2 prange = f.ctb_pu_range[ctb];
     const int p0 = prange.x, np = min(prange.y & 0xffffff, MAX_CTB_PUS);
     if (np == 0) return;
+    if (f.err && *f.err) return;              // malformed lists (prepare.cu)
     if (tid < CMAP_STRIDE * CMAP_STRIDE / 4) ((uint32_t *)cmap)[tid] = 0xffffffffu;
     __syncthreads();
     build_pu_records(f, recs, cmap, p0, np, cx0, cy0, bd, tid);

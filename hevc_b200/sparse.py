@@ -63,3 +63,46 @@ def to_levels(tus, quant, levels, log2_ctb, hs, vs, ctb_w):
     """(recs, quant_in_record_order, pairs) of a dense arena of un-scaled levels."""
     recs, pairs, order = to_sparse(tus, levels, log2_ctb, hs, vs, ctb_w, return_order=True)
     return recs, np.ascontiguousarray(np.asarray(quant)[order]), pairs
+
+
+# ---- the in-place form (ohcu_frame_arenas_get / ohcu_frame_commit_lists): where each CTB's records sit
+CTB_INDEX_DTYPE = np.dtype([("first_pu", "<u4"), ("n_pu", "<u4"), ("first_tu", "<u4"), ("n_tu", "<u4"),
+                            ("first_coef", "<u4"), ("n_coef", "<u4")])
+
+
+def _runs(ctb, nctb, what):
+    """first record and record count per CTB of a list grouped by CTB"""
+    first = np.zeros(nctb, np.uint32)
+    count = np.bincount(ctb, minlength=nctb).astype(np.uint32)
+    if len(ctb):
+        starts = np.flatnonzero(np.r_[True, ctb[1:] != ctb[:-1]])
+        if len(starts) != len(np.unique(ctb)):
+            raise ValueError(f"the {what} list is not grouped by CTB")
+        first[ctb[starts]] = starts
+    return first, count
+
+
+def group_by_ctb(recs, ctb):
+    """stable grouping of a record list by CTB (what a parser's CTB walk gives for free)"""
+    if len(ctb) and len(np.unique(ctb)) != 1 + np.count_nonzero(np.diff(ctb)):
+        order = np.argsort(ctb, kind="stable")
+        return recs[order].copy(), ctb[order], order
+    return recs, ctb, None
+
+
+def ctb_index(pus, recs, log2_ctb, hs, vs, ctb_w, nctb, pairs_per_tu=None):
+    """The ohcu_ctb_index array a parser fills while it walks the CTBs: PU list, TU list (records as handed to the
+    library) and, for the sparse / levels forms, the pairs (recs['pad'] per block)."""
+    idx = np.zeros(nctb, CTB_INDEX_DTYPE)
+    pc = ((pus["x0"].astype(np.int64) >> log2_ctb) + (pus["y0"].astype(np.int64) >> log2_ctb) * ctb_w) if len(pus) else np.zeros(0, np.int64)
+    idx["first_pu"], idx["n_pu"] = _runs(pc, nctb, "PU")
+    if len(recs):
+        tc = ctb_of_tus(recs, log2_ctb, hs, vs, ctb_w)
+        idx["first_tu"], idx["n_tu"] = _runs(tc, nctb, "TU")
+        if pairs_per_tu is not None:
+            per_ctb = np.bincount(tc, weights=pairs_per_tu, minlength=nctb).astype(np.uint32)
+            before = np.cumsum(pairs_per_tu) - pairs_per_tu
+            idx["n_coef"] = per_ctb
+            has = idx["n_tu"] > 0
+            idx["first_coef"][has] = before[idx["first_tu"][has]]
+    return idx

@@ -340,6 +340,100 @@ int ohcu_append_tu_levels(ohcu_ctx *ctx, int job, const ohcu_tu *recs,
 int ohcu_set_scaling_list(ohcu_ctx *ctx, int job, const uint8_t sl[4][6][64],
                           const uint8_t sl_dc[2][6]);
 
+/* ======================================================================== */
+/* In-place work lists (zero-copy host path)                                */
+/* ======================================================================== */
+/* The append calls above validate and copy every record on the submitting thread (1.5 ms of
+ * host time per 4K frame).  The reference's parser threads share nothing per frame and write
+ * their results straight into per-thread / per-frame arrays (HEVCLocalContext, hevcdec.h:508-510;
+ * s->sao, s->deblock, s->qp_y_tab, s->vertical_bs ... of pic_arrays_init, hevcdec.c:114-200).
+ * The in-place path gives the patched call sites those arrays INSIDE the job's pinned staging:
+ *   ohcu_frame_begin -> ohcu_frame_arenas_get (pointers) -> the parser fills records and tables in
+ *   place, noting for every CTB it finishes where its records sit (ohcu_ctb_index, the CTB order
+ *   of hls_decode_entry / hls_coding_quadtree, hevcdec.c:2864-2910) -> ohcu_frame_commit_lists
+ *   (counts only) -> ohcu_frame_flush.
+ * Nothing is copied or checked on the host.  A prepare kernel on the job's stream validates every
+ * record (bounds, alignment, CTB membership, reference slots, coefficient areas), derives the
+ * per-CTB ranges, the covered-CTB flags and the SAO / bs CTB flags that ohcu_set_sao and
+ * ohcu_set_deblock_derived compute on the host, and on a malformed list sets the job's error word:
+ * the job's kernels then do nothing and ohcu_frame_sync / ohcu_slot_sync of its output slot return
+ * OHCU_EINVAL with the offending record in ohcu_last_error().                            */
+typedef struct ohcu_ctb_index {      /* per CTB, raster order; zeroed by ohcu_frame_begin      */
+    uint32_t first_pu, n_pu;         /* the CTB's PUs in arenas.pus (<= 128; PUs up to 64x64)   */
+    uint32_t first_tu, n_tu;         /* its coded TBs in arenas.tus (<= 768)                    */
+    uint32_t first_coef, n_coef;     /* sparse / levels: its ohcu_coef pairs in arenas.coefs    */
+} ohcu_ctb_index;                    /* 24 bytes */
+
+typedef struct ohcu_frame_arenas {
+    ohcu_pu        *pus;             uint32_t max_pus;
+    uint32_t        max_tus;
+    ohcu_tu        *tus;
+    ohcu_tu_quant  *quant;           /* levels form: parallel to tus                            */
+    ohcu_coef      *coefs;           /* sparse / levels form: pairs, CTB after CTB              */
+    int16_t        *coeffs;          /* dense form: the same memory seen as int16 (tu.coeff_off
+                                        absolute, a multiple of 8)                              */
+    uint64_t        max_coefs;       /* capacity in pairs (= 2 int16 each)                      */
+    ohcu_ctb_index *ctbs;            /* ctb_width * ctb_height                                  */
+    ohcu_slice_tab *slices;          /* OHCU_MAX_SLICES; ref_slot entries not in use = OHCU_NO_REF */
+    uint8_t        *vertical_bs, *horizontal_bs;      /* as ohcu_deblock_in                     */
+    int8_t         *qp_y_tab;
+    ohcu_dbparams  *deblock;
+    uint8_t        *is_pcm;
+    ohcu_sao       *sao;             /* as ohcu_sao_in / ohcu_deblock_derive_in, per CTB:       */
+    uint8_t        *filter_slice_edges;
+    int32_t        *tab_slice_address;
+    int32_t        *tile_id;
+    uint8_t        *deblock_disabled;
+    uint8_t        *scaling_list;    /* sl[4][6][64] then sl_dc[2][6] (1548 bytes)              */
+} ohcu_frame_arenas;
+
+#define OHCU_NO_REF       0xff       /* ohcu_slice_tab.ref_slot entry that names no picture     */
+#define OHCU_COEF_DENSE   1
+#define OHCU_COEF_SPARSE  2
+#define OHCU_COEF_LEVELS  3
+#define OHCU_DEBLOCK_NONE    0
+#define OHCU_DEBLOCK_PLANES  1       /* vertical_bs / horizontal_bs were written                */
+#define OHCU_DEBLOCK_DERIVED 2       /* bs derived on the device (ohcu_set_deblock_derived)     */
+
+typedef struct ohcu_frame_counts {
+    uint32_t n_pu, n_tu;
+    uint64_t n_coef;                 /* pairs (sparse / levels) or int16 (dense) written        */
+    int32_t  n_slices;
+    int32_t  coef_form;              /* OHCU_COEF_*; 0 = no coded block                         */
+    int32_t  deblock;                /* OHCU_DEBLOCK_*                                          */
+    int32_t  sao;                    /* sao / filter_slice_edges / tab_slice_address / tile_id written */
+    int32_t  pcm;                    /* is_pcm written (used when the picture's pcm_or_bypass is set)  */
+    int32_t  scaling_list;           /* scaling_list written                                    */
+    int32_t  all_inter;              /* the caller's promise that the PUs cover every sample (a P / B
+                                        picture without intra CUs): the slot's previous content is then
+                                        not carried over.  Checked on the device.                */
+} ohcu_frame_counts;
+
+int ohcu_frame_arenas_get(ohcu_ctx *ctx, int job, ohcu_frame_arenas *out);
+int ohcu_frame_commit_lists(ohcu_ctx *ctx, int job, const ohcu_frame_counts *counts);
+
+/* Picture-level parameters the reference reads from the active PPS for EACH picture
+ * (hevc_filter.c:72, :281-282, :541-543; hevcdec.c:2822-2837).  ohcu_create takes the stream's
+ * initial values in ohcu_seq_params; a picture whose PPS differs overrides them for its job
+ * (between ohcu_frame_begin and ohcu_frame_flush, before ohcu_set_sao / ohcu_set_deblock_derived).  */
+typedef struct ohcu_pic_params {
+    int32_t pcm_or_bypass, cb_qp_offset, cr_qp_offset, no_tile_filter;
+} ohcu_pic_params;
+int ohcu_set_pic_params(ohcu_ctx *ctx, int job, const ohcu_pic_params *pp);
+
+/* PCM samples (a22): hls_pcm_sample -> put_pcm (hevcdec.c:1686-1721, hevcdsp_template.c:30-43).  The
+ * bit reader stays on the host; what it produced - the N x N samples of one plane, already shifted to
+ * the picture's bit depth (<< (BIT_DEPTH - pcm_bit_depth), template :39) - is placed in the picture
+ * after prediction + residual and before the loop filters (whose is_pcm / pcm_loop_filter_disable
+ * handling is ohcu_deblock_in.is_pcm).  samples: w*h values, uint8_t for 8-bit pictures, uint16_t above,
+ * row-major; copied before return.                                                          */
+int ohcu_append_pcm(ohcu_ctx *ctx, int job, int x0, int y0, int log2_size, int c_idx, const void *samples);
+
+/* hevc_refs.c:131-166 (ff_hevc_unref_frame / ff_hevc_clear_refs): the decoder no longer needs the
+ * picture in `slot`.  Reads of the slot fail with OHCU_ESTATE until it is written again; the memory
+ * stays allocated (the DPB is a fixed pool).                                                  */
+int ohcu_slot_release(ohcu_ctx *ctx, int slot);
+
 /* replaces the per-edge calls of deblocking_filter_CTB (hevc_filter.c:588-599,
  * 634-654, 686-697, 735-755).  Arrays are copied before return.  Not calling it
  * for a frame = no deblocking (all bs zero).                                    */
@@ -354,8 +448,10 @@ int ohcu_set_sao(ohcu_ctx *ctx, int job, const ohcu_sao_in *in);
 
 /* End of frame (where ff_hevc_hls_filter ran per CTB, hevc_filter.c:1211-1245):
  * upload the job's lists (async, pinned) and enqueue the batched launches
- *   MC + residual add (one kernel) -> deblock + SAO (one kernel) -> halo fill
- * on the job's stream.  Returns without waiting.                                 */
+ *   [prepare (in-place lists)] -> mc_kernel -> residual_kernel -> [pcm] ->
+ *   loopfilter_kernel (deblock + SAO fused) -> pad_kernel (halo fill)
+ * on the job's stream ([bs_kernel] beside the first two on a side stream when the boundary
+ * strengths are derived).  Returns without waiting.                              */
 int ohcu_frame_flush(ohcu_ctx *ctx, int job);
 
 /* Split form of flush, used by bench.py to time the launches with the lists

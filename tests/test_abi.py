@@ -36,3 +36,22 @@ def test_create_fails_loudly_without_device_or_with_bad_params():
     sp.bit_depth = 8
     if lib.ohcu_device_count() == 0:
         assert lib.ohcu_create(C.byref(h), 0, C.byref(sp)) == -5       # ENODEV, never a CPU fallback
+
+
+def test_struct_layout_matches_the_c_header(tmp_path):
+    """sizeof / offsetof of every struct of include/ohcu.h as the C compiler sees them (tests/c/abi_layout.c, plain
+    C99) against the ctypes mirror in hevc_b200/abi.py"""
+    import ctypes as C
+    import json
+    import subprocess
+    exe = str(tmp_path / "abi_layout")
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "c", "abi_layout.c"), "-o", exe])
+    layout = json.loads(subprocess.check_output([exe]))
+    text = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "ohcu.h")).read(), flags=re.S)
+    declared = set(re.findall(r"}\s*(ohcu_[a-z0-9_]+)\s*;", text))
+    assert declared == set(layout) == set(abi.STRUCTS), "a struct of ohcu.h is missing from abi_layout.c or abi.STRUCTS"
+    for name, cls in abi.STRUCTS.items():
+        assert C.sizeof(cls) == layout[name]["sizeof"], name
+        offs = {f[0]: getattr(cls, f[0]).offset for f in cls._fields_}
+        assert offs == layout[name]["fields"], f"{name}: {offs} != {layout[name]['fields']}"
