@@ -15,6 +15,7 @@ OHCU_ABI_VERSION = 1
 MAX_REFS = 16
 MAX_DPB = 32
 MAX_SLICES = 64
+NOALLOC_MAX_BYTES = 65536
 
 PF_L0, PF_L1, PF_BI = 1, 2, 3
 SAO_NOT_APPLIED, SAO_BAND, SAO_EDGE = 0, 1, 2
@@ -215,6 +216,7 @@ SYMBOLS = {
     "ohcu_dsp_mc_bi": (C.c_int, [_I, _I, _P, _S, _P, _S, _P, _I, _I, _I, _I]),
     "ohcu_dsp_mc_bi_w": (C.c_int, [_I, _I, _P, _S, _P, _S, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I]),
     "ohcu_dsp_idct": (C.c_int, [_I, _P, _I, _I]),
+    "ohcu_dsp_idct_noalloc": (C.c_int, [_I, _P, _I, _I, _I]),
     "ohcu_dsp_idct_dc": (C.c_int, [_I, _P, _I]),
     "ohcu_dsp_idct_4x4_luma": (C.c_int, [_I, _P]),
     "ohcu_dsp_transform_skip": (C.c_int, [_I, _P, _I]),

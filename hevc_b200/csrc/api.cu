@@ -27,6 +27,17 @@ static int fail(int code, const char *fmt, ...)
     va_end(ap);
     return code;
 }
+// the same for entry points that live beside their kernels (recon.cu: ohcu_dsp_idct_noalloc)
+namespace ohcu {
+int set_error(int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+}  // namespace ohcu
 #define CU(call)                                                                          \
     do {                                                                                  \
         cudaError_t e_ = (call);                                                          \

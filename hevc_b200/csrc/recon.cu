@@ -39,6 +39,8 @@
 //    dot-product pipe: IDP.2A does two 16x8-bit MACs per instruction at IMAD issue rate
 //    (profiles/r01_ubench_int_pipes.txt).  Horizontal pairs come straight from the window
 //    words (+ funnel shifts for odd positions), vertical pairs are built with PRMT.
+#include <mutex>
+
 #include "ohcu_internal.h"
 
 namespace ohcu {
@@ -1477,3 +1479,69 @@ int dsp_transform_add(int bd, uint8_t *dst, const int16_t *coeffs, ptrdiff_t str
 }
 
 }  // namespace ohcu
+
+// ================================================================= ohcu_dsp_idct_noalloc
+// The idct[] table entry once more (ohcu_dsp_idct above), for callers that must not allocate: the device
+// staging of the blocks is a file-scope array instead of dsp_scratch()'s cudaMalloc.  No counterpart in the
+// reference (include/ohcu.h).
+//   * g_noalloc_scratch lives in every GPU that loads the library until the process exits (64 KB).
+//   * In HOST code its name is a host-side stand-in, not a device address: the address a kernel may be given
+//     comes from cudaGetSymbolAddress, looked up once per device with that device current.
+//   * Every call shares the array and finds the previous call's contents in it.  Nothing has to start at zero:
+//     a call copies its blocks in before the kernel reads them and reads back only what it wrote.  Calls that
+//     overlap on the GPU (two threads, two streams) race on it - this entry point is serialised by a mutex and
+//     runs synchronously on the default stream.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[OHCU_NOALLOC_MAX_BYTES];
+
+namespace {
+std::mutex g_noalloc_mu;
+constexpr int NOALLOC_MAX_DEVICES = 64;
+int16_t *g_noalloc_ptr[NOALLOC_MAX_DEVICES];        // device address of g_noalloc_scratch, per device (nullptr = not set up)
+}
+
+extern "C" int ohcu_dsp_idct_noalloc(int bd, int16_t *coeffs, int log2_size, int col_limit, int nblocks)
+{
+    using namespace ohcu;
+    if (!coeffs || log2_size < 2 || log2_size > 5 || nblocks < 1)
+        return set_error(OHCU_EINVAL, "ohcu_dsp_idct_noalloc: bad argument (log2_size %d, nblocks %d)", log2_size, nblocks);
+    if (bd != 8 && bd != 9 && bd != 10 && bd != 12 && bd != 14)
+        return set_error(OHCU_EINVAL, "ohcu_dsp_idct_noalloc: unsupported bit depth %d", bd);
+    const size_t block = (size_t)2 << (2 * log2_size), bytes = block * (size_t)nblocks;
+    if (bytes > (size_t)OHCU_NOALLOC_MAX_BYTES)
+        return set_error(OHCU_EINVAL, "ohcu_dsp_idct_noalloc: %d blocks of %dx%d need %zu bytes, the static scratch holds %d "
+                         "(OHCU_NOALLOC_MAX_BYTES); split the call or use ohcu_dsp_idct", nblocks, 1 << log2_size, 1 << log2_size,
+                         bytes, OHCU_NOALLOC_MAX_BYTES);
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return set_error(OHCU_ENODEV, "ohcu_dsp_idct_noalloc: no CUDA device");
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return set_error(OHCU_EINVAL, "ohcu_dsp_idct_noalloc: device %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        // set-up, once per device, with that device current: the transform constants (per-device symbols) and the
+        // scratch array's DEVICE address
+        void *ptr = nullptr;
+        if (upload_dct_table() || upload_mc_taps()) return set_error(OHCU_ECUDA, "ohcu_dsp_idct_noalloc: constant upload failed");
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr)
+            return set_error(OHCU_ECUDA, "ohcu_dsp_idct_noalloc: cudaGetSymbolAddress -> %s", cudaGetErrorString(e));
+        g_noalloc_ptr[dev] = (int16_t *)ptr;
+    }
+    int16_t *d = g_noalloc_ptr[dev];
+    cudaError_t e = cudaMemcpy(d, coeffs, bytes, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return set_error(OHCU_ECUDA, "ohcu_dsp_idct_noalloc: upload -> %s", cudaGetErrorString(e));
+    ohcu_tu tu{};
+    tu.log2_size = (uint8_t)log2_size; tu.mode = OHCU_TU_IDCT; tu.col_limit = (int8_t)col_limit;
+    const size_t n16 = block / 2;
+    for (int b = 0; b < nblocks; b++) {
+        switch (log2_size) {
+        case 2: dsp_residual_kernel<2><<<1, 32>>>(d + b * n16, tu, bd, 0); break;
+        case 3: dsp_residual_kernel<3><<<1, 32>>>(d + b * n16, tu, bd, 0); break;
+        case 4: dsp_residual_kernel<4><<<1, 32>>>(d + b * n16, tu, bd, 1); break;
+        default: dsp_residual_kernel<5><<<1, 32>>>(d + b * n16, tu, bd, 1); break;
+        }
+    }
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaMemcpy(coeffs, d, bytes, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return set_error(OHCU_ECUDA, "ohcu_dsp_idct_noalloc: %s", cudaGetErrorString(e));
+    return 0;
+}

@@ -534,6 +534,15 @@ int ohcu_dsp_idct_4x4_luma(int bd, int16_t *coeffs);
 int ohcu_dsp_transform_skip(int bd, int16_t *coeffs, int log2_size);
 int ohcu_dsp_transform_rdpcm(int bd, int16_t *coeffs, int log2_size, int mode);
 int ohcu_dsp_transform_add(int bd, uint8_t *dst, const int16_t *coeffs, ptrdiff_t stride, int n);
+/*  idct[log2-2] on nblocks consecutive N x N blocks, WITHOUT any allocation.  No counterpart in the reference:
+ *  added for callers that cannot call cudaMalloc (code under CUDA graph
+ *  capture, tight serving loops, harnesses that forbid it).  Same results as ohcu_dsp_idct block by block; the
+ *  device staging is a static 64 KB array inside the library (held by every GPU that loads it until exit), so
+ *  nblocks * N * N * 2 bytes must not exceed OHCU_NOALLOC_MAX_BYTES (OHCU_EINVAL with the numbers in
+ *  ohcu_last_error() otherwise).  Runs on the CURRENT device, synchronously.  All calls share the array: they
+ *  are serialised inside the library, and anything else that would overlap with them on the GPU races.       */
+#define OHCU_NOALLOC_MAX_BYTES 65536
+int ohcu_dsp_idct_noalloc(int bd, int16_t *coeffs, int log2_size, int col_limit, int nblocks);
 /*  hevc_{h,v}_loop_filter_{luma,chroma}: pix = first Q sample, tc / no_p / no_q per 4-line
  *  segment                                                     hevcdsp.h:128-131             */
 int ohcu_dsp_loop_filter_luma(int bd, int vertical, uint8_t *pix, ptrdiff_t stride, int beta,
