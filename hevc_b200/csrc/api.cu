@@ -1105,16 +1105,19 @@ static void sort_tus_by_ctb(ohcu_ctx *c, Job &j)
     j.tu_sorted = true;
 }
 
-static int stage_impl(ohcu_ctx *c, int job);
+static int stage_impl(ohcu_ctx *c, int job, bool close);
 static void fill_frame_dev(const ohcu_ctx *c, const Job &j, FrameDev *f);
 // A stage that fails discards the job's lists (the job can be begun again).
 extern "C" int ohcu_frame_stage(ohcu_ctx *c, int job)
 {
-    const int rc = stage_impl(c, job);
+    const int rc = stage_impl(c, job, true);
     if (rc && c && job >= 0 && job < (int)c->jobs.size()) c->jobs[job].open = false;
     return rc;
 }
-static int stage_impl(ohcu_ctx *c, int job)
+// close = false: the job stays the caller's (ohcu_frame_begin keeps refusing it) until ohcu_frame_flush has enqueued
+// its launches; closing at the end of the upload let another frame thread begin the job - and reset its lists -
+// between the two halves of a flush once the ring wrapped around.
+static int stage_impl(ohcu_ctx *c, int job, bool close)
 {
     OPEN_JOB(c, job);
     if (!j.inplace && !j.pu_sorted) sort_pus_by_ctb(c, j);
@@ -1187,7 +1190,10 @@ static int stage_impl(ohcu_ctx *c, int job)
         std::lock_guard<std::mutex> lock(c->mu);
         c->launches++;
     }
-    j.open = false;
+    if (close) {
+        std::lock_guard<std::mutex> lock(c->mu);
+        j.open = false;
+    }
     j.staged = true;
     // the pinned staging is reusable once this event has fired
     CU(cudaEventRecord(j.done, st));
@@ -1309,9 +1315,13 @@ extern "C" int ohcu_frame_launch(ohcu_ctx *c, int job, int out_slot)
 
 extern "C" int ohcu_frame_flush(ohcu_ctx *c, int job)
 {
-    int rc = ohcu_frame_stage(c, job);
-    if (rc) return rc;
-    return ohcu_frame_launch_stages(c, job, -1, 0);
+    int rc = stage_impl(c, job, false);
+    if (!rc) rc = ohcu_frame_launch_stages(c, job, -1, 0);
+    if (c && job >= 0 && job < (int)c->jobs.size()) {
+        std::lock_guard<std::mutex> lock(c->mu);
+        c->jobs[job].open = false;
+    }
+    return rc;
 }
 
 extern "C" int ohcu_frame_sync(ohcu_ctx *c, int job)
