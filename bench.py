@@ -1,15 +1,18 @@
 #!/usr/bin/env python
 """bench.py — HEVC pixel-reconstruction hot path on B200: Mpixel/s reconstructed per GPU.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload 4k|1080p|8k]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                  [--workload 4k|1080p|1080p422|1080p444|8k]
 
-A step = one pass of the hot path (MC + residual, then deblock + SAO: two fused kernels
-and the halo fill per frame) over one batch of synthetic frames.  Default workload: BASELINE.json configs[2], 3840x2160 Main10 4:2:0 full
-reconstruction with weighted prediction.
+A step = one pass of the hot path (mc_kernel, residual_kernel, loopfilter_kernel = deblock + SAO fused, pad_kernel)
+over one batch of synthetic frames (160 4K frames per step by default, so that 20 steps time ~0.5 s of device work).
+Default workload: BASELINE.json configs[2], 3840x2160 Main10 4:2:0 full reconstruction with weighted prediction; the
+other BASELINE configs are --workload 1080p / 1080p422 / 1080p444 / 8k (64 independent frames, strong scaling).
 
-  value        whole-job Mpixel/s (luma W*H*frames / s), work lists resident in HBM
-  e2e          same metric through the C ABI with HOST buffers: list upload from pinned
-               memory, kernels, and the reconstructed picture copied back to pinned memory
+  value        whole-job Mpixel/s (luma W*H*frames / s), work lists resident in HBM, 8 frames in flight, 8 distinct
+               frames per GPU predicting from 16 distinct reference pictures (inputs > L2)
+  e2e          same metric through the C ABI with HOST buffers, driven by C frame threads (hevc_b200/csrc/e2e_driver.c):
+               lists into the job's pinned arenas, H2D, prepare + kernels, D2H of every reconstructed picture
   roofline     the dominant kernel (mc_kernel: motion compensation) against the measured HBM peak
   cpu_baseline the reference's own CPU path on the host cores: its C drivers + its SSE intrinsics (oracle/_ref/
                liboh_ref_simd.so, the fastest reference path buildable here), with the pure-C arms beside it
@@ -34,17 +37,25 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 WORKLOADS = {
-    # name: (width, height, bit_depth, chroma_format_idc, generator overrides, frames per step per GPU)
-    "4k": (3840, 2160, 10, 1, dict(weighted=1), 8),
-    "1080p": (1920, 1080, 8, 1, dict(), 16),
-    "8k": (7680, 4320, 10, 1, dict(weighted=1), 8),
+    # name: (width, height, bit_depth, chroma_format_idc, generator overrides,
+    #        frames in flight per GPU (resident leg), distinct synthetic frames per GPU, frames per step per GPU)
+    "4k": (3840, 2160, 10, 1, dict(weighted=1), 8, 8, 160),
+    "1080p": (1920, 1080, 8, 1, dict(), 16, 8, 640),
+    "1080p422": (1920, 1080, 10, 2, dict(rext=1, weighted=1), 16, 8, 320),
+    "1080p444": (1920, 1080, 10, 3, dict(rext=1), 16, 8, 320),
+    # 64 independent frames in all, sharded frame i -> rank i mod N: the job is fixed, so scaling is STRONG
+    "8k": (7680, 4320, 10, 1, dict(weighted=1), 8, 64, 64),
 }
 WORKLOAD_NAMES = {
     "4k": "3840x2160 Main10 4:2:0 full reconstruction, weighted prediction (BASELINE configs[2])",
     "1080p": "1920x1080 Main 8-bit 4:2:0 (BASELINE configs[1])",
+    "1080p422": "1920x1080 RExt 10-bit 4:2:2 (BASELINE configs[3])",
+    "1080p444": "1920x1080 RExt 10-bit 4:4:4 (BASELINE configs[3])",
     "8k": "7680x4320 Main10 4:2:0, 64 independent frames sharded across GPUs (BASELINE configs[4])",
 }
-N_DISTINCT = 4        # distinct synthetic frames; jobs reuse them round-robin
+N_REF_PAIRS = 8       # distinct pairs of reference pictures (DPB slots 0..15); frame d predicts from pair d mod 8
+FIRST_OUT = 2 * N_REF_PAIRS
+RING = 16             # output slots FIRST_OUT..31 in rotation (e2e leg), pinned output pictures
 # dram__bytes_read.sum + dram__bytes_write.sum of one mc_kernel launch, from the committed
 # `ncu --set full` capture of this same command (never measured inside a timed run)
 NCU_TRAFFIC = {"4k": 59145984}
@@ -58,13 +69,32 @@ def peaks():
     return 6650.0, "fallback"
 
 
-def make_inputs(workload, rank, world=1):
-    """The N_DISTINCT * world synthetic frames of the job are sharded frame i -> rank i mod world."""
+def frames_per_rank(workload, world):
+    """(distinct frames, frames per step) of one rank.  8k: the 64 frames of the job are split over the ranks."""
+    D, F = WORKLOADS[workload][6], WORKLOADS[workload][7]
+    if workload == "8k":
+        return max(1, D // world), max(1, F // world)
+    return D, F
+
+
+def make_inputs(workload, rank, world=1, distinct=None):
+    """The synthetic frames of this rank (frame i of the job -> rank i mod world) and the 16 reference pictures.
+    Frame d predicts from reference pair d mod 8 (DPB slots 2p, 2p + 1): 8 frames in flight read 16 different
+    pictures, so reference reads are not L2 hits by construction."""
     from hevc_b200 import shard, synth
-    w, h, bd, cf, kw, _ = WORKLOADS[workload]
-    mine = shard.frames_of_rank(N_DISTINCT * world, rank, world)
-    jobs = [synth.make_job(w, h, bd, cf, seed=shard.seed_of_frame(3000, i), **kw) for i in mine]
-    refs = [synth.make_picture(jobs[0].sp, 7000 + s) for s in range(2)]
+    w, h, bd, cf, kw = WORKLOADS[workload][:5]
+    D = distinct or frames_per_rank(workload, world)[0]
+    mine = shard.frames_of_rank(D * world, rank, world)
+    jobs = []
+    for d, i in enumerate(mine):
+        fj = synth.make_job(w, h, bd, cf, seed=shard.seed_of_frame(3000, i), **kw)
+        pair = d % N_REF_PAIRS
+        for l in range(2):
+            for r in range(16):
+                fj.slices["ref_slot"][:, l, r] = 2 * pair + (r + l) % 2
+        fj.sp.dpb_slots = 32
+        jobs.append(fj)
+    refs = [synth.make_picture(jobs[0].sp, 7000 + s) for s in range(2 * N_REF_PAIRS)]
     return jobs, refs
 
 
@@ -73,20 +103,15 @@ def levels_inputs(jobs):
     per block and random scaling lists (tests/levels_cases.py); job.coeffs is replaced by the scaled
     coefficients (CPU restatement of scale_and_clip_coeff), which is what the parity check and the CPU
     arms consume - the GPU arm is handed the levels (ohcu_append_tu_levels) and scales them itself.
-    Returns per job (recs, quant, pairs, (sl, sl_dc))."""
+    Returns per job (quant, levels, scaling)."""
     import levels_cases
     import oracle_lib
-    from hevc_b200.sparse import to_levels
     orc = oracle_lib.Lib("oracle")
     out = []
     for i, fj in enumerate(jobs):
-        sp = fj.sp
-        hs = 1 if sp.chroma_format_idc in (1, 2) else 0
-        vs = 1 if sp.chroma_format_idc == 1 else 0
-        ctb_w = (sp.width + (1 << sp.log2_ctb_size) - 1) >> sp.log2_ctb_size
         lv, quant, scaling = levels_cases.frame_levels(fj, seed=900 + i)
-        fj.coeffs = orc.dequant_tus(fj.tus, quant, lv, sp.bit_depth, scaling)
-        out.append(to_levels(fj.tus, quant, lv, sp.log2_ctb_size, hs, vs, ctb_w) + (scaling,))
+        fj.coeffs = orc.dequant_tus(fj.tus, quant, lv, fj.sp.bit_depth, scaling)
+        out.append((quant, lv, scaling))
     return out
 
 
@@ -125,23 +150,45 @@ def algorithmic_bytes(job):
 
 
 class ClockSampler:
+    """SM clock and throttle reasons sampled every 20 ms DURING the timed regions (NVML; nvidia-smi as a fallback
+    at whatever rate it manages)."""
+
     def __init__(self, device):
         self.device = device
-        self.rows = []
+        self.rows = []            # (sm_mhz, sm_max_mhz, [reasons])
         self.stop = threading.Event()
         self.th = threading.Thread(target=self.run, daemon=True)
 
     def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.device)
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            bits = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+                    "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                    "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+            while not self.stop.is_set():
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.rows.append((nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM), mx, [k for k, b in bits.items() if r & b]))
+                self.stop.wait(0.02)
+            return
+        except Exception:
+            pass
         q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         while not self.stop.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
                                       "-i", str(self.device)], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([x.strip() for x in out.strip().split(",")])
+                r = [x.strip() for x in out.strip().split(",")]
+                if len(r) >= 6 and r[0].isdigit():
+                    self.rows.append((int(r[0]), int(r[1]), [names[i] for i in range(4) if r[2 + i].lower().startswith("active")]))
             except Exception:
                 pass
-            self.stop.wait(0.2)
+            self.stop.wait(0.02)
 
     def __enter__(self):
         self.th.start()
@@ -152,12 +199,9 @@ class ClockSampler:
         self.th.join(timeout=6)
 
     def summary(self):
-        sm = [int(r[0]) for r in self.rows if len(r) >= 6 and r[0].isdigit()]
-        mx = [int(r[1]) for r in self.rows if len(r) >= 6 and r[1].isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
-        return {"sm_mhz": int(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+        sm = [r[0] for r in self.rows]
+        return {"sm_mhz": int(np.median(sm)) if sm else None, "sm_max_mhz": max(r[1] for r in self.rows) if sm else None,
+                "reasons": sorted({x for r in self.rows for x in r[2]}), "samples": len(sm)}
 
 
 # ------------------------------------------------------------------ reference arm
@@ -219,188 +263,129 @@ def cpu_reference(jobs, refs, steps, warmup, max_threads=None, all_arms=False):
 
 # ------------------------------------------------------------------ our arm
 def run_ours(args, rank, world):
-    from hevc_b200 import abi, backend, shard
-    jobs, refs = make_inputs(args.workload, rank, world)
-    sp = jobs[0].sp
+    from concurrent.futures import ThreadPoolExecutor
+    from hevc_b200 import abi, backend, driver, shard
+    D, F = frames_per_rank(args.workload, world)
     B = WORKLOADS[args.workload][5]
     if args.frames:
-        B = args.frames
+        F = args.frames
+    jobs, refs = make_inputs(args.workload, rank, world)
+    sp = jobs[0].sp
     device = int(os.environ.get("LOCAL_RANK", 0))
     hbm_peak, peak_kind = peaks()
-    # the e2e leg keeps 2B frames in flight (B being filled / uploaded while B run and drain)
-    if B % N_DISTINCT:
-        raise SystemExit(f"--frames must be a multiple of {N_DISTINCT} (the job ring is revisited with the same frame contents)")
-    E = min(2 * B, 28)                       # ring depth of the e2e leg (2 reference slots + E <= 32 DPB slots)
-    ctx = backend.Context(sp, device=device, dpb_slots=2 + max(B, E), jobs=max(B, E))
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
+    # frame threads of the e2e leg: the host's cores are shared by the ranks of the node
+    threads = args.host_threads or max(1, min(8, cores // max(1, world)))
+    # resident leg: J staged jobs (8k: every frame of the rank's share of the 64), launched round-robin
+    J = min(D, 64) if args.workload == "8k" else B
+    njobs = max(J, RING, threads)
+    ctx = backend.Context(sp, device=device, dpb_slots=32, jobs=njobs)
     lib, h = ctx.lib, ctx.handle
-    for s in range(2):
-        ctx.upload(s, refs[s])
-
+    for s, r in enumerate(refs):
+        ctx.upload(s, r)
     barrier = shard.barrier
-    # --coeffs sparse: significant coefficients as (position, level) pairs (ohcu_append_tu_sparse)
-    sparse_lists = [ctx.sparse_lists(fj) for fj in jobs] if args.coeffs == "sparse" else None
-    # --coeffs levels: the pairs carry un-scaled levels, the kernel dequantises (ohcu_append_tu_levels)
     level_lists = levels_inputs(jobs) if args.coeffs == "levels" else None
     derive = args.bs == "derived"
     if derive:
         derived_bs_inputs(jobs)
+    frames = driver.Frames(jobs, sp, coeffs=args.coeffs, derive_bs=derive, levels=level_lists)
 
-    # ---------------- resident leg: lists staged once, kernels only in the timed region
-    for k in range(B):
-        j = ctx.begin(2 + k)
-        assert j == k
-        if level_lists:
-            recs, q, pairs, scaling = level_lists[k % len(jobs)]
-            ctx.append(j, jobs[k % len(jobs)], levels=(q, scaling, (recs, q, pairs)), derive_bs=derive)
-        else:
-            ctx.append(j, jobs[k % len(jobs)], sparse=sparse_lists[k % len(jobs)] if sparse_lists else False, derive_bs=derive)
-        ctx.stage(j)
+    # ---------------- resident leg: lists staged once (through the in-place path), kernels only in the timed region
+    out_of = lambda k: FIRST_OUT + k % RING
+    res, _ = driver.run(ctx, frames, total_frames=njobs, threads=1, ring=RING, first_slot=FIRST_OUT, fill=driver.FILL_COPY,
+                        frame_by_job=True, timed=False)
     ctx.sync()
-    l0 = ctx.kernel_launches()
-    for _ in range(args.warmup):
-        for k in range(B):
-            ctx.launch(k, 2 + k)
+    rounds = max(1, F // J)                      # launches of each staged job per step
+    F = rounds * J
+    for _ in range(max(1, args.warmup)):
+        for r in range(rounds):
+            for k in range(J):
+                ctx.launch(k, out_of(k))
     ctx.sync()
     barrier()
     l1 = ctx.kernel_launches()
     with ClockSampler(device) as clk:
         ctx.timer_start()
         for _ in range(args.steps):
-            for k in range(B):
-                ctx.launch(k, 2 + k)
+            for r in range(rounds):
+                for k in range(J):
+                    ctx.launch(k, out_of(k))
         ms_resident = ctx.timer_stop()
     barrier()
     launches = ctx.kernel_launches() - l1
-    clocks = clk.summary()
+    resident_pics = {k: ctx.download(out_of(k)) for k in range(max(0, J - RING), J)}    # checked below
 
     # ---------------- per-stage timing of single frames (events on the job's own stream)
     ctx.set_profiling(True)
     stage_ms = np.zeros(abi.NUM_STAGES)
-    nprof = max(4, min(16, args.steps * B))
+    nprof = 16
     for i in range(nprof):
-        k = i % B
-        ctx.launch(k, 2 + k)
+        k = i % J
+        ctx.launch(k, out_of(k))
         ctx.sync(k)
         stage_ms += np.array(ctx.stage_ms(k))
     stage_ms /= nprof
     ctx.set_profiling(False)
 
-    # ---------------- e2e leg: host buffers -> H2D -> kernels -> D2H, through the C ABI
+    # ---------------- e2e leg: host lists -> pinned arenas -> H2D -> kernels -> D2H, through the C ABI, driven by the
+    # plain-C frame threads of hevc_b200/csrc/e2e_driver.c (no Python inside the timed region)
     full = (0, 0, sp.width, sp.height)
     if args.copy_out == "packed":
-        outs = [ctx.pinned_cropped(full) for _ in range(E)]
+        outs = [ctx.pinned_cropped(full) for _ in range(RING)]
+        dl = driver.DOWNLOAD_CROPPED
     else:
-        outs = [ctx.pinned_picture(slot_pitch=args.slot_pitch or args.copy_out == "pitch") for _ in range(E)]
-    h2d = d2h = 0
-
-    # which frame's coefficients a job arena holds (by arena address).  The submitting threads
-    # take jobs from the ring in whatever order they reach ohcu_frame_begin, so a frame can land
-    # on an arena that holds another frame's coefficients: then they are written again
-    arena_content = {}
-    rewrites = [0]
-
-    def in_place(ptr, cidx, src, copy_coeffs):
-        if copy_coeffs or arena_content.get(ptr.value) != cidx:
-            C.memmove(ptr.value, src.ctypes.data, src.nbytes)
-            arena_content[ptr.value] = cidx
-            if not copy_coeffs:
-                rewrites[0] += 1
-
-    def submit(i, copy_coeffs=False):
-        nonlocal h2d, d2h
-        k = i % E                            # output slot / pinned output buffer of this frame
-        cidx = k % len(jobs)
-        fj = jobs[cidx]
-        j = ctx.begin(2 + k)
-        for i in range(len(fj.slices)):
-            tab = abi.SliceTab.from_buffer_copy(fj.slices[i].tobytes())
-            abi.check(lib.ohcu_set_slice(h, j, i, C.byref(tab)))
-        abi.check(lib.ohcu_append_pu(h, j, fj.pus.ctypes.data, len(fj.pus)))
-        # the residual parser writes coefficients straight into the job's pinned arena
-        # (ohcu_reserve_coeffs, lc->tu.coeffs of hevcdec.h:333); the untimed first pass puts
-        # them there, later passes find them in place like a decoder that just parsed them
-        ptr = C.c_void_p(); off = C.c_uint32()
-        if level_lists:
-            recs, q, pairs, (sl, sl_dc) = level_lists[k % len(jobs)]
-            abi.check(lib.ohcu_reserve_coefs(h, j, len(pairs), C.byref(ptr)))
-            in_place(ptr, cidx, pairs, copy_coeffs)
-            abi.check(lib.ohcu_set_scaling_list(h, j, sl.ctypes.data, sl_dc.ctypes.data))
-            abi.check(lib.ohcu_append_tu_levels(h, j, recs.ctypes.data, q.ctypes.data, len(recs), ptr, len(pairs)))
-            coef_bytes = pairs.nbytes + 8 * len(fj.sao) + q.nbytes + sl.nbytes + sl_dc.nbytes
-        elif sparse_lists:
-            recs, pairs = sparse_lists[k % len(jobs)]
-            abi.check(lib.ohcu_reserve_coefs(h, j, len(pairs), C.byref(ptr)))
-            in_place(ptr, cidx, pairs, copy_coeffs)
-            abi.check(lib.ohcu_append_tu_sparse(h, j, recs.ctypes.data, len(recs), ptr, len(pairs)))
-            coef_bytes = pairs.nbytes + 8 * len(fj.sao)
-        else:
-            abi.check(lib.ohcu_reserve_coeffs(h, j, len(fj.coeffs), C.byref(ptr), C.byref(off)))
-            in_place(ptr, cidx, fj.coeffs, copy_coeffs)
-            abi.check(lib.ohcu_append_tu_inplace(h, j, fj.tus.ctypes.data, len(fj.tus)))
-            coef_bytes = fj.coeffs.nbytes
-        s = fj.sao_in()
-        if derive:
-            d = abi.DeblockDeriveIn()
-            d.qp_y_tab = fj.qp_y_tab.ctypes.data; d.deblock = fj.deblock.ctypes.data
-            d.is_pcm = fj.is_pcm.ctypes.data if sp.pcm_or_bypass else None
-            d.filter_slice_edges = fj.filter_slice_edges.ctypes.data
-            d.tab_slice_address = fj.tab_slice_address.ctypes.data; d.tile_id = fj.tile_id.ctypes.data
-            abi.check(lib.ohcu_set_deblock_derived(h, j, C.byref(d)))
-        else:
-            d = fj.deblock_in()
-            abi.check(lib.ohcu_set_deblock(h, j, C.byref(d)))
-        abi.check(lib.ohcu_set_sao(h, j, C.byref(s)))
-        ctx.flush(j)
-        if args.copy_out == "packed":
-            ctx.output_cropped(2 + k, full, out=outs[k], wait=False)
-        else:
-            ctx.download_async(2 + k, outs[k])
-        nctb = len(fj.sao)
-        h2d = (fj.pus.nbytes + 8 * nctb + fj.slices.nbytes + fj.tus.nbytes + coef_bytes + 8 * nctb +
-               (nctb if derive else fj.vbs.nbytes + fj.hbs.nbytes) + fj.qp_y_tab.nbytes + fj.deblock.nbytes + fj.sao.nbytes + 2 * nctb)
-        d2h = sum(p.strides[0] * (p.shape[0] - 1) + p.shape[1] * p.itemsize for p in outs[k])   # bytes the copies move
-
-    # frames are submitted by a few host threads, one frame each at a time, the way the
-    # reference's frame threads (hevcdec.h:53) would drive their own jobs
-    from concurrent.futures import ThreadPoolExecutor
-    pool = ThreadPoolExecutor(max(1, min(args.host_threads, B)))
-    # untimed first pass over every job arena of the ring (puts the coefficients in place);
-    # the resident leg left the ring at job B, so 2B submissions visit each arena once
-    for i in range(max(B, E)):
-        ctx.sync()
-        submit(i, copy_coeffs=True)
-    ctx.sync()
-    list(pool.map(submit, range(args.warmup * B)))
-    ctx.sync()
-    for k in range(E):
-        ctx.slot_sync(2 + k)
+        outs = [ctx.pinned_picture(slot_pitch=args.copy_out == "pitch") for _ in range(RING)]
+        dl = driver.DOWNLOAD_PLANES
+    fill = {"copy": driver.FILL_COPY, "append": driver.APPEND}[args.fill]
+    total = args.steps * F
+    driver.run(ctx, frames, total_frames=max(RING, args.warmup * min(F, 4 * RING)), threads=threads, ring=RING, first_slot=FIRST_OUT,
+               fill=fill, download=dl, outs=outs, timed=False)
     barrier()
-    ctx.timer_start()
-    t_host = time.perf_counter()
-    list(pool.map(submit, range(args.steps * B)))        # frames stream through, no per-step barrier
-    ms_e2e = ctx.timer_stop()
-    pool.shutdown()
-    t_host = (time.perf_counter() - t_host) * 1e3
+    with ClockSampler(device) as clk2:
+        r_e2e, last = driver.run(ctx, frames, total_frames=total, threads=threads, ring=RING, first_slot=FIRST_OUT, fill=fill,
+                                 download=dl, outs=outs)
     barrier()
+    ms_e2e, host_ms, cpu_ms = r_e2e.device_ms, r_e2e.host_ms, r_e2e.work_cpu_ms
+    e2e_pics = [(int(last[k]), [p.copy() for p in outs[k]]) for k in range(RING)]
+    d2h = sum(p.strides[0] * (p.shape[0] - 1) + p.shape[1] * p.itemsize for p in outs[0])
+    h2d = int(np.mean(frames.h2d_bytes))
+    # the same with the big lists found in place (a parser that wrote them there): the library's own host cost
+    driver.run(ctx, frames, total_frames=njobs, threads=1, ring=RING, first_slot=FIRST_OUT, fill=driver.FILL_COPY,
+               frame_by_job=True, timed=False)
+    r_inplace, _ = driver.run(ctx, frames, total_frames=total, threads=threads, ring=RING, first_slot=FIRST_OUT,
+                              fill=driver.FILL_NONE, frame_by_job=True, download=dl, outs=outs)
+    # ---------------- chained streams: picture t predicts from t-1 and t-2 of its stream (what a decoder does),
+    # lists in place, no download: the kernels' throughput when frames depend on each other
+    chain = {}
+    if args.workload != "8k" and not args.no_chain:
+        for S in (1, 2, 4):
+            rc_, _ = driver.run(ctx, frames, total_frames=max(3 * S, min(total, 60 * S)), threads=min(threads, S), ring=3 * S,
+                                first_slot=FIRST_OUT, fill=driver.FILL_NONE, frame_by_job=True, chain_streams=S, ref_slot=(0, 1))
+            chain[f"streams_{S}"] = round(rc_.frames / (rc_.device_ms * 1e-3), 1)
 
-    # ---------------- correctness spot check of what the timed runs produced
+    # ---------------- correctness of what the timed runs produced: EVERY distinct frame against the oracle replay
     import oracle_lib
-    check = "skipped"
-    if rank == 0 and not args.no_check and sp.width * sp.height <= 3840 * 2160:
-        want = oracle_lib.Lib("oracle").replay(jobs[0], list(refs) + [None] * (sp.dpb_slots - 2))
-        got = ctx.download(2)
-        check = "bit-exact" if all(np.array_equal(a, b) for a, b in zip(got, want)) and \
-            all(np.array_equal(a, b) for a, b in zip(outs[0], want)) and \
-            all(np.array_equal(a, b) for a, b in zip(outs[len(jobs)], want)) else "MISMATCH"
+    check, checked = "skipped", 0
+    if not args.no_check:
+        orc = oracle_lib.Lib("oracle")
+        need = sorted({d for d, _ in e2e_pics if d >= 0} | {k % D for k in resident_pics})
+        with ThreadPoolExecutor(min(cores, 16)) as pool:
+            want = dict(zip(need, pool.map(lambda d: orc.replay(jobs[d], list(refs) + [None] * 16), need)))
+        same = lambda a, b: all(np.array_equal(x, y) for x, y in zip(a, b))
+        ok = all(same(pic, want[d]) for d, pic in e2e_pics if d >= 0) and all(same(pic, want[k % D]) for k, pic in resident_pics.items())
+        checked = len(need)
+        check = "bit-exact" if ok else "MISMATCH"
+    bad = shard.max_over_ranks([1.0 if check == "MISMATCH" else 0.0], device=f"cuda:{device}")[0]
 
     # ---------------- reduce over ranks
-    frames_rank = args.steps * B
-    ms_resident, ms_e2e = shard.max_over_ranks([ms_resident, ms_e2e], device=f"cuda:{device}")
+    ms_resident, ms_e2e, ms_inplace, host_ms = shard.max_over_ranks([ms_resident, ms_e2e, r_inplace.device_ms, host_ms], device=f"cuda:{device}")
     ctx.close()
     if rank != 0:
         return
+    if bad:
+        check = "MISMATCH"
     px = sp.width * sp.height
-    total_frames = frames_rank * world
+    total_frames = total * world
     value = total_frames * px / (ms_resident * 1e-3) / 1e6
     e2e_value = total_frames * px / (ms_e2e * 1e-3) / 1e6
     ab = algorithmic_bytes(jobs[0])
@@ -412,26 +397,37 @@ def run_ours(args, rank, world):
     pad_ms = float(stage_ms[abi.STAGE_SAO])
     achieved = ab["mc"] / (mc_ms * 1e-3) / 1e9
     kern = [("mc", mc_ms), ("residual", res_ms), ("loopfilter", lf_ms), ("pad", pad_ms)]
+    clocks = clk.summary()
+    clocks["e2e"] = clk2.summary()
     line = {
         "metric": "Mpixel/s reconstructed per B200 (4K Main10); HBM GB/s vs peak", "value": round(value, 1),
         "unit": "Mpixel/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": round(ms_resident / args.steps, 4), "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": round(ms_resident / args.steps, 4), "higher_is_better": True,
+        "scaling": "strong" if args.workload == "8k" else "weak",
         "vs_baseline": None, "dtype": "int32 accumulate on u16 samples / int16 coefficients" if sp.bit_depth > 8
         else "int32 accumulate on u8 samples / int16 coefficients", "data": "synthetic",
-        "config": {"workload": WORKLOAD_NAMES[args.workload], "frames_per_step_per_gpu": B,
-                   "frames_in_flight": B, "frames_in_flight_e2e": E, "distinct_frames": len(jobs), "sharding": "independent frames per GPU, no collective",
-                   "l2": f"inputs larger than L2: {B} frames x ~{(ab['pipeline']) / 1e6:.0f} MB algorithmic traffic per step",
+        "config": {"workload": WORKLOAD_NAMES[args.workload], "frames_per_step_per_gpu": F,
+                   "frames_in_flight": min(J, RING), "frames_in_flight_e2e": RING, "distinct_frames_per_gpu": len(jobs),
+                   "reference_pictures": len(refs), "sharding": "independent frames per GPU, no collective",
+                   "l2": f"inputs larger than L2: {len(jobs)} distinct list sets, {len(refs)} reference pictures + {RING} output slots "
+                         f"of {ab['S'] / 1e6:.0f} MB, ~{ab['pipeline'] / 1e6:.0f} MB algorithmic traffic per frame",
                    "pus_per_frame": int(len(jobs[0].pus)), "tus_per_frame": int(len(jobs[0].tus)),
                    "coded_fraction": round(len(jobs[0].coeffs) / (ab['S'] / (2 if sp.bit_depth > 8 else 1)), 3),
-                   "coeffs": args.coeffs, "bs": args.bs, "copy_out": args.copy_out,
+                   "coeffs": args.coeffs, "bs": args.bs, "copy_out": args.copy_out, "fill": args.fill,
                    "significant_fraction": round(float(np.count_nonzero(jobs[0].coeffs)) / max(1, len(jobs[0].coeffs)), 3)},
         "frames_per_s": round(total_frames / (ms_resident * 1e-3), 1),
+        "timed_region_ms": round(ms_resident, 1),
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "e2e": {"value": round(e2e_value, 1), "unit": "Mpixel/s", "h2d_bytes_per_step": int(h2d * B),
-                "d2h_bytes_per_step": int(d2h * B), "frames_per_s": round(total_frames / (ms_e2e * 1e-3), 1),
-                "host_ms_per_step": round(t_host / args.steps, 3), "host_threads": max(1, min(args.host_threads, B)),
-                "coefficient_rewrites": rewrites[0]},
+        "e2e": {"value": round(e2e_value, 1), "unit": "Mpixel/s", "h2d_bytes_per_step": int(h2d * F),
+                "d2h_bytes_per_step": int(d2h * F), "frames_per_s": round(total_frames / (ms_e2e * 1e-3), 1),
+                "timed_region_ms": round(ms_e2e, 1), "host_ms_per_step": round(host_ms / args.steps, 3),
+                "host_cpu_ms_per_frame": round(cpu_ms / max(1, r_e2e.frames), 4), "host_threads": threads,
+                "driver": "hevc_b200/csrc/e2e_driver.c (C frame threads; lists memcpy'd into the job's pinned arenas, "
+                          "validated on the device)" if args.fill == "copy" else "e2e_driver.c, copying ohcu_append_* entry points",
+                "lists_in_place": {"frames_per_s": round(total_frames / (ms_inplace * 1e-3), 1),
+                                   "host_cpu_ms_per_frame": round(r_inplace.work_cpu_ms / max(1, r_inplace.frames), 4)}},
+        "chained_streams_frames_per_s": chain,
         "roofline": {"bound": "hbm", "kernel": "mc_kernel (motion compensation: qpel / epel, uni / bi / weighted)",
                      "achieved": round(achieved, 1),
                      "peak": hbm_peak, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "unit": "GB/s",
@@ -447,7 +443,7 @@ def run_ours(args, rank, world):
                      "algorithmic_mb_per_frame_survey_4pass": round(ab["pipeline_survey"] / 1e6, 2),
                      "gbs_at_value": round(ab["pipeline"] * total_frames / world / (ms_resident * 1e-3) / 1e9, 1),
                      "frac_of_peak_at_value": round(ab["pipeline"] * total_frames / world / (ms_resident * 1e-3) / 1e9 / hbm_peak, 4)},
-        "parity_check": check,
+        "parity_check": check, "parity_frames_checked": checked,
     }
     if world == 1 and not args.no_cpu:
         cb = cpu_reference(jobs, refs, steps=args.cpu_steps, warmup=1, all_arms=True)
@@ -459,7 +455,7 @@ def run_ours(args, rank, world):
 def run_reference(args, rank, world):
     if rank != 0:
         return
-    jobs, refs = make_inputs(args.workload, 0)
+    jobs, refs = make_inputs(args.workload, 0, distinct=min(frames_per_rank(args.workload, 1)[0], 16))
     if args.coeffs == "levels":
         levels_inputs(jobs)               # same coefficient values as the GPU arm reconstructs from
     if args.bs == "derived":
@@ -470,7 +466,7 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": "Mpixel/s reconstructed per B200 (4K Main10); HBM GB/s vs peak",
         "value": round(cb["value"], 2), "unit": "Mpixel/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(cb["ms_per_step"], 2), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None,
+        "scaling": "strong" if args.workload == "8k" else "weak", "vs_baseline": None,
         "dtype": "int32 accumulate on u16 samples / int16 coefficients" if sp.bit_depth > 8 else
         "int32 accumulate on u8 samples / int16 coefficients",
         "data": "synthetic", "config": {"workload": WORKLOAD_NAMES[args.workload]},
@@ -491,7 +487,12 @@ def main():
     ap.add_argument("--workload", default="4k", choices=list(WORKLOADS))
     ap.add_argument("--frames", type=int, default=0, help="frames per step per GPU (default per workload)")
     ap.add_argument("--cpu-steps", type=int, default=4, help="steps of the cpu_baseline leg")
-    ap.add_argument("--host-threads", type=int, default=4, help="threads submitting frames in the e2e leg")
+    ap.add_argument("--host-threads", type=int, default=0,
+                    help="frame threads of the e2e leg (default: min(8, host cores / ranks))")
+    ap.add_argument("--fill", default="copy", choices=["copy", "append"],
+                    help="e2e leg: lists memcpy'd into the job's pinned arenas and validated on the device (copy: the in-place path, "
+                         "ohcu_frame_arenas_get / ohcu_frame_commit_lists), or handed to the copying, host-validated ohcu_append_* calls")
+    ap.add_argument("--no-chain", action="store_true", help="skip the chained-streams leg")
     ap.add_argument("--coeffs", default="sparse", choices=["dense", "sparse", "levels"],
                     help="coefficient form handed to the library: (position, level) pairs of the significant "
                          "coefficients (ohcu_append_tu_sparse, what the residual parser produces), zero-filled N x N blocks, or "
@@ -502,8 +503,6 @@ def main():
     ap.add_argument("--copy-out", choices=["2d", "pitch", "packed"], default="2d",
                     help="e2e leg, device -> host: pitched 2-D copies into tight planes (2d), linear copies into planes with "
                          "the device pitch (pitch), or ohcu_slot_output_cropped: pack kernel + one linear copy (packed)")
-    ap.add_argument("--slot-pitch", action="store_true",
-                    help="e2e leg: host pictures with the device planes' row pitch (one linear copy per plane)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-check", action="store_true")
     args = ap.parse_args()

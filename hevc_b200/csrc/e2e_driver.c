@@ -141,10 +141,10 @@ static int fill_append(run_state *st, int job, const ohdrv_frame *f)
     return 0;
 }
 
-typedef struct thread_arg { run_state *st; double cpu_ms; int frames; } thread_arg;
+typedef struct thread_arg { run_state *st; double cpu_ms, work_ms; int frames; } thread_arg;
 
 /* one frame: wait for its turn on its ring entry / stream, begin, fill, flush, ask for the picture */
-static int submit_frame(run_state *st, int i)
+static int submit_frame(run_state *st, int i, double *work_ms)
 {
     const ohdrv_config *cfg = st->cfg;
     int k, key, ticket, slot_a = -1, slot_b = -1, fidx, rc = 0;
@@ -175,6 +175,7 @@ static int submit_frame(run_state *st, int i)
     }
     if (job < 0) { set_err(st, "ohcu_frame_begin", job); rc = job; goto out; }
     TRACE("frame %d: job %d\n", i, job);
+    const double w0 = now_ms(CLOCK_THREAD_CPUTIME_ID);           /* the library's and the fill's own CPU time: no waiting in it */
     if (cfg->frame_by_job) fidx = job;
     const ohdrv_frame *f = &st->frames[fidx % st->n_frames];
     if (cfg->fill == OHDRV_APPEND) rc = fill_append(st, job, f);
@@ -192,6 +193,7 @@ static int submit_frame(run_state *st, int i)
             set_err(st, "ohcu_slot_output_cropped_async", rc);
     }
     if (cfg->last_frame) cfg->last_frame[k] = fidx % st->n_frames;
+    *work_ms += now_ms(CLOCK_THREAD_CPUTIME_ID) - w0;
     TRACE("frame %d: submitted\n", i);
 out:
     atomic_store(&st->turn[key], ticket + 1);
@@ -214,7 +216,7 @@ static void *frame_thread(void *p)
             atomic_store(&st->turn[key], ticket + 1);
             continue;
         }
-        if (submit_frame(st, i) >= 0) ta->frames++;
+        if (submit_frame(st, i, &ta->work_ms) >= 0) ta->frames++;
     }
     ta->cpu_ms = now_ms(CLOCK_THREAD_CPUTIME_ID) - t0;
     return NULL;
@@ -251,7 +253,7 @@ int ohdrv_run(ohcu_ctx *ctx, const ohdrv_frame *frames, int n_frames, const ohdr
     if (cfg->timed && (rc = ohcu_timer_start(ctx))) { pthread_mutex_unlock(&run_mu); return rc; }
     const double w0 = now_ms(CLOCK_MONOTONIC);
     for (int t = 0; t < cfg->threads; t++) {
-        ta[t].st = &st; ta[t].cpu_ms = 0; ta[t].frames = 0;
+        ta[t].st = &st; ta[t].cpu_ms = 0; ta[t].work_ms = 0; ta[t].frames = 0;
         pthread_create(&th[t], NULL, frame_thread, &ta[t]);
     }
     for (int t = 0; t < cfg->threads; t++) pthread_join(th[t], NULL);
@@ -260,7 +262,7 @@ int ohdrv_run(ohcu_ctx *ctx, const ohdrv_frame *frames, int n_frames, const ohdr
     if (cfg->timed) rc = ohcu_timer_stop(ctx, &res->device_ms);
     else rc = ohcu_sync_all(ctx);
     res->wall_ms = now_ms(CLOCK_MONOTONIC) - w0;
-    for (int t = 0; t < cfg->threads; t++) { res->thread_cpu_ms += ta[t].cpu_ms; res->frames += ta[t].frames; }
+    for (int t = 0; t < cfg->threads; t++) { res->thread_cpu_ms += ta[t].cpu_ms; res->work_cpu_ms += ta[t].work_ms; res->frames += ta[t].frames; }
     pthread_mutex_destroy(&st.err_mu);
     if (atomic_load(&st.failed)) {
         snprintf(res->error, sizeof(res->error), "%s", st.err);

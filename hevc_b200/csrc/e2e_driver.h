@@ -79,7 +79,8 @@ typedef struct ohdrv_result {
     float device_ms;                /* ohcu_timer_stop: device time from the start event to the last job / download */
     double wall_ms;                 /* host wall clock of the same region                                      */
     double host_ms;                 /* until the last frame thread returned (everything enqueued)              */
-    double thread_cpu_ms;           /* CPU time summed over the frame threads                                  */
+    double thread_cpu_ms;           /* CPU time summed over the frame threads (includes CUDA's spin-waits)     */
+    double work_cpu_ms;             /* of which: filling the lists, flush, download calls (no waiting)         */
     int32_t frames;
     char error[512];
 } ohdrv_result;

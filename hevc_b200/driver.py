@@ -38,7 +38,7 @@ class Config(C.Structure):
 
 class Result(C.Structure):
     _fields_ = [("device_ms", C.c_float), ("wall_ms", C.c_double), ("host_ms", C.c_double),
-                ("thread_cpu_ms", C.c_double), ("frames", C.c_int32), ("error", C.c_char * 512)]
+                ("thread_cpu_ms", C.c_double), ("work_cpu_ms", C.c_double), ("frames", C.c_int32), ("error", C.c_char * 512)]
 
 
 _drv = None
