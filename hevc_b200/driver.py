@@ -9,8 +9,8 @@ import numpy as np
 from . import abi
 from .sparse import ctb_index, to_levels, to_sparse
 
-HERE = os.path.dirname(os.path.abspath(__file__))
-DRV_PATH = os.path.join(HERE, "libohcu_drv.so")
+# beside the libohcu.so in use (OHCU_LIB selects another build for A/B runs; its driver copy resolves it through $ORIGIN)
+DRV_PATH = os.path.join(os.path.dirname(os.path.abspath(abi.LIB_PATH)), "libohcu_drv.so")
 
 FILL_COPY, FILL_NONE, APPEND = 0, 1, 2
 DOWNLOAD_NONE, DOWNLOAD_PLANES, DOWNLOAD_CROPPED = 0, 1, 2
