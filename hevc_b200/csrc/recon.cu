@@ -993,7 +993,7 @@ __global__ void __launch_bounds__(RC_THREADS, RC_MINB) residual_kernel(const __g
     RC_MARK(1);
 
     // ---- TBs of the CTB sorted by size (counting sort) and the arena range their coefficients
-    //      occupy; runs while the first round of windows is in flight
+    //      occupy
     auto sort_tus = [&]() {
         if (nt > 0) {
             if (tid == RC_THREADS - 1 && f.ctb_coef_range) { const int2 cr = f.ctb_coef_range[ctb]; tu_cnt[15] = cr.x; tu_cnt[16] = cr.y; }

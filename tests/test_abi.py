@@ -55,3 +55,23 @@ def test_struct_layout_matches_the_c_header(tmp_path):
         assert C.sizeof(cls) == layout[name]["sizeof"], name
         offs = {f[0]: getattr(cls, f[0]).offset for f in cls._fields_}
         assert offs == layout[name]["fields"], f"{name}: {offs} != {layout[name]['fields']}"
+
+
+def test_cmake_builds_the_same_library(tmp_path):
+    """north_star: "the build (CMake with nvcc for sm_100a)".  CMakeLists.txt must configure, build for sm_100a only and
+    export exactly the symbols of the in-tree build (nvcc cross-compiles without a GPU)."""
+    import shutil
+    import subprocess
+    if not shutil.which("cmake") or not shutil.which("nvcc"):
+        import pytest
+        pytest.skip("cmake / nvcc not on PATH")
+    b = str(tmp_path / "b")
+    subprocess.check_call(["cmake", "-S", ROOT, "-B", b, "-DCMAKE_CUDA_COMPILER=" + shutil.which("nvcc")], stdout=subprocess.DEVNULL)
+    subprocess.check_call(["cmake", "--build", b, "-j", "8"], stdout=subprocess.DEVNULL)
+    so = os.path.join(b, "libohcu.so")
+    exported = {l.split()[-1] for l in subprocess.check_output(["nm", "-D", "--defined-only", so], text=True).splitlines()
+                if " T ohcu_" in l}
+    assert exported == _declared()
+    elfs = subprocess.check_output(["cuobjdump", "-lelf", so], text=True)
+    assert "sm_100a" in elfs and not re.search(r"sm_(?!100a)\d+", elfs), elfs
+    assert os.path.exists(os.path.join(b, "libohcu_drv.so"))
