@@ -336,24 +336,35 @@ def run_ours(args, rank, world):
     else:
         outs = [ctx.pinned_picture(slot_pitch=args.copy_out == "pitch") for _ in range(RING)]
         dl = driver.DOWNLOAD_PLANES
-    fill = {"copy": driver.FILL_COPY, "append": driver.APPEND}[args.fill]
     total = args.steps * F
-    driver.run(ctx, frames, total_frames=max(RING, args.warmup * min(F, 4 * RING)), threads=threads, ring=RING, first_slot=FIRST_OUT,
-               fill=fill, download=dl, outs=outs, timed=False)
+
+    def e2e_run(fill, n, timed=True):
+        """inplace: every job arena is first filled with the frame it will carry (untimed, as a parser that writes its
+        records where the library reads them would have), then only the small per-frame tables are written per frame"""
+        by_job = fill == "inplace"
+        if by_job:
+            driver.run(ctx, frames, total_frames=njobs, threads=1, ring=RING, first_slot=FIRST_OUT, fill=driver.FILL_COPY,
+                       frame_by_job=True, timed=False)
+        mode = {"inplace": driver.FILL_NONE, "copy": driver.FILL_COPY, "append": driver.APPEND}[fill]
+        return driver.run(ctx, frames, total_frames=n, threads=threads, ring=RING, first_slot=FIRST_OUT, fill=mode,
+                          frame_by_job=by_job, download=dl, outs=outs, timed=timed)
+
+    e2e_run(args.fill, max(RING, args.warmup * min(F, 4 * RING)), timed=False)
     barrier()
     with ClockSampler(device) as clk2:
-        r_e2e, last = driver.run(ctx, frames, total_frames=total, threads=threads, ring=RING, first_slot=FIRST_OUT, fill=fill,
-                                 download=dl, outs=outs)
+        r_e2e, last = e2e_run(args.fill, total)
     barrier()
     ms_e2e, host_ms, cpu_ms = r_e2e.device_ms, r_e2e.host_ms, r_e2e.work_cpu_ms
     e2e_pics = [(int(last[k]), [p.copy() for p in outs[k]]) for k in range(RING)]
     d2h = sum(p.strides[0] * (p.shape[0] - 1) + p.shape[1] * p.itemsize for p in outs[0])
     h2d = int(np.mean(frames.h2d_bytes))
-    # the same with the big lists found in place (a parser that wrote them there): the library's own host cost
+    # the other way of handing the lists over, for comparison: every list memcpy'd into the arenas per frame
+    # (or, when that is the main mode, found in place)
+    other = "copy" if args.fill == "inplace" else "inplace"
+    r_other, _ = e2e_run(other, total)
+    # leave every arena holding its own frame for the chained leg
     driver.run(ctx, frames, total_frames=njobs, threads=1, ring=RING, first_slot=FIRST_OUT, fill=driver.FILL_COPY,
                frame_by_job=True, timed=False)
-    r_inplace, _ = driver.run(ctx, frames, total_frames=total, threads=threads, ring=RING, first_slot=FIRST_OUT,
-                              fill=driver.FILL_NONE, frame_by_job=True, download=dl, outs=outs)
     # ---------------- chained streams: picture t predicts from t-1 and t-2 of its stream (what a decoder does),
     # lists in place, no download: the kernels' throughput when frames depend on each other
     chain = {}
@@ -378,7 +389,7 @@ def run_ours(args, rank, world):
     bad = shard.max_over_ranks([1.0 if check == "MISMATCH" else 0.0], device=f"cuda:{device}")[0]
 
     # ---------------- reduce over ranks
-    ms_resident, ms_e2e, ms_inplace, host_ms = shard.max_over_ranks([ms_resident, ms_e2e, r_inplace.device_ms, host_ms], device=f"cuda:{device}")
+    ms_resident, ms_e2e, ms_other, host_ms = shard.max_over_ranks([ms_resident, ms_e2e, r_other.device_ms, host_ms], device=f"cuda:{device}")
     ctx.close()
     if rank != 0:
         return
@@ -423,10 +434,14 @@ def run_ours(args, rank, world):
                 "d2h_bytes_per_step": int(d2h * F), "frames_per_s": round(total_frames / (ms_e2e * 1e-3), 1),
                 "timed_region_ms": round(ms_e2e, 1), "host_ms_per_step": round(host_ms / args.steps, 3),
                 "host_cpu_ms_per_frame": round(cpu_ms / max(1, r_e2e.frames), 4), "host_threads": threads,
-                "driver": "hevc_b200/csrc/e2e_driver.c (C frame threads; lists memcpy'd into the job's pinned arenas, "
-                          "validated on the device)" if args.fill == "copy" else "e2e_driver.c, copying ohcu_append_* entry points",
-                "lists_in_place": {"frames_per_s": round(total_frames / (ms_inplace * 1e-3), 1),
-                                   "host_cpu_ms_per_frame": round(r_inplace.work_cpu_ms / max(1, r_inplace.frames), 4)}},
+                "driver": "hevc_b200/csrc/e2e_driver.c: C frame threads; " + {
+                    "inplace": "the frame's lists sit in the job's pinned arenas where the parser wrote them (ohcu_frame_arenas_get / "
+                               "ohcu_frame_commit_lists), per frame the small tables are written, everything is uploaded and validated on the device",
+                    "copy": "every list memcpy'd into the job's pinned arenas per frame, validated on the device",
+                    "append": "the copying, host-validated ohcu_append_* / ohcu_set_* entry points"}[args.fill],
+                "lists_" + ("copied" if other == "copy" else "in_place"): {
+                    "frames_per_s": round(total_frames / (ms_other * 1e-3), 1),
+                    "host_cpu_ms_per_frame": round(r_other.work_cpu_ms / max(1, r_other.frames), 4)}},
         "chained_streams_frames_per_s": chain,
         "roofline": {"bound": "hbm", "kernel": "mc_kernel (motion compensation: qpel / epel, uni / bi / weighted)",
                      "achieved": round(achieved, 1),
@@ -489,9 +504,10 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=4, help="steps of the cpu_baseline leg")
     ap.add_argument("--host-threads", type=int, default=0,
                     help="frame threads of the e2e leg (default: min(8, host cores / ranks))")
-    ap.add_argument("--fill", default="copy", choices=["copy", "append"],
-                    help="e2e leg: lists memcpy'd into the job's pinned arenas and validated on the device (copy: the in-place path, "
-                         "ohcu_frame_arenas_get / ohcu_frame_commit_lists), or handed to the copying, host-validated ohcu_append_* calls")
+    ap.add_argument("--fill", default="inplace", choices=["inplace", "copy", "append"],
+                    help="e2e leg, how a frame's lists reach the library: found in the job's pinned arenas where the parser wrote them "
+                         "(inplace: ohcu_frame_arenas_get / ohcu_frame_commit_lists, validated on the device), memcpy'd into those arenas "
+                         "per frame (copy), or handed to the copying, host-validated ohcu_append_* calls (append)")
     ap.add_argument("--no-chain", action="store_true", help="skip the chained-streams leg")
     ap.add_argument("--coeffs", default="sparse", choices=["dense", "sparse", "levels"],
                     help="coefficient form handed to the library: (position, level) pairs of the significant "

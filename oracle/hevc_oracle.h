@@ -95,4 +95,13 @@ void or_dequant_tus(const struct ohcu_tu *tus, const struct ohcu_tu_quant *quant
 #ifdef __cplusplus
 }
 #endif
+/* ---- intra prediction (intra_oracle.c; hevcpred_template.c) */
+#define OR_CAND_BOTTOM_LEFT 1
+#define OR_CAND_LEFT        2
+#define OR_CAND_UP_LEFT     4
+#define OR_CAND_UP          8
+#define OR_CAND_UP_RIGHT   16
+void or_intra_pred(int bd, uint8_t *plane, ptrdiff_t stride, int pw, int ph, int x, int y, int log2_size, int c_idx,
+                   int mode, int cand, int filter_ok, int strong);
+
 #endif

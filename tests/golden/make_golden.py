@@ -7,6 +7,7 @@ Run in the build container (needs /root/reference):  python tests/golden/make_go
                       (tests/frame_cases.py) after MC, MC+residual, and the full pipeline
   frames_fullsize.json  the same for BASELINE configs[1..4] at their named sizes (1080p 8-bit, 4K Main10,
                       1080p 10-bit 4:2:2 / 4:4:4, 8K Main10), MC+residual and the full pipeline
+  intra_digests.json  intra prediction, every mode x size x availability pattern (tests/intra_cases.py)
   cfg1_416x240.npz    the full golden picture of BASELINE.json configs[0]
 """
 import hashlib
@@ -24,6 +25,7 @@ import frame_cases  # noqa: E402
 import leaf_cases  # noqa: E402
 import levels_cases  # noqa: E402
 import bs_cases  # noqa: E402
+import intra_cases  # noqa: E402
 import oracle_lib  # noqa: E402
 
 STAGE_SETS = {"mc": 1, "mc_res": 3, "mc_res_db": 7, "all": 15}
@@ -80,6 +82,11 @@ def main():
     with open(os.path.join(HERE, "bs_digests.json"), "w") as f:
         json.dump({"source": "ohref_boundary_strengths (hevc_filter.c ff_hevc_deblocking_boundary_strengths per leaf)",
                    "cases": bs}, f, indent=1, sort_keys=True)
+    # intra prediction: the reference's HEVCPredContext table (ff_hevc_pred_init) through oracle/ref_shim_pred.c
+    intra = {name: intra_cases.run_group(ref, calls, "ref") for name, calls in intra_cases.groups()}
+    with open(os.path.join(HERE, "intra_digests.json"), "w") as f:
+        json.dump({"source": "ohref_intra_pred (HEVCPredContext.intra_pred of ff_hevc_pred_init, hevcpred_template.c)",
+                   "cases": intra}, f, indent=1, sort_keys=True)
     print(f"{len(leaves)} leaf digests, {len(frames)} frame cases, {len(outs)} dequantisation cases written")
 
 

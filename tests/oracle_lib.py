@@ -141,6 +141,15 @@ class Lib:
         self._bs = getattr(self.lib, prefix + "boundary_strengths")
         self._bs.restype = C.c_int
         self._bs.argtypes = [C.POINTER(BsJobC)]
+        # intra prediction: oracle and reference take different arguments (tests/intra_cases.py)
+        if which == "oracle":
+            self.intra_pred = self.lib.or_intra_pred
+            self.intra_pred.restype = None
+            self.intra_pred.argtypes = [_I, _P, _S] + [_I] * 10
+        elif hasattr(self.lib, "ohref_intra_pred"):
+            self.intra_pred_ref = self.lib.ohref_intra_pred
+            self.intra_pred_ref.restype = _I
+            self.intra_pred_ref.argtypes = [_I, _P, _S] + [_I] * 11
         self._replay = getattr(self.lib, prefix + "replay_frame")
         self._replay.restype = C.c_int
         self._replay.argtypes = [C.POINTER(FrameJobC)]
