@@ -222,6 +222,7 @@ SYMBOLS = {
     "ohcu_dsp_transform_skip": (C.c_int, [_I, _P, _I]),
     "ohcu_dsp_transform_rdpcm": (C.c_int, [_I, _P, _I, _I]),
     "ohcu_dsp_transform_add": (C.c_int, [_I, _P, _P, _S, _I]),
+    "ohcu_dsp_intra_pred": (C.c_int, [_I, _P, _S] + [_I] * 10),
     "ohcu_dsp_loop_filter_luma": (C.c_int, [_I, _I, _P, _S, _I, _P, _P, _P]),
     "ohcu_dsp_loop_filter_chroma": (C.c_int, [_I, _I, _P, _S, _P, _P, _P]),
     "ohcu_dsp_sao_band_filter": (C.c_int, [_I, _P, _P, _S, _S, _P, _I, _I, _I]),

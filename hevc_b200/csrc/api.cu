@@ -1502,6 +1502,13 @@ extern "C" int ohcu_dsp_transform_add(int bd, uint8_t *dst, const int16_t *coeff
     DSP_ENTER();
     return DSP_RC(dsp_transform_add(bd, dst, coeffs, stride, n));
 }
+extern "C" int ohcu_dsp_intra_pred(int bd, uint8_t *plane, ptrdiff_t stride, int pw, int ph, int x, int y, int log2_size, int c_idx, int mode,
+                                   int cand, int filter_ok, int strong)
+{
+    DSP_ENTER();
+    if (!plane || (bd != 8 && bd != 9 && bd != 10 && bd != 12 && bd != 14)) return fail(OHCU_EINVAL, "bad plane or bit depth");
+    return DSP_RC(dsp_intra_pred(bd, plane, stride, pw, ph, x, y, log2_size, c_idx, mode, cand, filter_ok, strong));
+}
 extern "C" int ohcu_dsp_loop_filter_luma(int bd, int vertical, uint8_t *pix, ptrdiff_t stride, int beta, const int *tc, const uint8_t *no_p,
                                          const uint8_t *no_q)
 {

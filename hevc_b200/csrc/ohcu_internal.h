@@ -121,6 +121,8 @@ int dsp_loop_filter(int bd, int luma, int vertical, uint8_t *pix, ptrdiff_t stri
                     const uint8_t *no_q);
 int dsp_sao(int bd, int edge, uint8_t *dst, const uint8_t *src, ptrdiff_t stride_dst, ptrdiff_t stride_src, const int16_t *offset_val,
             int eo_or_band, int w, int h);
+int dsp_intra_pred(int bd, uint8_t *plane, ptrdiff_t stride, int pw, int ph, int x, int y, int log2_size, int c_idx, int mode, int cand,
+                   int filter_ok, int strong);                    // intra.cu
 void loopfilter_box(const FrameDev &f, int c, int *bw, int *bh);
 int launch_pad_picture(const FrameDev &f, const PlaneSet &pic, cudaStream_t st);   // fill the replicated halo
 int launch_copy_picture(const FrameDev &f, const PlaneSet &dst, const PlaneSet &src, cudaStream_t st);

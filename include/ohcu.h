@@ -543,6 +543,21 @@ int ohcu_dsp_transform_add(int bd, uint8_t *dst, const int16_t *coeffs, ptrdiff_
  *  are serialised inside the library, and anything else that would overlap with them on the GPU races.       */
 #define OHCU_NOALLOC_MAX_BYTES 65536
 int ohcu_dsp_idct_noalloc(int bd, int16_t *coeffs, int log2_size, int col_limit, int nblocks);
+/*  HEVCPredContext.intra_pred[log2_size - 2](s, x0, y0, c_idx)  hevcpred.h:30-41, hevcpred_template.c:30-345 and the
+ *  predictors it dispatches to (pred_planar :359, pred_dc :388, pred_angular :419): one N x N block of a plane predicted
+ *  IN PLACE from the reconstructed samples left of and above it (first step: the block function and
+ *  its table semantics; the frame-level wavefront kernel follows).  plane = sample (0, 0) of the plane (host), stride in
+ *  bytes, pw x ph its size in samples, (x, y) the block in plane samples, mode 0 planar, 1 DC, 2..34 angular.
+ *  cand = the five final availability flags the reference computes at hevcpred_template.c:103-107 (lc->na.cand_* combined
+ *  with the z-scan order test).  filter_ok = !sps->intra_smoothing_disabled_flag && (c_idx == 0 || chroma_format_idc == 3),
+ *  strong = sps->sps_strong_intra_smoothing_enable_flag.  constrained_intra_pred_flag must be 0.                       */
+#define OHCU_CAND_BOTTOM_LEFT 1
+#define OHCU_CAND_LEFT        2
+#define OHCU_CAND_UP_LEFT     4
+#define OHCU_CAND_UP          8
+#define OHCU_CAND_UP_RIGHT   16
+int ohcu_dsp_intra_pred(int bd, uint8_t *plane, ptrdiff_t stride, int pw, int ph, int x, int y, int log2_size, int c_idx,
+                        int mode, int cand, int filter_ok, int strong);
 /*  hevc_{h,v}_loop_filter_{luma,chroma}: pix = first Q sample, tc / no_p / no_q per 4-line
  *  segment                                                     hevcdsp.h:128-131             */
 int ohcu_dsp_loop_filter_luma(int bd, int vertical, uint8_t *pix, ptrdiff_t stride, int beta,

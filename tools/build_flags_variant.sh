@@ -6,5 +6,5 @@ name=$1; shift
 d=/root/repo/tools/variants/$name
 mkdir -p $d
 cd /root/repo/hevc_b200/csrc
-nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -shared "$@" -o $d/libohcu.so api.cu recon.cu loopfilter.cu picture.cu bs.cu prepare.cu
+nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -shared "$@" -o $d/libohcu.so api.cu recon.cu loopfilter.cu picture.cu bs.cu prepare.cu intra.cu
 cp /root/repo/hevc_b200/libohcu_drv.so $d/
