@@ -173,6 +173,7 @@ SYMBOLS = {
     "ohcu_slot_output_cropped": (C.c_int, [_P, C.c_int, C.POINTER(Crop), C.POINTER(_P * 3)]),
     "ohcu_slot_output_cropped_async": (C.c_int, [_P, C.c_int, C.POINTER(Crop), C.POINTER(_P * 3)]),
     "ohcu_slot_sync": (C.c_int, [_P, C.c_int]),
+    "ohcu_slot_md5": (C.c_int, [_P, C.c_int, _P]),
     "ohcu_frame_begin": (C.c_int, [_P, C.c_int, C.c_int]),
     "ohcu_set_slice": (C.c_int, [_P, C.c_int, C.c_int, C.POINTER(SliceTab)]),
     "ohcu_append_pu": (C.c_int, [_P, C.c_int, _P, C.c_int]),

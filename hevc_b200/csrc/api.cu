@@ -142,6 +142,7 @@ struct ohcu_ctx {
     int64_t launches = 0;
     void *l2_buf = nullptr;
     size_t l2_bytes = 0;
+    uint8_t *md5_d = nullptr;         // 48 bytes per slot (ohcu_slot_md5)
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     // Frame threads each drive their own job; the lists of a job are touched by one thread
     // at a time (caller's contract).  What jobs share — the job ring, the slots' ordering
@@ -293,6 +294,7 @@ extern "C" int ohcu_destroy(ohcu_ctx *c)
     for (int i = 1; i < COPY_LANES; i++) if (c->copy_lanes[i]) cudaStreamDestroy(c->copy_lanes[i]);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->l2_buf) cudaFree(c->l2_buf);
+    if (c->md5_d) cudaFree(c->md5_d);
     if (c->t0) cudaEventDestroy(c->t0);
     if (c->t1) cudaEventDestroy(c->t1);
     delete c;
@@ -606,6 +608,33 @@ extern "C" int ohcu_slot_output_cropped_async(ohcu_ctx *c, int slot, const ohcu_
 {
     return output_cropped_impl(c, slot, crop, planes, false);
 }
+// verify_md5 (hevcdec.c:4035-4098) without moving the picture: one MD5 per plane, computed on the device
+extern "C" int ohcu_slot_md5(ohcu_ctx *c, int slot, uint8_t md5[3][16])
+{
+    ENTER(c);
+    if (check_slot(c, slot)) return OHCU_EINVAL;
+    if (!md5) return fail(OHCU_EINVAL, "null argument");
+    Slot &s = c->slots[slot];
+    uint8_t *out = nullptr;
+    cudaStream_t cs;
+    {
+        std::lock_guard<std::mutex> lock(c->mu);
+        if (s.released) return fail(OHCU_ESTATE, "DPB slot %d was released and not written since", slot);
+        if (!c->md5_d) CU(cudaMalloc((void **)&c->md5_d, 48 * c->slots.size()));
+        out = c->md5_d + 48 * slot;
+        cs = c->copy_lanes[s.copy_lane];
+        if (s.has_ready) CU(cudaStreamWaitEvent(cs, s.ready, 0));
+        c->launches += launch_md5(s.pic.ps, c->nplanes, c->P, c->pw, c->ph, out, cs);
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(s.read_done, cs));                  // the next writer of the slot waits for the hash like for a download
+        s.has_read = true;
+    }
+    memset(md5, 0, 48);
+    CU(cudaMemcpyAsync(md5, out, 16 * c->nplanes, cudaMemcpyDeviceToHost, cs));
+    CU(cudaStreamSynchronize(cs));
+    return slot_list_error(c, slot);
+}
+
 extern "C" int ohcu_slot_sync(ohcu_ctx *c, int slot)
 {
     ENTER(c);

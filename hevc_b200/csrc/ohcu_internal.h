@@ -129,6 +129,7 @@ int launch_copy_picture(const FrameDev &f, const PlaneSet &dst, const PlaneSet &
 // the window of every plane packed without row gaps (ohcu_slot_output_cropped)
 int launch_crop_pack(const PlaneSet &pic, int nplanes, int P, const int left[3], const int top[3], const int w[3],
                      const int h[3], uint8_t *const dst[3], cudaStream_t st);
+int launch_md5(const PlaneSet &pic, int nplanes, int P, const int pw[3], const int ph[3], uint8_t *out48, cudaStream_t st);
 int launch_l2_flush(void *buf, size_t bytes, cudaStream_t st);
 int set_error(int code, const char *fmt, ...);     // text for ohcu_last_error() of the calling thread; returns code
 

@@ -170,3 +170,109 @@ int launch_l2_flush(void *buf, size_t bytes, cudaStream_t st)
 }
 
 }  // namespace ohcu
+
+// ================================================================= picture hash (verify_md5, hevcdec.c:4035-4098)
+// The SEI picture hash is one RFC 1321 MD5 per plane over its rows (w << pixel_shift bytes each, little endian).
+// MD5 is a serial chain of 64-byte blocks, so a plane is ONE thread's work: a warp per plane stages 512 bytes (eight
+// blocks) per step with 16-byte loads, lane 0 runs the chain out of shared memory.  This exists so that a conformance
+// run can verify pictures without moving them across the bus, and so that the cost is a measured number
+// (DESIGN.md section 4.6): a chain step is ~5 dependent ALU operations, nothing inside a plane runs in parallel.
+namespace ohcu {
+
+__constant__ uint32_t c_md5_k[64] = {
+    0xd76aa478, 0xe8c7b756, 0x242070db, 0xc1bdceee, 0xf57c0faf, 0x4787c62a, 0xa8304613, 0xfd469501, 0x698098d8, 0x8b44f7af,
+    0xffff5bb1, 0x895cd7be, 0x6b901122, 0xfd987193, 0xa679438e, 0x49b40821, 0xf61e2562, 0xc040b340, 0x265e5a51, 0xe9b6c7aa,
+    0xd62f105d, 0x02441453, 0xd8a1e681, 0xe7d3fbc8, 0x21e1cde6, 0xc33707d6, 0xf4d50d87, 0x455a14ed, 0xa9e3e905, 0xfcefa3f8,
+    0x676f02d9, 0x8d2a4c8a, 0xfffa3942, 0x8771f681, 0x6d9d6122, 0xfde5380c, 0xa4beea44, 0x4bdecfa9, 0xf6bb4b60, 0xbebfbc70,
+    0x289b7ec6, 0xeaa127fa, 0xd4ef3085, 0x04881d05, 0xd9d4d039, 0xe6db99e5, 0x1fa27cf8, 0xc4ac5665, 0xf4292244, 0x432aff97,
+    0xab9423a7, 0xfc93a039, 0x655b59c3, 0x8f0ccc92, 0xffeff47d, 0x85845dd1, 0x6fa87e4f, 0xfe2ce6e0, 0xa3014314, 0x4e0811a1,
+    0xf7537e82, 0xbd3af235, 0x2ad7d2bb, 0xeb86d391};
+__constant__ uint8_t c_md5_s[64] = {7, 12, 17, 22, 7, 12, 17, 22, 7, 12, 17, 22, 7, 12, 17, 22, 5, 9, 14, 20, 5, 9, 14, 20, 5, 9, 14, 20, 5, 9, 14, 20,
+                                    4, 11, 16, 23, 4, 11, 16, 23, 4, 11, 16, 23, 4, 11, 16, 23, 6, 10, 15, 21, 6, 10, 15, 21, 6, 10, 15, 21, 6, 10, 15, 21};
+
+__device__ __forceinline__ void md5_block(uint32_t (&h)[4], const uint32_t *m)
+{
+    uint32_t a = h[0], b = h[1], c = h[2], d = h[3];
+#pragma unroll
+    for (int i = 0; i < 64; i++) {
+        uint32_t f;
+        int g;
+        if (i < 16) { f = (b & c) | (~b & d); g = i; }
+        else if (i < 32) { f = (d & b) | (~d & c); g = (5 * i + 1) & 15; }
+        else if (i < 48) { f = b ^ c ^ d; g = (3 * i + 5) & 15; }
+        else { f = c ^ (b | ~d); g = (7 * i) & 15; }
+        f += a + c_md5_k[i] + m[g];
+        a = d; d = c; c = b;
+        b += __funnelshift_l(f, f, c_md5_s[i]);
+    }
+    h[0] += a; h[1] += b; h[2] += c; h[3] += d;
+}
+
+struct Md5Args { const uint8_t *p[3]; int pitch[3], wbytes[3], h[3]; uint8_t *out; };
+
+// one warp per plane (blockIdx.x)
+__global__ void __launch_bounds__(32) md5_kernel(const Md5Args a)
+{
+    __shared__ __align__(16) uint32_t buf[2][128];             // two stages of 512 bytes
+    const int pl = blockIdx.x, lane = threadIdx.x;
+    const uint8_t *base = a.p[pl];
+    const int pitch = a.pitch[pl], wb = a.wbytes[pl];
+    const unsigned long long total = (unsigned long long)wb * a.h[pl];
+    uint32_t h[4] = {0x67452301u, 0xefcdab89u, 0x98badcfeu, 0x10325476u};
+    // message bytes [off, off + 16) of the plane: rows are multiples of 4 bytes, a 16-byte group may straddle a row end
+    auto load16 = [&](unsigned long long off, uint32_t *dst) {
+        int row = (int)(off / wb), col = (int)(off - (unsigned long long)row * wb);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            uint32_t v = 0;
+            if (off + 4 * k < total) v = *(const uint32_t *)(base + (size_t)row * pitch + col);
+            dst[k] = v;
+            col += 4;
+            if (col >= wb) { col = 0; row++; }
+        }
+    };
+    const unsigned long long nfull = total / 64;               // whole blocks
+    unsigned long long blk = 0;
+    int stage = 0;
+    if (nfull) load16((unsigned long long)lane * 16, &buf[0][lane * 4]);
+    __syncwarp();
+    while (blk < nfull) {
+        const int nb = (int)min((unsigned long long)8, nfull - blk);
+        // prefetch the next eight blocks into the other stage while lane 0 chews on these
+        if (blk + 8 < nfull) load16((blk + 8) * 64 + (unsigned long long)lane * 16, &buf[stage ^ 1][lane * 4]);
+        if (lane == 0)
+            for (int i = 0; i < nb; i++) md5_block(h, &buf[stage][16 * i]);
+        __syncwarp();
+        blk += nb;
+        stage ^= 1;
+    }
+    if (lane == 0) {
+        // the tail: remaining bytes, 0x80, zeros, the bit length
+        uint32_t m[32];
+        const int rem = (int)(total - nfull * 64);
+        for (int i = 0; i < 32; i++) m[i] = 0;
+        for (int i = 0; i < rem; i += 4) {
+            const unsigned long long off = nfull * 64 + i;
+            const int row = (int)(off / wb), col = (int)(off - (unsigned long long)row * wb);
+            m[i >> 2] = *(const uint32_t *)(base + (size_t)row * pitch + col);
+        }
+        m[rem >> 2] = 0x80u;                                    // rem is a multiple of 4
+        const int words = rem + 9 > 64 ? 32 : 16;
+        m[words - 2] = (uint32_t)(total << 3);
+        m[words - 1] = (uint32_t)(total >> 29);
+        md5_block(h, m);
+        if (words == 32) md5_block(h, m + 16);
+        for (int i = 0; i < 4; i++) ((uint32_t *)(a.out + 16 * pl))[i] = h[i];
+    }
+}
+
+int launch_md5(const PlaneSet &pic, int nplanes, int P, const int pw[3], const int ph[3], uint8_t *out48, cudaStream_t st)
+{
+    Md5Args a{};
+    for (int i = 0; i < nplanes; i++) { a.p[i] = pic.p[i]; a.pitch[i] = pic.pitch[i]; a.wbytes[i] = pw[i] * P; a.h[i] = ph[i]; }
+    a.out = out48;
+    md5_kernel<<<nplanes, 32, 0, st>>>(a);
+    return 1;
+}
+
+}  // namespace ohcu

@@ -223,6 +223,11 @@ int ohcu_slot_download(ohcu_ctx *ctx, int slot, uint8_t *const planes[3],
 int ohcu_slot_download_async(ohcu_ctx *ctx, int slot, uint8_t *const planes[3],
                              const ptrdiff_t strides[3]);
 int ohcu_slot_sync(ohcu_ctx *ctx, int slot);   /* replaces ff_thread_await_progress */
+/* verify_md5 (hevcdec.c:4035-4098) with the picture left where it is: the SEI picture hash is one MD5 (RFC 1321) per plane
+ * over its rows of (width << pixel_shift) bytes, little endian; md5[c] receives plane c's digest (zeros for absent
+ * planes).  Waits for the slot's producer; synchronous.  MD5 is a serial chain, one thread per plane: ~10^2 ms for a 4K
+ * plane - a conformance tool, not a production path.                                          */
+int ohcu_slot_md5(ohcu_ctx *ctx, int slot, uint8_t md5[3][16]);
 /* Row pitch in bytes of the slots' device planes.  A host plane passed to the download
  * calls with exactly this stride (an AVFrame whose linesize the decoder's get_buffer chose
  * that way) is fetched as ONE linear copy per plane, which runs at the link rate next to

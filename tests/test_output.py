@@ -81,3 +81,21 @@ def test_device_crop_errors():
         for crop in [(0, 0, 418, 240), (-2, 0, 16, 16), (1, 0, 16, 16), (0, 0, 16, 15), (0, 0, 0, 16)]:
             with pytest.raises(abi.OhcuError):
                 ctx.output_cropped(0, crop)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("w,h,bd,cf", [(416, 240, 8, 1), (200, 72, 10, 1), (192, 128, 10, 3), (320, 184, 10, 2), (64, 64, 8, 0), (8, 8, 8, 1)])
+def test_picture_md5_on_the_device(w, h, bd, cf):
+    """ohcu_slot_md5 = verify_md5 (hevcdec.c:4035-4098): per plane, MD5 over the rows; the checker is hashlib (RFC 1321)"""
+    import ctypes as C
+    import hashlib
+    from hevc_b200 import abi, backend, synth
+    job = synth.make_job(w, h, bd, cf, seed=3)
+    pic = synth.make_picture(job.sp, 555)
+    with backend.Context(job.sp) as ctx:
+        ctx.upload(0, pic)
+        out = (C.c_uint8 * 48)()
+        abi.check(ctx.lib.ohcu_slot_md5(ctx.handle, 0, out))
+    got = bytes(out)
+    for c, p in enumerate(pic):
+        assert got[16 * c:16 * c + 16] == hashlib.md5(np.ascontiguousarray(p).tobytes()).digest(), f"plane {c}"
