@@ -34,6 +34,14 @@ FRAME_CASES = {
     "ctb32_8b": (288, 160, 8, 1, 7007, dict(sp_log2_ctb_size=5, split_pct=(0, 50, 40))),
     "ctb16_10b_444": (160, 96, 10, 3, 7008, dict(sp_log2_ctb_size=4, split_pct=(0, 0, 40))),
     "cfg2_small_1080like": (480, 272, 8, 1, 2001, {}),
+    # sao_edge_restore[0 / 1] (hevcdsp_template.c:380-529) directed: 3x3 .. 4x3 CTBs, SAO edge in every CTB (all four
+    # classes), so that every CTB meets the picture-border rule of its class and, with slices that switch
+    # loop_filter_across_slices off and tiles that are not filtered across, every vert / horiz / diag restore flag
+    "sao_restore_borders_8b": (192, 192, 8, 1, 8001, dict(sao_pct=(0, 100))),
+    "sao_restore_slices_10b": (192, 192, 10, 1, 8002, dict(sao_pct=(0, 100), n_slices=5, slices_no_lf=1)),
+    "sao_restore_tiles_8b_444": (256, 192, 8, 3, 8003, dict(sao_pct=(0, 100), tile_cols=2, tile_rows=3, sp_no_tile_filter=1)),
+    "sao_restore_slices_tiles_10b_422": (256, 192, 10, 2, 8004, dict(sao_pct=(10, 90), n_slices=4, slices_no_lf=1, tile_cols=3, tile_rows=2,
+                                                                     sp_no_tile_filter=1, rext=1)),
 }
 
 # BASELINE.json configs[1..4] at their named sizes (one picture each): grids of 510 - 8160 CTBs,
