@@ -34,7 +34,8 @@ class SeqParams(C.Structure):
         ("dpb_slots", C.c_int32), ("jobs", C.c_int32), ("sao_enabled", C.c_int32),
         ("pcm_or_bypass", C.c_int32), ("cb_qp_offset", C.c_int32), ("cr_qp_offset", C.c_int32),
         ("no_tile_filter", C.c_int32), ("max_pus", C.c_int32), ("max_tus", C.c_int32),
-        ("max_coeffs", C.c_int64),
+        ("max_coeffs", C.c_int64), ("intra", C.c_int32), ("max_ius", C.c_int32),
+        ("intra_smoothing_disabled", C.c_int32), ("strong_intra_smoothing", C.c_int32),
     ]
 
 
@@ -65,6 +66,15 @@ class TU(C.Structure):
         ("res_scale_val", C.c_int8), ("pad", C.c_uint16), ("coeff_off", C.c_uint32),
         ("cross_tu", C.c_uint32),
     ]
+
+
+class IU(C.Structure):
+    _fields_ = [("x0", C.c_uint16), ("y0", C.c_uint16), ("c_idx", C.c_uint8), ("log2_size", C.c_uint8),
+                ("mode", C.c_uint8), ("cand", C.c_uint8)]
+
+
+class IuIndex(C.Structure):
+    _fields_ = [("first_iu", C.c_uint32), ("n_iu", C.c_uint32)]
 
 
 class DBParams(C.Structure):
@@ -125,6 +135,7 @@ class FrameArenas(C.Structure):
         ("qp_y_tab", C.c_void_p), ("deblock", C.c_void_p), ("is_pcm", C.c_void_p), ("sao", C.c_void_p),
         ("filter_slice_edges", C.c_void_p), ("tab_slice_address", C.c_void_p), ("tile_id", C.c_void_p),
         ("deblock_disabled", C.c_void_p), ("scaling_list", C.c_void_p),
+        ("ius", C.c_void_p), ("iu_ctbs", C.c_void_p), ("max_ius", C.c_uint32), ("reserved", C.c_uint32),
     ]
 
 
@@ -132,7 +143,7 @@ class FrameCounts(C.Structure):
     _fields_ = [
         ("n_pu", C.c_uint32), ("n_tu", C.c_uint32), ("n_coef", C.c_uint64), ("n_slices", C.c_int32),
         ("coef_form", C.c_int32), ("deblock", C.c_int32), ("sao", C.c_int32), ("pcm", C.c_int32),
-        ("scaling_list", C.c_int32), ("all_inter", C.c_int32),
+        ("scaling_list", C.c_int32), ("all_inter", C.c_int32), ("n_iu", C.c_uint32),
     ]
 
 
@@ -144,10 +155,12 @@ class PicParams(C.Structure):
 NO_REF = 0xff
 COEF_DENSE, COEF_SPARSE, COEF_LEVELS = 1, 2, 3
 DEBLOCK_NONE, DEBLOCK_PLANES, DEBLOCK_DERIVED = 0, 1, 2
+TUF_INTRA, IU_CBF = 16, 32
 
 # every struct of include/ohcu.h by its C name: tests/test_abi.py compares sizeof / offsetof with a C program
 STRUCTS = {
     "ohcu_seq_params": SeqParams, "ohcu_slice_tab": SliceTab, "ohcu_pu": PU, "ohcu_tu": TU, "ohcu_dbparams": DBParams,
+    "ohcu_iu": IU, "ohcu_iu_index": IuIndex,
     "ohcu_sao": SAO, "ohcu_deblock_in": DeblockIn, "ohcu_deblock_derive_in": DeblockDeriveIn, "ohcu_sao_in": SaoIn,
     "ohcu_crop": Crop, "ohcu_coef": Coef, "ohcu_tu_quant": TuQuant, "ohcu_ctb_index": CtbIndex,
     "ohcu_frame_arenas": FrameArenas, "ohcu_frame_counts": FrameCounts, "ohcu_pic_params": PicParams,
@@ -177,6 +190,7 @@ SYMBOLS = {
     "ohcu_frame_begin": (C.c_int, [_P, C.c_int, C.c_int]),
     "ohcu_set_slice": (C.c_int, [_P, C.c_int, C.c_int, C.POINTER(SliceTab)]),
     "ohcu_append_pu": (C.c_int, [_P, C.c_int, _P, C.c_int]),
+    "ohcu_append_iu": (C.c_int, [_P, C.c_int, _P, C.c_int]),
     "ohcu_append_tu": (C.c_int, [_P, C.c_int, _P, C.c_int, _P, C.c_size_t]),
     "ohcu_reserve_coeffs": (C.c_int, [_P, C.c_int, C.c_size_t, C.POINTER(_P), C.POINTER(C.c_uint32)]),
     "ohcu_append_tu_inplace": (C.c_int, [_P, C.c_int, _P, C.c_int]),

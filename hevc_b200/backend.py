@@ -9,7 +9,7 @@ import numpy as np
 
 from . import abi
 from .abi import check
-from .sparse import ctb_index, to_levels, to_sparse
+from .sparse import ctb_index, iu_index, to_levels, to_sparse
 
 
 def _plane_args(planes):
@@ -129,6 +129,9 @@ class Context:
             tab = abi.SliceTab.from_buffer_copy(fj.slices[i].tobytes())
             check(lib.ohcu_set_slice(h, job_id, i, C.byref(tab)), "ohcu_set_slice")
         check(lib.ohcu_append_pu(h, job_id, fj.pus.ctypes.data, len(fj.pus)), "ohcu_append_pu")
+        ius = getattr(fj, "ius", None)
+        if ius is not None and len(ius):
+            check(lib.ohcu_append_iu(h, job_id, ius.ctypes.data, len(ius)), "ohcu_append_iu")
         if len(fj.tus) and levels is not None:
             quant, scaling = levels[:2]
             sp = self.sp
@@ -211,6 +214,11 @@ class Context:
             put(a.scaling_list, sl); put(a.scaling_list + sl.nbytes, sl_dc)
             n.scaling_list = 1
         n.n_pu, n.n_tu, n.n_coef, n.n_slices, n.coef_form = len(fj.pus), len(recs), len(pairs), len(fj.slices), form
+        ius = getattr(fj, "ius", None)
+        if ius is not None and len(ius):
+            assert a.ius and len(ius) <= a.max_ius, "the context was created without sp.intra"
+            put(a.ius, ius); put(a.iu_ctbs, iu_index(ius, sp.log2_ctb_size, hs, vs, ctb_w, nctb))
+            n.n_iu = len(ius)
         if use_deblock:
             put(a.qp_y_tab, fj.qp_y_tab); put(a.deblock, fj.deblock)
             if sp.pcm_or_bypass:

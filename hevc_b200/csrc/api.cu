@@ -124,6 +124,13 @@ struct Job {
     // PCM blocks (ohcu_append_pcm): allocated on first use
     PcmRec *pcm_h = nullptr, *pcm_d = nullptr; int n_pcm = 0, pcm_cap = 0;
     uint8_t *pcms_h = nullptr, *pcms_d = nullptr; size_t pcm_bytes = 0, pcms_cap = 0;
+    // intra blocks (ohcu_seq_params.intra): records, where each CTB's sit, the residual planes of their coded TBs,
+    // the wavefront's progress counters
+    Arena<ohcu_iu> ius;      int n_iu = 0;
+    Arena<ohcu_iu_index> iu_ctbs; int last_iu_ctb = -1;
+    uint8_t *resid_base = nullptr; PlaneSet resid{};
+    int *progress_d = nullptr;
+    bool inplace_iu = false;          // iu_ctbs was handed to the parser (zeroed again by the next ohcu_frame_begin)
 };
 
 struct ohcu_ctx {
@@ -282,6 +289,9 @@ extern "C" int ohcu_destroy(ohcu_ctx *c)
         if (j.pcm_d) cudaFree(j.pcm_d);
         if (j.pcms_h) cudaFreeHost(j.pcms_h);
         if (j.pcms_d) cudaFree(j.pcms_d);
+        free_arena(&j.ius); free_arena(&j.iu_ctbs);
+        if (j.resid_base) cudaFree(j.resid_base);
+        if (j.progress_d) cudaFree(j.progress_d);
         if (j.tab_h) cudaFreeHost(j.tab_h);
         if (j.tab_d) cudaFree(j.tab_d);
         if (j.done) cudaEventDestroy(j.done);
@@ -321,6 +331,9 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
                                  "(reference SAO reads chroma before its horizontal edges are filtered)");
     if ((sp->width & ((1 << sp->log2_min_cb_size) - 1)) || (sp->height & ((1 << sp->log2_min_cb_size) - 1)))
         return fail(OHCU_EINVAL, "picture size must be a multiple of the minimum CB size");
+    // ff_hevc_pred_init (hevcpred.c:62-76) has predictors for 8, 9, 10 and 12 bits only
+    if (sp->intra && sp->bit_depth > 12)
+        return fail(OHCU_EINVAL, "intra prediction at %d bits: the reference instantiates its predictors for 8, 9, 10 and 12 bits", sp->bit_depth);
     if (sp->dpb_slots < 1 || sp->dpb_slots > OHCU_MAX_DPB) return fail(OHCU_EINVAL, "dpb_slots out of range");
     if (sp->jobs < 1 || sp->jobs > 64) return fail(OHCU_EINVAL, "jobs out of range (1..64)");
 
@@ -357,6 +370,7 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
     if (c->sp.max_pus <= 0) c->sp.max_pus = (int)(((size_t)sp->width * sp->height) / 32);
     if (c->sp.max_tus <= 0) c->sp.max_tus = (int)(nsamp / 16);
     if (c->sp.max_coeffs <= 0) c->sp.max_coeffs = (int64_t)nsamp;
+    if (c->sp.max_ius <= 0) c->sp.max_ius = (int)(nsamp / 16);             // one predicted block per 4x4
 
     int rc = 0;
 #define TRY(x) do { rc = (x); if (rc) { ohcu_destroy(c); return rc; } } while (0)
@@ -388,6 +402,21 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
         TRYCU(cudaMalloc((void **)&j.err_d, sizeof(int)));
         TRYCU(cudaMemset(j.err_d, 0, sizeof(int)));
         *j.err_h = 0;
+        if (c->sp.intra) {
+            TRY(alloc_arena(&j.ius, c->sp.max_ius));
+            TRY(alloc_arena(&j.iu_ctbs, c->nctb));
+            memset(j.iu_ctbs.h, 0, sizeof(ohcu_iu_index) * c->nctb);
+            size_t off[3], total = 0;
+            for (int i = 0; i < c->nplanes; i++) {
+                j.resid.pitch[i] = (c->pw[i] * 2 + 255) & ~255;
+                off[i] = total;
+                total += (size_t)j.resid.pitch[i] * c->ph[i];
+            }
+            TRYCU(cudaMalloc((void **)&j.resid_base, total));
+            TRYCU(cudaMemset(j.resid_base, 0, total));
+            for (int i = 0; i < c->nplanes; i++) j.resid.p[i] = j.resid_base + off[i];
+            TRYCU(cudaMalloc((void **)&j.progress_d, sizeof(int) * c->ctb_h));
+        }
         // twice max_coeffs int16: the sparse form of a frame whose coefficients are all significant
         TRY(alloc_arena(&j.coeffs, 2 * (size_t)c->sp.max_coeffs));
         j.ctb_area.assign(c->nctb, 0);
@@ -691,6 +720,8 @@ extern "C" int ohcu_frame_begin(ohcu_ctx *c, int out_slot, int poc)
     j.pp.cr_qp_offset = c->sp.cr_qp_offset; j.pp.no_tile_filter = c->sp.no_tile_filter;
     j.inplace = false; j.all_inter = 0; j.n_coef_units = 0; j.n_pcm = 0; j.pcm_bytes = 0;
     memset(j.ctbs.h, 0, sizeof(ohcu_ctb_index) * c->nctb);
+    if (j.n_iu || j.inplace_iu) memset(j.iu_ctbs.h, 0, sizeof(ohcu_iu_index) * c->nctb);
+    j.n_iu = 0; j.last_iu_ctb = -1; j.inplace_iu = false;
     *j.err_h = 0;
     return id;
 }
@@ -764,6 +795,36 @@ extern "C" int ohcu_append_pu(ohcu_ctx *c, int job, const ohcu_pu *recs, int n)
     return 0;
 }
 
+extern "C" int ohcu_append_iu(ohcu_ctx *c, int job, const ohcu_iu *recs, int n)
+{
+    OPEN_JOB(c, job);
+    if (n < 0 || (n && !recs)) return fail(OHCU_EINVAL, "bad intra block list");
+    if (!c->sp.intra) return fail(OHCU_ESTATE, "the context was created without ohcu_seq_params.intra");
+    if ((size_t)j.n_iu + n > j.ius.cap) return fail(OHCU_EOVERFLOW, "intra block arena full (%zu)", j.ius.cap);
+    const int l2 = c->sp.log2_ctb_size, base = j.n_iu;
+    ohcu_iu_index *const idx = j.iu_ctbs.h;
+    int last = j.last_iu_ctb;
+    for (int i = 0; i < n; i++) {
+        const ohcu_iu u = recs[i];
+        if (!iu_ok(u, c->nplanes, c->pw, c->ph)) return fail(OHCU_EINVAL, "intra block record %d is malformed", base + i);
+        const int hs = u.c_idx ? c->hs : 0, vs = u.c_idx ? c->vs : 0, n1 = 1 << u.log2_size;
+        if (((u.x0 << hs) >> l2) != (((u.x0 + n1 - 1) << hs) >> l2) || ((u.y0 << vs) >> l2) != (((u.y0 + n1 - 1) << vs) >> l2))
+            return fail(OHCU_EINVAL, "intra block record %d crosses a CTB boundary", base + i);
+        const int ctb = ((u.x0 << hs) >> l2) + ((u.y0 << vs) >> l2) * c->ctb_w;
+        if (ctb != last) {
+            if (idx[ctb].n_iu) return fail(OHCU_EINVAL, "intra block record %d: the blocks of a CTB must be appended contiguously", base + i);
+            idx[ctb].first_iu = (uint32_t)(base + i);
+            last = ctb;
+        }
+        if (idx[ctb].n_iu >= 768u) return fail(OHCU_EINVAL, "intra block record %d: more than 768 blocks in CTB %d", base + i, ctb);
+        idx[ctb].n_iu++;
+        j.ius.h[base + i] = u;
+    }
+    j.last_iu_ctb = last;
+    j.n_iu += n;
+    return 0;
+}
+
 static int add_tus(ohcu_ctx *c, Job &j, const ohcu_tu *recs, int n, uint32_t rebase)
 {
     if ((size_t)j.n_tu + n > j.tus.cap) return fail(OHCU_EOVERFLOW, "TU arena full (%zu)", j.tus.cap);
@@ -775,12 +836,14 @@ static int add_tus(ohcu_ctx *c, Job &j, const ohcu_tu *recs, int n, uint32_t reb
     const int ths[3] = {0, c->hs, c->hs}, tvs[3] = {0, c->vs, c->vs};
     const int max_c = c->sp.chroma_format_idc ? 2 : 0;
     const size_t ncoeff = j.ncoeff;
+    const bool intra_ok = c->sp.intra != 0;          // OHCU_TUF_INTRA blocks need the job's residual planes
     int last = j.last_tu_ctb;
     bool sorted = j.tu_sorted, cross = j.has_cross;
     for (int i = 0; i < n; i++) {
         ohcu_tu tu = recs[i];
         const unsigned l = (unsigned)tu.log2_size - 2u;
-        if (l > 3u || tu.c_idx > max_c || tu.mode > OHCU_TU_BYPASS || (tu.mode == OHCU_TU_DST4 && l != 0))
+        if (l > 3u || tu.c_idx > max_c || tu.mode > OHCU_TU_BYPASS || (tu.mode == OHCU_TU_DST4 && l != 0) ||
+            ((tu.flags & OHCU_TUF_INTRA) && !intra_ok))
             return fail(OHCU_EINVAL, "TU record %d is malformed", base + i);
         const int n1 = 1 << tu.log2_size;
         if (tu.x0 + n1 > pw[tu.c_idx] || tu.y0 + n1 > ph[tu.c_idx] || ((tu.x0 | tu.y0) & 3) ||
@@ -876,6 +939,7 @@ static int append_pairs(ohcu_ctx *c, int job, const ohcu_tu *recs, const ohcu_tu
     const int max_c = c->sp.chroma_format_idc ? 2 : 0;
     const uint32_t area = (uint32_t)recon_sparse_ctb_coefs(c->sp.log2_ctb_size, c->nplanes, c->hs, c->vs);
     const size_t first_pair = j.ncoeff / 2;
+    const bool intra_ok = c->sp.intra != 0;
     size_t cursor = 0;
     int last = j.last_tu_ctb;
     bool cross = j.has_cross;
@@ -885,7 +949,8 @@ static int append_pairs(ohcu_ctx *c, int job, const ohcu_tu *recs, const ohcu_tu
     for (int i = 0; i < n; i++) {
         const ohcu_tu &tu = recs[i];
         const unsigned l = (unsigned)tu.log2_size - 2u;
-        if (l > 3u || tu.c_idx > max_c || tu.mode > OHCU_TU_BYPASS || (tu.mode == OHCU_TU_DST4 && l != 0))
+        if (l > 3u || tu.c_idx > max_c || tu.mode > OHCU_TU_BYPASS || (tu.mode == OHCU_TU_DST4 && l != 0) ||
+            ((tu.flags & OHCU_TUF_INTRA) && !intra_ok))
             return fail(OHCU_EINVAL, "TU record %d is malformed", base + i);
         const int n1 = 1 << tu.log2_size;
         if (tu.x0 + n1 > pw[tu.c_idx] || tu.y0 + n1 > ph[tu.c_idx] || ((tu.x0 | tu.y0) & 3) ||
@@ -1043,6 +1108,10 @@ extern "C" int ohcu_frame_arenas_get(ohcu_ctx *c, int job, ohcu_frame_arenas *ou
     out->is_pcm = j.is_pcm.h; out->sao = j.sao.h; out->filter_slice_edges = j.fse.h;
     out->tab_slice_address = j.tsa.h; out->tile_id = j.tile.h; out->deblock_disabled = j.dbk_disabled.h;
     out->scaling_list = j.sl_h;
+    if (c->sp.intra) {
+        out->ius = j.ius.h; out->iu_ctbs = j.iu_ctbs.h; out->max_ius = (uint32_t)j.ius.cap;
+        j.inplace_iu = true;
+    }
     return 0;
 }
 
@@ -1050,14 +1119,17 @@ extern "C" int ohcu_frame_commit_lists(ohcu_ctx *c, int job, const ohcu_frame_co
 {
     OPEN_JOB(c, job);
     if (!n) return fail(OHCU_EINVAL, "null argument");
-    if (j.n_pu || j.n_tu) return fail(OHCU_ESTATE, "job %d already holds appended lists", job);
+    if (j.n_pu || j.n_tu || j.n_iu) return fail(OHCU_ESTATE, "job %d already holds appended lists", job);
+    if (n->n_iu && !c->sp.intra) return fail(OHCU_ESTATE, "the context was created without ohcu_seq_params.intra");
+    if (n->n_iu > j.ius.cap) return fail(OHCU_EOVERFLOW, "intra block list larger than the job's arena");
+    if (n->n_iu && n->all_inter) return fail(OHCU_EINVAL, "all_inter promised for a picture with intra blocks");
     if (n->n_pu > j.pus.cap || n->n_tu > j.tus.cap) return fail(OHCU_EOVERFLOW, "lists larger than the job's arenas");
     if (n->coef_form < 0 || n->coef_form > 3 || (n->n_tu && !n->coef_form)) return fail(OHCU_EINVAL, "bad coef_form %d", n->coef_form);
     const uint64_t n16 = n->coef_form >= 2 ? 2 * n->n_coef : n->n_coef;
     if (n16 > j.coeffs.cap || n16 > 0xffffffffull) return fail(OHCU_EOVERFLOW, "coefficient arena full (%zu int16)", j.coeffs.cap);
     if (n->n_slices < 0 || n->n_slices > OHCU_MAX_SLICES || (n->n_pu && !n->n_slices)) return fail(OHCU_EINVAL, "bad n_slices %d", n->n_slices);
     if (n->deblock < 0 || n->deblock > 2) return fail(OHCU_EINVAL, "bad deblock mode %d", n->deblock);
-    j.n_pu = (int)n->n_pu; j.n_tu = (int)n->n_tu; j.n_slices = n->n_slices;
+    j.n_pu = (int)n->n_pu; j.n_tu = (int)n->n_tu; j.n_slices = n->n_slices; j.n_iu = (int)n->n_iu;
     j.ncoeff = (size_t)n16; j.n_coef_units = n->n_coef; j.coef_form = n->n_tu ? n->coef_form : 0;
     j.has_sl = n->scaling_list != 0;
     j.has_deblock = n->deblock != 0; j.bs_derived = n->deblock == OHCU_DEBLOCK_DERIVED;
@@ -1200,6 +1272,10 @@ static int stage_impl(ohcu_ctx *c, int job, bool close)
         CU(cudaMemcpyAsync(j.pcm_d, j.pcm_h, sizeof(PcmRec) * j.n_pcm, cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(j.pcms_d, j.pcms_h, j.pcm_bytes, cudaMemcpyHostToDevice, st));
     }
+    if (j.n_iu) {
+        CU(push_arena(j.ius, j.n_iu, st));
+        CU(push_arena(j.iu_ctbs, c->nctb, st));
+    }
     CU(cudaMemsetAsync(j.err_d, 0, sizeof(int), st));
     if (j.inplace) {
         // validation, per-CTB ranges and flags on the device (prepare.cu)
@@ -1243,6 +1319,10 @@ static void fill_frame_dev(const ohcu_ctx *c, const Job &j, FrameDev *f)
     f->bs_ctb_flags = j.has_deblock && j.bs_derived ? j.bs_flags.d : nullptr;
     f->sao = j.has_sao ? j.sao.d : nullptr; f->sao_ctb_flags = j.sao_flags.d;
     f->pcm_or_bypass = j.pp.pcm_or_bypass; f->cb_qp_offset = j.pp.cb_qp_offset; f->cr_qp_offset = j.pp.cr_qp_offset;
+    f->ius = j.ius.d; f->iu_index = j.iu_ctbs.d; f->n_iu = j.n_iu;
+    for (int i = 0; i < 3; i++) { f->resid[i] = (int16_t *)j.resid.p[i]; f->resid_pitch[i] = j.resid.pitch[i]; }
+    f->intra_progress = j.progress_d;
+    f->intra_smoothing_disabled = c->sp.intra_smoothing_disabled; f->strong_intra_smoothing = c->sp.strong_intra_smoothing;
     f->err = j.err_d;
 }
 
@@ -1315,6 +1395,11 @@ extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int 
     LAUNCHED(launch_recon(f, stages & 2, st));
     // PCM blocks replace prediction + residual of their samples (put_pcm), ahead of the loop filters
     if ((stages & 2) && j.n_pcm) LAUNCHED(launch_pcm(f, j.pcm_d, j.n_pcm, j.pcms_d, st));
+    // the intra blocks, predicted from what has been reconstructed around them, with their residual (intra.cu)
+    if ((stages & 2) && j.n_iu) {
+        CU(cudaMemsetAsync(j.progress_d, 0, sizeof(int) * c->ctb_h, st));
+        LAUNCHED(launch_intra(f, st));
+    }
     STAGE_EVENT(2);
     // deblocking and SAO run fused (loopfilter.cu); stage 3 carries their time
     if (derive) CU(cudaStreamWaitEvent(st, j.join, 0));

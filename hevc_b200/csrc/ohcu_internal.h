@@ -61,6 +61,15 @@ struct FrameDev {
     // SAO
     const ohcu_sao *sao;
     const uint16_t *sao_ctb_flags;   // per CTB, see SAOF_* below
+    // intra blocks (intra.cu): records in decoding order, where each CTB's sit, the residual planes residual_kernel
+    // leaves the OHCU_TUF_INTRA blocks in (int16, pitch in bytes), one progress counter per CTB row
+    const ohcu_iu *ius;
+    const ohcu_iu_index *iu_index;
+    int n_iu;
+    int16_t *resid[3];
+    int resid_pitch[3];
+    int *intra_progress;
+    int intra_smoothing_disabled, strong_intra_smoothing;
     // the job's error word (prepare.cu): non-zero = the lists are malformed, every kernel of the frame returns at once
     const int *err;
 };
@@ -79,7 +88,7 @@ struct PrepDev {
     uint64_t n_coef;
     int n_slices, coef_form, dpb_slots, out_slot, all_inter, no_tile_filter, has_sao, derive, area, has_sl;
 };
-enum { PE_INDEX = 1, PE_PU, PE_TU, PE_OVERLAP, PE_NOT_COVERED, PE_PAIRS };
+enum { PE_INDEX = 1, PE_PU, PE_TU, PE_OVERLAP, PE_NOT_COVERED, PE_PAIRS, PE_IU };
 int launch_prepare(const FrameDev &f, const PrepDev &p, cudaStream_t st);
 const char *prepare_error_text(int code);
 
@@ -112,6 +121,20 @@ int upload_dct_table();
 struct LfMaps { CUtensorMap m[3]; };        // the job's reconstructed picture, one box per plane
 int launch_loopfilter(const FrameDev &f, const LfMaps &maps, int flags, cudaStream_t st);   // flags: 1 deblock, 2 SAO
 int launch_bs_derive(const FrameDev &f, cudaStream_t st);      // vbs / hbs from the PU and TU lists (bs.cu)
+int launch_intra(const FrameDev &f, cudaStream_t st);          // the intra blocks, CTB wavefront (intra.cu)
+// an intra block record is well formed for this sequence (shared by ohcu_append_iu and prepare_kernel)
+__host__ __device__ inline bool iu_ok(const ohcu_iu &u, int nplanes, const int *pw, const int *ph)
+{
+    if (u.c_idx >= nplanes || u.log2_size < 2 || u.log2_size > 5 || u.mode > 34 || (u.cand & 0xc0)) return false;
+    const int n = 1 << u.log2_size;
+    if (((u.x0 | u.y0) & 3) || u.x0 + n > pw[u.c_idx] || u.y0 + n > ph[u.c_idx]) return false;
+    // neighbours named available must lie inside the plane
+    if ((u.cand & (OHCU_CAND_LEFT | OHCU_CAND_BOTTOM_LEFT | OHCU_CAND_UP_LEFT)) && u.x0 == 0) return false;
+    if ((u.cand & (OHCU_CAND_UP | OHCU_CAND_UP_RIGHT | OHCU_CAND_UP_LEFT)) && u.y0 == 0) return false;
+    if ((u.cand & OHCU_CAND_BOTTOM_LEFT) && u.y0 + n >= ph[u.c_idx]) return false;
+    if ((u.cand & OHCU_CAND_UP_RIGHT) && u.x0 + n >= pw[u.c_idx]) return false;
+    return true;
+}
 // per-entry test shims (recon.cu, loopfilter.cu)
 int dsp_mc(int bd, int luma, int family, uint8_t *dst, ptrdiff_t dststride, const uint8_t *src, ptrdiff_t srcstride,
            const int16_t *src2, int16_t *out16, int h, int denom, int wx0, int wx1, int ox0, int ox1, int mx, int my, int w);

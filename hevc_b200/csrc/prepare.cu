@@ -6,7 +6,8 @@
 // ahead of the frame's kernels, what ohcu_append_pu / ohcu_append_tu_* / ohcu_set_sao /
 // ohcu_set_deblock_derived / ohcu_frame_stage do on the submitting thread in the copying path:
 //   * every record of every CTB checked (bounds, 4-sample alignment, CTB membership, block sizes, modes,
-//     reference slots, coefficient areas, quantisers, cross-component references),
+//     reference slots, coefficient areas, quantisers, cross-component references; intra blocks: size, mode,
+//     CTB membership, available neighbours inside the plane),
 //   * per-CTB ranges for mc_kernel / residual_kernel / bs_kernel, with the "PUs cover the CTB" flag,
 //   * the SAO restore flags of sao_filter_CTB (hevc_filter.c:277-325) and the CTB-edge flags of
 //     lc->boundary_flags (hevcdec.c:2822-2837) for the bs derivation.
@@ -112,7 +113,8 @@ __global__ void __launch_bounds__(PREP_THREADS) prepare_kernel(const __grid_cons
         const uint32_t r = ix.first_tu + i;
         const ohcu_tu tu = f.tus[r];
         const unsigned l = (unsigned)tu.log2_size - 2u;
-        bool ok = l <= 3u && tu.c_idx <= max_c && tu.mode <= OHCU_TU_BYPASS && !(tu.mode == OHCU_TU_DST4 && l != 0);
+        bool ok = l <= 3u && tu.c_idx <= max_c && tu.mode <= OHCU_TU_BYPASS && !(tu.mode == OHCU_TU_DST4 && l != 0) &&
+                  (!(tu.flags & OHCU_TUF_INTRA) || f.resid[0]);
         if (ok) {
             const int n = 1 << tu.log2_size, c = tu.c_idx;
             const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
@@ -135,6 +137,25 @@ __global__ void __launch_bounds__(PREP_THREADS) prepare_kernel(const __grid_cons
         pairs += tu.pad;
     }
     if (pairs) atomicAdd(&s_pairs, pairs);
+    // ---- intra blocks: what ohcu_append_iu checks
+    if (f.n_iu) {
+        const ohcu_iu_index ii = f.iu_index[ctb];
+        if (ii.n_iu > 768u || (uint64_t)ii.first_iu + ii.n_iu > (uint64_t)f.n_iu) {
+            if (tid == 0) prep_fail(p.err, PE_IU, 0xffffffu);
+        } else {
+            for (uint32_t i = tid; i < ii.n_iu; i += PREP_THREADS) {
+                const uint32_t r = ii.first_iu + i;
+                const ohcu_iu u = f.ius[r];
+                bool ok = iu_ok(u, f.nplanes, f.pw, f.ph);
+                if (ok) {
+                    const int hs = u.c_idx ? f.hs : 0, vs = u.c_idx ? f.vs : 0, n = 1 << u.log2_size;
+                    ok = ((u.x0 << hs) >> l2) == ctbx && (((u.x0 + n - 1) << hs) >> l2) == ctbx &&
+                         ((u.y0 << vs) >> l2) == ctby && (((u.y0 + n - 1) << vs) >> l2) == ctby;
+                }
+                if (!ok) prep_fail(p.err, PE_IU, r);
+            }
+        }
+    }
     __syncthreads();
     if (tid != 0) return;
     const int valid = min(cs, f.width - (ctbx << l2)) * min(cs, f.height - (ctby << l2));
@@ -163,6 +184,7 @@ const char *prepare_error_text(int code)
     case PE_OVERLAP: return "PUs overlap or exceed the CTB (CTB";
     case PE_NOT_COVERED: return "all_inter was promised but the PUs do not cover the CTB (CTB";
     case PE_PAIRS: return "the TU records' pair counts do not add up to the CTB's n_coef (CTB";
+    case PE_IU: return "malformed intra block record (size, mode, outside its CTB or plane, a neighbour named available outside the plane; record";
     default: return "unknown error (";
     }
 }

@@ -539,10 +539,15 @@ __device__ __noinline__ void idct_mma(const int16_t *src, int16_t *t1, uint32_t 
 }
 
 // IDCT_DC (template :273-286) of one N x N block by the whole warp
-__device__ __forceinline__ void dc_block(int log2, int c0, uint32_t *tw, int tpitch, int bd, int lane)
+__device__ __forceinline__ void dc_block(int log2, int c0, uint32_t *tw, int tpitch, int bd, int lane, bool raw = false)
 {
     const int v = (((c0 + 1) >> 1) + (1 << (13 - bd))) >> (14 - bd), maxv = (1 << bd) - 1;
     const int n = 1 << log2, wl = log2 - 1;                // words per row = n / 2
+    if (raw) {
+        const uint32_t vv = (uint32_t)(v & 0xffff) * 0x10001u;
+        for (int i = lane; i < (n << wl); i += 32) tw[(i >> wl) * tpitch + (i & ((1 << wl) - 1))] = vv;
+        return;
+    }
     for (int i = lane; i < (n << wl); i += 32) tile_add_pair(tw + (i >> wl) * tpitch + (i & ((1 << wl) - 1)), v, v, maxv);
 }
 
@@ -605,11 +610,19 @@ __device__ void tu_batch(const FrameDev &f, const CtbTile &tile, int tu0, const 
         const int c = tu.c_idx;
         const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
         const int maxv = (1 << f.bd) - 1;
-        uint16_t *t = (uint16_t *)tile.p(c) + (tu.y0 - (cy0 >> vs)) * (2 * tile.pitch(c)) + (tu.x0 - (cx0 >> hs)) + g;
+        if (tu.flags & OHCU_TUF_INTRA) {
+            // the block's prediction does not exist yet: the residual waits in the job's residual plane (intra.cu adds it)
+            int16_t *d = (int16_t *)((uint8_t *)f.resid[c] + (size_t)tu.y0 * f.resid_pitch[c]) + tu.x0 + g;
+            const int rp = f.resid_pitch[c] >> 1;
 #pragma unroll 4
-        for (int r = 0; r < N; r++) {
-            uint16_t *d = t + r * 2 * tile.pitch(c);
-            *d = (uint16_t)min(max((int)*d + blk[r * S + g], 0), maxv);
+            for (int r = 0; r < N; r++) d[r * rp] = blk[r * S + g];
+        } else {
+            uint16_t *t = (uint16_t *)tile.p(c) + (tu.y0 - (cy0 >> vs)) * (2 * tile.pitch(c)) + (tu.x0 - (cx0 >> hs)) + g;
+#pragma unroll 4
+            for (int r = 0; r < N; r++) {
+                uint16_t *d = t + r * 2 * tile.pitch(c);
+                *d = (uint16_t)min(max((int)*d + blk[r * S + g], 0), maxv);
+            }
         }
     }
     if constexpr (MMA) {
@@ -624,9 +637,15 @@ __device__ void tu_batch(const FrameDev &f, const CtbTile &tile, int tu0, const 
             const int col_limit = __shfl_sync(0xffffffffu, (int)tu.col_limit, sl);
             const uint32_t off = __shfl_sync(0xffffffffu, tu.coeff_off, sl);
             const int hs = c ? f.hs : 0, vs = c ? f.vs : 0;
+            const bool intra = __shfl_sync(0xffffffffu, (int)tu.flags, sl) & OHCU_TUF_INTRA;
             uint32_t *tw = tile.p(c) + (y0 - (cy0 >> vs)) * tile.pitch(c) + ((x0 - (cx0 >> hs)) >> 1);
-            if (mode == OHCU_TU_DC) dc_block(LOG2, cs.at(off, 1)[0], tw, tile.pitch(c), f.bd, lane);
-            else idct_mma<LOG2>(cs.csm + (off - cs.clo), (int16_t *)&ws, tw, tile.pitch(c), col_limit, f.bd, lane);
+            int tp = tile.pitch(c);
+            if (intra) {                                               // residual plane instead of the tile, stored raw
+                tw = (uint32_t *)((uint8_t *)f.resid[c] + (size_t)y0 * f.resid_pitch[c]) + (x0 >> 1);
+                tp = f.resid_pitch[c] >> 2;
+            }
+            if (mode == OHCU_TU_DC) dc_block(LOG2, cs.at(off, 1)[0], tw, tp, f.bd, lane, intra);
+            else idct_mma<LOG2>(cs.csm + (off - cs.clo), (int16_t *)&ws, tw, tp, col_limit, f.bd, lane, intra);
             __syncwarp();
         }
     }

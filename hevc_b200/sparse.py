@@ -106,3 +106,14 @@ def ctb_index(pus, recs, log2_ctb, hs, vs, ctb_w, nctb, pairs_per_tu=None):
             has = idx["n_tu"] > 0
             idx["first_coef"][has] = before[idx["first_tu"][has]]
     return idx
+
+
+IU_INDEX_DTYPE = np.dtype([("first_iu", "<u4"), ("n_iu", "<u4")])
+
+
+def iu_index(ius, log2_ctb, hs, vs, ctb_w, nctb):
+    """The ohcu_iu_index array: where each CTB's intra blocks sit in a list in decoding order."""
+    idx = np.zeros(nctb, IU_INDEX_DTYPE)
+    if len(ius):
+        idx["first_iu"], idx["n_iu"] = _runs(ctb_of_tus(ius, log2_ctb, hs, vs, ctb_w), nctb, "intra block")
+    return idx

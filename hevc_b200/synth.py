@@ -27,6 +27,7 @@ SLICE_DTYPE = np.dtype([("ref_slot", "u1", (2, 16)), ("weight_flag", "u1"), ("lu
                         ("chroma_log2_weight_denom", "u1"), ("pad", "u1"),
                         ("luma_weight", "<i2", (2, 16)), ("luma_offset", "<i2", (2, 16)),
                         ("chroma_weight", "<i2", (2, 16, 2)), ("chroma_offset", "<i2", (2, 16, 2))])
+IU_DTYPE = np.dtype([("x0", "<u2"), ("y0", "<u2"), ("c_idx", "u1"), ("log2_size", "u1"), ("mode", "u1"), ("cand", "u1")])
 LEAF_DTYPE = np.dtype([("x0", "<u2"), ("y0", "<u2"), ("log2_size", "u1"), ("cbf_luma", "u1"), ("pad", "u1", (2,))])
 assert PU_DTYPE.itemsize == 20 and TU_DTYPE.itemsize == 20 and SAO_DTYPE.itemsize == 40
 assert SLICE_DTYPE.itemsize == C.sizeof(abi.SliceTab)
@@ -40,6 +41,7 @@ class SynthParams(C.Structure):
         ("cbf_pct", C.c_int32), ("dc_pct", C.c_int32), ("dst_pct", C.c_int32),
         ("dense_coeffs", C.c_int32), ("bi_pct", C.c_int32), ("split_pct", C.c_int32 * 3),
         ("bs_pct", C.c_int32 * 2), ("sao_pct", C.c_int32 * 2), ("n_refs", C.c_int32),
+        ("intra_pct", C.c_int32), ("intra_drop_pct", C.c_int32),
     ]
 
 
@@ -56,6 +58,7 @@ class _SynthFrame(C.Structure):
         ("sao", C.c_void_p), ("filter_slice_edges", C.c_void_p),
         ("tab_slice_address", C.c_void_p), ("tile_id", C.c_void_p),
         ("n_leaf", C.c_int32), ("leaves", C.c_void_p),
+        ("n_iu", C.c_int32), ("ius", C.c_void_p),
     ]
 
 
@@ -100,6 +103,8 @@ def default_params(width, height, bit_depth=8, chroma_format_idc=1, **overrides)
             if not hasattr(p, k):
                 raise AttributeError(k)
             setattr(p, k, v)
+    if p.intra_pct:
+        p.sp.intra = 1                    # the library sets aside residual planes and an arena for the intra blocks
     return p
 
 
@@ -169,6 +174,7 @@ class FrameJob:
             self.tab_slice_address = _copy(f.tab_slice_address, np.int32, nctb)
             self.tile_id = _copy(f.tile_id, np.int32, nctb)
             self.leaves = _copy(f.leaves, LEAF_DTYPE, f.n_leaf)     # transform-tree leaves, coded or not
+            self.ius = _copy(f.ius, IU_DTYPE, f.n_iu)               # intra blocks, decoding order
             self.ctb_width, self.ctb_height = f.ctb_width, f.ctb_height
         finally:
             lib.ohsynth_free(fp)

@@ -16,6 +16,9 @@
  *     (unless dense_coeffs, the hazard-1 test: dense blocks with arbitrary col_limit)
  *   - chroma TB geometry per chroma_format_idc (4:2:0 4x4-luma groups share one 4x4
  *     chroma TB; 4:2:2 has two stacked square chroma TBs)
+ *   - intra CUs (intra_pct): one ohcu_iu per predicted TB in hls_transform_unit order (luma, then the
+ *     chroma blocks; the four 4x4 luma blocks of an 8x8 share the chroma of the parent), availability flags
+ *     from what was reconstructed earlier in the same slice and tile; their coded TBs carry OHCU_TUF_INTRA
  *   - bs only on the 8x8 grid at CU/PU/TU boundaries; Cr SAO type/class copy Cb's
  *     (hevcdec.c:1261-1264); offset_val built as hevcdec.c:1289-1299
  */
@@ -47,6 +50,8 @@ typedef struct ohsynth_params {
     int32_t bs_pct[2];       /* P(bs=1), P(bs=2) in % on block boundaries            */
     int32_t sao_pct[2];      /* P(band), P(edge) in % per CTB and component type     */
     int32_t n_refs;          /* reference pictures used (DPB slots 0..n_refs-1), <= 4 */
+    int32_t intra_pct;       /* % of CUs intra-predicted (2Nx2N, NxN at 8x8): ohcu_iu records */
+    int32_t intra_drop_pct;  /* % of intra blocks with random availability flags cleared      */
 } ohsynth_params;
 
 /* one leaf of a transform tree (hls_transform_tree, hevcdec.c:1549): what
@@ -72,6 +77,7 @@ typedef struct ohsynth_frame {
     int32_t *tab_slice_address;
     int32_t *tile_id;
     int32_t n_leaf;    ohsynth_leaf *leaves;    /* transform-tree leaves in decoding order */
+    int32_t n_iu;      ohcu_iu *ius;            /* intra blocks in decoding order          */
 } ohsynth_frame;
 
 void ohsynth_default_params(ohsynth_params *p, int width, int height, int bit_depth,

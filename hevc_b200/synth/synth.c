@@ -46,8 +46,11 @@ typedef struct gen {
     rng r;
     int hs, vs, cfi;
     int W, H, bd;
-    int cap_pu, cap_tu;
+    int cap_pu, cap_tu, cap_iu;
     int64_t cap_coef;
+    uint8_t *done;          /* per 4x4 luma cell: reconstructed already (intra availability) */
+    int cell_w, cell_h;
+    int intra;              /* the CU being generated is intra */
     int slice;              /* current slice index */
     int qp;
     uint16_t scan_rank[4][32 * 32]; /* [log2-2][y*n+x] = position in coding order */
@@ -161,6 +164,7 @@ static int emit_tb(gen *g, int c_idx, int x, int y, int log2, int bypass, int cr
     int16_t *c;
     memset(&tu, 0, sizeof(tu));
     tu.x0 = (uint16_t)x; tu.y0 = (uint16_t)y; tu.c_idx = (uint8_t)c_idx; tu.log2_size = (uint8_t)log2;
+    if (g->intra) tu.flags |= OHCU_TUF_INTRA;
     if (cross_from >= 0) {
         static const int8_t scale[8] = { 1, 2, 4, 8, -1, -2, -4, -8 };
         tu.flags |= OHCU_TUF_CROSS;
@@ -221,6 +225,76 @@ static int emit_tb(gen *g, int c_idx, int x, int y, int log2, int bypass, int cr
     return g->f->n_tu - 1;
 }
 
+
+/* ------------------------------------------------------------------ intra blocks */
+static void mark_done(gen *g, int x, int y, int w, int h)
+{
+    for (int yy = y >> 2; yy < (y + h) >> 2 && yy < g->cell_h; yy++)
+        for (int xx = x >> 2; xx < (x + w) >> 2 && xx < g->cell_w; xx++)
+            g->done[yy * g->cell_w + xx] = 1;
+}
+/* the 4x4 luma cell at (xn, yn) was reconstructed before the block at (x, y) and may be read by it: inside the
+ * picture, earlier in decoding order, same slice and same tile (what lc->na.cand_* and the z-scan test of
+ * hevcpred_template.c:103-107 amount to) */
+static int avail(const gen *g, int x, int y, int xn, int yn)
+{
+    const ohsynth_frame *f = g->f;
+    int l2 = g->p->sp.log2_ctb_size, a, b;
+    if (xn < 0 || yn < 0 || xn >= g->W || yn >= g->H) return 0;
+    if (!g->done[(yn >> 2) * g->cell_w + (xn >> 2)]) return 0;
+    a = (y >> l2) * f->ctb_width + (x >> l2); b = (yn >> l2) * f->ctb_width + (xn >> l2);
+    return f->tab_slice_address[a] == f->tab_slice_address[b] && f->tile_id[a] == f->tile_id[b];
+}
+/* one predicted block of plane c_idx at plane position (x, y); has_res: a coded TB follows */
+static void emit_iu(gen *g, int c_idx, int x, int y, int log2, int mode, int has_res)
+{
+    ohsynth_frame *f = g->f;
+    ohcu_iu iu;
+    int hs = c_idx ? g->hs : 0, vs = c_idx ? g->vs : 0;
+    int xl = x << hs, yl = y << vs, wl = (1 << log2) << hs, hl = (1 << log2) << vs, cand = 0;
+    if (avail(g, xl, yl, xl - 1, yl + hl)) cand |= OHCU_CAND_BOTTOM_LEFT;
+    if (avail(g, xl, yl, xl - 1, yl))      cand |= OHCU_CAND_LEFT;
+    if (avail(g, xl, yl, xl - 1, yl - 1))  cand |= OHCU_CAND_UP_LEFT;
+    if (avail(g, xl, yl, xl, yl - 1))      cand |= OHCU_CAND_UP;
+    if (avail(g, xl, yl, xl + wl, yl - 1)) cand |= OHCU_CAND_UP_RIGHT;
+    if (g->p->intra_drop_pct && rnd_pct(&g->r, g->p->intra_drop_pct)) cand &= rnd_range(&g->r, 0, 31);
+    memset(&iu, 0, sizeof(iu));
+    iu.x0 = (uint16_t)x; iu.y0 = (uint16_t)y; iu.c_idx = (uint8_t)c_idx; iu.log2_size = (uint8_t)log2;
+    iu.mode = (uint8_t)mode; iu.cand = (uint8_t)(cand | (has_res ? OHCU_IU_CBF : 0));
+    if (f->n_iu == g->cap_iu) {
+        g->cap_iu = g->cap_iu ? g->cap_iu * 2 : 4096;
+        f->ius = realloc(f->ius, sizeof(ohcu_iu) * g->cap_iu);
+    }
+    f->ius[f->n_iu++] = iu;
+}
+static int draw_mode(gen *g)
+{
+    int k = rnd_range(&g->r, 0, 9);        /* planar, DC and the two pure directions more often */
+    return k == 0 ? 0 : k == 1 ? 1 : k == 2 ? 10 : k == 3 ? 26 : rnd_range(&g->r, 0, 34);
+}
+static void emit_tb_or_cross(gen *g, int c, int x, int y, int log2, int bypass, int cross, int coded);
+/* chroma blocks of an intra TU, luma position (x, y), luma size 1 << log2 (hls_transform_unit, hevcdec.c:1380-1526) */
+static void emit_chroma_intra(gen *g, int x, int y, int log2, int bypass, int luma_idx, int mode_c)
+{
+    int cfi = g->cfi;
+    if (!cfi) return;
+    for (int c = 1; c <= 2; c++) {
+        if (cfi == 3) {
+            int cross = (g->p->rext && luma_idx >= 0 && rnd_pct(&g->r, 25)) ? luma_idx : -1;
+            int coded = rnd_pct(&g->r, g->p->cbf_pct);
+            emit_iu(g, c, x, y, log2, mode_c, coded || cross >= 0);
+            emit_tb_or_cross(g, c, x, y, log2, bypass, cross, coded);
+        } else {
+            int l2c = log2 - 1, parts = cfi == 2 ? 2 : 1;
+            for (int i = 0; i < parts; i++) {
+                int coded = rnd_pct(&g->r, g->p->cbf_pct);
+                emit_iu(g, c, x >> 1, (y >> g->vs) + (i << l2c), l2c, mode_c, coded);
+                if (coded) emit_tb(g, c, x >> 1, (y >> g->vs) + (i << l2c), l2c, bypass, -1);
+            }
+        }
+    }
+}
+
 /* chroma TBs belonging to a luma block at (x,y) of size 1<<log2 (luma units) */
 static void emit_chroma(gen *g, int x, int y, int log2, int bypass, int luma_idx)
 {
@@ -229,22 +303,54 @@ static void emit_chroma(gen *g, int x, int y, int log2, int bypass, int luma_idx
     for (int c = 1; c <= 2; c++) {
         if (cfi == 3) {
             int cross = (g->p->rext && luma_idx >= 0 && rnd_pct(&g->r, 25)) ? luma_idx : -1;
-            if (rnd_pct(&g->r, g->p->cbf_pct))
-                emit_tb(g, c, x, y, log2, bypass, cross);
-            else if (cross >= 0) {
-                /* uncoded chroma with cross-component prediction (hevcdec.c:1430-1445):
-                 * residual = (res_scale_val * coeffs_y) >> 3 on top of zero coefficients */
-                int idx = emit_tb(g, c, x, y, log2, 1, cross);
-                ohcu_tu *tu = &g->f->tus[idx];
-                tu->flags &= ~(OHCU_TUF_RDPCM | OHCU_TUF_RDPCM_VERT);
-                memset(g->f->coeffs + tu->coeff_off, 0, sizeof(int16_t) << (2 * log2));
-            }
+            emit_tb_or_cross(g, c, x, y, log2, bypass, cross, rnd_pct(&g->r, g->p->cbf_pct));
         } else {
             int l2c = log2 - 1, parts = cfi == 2 ? 2 : 1;
             for (int i = 0; i < parts; i++)
                 if (rnd_pct(&g->r, g->p->cbf_pct))
                     emit_tb(g, c, x >> 1, (y >> g->vs) + (i << l2c), l2c, bypass, -1);
         }
+    }
+}
+
+static void emit_tb_or_cross(gen *g, int c, int x, int y, int log2, int bypass, int cross, int coded)
+{
+    if (coded)
+        emit_tb(g, c, x, y, log2, bypass, cross);
+    else if (cross >= 0) {
+        /* uncoded chroma with cross-component prediction (hevcdec.c:1430-1445):
+         * residual = (res_scale_val * coeffs_y) >> 3 on top of zero coefficients */
+        int idx = emit_tb(g, c, x, y, log2, 1, cross);
+        ohcu_tu *tu = &g->f->tus[idx];
+        tu->flags &= ~(OHCU_TUF_RDPCM | OHCU_TUF_RDPCM_VERT);
+        memset(g->f->coeffs + tu->coeff_off, 0, sizeof(int16_t) << (2 * log2));
+    }
+}
+
+/* transform tree of an intra CU: every leaf is predicted (luma, then chroma), coded or not.
+ * modes[4]: luma mode per quadrant of the CU (NxN) or four times the same; force: NxN splits at depth 0 */
+static void gen_tt_intra(gen *g, int x, int y, int log2, int bypass, const int *modes, int mode_c, int force, int quad)
+{
+    int split = log2 > 5 || force || (log2 > 2 && rnd_pct(&g->r, 35));
+    if (split) {
+        int h = 1 << (log2 - 1);
+        for (int i = 0; i < 4; i++)
+            gen_tt_intra(g, x + (i & 1) * h, y + (i >> 1) * h, log2 - 1, bypass, modes, mode_c, 0, force ? i : quad);
+        if (log2 == 3 && g->cfi && g->cfi != 3)
+            emit_chroma_intra(g, x, y, 3, bypass, -1, mode_c);
+        return;
+    }
+    paint_bs(g, x, y, 1 << log2, 1 << log2);
+    {
+        int luma_idx = -1, coded = rnd_pct(&g->r, g->p->cbf_pct);
+        ohsynth_leaf *lf = &g->f->leaves[g->f->n_leaf++];
+        emit_iu(g, 0, x, y, log2, modes[quad], coded);
+        if (coded)
+            luma_idx = emit_tb(g, 0, x, y, log2, bypass, -1);
+        mark_done(g, x, y, 1 << log2, 1 << log2);
+        lf->x0 = (uint16_t)x; lf->y0 = (uint16_t)y; lf->log2_size = (uint8_t)log2; lf->cbf_luma = luma_idx >= 0;
+        if (log2 > 2 || g->cfi == 3)
+            emit_chroma_intra(g, x, y, log2, bypass, luma_idx, mode_c);
     }
 }
 
@@ -292,6 +398,16 @@ static void gen_cu(gen *g, int x, int y, int log2)
             for (int xx = x >> p->sp.log2_min_pu_size; xx < (x + s) >> p->sp.log2_min_pu_size; xx++)
                 f->is_pcm[yy * f->min_pu_width + xx] = 1;
 
+    if (p->intra_pct && rnd_pct(&g->r, p->intra_pct)) {                  /* MODE_INTRA, hevcdec.c:2596-2640 */
+        int nxn = log2 == 3 && rnd_pct(&g->r, 40), modes[4], mode_c = draw_mode(g);
+        for (int i = 0; i < 4; i++) modes[i] = (nxn || !i) ? draw_mode(g) : modes[0];
+        paint_bs(g, x, y, s, s);
+        g->intra = 1;
+        gen_tt_intra(g, x, y, log2, bypass, modes, mode_c, nxn, 0);
+        g->intra = 0;
+        return;
+    }
+    mark_done(g, x, y, s, s);
     mode = rnd_range(&g->r, 0, 99);
     if (log2 == 3) {
         if (mode < 60)      emit_pu(g, x, y, s, s);
@@ -419,6 +535,8 @@ ohsynth_frame *ohsynth_generate(const ohsynth_params *p)
     f->ctb_width = (sp->width + ctb - 1) >> sp->log2_ctb_size;
     f->ctb_height = (sp->height + ctb - 1) >> sp->log2_ctb_size;
     nctb = f->ctb_width * f->ctb_height;
+    g->cell_w = (sp->width + 3) >> 2; g->cell_h = (sp->height + 3) >> 2;
+    g->done = calloc((size_t)g->cell_w * g->cell_h, 1);
     f->vbs = calloc((size_t)f->bs_width * f->bs_height, 1);
     f->hbs = calloc((size_t)f->bs_width * f->bs_height, 1);
     f->qp_y_tab = calloc((size_t)f->min_cb_width * f->min_cb_height, 1);
@@ -456,6 +574,7 @@ ohsynth_frame *ohsynth_generate(const ohsynth_params *p)
         gen_cqt(g, cx << sp->log2_ctb_size, cy << sp->log2_ctb_size, sp->log2_ctb_size);
     }
     free(slice_start);
+    free(g->done);
     free(g);
     return f;
 }
@@ -465,7 +584,7 @@ void ohsynth_free(ohsynth_frame *f)
     if (!f) return;
     free(f->slices); free(f->pus); free(f->tus); free(f->coeffs); free(f->vbs); free(f->hbs);
     free(f->qp_y_tab); free(f->deblock); free(f->is_pcm); free(f->sao);
-    free(f->filter_slice_edges); free(f->tab_slice_address); free(f->tile_id); free(f->leaves);
+    free(f->filter_slice_edges); free(f->tab_slice_address); free(f->tile_id); free(f->leaves); free(f->ius);
     free(f);
 }
 

@@ -80,6 +80,13 @@ typedef struct ohcu_seq_params {
     int32_t max_pus;              /* arena capacity per job; 0 = worst case        */
     int32_t max_tus;              /* arena capacity per job; 0 = worst case        */
     int64_t max_coeffs;           /* int16 arena capacity per job; 0 = worst case  */
+    int32_t intra;                /* 1: pictures may carry intra-predicted blocks (ohcu_iu): the jobs
+                                     get a residual plane set and an arena for the records.  0: a job
+                                     with intra units is refused (OHCU_ESTATE).  bit_depth <= 12:
+                                     ff_hevc_pred_init has no 14-bit predictors (hevcpred.c:62-76)  */
+    int32_t max_ius;              /* arena capacity per job; 0 = worst case        */
+    int32_t intra_smoothing_disabled;  /* sps->intra_smoothing_disabled_flag (hevcpred_template.c:275) */
+    int32_t strong_intra_smoothing;    /* sps->sps_strong_intra_smoothing_enable_flag (:282)          */
 } ohcu_seq_params;
 
 /* ---- per-slice tables (SliceHeader weights + RefPicList, hevcdec.c:202-306) */
@@ -120,6 +127,8 @@ typedef struct ohcu_pu {
 #define OHCU_TUF_RDPCM_VERT 2 /* mode argument of transform_rdpcm (1 = vertical)  */
 #define OHCU_TUF_ROTATE     4 /* 4x4 transform_skip rotation, hevc_cabac.c:1735   */
 #define OHCU_TUF_CROSS      8 /* cross-component prediction, hevc_cabac.c:1810    */
+#define OHCU_TUF_INTRA     16 /* the block sits on an intra-predicted TB: its residual is added
+                                 after the prediction of the ohcu_iu at the same position  */
 
 typedef struct ohcu_tu {
     uint16_t x0, y0;          /* position in samples of plane c_idx               */
@@ -135,6 +144,29 @@ typedef struct ohcu_tu {
     uint32_t cross_tu;        /* OHCU_TUF_CROSS: index (in this frame's TU list)
                                  of the luma TB whose residual is coeffs_y        */
 } ohcu_tu;                    /* 20 bytes */
+
+/* ---- one intra-predicted transform block: emitted where hls_transform_unit
+ *      calls s->hpc.intra_pred[log2 - 2](s, x0, y0, c_idx) (hevcdec.c:1335-1526), coded or not, in
+ *      that order.  A block reads the reconstructed samples left of and above it, so the list order is
+ *      the reconstruction order inside a CTB; across CTBs the device runs a wavefront (left, up-left,
+ *      up and up-right CTB first), which is the dependency the z-scan availability test allows.
+ *      cand: the five FINAL availability flags of hevcpred_template.c:103-107 (lc->na.cand_* combined
+ *      with the z-scan order test); constrained_intra_pred_flag must be 0.                          */
+#define OHCU_CAND_BOTTOM_LEFT 1
+#define OHCU_CAND_LEFT        2
+#define OHCU_CAND_UP_LEFT     4
+#define OHCU_CAND_UP          8
+#define OHCU_CAND_UP_RIGHT   16
+#define OHCU_IU_CBF          32   /* a coded TB (ohcu_tu with OHCU_TUF_INTRA, same c_idx, x0, y0, log2_size)
+                                     carries this block's residual (transform_add after the prediction)   */
+typedef struct ohcu_iu {
+    uint16_t x0, y0;          /* position in samples of plane c_idx               */
+    uint8_t  c_idx;           /* 0 Y, 1 Cb, 2 Cr                                  */
+    uint8_t  log2_size;       /* 2..5                                             */
+    uint8_t  mode;            /* 0 planar, 1 DC, 2..34 angular: lc->tu.intra_pred_mode, or
+                                 intra_pred_mode_c after the 4:2:2 tab_mode_idx mapping     */
+    uint8_t  cand;            /* OHCU_CAND_* | OHCU_IU_CBF                        */
+} ohcu_iu;                    /* 8 bytes */
 
 /* ---- DBParams, hevcdec.h:353-356 */
 typedef struct ohcu_dbparams {
@@ -278,6 +310,12 @@ int ohcu_append_pu(ohcu_ctx *ctx, int job, const ohcu_pu *recs, int n);
 int ohcu_append_tu(ohcu_ctx *ctx, int job, const ohcu_tu *recs, int n,
                    const int16_t *coeffs, size_t ncoeff);
 
+/* replaces the s->hpc.intra_pred[] calls of hls_transform_unit (hevcdec.c:1335-1526).  recs are copied
+ * before return; the blocks of one CTB must be appended contiguously and in decoding order, CTBs in any
+ * order.  The residual of a block with OHCU_IU_CBF arrives through ohcu_append_tu* as a record with
+ * OHCU_TUF_INTRA at the same position (either call first).  Needs ohcu_seq_params.intra.              */
+int ohcu_append_iu(ohcu_ctx *ctx, int job, const ohcu_iu *recs, int n);
+
 /* Zero-copy variant: reserve ncoeff int16 in the job's PINNED coefficient
  * arena and let the residual parser (lc->tu.coeffs, hevcdec.h:333) write there
  * directly.  *arena_off receives the absolute offset to store in coeff_off of
@@ -368,6 +406,9 @@ typedef struct ohcu_ctb_index {      /* per CTB, raster order; zeroed by ohcu_fr
     uint32_t first_tu, n_tu;         /* its coded TBs in arenas.tus (<= 768)                    */
     uint32_t first_coef, n_coef;     /* sparse / levels: its ohcu_coef pairs in arenas.coefs    */
 } ohcu_ctb_index;                    /* 24 bytes */
+typedef struct ohcu_iu_index {       /* per CTB, raster order; zeroed by ohcu_frame_begin      */
+    uint32_t first_iu, n_iu;         /* the CTB's intra blocks in arenas.ius, decoding order    */
+} ohcu_iu_index;                     /* 8 bytes */
 
 typedef struct ohcu_frame_arenas {
     ohcu_pu        *pus;             uint32_t max_pus;
@@ -390,6 +431,9 @@ typedef struct ohcu_frame_arenas {
     int32_t        *tile_id;
     uint8_t        *deblock_disabled;
     uint8_t        *scaling_list;    /* sl[4][6][64] then sl_dc[2][6] (1548 bytes)              */
+    ohcu_iu        *ius;             /* intra blocks (NULL unless ohcu_seq_params.intra)        */
+    ohcu_iu_index  *iu_ctbs;         /* ctb_width * ctb_height                                  */
+    uint32_t        max_ius, reserved;
 } ohcu_frame_arenas;
 
 #define OHCU_NO_REF       0xff       /* ohcu_slice_tab.ref_slot entry that names no picture     */
@@ -412,6 +456,7 @@ typedef struct ohcu_frame_counts {
     int32_t  all_inter;              /* the caller's promise that the PUs cover every sample (a P / B
                                         picture without intra CUs): the slot's previous content is then
                                         not carried over.  Checked on the device.                */
+    uint32_t n_iu;                   /* intra blocks written to arenas.ius                      */
 } ohcu_frame_counts;
 
 int ohcu_frame_arenas_get(ohcu_ctx *ctx, int job, ohcu_frame_arenas *out);
@@ -556,11 +601,6 @@ int ohcu_dsp_idct_noalloc(int bd, int16_t *coeffs, int log2_size, int col_limit,
  *  cand = the five final availability flags the reference computes at hevcpred_template.c:103-107 (lc->na.cand_* combined
  *  with the z-scan order test).  filter_ok = !sps->intra_smoothing_disabled_flag && (c_idx == 0 || chroma_format_idc == 3),
  *  strong = sps->sps_strong_intra_smoothing_enable_flag.  constrained_intra_pred_flag must be 0.                       */
-#define OHCU_CAND_BOTTOM_LEFT 1
-#define OHCU_CAND_LEFT        2
-#define OHCU_CAND_UP_LEFT     4
-#define OHCU_CAND_UP          8
-#define OHCU_CAND_UP_RIGHT   16
 int ohcu_dsp_intra_pred(int bd, uint8_t *plane, ptrdiff_t stride, int pw, int ph, int x, int y, int log2_size, int c_idx,
                         int mode, int cand, int filter_ok, int strong);
 /*  hevc_{h,v}_loop_filter_{luma,chroma}: pix = first Q sample, tc / no_p / no_q per 4-line

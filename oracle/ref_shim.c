@@ -276,6 +276,83 @@ static void ref_predict_pu(ref_state *st, const oh_frame_job *job, const ohcu_pu
 
 static void *zalloc(size_t n) { void *p = calloc(1, n ? n : 1); return p; }
 
+/* one coded TB: residual through the reference's table, then transform_add */
+static void ref_residual_tu(ref_state *st, HEVCDSPContext *t, const oh_frame_job *job, const ohcu_tu *tu, int P)
+{
+    DECLARE_ALIGNED(32, int16_t, res)[32 * 32];
+    DECLARE_ALIGNED(32, int16_t, res_y)[32 * 32];
+    int c = tu->c_idx, n2 = 1 << (2 * tu->log2_size);
+    ref_tu_residual(t, tu, job->coeffs, res);
+    if (tu->flags & OHCU_TUF_CROSS) {
+        ref_tu_residual(t, &job->tus[tu->cross_tu], job->coeffs, res_y);
+        for (int k = 0; k < n2; k++)
+            res[k] = res[k] + ((tu->res_scale_val * res_y[k]) >> 3);
+    }
+    t->transform_add[tu->log2_size - 2](
+        st->cur.data[c] + tu->y0 * st->cur.linesize[c] + tu->x0 * P, res, st->cur.linesize[c]);
+}
+
+/* The intra blocks through the reference's own HEVCPredContext (ff_hevc_pred_init, hevcpred.c; intra_pred
+ * hevcpred_template.c:30-345), in hls_transform_unit order with each block's transform_add behind it
+ * (hevcdec.c:1335-1526).  Availability: the job carries the five final flags; the z-scan table handed to the
+ * reference makes the current block the last one in order, so its own test (:103-107) leaves them as they are. */
+static int ref_intra_blocks(ref_state *st, HEVCDSPContext *t, const oh_frame_job *job, int P)
+{
+    const ohcu_seq_params *sp = &job->sp;
+    HEVCContext *s = &st->s;
+    HEVCSPS *sps = &st->sps;
+    HEVCPPS *pps = &st->pps;
+    HEVCLocalContext *lc = &st->lc;
+    const int log2_min_tb = 2, mask = (1 << (sp->log2_ctb_size - log2_min_tb)) - 1, tw = mask + 2;
+    int nplanes = sp->chroma_format_idc ? 3 : 1, rc = 0, cw[3];
+    int *zs = malloc(sizeof(int) * tw * tw);
+    int32_t *map[3] = { NULL, NULL, NULL };
+
+    sps->log2_min_tb_size = log2_min_tb;
+    sps->tb_mask = mask;
+    sps->intra_smoothing_disabled_flag = sp->intra_smoothing_disabled;
+    sps->sps_strong_intra_smoothing_enable_flag = sp->strong_intra_smoothing;
+    pps->constrained_intra_pred_flag = 0;
+    for (int i = 0; i < tw * tw; i++) zs[i] = -1;
+    pps->min_tb_addr_zs_tab = zs;
+    pps->min_tb_addr_zs = &zs[tw + 1];
+    ff_hevc_pred_init(&s->hpc, sp->bit_depth);
+    for (int c = 0; c < nplanes; c++) {
+        cw[c] = ((sp->width >> sps->hshift[c]) + 3) >> 2;
+        map[c] = zalloc(sizeof(int32_t) * cw[c] * (((sp->height >> sps->vshift[c]) + 3) >> 2));
+    }
+    for (int i = 0; i < job->n_tu; i++) {
+        const ohcu_tu *tu = &job->tus[i];
+        if ((tu->flags & OHCU_TUF_INTRA) && tu->c_idx < nplanes)
+            map[tu->c_idx][(tu->y0 >> 2) * cw[tu->c_idx] + (tu->x0 >> 2)] = i + 1;
+    }
+    for (int i = 0; i < job->n_iu; i++) {
+        const ohcu_iu *iu = &job->ius[i];
+        int c = iu->c_idx, x0, y0, cell;
+        if (c >= nplanes || iu->log2_size < 2 || iu->log2_size > 5 || iu->mode > 34) { rc = -1; break; }
+        x0 = iu->x0 << sps->hshift[c]; y0 = iu->y0 << sps->vshift[c];      /* the reference takes luma coordinates */
+        cell = ((y0 >> log2_min_tb) & mask) * tw + ((x0 >> log2_min_tb) & mask);
+        pps->min_tb_addr_zs[cell] = 1 << 20;
+        lc->tu.intra_pred_mode = lc->tu.intra_pred_mode_c = iu->mode;
+        lc->na.cand_bottom_left = !!(iu->cand & OHCU_CAND_BOTTOM_LEFT);
+        lc->na.cand_left = !!(iu->cand & OHCU_CAND_LEFT);
+        lc->na.cand_up_left = !!(iu->cand & OHCU_CAND_UP_LEFT);
+        lc->na.cand_up = !!(iu->cand & OHCU_CAND_UP);
+        lc->na.cand_up_right = !!(iu->cand & OHCU_CAND_UP_RIGHT);
+        s->hpc.intra_pred[iu->log2_size - 2](s, x0, y0, c);
+        pps->min_tb_addr_zs[cell] = -1;
+        if (iu->cand & OHCU_IU_CBF) {
+            int k = map[c][(iu->y0 >> 2) * cw[c] + (iu->x0 >> 2)];
+            if (!k || job->tus[k - 1].log2_size != iu->log2_size) { rc = -1; break; }
+            ref_residual_tu(st, t, job, &job->tus[k - 1], P);
+        }
+    }
+    for (int c = 0; c < 3; c++) free(map[c]);
+    free(zs);
+    pps->min_tb_addr_zs_tab = NULL; pps->min_tb_addr_zs = NULL;
+    return rc;
+}
+
 int ohref_replay_frame(const oh_frame_job *job)
 {
     const ohcu_seq_params *sp = &job->sp;
@@ -356,19 +433,13 @@ int ohref_replay_frame(const oh_frame_job *job)
 
     /* --- residual: dispatcher tail of ff_hevc_hls_transform{,_c} (hevc_cabac.c:1807-1818) --- */
     if (stages & OH_STAGE_RESIDUAL) {
-        DECLARE_ALIGNED(32, int16_t, res)[32 * 32];
-        DECLARE_ALIGNED(32, int16_t, res_y)[32 * 32];
-        for (int i = 0; i < job->n_tu; i++) {
-            const ohcu_tu *tu = &job->tus[i];
-            int c = tu->c_idx, n2 = 1 << (2 * tu->log2_size);
-            ref_tu_residual(t, tu, job->coeffs, res);
-            if (tu->flags & OHCU_TUF_CROSS) {
-                ref_tu_residual(t, &job->tus[tu->cross_tu], job->coeffs, res_y);
-                for (int k = 0; k < n2; k++)
-                    res[k] = res[k] + ((tu->res_scale_val * res_y[k]) >> 3);
-            }
-            t->transform_add[tu->log2_size - 2](
-                st->cur.data[c] + tu->y0 * st->cur.linesize[c] + tu->x0 * P, res, st->cur.linesize[c]);
+        for (int i = 0; i < job->n_tu; i++)
+            if (!(job->tus[i].flags & OHCU_TUF_INTRA))
+                ref_residual_tu(st, t, job, &job->tus[i], P);
+        if (job->n_iu && ref_intra_blocks(st, t, job, P)) {
+            for (int c = 0; c < nplanes; c++) free(curbuf[c]);
+            free(pps->ctb_addr_rs_to_ts); free(pps->tile_id); free(st);
+            return OHCU_EINVAL;
         }
     }
 

@@ -8,6 +8,7 @@
  *              videodsp_template.c:22-100 (restated as a replicate clamp of the
  *              source coordinates, applied always: it is idempotent inside the picture)
  *   residual   ff_hevc_hls_transform{,_c} hevc_cabac.c:1695-1906
+ *   intra      the s->hpc.intra_pred[] calls of hls_transform_unit hevcdec.c:1335-1526 (intra_oracle.c)
  *   deblock    deblocking_filter_CTB hevc_filter.c:525-762 (per CTB, raster order)
  *   SAO        sao_filter_CTB hevc_filter.c:264-502 + restore_tqb_pixels :229-260,
  *              restated out of place from a snapshot of the deblocked picture (the
@@ -143,6 +144,42 @@ static void tu_residual(const rp *r, const ohcu_tu *tu, int16_t *out)
     case OHCU_TU_DC:   or_idct_dc(r->bd, out, tu->log2_size); break; /* :1794-1796 */
     default:           or_idct(r->bd, out, tu->log2_size, tu->col_limit); break; /* :1805 */
     }
+}
+
+/* the intra blocks in decoding order: prediction from the picture as reconstructed so far, then the residual of
+ * the coded TB at the same position (hls_transform_unit, hevcdec.c:1335-1526) */
+static void residual_tu(const rp *r, const ohcu_tu *tu);
+static int intra_blocks(const rp *r)
+{
+    const oh_frame_job *job = r->job;
+    const ohcu_seq_params *sp = r->sp;
+    int32_t *map[3] = { NULL, NULL, NULL };
+    int cw[3], rc = 0;
+    for (int c = 0; c < r->nplanes; c++) {
+        cw[c] = ((sp->width >> r->hs[c]) + 3) >> 2;
+        map[c] = calloc((size_t)cw[c] * (((sp->height >> r->vs[c]) + 3) >> 2), sizeof(int32_t));
+    }
+    for (int i = 0; i < job->n_tu; i++) {
+        const ohcu_tu *tu = &job->tus[i];
+        if ((tu->flags & OHCU_TUF_INTRA) && tu->c_idx < r->nplanes)
+            map[tu->c_idx][(tu->y0 >> 2) * cw[tu->c_idx] + (tu->x0 >> 2)] = i + 1;
+    }
+    for (int i = 0; i < job->n_iu && !rc; i++) {
+        const ohcu_iu *iu = &job->ius[i];
+        int c = iu->c_idx, pw, ph;
+        if (c >= r->nplanes || iu->log2_size < 2 || iu->log2_size > 5 || iu->mode > 34) { rc = OHCU_EINVAL; break; }
+        pw = sp->width >> r->hs[c]; ph = sp->height >> r->vs[c];
+        or_intra_pred(r->bd, r->cur.data[c], r->cur.stride[c], pw, ph, iu->x0, iu->y0, iu->log2_size, c, iu->mode,
+                      iu->cand & 31, !sp->intra_smoothing_disabled && (c == 0 || sp->chroma_format_idc == 3),
+                      sp->strong_intra_smoothing);
+        if (iu->cand & OHCU_IU_CBF) {
+            int t = map[c][(iu->y0 >> 2) * cw[c] + (iu->x0 >> 2)];
+            if (!t || job->tus[t - 1].log2_size != iu->log2_size) { rc = OHCU_EINVAL; break; }
+            residual_tu(r, &job->tus[t - 1]);
+        }
+    }
+    for (int c = 0; c < 3; c++) free(map[c]);
+    return rc;
 }
 
 static void residual_tu(const rp *r, const ohcu_tu *tu)
@@ -414,9 +451,19 @@ int or_replay_frame(const oh_frame_job *job)
             for (int c = 0; c < r.nplanes; c++)
                 predict_plane(&r, pu, &job->slices[pu->slice], c);
         }
-    if (stages & OH_STAGE_RESIDUAL)
+    if (stages & OH_STAGE_RESIDUAL) {
         for (int i = 0; i < job->n_tu; i++)
-            residual_tu(&r, &job->tus[i]);
+            if (!(job->tus[i].flags & OHCU_TUF_INTRA))
+                residual_tu(&r, &job->tus[i]);
+        if (job->n_iu) {
+            int rc;
+            /* ff_hevc_pred_init (hevcpred.c:62-76) instantiates 8, 9, 10 and 12 bits only; any other depth gets the
+             * 8-bit predictors, which read 16-bit planes as bytes: no defined behaviour to restate */
+            if (sp->bit_depth > 12 || sp->bit_depth == 11) return OHCU_EINVAL;
+            rc = intra_blocks(&r);
+            if (rc) return rc;
+        }
+    }
     if ((stages & OH_STAGE_DEBLOCK) && job->deblock)
         for (int y = 0; y < sp->height; y += r.ctb_size)
             for (int x = 0; x < sp->width; x += r.ctb_size)

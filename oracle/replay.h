@@ -11,7 +11,10 @@
  *                        (hevc_filter.c:264-762, 1211-1245); only built when
  *                        /root/reference is present (oracle/Makefile -> oracle/_ref/).
  * Both process in the reference's order: all PUs (hls_prediction_unit order),
- * all TUs (transform_add), then per CTB in raster order the one-CTB-delayed
+ * all TUs of inter CUs (transform_add), then the intra blocks in decoding order, each
+ * predicted from the samples reconstructed so far and followed by its own transform_add
+ * (hevcdec.c:1335-1526; inter reconstruction never reads the current picture, so moving
+ * it ahead of the intra blocks changes nothing), then per CTB in raster order the one-CTB-delayed
  * deblock + SAO of ff_hevc_hls_filters (hevcdec.c:2898-2903).
  */
 #ifndef OH_REPLAY_H
@@ -42,7 +45,9 @@ typedef struct oh_frame_job {
     const ohcu_sao_in *sao;           /* NULL = no SAO        */
     const oh_picture *dpb;            /* sp.dpb_slots reference pictures */
     oh_picture out;                   /* reconstructed picture (written) */
-    int32_t stages;                   /* bit mask: 1 MC, 2 residual, 4 deblock, 8 SAO; 0 = all */
+    int32_t stages;                   /* bit mask: 1 MC, 2 residual (+ intra blocks), 4 deblock, 8 SAO; 0 = all */
+    int32_t n_iu;                     /* intra blocks (hls_transform_unit order); their coded TBs are the tus */
+    const ohcu_iu *ius;               /* with OHCU_TUF_INTRA at the same position                              */
 } oh_frame_job;
 
 #define OH_STAGE_MC       1

@@ -20,7 +20,8 @@ int main(void)
         F(ohcu_seq_params, log2_min_pu_size) F(ohcu_seq_params, dpb_slots) F(ohcu_seq_params, jobs)
         F(ohcu_seq_params, sao_enabled) F(ohcu_seq_params, pcm_or_bypass) F(ohcu_seq_params, cb_qp_offset)
         F(ohcu_seq_params, cr_qp_offset) F(ohcu_seq_params, no_tile_filter) F(ohcu_seq_params, max_pus)
-        F(ohcu_seq_params, max_tus) F(ohcu_seq_params, max_coeffs) E()
+        F(ohcu_seq_params, max_tus) F(ohcu_seq_params, max_coeffs) F(ohcu_seq_params, intra) F(ohcu_seq_params, max_ius)
+        F(ohcu_seq_params, intra_smoothing_disabled) F(ohcu_seq_params, strong_intra_smoothing) E()
     S(ohcu_slice_tab) F(ohcu_slice_tab, ref_slot) F(ohcu_slice_tab, weight_flag) F(ohcu_slice_tab, luma_log2_weight_denom)
         F(ohcu_slice_tab, chroma_log2_weight_denom) F(ohcu_slice_tab, pad) F(ohcu_slice_tab, luma_weight)
         F(ohcu_slice_tab, luma_offset) F(ohcu_slice_tab, chroma_weight) F(ohcu_slice_tab, chroma_offset) E()
@@ -28,6 +29,8 @@ int main(void)
         F(ohcu_pu, mv) F(ohcu_pu, ref_idx) F(ohcu_pu, pad) E()
     S(ohcu_tu) F(ohcu_tu, x0) F(ohcu_tu, y0) F(ohcu_tu, c_idx) F(ohcu_tu, log2_size) F(ohcu_tu, mode) F(ohcu_tu, flags)
         F(ohcu_tu, col_limit) F(ohcu_tu, res_scale_val) F(ohcu_tu, pad) F(ohcu_tu, coeff_off) F(ohcu_tu, cross_tu) E()
+    S(ohcu_iu) F(ohcu_iu, x0) F(ohcu_iu, y0) F(ohcu_iu, c_idx) F(ohcu_iu, log2_size) F(ohcu_iu, mode) F(ohcu_iu, cand) E()
+    S(ohcu_iu_index) F(ohcu_iu_index, first_iu) F(ohcu_iu_index, n_iu) E()
     S(ohcu_dbparams) F(ohcu_dbparams, beta_offset) F(ohcu_dbparams, tc_offset) E()
     S(ohcu_sao) F(ohcu_sao, type_idx) F(ohcu_sao, eo_class) F(ohcu_sao, band_position) F(ohcu_sao, pad)
         F(ohcu_sao, offset_val) E()
@@ -50,11 +53,12 @@ int main(void)
         F(ohcu_frame_arenas, vertical_bs) F(ohcu_frame_arenas, horizontal_bs) F(ohcu_frame_arenas, qp_y_tab)
         F(ohcu_frame_arenas, deblock) F(ohcu_frame_arenas, is_pcm) F(ohcu_frame_arenas, sao)
         F(ohcu_frame_arenas, filter_slice_edges) F(ohcu_frame_arenas, tab_slice_address) F(ohcu_frame_arenas, tile_id)
-        F(ohcu_frame_arenas, deblock_disabled) F(ohcu_frame_arenas, scaling_list) E()
+        F(ohcu_frame_arenas, deblock_disabled) F(ohcu_frame_arenas, scaling_list)
+        F(ohcu_frame_arenas, ius) F(ohcu_frame_arenas, iu_ctbs) F(ohcu_frame_arenas, max_ius) F(ohcu_frame_arenas, reserved) E()
     S(ohcu_frame_counts) F(ohcu_frame_counts, n_pu) F(ohcu_frame_counts, n_tu) F(ohcu_frame_counts, n_coef)
         F(ohcu_frame_counts, n_slices) F(ohcu_frame_counts, coef_form) F(ohcu_frame_counts, deblock)
         F(ohcu_frame_counts, sao) F(ohcu_frame_counts, pcm) F(ohcu_frame_counts, scaling_list)
-        F(ohcu_frame_counts, all_inter) E()
+        F(ohcu_frame_counts, all_inter) F(ohcu_frame_counts, n_iu) E()
     S(ohcu_pic_params) F(ohcu_pic_params, pcm_or_bypass) F(ohcu_pic_params, cb_qp_offset)
         F(ohcu_pic_params, cr_qp_offset) F(ohcu_pic_params, no_tile_filter) E()
     printf("}\n");

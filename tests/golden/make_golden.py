@@ -42,7 +42,7 @@ def main():
         job, refs = frame_cases.build_case(name)
         frames[name] = {
             "n_pu": int(len(job.pus)), "n_tu": int(len(job.tus)), "ncoeff": int(len(job.coeffs)),
-            "lists": hashlib.sha256(job.pus.tobytes() + job.tus.tobytes() + job.coeffs.tobytes()).hexdigest(),
+            "lists": frame_cases.lists_digest(job),
         }
         for key, st in STAGE_SETS.items():
             out = ref.replay(job, refs, out_init=refs[-1], stages=st)

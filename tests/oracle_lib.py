@@ -35,6 +35,7 @@ class FrameJobC(C.Structure):
         ("coeffs", C.c_void_p), ("ncoeff", C.c_int64),
         ("deblock", C.POINTER(abi.DeblockIn)), ("sao", C.POINTER(abi.SaoIn)),
         ("dpb", C.POINTER(Picture)), ("out", Picture), ("stages", C.c_int32),
+        ("n_iu", C.c_int32), ("ius", C.c_void_p),
     ]
 
 
@@ -248,6 +249,9 @@ class Lib:
             fj.out.data[c] = out[c].ctypes.data
             fj.out.stride[c] = out[c].strides[0]
         fj.stages = stages
+        ius = getattr(job, "ius", None)
+        if ius is not None and len(ius):
+            fj.n_iu = len(ius); fj.ius = ius.ctypes.data
         rc = self._replay(C.byref(fj))
         if rc != 0:
             raise RuntimeError(f"{self.which} replay failed: {rc}")
