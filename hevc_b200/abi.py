@@ -156,6 +156,8 @@ NO_REF = 0xff
 COEF_DENSE, COEF_SPARSE, COEF_LEVELS = 1, 2, 3
 DEBLOCK_NONE, DEBLOCK_PLANES, DEBLOCK_DERIVED = 0, 1, 2
 TUF_INTRA, IU_CBF = 16, 32
+CAND_BOTTOM_LEFT, CAND_LEFT, CAND_UP_LEFT, CAND_UP, CAND_UP_RIGHT = 1, 2, 4, 8, 16
+EINVAL, ENOMEM, ECUDA, ESTATE, ENODEV, EOVERFLOW = -1, -2, -3, -4, -5, -6
 
 # every struct of include/ohcu.h by its C name: tests/test_abi.py compares sizeof / offsetof with a C program
 STRUCTS = {

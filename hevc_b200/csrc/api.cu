@@ -377,7 +377,7 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
 #define TRYCU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { ohcu_destroy(c); \
         return fail(e_ == cudaErrorMemoryAllocation ? OHCU_ENOMEM : OHCU_ECUDA, "%s -> %s", #x, cudaGetErrorString(e_)); } } while (0)
     if (upload_dct_table() || upload_mc_taps()) { ohcu_destroy(c); return fail(OHCU_ECUDA, "constant upload failed"); }
-    if (recon_set_attrs() || loopfilter_set_attrs()) { ohcu_destroy(c); return fail(OHCU_ECUDA, "cudaFuncSetAttribute failed"); }
+    if (recon_set_attrs() || loopfilter_set_attrs() || intra_set_attrs()) { ohcu_destroy(c); return fail(OHCU_ECUDA, "cudaFuncSetAttribute failed"); }
     c->slots.resize(sp->dpb_slots);
     for (auto &s : c->slots) {
         TRY(alloc_picture(c, &s.pic, true));
@@ -806,10 +806,9 @@ extern "C" int ohcu_append_iu(ohcu_ctx *c, int job, const ohcu_iu *recs, int n)
     int last = j.last_iu_ctb;
     for (int i = 0; i < n; i++) {
         const ohcu_iu u = recs[i];
-        if (!iu_ok(u, c->nplanes, c->pw, c->ph)) return fail(OHCU_EINVAL, "intra block record %d is malformed", base + i);
-        const int hs = u.c_idx ? c->hs : 0, vs = u.c_idx ? c->vs : 0, n1 = 1 << u.log2_size;
-        if (((u.x0 << hs) >> l2) != (((u.x0 + n1 - 1) << hs) >> l2) || ((u.y0 << vs) >> l2) != (((u.y0 + n1 - 1) << vs) >> l2))
-            return fail(OHCU_EINVAL, "intra block record %d crosses a CTB boundary", base + i);
+        if (!iu_ok(u, c->nplanes, c->pw, c->ph, c->hs, c->vs, l2))
+            return fail(OHCU_EINVAL, "intra block record %d is malformed (size, mode, position, or a neighbour named available that cannot be)", base + i);
+        const int hs = u.c_idx ? c->hs : 0, vs = u.c_idx ? c->vs : 0;
         const int ctb = ((u.x0 << hs) >> l2) + ((u.y0 << vs) >> l2) * c->ctb_w;
         if (ctb != last) {
             if (idx[ctb].n_iu) return fail(OHCU_EINVAL, "intra block record %d: the blocks of a CTB must be appended contiguously", base + i);

@@ -11,7 +11,8 @@
 // 1 if the transform block on either side has cbf_luma, else the motion rule; inside the leaf
 // only the motion rule.  "A transform-block boundary with cbf_luma on a side" is the same as
 // "on the perimeter of a coded luma TB", so the coded TBs of the TU list are enough and the
-// transform tree itself need not cross the bus.  4x4 blocks no PU covers count as intra.
+// transform tree itself need not cross the bus.  4x4 blocks no PU covers count as intra (2), except inside one
+// intra leaf - the luma ohcu_iu blocks are the leaves of the intra CUs - which is no boundary.
 //
 // One CTA per CTB.  The PUs and coded luma TBs of the CTB, of its left and of its upper neighbour
 // enter a (cells + 1)^2 map of 4x4 cells in shared memory (PU index, TB index); then one thread
@@ -27,7 +28,7 @@ namespace ohcu {
 constexpr int BS_THREADS = BS_NTHREADS;      // 128: all CTBs of a 4K picture are resident at once (16 CTAs per SM)
 constexpr int BS_CELLS = 17;                 // 16 cells of a 64x64 CTB + the neighbour's column / row
 
-struct BsCell { int pu, tb; };
+struct BsCell { int pu, tb, iu; };
 
 __device__ __forceinline__ bool bs_far(const int16_t a[2], const int16_t b[2])
 {
@@ -65,18 +66,18 @@ __global__ void __launch_bounds__(BS_THREADS) bs_kernel(const __grid_constant__ 
     const int ctb = blockIdx.x, ctbx = ctb % f.ctb_w, ctby = ctb / f.ctb_w;
     const int cs = 1 << f.log2_ctb, n4 = cs >> 2;
     const int gx0 = (ctbx << f.log2_ctb) >> 2, gy0 = (ctby << f.log2_ctb) >> 2;     // cell coordinates of the CTB's origin
-    for (int i = tid; i < BS_CELLS * BS_CELLS; i += BS_THREADS) cell[i] = BsCell{-1, -1};
+    for (int i = tid; i < BS_CELLS * BS_CELLS; i += BS_THREADS) cell[i] = BsCell{-1, -1, -1};
     __syncthreads();
 
     // ---- the cell map: this CTB, its left and its upper neighbour (clipped to the window)
     const int nb[3] = {ctb, ctbx > 0 ? ctb - 1 : -1, ctby > 0 ? ctb - f.ctb_w : -1};
-    auto paint = [&](int x4, int y4, int w4, int h4, int idx, bool is_tb) {
+    auto paint = [&](int x4, int y4, int w4, int h4, int idx, int what) {      // what: 0 PU, 1 coded luma TB, 2 intra leaf
         // rectangle in picture cells -> window cells [-1, n4)
         const int xa = max(x4 - gx0, -1), xb = min(x4 + w4 - gx0, n4), ya = max(y4 - gy0, -1), yb = min(y4 + h4 - gy0, n4);
         for (int y = ya; y < yb; y++)
             for (int x = xa; x < xb; x++) {
                 BsCell &c = cell[(y + 1) * BS_CELLS + x + 1];
-                if (is_tb) c.tb = idx; else c.pu = idx;
+                if (what == 1) c.tb = idx; else if (what == 2) c.iu = idx; else c.pu = idx;
             }
     };
     int2 pr[3], tr[3];
@@ -90,11 +91,18 @@ __global__ void __launch_bounds__(BS_THREADS) bs_kernel(const __grid_constant__ 
         const int np = min(pr[k].y & 0xffffff, 128);
         for (int i = tid; i < np; i += BS_THREADS) {
             const ohcu_pu &pu = f.pus[pr[k].x + i];
-            paint(pu.x0 >> 2, pu.y0 >> 2, pu.w >> 2, pu.h >> 2, pr[k].x + i, false);
+            paint(pu.x0 >> 2, pu.y0 >> 2, pu.w >> 2, pu.h >> 2, pr[k].x + i, 0);
         }
         for (int i = tid; i < tr[k].y; i += BS_THREADS) {
             const ohcu_tu &tu = f.tus[tr[k].x + i];
-            if (tu.c_idx == 0) paint(tu.x0 >> 2, tu.y0 >> 2, 1 << (tu.log2_size - 2), 1 << (tu.log2_size - 2), tr[k].x + i, true);
+            if (tu.c_idx == 0) paint(tu.x0 >> 2, tu.y0 >> 2, 1 << (tu.log2_size - 2), 1 << (tu.log2_size - 2), tr[k].x + i, 1);
+        }
+        if (f.n_iu > 0 && nb[k] >= 0) {                    // the luma intra blocks are the leaves of the intra CUs
+            const ohcu_iu_index ii = f.iu_index[nb[k]];
+            for (uint32_t i = tid; i < min(ii.n_iu, 768u); i += BS_THREADS) {
+                const ohcu_iu &u = f.ius[ii.first_iu + i];
+                if (u.c_idx == 0) paint(u.x0 >> 2, u.y0 >> 2, 1 << (u.log2_size - 2), 1 << (u.log2_size - 2), (int)(ii.first_iu + i), 2);
+            }
         }
     }
     __syncthreads();
@@ -114,7 +122,7 @@ __global__ void __launch_bounds__(BS_THREADS) bs_kernel(const __grid_constant__ 
         if (!(flags & BSF_DISABLED) && !(on_ctb_edge && (flags & (dir ? BSF_NO_UP : BSF_NO_LEFT)))) {
             const BsCell q = cell[(cy + 1) * BS_CELLS + cx + 1];
             const BsCell p = dir ? cell[cy * BS_CELLS + cx + 1] : cell[(cy + 1) * BS_CELLS + cx];
-            if (q.pu < 0 || p.pu < 0) bs = 2;
+            if (q.pu < 0 || p.pu < 0) bs = (q.iu >= 0 && q.iu == p.iu) ? 0 : 2;      // inside one intra leaf: no edge
             else if (q.tb != p.tb && (q.tb >= 0 || p.tb >= 0)) bs = 1;
             else if (q.pu != p.pu) bs = bs_motion(f, f.pus[q.pu], f.pus[p.pu]);
         }

@@ -116,23 +116,28 @@ int launch_recon(const FrameDev &f, int flags, cudaStream_t st);   // flags: 1 M
 int recon_sparse_ctb_coefs(int log2_ctb, int nplanes, int hs, int vs);   // int16 a CTB's rebuilt coefficient area may hold (sparse form)
 int recon_set_attrs();                     // per-device function attributes (dynamic shared memory opt-in)
 int loopfilter_set_attrs();
+int intra_set_attrs();
 int upload_mc_taps();
 int upload_dct_table();
 struct LfMaps { CUtensorMap m[3]; };        // the job's reconstructed picture, one box per plane
 int launch_loopfilter(const FrameDev &f, const LfMaps &maps, int flags, cudaStream_t st);   // flags: 1 deblock, 2 SAO
 int launch_bs_derive(const FrameDev &f, cudaStream_t st);      // vbs / hbs from the PU and TU lists (bs.cu)
 int launch_intra(const FrameDev &f, cudaStream_t st);          // the intra blocks, CTB wavefront (intra.cu)
-// an intra block record is well formed for this sequence (shared by ohcu_append_iu and prepare_kernel)
-__host__ __device__ inline bool iu_ok(const ohcu_iu &u, int nplanes, const int *pw, const int *ph)
+// an intra block record is well formed for this sequence (shared by ohcu_append_iu and prepare_kernel): inside its
+// plane and one CTB, and no neighbour named available that the decoding order cannot have produced yet - outside the
+// plane, below the CTB, or right of the CTB on any row but the one above it (intra_kernel stages exactly that much)
+__host__ __device__ inline bool iu_ok(const ohcu_iu &u, int nplanes, const int *pw, const int *ph, int hs, int vs, int log2_ctb)
 {
     if (u.c_idx >= nplanes || u.log2_size < 2 || u.log2_size > 5 || u.mode > 34 || (u.cand & 0xc0)) return false;
     const int n = 1 << u.log2_size;
     if (((u.x0 | u.y0) & 3) || u.x0 + n > pw[u.c_idx] || u.y0 + n > ph[u.c_idx]) return false;
-    // neighbours named available must lie inside the plane
+    const int sw = (1 << log2_ctb) >> (u.c_idx ? hs : 0), sh = (1 << log2_ctb) >> (u.c_idx ? vs : 0);
+    const int bx = u.x0 & (sw - 1), by = u.y0 & (sh - 1);
+    if (bx + n > sw || by + n > sh) return false;
     if ((u.cand & (OHCU_CAND_LEFT | OHCU_CAND_BOTTOM_LEFT | OHCU_CAND_UP_LEFT)) && u.x0 == 0) return false;
     if ((u.cand & (OHCU_CAND_UP | OHCU_CAND_UP_RIGHT | OHCU_CAND_UP_LEFT)) && u.y0 == 0) return false;
-    if ((u.cand & OHCU_CAND_BOTTOM_LEFT) && u.y0 + n >= ph[u.c_idx]) return false;
-    if ((u.cand & OHCU_CAND_UP_RIGHT) && u.x0 + n >= pw[u.c_idx]) return false;
+    if ((u.cand & OHCU_CAND_BOTTOM_LEFT) && (u.y0 + n >= ph[u.c_idx] || by + n >= sh)) return false;
+    if ((u.cand & OHCU_CAND_UP_RIGHT) && (u.x0 + n >= pw[u.c_idx] || (bx + n >= sw && by > 0))) return false;
     return true;
 }
 // per-entry test shims (recon.cu, loopfilter.cu)

@@ -146,11 +146,10 @@ __global__ void __launch_bounds__(PREP_THREADS) prepare_kernel(const __grid_cons
             for (uint32_t i = tid; i < ii.n_iu; i += PREP_THREADS) {
                 const uint32_t r = ii.first_iu + i;
                 const ohcu_iu u = f.ius[r];
-                bool ok = iu_ok(u, f.nplanes, f.pw, f.ph);
+                bool ok = iu_ok(u, f.nplanes, f.pw, f.ph, f.hs, f.vs, l2);
                 if (ok) {
-                    const int hs = u.c_idx ? f.hs : 0, vs = u.c_idx ? f.vs : 0, n = 1 << u.log2_size;
-                    ok = ((u.x0 << hs) >> l2) == ctbx && (((u.x0 + n - 1) << hs) >> l2) == ctbx &&
-                         ((u.y0 << vs) >> l2) == ctby && (((u.y0 + n - 1) << vs) >> l2) == ctby;
+                    const int hs = u.c_idx ? f.hs : 0, vs = u.c_idx ? f.vs : 0;
+                    ok = ((u.x0 << hs) >> l2) == ctbx && ((u.y0 << vs) >> l2) == ctby;
                 }
                 if (!ok) prep_fail(p.err, PE_IU, r);
             }

@@ -205,7 +205,10 @@ typedef struct ohcu_deblock_in {
  *        coded luma TBs          ->  cbf_luma: an edge unit lies on a transform-block
  *                                    boundary with cbf_luma on a side exactly when it lies
  *                                    on the perimeter of a coded luma TB
- *      4x4 blocks no PU covers count as intra (bs 2).  The per-CTB tables say where the
+ *      4x4 blocks no PU covers count as intra (bs 2 on their edges); the luma ohcu_iu blocks are
+ *      the leaves of the intra CUs, so an edge unit inside one of them is no boundary (0).  PCM
+ *      CUs carry neither PUs nor intra blocks: send the planes (ohcu_set_deblock) for pictures
+ *      that use them.  The per-CTB tables say where the
  *      reference suppresses CTB-boundary edges (lc->boundary_flags, hevcdec.c:2822-2837, with
  *      slice_loop_filter_across_slices_enabled_flag of the CTB's slice and
  *      seq.no_tile_filter) and which slices have slice_deblocking_filter_disabled_flag. */

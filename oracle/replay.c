@@ -498,9 +498,11 @@ int or_replay_frame(const oh_frame_job *job)
  * An edge unit is "a transform-block boundary with cbf_luma on a side" exactly when it lies on
  * the perimeter of a CODED luma TB, so the coded TBs the ABI already has are enough: the edge
  * separates two 4x4 cells that do not belong to the same coded TB and one of them belongs to
- * one.  Cells no PU covers count as intra.  The motion rule compares reference PICTURES (the
+ * one.  Cells no PU covers count as intra: an edge with such a cell on a side is 2 - unless both cells
+ * lie in the same intra leaf, which is no transform-tree boundary at all (the luma ohcu_iu blocks ARE the
+ * leaves of the intra CUs).  The motion rule compares reference PICTURES (the
  * reference compares POCs; here DPB slots, one picture per slot). */
-typedef struct bs_cell { int32_t pu, tb; } bs_cell;
+typedef struct bs_cell { int32_t pu, tb, iu; } bs_cell;
 
 static int bs_far(const int16_t a[2], const int16_t b[2])
 {
@@ -534,7 +536,7 @@ static int bs_motion(const oh_bs_job *job, const ohcu_pu *c, const ohcu_pu *n)
 
 static int bs_unit(const oh_bs_job *job, const bs_cell *q, const bs_cell *p)
 {
-    if (q->pu < 0 || p->pu < 0) return 2;
+    if (q->pu < 0 || p->pu < 0) return (q->iu >= 0 && q->iu == p->iu) ? 0 : 2;
     if (q->tb != p->tb && (q->tb >= 0 || p->tb >= 0)) return 1;
     if (q->pu == p->pu) return 0;
     return bs_motion(job, &job->pus[q->pu], &job->pus[p->pu]);
@@ -547,7 +549,14 @@ int or_boundary_strengths(const oh_bs_job *job)
     const int l2 = sp->log2_ctb_size, ctb_w = (W + (1 << l2) - 1) >> l2, cmask = (1 << l2) - 1;
     bs_cell *g = malloc(sizeof(bs_cell) * (size_t)gw * gh);
     if (!g) return OHCU_ENOMEM;
-    for (int i = 0; i < gw * gh; i++) g[i].pu = g[i].tb = -1;
+    for (int i = 0; i < gw * gh; i++) g[i].pu = g[i].tb = g[i].iu = -1;
+    for (int i = 0; i < job->n_iu; i++) {
+        const ohcu_iu *iu = &job->ius[i];
+        const int n4 = 1 << (iu->log2_size - 2);
+        if (iu->c_idx) continue;
+        for (int y = iu->y0 >> 2; y < (iu->y0 >> 2) + n4 && y < gh; y++)
+            for (int x = iu->x0 >> 2; x < (iu->x0 >> 2) + n4 && x < gw; x++) g[y * gw + x].iu = i;
+    }
     for (int i = 0; i < job->n_pu; i++) {
         const ohcu_pu *pu = &job->pus[i];
         for (int y = pu->y0 >> 2; y < (pu->y0 + pu->h) >> 2 && y < gh; y++)

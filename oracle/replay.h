@@ -78,6 +78,7 @@ typedef struct oh_bs_job {
     const int32_t *tile_id;                       /* per CTB; NULL = one tile  */
     const uint8_t *deblock_disabled;              /* per CTB: slice_deblocking_filter_disabled_flag; NULL = 0 */
     uint8_t *vbs, *hbs;                           /* out: ((width >> 2) + 1) * ((height >> 2) + 1) each */
+    int32_t n_iu;      const ohcu_iu *ius;        /* intra blocks; the luma ones are the leaves of the intra CUs */
 } oh_bs_job;
 
 int or_boundary_strengths(const oh_bs_job *job);

@@ -21,6 +21,9 @@ BS_CASES = {
     # no coded luma TB at all: every unit is decided by the motion rule
     "cfg1_near_nocbf": ("cfg1_416x240_8b_420", 22, 5, 50),
     "slices_tiles_nocbf": ("slices_tiles_8b_420", 23, 5, 50),
+    # intra CUs between the inter ones: an edge with an intra side is 2 (hevc_filter.c:1030, :1062)
+    "intra_near": ("intra_8b_420", 24, 6, 40),
+    "intra_slices_tiles": ("intra_slices_tiles_8b", 25, 6, 40),
     "tiny": ("tiny_8x8", 20, 4, 50),
     "one_ctb": ("one_ctb", 21, 4, 50),
 }

@@ -48,6 +48,7 @@ class BsJobC(C.Structure):
         ("n_leaf", C.c_int32), ("leaves", C.c_void_p),
         ("filter_slice_edges", C.c_void_p), ("tab_slice_address", C.c_void_p), ("tile_id", C.c_void_p),
         ("deblock_disabled", C.c_void_p), ("vbs", C.c_void_p), ("hbs", C.c_void_p),
+        ("n_iu", C.c_int32), ("ius", C.c_void_p),
     ]
 
 
@@ -195,6 +196,8 @@ class Lib:
             deblock_disabled = np.ascontiguousarray(deblock_disabled, dtype=np.uint8)
             bj.deblock_disabled = deblock_disabled.ctypes.data
         bj.vbs = vbs.ctypes.data; bj.hbs = hbs.ctypes.data
+        if len(getattr(job, "ius", ())):
+            bj.n_iu = len(job.ius); bj.ius = job.ius.ctypes.data
         rc = self._bs(C.byref(bj))
         if rc != 0:
             raise RuntimeError(f"{self.which} boundary_strengths failed: {rc}")
