@@ -125,7 +125,7 @@ struct Job {
     PcmRec *pcm_h = nullptr, *pcm_d = nullptr; int n_pcm = 0, pcm_cap = 0;
     uint8_t *pcms_h = nullptr, *pcms_d = nullptr; size_t pcm_bytes = 0, pcms_cap = 0;
     // intra blocks (ohcu_seq_params.intra): records, where each CTB's sit, the residual planes of their coded TBs,
-    // the wavefront's progress counters
+    // the ticket and per-CTB done flags of intra_kernel
     Arena<ohcu_iu> ius;      int n_iu = 0;
     Arena<ohcu_iu_index> iu_ctbs; int last_iu_ctb = -1;
     uint8_t *resid_base = nullptr; PlaneSet resid{};
@@ -415,7 +415,7 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
             TRYCU(cudaMalloc((void **)&j.resid_base, total));
             TRYCU(cudaMemset(j.resid_base, 0, total));
             for (int i = 0; i < c->nplanes; i++) j.resid.p[i] = j.resid_base + off[i];
-            TRYCU(cudaMalloc((void **)&j.progress_d, sizeof(int) * c->ctb_h));
+            TRYCU(cudaMalloc((void **)&j.progress_d, sizeof(int) * (c->nctb + 1)));     // ticket + one flag per CTB
         }
         // twice max_coeffs int16: the sparse form of a frame whose coefficients are all significant
         TRY(alloc_arena(&j.coeffs, 2 * (size_t)c->sp.max_coeffs));
@@ -1396,7 +1396,7 @@ extern "C" int ohcu_frame_launch_stages(ohcu_ctx *c, int job, int out_slot, int 
     if ((stages & 2) && j.n_pcm) LAUNCHED(launch_pcm(f, j.pcm_d, j.n_pcm, j.pcms_d, st));
     // the intra blocks, predicted from what has been reconstructed around them, with their residual (intra.cu)
     if ((stages & 2) && j.n_iu) {
-        CU(cudaMemsetAsync(j.progress_d, 0, sizeof(int) * c->ctb_h, st));
+        CU(cudaMemsetAsync(j.progress_d, 0, sizeof(int) * (c->nctb + 1), st));
         LAUNCHED(launch_intra(f, st));
     }
     STAGE_EVENT(2);

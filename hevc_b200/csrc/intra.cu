@@ -14,12 +14,11 @@
 
 namespace ohcu {
 
-enum { CAND_BL = 1, CAND_L = 2, CAND_UL = 4, CAND_U = 8, CAND_UR = 16 };
+enum { CAND_BL = 1, CAND_L = 2, CAND_UL = 4, CAND_U = 8, CAND_UR = 16 };      // bits 0..4: the order the reference walks the groups in
 
 struct IntraScratch {                 // per warp
     int16_t raw[2][66];               // [0] left, [1] top; index i + 1 holds sample i, index 0 the corner
     int16_t flt[2][66];               // smoothed copies
-    int16_t ref[100];                 // angular: ref[k + 32], k = -32 .. 2N
 };
 
 __constant__ int8_t c_intra_angle[33] = {32, 26, 21, 17, 13, 9, 5, 2, 0, -2, -5, -9, -13, -17, -21, -26, -32,
@@ -56,65 +55,64 @@ template <typename pixel> struct TileSurf {
 // cand: CAND_* final availability; filter_ok: !intra_smoothing_disabled && (c_idx == 0 || chroma_format_idc == 3);
 // strong: sps strong smoothing flag; res: the block's residual (first sample, pitch in int16) added to the prediction with
 // the clip of transform_add (hevcdsp_template.c:45-84), or nullptr.
-template <typename Surf>
-__device__ void intra_pred_tb(const Surf &sf, int tr_size, int bl_size, int log2_size, int c_idx, int mode, int cand,
-                              int filter_ok, int strong, int bd, IntraScratch &s, int lane, const int16_t *res = nullptr,
-                              int res_pitch = 0)
+// (one instance per block size: trip counts and index arithmetic fold at compile time)
+template <int log2_size, typename Surf>
+__device__ __noinline__ void intra_pred_size(const Surf &sf, int tr_size, int bl_size, int c_idx, int mode, int cand, int filter_ok,
+                                             int strong, int bd, IntraScratch &s, int lane, const int16_t *res, int res_pitch)
 {
-    const int n = 1 << log2_size, n2 = 2 * n;
+    constexpr int n = 1 << log2_size, n2 = 2 * n;
     const int maxv = (1 << bd) - 1;
     auto put = [&](int xx, int yy, int v) {
         if (res) v = min(max(v + (int)res[yy * res_pitch + xx], 0), maxv);
         sf.st(xx, yy, v);
     };
     int16_t *left = s.raw[0] + 1, *top = s.raw[1] + 1;
-    bool bl = cand & CAND_BL, lf = cand & CAND_L, ul = cand & CAND_UL, up = cand & CAND_U, ur = cand & CAND_UR;
 
-    // ---- what exists (:152-171); runs that leave the picture repeat their last sample
-    for (int i = lane; i < n2; i += 32) {
-        int t = 0, l = 0;
-        if (i < n) {
-            if (up) t = sf.ld(i, -1);
-            if (lf) l = sf.ld(-1, i);
+    // ---- reference samples with the substitution of unavailable ones folded into the fetch (:152-272).
+    // The reference walks from the bottom-left end up the left column, over the corner and along the top row: a group
+    // that is missing (BL, L, UL, U, UR = bits 0..4 of cand) repeats the last sample of the nearest available group before
+    // it, and the groups before the first available one repeat that group's first sample; nothing available: mid-grey.
+    // Every reference sample therefore IS one sample of the picture (or the constant): gw[g] says which, per group.
+    const int avail = cand & 31;
+    constexpr uint32_t OWN = 1u << 17, GREY = 1u << 16;
+    auto pack = [](int X, int Y) { return (uint32_t)(X + 1) | ((uint32_t)(Y + 1) << 8); };
+    uint32_t gw[5];
+#pragma unroll
+    for (int g = 0; g < 5; g++) {
+        const int lower = avail & ((1 << g) - 1);
+        uint32_t w;
+        if ((avail >> g) & 1) {
+            w = OWN;
+        } else if (lower) {                                // last sample (in walking order) of the nearest group before g
+            const int h = 31 - __clz(lower);
+            w = h == 0 ? pack(-1, n) : h == 1 ? pack(-1, 0) : h == 2 ? pack(-1, -1) : pack(n - 1, -1);
+        } else if (avail) {                                // first sample of the first available group
+            const int fg = __ffs(avail) - 1;
+            w = fg == 1 ? pack(-1, n - 1) : fg == 2 ? pack(-1, -1) : fg == 3 ? pack(0, -1) : pack(n, -1);
         } else {
-            if (ur) t = sf.ld(n + min(i - n, tr_size - 1), -1);
-            if (bl) l = sf.ld(-1, n + min(i - n, bl_size - 1));
+            w = GREY;
         }
-        top[i] = (int16_t)t;
-        left[i] = (int16_t)l;
+        gw[g] = w;
     }
-    int corner = ul ? sf.ld(-1, -1) : 0;
-    __syncwarp();
-    // ---- substitution (:245-272), warp-uniform decisions
-    if (!bl) {
-        if (lf) {
-            const int v = left[n - 1];
-            for (int i = n + lane; i < n2; i += 32) left[i] = (int16_t)v;
-        } else {
-            int v;
-            const bool any = ul || up || ur;
-            if (ul) v = corner;
-            else if (up) { v = top[0]; ul = true; }
-            else if (ur) { v = top[n]; up = ul = true; for (int i = lane; i < n; i += 32) top[i] = (int16_t)v; }
-            else { v = 1 << (bd - 1); for (int i = lane; i < n2; i += 32) top[i] = (int16_t)v; }
-            corner = v;
-            for (int i = lane; i < n2; i += 32) left[i] = (int16_t)v;
-            if (any) lf = true;
+    // side 0: left column (i = row), side 1: top row (i = column); i = -1: the corner; runs that leave the picture repeat
+    // their last sample (:109-112, :158, :168)
+    auto fetch = [&](int side, int i) -> int {
+        const int g = i < 0 ? 2 : (side ? (i < n ? 3 : 4) : (i < n ? 1 : 0));
+        const uint32_t w = g == 0 ? gw[0] : g == 1 ? gw[1] : g == 2 ? gw[2] : g == 3 ? gw[3] : gw[4];
+        int X = (int)(w & 255u) - 1, Y = (int)((w >> 8) & 255u) - 1;
+        if (w & OWN) {
+            const int j = i < n ? i : n + min(i - n, (side ? tr_size : bl_size) - 1);
+            X = side ? j : -1; Y = side ? -1 : j;
         }
-        __syncwarp();
+        int v = 1 << (bd - 1);
+        if (!(w & GREY)) v = sf.ld(X, Y);
+        return v;
+    };
+    for (int t = lane; t < 2 * n2; t += 32) {
+        const int side = t >= n2, i = t - (side ? n2 : 0);
+        s.raw[side][i + 1] = (int16_t)fetch(side, i);
     }
-    if (!lf) {
-        const int v = left[n];
-        for (int i = lane; i < n; i += 32) left[i] = (int16_t)v;
-        __syncwarp();
-    }
-    if (!ul) corner = left[0];
-    if (!up) for (int i = lane; i < n; i += 32) top[i] = (int16_t)corner;
-    if (!ur) {
-        __syncwarp();
-        const int v = top[n - 1];
-        for (int i = n + lane; i < n2; i += 32) top[i] = (int16_t)v;
-    }
+    const int corner = fetch(0, -1);
     if (lane == 0) left[-1] = top[-1] = (int16_t)corner;
     __syncwarp();
 
@@ -123,27 +121,20 @@ __device__ void intra_pred_tb(const Surf &sf, int tr_size, int bl_size, int log2
         const int dist = min(abs(mode - 26), abs(mode - 10));
         const int thresh = log2_size == 3 ? 7 : (log2_size == 4 ? 1 : 0);
         if (dist > thresh) {
-            int16_t *fl = s.flt[0] + 1, *ft = s.flt[1] + 1;
-            const bool bilinear = strong && c_idx == 0 && log2_size == 5 && abs(top[-1] + top[63] - 2 * top[31]) < (1 << (bd - 5)) &&
-                                  abs(left[-1] + left[63] - 2 * left[31]) < (1 << (bd - 5));
-            for (int i = lane - 1; i < n2; i += 32) {
-                int a, b;
-                if (bilinear) {
-                    a = (i < 0 || i == 63) ? left[i] : ((63 - i) * left[-1] + (i + 1) * left[63] + 32) >> 6;
-                    b = (i < 0 || i == 63) ? top[i] : ((63 - i) * top[-1] + (i + 1) * top[63] + 32) >> 6;
-                } else if (i < 0) {
-                    a = b = (left[0] + 2 * left[-1] + top[0] + 2) >> 2;
-                } else if (i == n2 - 1) {
-                    a = left[i]; b = top[i];
-                } else {
-                    a = (left[i + 1] + 2 * left[i] + left[i - 1] + 2) >> 2;
-                    b = (top[i + 1] + 2 * top[i] + top[i - 1] + 2) >> 2;
-                }
-                fl[i] = (int16_t)a;
-                ft[i] = (int16_t)b;
+            const bool bilinear = strong && c_idx == 0 && log2_size == 5 && abs(corner + top[63] - 2 * top[31]) < (1 << (bd - 5)) &&
+                                  abs(corner + left[63] - 2 * left[31]) < (1 << (bd - 5));
+            for (int t = lane; t < 2 * n2; t += 32) {
+                const int side = t >= n2, i = t - (side ? n2 : 0);
+                const int16_t *r = s.raw[side] + 1;
+                int v;
+                if (i == n2 - 1) v = r[i];
+                else if (bilinear) v = ((63 - i) * corner + (i + 1) * r[63] + 32) >> 6;
+                else v = (r[i + 1] + 2 * r[i] + r[i - 1] + 2) >> 2;
+                s.flt[side][i + 1] = (int16_t)v;
             }
+            if (lane == 0) s.flt[0][0] = s.flt[1][0] = (int16_t)(bilinear ? corner : (left[0] + 2 * corner + top[0] + 2) >> 2);
             __syncwarp();
-            left = fl; top = ft;
+            left = s.flt[0] + 1; top = s.flt[1] + 1;
         }
     }
 
@@ -156,7 +147,7 @@ __device__ void intra_pred_tb(const Surf &sf, int tr_size, int bl_size, int log2
         }
     } else if (mode == 1) {                                // DC, :388-417
         int sum = 0;
-        for (int i = lane; i < n; i += 32) sum += left[i] + top[i];
+        for (int t = lane; t < n2; t += 32) sum += t < n ? left[t] : top[t - n];
 #pragma unroll
         for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
         const int dc = (sum + n) >> (log2_size + 1);
@@ -174,46 +165,59 @@ __device__ void intra_pred_tb(const Surf &sf, int tr_size, int bl_size, int log2
         const int angle = c_intra_angle[mode - 2];
         const bool vertical = mode >= 18;
         const int16_t *mn = vertical ? top : left, *sd = vertical ? left : top;
-        int16_t *ref = s.ref + 32;
-        const int last = (n * angle) >> 5;
-        for (int k = lane; k <= n2; k += 32) ref[k] = mn[k - 1];
-        if (angle < 0 && last < -1) {
-            const int inv = c_intra_inv_angle[mode - 11];
-            for (int k = last + lane; k <= -1; k += 32) ref[k] = sd[-1 + ((k * inv + 128) >> 8)];
-        }
-        __syncwarp();
+        const int inv = angle < 0 ? c_intra_inv_angle[mode - 11] : 0;
+        const bool edge26 = edge && mode == 26, edge10 = edge && mode == 10;
+#pragma unroll
         for (int i = lane; i < n * n; i += 32) {
             const int xx = i & (n - 1), yy = i >> log2_size;
             const int a = vertical ? yy : xx, b = vertical ? xx : yy;
-            const int idx = ((a + 1) * angle) >> 5, fact = ((a + 1) * angle) & 31;
-            int v = fact ? ((32 - fact) * ref[b + idx + 1] + fact * ref[b + idx + 2] + 16) >> 5 : ref[b + idx + 1];
-            if (edge) {
-                if (mode == 26 && xx == 0) v = min(max(top[0] + ((left[yy] - left[-1]) >> 1), 0), maxv);
-                if (mode == 10 && yy == 0) v = min(max(left[0] + ((top[xx] - top[-1]) >> 1), 0), maxv);
-            }
+            const int pos = (a + 1) * angle, k = b + (pos >> 5) + 1, fact = pos & 31;
+            // ref[k] = main[k - 1] for k >= 0, and for the negative angles that reach below 0 the side array projected
+            // through the inverse angle (:440-447): taken straight from the two arrays
+            int v = k >= 0 ? mn[k - 1] : sd[-1 + ((k * inv + 128) >> 8)];
+            if (fact) v = ((32 - fact) * v + fact * (k + 1 >= 0 ? mn[k] : sd[-1 + (((k + 1) * inv + 128) >> 8)]) + 16) >> 5;
+            if (edge26 && xx == 0) v = min(max(top[0] + ((left[yy] - left[-1]) >> 1), 0), maxv);
+            if (edge10 && yy == 0) v = min(max(left[0] + ((top[xx] - top[-1]) >> 1), 0), maxv);
             put(xx, yy, v);
         }
     }
     __syncwarp();
 }
 
+template <typename Surf>
+__device__ __forceinline__ void intra_pred_tb(const Surf &sf, int tr_size, int bl_size, int log2_size, int c_idx, int mode, int cand,
+                                              int filter_ok, int strong, int bd, IntraScratch &s, int lane, const int16_t *res = nullptr,
+                                              int res_pitch = 0)
+{
+    switch (log2_size) {
+    case 2: intra_pred_size<2>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, res, res_pitch); break;
+    case 3: intra_pred_size<3>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, res, res_pitch); break;
+    case 4: intra_pred_size<4>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, res, res_pitch); break;
+    default: intra_pred_size<5>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, res, res_pitch); break;
+    }
+}
 
-// ================================================================= frame level: the CTB wavefront
+
+// ================================================================= frame level: CTBs in dependency order
 // hls_transform_unit predicts a block right before it adds the block's residual (hevcdec.c:1335-1526), in decoding
 // order; a block reads only samples of blocks decoded earlier: its own CTB, and the CTBs left, up-left, up and
 // up-right of it (the z-scan availability test, hevcpred_template.c:103-107).  Everything that is not intra has been
 // reconstructed by mc_kernel / residual_kernel / pcm_kernel before this kernel starts, and residual_kernel has left
 // the intra blocks' residuals in the job's residual planes.  What remains is the dependency between intra blocks:
-//   * one CTA per CTB row walks its CTBs left to right; before a CTB with intra blocks it waits until the row above
-//     has finished the CTB up-right of it (progress counter per row: CTBs finished) - the wavefront the reference's
-//     WPP threads run (hls_decode_entry_wpp, hevcdec.c:2966-3051);
-//   * the CTB's samples (with the row above and the column left of it) and its residuals are staged in shared memory by
-//     the whole CTA with 16-byte loads, so that the chain of blocks inside the CTB - each one reads what the one before
-//     wrote - never waits for global memory; predicted samples are written to the tile and through to the picture;
+//   * one CTA per CTB, CTBs handed out in raster order by a ticket (a CTA only ever waits for CTBs taken before its
+//     own, which are running or done).  A CTB without intra blocks leaves at once.  The others stage the CTB's samples
+//     and residuals in shared memory with 16-byte loads - all in flight together, and ahead of any wait - and look at
+//     their own records to see WHICH neighbour CTBs they read (a block on the CTB's left column with its left
+//     neighbour available, ...): only those, and only if they hold intra blocks themselves, are waited for (one flag
+//     per CTB, release / acquire).  Intra CTBs that do not touch each other run side by side; an all-intra picture
+//     degenerates to the wavefront the reference's WPP threads run (hls_decode_entry_wpp, hevcdec.c:2966-3051);
+//   * after the wait: the column left of the CTB and the row above it (with the corner and the top-right run), one
+//     more round trip; then the chain of blocks inside the CTB - each one reads what the one before wrote - runs
+//     out of shared memory, predicted samples written to the tile and through to the picture;
 //   * inside a CTB the three planes are independent: warp c takes plane c's blocks in list order.
-// A CTB without intra blocks costs a counter store.
 constexpr int INTRA_THREADS = 256;
 constexpr int INTRA_MAX_IU = 768;          // per CTB: 256 4x4 blocks in each of three planes
+enum { NEED_L = 1, NEED_UL = 2, NEED_U = 4, NEED_UR = 8 };
 
 __device__ __forceinline__ int ld_acquire(const int *p)
 {
@@ -221,29 +225,42 @@ __device__ __forceinline__ int ld_acquire(const int *p)
     asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+// The waiting thread sits in the CTA's LAST warp: warps 0..2 predict, and a warp's scheduler is its number modulo 4, so
+// the poll loops of the CTAs that share an SM with a working one never compete with its predicting warps for issue
+// slots (measured: with thread 0 polling every 20 ns, 89% of the kernel's executed instructions were poll loops).
+constexpr int INTRA_SPIN_TID = 224;
+__device__ __forceinline__ void spin_until_set(const int *flag)
+{
+    unsigned ns = 100;
+    while (!ld_acquire(flag)) {
+        __nanosleep(ns);
+        if (ns < 800) ns += ns;
+    }
+}
 __device__ __forceinline__ void st_release(int *p, int v)
 {
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-// eight samples of a picture row (16-byte / 8-byte load past the L1) widened into the tile
-template <typename pixel> __device__ __forceinline__ void load8(uint16_t *dst, const pixel *src)
+// eight samples of a picture row: a 16-byte / 8-byte load past the L1 into registers, widened into the tile later -
+// a thread issues ALL its loads of a CTB before the first store, so that they are in flight together
+template <typename pixel> __device__ __forceinline__ uint4 ld8(const pixel *src)
 {
-    if (sizeof(pixel) == 2) {
-        *(uint4 *)dst = __ldcg((const uint4 *)src);
-    } else {
-        const uint2 v = __ldcg((const uint2 *)src);
-        uint4 o;
-        o.x = __byte_perm(v.x, 0, 0x4140); o.y = __byte_perm(v.x, 0, 0x4342);
-        o.z = __byte_perm(v.y, 0, 0x4140); o.w = __byte_perm(v.y, 0, 0x4342);
-        *(uint4 *)dst = o;
-    }
+    if (sizeof(pixel) == 2) return __ldcg((const uint4 *)src);
+    const uint2 v = __ldcg((const uint2 *)src);
+    return make_uint4(v.x, v.y, 0, 0);
+}
+template <typename pixel> __device__ __forceinline__ void st8(uint16_t *dst, uint4 v)
+{
+    if (sizeof(pixel) == 1)
+        v = make_uint4(__byte_perm(v.x, 0, 0x4140), __byte_perm(v.x, 0, 0x4342), __byte_perm(v.y, 0, 0x4140), __byte_perm(v.y, 0, 0x4342));
+    *(uint4 *)dst = v;
 }
 
 struct IntraTile {                         // one plane's staging (pointers into dynamic shared memory)
     uint16_t *top, *body;
     int16_t *res;
-    int sw, sh, bpitch;                    // CTB size in samples of the plane, tile pitch
+    int sw, sh, bpitch, cshift;            // CTB size in samples of the plane, tile pitch, log2(chunks of 8 per row)
 };
 
 template <typename pixel>
@@ -252,92 +269,171 @@ __global__ void __launch_bounds__(INTRA_THREADS) intra_kernel(const __grid_const
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ IntraScratch scratch[3];
     __shared__ ohcu_iu s_iu[INTRA_MAX_IU];
+    __shared__ IntraTile tile[3];                          // (indexed by run-time plane numbers: not registers)
+    __shared__ int rows[3], oy[3];
+    __shared__ int s_ctb, s_need;
     if (f.err && *f.err) return;                           // malformed lists: every CTA leaves, nobody waits
-    const int row = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int S = 1 << f.log2_ctb;
-    // carve: per plane top (TILE_X0 + 2 sw), body (sh rows of sw + TILE_X0), residual (sh x sw); then the row's index
-    IntraTile tile[3];
-    size_t off = 0;
-    for (int c = 0; c < 3; c++) {
-        IntraTile &t = tile[c];
-        t.sw = S >> (c ? f.hs : 0); t.sh = S >> (c ? f.vs : 0); t.bpitch = t.sw + TILE_X0;
-        if (c >= f.nplanes) { t.top = t.body = nullptr; t.res = nullptr; continue; }
-        t.top = (uint16_t *)(smem + off);  off += (size_t)(TILE_X0 + 2 * t.sw) * 2;
-        t.body = (uint16_t *)(smem + off); off += (size_t)t.sh * t.bpitch * 2;
-        t.res = (int16_t *)(smem + off);   off += (size_t)t.sh * t.sw * 2;
-    }
-    uint2 *s_index = (uint2 *)(smem + off);
-    for (int i = tid; i < f.ctb_w; i += INTRA_THREADS) {
-        const ohcu_iu_index ix = f.iu_index[row * f.ctb_w + i];
-        s_index[i] = make_uint2(ix.first_iu, ix.n_iu);
-    }
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    int *const ticket = f.intra_progress, *const done = f.intra_progress + 1;
+    if (tid == 0) { s_ctb = atomicAdd(ticket, 1); s_need = 0; }
     __syncthreads();
-    int *const progress = f.intra_progress;
-    const int filter_luma = !f.intra_smoothing_disabled, filter_chroma = filter_luma && f.cfi == 3;
-    for (int cx = 0; cx < f.ctb_w; cx++) {
-        const uint2 ix = s_index[cx];
-        if (ix.y) {
-            // ---- what does not depend on the row above: records, residuals, the CTB's own rows, the column left of it
-            int cbf = 0;
-            for (uint32_t i = tid; i < ix.y; i += INTRA_THREADS) {
-                const ohcu_iu u = f.ius[ix.x + i];
-                s_iu[i] = u;
-                cbf |= u.cand & OHCU_IU_CBF;
-            }
-            if (row > 0 && tid == 0) {                     // meanwhile: the row above must have finished the CTB up-right
-                const int need = min(cx + 2, f.ctb_w);
-                while (ld_acquire(progress + row - 1) < need) __nanosleep(20);
-                __threadfence();
-            }
-            cbf = __syncthreads_or(cbf);
-            for (int c = 0; c < f.nplanes; c++) {
-                const IntraTile &t = tile[c];
-                const pixel *pl = (const pixel *)f.work.p[c];
-                const int pitch = f.work.pitch[c] / (int)sizeof(pixel), pw = f.pw[c], ph = f.ph[c];
-                const int ox = cx * t.sw, oy = row * t.sh, rows = min(t.sh, ph - oy), cpr = t.sw >> 3;   // chunks per row
-                for (int i = tid; i < rows * cpr; i += INTRA_THREADS) {
-                    const int y = i / cpr, k = i - y * cpr, x = ox + 8 * k;
-                    if (x < pw) load8<pixel>(t.body + y * t.bpitch + TILE_X0 + 8 * k, pl + (size_t)(oy + y) * pitch + x);
-                    if (cbf && x < pw)
-                        *(uint4 *)(t.res + y * t.sw + 8 * k) =
-                            __ldcg((const uint4 *)((const uint8_t *)f.resid[c] + (size_t)(oy + y) * f.resid_pitch[c]) + ((ox >> 3) + k));
-                }
-                if (ox > 0)
-                    for (int y = tid; y < rows; y += INTRA_THREADS)
-                        t.body[y * t.bpitch + TILE_X0 - 1] = __ldcg(pl + (size_t)(oy + y) * pitch + ox - 1);
-                // ---- the row above the CTB: corner, top, top-right (the wait above covers it)
-                if (oy > 0) {
-                    for (int k = tid; k < 2 * cpr; k += INTRA_THREADS)
-                        if (ox + 8 * k < pw) load8<pixel>(t.top + TILE_X0 + 8 * k, pl + (size_t)(oy - 1) * pitch + ox + 8 * k);
-                    if (ox > 0 && tid == INTRA_THREADS - 1) t.top[TILE_X0 - 1] = __ldcg(pl + (size_t)(oy - 1) * pitch + ox - 1);
-                }
-            }
-            __syncthreads();
-            if (warp < f.nplanes) {
-                const IntraTile &t = tile[warp];
-                pixel *plane = (pixel *)f.work.p[warp];
-                const int pitch = f.work.pitch[warp] / (int)sizeof(pixel), pw = f.pw[warp], ph = f.ph[warp];
-                const int ox = cx * t.sw, oy = row * t.sh;
-                TileSurf<pixel> sf;
-                sf.top = t.top; sf.body = t.body; sf.bpitch = t.bpitch; sf.pitch = pitch;
-                for (uint32_t i = 0; i < ix.y; i++) {
-                    const ohcu_iu u = s_iu[i];
-                    if (u.c_idx != warp) continue;
-                    const int n = 1 << u.log2_size;
-                    sf.bx = u.x0 - ox; sf.by = u.y0 - oy;
-                    sf.blk = plane + (size_t)u.y0 * pitch + u.x0;
-                    const int16_t *res = (u.cand & OHCU_IU_CBF) ? t.res + sf.by * t.sw + sf.bx : nullptr;
-                    intra_pred_tb(sf, max(0, min(u.x0 + 2 * n, pw) - (u.x0 + n)), max(0, min(u.y0 + 2 * n, ph) - (u.y0 + n)), u.log2_size,
-                                  warp, u.mode, u.cand & 31, warp ? filter_chroma : filter_luma, f.strong_intra_smoothing, f.bd,
-                                  scratch[warp], lane, res, t.sw);
-                }
-            }
-            __syncthreads();                               // every plane of the CTB is written
+    const int ctb = s_ctb, cx = ctb % f.ctb_w, row = ctb / f.ctb_w;
+    const ohcu_iu_index ixr = f.iu_index[ctb];
+    const uint2 ix = make_uint2(ixr.first_iu, ixr.n_iu);
+    if (!ix.y) return;                                     // (nobody waits for a CTB without intra blocks)
+    // which neighbour CTBs hold intra blocks (thread 0 waits for those this CTB reads)
+    int nb_intra = 0;
+    if (tid == INTRA_SPIN_TID) {
+        if (cx > 0) nb_intra |= f.iu_index[ctb - 1].n_iu ? NEED_L : 0;
+        if (row > 0) {
+            if (cx > 0) nb_intra |= f.iu_index[ctb - f.ctb_w - 1].n_iu ? NEED_UL : 0;
+            nb_intra |= f.iu_index[ctb - f.ctb_w].n_iu ? NEED_U : 0;
+            if (cx + 1 < f.ctb_w) nb_intra |= f.iu_index[ctb - f.ctb_w + 1].n_iu ? NEED_UR : 0;
+        }
+    }
+    const int S = 1 << f.log2_ctb;
+    // carve: per plane top (TILE_X0 + 2 sw), body (sh rows of sw + TILE_X0), residual (sh x sw)
+    size_t off = 0;
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        IntraTile t;
+        t.sw = S >> (c ? f.hs : 0); t.sh = S >> (c ? f.vs : 0); t.bpitch = t.sw + TILE_X0; t.cshift = 31 - __clz(t.sw) - 3;
+        t.top = t.body = nullptr; t.res = nullptr;
+        if (c < f.nplanes) {
+            t.top = (uint16_t *)(smem + off);  off += (size_t)(TILE_X0 + 2 * t.sw) * 2;
+            t.body = (uint16_t *)(smem + off); off += (size_t)t.sh * t.bpitch * 2;
+            t.res = (int16_t *)(smem + off);   off += (size_t)t.sh * t.sw * 2;
+        } else {
+            t.sh = 0;
         }
         if (tid == 0) {
-            __threadfence();
-            st_release(progress + row, cx + 1);
+            tile[c] = t;
+            oy[c] = row * t.sh;
+            rows[c] = c < f.nplanes ? min(t.sh, f.ph[c] - row * t.sh) : 0;
         }
+    }
+    __syncthreads();
+    const int filter_luma = !f.intra_smoothing_disabled, filter_chroma = filter_luma && f.cfi == 3;
+    const int nb0 = rows[0] << tile[0].cshift, nb1 = rows[1] << tile[1].cshift, nb2 = rows[2] << tile[2].cshift;
+    constexpr int KB = 6;                                  // body chunks per thread: 3 planes x 64 rows x 8 chunks / 256
+
+    // ---- loads that depend on no other intra CTB, all issued before the wait: records, the CTB's own rows, their residuals
+    uint2 rec[3];
+#pragma unroll
+    for (int q = 0; q < 3; q++) {
+        const uint32_t i = tid + q * INTRA_THREADS;
+        rec[q] = i < ix.y ? __ldg((const uint2 *)(f.ius + ix.x + i)) : make_uint2(0, 0);
+    }
+    uint4 va[KB], vb[KB];
+#pragma unroll
+    for (int q = 0; q < KB; q++) {
+        int i = tid + q * INTRA_THREADS;
+        const int c = i < nb0 ? 0 : (i < nb0 + nb1 ? 1 : 2);
+        i -= c == 0 ? 0 : (c == 1 ? nb0 : nb0 + nb1);
+        va[q] = vb[q] = make_uint4(0, 0, 0, 0);
+        if (i < (c == 2 ? nb2 : 1 << 30)) {
+            const IntraTile &t = tile[c];
+            const int y = i >> t.cshift, k = i & ((1 << t.cshift) - 1), x = cx * t.sw + 8 * k;
+            if (x < f.pw[c]) {
+                va[q] = ld8<pixel>((const pixel *)(f.work.p[c] + (size_t)(oy[c] + y) * f.work.pitch[c]) + x);
+                vb[q] = __ldcg((const uint4 *)((const uint8_t *)f.resid[c] + (size_t)(oy[c] + y) * f.resid_pitch[c]) + (x >> 3));
+            }
+        }
+    }
+    // ---- the records: into shared memory, and which neighbour CTBs their blocks read
+    int need = 0;
+#pragma unroll
+    for (int q = 0; q < 3; q++) {
+        const uint32_t i = tid + q * INTRA_THREADS;
+        if (i < ix.y) {
+            *(uint2 *)&s_iu[i] = rec[q];
+            const ohcu_iu u = s_iu[i];
+            const IntraTile &t = tile[u.c_idx];
+            const int n = 1 << u.log2_size, bx = u.x0 & (t.sw - 1), by = u.y0 & (t.sh - 1);
+            if (bx == 0) {
+                if (u.cand & (CAND_L | CAND_BL)) need |= NEED_L;
+                if (u.cand & CAND_UL) need |= by ? NEED_L : NEED_UL;
+            }
+            if (by == 0) {
+                if ((u.cand & CAND_U) || (bx && (u.cand & CAND_UL))) need |= NEED_U;
+                if (u.cand & CAND_UR) need |= (bx + n < t.sw ? NEED_U : 0) | (bx + 2 * n > t.sw ? NEED_UR : 0);
+            }
+        }
+    }
+    need = __reduce_or_sync(0xffffffffu, need);
+    if (lane == 0 && need) atomicOr(&s_need, need);
+#pragma unroll
+    for (int q = 0; q < KB; q++) {
+        int i = tid + q * INTRA_THREADS;
+        const int c = i < nb0 ? 0 : (i < nb0 + nb1 ? 1 : 2);
+        i -= c == 0 ? 0 : (c == 1 ? nb0 : nb0 + nb1);
+        if (i < (c == 2 ? nb2 : 1 << 30)) {
+            const IntraTile &t = tile[c];
+            const int y = i >> t.cshift, k = i & ((1 << t.cshift) - 1);
+            st8<pixel>(t.body + y * t.bpitch + TILE_X0 + 8 * k, va[q]);
+            *(uint4 *)(t.res + y * t.sw + 8 * k) = vb[q];
+        }
+    }
+    __syncthreads();
+    // ---- wait for the neighbour CTBs this one reads intra samples of
+    if (tid == INTRA_SPIN_TID) {
+        const int w = s_need & nb_intra;
+        if (w) {
+            if (w & NEED_L) spin_until_set(done + ctb - 1);
+            if (w & NEED_UL) spin_until_set(done + ctb - f.ctb_w - 1);
+            if (w & NEED_U) spin_until_set(done + ctb - f.ctb_w);
+            if (w & NEED_UR) spin_until_set(done + ctb - f.ctb_w + 1);
+            __threadfence();
+        }
+    }
+    __syncthreads();
+    // ---- the column left of the CTB, the row above it: corner, top, top-right
+    {
+        int i = tid;
+        const int c = i < rows[0] ? 0 : (i < rows[0] + rows[1] ? 1 : 2);
+        i -= c == 0 ? 0 : (c == 1 ? rows[0] : rows[0] + rows[1]);
+        if (cx > 0 && i < rows[c])
+            tile[c].body[i * tile[c].bpitch + TILE_X0 - 1] =
+                (uint16_t)__ldcg((const pixel *)(f.work.p[c] + (size_t)(oy[c] + i) * f.work.pitch[c]) + cx * tile[c].sw - 1);
+    }
+    if (row > 0 && warp >= 5) {                            // warps 5, 6, 7: one plane each
+        const int c = warp - 5;
+        if (c < f.nplanes) {
+            const IntraTile &t = tile[c];
+            const pixel *above = (const pixel *)(f.work.p[c] + (size_t)(oy[c] - 1) * f.work.pitch[c]) + cx * t.sw;
+            const int nk = 2 << t.cshift;                  // <= 16 chunks
+            uint4 v = make_uint4(0, 0, 0, 0);
+            int corner = 0;
+            if (lane < nk && cx * t.sw + 8 * lane < f.pw[c]) v = ld8<pixel>(above + 8 * lane);
+            if (lane == 31 && cx > 0) corner = __ldcg(above - 1);
+            if (lane < nk) st8<pixel>(t.top + TILE_X0 + 8 * lane, v);
+            if (lane == 31) t.top[TILE_X0 - 1] = (uint16_t)corner;
+        }
+    }
+    __syncthreads();
+    if (warp < f.nplanes) {
+        const IntraTile &t = tile[warp];
+        pixel *plane = (pixel *)f.work.p[warp];
+        const int pitch = f.work.pitch[warp] / (int)sizeof(pixel), pw = f.pw[warp], ph = f.ph[warp];
+        const int ox = cx * t.sw;
+        TileSurf<pixel> sf;
+        sf.top = t.top; sf.body = t.body; sf.bpitch = t.bpitch; sf.pitch = pitch;
+        for (uint32_t i = 0; i < ix.y; i++) {
+            const ohcu_iu u = s_iu[i];
+            if (u.c_idx != warp) continue;
+            const int n = 1 << u.log2_size;
+            sf.bx = u.x0 - ox; sf.by = u.y0 - oy[warp];
+            sf.blk = plane + (size_t)u.y0 * pitch + u.x0;
+            const int16_t *res = (u.cand & OHCU_IU_CBF) ? t.res + sf.by * t.sw + sf.bx : nullptr;
+            intra_pred_tb(sf, max(0, min(u.x0 + 2 * n, pw) - (u.x0 + n)), max(0, min(u.y0 + 2 * n, ph) - (u.y0 + n)), u.log2_size,
+                          warp, u.mode, u.cand & 31, warp ? filter_chroma : filter_luma, f.strong_intra_smoothing, f.bd,
+                          scratch[warp], lane, res, t.sw);
+        }
+    }
+    __syncthreads();                                       // every plane of the CTB is written
+    if (tid == 0) {
+        __threadfence();
+        st_release(done + ctb, 1);
     }
 }
 
@@ -349,13 +445,13 @@ static size_t intra_smem_bytes(const FrameDev &f)
         const int sw = S >> (c ? f.hs : 0), sh = S >> (c ? f.vs : 0);
         b += (size_t)(TILE_X0 + 2 * sw) * 2 + (size_t)sh * (sw + TILE_X0) * 2 + (size_t)sh * sw * 2;
     }
-    return b + sizeof(uint2) * f.ctb_w;
+    return b;
 }
 
 int intra_set_attrs()
 {
-    // three 64x64 planes of samples and residuals, the row index of a 16384-wide picture with 16x16 CTBs
-    const int bytes = 80 * 1024;
+    // three 64x64 planes of samples and residuals
+    const int bytes = 64 * 1024;
     if (cudaFuncSetAttribute(intra_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess ||
         cudaFuncSetAttribute(intra_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess)
         return -1;
@@ -367,9 +463,9 @@ int launch_intra(const FrameDev &f, cudaStream_t st)
     if (f.n_iu <= 0) return 0;
     if (!f.ius || !f.iu_index || !f.intra_progress || !f.resid[0]) return -1;
     const size_t smem = intra_smem_bytes(f);
-    if (smem > 80 * 1024) return -1;
-    if (f.bd > 8) intra_kernel<uint16_t><<<f.ctb_h, INTRA_THREADS, smem, st>>>(f);
-    else          intra_kernel<uint8_t><<<f.ctb_h, INTRA_THREADS, smem, st>>>(f);
+    if (smem > 64 * 1024) return -1;
+    if (f.bd > 8) intra_kernel<uint16_t><<<f.ctb_w * f.ctb_h, INTRA_THREADS, smem, st>>>(f);
+    else          intra_kernel<uint8_t><<<f.ctb_w * f.ctb_h, INTRA_THREADS, smem, st>>>(f);
     return 1;
 }
 

@@ -62,7 +62,7 @@ struct FrameDev {
     const ohcu_sao *sao;
     const uint16_t *sao_ctb_flags;   // per CTB, see SAOF_* below
     // intra blocks (intra.cu): records in decoding order, where each CTB's sit, the residual planes residual_kernel
-    // leaves the OHCU_TUF_INTRA blocks in (int16, pitch in bytes), one progress counter per CTB row
+    // leaves the OHCU_TUF_INTRA blocks in (int16, pitch in bytes), a ticket followed by one done flag per CTB
     const ohcu_iu *ius;
     const ohcu_iu_index *iu_index;
     int n_iu;
