@@ -187,13 +187,14 @@ static int emit_tb(gen *g, int c_idx, int x, int y, int log2, int bypass, int cr
             c[i] = (int16_t)(rnd_pct(&g->r, 2) ? rnd_range(&g->r, -32768, 32767) : rnd_laplace(&g->r, 300));
     } else if (p->dense_coeffs) {
         /* hazard 1: dense block, arbitrary col_limit (exercises the zero-skip masks) */
-        tu.mode = (c_idx == 0 && log2 == 2 && rnd_pct(&g->r, p->dst_pct)) ? OHCU_TU_DST4 : OHCU_TU_IDCT;
+        tu.mode = (c_idx == 0 && log2 == 2 && (g->intra || rnd_pct(&g->r, p->dst_pct))) ? OHCU_TU_DST4 : OHCU_TU_IDCT;
         tu.col_limit = (int8_t)rnd_range(&g->r, 1, n + 8);
         c = push_tu(g, &tu);
         for (int i = 0; i < n * n; i++)
             c[i] = (int16_t)(rnd_pct(&g->r, 3) ? rnd_range(&g->r, -32768, 32767) : rnd_laplace(&g->r, 400));
     } else {
-        int lx, ly, last_rank, dst4 = c_idx == 0 && log2 == 2 && rnd_pct(&g->r, p->dst_pct);
+        /* 4x4 luma blocks of intra CUs always take the DST (hevc_cabac.c:1790); dst_pct spreads it over inter CUs too */
+        int lx, ly, last_rank, dst4 = c_idx == 0 && log2 == 2 && (g->intra || rnd_pct(&g->r, p->dst_pct));
         if (rnd_pct(&g->r, p->dc_pct)) {
             lx = ly = 0;
         } else {

@@ -77,7 +77,7 @@ static void emit_tu(glue_state *st, const oh_frame_job *job, const ohcu_tu *tu)
     tr->scan_ctx.last_significant_coeff_x = lx;
     tr->scan_ctx.last_significant_coeff_y = ly;
     lc->cu.cu_transquant_bypass_flag = tu->mode == OHCU_TU_BYPASS;
-    lc->cu.pred_mode = (tu->mode == OHCU_TU_DST4 || (tu->flags & OHCU_TUF_ROTATE)) ? MODE_INTRA : MODE_INTER;
+    lc->cu.pred_mode = (tu->mode == OHCU_TU_DST4 || (tu->flags & (OHCU_TUF_ROTATE | OHCU_TUF_INTRA))) ? MODE_INTRA : MODE_INTER;
     st->sps.transform_skip_rotation_enabled_flag = !!(tu->flags & OHCU_TUF_ROTATE);
     tr->transform_skip_flag = tu->mode == OHCU_TU_SKIP;
     tr->explicit_rdpcm_flag = !!(tu->flags & OHCU_TUF_RDPCM);
@@ -87,6 +87,85 @@ static void emit_tu(glue_state *st, const oh_frame_job *job, const ohcu_tu *tu)
     lc->tu.res_scale_val = tu->res_scale_val;
     if (c) ff_hevc_hls_transform_c(s, lc, tu->x0 << st->sps.hshift[c], tu->y0 << st->sps.vshift[c], c, 3);
     else ff_hevc_hls_transform(s, lc, tu->x0, tu->y0, 3);
+}
+
+/* one intra block through the PATCHED intra_pred (hevcpred_template.c -> ff_ohcu_emit_iu).  The record carries the five
+ * final availability flags; lc->na takes them and the z-scan table makes the block the last one in decoding order, so
+ * that the flags the reference derives (:103-107) - the ones the patch hands to the glue - are the record's. */
+static void emit_iu(glue_state *st, const ohcu_iu *iu, int *zs, int tw, int mask)
+{
+    HEVCContext *s = &st->s;
+    HEVCLocalContext *lc = &st->lc;
+    const int c = iu->c_idx, x0 = iu->x0 << st->sps.hshift[c], y0 = iu->y0 << st->sps.vshift[c];
+    int *cell = &zs[tw + 1 + ((y0 >> 2) & mask) * tw + ((x0 >> 2) & mask)];
+    *cell = 1 << 20;
+    lc->cu.pred_mode = MODE_INTRA;
+    lc->tu.intra_pred_mode = lc->tu.intra_pred_mode_c = iu->mode;
+    lc->na.cand_bottom_left = !!(iu->cand & OHCU_CAND_BOTTOM_LEFT);
+    lc->na.cand_left = !!(iu->cand & OHCU_CAND_LEFT);
+    lc->na.cand_up_left = !!(iu->cand & OHCU_CAND_UP_LEFT);
+    lc->na.cand_up = !!(iu->cand & OHCU_CAND_UP);
+    lc->na.cand_up_right = !!(iu->cand & OHCU_CAND_UP_RIGHT);
+    s->hpc.intra_pred[iu->log2_size - 2](s, x0, y0, c);
+    *cell = -1;
+}
+
+/* The coded blocks and intra blocks of the picture in an order a decoder could produce: CTB after CTB; inside a CTB every
+ * intra block followed by its own coded block (hls_transform_unit predicts, then adds the residual), then the CTB's other
+ * coded blocks. */
+static void emit_blocks(glue_state *st, const oh_frame_job *job)
+{
+    const ohcu_seq_params *sp = &job->sp;
+    HEVCSPS *sps = &st->sps;
+    HEVCPPS *pps = &st->pps;
+    const int l2 = sp->log2_ctb_size, mask = (1 << (l2 - 2)) - 1, tw = mask + 2, nplanes = sp->chroma_format_idc ? 3 : 1;
+    const int nctb = sps->ctb_width * sps->ctb_height;
+    int *zs = malloc(sizeof(int) * tw * tw), cw[3];
+    int32_t *map[3] = { NULL, NULL, NULL };
+    int *tu_first = zalloc(sizeof(int) * (nctb + 1)), *iu_first = zalloc(sizeof(int) * (nctb + 1));
+    int *tu_order = zalloc(sizeof(int) * (job->n_tu + 1)), *iu_order = zalloc(sizeof(int) * (job->n_iu + 1));
+    uint8_t *tu_done = zalloc(job->n_tu + 1);
+#define CTB_OF(r) (((((r)->x0 << sps->hshift[(r)->c_idx]) >> l2)) + ((((r)->y0 << sps->vshift[(r)->c_idx]) >> l2)) * sps->ctb_width)
+    for (int i = 0; i < tw * tw; i++) zs[i] = -1;
+    sps->log2_min_tb_size = 2;
+    sps->tb_mask = mask;
+    pps->min_tb_addr_zs_tab = zs;
+    pps->min_tb_addr_zs = &zs[tw + 1];
+    ff_hevc_pred_init(&st->s.hpc, sp->bit_depth);
+    for (int c = 0; c < nplanes; c++) {
+        cw[c] = ((sp->width >> sps->hshift[c]) + 3) >> 2;
+        map[c] = zalloc(sizeof(int32_t) * cw[c] * (((sp->height >> sps->vshift[c]) + 3) >> 2));
+    }
+    /* counting sort of both lists by CTB (stable: list order inside a CTB) */
+    for (int i = 0; i < job->n_tu; i++) tu_first[CTB_OF(&job->tus[i]) + 1]++;
+    for (int i = 0; i < job->n_iu; i++) iu_first[CTB_OF(&job->ius[i]) + 1]++;
+    for (int k = 0; k < nctb; k++) { tu_first[k + 1] += tu_first[k]; iu_first[k + 1] += iu_first[k]; }
+    {
+        int *tc = zalloc(sizeof(int) * nctb), *ic = zalloc(sizeof(int) * nctb);
+        for (int i = 0; i < job->n_tu; i++) { const int k = CTB_OF(&job->tus[i]); tu_order[tu_first[k] + tc[k]++] = i; }
+        for (int i = 0; i < job->n_iu; i++) { const int k = CTB_OF(&job->ius[i]); iu_order[iu_first[k] + ic[k]++] = i; }
+        free(tc); free(ic);
+    }
+    for (int i = 0; i < job->n_tu; i++) {
+        const ohcu_tu *tu = &job->tus[i];
+        if (tu->flags & OHCU_TUF_INTRA) map[tu->c_idx][(tu->y0 >> 2) * cw[tu->c_idx] + (tu->x0 >> 2)] = i + 1;
+    }
+    for (int k = 0; k < nctb; k++) {
+        for (int q = iu_first[k]; q < iu_first[k + 1]; q++) {
+            const ohcu_iu *iu = &job->ius[iu_order[q]];
+            emit_iu(st, iu, zs, tw, mask);
+            if (iu->cand & OHCU_IU_CBF) {
+                const int t = map[iu->c_idx][(iu->y0 >> 2) * cw[iu->c_idx] + (iu->x0 >> 2)];
+                if (t) { emit_tu(st, job, &job->tus[t - 1]); tu_done[t - 1] = 1; }
+            }
+        }
+        for (int q = tu_first[k]; q < tu_first[k + 1]; q++)
+            if (!tu_done[tu_order[q]]) emit_tu(st, job, &job->tus[tu_order[q]]);
+    }
+#undef CTB_OF
+    for (int c = 0; c < 3; c++) free(map[c]);
+    free(zs); free(tu_first); free(iu_first); free(tu_order); free(iu_order); free(tu_done);
+    pps->min_tb_addr_zs_tab = NULL; pps->min_tb_addr_zs = NULL;
 }
 
 int ohglue_replay_frame(const oh_frame_job *job, int device)
@@ -118,6 +197,8 @@ int ohglue_replay_frame(const oh_frame_job *job, int device)
     sps->hshift[1] = sps->hshift[2] = (sp->chroma_format_idc == 1 || sp->chroma_format_idc == 2);
     sps->vshift[1] = sps->vshift[2] = (sp->chroma_format_idc == 1);
     sps->sao_enabled_flag = sp->sao_enabled && job->sao;
+    sps->intra_smoothing_disabled_flag = sp->intra_smoothing_disabled;
+    sps->sps_strong_intra_smoothing_enable_flag = sp->strong_intra_smoothing;
     pps->transquant_bypass_enable_flag = !!sp->pcm_or_bypass;
     pps->pps_cb_qp_offset = sp->cb_qp_offset;
     pps->pps_cr_qp_offset = sp->cr_qp_offset;
@@ -166,7 +247,7 @@ int ohglue_replay_frame(const oh_frame_job *job, int device)
         mvf.pred_flag = pu->pred_flag;
         ff_ohcu_emit_pu(s, pu->x0, pu->y0, pu->w, pu->h, &mvf);
     }
-    for (int i = 0; i < job->n_tu; i++) emit_tu(st, job, &job->tus[i]);
+    emit_blocks(st, job);
 
     /* the arrays the CPU loop filters would read (pic_arrays_init, hevcdec.c:114-200) */
     {

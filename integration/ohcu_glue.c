@@ -39,6 +39,10 @@ int ff_ohcu_set_sps(HEVCContext *s, const HEVCSPS *sps)
     sp.dpb_slots = FF_ARRAY_ELEMS(s->DPB);
     sp.jobs = 4;
     sp.sao_enabled = sps->sao_enabled_flag;
+    /* intra blocks on the device: the depths ff_hevc_pred_init has predictors for (hevcpred.c:62-76) */
+    sp.intra = g->intra_ok = sp.bit_depth <= 12;
+    sp.intra_smoothing_disabled = sps->intra_smoothing_disabled_flag;
+    sp.strong_intra_smoothing = sps->sps_strong_intra_smoothing_enable_flag;
     if (pps) {                                            /* initial values; every picture sets its own (ff_ohcu_frame_start) */
         sp.pcm_or_bypass = (sps->pcm_enabled_flag && sps->pcm.loop_filter_disable_flag) || pps->transquant_bypass_enable_flag;
         sp.cb_qp_offset = pps->pps_cb_qp_offset;
@@ -61,8 +65,8 @@ int ff_ohcu_frame_start(HEVCContext *s)
     g->active = 0;
     g->failed = 0;
     if (!g->ctx) return 0;
-    /* pictures with intra CUs stay on the CPU path for now (see ohcu_glue.h) */
-    if (s->sh.slice_type == HEVC_SLICE_I) return 0;
+    /* I pictures the device cannot predict stay on the CPU path (see ohcu_glue.h) */
+    if (s->sh.slice_type == HEVC_SLICE_I && (!g->intra_ok || pps->constrained_intra_pred_flag)) return 0;
     g->out_slot = (int)(s->ref - s->DPB);
     g->job = ohcu_frame_begin(g->ctx, g->out_slot, s->poc);
     if (g->job < 0) { glue_fail(s, g->job, "ohcu_frame_begin"); return g->job; }
@@ -80,6 +84,7 @@ int ff_ohcu_frame_start(HEVCContext *s)
     g->cur_ctb = -1;
     g->ctb_coef_base = 0;
     g->last_luma_tu = -1;
+    g->last_iu[0] = g->last_iu[1] = g->last_iu[2] = -1;
     g->active = 1;
     return 0;
 }
@@ -93,7 +98,7 @@ void ff_ohcu_slice_start(HEVCContext *s)
     const RefPicList *rpl = s->ref->refPicList[s->slice_idx];     /* as hls_prediction_unit takes it, hevcdec.c:2130 */
     ohcu_slice_tab *t;
     if (!g->active) return;
-    if (sh->slice_type == HEVC_SLICE_I) { glue_fail(s, OHCU_EINVAL, "intra slice inside a device picture"); return; }
+    if (sh->slice_type == HEVC_SLICE_I && !g->intra_ok) { glue_fail(s, OHCU_EINVAL, "intra slice inside a device picture"); return; }
     if (s->slice_idx >= OHCU_MAX_SLICES) { glue_fail(s, OHCU_EOVERFLOW, "slice table"); return; }
     g->cur_slice = s->slice_idx;
     if (g->cur_slice + 1 > g->n.n_slices) g->n.n_slices = g->cur_slice + 1;
@@ -157,6 +162,80 @@ void ff_ohcu_emit_pu(HEVCContext *s, int x0, int y0, int nPbW, int nPbH, const M
 /* replaces the tail of ff_hevc_hls_transform / ff_hevc_hls_transform_c (hevc_cabac.c:1727-1818, :1843-1905): which
  * inverse transform the block takes is decided exactly as there, the coefficients (lc->tu.coeffs, hevcdec.h:333) go
  * out as (position, level) pairs */
+/* A coded block of an intra CU: intra_pred has just emitted the block's ohcu_iu (hls_transform_unit predicts, then
+ * adds the residual, hevcdec.c:1335-1526).  The record learns that a residual follows, the TB that it waits for the
+ * prediction. */
+static void glue_mark_intra(HEVCContext *s, const HEVCLocalContext *lc, ohcu_tu *tu)
+{
+    OHCUGlue *g = G(s);
+    ohcu_iu *u;
+    if (lc->cu.pred_mode != MODE_INTRA || g->last_iu[tu->c_idx] < 0) return;
+    u = &g->a.ius[g->last_iu[tu->c_idx]];
+    if (u->x0 != tu->x0 || u->y0 != tu->y0 || u->log2_size != tu->log2_size) return;
+    u->cand |= OHCU_IU_CBF;
+    tu->flags |= OHCU_TUF_INTRA;
+}
+
+/* intra_pred (hevcpred_template.c:30-345), called by hls_transform_unit for every TB of an intra CU: after it has
+ * derived cand_bottom_left .. cand_up_right (:103-107) the patched function hands the block over and returns.
+ * x0, y0: luma coordinates, as intra_pred takes them.  Returns 1 when the block is the device's. */
+int ff_ohcu_emit_iu(HEVCContext *s, int x0, int y0, int log2_size, int c_idx, int mode, int cand)
+{
+    OHCUGlue *g = G(s);
+    const HEVCSPS *sps = s->ps.sps;
+    ohcu_iu_index *ix;
+    ohcu_iu *u;
+    if (!g->active) return 0;
+    if (g->failed) return 1;
+    if (!g->a.ius || s->ps.pps->constrained_intra_pred_flag) { glue_fail(s, OHCU_EINVAL, "intra CU the device cannot predict"); return 1; }
+    if (g->n.n_iu >= g->a.max_ius) { glue_fail(s, OHCU_EOVERFLOW, "intra block list"); return 1; }
+    glue_ctb(s, x0, y0);
+    ix = &g->a.iu_ctbs[g->cur_ctb];
+    if (!ix->n_iu) ix->first_iu = g->n.n_iu;
+    ix->n_iu++;
+    u = &g->a.ius[g->n.n_iu];
+    u->x0 = (uint16_t)(x0 >> sps->hshift[c_idx]);
+    u->y0 = (uint16_t)(y0 >> sps->vshift[c_idx]);
+    u->c_idx = (uint8_t)c_idx;
+    u->log2_size = (uint8_t)log2_size;
+    u->mode = (uint8_t)mode;
+    u->cand = (uint8_t)(cand & 31);
+    g->last_iu[c_idx] = g->n.n_iu;
+    g->n.n_iu++;
+    return 1;
+}
+
+/* hls_transform_unit, hevcdec.c:1430-1445 / :1460-1475: a chroma block without coded coefficients in a TU with
+ * cross-component prediction still receives (res_scale_val * coeffs_y) >> 3: a record with no coefficients of its own */
+void ff_ohcu_emit_cross(HEVCContext *s, HEVCLocalContext *lc, int x0, int y0, int c_idx, int log2_size)
+{
+    OHCUGlue *g = G(s);
+    const HEVCSPS *sps = s->ps.sps;
+    const int n = 1 << log2_size;
+    ohcu_ctb_index *ix;
+    ohcu_tu *tu;
+    if (!g->active || g->failed) return;
+    if (g->n.n_tu >= g->a.max_tus) { glue_fail(s, OHCU_EOVERFLOW, "TU list"); return; }
+    if (g->last_luma_tu < 0 || g->last_luma_x != x0 || g->last_luma_y != y0) { glue_fail(s, OHCU_EINVAL, "cross-component block without its luma block"); return; }
+    ix = glue_ctb(s, x0, y0);
+    if (!ix->n_tu) { ix->first_tu = g->n.n_tu; ix->first_coef = (uint32_t)g->n.n_coef; }
+    ix->n_tu++;
+    tu = &g->a.tus[g->n.n_tu];
+    memset(tu, 0, sizeof(*tu));
+    tu->x0 = (uint16_t)(x0 >> sps->hshift[c_idx]);
+    tu->y0 = (uint16_t)(y0 >> sps->vshift[c_idx]);
+    tu->c_idx = (uint8_t)c_idx;
+    tu->log2_size = (uint8_t)log2_size;
+    tu->mode = OHCU_TU_BYPASS;                       /* zero coefficients, used as they are */
+    tu->flags = OHCU_TUF_CROSS;
+    tu->res_scale_val = (int8_t)lc->tu.res_scale_val;
+    tu->cross_tu = (uint32_t)g->last_luma_tu;
+    glue_mark_intra(s, lc, tu);
+    tu->coeff_off = g->ctb_coef_base;
+    g->ctb_coef_base += (uint32_t)(n * n);
+    g->n.n_tu++;
+}
+
 void ff_ohcu_emit_tu(HEVCContext *s, HEVCLocalContext *lc, int x0, int y0, int c_idx)
 {
     OHCUGlue *g = G(s);
@@ -215,6 +294,7 @@ void ff_ohcu_emit_tu(HEVCContext *s, HEVCLocalContext *lc, int x0, int y0, int c
         tu->cross_tu = (uint32_t)g->last_luma_tu;
     }
     if (!c_idx) { g->last_luma_tu = g->n.n_tu; g->last_luma_x = x0; g->last_luma_y = y0; }
+    glue_mark_intra(s, lc, tu);
     /* the significant coefficients of the block, positions inside the CTB's coefficient area */
     pairs = g->a.coefs + g->n.n_coef;
     for (int i = 0; i < n * n; i++)

@@ -18,8 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GLUE_SO = os.path.join(ROOT, "integration", "_build", "libohglue.so")
 GOLDEN = os.path.join(ROOT, "tests", "golden", "frames.json")
 # dense_coeffs_*: coefficients beyond col_limit, which no parser produces (the glue derives col_limit from the block)
-# intra_*: the patch set does not emit ohcu_iu records yet (the intra_pred call sites of hls_transform_unit)
-CASES = [n for n in frame_cases.FRAME_CASES if not n.startswith("dense_coeffs") and not n.startswith("intra_")]
+CASES = [n for n in frame_cases.FRAME_CASES if not n.startswith("dense_coeffs")]
 
 
 def _replay(lib, job, refs, out_init):
@@ -45,6 +44,8 @@ def _replay(lib, job, refs, out_init):
     for c in range(nplanes):
         fj.out.data[c] = out[c].ctypes.data; fj.out.stride[c] = out[c].strides[0]
     fj.stages = 0
+    if len(job.ius):
+        fj.n_iu = len(job.ius); fj.ius = job.ius.ctypes.data
     rc = lib.ohglue_replay_frame(C.byref(fj), 0)
     assert rc == 0, f"ohglue_replay_frame -> {rc}"
     return out
