@@ -77,6 +77,9 @@ def frames_per_rank(workload, world):
     return D, F
 
 
+INTRA_PCT, INTRA_GOP = 0, 0          # --intra-pct / --gop: share of intra CUs in every frame, every GOP-th frame all intra
+
+
 def make_inputs(workload, rank, world=1, distinct=None):
     """The synthetic frames of this rank (frame i of the job -> rank i mod world) and the 16 reference pictures.
     Frame d predicts from reference pair d mod 8 (DPB slots 2p, 2p + 1): 8 frames in flight read 16 different
@@ -87,7 +90,10 @@ def make_inputs(workload, rank, world=1, distinct=None):
     mine = shard.frames_of_rank(D * world, rank, world)
     jobs = []
     for d, i in enumerate(mine):
-        fj = synth.make_job(w, h, bd, cf, seed=shard.seed_of_frame(3000, i), **kw)
+        ikw = {}
+        if INTRA_PCT or INTRA_GOP:
+            ikw = dict(sp_intra=1, intra_pct=100 if (INTRA_GOP and i % INTRA_GOP == 0) else INTRA_PCT)
+        fj = synth.make_job(w, h, bd, cf, seed=shard.seed_of_frame(3000, i), **kw, **ikw)
         pair = d % N_REF_PAIRS
         for l in range(2):
             for r in range(16):
@@ -417,8 +423,9 @@ def run_ours(args, rank, world):
         "scaling": "strong" if args.workload == "8k" else "weak",
         "vs_baseline": None, "dtype": "int32 accumulate on u16 samples / int16 coefficients" if sp.bit_depth > 8
         else "int32 accumulate on u8 samples / int16 coefficients", "data": "synthetic",
-        "config": {"workload": WORKLOAD_NAMES[args.workload], "frames_per_step_per_gpu": F,
-                   "frames_in_flight": min(J, RING), "frames_in_flight_e2e": RING, "distinct_frames_per_gpu": len(jobs),
+        "config": {"workload": WORKLOAD_NAMES[args.workload] + (f", {INTRA_PCT}% intra CUs" if INTRA_PCT else "") +
+                               (f", every {INTRA_GOP}th picture all intra" if INTRA_GOP else ""),
+                   "frames_per_step_per_gpu": F, "frames_in_flight": min(J, RING), "frames_in_flight_e2e": RING, "distinct_frames_per_gpu": len(jobs),
                    "reference_pictures": len(refs), "sharding": "independent frames per GPU, no collective",
                    "l2": f"inputs larger than L2: {len(jobs)} distinct list sets, {len(refs)} reference pictures + {RING} output slots "
                          f"of {ab['S'] / 1e6:.0f} MB, ~{ab['pipeline'] / 1e6:.0f} MB algorithmic traffic per frame",
@@ -519,9 +526,13 @@ def main():
     ap.add_argument("--copy-out", choices=["2d", "pitch", "packed"], default="2d",
                     help="e2e leg, device -> host: pitched 2-D copies into tight planes (2d), linear copies into planes with "
                          "the device pitch (pitch), or ohcu_slot_output_cropped: pack kernel + one linear copy (packed)")
+    ap.add_argument("--intra-pct", type=int, default=0, help="share of intra-predicted CUs in every frame (default 0: the headline workload)")
+    ap.add_argument("--gop", type=int, default=0, help="every GOP-th frame of the job is all intra (an I picture); 0 = none")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-check", action="store_true")
     args = ap.parse_args()
+    global INTRA_PCT, INTRA_GOP
+    INTRA_PCT, INTRA_GOP = args.intra_pct, args.gop
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     if args.impl == "reference":

@@ -150,6 +150,7 @@ struct ohcu_ctx {
     void *l2_buf = nullptr;
     size_t l2_bytes = 0;
     uint8_t *md5_d = nullptr;         // 48 bytes per slot (ohcu_slot_md5)
+    int *intra_order_d = nullptr;     // CTB addresses in wavefront order (intra_kernel)
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     // Frame threads each drive their own job; the lists of a job are touched by one thread
     // at a time (caller's contract).  What jobs share — the job ring, the slots' ordering
@@ -305,6 +306,7 @@ extern "C" int ohcu_destroy(ohcu_ctx *c)
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->l2_buf) cudaFree(c->l2_buf);
     if (c->md5_d) cudaFree(c->md5_d);
+    if (c->intra_order_d) cudaFree(c->intra_order_d);
     if (c->t0) cudaEventDestroy(c->t0);
     if (c->t1) cudaEventDestroy(c->t1);
     delete c;
@@ -450,6 +452,18 @@ extern "C" int ohcu_create(ohcu_ctx **out, int device, const ohcu_seq_params *sp
                 memset(j.tab_h, 0, off);
             }
         }
+    }
+    if (c->sp.intra) {
+        // intra_kernel takes CTBs along anti-diagonals x + 2 y: every CTB a block can read (left, up-left, up, up-right)
+        // lies on an earlier one, and a limited number of CTAs then covers whole wavefronts instead of a few CTB rows
+        std::vector<int> order;
+        order.reserve(c->nctb);
+        for (int d = 0; d <= c->ctb_w - 1 + 2 * (c->ctb_h - 1); d++)
+            for (int y = std::max(0, (d - (c->ctb_w - 1) + 1) / 2); y <= std::min(c->ctb_h - 1, d / 2); y++)
+                order.push_back(y * c->ctb_w + d - 2 * y);
+        if ((int)order.size() != c->nctb) { ohcu_destroy(c); return fail(OHCU_ECUDA, "internal: wavefront order"); }
+        TRYCU(cudaMalloc((void **)&c->intra_order_d, sizeof(int) * c->nctb));
+        TRYCU(cudaMemcpy(c->intra_order_d, order.data(), sizeof(int) * c->nctb, cudaMemcpyHostToDevice));
     }
     TRYCU(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     c->copy_lanes[0] = c->copy_stream;
@@ -1320,7 +1334,7 @@ static void fill_frame_dev(const ohcu_ctx *c, const Job &j, FrameDev *f)
     f->pcm_or_bypass = j.pp.pcm_or_bypass; f->cb_qp_offset = j.pp.cb_qp_offset; f->cr_qp_offset = j.pp.cr_qp_offset;
     f->ius = j.ius.d; f->iu_index = j.iu_ctbs.d; f->n_iu = j.n_iu;
     for (int i = 0; i < 3; i++) { f->resid[i] = (int16_t *)j.resid.p[i]; f->resid_pitch[i] = j.resid.pitch[i]; }
-    f->intra_progress = j.progress_d;
+    f->intra_progress = j.progress_d; f->intra_order = c->intra_order_d;
     f->intra_smoothing_disabled = c->sp.intra_smoothing_disabled; f->strong_intra_smoothing = c->sp.strong_intra_smoothing;
     f->err = j.err_d;
 }

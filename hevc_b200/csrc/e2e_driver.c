@@ -76,9 +76,14 @@ static int fill_inplace(run_state *st, int job, const ohdrv_frame *f, int copy, 
         memcpy(a.tus, f->tus, (size_t)f->n_tu * sizeof(ohcu_tu));
         if (f->coef_form == OHCU_COEF_LEVELS) memcpy(a.quant, f->quant, (size_t)f->n_tu * sizeof(ohcu_tu_quant));
         memcpy(a.coefs, f->coefs, (size_t)f->n_coef * (f->coef_form >= OHCU_COEF_SPARSE ? sizeof(ohcu_coef) : sizeof(int16_t)));
+        if (f->n_iu) memcpy(a.ius, f->ius, (size_t)f->n_iu * sizeof(ohcu_iu));
     }
     /* the small tables are written every frame in both modes */
     memcpy(a.ctbs, f->ctbs, (size_t)st->nctb * sizeof(ohcu_ctb_index));
+    if (f->n_iu) {
+        if (!a.ius) return OHCU_ESTATE;
+        memcpy(a.iu_ctbs, f->iu_ctbs, (size_t)st->nctb * sizeof(ohcu_iu_index));
+    }
     memcpy(a.slices, f->slices, (size_t)f->n_slices * sizeof(ohcu_slice_tab));
     if (slot_a >= 0)                                   /* chain mode: this picture predicts from the two previous ones */
         for (int s = 0; s < f->n_slices; s++)
@@ -103,7 +108,7 @@ static int fill_inplace(run_state *st, int job, const ohdrv_frame *f, int copy, 
     }
     if (f->has_sao) memcpy(a.sao, f->sao, (size_t)st->nctb * sizeof(ohcu_sao));
     n.n_pu = f->n_pu; n.n_tu = f->n_tu; n.n_coef = f->n_coef; n.n_slices = f->n_slices; n.coef_form = f->n_tu ? f->coef_form : 0;
-    n.deblock = f->deblock; n.sao = f->has_sao; n.all_inter = f->all_inter;
+    n.deblock = f->deblock; n.sao = f->has_sao; n.all_inter = f->all_inter; n.n_iu = f->n_iu;
     return ohcu_frame_commit_lists(st->ctx, job, &n);
 }
 
@@ -114,6 +119,7 @@ static int fill_append(run_state *st, int job, const ohdrv_frame *f)
     for (int s = 0; s < f->n_slices; s++)
         if ((rc = ohcu_set_slice(st->ctx, job, s, &f->slices[s]))) return rc;
     if ((rc = ohcu_append_pu(st->ctx, job, f->pus, (int)f->n_pu))) return rc;
+    if (f->n_iu && (rc = ohcu_append_iu(st->ctx, job, f->ius, (int)f->n_iu))) return rc;
     if (f->n_tu) {
         if (f->coef_form == OHCU_COEF_LEVELS) {
             if (f->scaling_list &&

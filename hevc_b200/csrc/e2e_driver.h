@@ -51,7 +51,9 @@ typedef struct ohdrv_frame {
     const int32_t *tsa, *tile;
     const uint8_t *scaling_list;    /* 1548 bytes or NULL                                                      */
     int32_t all_inter;
-    int32_t pad;
+    uint32_t n_iu;                  /* intra blocks (the context needs ohcu_seq_params.intra)                  */
+    const ohcu_iu *ius;
+    const ohcu_iu_index *iu_ctbs;   /* per CTB                                                                 */
 } ohdrv_frame;
 
 typedef struct ohdrv_config {

@@ -10,6 +10,8 @@
 // lane and step.  A block depends on the reconstructed samples left of and above it, so the frame-level kernel
 // (intra_kernel below) walks the CTBs as a wavefront, with the CTB's samples and residuals staged in shared memory;
 // the per-entry shim tests the block function 1:1 against the reference table.
+#include <algorithm>
+
 #include "ohcu_internal.h"
 
 namespace ohcu {
@@ -204,8 +206,9 @@ __device__ __forceinline__ void intra_pred_tb(const Surf &sf, int tr_size, int b
 // up-right of it (the z-scan availability test, hevcpred_template.c:103-107).  Everything that is not intra has been
 // reconstructed by mc_kernel / residual_kernel / pcm_kernel before this kernel starts, and residual_kernel has left
 // the intra blocks' residuals in the job's residual planes.  What remains is the dependency between intra blocks:
-//   * one CTA per CTB, CTBs handed out in raster order by a ticket (a CTA only ever waits for CTBs taken before its
-//     own, which are running or done).  A CTB without intra blocks leaves at once.  The others stage the CTB's samples
+//   * a CTA takes one CTB at a time, CTBs handed out along the anti-diagonals x + 2 y by a ticket (everything a CTB can
+//     read lies on an earlier diagonal: a CTA only ever waits for CTBs taken before its own, which are running or done);
+//     CTBs without intra blocks are passed over.  It stages the CTB's samples
 //     and residuals in shared memory with 16-byte loads - all in flight together, and ahead of any wait - and look at
 //     their own records to see WHICH neighbour CTBs they read (a block on the CTB's left column with its left
 //     neighbour available, ...): only those, and only if they hold intra blocks themselves, are waited for (one flag
@@ -275,12 +278,22 @@ __global__ void __launch_bounds__(INTRA_THREADS) intra_kernel(const __grid_const
     if (f.err && *f.err) return;                           // malformed lists: every CTA leaves, nobody waits
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     int *const ticket = f.intra_progress, *const done = f.intra_progress + 1;
-    if (tid == 0) { s_ctb = atomicAdd(ticket, 1); s_need = 0; }
+    const int nctb = f.ctb_w * f.ctb_h;
+  for (;;) {                                               // persistent: at most one CTA per SM, the rest of the GPU stays free for the other frames in flight
+    __syncthreads();                                       // the previous CTB is finished with the shared state
+    if (tid == 0) {
+        int c;
+        do {                                               // (nobody waits for a CTB without intra blocks)
+            c = atomicAdd(ticket, 1);
+            c = c < nctb ? f.intra_order[c] : nctb;
+        } while (c < nctb && !f.iu_index[c].n_iu);
+        s_ctb = c; s_need = 0;
+    }
     __syncthreads();
     const int ctb = s_ctb, cx = ctb % f.ctb_w, row = ctb / f.ctb_w;
+    if (ctb >= nctb) return;
     const ohcu_iu_index ixr = f.iu_index[ctb];
     const uint2 ix = make_uint2(ixr.first_iu, ixr.n_iu);
-    if (!ix.y) return;                                     // (nobody waits for a CTB without intra blocks)
     // which neighbour CTBs hold intra blocks (thread 0 waits for those this CTB reads)
     int nb_intra = 0;
     if (tid == INTRA_SPIN_TID) {
@@ -435,6 +448,7 @@ __global__ void __launch_bounds__(INTRA_THREADS) intra_kernel(const __grid_const
         __threadfence();
         st_release(done + ctb, 1);
     }
+  }
 }
 
 static size_t intra_smem_bytes(const FrameDev &f)
@@ -461,11 +475,21 @@ int intra_set_attrs()
 int launch_intra(const FrameDev &f, cudaStream_t st)
 {
     if (f.n_iu <= 0) return 0;
-    if (!f.ius || !f.iu_index || !f.intra_progress || !f.resid[0]) return -1;
+    if (!f.ius || !f.iu_index || !f.intra_progress || !f.intra_order || !f.resid[0]) return -1;
     const size_t smem = intra_smem_bytes(f);
     if (smem > 64 * 1024) return -1;
-    if (f.bd > 8) intra_kernel<uint16_t><<<f.ctb_w * f.ctb_h, INTRA_THREADS, smem, st>>>(f);
-    else          intra_kernel<uint8_t><<<f.ctb_w * f.ctb_h, INTRA_THREADS, smem, st>>>(f);
+    // the wavefront of an all-intra picture is at most min(ctb_h, ctb_w / 2) + 1 CTBs wide; pictures with scattered intra
+    // CTBs use every CTA.  One CTA per SM at most: spinning CTAs must not take the registers of the other frames' kernels
+    // (with one CTA per CTB, 444 resident CTAs of an I picture held 94 % of the register files: 8 frames in flight
+    // with one I picture among them ran at 564 frame/s)
+    static int sm_count[64];                               // per device, looked up once
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return -1;
+    if (!sm_count[dev] && cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
+    const int sms = sm_count[dev];
+    const int grid = std::min(f.ctb_w * f.ctb_h, sms);
+    if (f.bd > 8) intra_kernel<uint16_t><<<grid, INTRA_THREADS, smem, st>>>(f);
+    else          intra_kernel<uint8_t><<<grid, INTRA_THREADS, smem, st>>>(f);
     return 1;
 }
 

@@ -69,6 +69,7 @@ struct FrameDev {
     int16_t *resid[3];
     int resid_pitch[3];
     int *intra_progress;
+    const int *intra_order;          // CTBs in wavefront order (x + 2 y ascending): the order the tickets hand them out in
     int intra_smoothing_disabled, strong_intra_smoothing;
     // the job's error word (prepare.cu): non-zero = the lists are malformed, every kernel of the frame returns at once
     const int *err;

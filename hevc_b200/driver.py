@@ -7,7 +7,7 @@ import os
 import numpy as np
 
 from . import abi
-from .sparse import ctb_index, to_levels, to_sparse
+from .sparse import ctb_index, iu_index, to_levels, to_sparse
 
 # beside the libohcu.so in use (OHCU_LIB selects another build for A/B runs; its driver copy resolves it through $ORIGIN)
 DRV_PATH = os.path.join(os.path.dirname(os.path.abspath(abi.LIB_PATH)), "libohcu_drv.so")
@@ -23,7 +23,8 @@ class Frame(C.Structure):
         ("slices", C.c_void_p), ("ctbs", C.c_void_p), ("deblock", C.c_int32), ("has_sao", C.c_int32),
         ("vbs", C.c_void_p), ("hbs", C.c_void_p), ("qp", C.c_void_p), ("db", C.c_void_p), ("is_pcm", C.c_void_p),
         ("sao", C.c_void_p), ("fse", C.c_void_p), ("tsa", C.c_void_p), ("tile", C.c_void_p),
-        ("scaling_list", C.c_void_p), ("all_inter", C.c_int32), ("pad", C.c_int32),
+        ("scaling_list", C.c_void_p), ("all_inter", C.c_int32), ("n_iu", C.c_uint32),
+        ("ius", C.c_void_p), ("iu_ctbs", C.c_void_p),
     ]
 
 
@@ -97,6 +98,11 @@ class Frames:
                 arrays["scaling_list"] = sl
             if sp.pcm_or_bypass:
                 arrays["is_pcm"] = fj.is_pcm
+            ius = getattr(fj, "ius", None)
+            if ius is not None and len(ius):
+                arrays["ius"] = ius
+                arrays["iu_ctbs"] = iu_index(ius, sp.log2_ctb_size, hs, vs, ctb_w, nctb)
+                f.n_iu = len(ius)
             for name, a in arrays.items():
                 a = np.ascontiguousarray(a)
                 self.keep.append(a)
@@ -108,7 +114,8 @@ class Frames:
             # bytes that cross the bus per frame (what stage uploads)
             up = fj.pus.nbytes + recs.nbytes + pairs.nbytes + fj.slices.nbytes + idx.nbytes + 3 * 8 * nctb + \
                 fj.qp_y_tab.nbytes + fj.deblock.nbytes + fj.sao.nbytes + 10 * nctb + \
-                (0 if derive_bs else fj.vbs.nbytes + fj.hbs.nbytes) + (quant.nbytes if quant is not None else 0)
+                (0 if derive_bs else fj.vbs.nbytes + fj.hbs.nbytes) + (quant.nbytes if quant is not None else 0) + \
+                (ius.nbytes + 8 * nctb if f.n_iu else 0)
             self.h2d_bytes.append(int(up))
 
 
