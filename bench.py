@@ -58,8 +58,8 @@ FIRST_OUT = 2 * N_REF_PAIRS
 RING = 16             # output slots FIRST_OUT..31 in rotation (e2e leg), pinned output pictures
 # dram__bytes_read.sum + dram__bytes_write.sum of one mc_kernel launch, from the committed
 # `ncu --set full` capture of this same command (never measured inside a timed run)
-NCU_TRAFFIC = {"4k": 59145984}
-NCU_TRAFFIC_SOURCE = "profiles/r01_v13_ncu_kernels.txt (53.62 MB read + 5.53 MB write; the reference pictures and part of the written prediction stay in L2)"
+NCU_TRAFFIC = {"4k": 59612928}
+NCU_TRAFFIC_SOURCE = "profiles/r02_final_ncu_kernels.txt (53.85 MB read + 5.76 MB write; the reference pictures and part of the written prediction stay in L2)"
 
 
 def peaks():
