@@ -267,6 +267,29 @@ def cpu_reference(jobs, refs, steps, warmup, max_threads=None, all_arms=False):
     return out
 
 
+def bind_to_gpu_numa(device):
+    """Best effort: run this rank's threads (and first-touch its pinned staging) on the NUMA node its GPU hangs off.
+    Returns the node, or None when the topology cannot be read."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(device)
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= set(os.sched_getaffinity(0))
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except Exception:
+        return None
+
+
 # ------------------------------------------------------------------ our arm
 def run_ours(args, rank, world):
     from concurrent.futures import ThreadPoolExecutor
@@ -282,6 +305,8 @@ def run_ours(args, rank, world):
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
     # frame threads of the e2e leg: the host's cores are shared by the ranks of the node
     threads = args.host_threads or max(1, min(8, cores // max(1, world)))
+    # several ranks on one node: each one's threads and pinned buffers on the NUMA node of its GPU (--no-numa: as scheduled)
+    numa_node = bind_to_gpu_numa(device) if (world > 1 and not args.no_numa) else None
     # resident leg: J staged jobs (8k: every frame of the rank's share of the 64), launched round-robin
     J = min(D, 64) if args.workload == "8k" else B
     njobs = max(J, RING, threads)
@@ -440,7 +465,7 @@ def run_ours(args, rank, world):
         "e2e": {"value": round(e2e_value, 1), "unit": "Mpixel/s", "h2d_bytes_per_step": int(h2d * F),
                 "d2h_bytes_per_step": int(d2h * F), "frames_per_s": round(total_frames / (ms_e2e * 1e-3), 1),
                 "timed_region_ms": round(ms_e2e, 1), "host_ms_per_step": round(host_ms / args.steps, 3),
-                "host_cpu_ms_per_frame": round(cpu_ms / max(1, r_e2e.frames), 4), "host_threads": threads,
+                "host_cpu_ms_per_frame": round(cpu_ms / max(1, r_e2e.frames), 4), "host_threads": threads, "numa_node": numa_node,
                 "driver": "hevc_b200/csrc/e2e_driver.c: C frame threads; " + {
                     "inplace": "the frame's lists sit in the job's pinned arenas where the parser wrote them (ohcu_frame_arenas_get / "
                                "ohcu_frame_commit_lists), per frame the small tables are written, everything is uploaded and validated on the device",
@@ -528,6 +553,7 @@ def main():
                          "the device pitch (pitch), or ohcu_slot_output_cropped: pack kernel + one linear copy (packed)")
     ap.add_argument("--intra-pct", type=int, default=0, help="share of intra-predicted CUs in every frame (default 0: the headline workload)")
     ap.add_argument("--gop", type=int, default=0, help="every GOP-th frame of the job is all intra (an I picture); 0 = none")
+    ap.add_argument("--no-numa", action="store_true", help="N > 1: do not bind each rank to the NUMA node of its GPU")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-check", action="store_true")
     args = ap.parse_args()
