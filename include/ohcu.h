@@ -501,7 +501,7 @@ int ohcu_set_sao(ohcu_ctx *ctx, int job, const ohcu_sao_in *in);
 
 /* End of frame (where ff_hevc_hls_filter ran per CTB, hevc_filter.c:1211-1245):
  * upload the job's lists (async, pinned) and enqueue the batched launches
- *   [prepare (in-place lists)] -> mc_kernel -> residual_kernel -> [pcm] ->
+ *   [prepare (in-place lists)] -> mc_kernel -> residual_kernel -> [pcm] -> [intra_kernel] ->
  *   loopfilter_kernel (deblock + SAO fused) -> pad_kernel (halo fill)
  * on the job's stream ([bs_kernel] beside the first two on a side stream when the boundary
  * strengths are derived).  Returns without waiting.                              */
@@ -598,11 +598,11 @@ int ohcu_dsp_transform_add(int bd, uint8_t *dst, const int16_t *coeffs, ptrdiff_
 int ohcu_dsp_idct_noalloc(int bd, int16_t *coeffs, int log2_size, int col_limit, int nblocks);
 /*  HEVCPredContext.intra_pred[log2_size - 2](s, x0, y0, c_idx)  hevcpred.h:30-41, hevcpred_template.c:30-345 and the
  *  predictors it dispatches to (pred_planar :359, pred_dc :388, pred_angular :419): one N x N block of a plane predicted
- *  IN PLACE from the reconstructed samples left of and above it (first step: the block function and
- *  its table semantics; the frame-level wavefront kernel follows).  plane = sample (0, 0) of the plane (host), stride in
+ *  IN PLACE from the reconstructed samples left of and above it (the block function with its table
+ *  semantics; pictures go through ohcu_iu records and intra_kernel).  plane = sample (0, 0) of the plane (host), stride in
  *  bytes, pw x ph its size in samples, (x, y) the block in plane samples, mode 0 planar, 1 DC, 2..34 angular.
  *  cand = the five final availability flags the reference computes at hevcpred_template.c:103-107 (lc->na.cand_* combined
- *  with the z-scan order test).  filter_ok = !sps->intra_smoothing_disabled_flag && (c_idx == 0 || chroma_format_idc == 3),
+ *  with the z-scan order test), OHCU_CAND_*.  filter_ok = !sps->intra_smoothing_disabled_flag && (c_idx == 0 || chroma_format_idc == 3),
  *  strong = sps->sps_strong_intra_smoothing_enable_flag.  constrained_intra_pred_flag must be 0.                       */
 int ohcu_dsp_intra_pred(int bd, uint8_t *plane, ptrdiff_t stride, int pw, int ph, int x, int y, int log2_size, int c_idx,
                         int mode, int cand, int filter_ok, int strong);
