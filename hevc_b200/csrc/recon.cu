@@ -124,6 +124,14 @@ __device__ __forceinline__ int dp2hi(uint32_t a, uint32_t b, int c) { return __d
 
 // NT-tap FIR along a row: W[j] holds samples 2j (low half) and 2j+1;
 // out[i] = sum_k tap[k] * sample[i + k], i = 0..OW-1
+// four unsigned bytes x four signed bytes + c
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c)
+{
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
 template <int NT, int OW>
 __device__ __forceinline__ void fir_row(const uint32_t (&W)[(OW + NT) / 2], uint32_t F0, uint32_t F1, int (&out)[OW])
 {
@@ -778,22 +786,26 @@ __device__ __forceinline__ void mc_filter(const uint8_t *win, int pitch, int col
             for (int j = 0; j < NW; j++) T[j] = odd ? U[j + 1] : U[j];
 #pragma unroll
             for (int j = 0; j < NW; j++) W[j] = __funnelshift_r(T[j], T[j + 1 < NW ? j + 1 : j], sh);
+        }
+        int o[OW];
+        if (HIGH) {
+            fir_row<NT, OW>(W, FX0, FX1, o);
         } else {
+            // 8-bit samples stay packed four to a word: one dp4a (u8 x s8) per four taps instead of two dp2a on widened pairs
             constexpr int NB = (NW + 1) / 2 + 1;
             const uint32_t *p = (const uint32_t *)rowp + (col0 >> 2);
             const int sh = (col0 & 3) * 8;
-            uint32_t T[NB];
+            uint32_t T[NB], A[NB - 1];
 #pragma unroll
             for (int j = 0; j < NB; j++) T[j] = __ldg(p + j);
 #pragma unroll
-            for (int j = 0; j < NB - 1; j++) {
-                const uint32_t v = __funnelshift_r(T[j], T[j + 1], sh);
-                W[2 * j] = __byte_perm(v, 0, 0x4140);
-                if (2 * j + 1 < NW) W[2 * j + 1] = __byte_perm(v, 0, 0x4342);
+            for (int j = 0; j < NB - 1; j++) A[j] = __funnelshift_r(T[j], T[j + 1], sh);
+#pragma unroll
+            for (int k = 0; k < OW; k++) {
+                o[k] = dp4a_us(k ? __funnelshift_r(A[0], A[1], 8 * k) : A[0], FX0, 0);
+                if (NT == 8) o[k] = dp4a_us(k ? __funnelshift_r(A[1], A[2 < NB - 1 ? 2 : 0], 8 * k) : A[1], FX1, o[k]);
             }
         }
-        int o[OW];
-        fir_row<NT, OW>(W, FX0, FX1, o);
 #pragma unroll
         for (int k = 0; k < OW / 2; k++)
             hb[r][k] = __byte_perm((uint32_t)(o[2 * k] >> sh1), (uint32_t)(o[2 * k + 1] >> sh1), 0x5410);

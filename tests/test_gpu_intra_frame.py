@@ -181,3 +181,50 @@ def test_intra_residual_stage_alone_on_a_given_picture(oracle):
         got = ctx.reconstruct(job, refs, out_init=refs[-1], stages=2)
     want = oracle.replay(job, refs, out_init=refs[-1], stages=2)
     assert _diff(got, want) is None, _diff(got, want)
+
+
+def test_intra_blocks_read_pcm_neighbours(oracle):
+    """PCM CUs are placed after the inter reconstruction and BEFORE the intra blocks (hls_pcm_sample runs in decoding order,
+    hevcdec.c:1686-1721; its samples are what an intra block next to it predicts from).  Square 2Nx2N inter CUs of a picture
+    with intra CUs become PCM; expected picture: oracle replay in the same four steps."""
+    import copy
+    job = synth.make_job(256, 192, 10, 1, seed=93, intra_pct=50, sp_pcm_or_bypass=1)
+    refs = [synth.make_picture(job.sp, 930 + s) for s in range(job.sp.dpb_slots)]
+    rng = np.random.default_rng(6)
+    sq = np.flatnonzero((job.pus["w"] == job.pus["h"]) & (job.pus["w"] >= 8) & (job.pus["w"] <= 32))
+    picks = [int(i) for i in sq[rng.choice(len(sq), size=min(12, len(sq)), replace=False)]]
+    # 1. everything that is not intra
+    inter = copy.copy(job)
+    inter.ius = job.ius[:0]
+    pic = oracle.replay(inter, refs, out_init=refs[-1], stages=3)
+    # 2. the PCM samples
+    pcm = np.zeros((job.sp.height >> 2, job.sp.width >> 2), np.uint8)
+    recs = []
+    for i in picks:
+        x0, y0, n = int(job.pus["x0"][i]), int(job.pus["y0"][i]), int(job.pus["w"][i])
+        l2 = n.bit_length() - 1
+        for c in range(3):
+            s = 1 if c else 0
+            blk = (rng.integers(0, 256, size=(n >> s, n >> s)) << 2).astype(np.uint16)
+            pic[c][y0 >> s:(y0 >> s) + (n >> s), x0 >> s:(x0 >> s) + (n >> s)] = blk
+            recs.append((x0 >> s, y0 >> s, l2 - s, c, np.ascontiguousarray(blk)))
+        pcm[y0 >> 2:(y0 + n) >> 2, x0 >> 2:(x0 + n) >> 2] = 1
+    # 3. the intra blocks with their residuals, 4. the loop filters
+    intra = copy.copy(job)
+    intra.tus = np.ascontiguousarray(job.tus[(job.tus["flags"] & abi.TUF_INTRA) != 0])
+    pic = oracle.replay(intra, refs, out_init=pic, stages=2)
+    job.is_pcm = pcm.reshape(-1).copy()
+    want = oracle.replay(job, refs, out_init=pic, stages=12)
+    with backend.Context(job.sp) as ctx:
+        out_slot = job.sp.dpb_slots - 1
+        for i, r in enumerate(refs[:-1]):
+            ctx.upload(i, r)
+        ctx.upload(out_slot, refs[-1])
+        j = ctx.begin(out_slot)
+        ctx.append(j, job, sparse=True)
+        for x, y, l2, c, blk in recs:
+            abi.check(ctx.lib.ohcu_append_pcm(ctx.handle, j, x, y, l2, c, blk.ctypes.data))
+        ctx.flush(j)
+        ctx.sync(j)
+        got = ctx.download(out_slot)
+    assert _diff(got, want) is None, _diff(got, want)
