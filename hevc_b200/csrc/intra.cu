@@ -53,6 +53,125 @@ template <typename pixel> struct TileSurf {
     }
 };
 
+// ---- reference samples with the substitution of unavailable ones folded into the fetch (:152-272).
+// The reference walks from the bottom-left end up the left column, over the corner and along the top row: a group
+// that is missing (BL, L, UL, U, UR = bits 0..4 of cand) repeats the last sample of the nearest available group before
+// it, and the groups before the first available one repeat that group's first sample; nothing available: mid-grey.
+// Every reference sample therefore IS one sample of the picture (or the constant): gw[g] says which, per group.
+constexpr uint32_t REF_OWN = 1u << 17, REF_GREY = 1u << 16;
+template <int n>
+__device__ __forceinline__ void ref_sources(int avail, uint32_t (&gw)[5])
+{
+    auto pack = [](int X, int Y) { return (uint32_t)(X + 1) | ((uint32_t)(Y + 1) << 8); };
+#pragma unroll
+    for (int g = 0; g < 5; g++) {
+        const int lower = avail & ((1 << g) - 1);
+        uint32_t w;
+        if ((avail >> g) & 1) {
+            w = REF_OWN;
+        } else if (lower) {                                // last sample (in walking order) of the nearest group before g
+            const int h = 31 - __clz(lower);
+            w = h == 0 ? pack(-1, n) : h == 1 ? pack(-1, 0) : h == 2 ? pack(-1, -1) : pack(n - 1, -1);
+        } else if (avail) {                                // first sample of the first available group
+            const int fg = __ffs(avail) - 1;
+            w = fg == 1 ? pack(-1, n - 1) : fg == 2 ? pack(-1, -1) : fg == 3 ? pack(0, -1) : pack(n, -1);
+        } else {
+            w = REF_GREY;
+        }
+        gw[g] = w;
+    }
+}
+// side 0: left column (i = row), side 1: top row (i = column); i = -1: the corner; runs that leave the picture repeat
+// their last sample (:109-112, :158, :168)
+template <int n, typename Surf>
+__device__ __forceinline__ int ref_fetch(const Surf &sf, const uint32_t (&gw)[5], int side, int i, int tr_size, int bl_size, int bd)
+{
+    const int g = i < 0 ? 2 : (side ? (i < n ? 3 : 4) : (i < n ? 1 : 0));
+    const uint32_t w = g == 0 ? gw[0] : g == 1 ? gw[1] : g == 2 ? gw[2] : g == 3 ? gw[3] : gw[4];
+    int X = (int)(w & 255u) - 1, Y = (int)((w >> 8) & 255u) - 1;
+    if (w & REF_OWN) {
+        const int j = i < n ? i : n + min(i - n, (side ? tr_size : bl_size) - 1);
+        X = side ? j : -1; Y = side ? -1 : j;
+    }
+    int v = 1 << (bd - 1);
+    if (!(w & REF_GREY)) v = sf.ld(X, Y);
+    return v;
+}
+
+// ---- 4x4 and 8x8 blocks: the 4N reference samples live in ONE register across the warp (lanes 0..15 the left column,
+// lanes 16..31 the top row, the corner in every lane), smoothing and the predictors read them with shuffles: no scratch
+// array, no warp barrier, a third of the dependent instructions of the general path.  These are most of a picture's blocks.
+template <int log2_size, typename Surf>
+__device__ __noinline__ void intra_pred_small(const Surf &sf, int tr_size, int bl_size, int c_idx, int mode, int cand, int filter_ok,
+                                              int bd, int lane, const int16_t *res, int res_pitch)
+{
+    constexpr int n = 1 << log2_size, n2 = 2 * n;
+    constexpr unsigned FULL = 0xffffffffu;
+    static_assert(n2 <= 16, "one register holds both arrays");
+    const int maxv = (1 << bd) - 1;
+    uint32_t gw[5];
+    ref_sources<n>(cand & 31, gw);
+    const int side = lane >> 4, i = lane & 15;
+    int r = i < n2 ? ref_fetch<n>(sf, gw, side, i, tr_size, bl_size, bd) : 0;
+    int corner = ref_fetch<n>(sf, gw, 0, -1, tr_size, bl_size, bd);
+    // smoothing (:274-326): 8x8 only (4x4 is never smoothed, the strong form is for 32x32)
+    if (n == 8 && filter_ok && mode != 1 && min(abs(mode - 26), abs(mode - 10)) > 7) {
+        const int up = __shfl_down_sync(FULL, r, 1), dn = __shfl_up_sync(FULL, r, 1);
+        const int l0 = __shfl_sync(FULL, r, 0), t0 = __shfl_sync(FULL, r, 16);
+        if (i != n2 - 1) r = (up + 2 * r + (i == 0 ? corner : dn) + 2) >> 2;
+        corner = (l0 + 2 * corner + t0 + 2) >> 2;
+    }
+    auto L = [&](int j) { return __shfl_sync(FULL, r, j & 15); };             // left[j], j >= 0
+    auto T = [&](int j) { return __shfl_sync(FULL, r, 16 + (j & 15)); };      // top[j], j >= 0
+    const bool edge = c_idx == 0;
+#pragma unroll
+    for (int s = 0; s < (n * n + 31) / 32; s++) {
+        const int idx = lane + 32 * s, xx = idx & (n - 1), yy = (idx >> log2_size) & (n - 1);
+        int v;
+        if (mode == 0) {                                   // planar, :359-372
+            const int ly = L(yy), tn = T(n), tx = T(xx), ln = L(n);
+            v = ((n - 1 - xx) * ly + (xx + 1) * tn + (n - 1 - yy) * tx + (yy + 1) * ln + n) >> (log2_size + 1);
+        } else if (mode == 1) {                            // DC, :388-417
+            int sum = i < n ? r : 0;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(FULL, sum, o);
+            const int dc = (sum + n) >> (log2_size + 1);
+            const int ly = L(yy), tx = T(xx), l0 = L(0), t0 = T(0);
+            v = dc;
+            if (edge) {
+                if (!(xx | yy)) v = (l0 + 2 * dc + t0 + 2) >> 2;
+                else if (!yy) v = (tx + 3 * dc + 2) >> 2;
+                else if (!xx) v = (ly + 3 * dc + 2) >> 2;
+            }
+        } else {                                           // angular, :419-505
+            const int angle = c_intra_angle[mode - 2];
+            const bool vertical = mode >= 18;
+            const int mbase = vertical ? 16 : 0, sbase = vertical ? 0 : 16;
+            const int inv = angle < 0 ? c_intra_inv_angle[mode - 11] : 0;
+            const int a = vertical ? yy : xx, b = vertical ? xx : yy;
+            const int pos = (a + 1) * angle, k = b + (pos >> 5) + 1, fact = pos & 31;
+            // ref[k] = main[k - 1] (k >= 0) or the side array through the inverse angle (:440-447); index -1 = the corner
+            auto ref = [&](int kk) {
+                const int j = kk >= 0 ? kk - 1 : -1 + ((kk * inv + 128) >> 8);
+                const int got = __shfl_sync(FULL, r, ((kk >= 0 ? mbase : sbase) + j) & 31);
+                return j < 0 ? corner : got;
+            };
+            const int r0 = ref(k), r1 = ref(k + 1);
+            v = fact ? ((32 - fact) * r0 + fact * r1 + 16) >> 5 : r0;
+            if (edge && (mode == 26 || mode == 10)) {      // (uniform)
+                const int ly = L(yy), tx = T(xx), l0 = L(0), t0 = T(0);
+                if (mode == 26 && xx == 0) v = min(max(t0 + ((ly - corner) >> 1), 0), maxv);
+                if (mode == 10 && yy == 0) v = min(max(l0 + ((tx - corner) >> 1), 0), maxv);
+            }
+        }
+        if (idx < n * n) {
+            if (res) v = min(max(v + (int)res[yy * res_pitch + xx], 0), maxv);
+            sf.st(xx, yy, v);
+        }
+    }
+    __syncwarp();
+}
+
 // sf: the block's surface; tr_size / bl_size: samples of the top-right / bottom-left run inside the picture (:109-112);
 // cand: CAND_* final availability; filter_ok: !intra_smoothing_disabled && (c_idx == 0 || chroma_format_idc == 3);
 // strong: sps strong smoothing flag; res: the block's residual (first sample, pitch in int16) added to the prediction with
@@ -70,46 +189,9 @@ __device__ __noinline__ void intra_pred_size(const Surf &sf, int tr_size, int bl
     };
     int16_t *left = s.raw[0] + 1, *top = s.raw[1] + 1;
 
-    // ---- reference samples with the substitution of unavailable ones folded into the fetch (:152-272).
-    // The reference walks from the bottom-left end up the left column, over the corner and along the top row: a group
-    // that is missing (BL, L, UL, U, UR = bits 0..4 of cand) repeats the last sample of the nearest available group before
-    // it, and the groups before the first available one repeat that group's first sample; nothing available: mid-grey.
-    // Every reference sample therefore IS one sample of the picture (or the constant): gw[g] says which, per group.
-    const int avail = cand & 31;
-    constexpr uint32_t OWN = 1u << 17, GREY = 1u << 16;
-    auto pack = [](int X, int Y) { return (uint32_t)(X + 1) | ((uint32_t)(Y + 1) << 8); };
     uint32_t gw[5];
-#pragma unroll
-    for (int g = 0; g < 5; g++) {
-        const int lower = avail & ((1 << g) - 1);
-        uint32_t w;
-        if ((avail >> g) & 1) {
-            w = OWN;
-        } else if (lower) {                                // last sample (in walking order) of the nearest group before g
-            const int h = 31 - __clz(lower);
-            w = h == 0 ? pack(-1, n) : h == 1 ? pack(-1, 0) : h == 2 ? pack(-1, -1) : pack(n - 1, -1);
-        } else if (avail) {                                // first sample of the first available group
-            const int fg = __ffs(avail) - 1;
-            w = fg == 1 ? pack(-1, n - 1) : fg == 2 ? pack(-1, -1) : fg == 3 ? pack(0, -1) : pack(n, -1);
-        } else {
-            w = GREY;
-        }
-        gw[g] = w;
-    }
-    // side 0: left column (i = row), side 1: top row (i = column); i = -1: the corner; runs that leave the picture repeat
-    // their last sample (:109-112, :158, :168)
-    auto fetch = [&](int side, int i) -> int {
-        const int g = i < 0 ? 2 : (side ? (i < n ? 3 : 4) : (i < n ? 1 : 0));
-        const uint32_t w = g == 0 ? gw[0] : g == 1 ? gw[1] : g == 2 ? gw[2] : g == 3 ? gw[3] : gw[4];
-        int X = (int)(w & 255u) - 1, Y = (int)((w >> 8) & 255u) - 1;
-        if (w & OWN) {
-            const int j = i < n ? i : n + min(i - n, (side ? tr_size : bl_size) - 1);
-            X = side ? j : -1; Y = side ? -1 : j;
-        }
-        int v = 1 << (bd - 1);
-        if (!(w & GREY)) v = sf.ld(X, Y);
-        return v;
-    };
+    ref_sources<n>(cand & 31, gw);
+    auto fetch = [&](int side, int i) -> int { return ref_fetch<n>(sf, gw, side, i, tr_size, bl_size, bd); };
     for (int t = lane; t < 2 * n2; t += 32) {
         const int side = t >= n2, i = t - (side ? n2 : 0);
         s.raw[side][i + 1] = (int16_t)fetch(side, i);
@@ -192,8 +274,8 @@ __device__ __forceinline__ void intra_pred_tb(const Surf &sf, int tr_size, int b
                                               int res_pitch = 0)
 {
     switch (log2_size) {
-    case 2: intra_pred_size<2>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, res, res_pitch); break;
-    case 3: intra_pred_size<3>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, res, res_pitch); break;
+    case 2: intra_pred_small<2>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, bd, lane, res, res_pitch); break;
+    case 3: intra_pred_small<3>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, bd, lane, res, res_pitch); break;
     case 4: intra_pred_size<4>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, res, res_pitch); break;
     default: intra_pred_size<5>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, res, res_pitch); break;
     }
@@ -266,9 +348,26 @@ struct IntraTile {                         // one plane's staging (pointers into
     int sw, sh, bpitch, cshift;            // CTB size in samples of the plane, tile pitch, log2(chunks of 8 per row)
 };
 
+// -DINTRA_PROFILE: thread 0 of every CTA adds the cycles between phase marks to g_intra_prof (tools/intra_phases.py)
+#ifdef INTRA_PROFILE
+__device__ unsigned long long g_intra_prof[8];
+#define IP_MARK(k) do { if (threadIdx.x == 0) { const long long t_ = clock64(); atomicAdd(&g_intra_prof[k], (unsigned long long)(t_ - ip_t)); ip_t = t_; } } while (0)
+extern "C" int ohcu_intra_profile(unsigned long long *out, int reset)
+{
+    if (cudaMemcpyFromSymbol(out, g_intra_prof, sizeof(g_intra_prof)) != cudaSuccess) return -1;
+    if (reset) { unsigned long long z[8] = {}; cudaMemcpyToSymbol(g_intra_prof, z, sizeof(z)); }
+    return 0;
+}
+#else
+#define IP_MARK(k) do { } while (0)
+#endif
+
 template <typename pixel>
 __global__ void __launch_bounds__(INTRA_THREADS) intra_kernel(const __grid_constant__ FrameDev f)
 {
+#ifdef INTRA_PROFILE
+    long long ip_t = clock64();
+#endif
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ IntraScratch scratch[3];
     __shared__ ohcu_iu s_iu[INTRA_MAX_IU];
@@ -292,6 +391,7 @@ __global__ void __launch_bounds__(INTRA_THREADS) intra_kernel(const __grid_const
     __syncthreads();
     const int ctb = s_ctb, cx = ctb % f.ctb_w, row = ctb / f.ctb_w;
     if (ctb >= nctb) return;
+    IP_MARK(0);                                            // ticket
     const ohcu_iu_index ixr = f.iu_index[ctb];
     const uint2 ix = make_uint2(ixr.first_iu, ixr.n_iu);
     // which neighbour CTBs hold intra blocks (thread 0 waits for those this CTB reads)
@@ -388,6 +488,7 @@ __global__ void __launch_bounds__(INTRA_THREADS) intra_kernel(const __grid_const
         }
     }
     __syncthreads();
+    IP_MARK(1);                                            // records, own rows, residuals
     // ---- wait for the neighbour CTBs this one reads intra samples of
     if (tid == INTRA_SPIN_TID) {
         const int w = s_need & nb_intra;
@@ -400,6 +501,7 @@ __global__ void __launch_bounds__(INTRA_THREADS) intra_kernel(const __grid_const
         }
     }
     __syncthreads();
+    IP_MARK(2);                                            // wait
     // ---- the column left of the CTB, the row above it: corner, top, top-right
     {
         int i = tid;
@@ -424,6 +526,7 @@ __global__ void __launch_bounds__(INTRA_THREADS) intra_kernel(const __grid_const
         }
     }
     __syncthreads();
+    IP_MARK(3);                                            // left column, top row
     if (warp < f.nplanes) {
         const IntraTile &t = tile[warp];
         pixel *plane = (pixel *)f.work.p[warp];
@@ -444,10 +547,15 @@ __global__ void __launch_bounds__(INTRA_THREADS) intra_kernel(const __grid_const
         }
     }
     __syncthreads();                                       // every plane of the CTB is written
+    IP_MARK(4);                                            // the blocks (thread 0: plane 0's, then the wait for the others)
     if (tid == 0) {
         __threadfence();
         st_release(done + ctb, 1);
     }
+    IP_MARK(5);                                            // fence + release
+#ifdef INTRA_PROFILE
+    if (tid == 0) atomicAdd(&g_intra_prof[7], 1ull);
+#endif
   }
 }
 
