@@ -16,6 +16,17 @@
 
 namespace ohcu {
 
+// -DINTRA_PROFILE: cycle counters (tools/intra_phases.py): [0..5] the phases of a CTB in intra_kernel (thread 0),
+// [8..13] the steps of a 4x4 / 8x8 block in intra_pred_small (lane 0 of the luma warp), [7] CTBs, [14] blocks
+#ifdef INTRA_PROFILE
+__device__ unsigned long long g_intra_prof[16];
+#define IB_START() long long ib_t = clock64()
+#define IB_MARK(k) do { if (lane == 0 && c_idx == 0) { const long long t_ = clock64(); atomicAdd(&g_intra_prof[k], (unsigned long long)(t_ - ib_t)); ib_t = t_; } } while (0)
+#else
+#define IB_START() do { } while (0)
+#define IB_MARK(k) do { } while (0)
+#endif
+
 enum { CAND_BL = 1, CAND_L = 2, CAND_UL = 4, CAND_U = 8, CAND_UR = 16 };      // bits 0..4: the order the reference walks the groups in
 
 struct IntraScratch {                 // per warp
@@ -43,8 +54,9 @@ template <typename pixel> struct TileSurf {
     pixel *blk; int pitch;                             // the block in the picture
     __device__ __forceinline__ int ld(int x, int y) const
     {
+        // one load whichever array the sample is in (`body` follows `top` in the tile: an offset, not a branch)
         const int X = bx + x + TILE_X0, Y = by + y;
-        return Y < 0 ? top[X] : body[Y * bpitch + X];
+        return top[X + (Y < 0 ? 0 : (int)(body - top) + Y * bpitch)];
     }
     __device__ __forceinline__ void st(int x, int y, int v) const
     {
@@ -109,11 +121,14 @@ __device__ __noinline__ void intra_pred_small(const Surf &sf, int tr_size, int b
     constexpr unsigned FULL = 0xffffffffu;
     static_assert(n2 <= 16, "one register holds both arrays");
     const int maxv = (1 << bd) - 1;
+    IB_START();
     uint32_t gw[5];
     ref_sources<n>(cand & 31, gw);
+    IB_MARK(8);                                            // where the reference samples come from
     const int side = lane >> 4, i = lane & 15;
     int r = i < n2 ? ref_fetch<n>(sf, gw, side, i, tr_size, bl_size, bd) : 0;
     int corner = ref_fetch<n>(sf, gw, 0, -1, tr_size, bl_size, bd);
+    IB_MARK(9);                                            // fetched
     // smoothing (:274-326): 8x8 only (4x4 is never smoothed, the strong form is for 32x32)
     if (n == 8 && filter_ok && mode != 1 && min(abs(mode - 26), abs(mode - 10)) > 7) {
         const int up = __shfl_down_sync(FULL, r, 1), dn = __shfl_up_sync(FULL, r, 1);
@@ -121,6 +136,7 @@ __device__ __noinline__ void intra_pred_small(const Surf &sf, int tr_size, int b
         if (i != n2 - 1) r = (up + 2 * r + (i == 0 ? corner : dn) + 2) >> 2;
         corner = (l0 + 2 * corner + t0 + 2) >> 2;
     }
+    IB_MARK(10);                                           // smoothed
     auto L = [&](int j) { return __shfl_sync(FULL, r, j & 15); };             // left[j], j >= 0
     auto T = [&](int j) { return __shfl_sync(FULL, r, 16 + (j & 15)); };      // top[j], j >= 0
     const bool edge = c_idx == 0;
@@ -164,12 +180,18 @@ __device__ __noinline__ void intra_pred_small(const Surf &sf, int tr_size, int b
                 if (mode == 10 && yy == 0) v = min(max(l0 + ((tx - corner) >> 1), 0), maxv);
             }
         }
+        IB_MARK(11);                                       // predicted
         if (idx < n * n) {
             if (res) v = min(max(v + (int)res[yy * res_pitch + xx], 0), maxv);
             sf.st(xx, yy, v);
         }
+        IB_MARK(12);                                       // residual added, stored
     }
     __syncwarp();
+    IB_MARK(13);
+#ifdef INTRA_PROFILE
+    if (lane == 0 && c_idx == 0) atomicAdd(&g_intra_prof[14], 1ull);
+#endif
 }
 
 // sf: the block's surface; tr_size / bl_size: samples of the top-right / bottom-left run inside the picture (:109-112);
@@ -350,12 +372,11 @@ struct IntraTile {                         // one plane's staging (pointers into
 
 // -DINTRA_PROFILE: thread 0 of every CTA adds the cycles between phase marks to g_intra_prof (tools/intra_phases.py)
 #ifdef INTRA_PROFILE
-__device__ unsigned long long g_intra_prof[8];
 #define IP_MARK(k) do { if (threadIdx.x == 0) { const long long t_ = clock64(); atomicAdd(&g_intra_prof[k], (unsigned long long)(t_ - ip_t)); ip_t = t_; } } while (0)
 extern "C" int ohcu_intra_profile(unsigned long long *out, int reset)
 {
     if (cudaMemcpyFromSymbol(out, g_intra_prof, sizeof(g_intra_prof)) != cudaSuccess) return -1;
-    if (reset) { unsigned long long z[8] = {}; cudaMemcpyToSymbol(g_intra_prof, z, sizeof(z)); }
+    if (reset) { unsigned long long z[16] = {}; cudaMemcpyToSymbol(g_intra_prof, z, sizeof(z)); }
     return 0;
 }
 #else

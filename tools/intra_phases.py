@@ -15,7 +15,7 @@ for s, r in enumerate(refs):
     ctx.upload(s, r)
 j = ctx.begin(job.sp.dpb_slots - 1); ctx.append_inplace(j, job, coeffs="sparse"); ctx.stage(j)
 ctx.launch(j, job.sp.dpb_slots - 1); ctx.sync(j)
-out = (C.c_ulonglong * 8)()
+out = (C.c_ulonglong * 16)()
 lib.ohcu_intra_profile(out, 1)
 ctx.launch(j, job.sp.dpb_slots - 1); ctx.sync(j)
 lib.ohcu_intra_profile(out, 0)
@@ -24,3 +24,6 @@ names = ["ticket", "records + own rows + residuals", "wait for neighbour CTBs", 
 print(f"intra_pct={pct} free={'--free' in sys.argv}: {n} CTBs with intra blocks, cycles per CTB (thread 0):")
 for k, name in enumerate(names):
     print(f"  {name:34s} {out[k] / n:10.0f}")
+nb = max(1, out[14])
+print(f"  4x4 / 8x8 luma blocks: {nb}, cycles per block (lane 0): sources {out[8] / nb:.0f}, fetch {out[9] / nb:.0f}, smoothing {out[10] / nb:.0f}, "
+      f"predict {out[11] / nb:.0f}, residual + store {out[12] / nb:.0f}, tail {out[13] / nb:.0f}")
