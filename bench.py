@@ -295,7 +295,7 @@ def run_ours(args, rank, world):
     from concurrent.futures import ThreadPoolExecutor
     from hevc_b200 import abi, backend, driver, shard
     D, F = frames_per_rank(args.workload, world)
-    B = WORKLOADS[args.workload][5]
+    B = args.in_flight or WORKLOADS[args.workload][5]
     if args.frames:
         F = args.frames
     jobs, refs = make_inputs(args.workload, rank, world)
@@ -553,6 +553,7 @@ def main():
                          "the device pitch (pitch), or ohcu_slot_output_cropped: pack kernel + one linear copy (packed)")
     ap.add_argument("--intra-pct", type=int, default=0, help="share of intra-predicted CUs in every frame (default 0: the headline workload)")
     ap.add_argument("--gop", type=int, default=0, help="every GOP-th frame of the job is all intra (an I picture); 0 = none")
+    ap.add_argument("--in-flight", type=int, default=0, help="frames in flight of the resident leg (default per workload)")
     ap.add_argument("--no-numa", action="store_true", help="N > 1: do not bind each rank to the NUMA node of its GPU")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-check", action="store_true")
