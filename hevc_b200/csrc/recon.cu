@@ -43,6 +43,13 @@
 
 #include "ohcu_internal.h"
 
+#ifndef MC_PREFETCH
+#define MC_PREFETCH 0      // 1: prefetch.global.L1 of the window's rows ahead of the row loop (A/B builds)
+#endif
+#ifndef MC_PREFETCH_FROM
+#define MC_PREFETCH_FROM 2
+#endif
+
 namespace ohcu {
 
 constexpr int RC_WARPS = 8;
@@ -769,6 +776,12 @@ __device__ __forceinline__ void mc_filter(const uint8_t *win, int pitch, int col
     constexpr int NW = (OW + NT) / 2, NR = OH + NT - 1;
     uint32_t hb[NR][OW / 2];
     const uint8_t *rowp = win + row0 * pitch;
+#if MC_PREFETCH
+    // every row of the cell's window requested at once: the misses of the later rows overlap with the filtering of the first
+#pragma unroll
+    for (int r = MC_PREFETCH_FROM; r < NR; r++)
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(rowp + r * pitch + col0 * (HIGH ? 2 : 1)));
+#endif
 #pragma unroll
     for (int r = 0; r < NR; r++) {
         uint32_t W[NW];
