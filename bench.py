@@ -5,7 +5,7 @@
                   [--workload 4k|1080p|1080p422|1080p444|8k]
 
 A step = one pass of the hot path (mc_kernel, residual_kernel, loopfilter_kernel = deblock + SAO fused, pad_kernel)
-over one batch of synthetic frames (160 4K frames per step by default, so that 20 steps time ~0.5 s of device work).
+over one batch of synthetic frames (192 4K frames per step by default, so that 20 steps time 0.55 s of device work).
 Default workload: BASELINE.json configs[2], 3840x2160 Main10 4:2:0 full reconstruction with weighted prediction; the
 other BASELINE configs are --workload 1080p / 1080p422 / 1080p444 / 8k (64 independent frames, strong scaling).
 
@@ -39,9 +39,9 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 WORKLOADS = {
     # name: (width, height, bit_depth, chroma_format_idc, generator overrides,
     #        frames in flight per GPU (resident leg), distinct synthetic frames per GPU, frames per step per GPU)
-    "4k": (3840, 2160, 10, 1, dict(weighted=1), 8, 8, 160),
-    "1080p": (1920, 1080, 8, 1, dict(), 16, 8, 640),
-    "1080p422": (1920, 1080, 10, 2, dict(rext=1, weighted=1), 16, 8, 320),
+    "4k": (3840, 2160, 10, 1, dict(weighted=1), 8, 8, 192),
+    "1080p": (1920, 1080, 8, 1, dict(), 16, 8, 704),
+    "1080p422": (1920, 1080, 10, 2, dict(rext=1, weighted=1), 16, 8, 448),
     "1080p444": (1920, 1080, 10, 3, dict(rext=1), 16, 8, 320),
     # 64 independent frames in all, sharded frame i -> rank i mod N: the job is fixed, so scaling is STRONG
     "8k": (7680, 4320, 10, 1, dict(weighted=1), 8, 64, 64),
