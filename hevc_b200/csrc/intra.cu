@@ -38,30 +38,56 @@ __constant__ int8_t c_intra_angle[33] = {32, 26, 21, 17, 13, 9, 5, 2, 0, -2, -5,
                                          -26, -21, -17, -13, -9, -5, -2, 0, 2, 5, 9, 13, 17, 21, 26, 32};
 __constant__ int16_t c_intra_inv_angle[15] = {-4096, -1638, -910, -630, -482, -390, -315, -256, -315, -390, -482, -630, -910, -1638, -4096};
 
+// An int16 array in shared memory addressed with ld.shared / st.shared (see TileSurf); index -1 is valid where the
+// array has an element in front of it.
+struct SArr {
+    uint32_t a;                                            // shared address of element 0
+    __device__ __forceinline__ int operator[](int i) const
+    {
+        int v;
+        asm volatile("ld.shared.s16 %0, [%1];" : "=r"(v) : "r"(a + 2u * (uint32_t)i) : "memory");
+        return v;
+    }
+    __device__ __forceinline__ void set(int i, int v) const { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a + 2u * (uint32_t)i), "r"(v) : "memory"); }
+};
+
 // Where a block's samples live.  ld / st take coordinates relative to the block's first sample.
 template <typename pixel> struct PlaneSurf {           // a plane in global memory (per-entry shim)
     pixel *blk; int pitch;                             // first sample of the block, pitch in samples
     __device__ __forceinline__ int ld(int x, int y) const { return (int)__ldcg(blk + (ptrdiff_t)y * pitch + x); }
     __device__ __forceinline__ void st(int x, int y, int v) const { blk[(ptrdiff_t)y * pitch + x] = (pixel)v; }
+    __device__ __forceinline__ int res(int, int) const { return 0; }           // (the shim predicts only)
 };
 // The CTB's samples in shared memory (intra_kernel): row -1 (corner, top, top-right of the CTB) in `top`, the CTB's own
 // rows with the column left of it in `body`; sample x of a row sits at index x + TILE_X0.  Stores go to the tile and
 // through to the picture.
 constexpr int TILE_X0 = 8;
 template <typename pixel> struct TileSurf {
-    uint16_t *top, *body; int bpitch;
+    // 32-bit shared-memory addresses and ld.shared / st.shared: the structs that carry the tile travel through shared
+    // memory and function calls, where the compiler only knows generic pointers - a generic load that resolves to shared
+    // memory takes the L1 path's latency, and the chain of blocks is made of these loads
+    uint32_t top_s; int body_off, bpitch;              // `top` (shared address), where `body` starts behind it (samples)
+    uint32_t res_s; int res_pitch;                     // the block's residual (shared address of its first value), pitch in int16
     int bx, by;                                        // the block inside the CTB
     pixel *blk; int pitch;                             // the block in the picture
     __device__ __forceinline__ int ld(int x, int y) const
     {
         // one load whichever array the sample is in (`body` follows `top` in the tile: an offset, not a branch)
         const int X = bx + x + TILE_X0, Y = by + y;
-        return top[X + (Y < 0 ? 0 : (int)(body - top) + Y * bpitch)];
+        uint32_t v;
+        asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(top_s + 2u * (uint32_t)(X + (Y < 0 ? 0 : body_off + Y * bpitch))) : "memory");
+        return (int)v;
     }
     __device__ __forceinline__ void st(int x, int y, int v) const
     {
-        body[(by + y) * bpitch + bx + x + TILE_X0] = (uint16_t)v;
+        asm volatile("st.shared.u16 [%0], %1;" ::"r"(top_s + 2u * (uint32_t)(body_off + (by + y) * bpitch + bx + x + TILE_X0)), "r"(v) : "memory");
         blk[(ptrdiff_t)y * pitch + x] = (pixel)v;
+    }
+    __device__ __forceinline__ int res(int x, int y) const
+    {
+        int v;
+        asm volatile("ld.shared.s16 %0, [%1];" : "=r"(v) : "r"(res_s + 2u * (uint32_t)(y * res_pitch + x)) : "memory");
+        return v;
     }
 };
 
@@ -115,7 +141,7 @@ __device__ __forceinline__ int ref_fetch(const Surf &sf, const uint32_t (&gw)[5]
 // array, no warp barrier, a third of the dependent instructions of the general path.  These are most of a picture's blocks.
 template <int log2_size, typename Surf>
 __device__ __noinline__ void intra_pred_small(const Surf &sf, int tr_size, int bl_size, int c_idx, int mode, int cand, int filter_ok,
-                                              int bd, int lane, const int16_t *res, int res_pitch)
+                                              int bd, int lane, bool has_res)
 {
     constexpr int n = 1 << log2_size, n2 = 2 * n;
     constexpr unsigned FULL = 0xffffffffu;
@@ -182,7 +208,7 @@ __device__ __noinline__ void intra_pred_small(const Surf &sf, int tr_size, int b
         }
         IB_MARK(11);                                       // predicted
         if (idx < n * n) {
-            if (res) v = min(max(v + (int)res[yy * res_pitch + xx], 0), maxv);
+            if (has_res) v = min(max(v + sf.res(xx, yy), 0), maxv);
             sf.st(xx, yy, v);
         }
         IB_MARK(12);                                       // residual added, stored
@@ -196,30 +222,33 @@ __device__ __noinline__ void intra_pred_small(const Surf &sf, int tr_size, int b
 
 // sf: the block's surface; tr_size / bl_size: samples of the top-right / bottom-left run inside the picture (:109-112);
 // cand: CAND_* final availability; filter_ok: !intra_smoothing_disabled && (c_idx == 0 || chroma_format_idc == 3);
-// strong: sps strong smoothing flag; res: the block's residual (first sample, pitch in int16) added to the prediction with
-// the clip of transform_add (hevcdsp_template.c:45-84), or nullptr.
+// strong: sps strong smoothing flag; has_res: the surface's residual (Surf::res) is added to the prediction with the clip of
+// transform_add (hevcdsp_template.c:45-84).
 // (one instance per block size: trip counts and index arithmetic fold at compile time)
 template <int log2_size, typename Surf>
 __device__ __noinline__ void intra_pred_size(const Surf &sf, int tr_size, int bl_size, int c_idx, int mode, int cand, int filter_ok,
-                                             int strong, int bd, IntraScratch &s, int lane, const int16_t *res, int res_pitch)
+                                             int strong, int bd, IntraScratch &s, int lane, bool has_res)
 {
     constexpr int n = 1 << log2_size, n2 = 2 * n;
     const int maxv = (1 << bd) - 1;
     auto put = [&](int xx, int yy, int v) {
-        if (res) v = min(max(v + (int)res[yy * res_pitch + xx], 0), maxv);
+        if (has_res) v = min(max(v + sf.res(xx, yy), 0), maxv);
         sf.st(xx, yy, v);
     };
-    int16_t *left = s.raw[0] + 1, *top = s.raw[1] + 1;
+    // the scratch arrays through their shared addresses: element i of an array sits at index i + 1, the corner at 0
+    const SArr raw[2] = {{(uint32_t)__cvta_generic_to_shared(s.raw[0]) + 2u}, {(uint32_t)__cvta_generic_to_shared(s.raw[1]) + 2u}};
+    const SArr flt[2] = {{(uint32_t)__cvta_generic_to_shared(s.flt[0]) + 2u}, {(uint32_t)__cvta_generic_to_shared(s.flt[1]) + 2u}};
+    SArr left = raw[0], top = raw[1];
 
     uint32_t gw[5];
     ref_sources<n>(cand & 31, gw);
     auto fetch = [&](int side, int i) -> int { return ref_fetch<n>(sf, gw, side, i, tr_size, bl_size, bd); };
     for (int t = lane; t < 2 * n2; t += 32) {
         const int side = t >= n2, i = t - (side ? n2 : 0);
-        s.raw[side][i + 1] = (int16_t)fetch(side, i);
+        (side ? raw[1] : raw[0]).set(i, fetch(side, i));
     }
     const int corner = fetch(0, -1);
-    if (lane == 0) left[-1] = top[-1] = (int16_t)corner;
+    if (lane == 0) { left.set(-1, corner); top.set(-1, corner); }
     __syncwarp();
 
     // ---- smoothing (:274-326)
@@ -231,16 +260,19 @@ __device__ __noinline__ void intra_pred_size(const Surf &sf, int tr_size, int bl
                                   abs(corner + left[63] - 2 * left[31]) < (1 << (bd - 5));
             for (int t = lane; t < 2 * n2; t += 32) {
                 const int side = t >= n2, i = t - (side ? n2 : 0);
-                const int16_t *r = s.raw[side] + 1;
+                const SArr r = side ? raw[1] : raw[0];
                 int v;
                 if (i == n2 - 1) v = r[i];
                 else if (bilinear) v = ((63 - i) * corner + (i + 1) * r[63] + 32) >> 6;
                 else v = (r[i + 1] + 2 * r[i] + r[i - 1] + 2) >> 2;
-                s.flt[side][i + 1] = (int16_t)v;
+                (side ? flt[1] : flt[0]).set(i, v);
             }
-            if (lane == 0) s.flt[0][0] = s.flt[1][0] = (int16_t)(bilinear ? corner : (left[0] + 2 * corner + top[0] + 2) >> 2);
+            if (lane == 0) {
+                const int fc = bilinear ? corner : (left[0] + 2 * corner + top[0] + 2) >> 2;
+                flt[0].set(-1, fc); flt[1].set(-1, fc);
+            }
             __syncwarp();
-            left = s.flt[0] + 1; top = s.flt[1] + 1;
+            left = flt[0]; top = flt[1];
         }
     }
 
@@ -270,7 +302,7 @@ __device__ __noinline__ void intra_pred_size(const Surf &sf, int tr_size, int bl
     } else {                                               // angular, :419-505
         const int angle = c_intra_angle[mode - 2];
         const bool vertical = mode >= 18;
-        const int16_t *mn = vertical ? top : left, *sd = vertical ? left : top;
+        const SArr mn = vertical ? top : left, sd = vertical ? left : top;
         const int inv = angle < 0 ? c_intra_inv_angle[mode - 11] : 0;
         const bool edge26 = edge && mode == 26, edge10 = edge && mode == 10;
 #pragma unroll
@@ -292,14 +324,13 @@ __device__ __noinline__ void intra_pred_size(const Surf &sf, int tr_size, int bl
 
 template <typename Surf>
 __device__ __forceinline__ void intra_pred_tb(const Surf &sf, int tr_size, int bl_size, int log2_size, int c_idx, int mode, int cand,
-                                              int filter_ok, int strong, int bd, IntraScratch &s, int lane, const int16_t *res = nullptr,
-                                              int res_pitch = 0)
+                                              int filter_ok, int strong, int bd, IntraScratch &s, int lane, bool has_res = false)
 {
     switch (log2_size) {
-    case 2: intra_pred_small<2>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, bd, lane, res, res_pitch); break;
-    case 3: intra_pred_small<3>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, bd, lane, res, res_pitch); break;
-    case 4: intra_pred_size<4>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, res, res_pitch); break;
-    default: intra_pred_size<5>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, res, res_pitch); break;
+    case 2: intra_pred_small<2>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, bd, lane, has_res); break;
+    case 3: intra_pred_small<3>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, bd, lane, has_res); break;
+    case 4: intra_pred_size<4>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, has_res); break;
+    default: intra_pred_size<5>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, has_res); break;
     }
 }
 
@@ -554,17 +585,19 @@ __global__ void __launch_bounds__(INTRA_THREADS) intra_kernel(const __grid_const
         const int pitch = f.work.pitch[warp] / (int)sizeof(pixel), pw = f.pw[warp], ph = f.ph[warp];
         const int ox = cx * t.sw;
         TileSurf<pixel> sf;
-        sf.top = t.top; sf.body = t.body; sf.bpitch = t.bpitch; sf.pitch = pitch;
+        sf.top_s = (uint32_t)__cvta_generic_to_shared(t.top); sf.body_off = (int)(t.body - t.top); sf.bpitch = t.bpitch; sf.pitch = pitch;
+        sf.res_pitch = t.sw;
+        const uint32_t res0 = (uint32_t)__cvta_generic_to_shared(t.res);
         for (uint32_t i = 0; i < ix.y; i++) {
             const ohcu_iu u = s_iu[i];
             if (u.c_idx != warp) continue;
             const int n = 1 << u.log2_size;
             sf.bx = u.x0 - ox; sf.by = u.y0 - oy[warp];
             sf.blk = plane + (size_t)u.y0 * pitch + u.x0;
-            const int16_t *res = (u.cand & OHCU_IU_CBF) ? t.res + sf.by * t.sw + sf.bx : nullptr;
+            sf.res_s = res0 + 2u * (uint32_t)(sf.by * t.sw + sf.bx);
             intra_pred_tb(sf, max(0, min(u.x0 + 2 * n, pw) - (u.x0 + n)), max(0, min(u.y0 + 2 * n, ph) - (u.y0 + n)), u.log2_size,
                           warp, u.mode, u.cand & 31, warp ? filter_chroma : filter_luma, f.strong_intra_smoothing, f.bd,
-                          scratch[warp], lane, res, t.sw);
+                          scratch[warp], lane, (u.cand & OHCU_IU_CBF) != 0);
         }
     }
     __syncthreads();                                       // every plane of the CTB is written
