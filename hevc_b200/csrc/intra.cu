@@ -95,44 +95,30 @@ template <typename pixel> struct TileSurf {
 // The reference walks from the bottom-left end up the left column, over the corner and along the top row: a group
 // that is missing (BL, L, UL, U, UR = bits 0..4 of cand) repeats the last sample of the nearest available group before
 // it, and the groups before the first available one repeat that group's first sample; nothing available: mid-grey.
-// Every reference sample therefore IS one sample of the picture (or the constant): gw[g] says which, per group.
-constexpr uint32_t REF_OWN = 1u << 17, REF_GREY = 1u << 16;
-template <int n>
-__device__ __forceinline__ void ref_sources(int avail, uint32_t (&gw)[5])
-{
-    auto pack = [](int X, int Y) { return (uint32_t)(X + 1) | ((uint32_t)(Y + 1) << 8); };
-#pragma unroll
-    for (int g = 0; g < 5; g++) {
-        const int lower = avail & ((1 << g) - 1);
-        uint32_t w;
-        if ((avail >> g) & 1) {
-            w = REF_OWN;
-        } else if (lower) {                                // last sample (in walking order) of the nearest group before g
-            const int h = 31 - __clz(lower);
-            w = h == 0 ? pack(-1, n) : h == 1 ? pack(-1, 0) : h == 2 ? pack(-1, -1) : pack(n - 1, -1);
-        } else if (avail) {                                // first sample of the first available group
-            const int fg = __ffs(avail) - 1;
-            w = fg == 1 ? pack(-1, n - 1) : fg == 2 ? pack(-1, -1) : fg == 3 ? pack(0, -1) : pack(n, -1);
-        } else {
-            w = REF_GREY;
-        }
-        gw[g] = w;
-    }
-}
+// Every reference sample therefore IS one sample of the picture (or the constant).  Which one, per group, is a function of
+// the five flags alone: c_ref_src[cand] holds six bits per group - bit 0 the group's own samples, bit 1 mid-grey, else the
+// coordinates of the one sample it repeats as x = (bit 2 ? 0 : -1) + (bit 3 ? N : 0), y = (bit 4 ? 0 : -1) + (bit 5 ? N : 0):
+//   last sample of the nearest available group before it   BL (-1, N)   L (-1, 0)   UL (-1, -1)   U (N - 1, -1)
+//   first sample of the first available group              L (-1, N - 1)   UL (-1, -1)   U (0, -1)   UR (N, -1)
+__constant__ uint32_t c_ref_src[32] = {
+    0x02082082u, 0x30c30c01u, 0x10410060u, 0x10410041u, 0x00001000u, 0x00001c01u, 0x00001060u, 0x00001041u,
+    0x08044104u, 0x08070c01u, 0x08050060u, 0x08050041u, 0x08041000u, 0x08041c01u, 0x08041060u, 0x08041041u,
+    0x0130c30cu, 0x01c30c01u, 0x01410060u, 0x01410041u, 0x01001000u, 0x01001c01u, 0x01001060u, 0x01001041u,
+    0x01044104u, 0x01070c01u, 0x01050060u, 0x01050041u, 0x01041000u, 0x01041c01u, 0x01041060u, 0x01041041u};
 // side 0: left column (i = row), side 1: top row (i = column); i = -1: the corner; runs that leave the picture repeat
-// their last sample (:109-112, :158, :168)
+// their last sample (:109-112, :158, :168).  src = c_ref_src[cand & 31]
 template <int n, typename Surf>
-__device__ __forceinline__ int ref_fetch(const Surf &sf, const uint32_t (&gw)[5], int side, int i, int tr_size, int bl_size, int bd)
+__device__ __forceinline__ int ref_fetch(const Surf &sf, uint32_t src, int side, int i, int tr_size, int bl_size, int bd)
 {
-    const int g = i < 0 ? 2 : (side ? (i < n ? 3 : 4) : (i < n ? 1 : 0));
-    const uint32_t w = g == 0 ? gw[0] : g == 1 ? gw[1] : g == 2 ? gw[2] : g == 3 ? gw[3] : gw[4];
-    int X = (int)(w & 255u) - 1, Y = (int)((w >> 8) & 255u) - 1;
-    if (w & REF_OWN) {
+    const int g = i < 0 ? 2 : 2 + (side ? 1 : -1) * (i < n ? 1 : 2);       // BL 0, L 1, UL 2, U 3, UR 4
+    const uint32_t w = src >> (6 * g);
+    int X = (int)((w >> 2) & 1u) - 1 + ((w & 8u) ? n : 0), Y = (int)((w >> 4) & 1u) - 1 + ((w & 32u) ? n : 0);
+    if (w & 1u) {
         const int j = i < n ? i : n + min(i - n, (side ? tr_size : bl_size) - 1);
         X = side ? j : -1; Y = side ? -1 : j;
     }
     int v = 1 << (bd - 1);
-    if (!(w & REF_GREY)) v = sf.ld(X, Y);
+    if (!(w & 2u)) v = sf.ld(X, Y);
     return v;
 }
 
@@ -140,7 +126,7 @@ __device__ __forceinline__ int ref_fetch(const Surf &sf, const uint32_t (&gw)[5]
 // lanes 16..31 the top row, the corner in every lane), smoothing and the predictors read them with shuffles: no scratch
 // array, no warp barrier, a third of the dependent instructions of the general path.  These are most of a picture's blocks.
 template <int log2_size, typename Surf>
-__device__ __noinline__ void intra_pred_small(const Surf &sf, int tr_size, int bl_size, int c_idx, int mode, int cand, int filter_ok,
+__device__ __forceinline__ void intra_pred_small(const Surf &sf, int tr_size, int bl_size, int c_idx, int mode, int cand, int filter_ok,
                                               int bd, int lane, bool has_res)
 {
     constexpr int n = 1 << log2_size, n2 = 2 * n;
@@ -148,12 +134,11 @@ __device__ __noinline__ void intra_pred_small(const Surf &sf, int tr_size, int b
     static_assert(n2 <= 16, "one register holds both arrays");
     const int maxv = (1 << bd) - 1;
     IB_START();
-    uint32_t gw[5];
-    ref_sources<n>(cand & 31, gw);
+    const uint32_t src = c_ref_src[cand & 31];
     IB_MARK(8);                                            // where the reference samples come from
     const int side = lane >> 4, i = lane & 15;
-    int r = i < n2 ? ref_fetch<n>(sf, gw, side, i, tr_size, bl_size, bd) : 0;
-    int corner = ref_fetch<n>(sf, gw, 0, -1, tr_size, bl_size, bd);
+    int r = i < n2 ? ref_fetch<n>(sf, src, side, i, tr_size, bl_size, bd) : 0;
+    int corner = ref_fetch<n>(sf, src, 0, -1, tr_size, bl_size, bd);
     IB_MARK(9);                                            // fetched
     // smoothing (:274-326): 8x8 only (4x4 is never smoothed, the strong form is for 32x32)
     if (n == 8 && filter_ok && mode != 1 && min(abs(mode - 26), abs(mode - 10)) > 7) {
@@ -226,7 +211,7 @@ __device__ __noinline__ void intra_pred_small(const Surf &sf, int tr_size, int b
 // transform_add (hevcdsp_template.c:45-84).
 // (one instance per block size: trip counts and index arithmetic fold at compile time)
 template <int log2_size, typename Surf>
-__device__ __noinline__ void intra_pred_size(const Surf &sf, int tr_size, int bl_size, int c_idx, int mode, int cand, int filter_ok,
+__device__ __forceinline__ void intra_pred_size(const Surf &sf, int tr_size, int bl_size, int c_idx, int mode, int cand, int filter_ok,
                                              int strong, int bd, IntraScratch &s, int lane, bool has_res)
 {
     constexpr int n = 1 << log2_size, n2 = 2 * n;
@@ -240,9 +225,8 @@ __device__ __noinline__ void intra_pred_size(const Surf &sf, int tr_size, int bl
     const SArr flt[2] = {{(uint32_t)__cvta_generic_to_shared(s.flt[0]) + 2u}, {(uint32_t)__cvta_generic_to_shared(s.flt[1]) + 2u}};
     SArr left = raw[0], top = raw[1];
 
-    uint32_t gw[5];
-    ref_sources<n>(cand & 31, gw);
-    auto fetch = [&](int side, int i) -> int { return ref_fetch<n>(sf, gw, side, i, tr_size, bl_size, bd); };
+    const uint32_t src = c_ref_src[cand & 31];
+    auto fetch = [&](int side, int i) -> int { return ref_fetch<n>(sf, src, side, i, tr_size, bl_size, bd); };
     for (int t = lane; t < 2 * n2; t += 32) {
         const int side = t >= n2, i = t - (side ? n2 : 0);
         (side ? raw[1] : raw[0]).set(i, fetch(side, i));
