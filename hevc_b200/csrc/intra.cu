@@ -126,7 +126,7 @@ __device__ __forceinline__ int ref_fetch(const Surf &sf, uint32_t src, int side,
 // lanes 16..31 the top row, the corner in every lane), smoothing and the predictors read them with shuffles: no scratch
 // array, no warp barrier, a third of the dependent instructions of the general path.  These are most of a picture's blocks.
 template <int log2_size, typename Surf>
-__device__ __forceinline__ void intra_pred_small(const Surf &sf, int tr_size, int bl_size, int c_idx, int mode, int cand, int filter_ok,
+__device__ __forceinline__ void intra_pred_small(const Surf &sf, uint32_t src, int tr_size, int bl_size, int c_idx, int mode, int filter_ok,
                                               int bd, int lane, bool has_res)
 {
     constexpr int n = 1 << log2_size, n2 = 2 * n;
@@ -134,8 +134,14 @@ __device__ __forceinline__ void intra_pred_small(const Surf &sf, int tr_size, in
     static_assert(n2 <= 16, "one register holds both arrays");
     const int maxv = (1 << bd) - 1;
     IB_START();
-    const uint32_t src = c_ref_src[cand & 31];
-    IB_MARK(8);                                            // where the reference samples come from
+    IB_MARK(8);
+    // the block's residual first: these loads depend on nothing and are back before the prediction needs them
+    int rv[(n * n + 31) / 32];
+#pragma unroll
+    for (int s = 0; s < (n * n + 31) / 32; s++) {
+        const int idx = lane + 32 * s;
+        rv[s] = (has_res && idx < n * n) ? sf.res(idx & (n - 1), idx >> log2_size) : 0;
+    }
     const int side = lane >> 4, i = lane & 15;
     int r = i < n2 ? ref_fetch<n>(sf, src, side, i, tr_size, bl_size, bd) : 0;
     int corner = ref_fetch<n>(sf, src, 0, -1, tr_size, bl_size, bd);
@@ -193,7 +199,7 @@ __device__ __forceinline__ void intra_pred_small(const Surf &sf, int tr_size, in
         }
         IB_MARK(11);                                       // predicted
         if (idx < n * n) {
-            if (has_res) v = min(max(v + sf.res(xx, yy), 0), maxv);
+            if (has_res) v = min(max(v + rv[s], 0), maxv);
             sf.st(xx, yy, v);
         }
         IB_MARK(12);                                       // residual added, stored
@@ -211,7 +217,7 @@ __device__ __forceinline__ void intra_pred_small(const Surf &sf, int tr_size, in
 // transform_add (hevcdsp_template.c:45-84).
 // (one instance per block size: trip counts and index arithmetic fold at compile time)
 template <int log2_size, typename Surf>
-__device__ __forceinline__ void intra_pred_size(const Surf &sf, int tr_size, int bl_size, int c_idx, int mode, int cand, int filter_ok,
+__device__ __forceinline__ void intra_pred_size(const Surf &sf, uint32_t src, int tr_size, int bl_size, int c_idx, int mode, int filter_ok,
                                              int strong, int bd, IntraScratch &s, int lane, bool has_res)
 {
     constexpr int n = 1 << log2_size, n2 = 2 * n;
@@ -225,7 +231,6 @@ __device__ __forceinline__ void intra_pred_size(const Surf &sf, int tr_size, int
     const SArr flt[2] = {{(uint32_t)__cvta_generic_to_shared(s.flt[0]) + 2u}, {(uint32_t)__cvta_generic_to_shared(s.flt[1]) + 2u}};
     SArr left = raw[0], top = raw[1];
 
-    const uint32_t src = c_ref_src[cand & 31];
     auto fetch = [&](int side, int i) -> int { return ref_fetch<n>(sf, src, side, i, tr_size, bl_size, bd); };
     for (int t = lane; t < 2 * n2; t += 32) {
         const int side = t >= n2, i = t - (side ? n2 : 0);
@@ -306,18 +311,18 @@ __device__ __forceinline__ void intra_pred_size(const Surf &sf, int tr_size, int
     __syncwarp();
 }
 
+// src: c_ref_src[cand & 31]
 template <typename Surf>
-__device__ __forceinline__ void intra_pred_tb(const Surf &sf, int tr_size, int bl_size, int log2_size, int c_idx, int mode, int cand,
+__device__ __forceinline__ void intra_pred_tb(const Surf &sf, uint32_t src, int tr_size, int bl_size, int log2_size, int c_idx, int mode,
                                               int filter_ok, int strong, int bd, IntraScratch &s, int lane, bool has_res = false)
 {
     switch (log2_size) {
-    case 2: intra_pred_small<2>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, bd, lane, has_res); break;
-    case 3: intra_pred_small<3>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, bd, lane, has_res); break;
-    case 4: intra_pred_size<4>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, has_res); break;
-    default: intra_pred_size<5>(sf, tr_size, bl_size, c_idx, mode, cand, filter_ok, strong, bd, s, lane, has_res); break;
+    case 2: intra_pred_small<2>(sf, src, tr_size, bl_size, c_idx, mode, filter_ok, bd, lane, has_res); break;
+    case 3: intra_pred_small<3>(sf, src, tr_size, bl_size, c_idx, mode, filter_ok, bd, lane, has_res); break;
+    case 4: intra_pred_size<4>(sf, src, tr_size, bl_size, c_idx, mode, filter_ok, strong, bd, s, lane, has_res); break;
+    default: intra_pred_size<5>(sf, src, tr_size, bl_size, c_idx, mode, filter_ok, strong, bd, s, lane, has_res); break;
     }
 }
-
 
 // ================================================================= frame level: CTBs in dependency order
 // hls_transform_unit predicts a block right before it adds the block's residual (hevcdec.c:1335-1526), in decoding
@@ -406,7 +411,7 @@ __global__ void __launch_bounds__(INTRA_THREADS) intra_kernel(const __grid_const
 #endif
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ IntraScratch scratch[3];
-    __shared__ ohcu_iu s_iu[INTRA_MAX_IU];
+    __shared__ __align__(16) uint4 s_blk[INTRA_MAX_IU];      // per block, prepared in parallel: see the record loop below
     __shared__ IntraTile tile[3];                          // (indexed by run-time plane numbers: not registers)
     __shared__ int rows[3], oy[3];
     __shared__ int s_ctb, s_need;
@@ -495,10 +500,22 @@ __global__ void __launch_bounds__(INTRA_THREADS) intra_kernel(const __grid_const
     for (int q = 0; q < 3; q++) {
         const uint32_t i = tid + q * INTRA_THREADS;
         if (i < ix.y) {
-            *(uint2 *)&s_iu[i] = rec[q];
-            const ohcu_iu u = s_iu[i];
+            union { uint2 w; ohcu_iu u; } cv;
+            cv.w = rec[q];
+            const ohcu_iu u = cv.u;
             const IntraTile &t = tile[u.c_idx];
             const int n = 1 << u.log2_size, bx = u.x0 & (t.sw - 1), by = u.y0 & (t.sh - 1);
+            // everything about the block that does not depend on samples, so that the chain of blocks starts from one load:
+            //   x  where its reference samples come from (c_ref_src)        y  offset of its first sample in the plane
+            //   z  bx | by << 8 | top-right run << 16 | bottom-left run << 24  (samples inside the picture, :109-112)
+            //   w  mode | log2 size << 8 | coded << 12 | plane << 16
+            {
+                const int c = u.c_idx, pw = f.pw[c], ph = f.ph[c];
+                const int tr = max(0, min(u.x0 + 2 * n, pw) - (u.x0 + n)), bl = max(0, min(u.y0 + 2 * n, ph) - (u.y0 + n));
+                s_blk[i] = make_uint4(c_ref_src[u.cand & 31], (uint32_t)u.y0 * (uint32_t)(f.work.pitch[c] / (int)sizeof(pixel)) + u.x0,
+                                      (uint32_t)bx | (uint32_t)by << 8 | (uint32_t)tr << 16 | (uint32_t)bl << 24,
+                                      (uint32_t)u.mode | (uint32_t)u.log2_size << 8 | ((u.cand & OHCU_IU_CBF) ? 1u << 12 : 0u) | (uint32_t)c << 16);
+            }
             if (bx == 0) {
                 if (u.cand & (CAND_L | CAND_BL)) need |= NEED_L;
                 if (u.cand & CAND_UL) need |= by ? NEED_L : NEED_UL;
@@ -566,22 +583,20 @@ __global__ void __launch_bounds__(INTRA_THREADS) intra_kernel(const __grid_const
     if (warp < f.nplanes) {
         const IntraTile &t = tile[warp];
         pixel *plane = (pixel *)f.work.p[warp];
-        const int pitch = f.work.pitch[warp] / (int)sizeof(pixel), pw = f.pw[warp], ph = f.ph[warp];
-        const int ox = cx * t.sw;
+        const int pitch = f.work.pitch[warp] / (int)sizeof(pixel);
         TileSurf<pixel> sf;
         sf.top_s = (uint32_t)__cvta_generic_to_shared(t.top); sf.body_off = (int)(t.body - t.top); sf.bpitch = t.bpitch; sf.pitch = pitch;
         sf.res_pitch = t.sw;
         const uint32_t res0 = (uint32_t)__cvta_generic_to_shared(t.res);
+        const int filt = warp ? filter_chroma : filter_luma;
         for (uint32_t i = 0; i < ix.y; i++) {
-            const ohcu_iu u = s_iu[i];
-            if (u.c_idx != warp) continue;
-            const int n = 1 << u.log2_size;
-            sf.bx = u.x0 - ox; sf.by = u.y0 - oy[warp];
-            sf.blk = plane + (size_t)u.y0 * pitch + u.x0;
+            const uint4 b = s_blk[i];
+            if ((int)(b.w >> 16) != warp) continue;
+            sf.bx = b.z & 255; sf.by = (b.z >> 8) & 255;
+            sf.blk = plane + b.y;
             sf.res_s = res0 + 2u * (uint32_t)(sf.by * t.sw + sf.bx);
-            intra_pred_tb(sf, max(0, min(u.x0 + 2 * n, pw) - (u.x0 + n)), max(0, min(u.y0 + 2 * n, ph) - (u.y0 + n)), u.log2_size,
-                          warp, u.mode, u.cand & 31, warp ? filter_chroma : filter_luma, f.strong_intra_smoothing, f.bd,
-                          scratch[warp], lane, (u.cand & OHCU_IU_CBF) != 0);
+            intra_pred_tb(sf, b.x, (int)((b.z >> 16) & 255), (int)(b.z >> 24), (int)((b.w >> 8) & 15), warp, (int)(b.w & 255), filt,
+                          f.strong_intra_smoothing, f.bd, scratch[warp], lane, (b.w >> 12) & 1);
         }
     }
     __syncthreads();                                       // every plane of the CTB is written
@@ -648,8 +663,8 @@ __global__ void dsp_intra_kernel(pixel *plane, int pitch, int pw, int ph, int x,
     const int n = 1 << log2_size;
     PlaneSurf<pixel> sf;
     sf.blk = plane + (size_t)y * pitch + x; sf.pitch = pitch;
-    intra_pred_tb(sf, max(0, min(x + 2 * n, pw) - (x + n)), max(0, min(y + 2 * n, ph) - (y + n)), log2_size, c_idx, mode, cand, filter_ok,
-                  strong, bd, s, threadIdx.x);
+    intra_pred_tb(sf, c_ref_src[cand & 31], max(0, min(x + 2 * n, pw) - (x + n)), max(0, min(y + 2 * n, ph) - (y + n)), log2_size, c_idx, mode,
+                  filter_ok, strong, bd, s, threadIdx.x);
 }
 
 int dsp_intra_pred(int bd, uint8_t *plane, ptrdiff_t stride, int pw, int ph, int x, int y, int log2_size, int c_idx, int mode, int cand,
